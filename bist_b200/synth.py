@@ -1,0 +1,143 @@
+"""Seeded synthetic AVSD-shaped inputs and weights for the BiST video hot path.
+
+Host-side harness code shared by tests/, bench.py, __graft_entry__.py and
+oracle/make_golden.py.  Everything is drawn from numpy's legacy ``RandomState`` streams
+(frozen by numpy's compatibility policy), so a (seed, shape) pair names the same tensors
+in the build container, on the GPU box and in the committed golden fixtures.
+
+Shapes and distributions follow SURVEY.md §8(d):
+  * ``fts`` ~ U[0,1) fp32 [B,T,S,D] (ResNeXt post-ReLU features are non-negative), with a
+    per-sample valid length T_i ~ U{ceil(T/2)..T} (T_0 = T) and clips t >= T_i zeroed, so
+    that ``temporal_mask = fts.sum(2).sum(-1) != 0`` reproduces data/dataset.py:79;
+  * token ids ~ U{4..V-1}, pad id 1 on the tail, lengths ~ U{ceil(L/2)..L} (first = L);
+  * weights: xavier-uniform matrices (mtn.py:163-165), biases N(0, 0.02), LayerNorm
+    gains 1 + N(0, 0.1) and offsets N(0, 0.1) so every affine path is exercised.
+"""
+import math
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+PAD_ID = 1  # data/dataset.py collate_fn pads with 1
+
+
+class SynthBatch(SimpleNamespace):
+    """Duck-typed stand-in for data/dataset.py:59 ``Batch`` (only the fields the path reads)."""
+
+    def to(self, device, non_blocking=False):
+        out = SynthBatch()
+        for k, v in self.__dict__.items():
+            setattr(out, k, v.to(device, non_blocking=non_blocking) if torch.is_tensor(v) else v)
+        return out
+
+
+def make_batch(seed, B, T, S, D, Lq, vocab=4096, full_clips=False, full_query=False):
+    """Seeded batch with the fields of SURVEY.md §8(b): fts, temporal_mask, query, query_mask."""
+    rs = np.random.RandomState(seed)
+    fts = rs.uniform(0.0, 1.0, size=(B, T, S, D)).astype(np.float32)
+    t_len = rs.randint(int(math.ceil(T / 2)), T + 1, size=B)
+    t_len[0] = T
+    q_len = rs.randint(int(math.ceil(Lq / 2)), Lq + 1, size=B)
+    q_len[0] = Lq
+    if full_clips:
+        t_len[:] = T
+    if full_query:
+        q_len[:] = Lq
+    for i in range(B):
+        fts[i, t_len[i]:] = 0.0
+    query = rs.randint(4, vocab, size=(B, Lq)).astype(np.int64)
+    for i in range(B):
+        query[i, q_len[i]:] = PAD_ID
+    b = SynthBatch()
+    b.fts = torch.from_numpy(fts)
+    b.query = torch.from_numpy(query)
+    b.query_mask = (b.query != PAD_ID).unsqueeze(-2)                  # dataset.py:66
+    b.temporal_mask = (b.fts.sum(2).sum(-1) != 0).unsqueeze(-2)       # dataset.py:79
+    b.spatial_mask = (b.fts.sum(1).sum(-1) != 0).unsqueeze(-2)        # dataset.py:78 (unused by the path)
+    b.t_len = torch.from_numpy(t_len.astype(np.int64))
+    b.q_len = torch.from_numpy(q_len.astype(np.int64))
+    return b
+
+
+def make_encoded_query(seed, B, Lq, d):
+    """Stand-in for ft['encoded_query'] (= LayerNorm of scaled embeddings + PE): N(0,1)."""
+    rs = np.random.RandomState(seed + 7919)
+    return torch.from_numpy(rs.standard_normal(size=(B, Lq, d)).astype(np.float32))
+
+
+def _xavier(rs, out_f, in_f):
+    a = math.sqrt(6.0 / (in_f + out_f))
+    return rs.uniform(-a, a, size=(out_f, in_f)).astype(np.float32)
+
+
+def _bias(rs, n):
+    return (0.02 * rs.standard_normal(size=(n,))).astype(np.float32)
+
+
+def _ln(rs, P, pre, n):
+    P[pre + "a_2"] = (1.0 + 0.1 * rs.standard_normal(size=(n,))).astype(np.float32)
+    P[pre + "b_2"] = (0.1 * rs.standard_normal(size=(n,))).astype(np.float32)
+
+
+def _mha(rs, P, pre, d):
+    for i in range(4):
+        P[f"{pre}linears.{i}.weight"] = _xavier(rs, d, d)
+        P[f"{pre}linears.{i}.bias"] = _bias(rs, d)
+
+
+def _ffn(rs, P, pre, d, d_ff):
+    P[pre + "w_1.weight"] = _xavier(rs, d_ff, d)
+    P[pre + "w_1.bias"] = _bias(rs, d_ff)
+    P[pre + "w_2.weight"] = _xavier(rs, d, d_ff)
+    P[pre + "w_2.bias"] = _bias(rs, d)
+
+
+def layer_param_names(nb_attn, nb_ff):
+    """state_dict key suffixes of one VidEncoderLayer4 (SURVEY.md §8(a) parameter list)."""
+    names = []
+    for a in range(nb_attn):
+        for i in range(4):
+            names += [f"attn.{a}.linears.{i}.weight", f"attn.{a}.linears.{i}.bias"]
+    for f in range(nb_ff):
+        names += [f"ff.{f}.w_1.weight", f"ff.{f}.w_1.bias", f"ff.{f}.w_2.weight", f"ff.{f}.w_2.bias"]
+    for s in range(nb_attn + nb_ff):
+        names += [f"sublayer.{s}.norm.a_2", f"sublayer.{s}.norm.b_2"]
+    return names
+
+
+def make_params(seed, d, D, n_blocks, t2s=True, s2t=True, d_ff=None,
+                enc_pre="vid_encoder.", dec_pre="mutlimodal_decoder."):
+    """Video-path parameters keyed exactly like the reference ``MTN.state_dict()``.
+
+    Returns dict[str, torch.FloatTensor] (CPU).  With one direction off the layer has
+    3 attn / 1 ff / 4 sublayer clones (mtn.py:123-128).
+    """
+    rs = np.random.RandomState(seed + 104729)
+    d_ff = d_ff or 4 * d                                               # mtn.py:70
+    nb_attn, nb_ff = (6, 2) if (t2s and s2t) else (3, 1)
+    P = {}
+    P[enc_pre + "W.weight"] = _xavier(rs, d, D)
+    P[enc_pre + "W.bias"] = _bias(rs, d)
+    _ln(rs, P, enc_pre + "in_norm.", d)
+    for blk in range(n_blocks):
+        pre = f"{dec_pre}v_layers.{blk}."
+        for a in range(nb_attn):
+            _mha(rs, P, f"{pre}attn.{a}.", d)
+        for f in range(nb_ff):
+            _ffn(rs, P, f"{pre}ff.{f}.", d, d_ff)
+        for s in range(nb_attn + nb_ff):
+            _ln(rs, P, f"{pre}sublayer.{s}.norm.", d)
+    _ln(rs, P, dec_pre + "spatial_out_norm.", d)
+    _ln(rs, P, dec_pre + "temporal_out_norm.", d)
+    return {k: torch.from_numpy(v) for k, v in P.items()}
+
+
+def shard_rows(n_rows, world_size, rank):
+    """Contiguous, balanced split of ``n_rows`` dialogue turns over ranks.
+
+    Returns (start, stop).  The first ``n_rows % world_size`` ranks get one extra row.
+    """
+    base, rem = divmod(n_rows, world_size)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)

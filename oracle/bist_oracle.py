@@ -1,0 +1,208 @@
+"""CPU oracle for the BiST video hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file is a functional (no nn.Module, no state) restatement, on plain torch CPU
+tensors, of the reference algorithm for the path named in BASELINE.json:
+
+    VidEncoder8.forward            /root/reference/model/encoder.py:72-93
+    VidEncoderLayer4.forward       /root/reference/model/encoder.py:172-201
+      .temporal2spatial            /root/reference/model/encoder.py:109-139
+      .spatial2temporal            /root/reference/model/encoder.py:141-170
+    LayerNorm / SublayerConnection / attention / MultiHeadedAttention /
+    PositionwiseFeedForward        /root/reference/model/modules.py:20-113
+    output norms                   /root/reference/model/decoder.py:107-129
+
+It deliberately keeps the reference's *formulation* (query block copied S or T times,
+K/V projections of every video row, materialised score tensors) so that (a) it is an
+independent check of the re-associated CUDA path and (b) its CPU timing is
+representative of the reference's own CPU path (bench.py `cpu_baseline`, kind="port").
+
+Who may use it: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+`--impl reference` legs.  The product package `bist_b200` never imports it.
+
+How it is pinned (the reference ships no tests or golden vectors):
+  * tests/golden/*.npz were produced by running the UNMODIFIED reference modules
+    (imported from /root/reference in the build container) on seeded inputs; the
+    generating script is oracle/make_golden.py; tests/test_oracle.py checks this
+    oracle against every fixture (fp32, <=2e-6 normalised error).
+  * when /root/reference is present (build container only) tests/test_oracle.py also
+    runs the live reference beside the oracle on fresh random shapes.
+
+All parameters are passed as a flat dict using the reference's state_dict key names,
+so a reference `state_dict()` can be fed in unchanged.
+"""
+import math
+
+import torch
+
+__all__ = [
+    "layer_norm", "linear", "sdp_attention", "mha", "ffn", "sublayer",
+    "vid_encoder8", "temporal2spatial", "spatial2temporal", "vid_encoder_layer4",
+    "video_path", "norm_err",
+]
+
+
+def norm_err(a, b):
+    """Parity metric of SURVEY.md §8(c): max|a-b| / max|b| (b = reference)."""
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+# ----------------------------------------------------------------------------- blocks
+def layer_norm(x, a_2, b_2, eps=1e-6):
+    """modules.py:28-31 — unbiased std (divide by d-1); eps is added to the std."""
+    mu = x.mean(dim=-1, keepdim=True)
+    sd = x.std(dim=-1, keepdim=True)          # torch default: Bessel-corrected
+    return a_2 * (x - mu) / (sd + eps) + b_2
+
+
+def linear(x, w, b=None):
+    """nn.Linear: x @ w.T + b."""
+    y = x.matmul(w.t())
+    return y if b is None else y + b
+
+
+def sdp_attention(q, k, v, mask=None):
+    """modules.py:54-64 (dropout is identity in eval).  mask==0 -> score := -1e9."""
+    s = q.matmul(k.transpose(-2, -1)) / math.sqrt(q.shape[-1])
+    if mask is not None:
+        s = s.masked_fill(mask == 0, -1e9)
+    p = torch.softmax(s, dim=-1)
+    return p.matmul(v), p
+
+
+def mha(P, pre, h, query, key, value, mask=None):
+    """modules.py:81-100.  P[pre+'linears.{0..3}.{weight,bias}'].  Returns (out, attn)."""
+    if mask is not None:
+        mask = mask.unsqueeze(1)                                   # :85 same mask for all heads
+    nb = query.shape[0]
+    d_model = P[pre + "linears.0.weight"].shape[0]
+    dk = d_model // h
+
+    def split(i, x):
+        y = linear(x, P[pre + f"linears.{i}.weight"], P[pre + f"linears.{i}.bias"])
+        return y.view(nb, -1, h, dk).transpose(1, 2)               # :89-91
+
+    q, k, v = split(0, query), split(1, key), split(2, value)
+    ctx, p = sdp_attention(q, k, v, mask)                          # :94
+    ctx = ctx.transpose(1, 2).contiguous().view(nb, -1, h * dk)    # :98-99
+    return linear(ctx, P[pre + "linears.3.weight"], P[pre + "linears.3.bias"]), p
+
+
+def ffn(P, pre, x):
+    """modules.py:112-113 (dropout identity)."""
+    hid = torch.relu(linear(x, P[pre + "w_1.weight"], P[pre + "w_1.bias"]))
+    return linear(hid, P[pre + "w_2.weight"], P[pre + "w_2.bias"])
+
+
+def sublayer(P, pre, x, fn):
+    """modules.py:42-44: x + sublayer(norm(x)); only x is normed."""
+    return x + fn(layer_norm(x, P[pre + "norm.a_2"], P[pre + "norm.b_2"]))
+
+
+# ----------------------------------------------------------------------------- a1
+def vid_encoder8(P, pre, fts, audio_fts=None, no_w_audio=False):
+    """encoder.py:72-93.  Returns (spatiotemporal_ft, encoded_audio-or-None).
+
+    vid_position is always None in the reference (mtn.py:108), so :76-79 never runs.
+    """
+    out = torch.relu(linear(fts, P[pre + "W.weight"], P[pre + "W.bias"]))          # :75
+    out = layer_norm(out, P[pre + "in_norm.a_2"], P[pre + "in_norm.b_2"])          # :80
+    aud = None
+    if audio_fts is not None:
+        aud = audio_fts if no_w_audio else torch.relu(
+            linear(audio_fts, P[pre + "a_W.weight"], P[pre + "a_W.bias"]))         # :84-87
+        aud = layer_norm(aud, P[pre + "a_in_norm.a_2"], P[pre + "a_in_norm.b_2"])  # :90
+    return out, aud
+
+
+# ----------------------------------------------------------------------------- a3 / a4
+def temporal2spatial(P, pre, h, x, vft, temporal_mask, ai, fi, si):
+    """encoder.py:109-139.  x [B,Lq,d]; vft [B,T,S,d]; temporal_mask [B,1,T] bool.
+
+    ai/fi/si = indices of the first attn / ff / sublayer clone used (reference keeps
+    them as mutable cursors, encoder.py:122-137).
+    """
+    B, T, S, d = vft.shape
+    Lq = x.shape[1]
+    kv = vft.permute(0, 2, 1, 3).reshape(B * S, T, d)                              # :111-112
+    xe = x.unsqueeze(1).expand(B, S, Lq, d).reshape(B * S, Lq, d)                  # :114-115
+    me = temporal_mask.unsqueeze(1).expand(B, S, 1, T).reshape(B * S, 1, T)        # :117-119
+    t_out = sublayer(P, f"{pre}sublayer.{si}.", xe,
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, me)[0])    # :121
+    kv2 = t_out.reshape(B, S, Lq, d).permute(0, 2, 1, 3).reshape(B * Lq, S, d)     # :125-126
+    x1 = x.reshape(B * Lq, 1, d)                                                   # :128
+    ts = sublayer(P, f"{pre}sublayer.{si + 1}.", x1,
+                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, None)[0])  # :130
+    ts = ts.reshape(B, Lq, d)                                                      # :134
+    return sublayer(P, f"{pre}sublayer.{si + 2}.", ts,
+                    lambda z: ffn(P, f"{pre}ff.{fi}.", z))                         # :135
+
+
+def spatial2temporal(P, pre, h, x, vft, temporal_mask, ai, fi, si):
+    """encoder.py:141-170 (mirror order: over S per clip without mask, then over T with mask)."""
+    B, T, S, d = vft.shape
+    Lq = x.shape[1]
+    kv = vft.reshape(B * T, S, d)                                                  # :143
+    xe = x.unsqueeze(1).expand(B, T, Lq, d).reshape(B * T, Lq, d)                  # :145-146
+    s_out = sublayer(P, f"{pre}sublayer.{si}.", xe,
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, None)[0])  # :148
+    kv2 = s_out.reshape(B, T, Lq, d).permute(0, 2, 1, 3).reshape(B * Lq, T, d)     # :152-153
+    x1 = x.reshape(B * Lq, 1, d)                                                   # :155
+    me = temporal_mask.unsqueeze(1).expand(B, Lq, 1, T).reshape(B * Lq, 1, T)      # :157-159
+    st = sublayer(P, f"{pre}sublayer.{si + 1}.", x1,
+                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, me)[0])  # :161
+    st = st.reshape(B, Lq, d)                                                      # :165
+    return sublayer(P, f"{pre}sublayer.{si + 2}.", st,
+                    lambda z: ffn(P, f"{pre}ff.{fi}.", z))                         # :166
+
+
+# ----------------------------------------------------------------------------- a2
+def vid_encoder_layer4(P, pre, h, in_t2s, in_s2t, vft, query_mask, temporal_mask,
+                       t2s=True, s2t=True):
+    """encoder.py:172-201 with enc_st_combine == 'none'.  Returns (t2s_out, s2t_out).
+
+    Clone indexing follows the reference cursors: with both directions on, t2s uses
+    attn 0-2 / ff 0 / sublayer 0-3 and s2t uses attn 3-5 / ff 1 / sublayer 4-7; with one
+    direction off the surviving one uses attn 0-2 / ff 0 / sublayer 0-3.
+    """
+    ai = fi = si = 0
+    o_t2s, o_s2t = in_t2s, in_s2t
+    if t2s:
+        x = sublayer(P, f"{pre}sublayer.{si}.", in_t2s,
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, z, z, query_mask)[0])  # :176
+        o_t2s = temporal2spatial(P, pre, h, x, vft, temporal_mask, ai + 1, fi, si + 1)  # :179
+        ai, fi, si = ai + 3, fi + 1, si + 4
+    if s2t:
+        a0, f0, s0 = ai, fi, si
+        x = sublayer(P, f"{pre}sublayer.{s0}.", in_s2t,
+                     lambda z: mha(P, f"{pre}attn.{a0}.", h, z, z, z, query_mask)[0])  # :184
+        o_s2t = spatial2temporal(P, pre, h, x, vft, temporal_mask, a0 + 1, f0, s0 + 1)  # :187
+    return o_t2s, o_s2t
+
+
+# ----------------------------------------------------------------------------- a1 + L x a2 + a10
+def video_path(P, h, fts, encoded_query, query_mask, temporal_mask, n_blocks,
+               t2s=True, s2t=True,
+               enc_pre="vid_encoder.", dec_pre="mutlimodal_decoder."):
+    """The slice of MTN.forward that is the hot path (mtn.py:49-51, decoder.py:107-129).
+
+    Returns dict(spatiotemporal_ft, t2s, s2t, temporal_ft, spatial_ft) where t2s/s2t are
+    the raw streams after the last block and temporal_ft/spatial_ft their output norms
+    (decoder.py:126-129; overwritten every block, so only the last block's survive).
+    """
+    vft, _ = vid_encoder8(P, enc_pre, fts)
+    cur_t2s = cur_s2t = encoded_query                                              # decoder.py:109-110
+    out = {"spatiotemporal_ft": vft}
+    for blk in range(n_blocks):
+        cur_t2s, cur_s2t = vid_encoder_layer4(
+            P, f"{dec_pre}v_layers.{blk}.", h, cur_t2s, cur_s2t, vft,
+            query_mask, temporal_mask, t2s=t2s, s2t=s2t)                           # decoder.py:116
+    out["t2s"], out["s2t"] = cur_t2s, cur_s2t
+    if s2t:
+        out["temporal_ft"] = layer_norm(cur_s2t, P[dec_pre + "temporal_out_norm.a_2"],
+                                        P[dec_pre + "temporal_out_norm.b_2"])      # decoder.py:127
+    if t2s:
+        out["spatial_ft"] = layer_norm(cur_t2s, P[dec_pre + "spatial_out_norm.a_2"],
+                                       P[dec_pre + "spatial_out_norm.b_2"])        # decoder.py:129
+    return out

@@ -1,0 +1,169 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (TEST INFRASTRUCTURE).
+
+Run in the build container only (needs /root/reference):
+
+    python oracle/make_golden.py            # rewrites tests/golden/
+
+For every case below the reference model is built with ``model.mtn.make_model``
+(/root/reference/model/mtn.py:63-167), its video-path parameters are overwritten with the
+seeded values of ``bist_b200.synth.make_params`` (checked to be a key-for-key, shape-for-shape
+subset of the reference ``state_dict``), and the hot path is driven exactly as
+``MultimodalDecoder8.forward`` drives it (/root/reference/model/decoder.py:107-129).  Only the
+case description (seeds + shapes) and the reference OUTPUTS are stored; inputs and weights
+are regenerated from the seeds by the tests, which keeps the fixtures small.
+
+A second fixture (modules.npz) pins the generic blocks of model/modules.py
+(LayerNorm, MultiHeadedAttention incl. ``.attn``, PositionwiseFeedForward,
+SublayerConnection) on their own.
+"""
+import argparse
+import json
+import os
+import sys
+import types
+import warnings
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+REF = os.environ.get("BIST_REFERENCE", "/root/reference")
+
+from bist_b200 import synth  # noqa: E402
+
+CASES = {
+    # name: dict(seed, B, T, S, D, d, h, Lq, n_blocks, t2s, s2t [, full_clips])
+    "both_small":  dict(seed=11, B=3, T=5, S=4, D=96, d=64, h=4, Lq=6, n_blocks=2, t2s=1, s2t=1),
+    "t2s_only":    dict(seed=12, B=2, T=4, S=3, D=80, d=64, h=4, Lq=5, n_blocks=2, t2s=1, s2t=0),
+    "s2t_only":    dict(seed=13, B=2, T=4, S=3, D=80, d=64, h=4, Lq=5, n_blocks=2, t2s=0, s2t=1),
+    "lq1_ragged":  dict(seed=14, B=2, T=3, S=7, D=40, d=32, h=2, Lq=1, n_blocks=1, t2s=1, s2t=1),
+    "exec_sh_d128": dict(seed=15, B=2, T=6, S=16, D=256, d=128, h=8, Lq=5, n_blocks=1, t2s=1, s2t=1),
+    "long_video":  dict(seed=16, B=1, T=33, S=49, D=64, d=64, h=8, Lq=3, n_blocks=1, t2s=1, s2t=1),
+    "cfg1_d512":   dict(seed=17, B=4, T=8, S=16, D=2048, d=512, h=8, Lq=16, n_blocks=3, t2s=1, s2t=1),
+}
+
+
+def import_reference():
+    """Import /root/reference unmodified; stub the absent, unused ``nltk``."""
+    if not os.path.isdir(REF):
+        raise SystemExit(f"reference tree not found at {REF}")
+    nltk = types.ModuleType("nltk")
+    nltk_util = types.ModuleType("nltk.util")
+    nltk_util.ngrams = lambda *a, **k: []
+    nltk.util = nltk_util
+    sys.modules.setdefault("nltk", nltk)
+    sys.modules.setdefault("nltk.util", nltk_util)
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    warnings.filterwarnings("ignore")
+    import model.mtn as mtn            # noqa
+    import model.modules as modules    # noqa
+    return mtn, modules
+
+
+def ref_args(c):
+    return argparse.Namespace(
+        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=0, nb_aenc_blocks=0,
+        d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft="query", auto_encoder=0,
+        t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none", enc_vc_combine="none",
+        dec_st_combine="seq", include_caption="none", mask_unk=1)
+
+
+def run_reference_case(mtn, c):
+    torch.manual_seed(0)
+    model = mtn.make_model(64, 64, ref_args(c), ft_sizes=[c["D"]]).eval()
+    P = synth.make_params(c["seed"], c["d"], c["D"], c["n_blocks"], bool(c["t2s"]), bool(c["s2t"]))
+    sd = model.state_dict()
+    for k, v in P.items():                       # pins the parameter names and shapes (§8(b))
+        assert k in sd, f"{k} is not a reference state_dict key"
+        assert tuple(sd[k].shape) == tuple(v.shape), (k, sd[k].shape, v.shape)
+    vid_keys = [k for k in sd if k.startswith("vid_encoder.") or ".v_layers." in k
+                or "spatial_out_norm" in k or "temporal_out_norm" in k]
+    assert sorted(vid_keys) == sorted(P.keys()), "synth.make_params must cover the whole video path"
+    model.load_state_dict(P, strict=False)
+
+    b = synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"])
+    eq = synth.make_encoded_query(c["seed"], c["B"], c["Lq"], c["d"])
+    out = {}
+    with torch.no_grad():
+        ft = {"encoded_query": eq}
+        ft = model.vid_encoder(b, ft)                                 # mtn.py:49-51
+        dec = model.mutlimodal_decoder
+        in_ft = {"t2s": eq, "s2t": eq}                                # decoder.py:109-110
+        for blk in range(c["n_blocks"]):
+            in_ft = dec.v_layers[blk](in_ft, ft, b)                   # decoder.py:116
+            if c["t2s"]:
+                out[f"t2s_{blk}"] = in_ft["t2s"].numpy().copy()
+            if c["s2t"]:
+                out[f"s2t_{blk}"] = in_ft["s2t"].numpy().copy()
+        if c["s2t"]:
+            out["temporal_ft"] = dec.temporal_out_norm(in_ft["s2t"]).numpy()   # decoder.py:127
+        if c["t2s"]:
+            out["spatial_ft"] = dec.spatial_out_norm(in_ft["t2s"]).numpy()     # decoder.py:129
+    vft = ft["spatiotemporal_ft"].numpy()
+    if vft.size > 200_000:                       # keep the fixture small: strided sample
+        out["vft_sample"] = vft[:, ::3, ::5, :].copy()
+        out["vft_stride"] = np.array([3, 5])
+    else:
+        out["vft_sample"] = vft
+        out["vft_stride"] = np.array([1, 1])
+    return out
+
+
+def run_modules_fixture(modules):
+    """Generic blocks of model/modules.py on their own."""
+    rs = np.random.RandomState(99)
+    d, h, Bp, Lq, Lk, dff = 48, 4, 3, 5, 7, 96
+    out = {"meta": np.array(json.dumps(dict(d=d, h=h, Bp=Bp, Lq=Lq, Lk=Lk, dff=dff)))}
+    x = torch.from_numpy(rs.standard_normal((Bp, Lq, d)).astype(np.float32))
+    kv = torch.from_numpy(rs.standard_normal((Bp, Lk, d)).astype(np.float32))
+    mask_k = torch.from_numpy(rs.uniform(size=(Bp, 1, Lk)) > 0.3)
+    mask_k[:, :, 0] = True
+    mask_qk = torch.from_numpy(rs.uniform(size=(Bp, Lq, Lk)) > 0.3)
+    mask_qk[:, :, 0] = True
+    mask_qk[1, 2, :] = False                      # a fully masked row -> uniform probabilities
+    out.update(x=x.numpy(), kv=kv.numpy(), mask_k=mask_k.numpy(), mask_qk=mask_qk.numpy())
+
+    ln = modules.LayerNorm(d)
+    att = modules.MultiHeadedAttention(h, d).eval()
+    ff = modules.PositionwiseFeedForward(d, dff).eval()
+    sc = modules.SublayerConnection(d, 0.1).eval()
+    with torch.no_grad():
+        for name, m in (("ln", ln), ("att", att), ("ff", ff), ("sc", sc)):
+            for k, p in m.state_dict().items():
+                v = rs.standard_normal(tuple(p.shape)).astype(np.float32) * (0.2 if p.dim() > 1 else 0.1)
+                if k.endswith("a_2"):
+                    v = 1.0 + v
+                p.copy_(torch.from_numpy(v))
+                out[f"{name}.{k}"] = v
+        out["ln_out"] = ln(x).numpy()
+        out["att_out_k"] = att(x, kv, kv, mask_k).numpy()
+        out["att_p_k"] = att.attn.numpy().copy()
+        out["att_out_qk"] = att(x, kv, kv, mask_qk).numpy()
+        out["att_p_qk"] = att.attn.numpy().copy()
+        out["att_out_nomask"] = att(x, kv, kv, None).numpy()
+        out["ff_out"] = ff(x).numpy()
+        out["sc_out"] = sc(x, ff).numpy()
+    return out
+
+
+def main():
+    mtn, modules = import_reference()
+    gold = os.path.join(ROOT, "tests", "golden")
+    os.makedirs(gold, exist_ok=True)
+    for name, c in CASES.items():
+        out = run_reference_case(mtn, c)
+        out["meta"] = np.array(json.dumps(c))
+        path = os.path.join(gold, f"path_{name}.npz")
+        np.savez_compressed(path, **out)
+        print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")
+    path = os.path.join(gold, "modules.npz")
+    np.savez_compressed(path, **run_modules_fixture(modules))
+    print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")
+
+
+if __name__ == "__main__":
+    main()
