@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py — BiST video-encoder forward throughput on B200 (BASELINE.json configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W [--precision bf16|fp32] [--impl ours|reference]
+
+A step is one forward of the hot path (VidEncoder8 projection + 3 x VidEncoderLayer4 + output
+norms) over one synthetic batch of B=64 dialogue turns, T=40 clips, S=16 regions, D=2048,
+d_model=512, Lq=16.  One process per GPU; for N>1 every rank runs its own batch of 64 turns
+(dialogue turns are independent, no data-path collective; weak scaling) and the time is the max
+over ranks.  Prints ONE JSON line on rank 0 (contract in the task statement):
+  value     turns/s with inputs resident in HBM
+  e2e       turns/s through the public module API with pinned HOST inputs, H2D and D2H inside
+  roofline  dominant kernel, per-launch CUDA-event time from the library's profiling hooks
+  cpu_baseline  the CPU oracle (port of the reference formulation) on this box's host cores
+`--impl reference` times that CPU oracle alone on the same config (the reference is pure
+Python/PyTorch and /root/reference does not travel to the GPU box; oracle/bist_oracle.py keeps
+the reference's formulation op for op).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+CFG = dict(B=64, T=40, S=16, D=2048, d=512, h=8, Lq=16, n_blocks=3)
+WORKLOAD = "BiST video encoder forward (VidEncoder8 + 3x VidEncoderLayer4 s2t+t2s + out norms), B=64 T=40 S=16 D=2048 d_model=512 Lq=16"
+METRIC, UNIT = "dialogue_turns_per_sec", "turns/s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return dict(hbm=j["hbm_gbs"], tc_burst=j["bf16_tflops"], tc_sust=j["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tc_burst=1590.0, tc_sust=1400.0, src="fallback")
+
+
+def algorithmic_bytes(c, e_act):
+    """fts read (fp32) + vft write + one vft read per block + weights + query streams."""
+    N, Q, d, D, L = c["B"] * c["T"] * c["S"], c["B"] * c["Lq"], c["d"], c["D"], c["n_blocks"]
+    return N * D * 4 + N * d * e_act + L * N * d * e_act + (D * d + 40 * L * d * d) * e_act + (1 + 2 * L) * 2 * Q * d * 4
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 100 ms during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_oracle_turns_per_sec(c, rows, reps, threads):
+    """Time the CPU oracle (reference formulation) on `rows` dialogue turns of the workload."""
+    from bist_b200 import synth
+    from oracle import bist_oracle as O
+    torch.set_num_threads(threads)
+    P = synth.make_params(0, c["d"], c["D"], c["n_blocks"])
+    b = synth.make_batch(1, rows, c["T"], c["S"], c["D"], c["Lq"])
+    eq = synth.make_encoded_query(1, rows, c["Lq"], c["d"])
+    best = float("inf")
+    with torch.no_grad():
+        for i in range(reps + 1):          # first pass is the warm-up
+            t0 = time.perf_counter()
+            O.video_path(P, c["h"], b.fts, eq, b.query_mask, b.temporal_mask, c["n_blocks"])
+            dt = time.perf_counter() - t0
+            if i > 0:
+                best = min(best, dt)
+    return rows / best, best
+
+
+def kernel_model(c, e_act, nd=2):
+    """Algorithmic flops / bytes PER LAUNCH of the tagged kernels."""
+    B, T, S, D, d, h, Lq = c["B"], c["T"], c["S"], c["D"], c["d"], c["h"], c["Lq"]
+    N, TS, Q = B * T * S, T * S, B * Lq
+    gavg = (S + T) / 2.0
+    return {
+        "vidproj_gemm": (2.0 * N * D * d, N * D * 4 + d * D * e_act + N * d * 4),
+        "vidproj_fused": (2.0 * N * D * d, N * D * 4 + d * D * e_act + N * d * e_act),
+        "xv_gemm": (2.0 * N * d * nd * d, N * d * e_act + nd * d * d * e_act + N * nd * d * e_act),
+        "scores1_gemm": (2.0 * B * Lq * h * TS * d, N * d * e_act + Q * h * d * 4 + B * Lq * h * TS * 4),
+        "o1_gemm": (2.0 * B * gavg * Lq * d * d, 2 * B * gavg * Lq * d * e_act + d * d * e_act + Q * d * 4),
+    }
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    rows = 16
+    from bist_b200 import synth
+    from oracle import bist_oracle as O
+    torch.set_num_threads(threads)
+    c = CFG
+    P = synth.make_params(0, c["d"], c["D"], c["n_blocks"])
+    b = synth.make_batch(1, rows, c["T"], c["S"], c["D"], c["Lq"])
+    eq = synth.make_encoded_query(1, rows, c["Lq"], c["d"])
+    times = []
+    with torch.no_grad():
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            O.video_path(P, c["h"], b.fts, eq, b.query_mask, b.temporal_mask, c["n_blocks"])
+            if i >= args.warmup:
+                times.append(time.perf_counter() - t0)
+    total = sum(times)
+    v = rows * len(times) / total
+    sample = "%d of the %d dialogue turns of the workload per step, fp32, torch CPU, %d threads" % (rows, c["B"], threads)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "rows_per_step": rows},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from bist_b200 import VideoPath, _lib, synth
+    L = _lib.lib()
+    _lib.check(L.bist_device_check(), "bist_device_check")
+    c = CFG
+    e_act = 2 if args.precision == "bf16" else 4
+    model = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], precision=args.precision).to(dev)
+    model.load_state_dict(synth.make_params(0, c["d"], c["D"], c["n_blocks"]), strict=True)
+    hb = synth.make_batch(1 + rank, c["B"], c["T"], c["S"], c["D"], c["Lq"])
+    heq = synth.make_encoded_query(1 + rank, c["B"], c["Lq"], c["d"]).pin_memory()
+    hb.fts, hb.query_mask, hb.temporal_mask = hb.fts.pin_memory(), hb.query_mask.pin_memory(), hb.temporal_mask.pin_memory()
+    db, deq = hb.to(dev), heq.to(dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident throughput -----------------------------------------------------------
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 3)):
+            model(db, deq)
+        sampler = ClockSampler(local)
+        n0 = L.bist_launch_count()
+        ms_total = timed(lambda: model(db, deq), args.steps)
+        launches = L.bist_launch_count() - n0
+        clocks = sampler.stop()
+        ms_step = ms_total / args.steps
+        value = world * c["B"] / (ms_step * 1e-3)
+
+        # ---- end to end: pinned host inputs -> H2D -> forward -> D2H of the encoder outputs ------
+        out_t = torch.empty((c["B"], c["Lq"], c["d"]), dtype=torch.float32).pin_memory()
+        out_s = torch.empty_like(out_t).pin_memory()
+
+        def e2e_step():
+            b = hb.to(dev, non_blocking=True)
+            eq = heq.to(dev, non_blocking=True)
+            ft = model(b, eq)
+            out_t.copy_(ft["temporal_ft"], non_blocking=True)
+            out_s.copy_(ft["spatial_ft"], non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        e2e_ms = timed(e2e_step, args.steps) / args.steps
+        h2d = hb.fts.numel() * 4 + hb.query_mask.numel() + hb.temporal_mask.numel() + hb.query.numel() * 8 + \
+            hb.spatial_mask.numel() + hb.t_len.numel() * 8 + hb.q_len.numel() * 8 + heq.numel() * 4
+        d2h = 2 * out_t.numel() * 4
+
+        # ---- per-kernel CUDA-event times (library hooks), separate pass --------------------------
+        torch.cuda.synchronize()
+        L.bist_prof_enable(1)
+        prof_steps = min(args.steps, 5)
+        for _ in range(prof_steps):
+            model(db, deq)
+        import ctypes
+        buf = ctypes.create_string_buffer(1 << 16)
+        _lib.check(L.bist_prof_collect(buf, len(buf)), "bist_prof_collect")
+        L.bist_prof_enable(0)
+    kern = {}
+    for ln in buf.value.decode().strip().splitlines():
+        tag, n, tot = ln.split(",")
+        kern[tag] = {"launches_per_step": int(n) / prof_steps, "ms_per_step": float(tot) / prof_steps,
+                     "us_per_launch": 1e3 * float(tot) / int(n)}
+    peaks = load_peaks()
+    km = kernel_model(c, e_act)
+    total_k = sum(v["ms_per_step"] for v in kern.values()) or 1.0
+    top = max(kern, key=lambda t: kern[t]["ms_per_step"]) if kern else None
+    roof = None
+    if top in km:
+        fl, by = km[top]
+        sec = kern[top]["us_per_launch"] * 1e-6
+        ridge = peaks["tc_sust"] * 1e12 / (peaks["hbm"] * 1e9)
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(args.precision, {}).get(top)
+        if fl / by > ridge:
+            a, p = fl / sec / 1e12, peaks["tc_sust"]
+            roof = {"bound": "tensor", "achieved": a, "peak": p, "unit": "TFLOP/s", "frac": a / p, "traffic": traffic}
+        else:
+            a, p = by / sec / 1e9, peaks["hbm"]
+            roof = {"bound": "hbm", "achieved": a, "peak": p, "unit": "GB/s", "frac": a / p, "traffic": traffic}
+        roof.update({"kernel": top, "us_per_launch": kern[top]["us_per_launch"], "share_of_step": kern[top]["ms_per_step"] / total_k,
+                     "peak_source": peaks["src"] + " (sustained bf16 / copy bandwidth)"})
+    whole = algorithmic_bytes(c, e_act) / (ms_step * 1e-3) / 1e9
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, best = cpu_oracle_turns_per_sec(c, 16, 3, threads)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": "16 of the 64 dialogue turns, best of 3 after 1 warm-up (%.2f s each), fp32 torch CPU" % best}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "turns_per_gpu": c["B"], "precision": args.precision,
+                           "l2": "inputs larger than L2 (335 MB fts read per step vs 126 MB L2), no explicit flush",
+                           "parallelism": "dialogue turns sharded over %d GPU(s), no collective" % world},
+                "clocks": clocks,
+                "e2e": {"value": world * c["B"] / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": int(launches),
+                "roofline": roof,
+                "encoder_algorithmic_gbs": whole, "encoder_frac_of_hbm_peak": whole / peaks["hbm"],
+                "kernels": kern,
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("BIST_PRECISION", "bf16"), choices=["fp32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -9,8 +9,9 @@ __version__ = "0.1.0"
 
 _LAZY = {
     "LayerNorm": "modules", "SublayerConnection": "modules", "MultiHeadedAttention": "modules",
-    "PositionwiseFeedForward": "modules", "clones": "modules", "attention": "modules",
+    "PositionwiseFeedForward": "modules", "clones": "modules",
     "VidEncoder8": "encoder", "VidEncoderLayer4": "encoder", "VideoPath": "encoder",
+    "set_precision": "encoder",
 }
 
 

@@ -1,0 +1,212 @@
+// C-ABI entry points of libbist_b200.so (include/bist_b200.h): error plumbing and the generic
+// blocks of /root/reference/model/modules.py (LayerNorm, Linear, MultiHeadedAttention,
+// PositionwiseFeedForward) plus the VidEncoder8 projection.  The VidEncoderLayer4 entry points
+// live in st_layer.cu.
+#include <math.h>
+#include <stdarg.h>
+
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace bist {
+
+static thread_local char g_err[1024] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- per-launch event timing (off by default) ---------------------------------------------
+struct ProfRec { const char* tag; cudaEvent_t e0, e1; };
+static std::atomic<int> g_prof_on{0};
+static std::mutex g_prof_mu;
+static std::vector<ProfRec*> g_prof_recs;
+
+ProfScope::ProfScope(const char* tag, cudaStream_t s) : rec(nullptr), st(s) {
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  ProfRec* r = new ProfRec{tag, nullptr, nullptr};
+  if (cudaEventCreate(&r->e0) != cudaSuccess || cudaEventCreate(&r->e1) != cudaSuccess) { delete r; return; }
+  cudaEventRecord(r->e0, st);
+  rec = r;
+}
+ProfScope::~ProfScope() {
+  if (!rec) return;
+  ProfRec* r = (ProfRec*)rec;
+  cudaEventRecord(r->e1, st);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_recs.push_back(r);
+}
+
+int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken);  // gemm_tc.cu
+
+int gemm(const GemmArgs& g, cudaStream_t st) {
+  bool taken = false;
+  int rc = gemm_tc(g, st, &taken);
+  if (taken) return rc;
+  return gemm_simt(g, st);
+}
+
+}  // namespace bist
+
+using namespace bist;
+
+extern "C" {
+
+int bist_version(void) { return BIST_B200_VERSION; }
+const char* bist_last_error(void) { return g_err; }
+int64_t bist_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int bist_prof_enable(int on) {
+  g_prof_on.store(on ? 1 : 0);
+  return 0;
+}
+
+// Synchronises the device, then writes "tag,launches,total_ms\n" lines (one per tag) into buf.
+int bist_prof_collect(char* buf, size_t cap) {
+  BIST_CHECK_ARG(buf && cap > 0, "prof_collect: bad buffer");
+  BIST_CUDA(cudaDeviceSynchronize());
+  std::map<std::string, std::pair<long long, double>> agg;
+  {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (ProfRec* r : g_prof_recs) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, r->e0, r->e1) == cudaSuccess) {
+        auto& a = agg[r->tag];
+        a.first += 1;
+        a.second += ms;
+      }
+      cudaEventDestroy(r->e0);
+      cudaEventDestroy(r->e1);
+      delete r;
+    }
+    g_prof_recs.clear();
+  }
+  size_t used = 0;
+  buf[0] = 0;
+  for (auto& kv : agg) {
+    int n = snprintf(buf + used, cap - used, "%s,%lld,%.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    if (n < 0 || (size_t)n >= cap - used) break;
+    used += n;
+  }
+  return 0;
+}
+
+int bist_device_check(void) {
+  int dev = 0;
+  BIST_CUDA(cudaGetDevice(&dev));
+  int major = 0;
+  BIST_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) {
+    set_error("libbist_b200 is built for sm_100a only; device %d has compute capability %d.x", dev, major);
+    return BIST_ERR_DEVICE;
+  }
+  return 0;
+}
+
+int bist_ln_fwd(const void* x, const float* a_2, const float* b_2, void* y, int64_t rows, int64_t d, float eps,
+                int x_dtype, int y_dtype, void* stream) {
+  return layer_norm(x, a_2, b_2, y, rows, d, eps, x_dtype, y_dtype, (cudaStream_t)stream);
+}
+
+int bist_linear_fwd(const void* x, const void* w, const float* bias, const void* residual, void* y, int64_t M,
+                    int64_t N, int64_t K, int relu, int x_dtype, int w_dtype, int y_dtype, void* stream) {
+  BIST_CHECK_ARG(x && w && y, "linear: null pointer");
+  BIST_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31),
+                 "linear: bad shape");
+  BIST_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(w_dtype) && dtype_ok(y_dtype), "linear: bad dtype");
+  GemmArgs g;
+  g.A = x; g.W = w; g.C = y; g.bias = bias; g.R = residual;
+  g.M = (int)M; g.N = (int)N; g.K = (int)K;
+  g.a = rows_dense(K); g.w = rows_dense(K); g.c = rows_dense(N); g.r = rows_dense(N);
+  g.relu = relu;
+  g.a_dtype = x_dtype; g.w_dtype = w_dtype; g.c_dtype = y_dtype; g.r_dtype = y_dtype;
+  return gemm(g, (cudaStream_t)stream);
+}
+
+// ----------------------------------------------------------------------------- MultiHeadedAttention
+size_t bist_mha_workspace_bytes(int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int64_t d_in, int64_t h) {
+  (void)d_in;
+  size_t e = 4;  // sized for fp32; bf16 needs less
+  size_t n = 0;
+  n += align_up((size_t)Bp * Lq * d * e, 256);      // q
+  n += 2 * align_up((size_t)Bp * Lk * d * e, 256);  // k, v
+  n += align_up((size_t)Bp * Lq * d * e, 256);      // ctx
+  n += align_up((size_t)Bp * Lq * h * Lk * 4, 256); // scores
+  return n + 1024;
+}
+
+int bist_mha_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
+                 const bist_mha_params_t* P, void* out, float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk,
+                 int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(query && key && value && P && out && ws, "mha: null pointer");
+  BIST_CHECK_ARG(Bp > 0 && Lq > 0 && Lk > 0 && d > 0 && d_in > 0 && h > 0 && d % h == 0, "mha: bad shape");
+  BIST_CHECK_ARG(dtype_ok(dtype), "mha: bad dtype");
+  BIST_CHECK_ARG((mask_mode == BIST_MASK_NONE) == (mask == nullptr) && mask_mode >= 0 && mask_mode <= 2,
+                 "mha: mask and mask_mode disagree");
+  for (int i = 0; i < 4; ++i) BIST_CHECK_ARG(P->w[i] && P->b[i], "mha: null parameter %d", i);
+  BIST_CHECK_ARG(Bp * h <= 65535 * 1LL, "mha: Bp*h too large");
+  const int dk = (int)(d / h);
+  const size_t e = dtype_size(dtype);
+  Arena A(ws, ws_bytes);
+  void* q = A.take((size_t)Bp * Lq * d * e);
+  void* k = A.take((size_t)Bp * Lk * d * e);
+  void* v = A.take((size_t)Bp * Lk * d * e);
+  void* ctx = A.take((size_t)Bp * Lq * d * e);
+  float* sc = (float*)A.take((size_t)Bp * Lq * h * Lk * 4);
+  if (!A.ok) { set_error("mha: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+
+  // modules.py:89-91 — the three input projections
+  const void* in[3] = {query, key, value};
+  void* proj[3] = {q, k, v};
+  const int64_t rows[3] = {Bp * Lq, Bp * Lk, Bp * Lk};
+  for (int i = 0; i < 3; ++i)
+    BIST_TRY(bist_linear_fwd(in[i], P->w[i], P->b[i], nullptr, proj[i], rows[i], d, d_in, 0, dtype, dtype, dtype, st));
+
+  // modules.py:57-58 — scores[b,l,hh,k] = q[b,l,hh,:].k[b,k,hh,:] / sqrt(dk), batched over (b,hh)
+  GemmArgs g;
+  g.A = q; g.W = k; g.C = sc;
+  g.M = (int)Lq; g.N = (int)Lk; g.K = dk;
+  g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(h * Lk);
+  g.Z = (int)(Bp * h); g.zin = (int)h;
+  g.az = {Lq * d, dk}; g.wz = {Lk * d, dk}; g.cz = {Lq * h * Lk, Lk};
+  g.alpha = 1.f / sqrtf((float)dk);
+  g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = BIST_F32;
+  BIST_TRY(gemm(g, st));
+
+  // modules.py:59-64 — mask, softmax, weighted sum
+  SoftmaxPvArgs a;
+  a.S = sc; a.sg = rows_dense(Lq * h * Lk); a.s_l = h * Lk; a.s_h = Lk;
+  a.mask = mask; a.m_b = (mask_mode == BIST_MASK_FULL) ? Lq * Lk : Lk; a.m_l = (mask_mode == BIST_MASK_FULL) ? Lk : 0;
+  a.V = v; a.v = rows_dense(d); a.vg = rows_dense(Lk * d);
+  a.ctx = ctx; a.p_out = attn_out;
+  a.G = (int)Bp; a.Lq = (int)Lq; a.h = (int)h; a.dk = dk; a.nk = (int)Lk;
+  a.v_dtype = dtype; a.ctx_dtype = dtype;
+  BIST_TRY(softmax_pv(a, st));
+
+  // modules.py:98-100 — output projection
+  return bist_linear_fwd(ctx, P->w[3], P->b[3], nullptr, out, Bp * Lq, d_in, d, 0, dtype, dtype, dtype, st);
+}
+
+// ----------------------------------------------------------------------------- PositionwiseFeedForward
+int bist_ffn_fwd(const void* x, const void* w1, const float* b1, const void* w2, const float* b2, void* y,
+                 int64_t rows, int64_t d, int64_t d_ff, int64_t d_out, void* ws, size_t ws_bytes, int dtype,
+                 void* stream) {
+  BIST_CHECK_ARG(x && w1 && w2 && y && ws, "ffn: null pointer");
+  BIST_CHECK_ARG(dtype_ok(dtype), "ffn: bad dtype");
+  if (ws_bytes < (size_t)rows * d_ff * dtype_size(dtype)) { set_error("ffn: workspace too small"); return BIST_ERR_WORKSPACE; }
+  BIST_TRY(bist_linear_fwd(x, w1, b1, nullptr, ws, rows, d_ff, d, 1, dtype, dtype, dtype, stream));
+  return bist_linear_fwd(ws, w2, b2, nullptr, y, rows, d_out, d_ff, 0, dtype, dtype, dtype, stream);
+}
+
+}  // extern "C"

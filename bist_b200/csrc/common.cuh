@@ -1,0 +1,195 @@
+// Internal helpers shared by the kernels of libbist_b200.so (not part of the ABI).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/bist_b200.h"
+
+namespace bist {
+
+// ---- error plumbing (api.cu owns the storage) -------------------------------------------
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+// Optional per-launch CUDA-event timing (bist_prof_enable): declare one right before a launch.
+struct ProfScope {
+  void* rec;
+  cudaStream_t st;
+  ProfScope(const char* tag, cudaStream_t st);
+  ~ProfScope();
+};
+
+#define BIST_CHECK_ARG(cond, ...)                 \
+  do {                                            \
+    if (!(cond)) {                                \
+      ::bist::set_error(__VA_ARGS__);             \
+      return BIST_ERR_ARG;                        \
+    }                                             \
+  } while (0)
+
+#define BIST_CUDA(call)                                                                   \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess) {                                                             \
+      ::bist::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      return BIST_ERR_CUDA;                                                               \
+    }                                                                                     \
+  } while (0)
+
+#define BIST_TRY(call)        \
+  do {                        \
+    int rc__ = (call);        \
+    if (rc__ != 0) return rc__; \
+  } while (0)
+
+// Check the launch that just happened (no sync) and count it.
+#define BIST_LAUNCHED()                     \
+  do {                                      \
+    ::bist::count_launch();                 \
+    BIST_CUDA(cudaGetLastError());          \
+  } while (0)
+
+static inline size_t dtype_size(int dt) { return dt == BIST_BF16 ? 2 : 4; }
+static inline bool dtype_ok(int dt) { return dt == BIST_F32 || dt == BIST_BF16; }
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// A bump allocator over the caller's workspace.
+struct Arena {
+  char* base;
+  size_t cap, used = 0;
+  bool ok = true;
+  Arena(void* p, size_t n) : base(reinterpret_cast<char*>(p)), cap(n) {}
+  void* take(size_t bytes) {
+    size_t off = align_up(used, 256);
+    if (off + bytes > cap) { ok = false; return nullptr; }
+    used = off + bytes;
+    return base + off;
+  }
+};
+
+// ---- element access ---------------------------------------------------------------------
+__device__ __forceinline__ float to_f32(float v) { return v; }
+__device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+
+// Load 4 consecutive elements as floats (address must be 16 B aligned for float, 8 B for bf16).
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+  uint2 u = *reinterpret_cast<const uint2*>(p);
+  __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&u.x);
+  __nv_bfloat162 b = *reinterpret_cast<__nv_bfloat162*>(&u.y);
+  float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+  return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- two-level row addressing -----------------------------------------------------------
+// Element offset of logical row r: (r / inner) * outer_stride + (r % inner) * inner_stride.
+// Lets one GEMM / attention kernel walk [B,T,S,d] as rows (b,t,s) or (b,s,t), broadcast a
+// [B,Lq,d] residual over a group dimension, or pick a per-head column slice, without a copy.
+// An optional modulus on the inner index (`mod`) broadcasts rows: (b, g, l) -> (b, l).
+struct RowMap {
+  int inner;
+  long long so, si;
+  int mod;
+  __host__ __device__ __forceinline__ long long off(int r) const {
+    return (long long)(r / inner) * so + (long long)((r % inner) % mod) * si;
+  }
+};
+constexpr int kNoSplit = 1 << 30;
+static inline RowMap rows_dense(long long ld) { return RowMap{kNoSplit, 0, ld, kNoSplit}; }
+static inline RowMap rows_2level(int inner, long long so, long long si) { return RowMap{inner, so, si, kNoSplit}; }
+static inline RowMap rows_bcast(int inner, long long so, int mod, long long si) { return RowMap{inner, so, si, mod}; }
+
+// Batch index z -> (z / zin, z % zin) with one stride each.
+struct BatchMap {
+  long long s0, s1;
+  __host__ __device__ __forceinline__ long long off(int z, int zin) const {
+    return (long long)(z / zin) * s0 + (long long)(z % zin) * s1;
+  }
+};
+
+// ---- generic GEMM:  C = act(alpha * A . W^T + bias) + R ------------------------------------
+struct GemmArgs {
+  const void* A = nullptr;  // [M,K] rows via `a`, K contiguous
+  const void* W = nullptr;  // [N,K] rows via `w`, K contiguous
+  void* C = nullptr;        // [M,N] rows via `c`, N contiguous
+  const float* bias = nullptr;  // [N] fp32 or null
+  const void* R = nullptr;      // residual rows via `r`, N contiguous, or null
+  int M = 0, N = 0, K = 0;
+  RowMap a{kNoSplit, 0, 0, kNoSplit}, w{kNoSplit, 0, 0, kNoSplit}, c{kNoSplit, 0, 0, kNoSplit}, r{kNoSplit, 0, 0, kNoSplit};
+  int Z = 1, zin = 1;  // batch count and inner batch extent
+  BatchMap az{0, 0}, wz{0, 0}, cz{0, 0}, rz{0, 0}, bz{0, 0};
+  float alpha = 1.f;
+  int relu = 0;
+  const char* tag = "gemm";  // label for bist_prof_collect
+  int a_dtype = BIST_F32, w_dtype = BIST_F32, c_dtype = BIST_F32, r_dtype = BIST_F32;
+};
+int gemm(const GemmArgs& g, cudaStream_t st);       // dispatches to the kernels below
+int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate GEMM, any shape
+
+// ---- LayerNorm ----------------------------------------------------------------------------
+// Rows [k*group_rows, (k+1)*group_rows) use a2 + k*pstride, b2 + k*pstride (batched directions).
+int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d,
+               float eps, int x_dtype, int y_dtype, cudaStream_t st, int64_t group_rows = 0,
+               int64_t pstride = 0);
+
+// ---- softmax + weighted sum over projected values ---------------------------------------------
+// For every group g in [0,G): scores S[g] [Lq*h rows (l-major, h-minor), nk] fp32 (row stride
+// ld_s), optional mask, softmax over nk, ctx[g][l, hh*dk + j] = sum_k p[l,hh,k] * V[g][k, hh*dk+j].
+struct SoftmaxPvArgs {
+  const float* S = nullptr;
+  RowMap sg{kNoSplit, 0, 0, kNoSplit};  // group g -> base offset of S
+  long long s_l = 0, s_h = 0;  // strides of the (l, h) row of S; keys contiguous
+  const uint8_t* mask = nullptr;  // null or uint8, 0 = masked
+  int mask_gdiv = 1, mask_gmod = kNoSplit;  // mask batch index = (g / mask_gdiv) % mask_gmod
+  long long m_b = 0, m_l = 0;  // mask strides (batch, query row; m_l = 0 for key masks)
+  const void* V = nullptr;
+  RowMap v{kNoSplit, 0, 0, kNoSplit};   // key row k -> offset within the group's V
+  RowMap vg{kNoSplit, 0, 0, kNoSplit};  // group g  -> base offset of V
+  void* ctx = nullptr;      // [G, Lq, d] dense
+  float* p_out = nullptr;   // optional fp32 [G, h, Lq, nk]
+  int G = 0, Lq = 0, h = 0, dk = 0, nk = 0;
+  int v_dtype = BIST_F32, ctx_dtype = BIST_F32;
+};
+int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st);
+
+// ---- stage 2 of t2s / s2t: one query row attends over its G stage-1 summaries ---------------------
+// For every (b,l): scores[hh,g] = qf[b,l,hh,:] . X1[b,g,l,:] (qf pre-scaled), optional key mask
+// [B,G], softmax over g, ctxx[b,l,hh,:] = sum_g p[hh,g] X1[b,g,l,:]   (fp32 [B*Lq, h, d]).
+int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, float* ctxx, int B, int G,
+                int Lq, int h, int d, int x1_dtype, cudaStream_t st);
+
+// ---- weight packing helpers ------------------------------------------------------------------
+// dst[r, c] = scale * src[r, c] (transpose = 0) or scale * src[c, r] (transpose = 1); dst is
+// [rows, cols] dense of dst_dtype, src fp32 dense.
+int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, float scale,
+                int dst_dtype, cudaStream_t st);
+
+}  // namespace bist

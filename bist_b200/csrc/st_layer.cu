@@ -1,0 +1,345 @@
+// VidEncoderLayer4.forward (enc_st_combine == 'none') — /root/reference/model/encoder.py:172-201 with
+// temporal2spatial (:109-139) and spatial2temporal (:141-170), eval mode.
+//
+// Formulation: the reference copies the query block S (or T) times and projects every
+// video row to keys and values.  Here
+//   * the query-side work (LayerNorm, Q projection) is done once per (b,l) instead of once per copy;
+//   * the key projection is folded into the query:  q_h.(W_k,h x + b_k,h) = (q_h W_k,h).x + const, and
+//     the constant cancels in the softmax, so stage-1 scores are ONE batched GEMM of the folded
+//     queries [Lq*h, d] against the raw video rows, and the key bias never appears;
+//   * stage 2 (one query row against its G stage-1 summaries) folds both key and value projections.
+// Only the stage-1 value projection touches every video row (one GEMM for both directions).
+#include <math.h>
+
+#include "common.cuh"
+
+namespace bist {
+namespace {
+
+struct PackedLayout {
+  // matrix section, element offsets relative to the direction base
+  size_t wqkv0, wo0, wq1, wkt1, wo1, wq2, wkt2, wv2, wo2, w1, w2, dir_stride;
+  size_t wv1cat, mat_elems;
+  // fp32 section, float offsets relative to the direction base
+  size_t bqkv0, bo0, bq1, bo1, bq2, bv2, bo2, b1, b2, ln_a, ln_b, fdir_stride;
+  size_t bv1cat, f_elems;
+  size_t f_byte_off, total_bytes;
+};
+
+PackedLayout packed_layout(int64_t d, int64_t dff, int n_dirs, int dtype) {
+  PackedLayout L;
+  size_t o = 0;
+  auto m = [&](size_t n) { size_t r = o; o += n; return r; };
+  const size_t dd = (size_t)d * d;
+  L.wqkv0 = m(3 * dd); L.wo0 = m(dd); L.wq1 = m(dd); L.wkt1 = m(dd); L.wo1 = m(dd);
+  L.wq2 = m(dd); L.wkt2 = m(dd); L.wv2 = m(dd); L.wo2 = m(dd);
+  L.w1 = m((size_t)dff * d); L.w2 = m((size_t)d * dff);
+  L.dir_stride = o;
+  L.wv1cat = L.dir_stride * n_dirs;
+  L.mat_elems = L.wv1cat + (size_t)n_dirs * dd;
+  o = 0;
+  L.bqkv0 = m(3 * d); L.bo0 = m(d); L.bq1 = m(d); L.bo1 = m(d); L.bq2 = m(d); L.bv2 = m(d); L.bo2 = m(d);
+  L.b1 = m(dff); L.b2 = m(d); L.ln_a = m(4 * d); L.ln_b = m(4 * d);
+  L.fdir_stride = o;
+  L.bv1cat = L.fdir_stride * n_dirs;
+  L.f_elems = L.bv1cat + (size_t)n_dirs * d;
+  L.f_byte_off = align_up(L.mat_elems * dtype_size(dtype), 256);
+  L.total_bytes = L.f_byte_off + L.f_elems * 4;
+  return L;
+}
+
+struct Workspace {
+  float *nbuf, *qkv0, *sc0, *cbuf, *x, *qbuf, *qf, *ctxx2, *ts, *ffh;
+  void* xv;
+  float* sc1[2];
+  void* ctx1[2];
+  void* out1[2];
+  size_t bytes;
+  bool ok;
+};
+
+Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t dff,
+                int64_t h, int nd, const int* kinds, int dtype) {
+  Arena A(base, cap);
+  Workspace W;
+  const size_t Q = (size_t)B * Lq, e = dtype_size(dtype);
+  auto f = [&](size_t n) { return (float*)A.take(n * 4); };
+  W.nbuf = f(nd * Q * d); W.qkv0 = f(nd * Q * 3 * d); W.sc0 = f(nd * Q * h * Lq); W.cbuf = f(nd * Q * d);
+  W.x = f(nd * Q * d); W.qbuf = f(nd * Q * d); W.qf = f(nd * Q * h * d); W.ctxx2 = f(nd * Q * h * d);
+  W.ts = f(nd * Q * d); W.ffh = f(nd * Q * dff);
+  W.xv = A.take((size_t)B * T * S * nd * d * e);
+  for (int u = 0; u < 2; ++u) { W.sc1[u] = nullptr; W.ctx1[u] = W.out1[u] = nullptr; }
+  for (int u = 0; u < nd; ++u) {
+    const size_t G = kinds[u] == 0 ? S : T;
+    W.sc1[u] = f(Q * h * T * S);
+    W.ctx1[u] = A.take((size_t)B * G * Lq * d * e);
+    W.out1[u] = A.take((size_t)B * G * Lq * d * e);
+  }
+  W.bytes = A.used + 256;
+  W.ok = A.ok;
+  return W;
+}
+
+int active_dirs(int n_dirs, int dir_mask, int* kinds) {
+  int nd = 0;
+  if (dir_mask & 1) kinds[nd++] = 0;
+  if (dir_mask & 2) kinds[nd++] = 1;
+  if (n_dirs == 1 && nd != 1) return -1;
+  return nd;
+}
+
+}  // namespace
+}  // namespace bist
+
+using namespace bist;
+
+extern "C" {
+
+size_t bist_st_layer_packed_bytes(int64_t d, int64_t d_ff, int n_dirs, int dtype) {
+  if (d <= 0 || d_ff <= 0 || (n_dirs != 1 && n_dirs != 2) || !dtype_ok(dtype)) return 0;
+  return packed_layout(d, d_ff, n_dirs, dtype).total_bytes;
+}
+
+int bist_st_layer_pack(const bist_st_layer_params_t* P, void* packed, size_t packed_bytes, int64_t d, int64_t dff,
+                       int64_t h, int n_dirs, int dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(P && packed, "pack: null pointer");
+  BIST_CHECK_ARG(d > 0 && dff > 0 && h > 0 && d % h == 0 && (n_dirs == 1 || n_dirs == 2) && dtype_ok(dtype),
+                 "pack: bad argument");
+  BIST_CHECK_ARG(d % 4 == 0 && dff % 4 == 0, "pack: d and d_ff must be multiples of 4");
+  const PackedLayout L = packed_layout(d, dff, n_dirs, dtype);
+  if (packed_bytes < L.total_bytes) { set_error("pack: buffer too small"); return BIST_ERR_WORKSPACE; }
+  const size_t e = dtype_size(dtype);
+  char* mat = (char*)packed;
+  float* fs = (float*)((char*)packed + L.f_byte_off);
+  const float rs = 1.f / sqrtf((float)(d / h));
+  const int di = (int)d, fi = (int)dff;
+  auto M = [&](size_t off) { return (void*)(mat + off * e); };
+  for (int u = 0; u < n_dirs; ++u) {
+    const int ab = 3 * u;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 4; ++j) BIST_CHECK_ARG(P->attn_w[ab + i][j] && P->attn_b[ab + i][j], "pack: null attn parameter");
+    BIST_CHECK_ARG(P->ff_w1[u] && P->ff_b1[u] && P->ff_w2[u] && P->ff_b2[u], "pack: null ff parameter");
+    const size_t mb = u * L.dir_stride, fb = u * L.fdir_stride;
+    for (int j = 0; j < 3; ++j)
+      BIST_TRY(pack_matrix(P->attn_w[ab][j], M(mb + L.wqkv0 + (size_t)j * d * d), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab][3], M(mb + L.wo0), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][0], M(mb + L.wq1), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][1], M(mb + L.wkt1), di, di, 1, rs, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][2], M(L.wv1cat + (size_t)u * d * d), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][3], M(mb + L.wo1), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 2][0], M(mb + L.wq2), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 2][1], M(mb + L.wkt2), di, di, 1, rs, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 2][2], M(mb + L.wv2), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 2][3], M(mb + L.wo2), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->ff_w1[u], M(mb + L.w1), fi, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->ff_w2[u], M(mb + L.w2), di, fi, 0, 1.f, dtype, st));
+    auto V = [&](const float* src, size_t off, int n) { return pack_matrix(src, fs + off, 1, n, 0, 1.f, BIST_F32, st); };
+    for (int j = 0; j < 3; ++j) BIST_TRY(V(P->attn_b[ab][j], fb + L.bqkv0 + (size_t)j * d, di));
+    BIST_TRY(V(P->attn_b[ab][3], fb + L.bo0, di));
+    BIST_TRY(V(P->attn_b[ab + 1][0], fb + L.bq1, di));
+    BIST_TRY(V(P->attn_b[ab + 1][2], L.bv1cat + (size_t)u * d, di));
+    BIST_TRY(V(P->attn_b[ab + 1][3], fb + L.bo1, di));
+    BIST_TRY(V(P->attn_b[ab + 2][0], fb + L.bq2, di));
+    BIST_TRY(V(P->attn_b[ab + 2][2], fb + L.bv2, di));
+    BIST_TRY(V(P->attn_b[ab + 2][3], fb + L.bo2, di));
+    BIST_TRY(V(P->ff_b1[u], fb + L.b1, fi));
+    BIST_TRY(V(P->ff_b2[u], fb + L.b2, di));
+    for (int i = 0; i < 4; ++i) {
+      BIST_CHECK_ARG(P->ln_a[4 * u + i] && P->ln_b[4 * u + i], "pack: null norm parameter");
+      BIST_TRY(V(P->ln_a[4 * u + i], fb + L.ln_a + (size_t)i * d, di));
+      BIST_TRY(V(P->ln_b[4 * u + i], fb + L.ln_b + (size_t)i * d, di));
+    }
+  }
+  return 0;
+}
+
+size_t bist_st_layer_workspace_bytes(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t d_ff,
+                                     int64_t h, int n_dirs, int dtype) {
+  if (B <= 0 || T <= 0 || S <= 0 || Lq <= 0 || d <= 0 || d_ff <= 0 || h <= 0 || !dtype_ok(dtype)) return 0;
+  int kinds[2] = {0, 1};
+  const int nd = n_dirs == 2 ? 2 : 1;
+  if (nd == 1) kinds[0] = T > S ? 1 : 0;  // the larger of the two single-direction footprints
+  Workspace W = carve(nullptr, (size_t)-1, B, T, S, Lq, d, d_ff, h, nd, kinds, dtype);
+  return W.bytes;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------- forward
+extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const void* vft,
+                                 const uint8_t* query_mask, const uint8_t* temporal_mask, const void* packed,
+                                 float* out_t2s, float* out_s2t, int64_t B, int64_t T, int64_t S, int64_t Lq,
+                                 int64_t d, int64_t dff, int64_t h, int n_dirs, int dir_mask, float eps, void* ws,
+                                 size_t ws_bytes, int dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(vft && query_mask && temporal_mask && packed && ws, "st_layer: null pointer");
+  BIST_CHECK_ARG(B > 0 && T > 0 && S > 0 && Lq > 0 && d > 0 && dff > 0 && h > 0 && d % h == 0,
+                 "st_layer: bad shape B=%lld T=%lld S=%lld Lq=%lld d=%lld h=%lld", (long long)B, (long long)T,
+                 (long long)S, (long long)Lq, (long long)d, (long long)h);
+  BIST_CHECK_ARG(d % 4 == 0 && dff % 4 == 0, "st_layer: d and d_ff must be multiples of 4");
+  BIST_CHECK_ARG((n_dirs == 1 || n_dirs == 2) && dtype_ok(dtype) && (dir_mask & ~3) == 0 && dir_mask != 0,
+                 "st_layer: bad n_dirs/dir_mask/dtype");
+  BIST_CHECK_ARG(B * T * S < (1LL << 31) / 2 && B * Lq * h < (1LL << 31), "st_layer: problem too large");
+  int kinds[2];
+  const int nd = active_dirs(n_dirs, dir_mask, kinds);
+  BIST_CHECK_ARG(nd > 0, "st_layer: a single-direction layer needs exactly one bit in dir_mask");
+  const float* x_in[2];
+  float* x_out[2];
+  for (int u = 0; u < nd; ++u) {
+    x_in[u] = kinds[u] == 0 ? in_t2s : in_s2t;
+    x_out[u] = kinds[u] == 0 ? out_t2s : out_s2t;
+    BIST_CHECK_ARG(x_in[u] && x_out[u], "st_layer: null stream pointer for an active direction");
+  }
+  const Workspace W = carve(ws, ws_bytes, B, T, S, Lq, d, dff, h, nd, kinds, dtype);
+  if (!W.ok) { set_error("st_layer: workspace too small (%zu bytes given)", ws_bytes); return BIST_ERR_WORKSPACE; }
+
+  const PackedLayout L = packed_layout(d, dff, n_dirs, dtype);
+  const int pu0 = n_dirs == 2 ? kinds[0] : 0;  // packed index of slot 0; slot 1 is pu0 + 1
+  const size_t e = dtype_size(dtype);
+  const char* mat = (const char*)packed + (size_t)pu0 * L.dir_stride * e;
+  const float* fs = (const float*)((const char*)packed + L.f_byte_off) + (size_t)pu0 * L.fdir_stride;
+  auto Mw = [&](size_t off) { return (const void*)(mat + off * e); };
+  const long long ms = (long long)L.dir_stride, fsd = (long long)L.fdir_stride;
+  const int Q = (int)(B * Lq), dk = (int)(d / h), di = (int)d, hi = (int)h;
+  const long long Qd = (long long)Q * d;
+
+  // Batched (over the active directions) linear layer on [Q, K] fp32 activations in the workspace.
+  auto lin = [&](const float* Ain, long long a_dir, size_t w_off, size_t b_off, float* Cout, long long c_dir, int N,
+                 int K, int relu, const float* R, long long r_dir) {
+    GemmArgs g;
+    g.A = Ain; g.W = Mw(w_off); g.C = Cout; g.bias = fs + b_off; g.R = R;
+    g.M = Q; g.N = N; g.K = K;
+    g.a = rows_dense(K); g.w = rows_dense(K); g.c = rows_dense(N); g.r = rows_dense(N);
+    g.Z = nd; g.zin = 1;
+    g.az = {a_dir, 0}; g.wz = {ms, 0}; g.cz = {c_dir, 0}; g.rz = {r_dir, 0}; g.bz = {fsd, 0};
+    g.relu = relu; g.w_dtype = dtype; g.tag = "query_side_gemm";
+    return gemm(g, st);
+  };
+  // Query-side fold of a key projection: qf[u][q,hh,:] = q[u][q, hh*dk:(hh+1)*dk] . WkT[u][:, hh*dk:(hh+1)*dk]^T
+  auto fold = [&](size_t wkt_off) {
+    GemmArgs g;
+    g.A = W.qbuf; g.W = Mw(wkt_off); g.C = W.qf;
+    g.M = Q; g.N = di; g.K = dk;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(h * d);
+    g.Z = nd * hi; g.zin = hi;
+    g.az = {Qd, dk}; g.wz = {ms, dk}; g.cz = {Qd * h, d};
+    g.w_dtype = dtype;
+    return gemm(g, st);
+  };
+
+  // ---- self-attention over the query tokens (encoder.py:176 / :184) -------------------------------
+  for (int u = 0; u < nd; ++u)
+    BIST_TRY(layer_norm(x_in[u], fs + u * fsd + L.ln_a, fs + u * fsd + L.ln_b, W.nbuf + u * Qd, Q, d, eps, BIST_F32,
+                        BIST_F32, st));
+  BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, 3 * di, di, 0, nullptr, 0));
+  {
+    GemmArgs g;  // scores[u,b,l,hh,k] = q.k / sqrt(dk)
+    g.A = W.qkv0; g.W = W.qkv0 + d; g.C = W.sc0;
+    g.M = (int)Lq; g.N = (int)Lq; g.K = dk;
+    g.a = rows_dense(3 * d); g.w = rows_dense(3 * d); g.c = rows_dense(h * Lq);
+    g.Z = (int)(nd * B * h); g.zin = hi;
+    g.az = {Lq * 3 * d, dk}; g.wz = {Lq * 3 * d, dk}; g.cz = {Lq * h * Lq, Lq};
+    g.alpha = 1.f / sqrtf((float)dk);
+    BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B*h too large");
+    BIST_TRY(gemm(g, st));
+    SoftmaxPvArgs a;
+    a.S = W.sc0; a.sg = rows_dense(Lq * h * Lq); a.s_l = h * Lq; a.s_h = Lq;
+    a.mask = query_mask; a.mask_gmod = (int)B; a.m_b = Lq; a.m_l = 0;
+    a.V = W.qkv0 + 2 * d; a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
+    a.ctx = W.cbuf;
+    a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
+    BIST_TRY(softmax_pv(a, st));
+  }
+  // output projection + residual with the (possibly aliased, not strided) layer inputs (modules.py:44)
+  for (int u = 0; u < nd; ++u) {
+    GemmArgs g;
+    g.A = W.cbuf + u * Qd; g.W = Mw(L.wo0 + (size_t)u * L.dir_stride); g.C = W.x + u * Qd;
+    g.bias = fs + u * fsd + L.bo0; g.R = x_in[u];
+    g.M = Q; g.N = di; g.K = di;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
+    g.w_dtype = dtype;
+    BIST_TRY(gemm(g, st));
+  }
+
+  // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
+  BIST_TRY(layer_norm(W.x, fs + L.ln_a + d, fs + L.ln_b + d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.wq1, L.bq1, W.qbuf, Qd, di, di, 0, nullptr, 0));
+  BIST_TRY(fold(L.wkt1));
+  const long long TS = T * S, xvld = (long long)nd * d;
+  {
+    GemmArgs g;  // values of every video row for the active directions: XV = vft . [Wv1]^T + bv1
+    g.A = vft; g.W = (const char*)packed + (L.wv1cat + (size_t)pu0 * d * d) * e; g.C = W.xv;
+    g.bias = (const float*)((const char*)packed + L.f_byte_off) + L.bv1cat + (size_t)pu0 * d;
+    g.M = (int)(B * TS); g.N = nd * di; g.K = di;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(xvld);
+    g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
+    BIST_TRY(gemm(g, st));
+  }
+  for (int u = 0; u < nd; ++u) {
+    const bool t2s = kinds[u] == 0;
+    const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
+    GemmArgs g;  // scores1[b, (l,hh), key-ordered video rows] = qf . x   (keys contiguous per group)
+    g.A = W.qf + u * Qd * h; g.W = vft; g.C = W.sc1[u];
+    g.M = (int)(Lq * h); g.N = (int)TS; g.K = di;
+    g.a = rows_dense(d); g.c = rows_dense(TS);
+    g.w = t2s ? rows_2level((int)T, d, S * d) : rows_dense(d);  // t2s walks rows as (s, t)
+    g.Z = (int)B; g.zin = 1;
+    g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
+    g.w_dtype = dtype; g.tag = "scores1_gemm";
+    BIST_TRY(gemm(g, st));
+    SoftmaxPvArgs a;
+    a.S = W.sc1[u]; a.sg = rows_2level(G, Lq * h * TS, nk); a.s_l = h * TS; a.s_h = TS;
+    if (t2s) { a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0; }  // encoder.py:117-121
+    a.V = (const char*)W.xv + (size_t)u * d * e;
+    a.vg = t2s ? rows_2level((int)S, TS * xvld, xvld) : rows_dense(S * xvld);
+    a.v = t2s ? rows_dense(S * xvld) : rows_dense(xvld);
+    a.ctx = W.ctx1[u];
+    a.G = (int)(B * G); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = nk;
+    a.v_dtype = dtype; a.ctx_dtype = dtype;
+    BIST_TRY(softmax_pv(a, st));
+    GemmArgs o;  // out1[b,g,l,:] = x[b,l,:] + ctx1[b,g,l,:] . Wo1^T + bo1
+    o.A = W.ctx1[u]; o.W = Mw(L.wo1 + (size_t)u * L.dir_stride); o.C = W.out1[u];
+    o.bias = fs + u * fsd + L.bo1; o.R = W.x + u * Qd;
+    o.M = (int)(B * G * Lq); o.N = di; o.K = di;
+    o.a = rows_dense(d); o.w = rows_dense(d); o.c = rows_dense(d);
+    o.r = rows_bcast((int)(G * Lq), Lq * d, (int)Lq, d);
+    o.a_dtype = dtype; o.w_dtype = dtype; o.c_dtype = dtype; o.r_dtype = BIST_F32; o.tag = "o1_gemm";
+    BIST_TRY(gemm(o, st));
+  }
+
+  // ---- stage 2 (encoder.py:125-132 / :152-161) ------------------------------------------------------
+  BIST_TRY(layer_norm(W.x, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.wq2, L.bq2, W.qbuf, Qd, di, di, 0, nullptr, 0));
+  BIST_TRY(fold(L.wkt2));
+  for (int u = 0; u < nd; ++u) {
+    const bool t2s = kinds[u] == 0;
+    BIST_TRY(stage2_attn(W.qf + u * Qd * h, W.out1[u], t2s ? nullptr : temporal_mask, W.ctxx2 + u * Qd * h, (int)B,
+                         (int)(t2s ? S : T), (int)Lq, hi, di, dtype, st));
+  }
+  {
+    GemmArgs g;  // value projection after the weighted sum: ctx2[q, hh*dk+j] = ctxx2[q,hh,:] . Wv2[hh*dk+j,:] + bv2
+    g.A = W.ctxx2; g.W = Mw(L.wv2); g.C = W.cbuf; g.bias = fs + L.bv2;
+    g.M = Q; g.N = dk; g.K = di;
+    g.a = rows_dense(h * d); g.w = rows_dense(d); g.c = rows_dense(d);
+    g.Z = nd * hi; g.zin = hi;
+    g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.bz = {fsd, dk};
+    g.w_dtype = dtype;
+    BIST_TRY(gemm(g, st));
+  }
+  BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, di, di, 0, W.x, Qd));
+
+  // ---- feed-forward (encoder.py:134-135 / :165-166) -----------------------------------------------
+  BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, (int)dff, di, 1, nullptr, 0));
+  for (int u = 0; u < nd; ++u) {
+    GemmArgs g;
+    g.A = W.ffh + (long long)u * Q * dff; g.W = Mw(L.w2 + (size_t)u * L.dir_stride); g.C = x_out[u];
+    g.bias = fs + u * fsd + L.b2; g.R = W.ts + u * Qd;
+    g.M = Q; g.N = di; g.K = (int)dff;
+    g.a = rows_dense(dff); g.w = rows_dense(dff); g.c = rows_dense(d); g.r = rows_dense(d);
+    g.w_dtype = dtype;
+    BIST_TRY(gemm(g, st));
+  }
+  return 0;
+}

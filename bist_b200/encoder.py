@@ -1,0 +1,245 @@
+"""Drop-in mirrors of the video hot path of /root/reference/model/encoder.py over libbist_b200.so.
+
+``VidEncoder8``       encoder.py:55-93   (2048 -> d_model projection + ReLU + LayerNorm)
+``VidEncoderLayer4``  encoder.py:95-201  (query self-attention, temporal2spatial, spatial2temporal)
+``VideoPath``         the slice of ``MTN.forward`` that is the hot path (mtn.py:49-51 and
+                      decoder.py:107-129), with the reference's parameter names, used by
+                      bench.py and the parity tests.
+
+Constructor and forward signatures, the ``b`` / ``ft`` / ``in_ft`` dict protocol and the
+state_dict key names are the reference's.  ``precision`` ("fp32" | "bf16") selects the storage
+type of the projected video tensor and of the weights inside the kernels; parameters stay
+fp32 masters and the [B,Lq,d] query streams stay fp32 in both modes.
+"""
+import copy
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .modules import LayerNorm, SublayerConnection, clones, _eval_only, _ws
+
+_TORCH_DTYPE = {"fp32": torch.float32, "bf16": torch.bfloat16}
+
+
+def set_precision(module, precision):
+    """Set the compute/storage precision of every bist_b200 video module under `module`."""
+    if precision not in _TORCH_DTYPE:
+        raise ValueError("precision must be 'fp32' or 'bf16'")
+    for m in module.modules():
+        if isinstance(m, (VidEncoder8, VidEncoderLayer4)):
+            m.precision = precision
+    return module
+
+
+def _mask_bytes(mask, B, L):
+    m = mask.reshape(B, L)
+    m = m if m.dtype == torch.bool else (m != 0)
+    return m.contiguous().view(torch.uint8)
+
+
+class VidEncoder8(nn.Module):
+    "encoder.py:55-93."
+
+    def __init__(self, W, a_W, vid_position, v_N, a_N, size, args):
+        super(VidEncoder8, self).__init__()
+        self.v_N = v_N
+        self.a_N = a_N
+        self.args = args
+        self.precision = "fp32"
+        if self.v_N > 0:
+            self.W = W
+            self.vid_position = vid_position
+            self.in_norm = LayerNorm(size)
+        if self.a_N > 0:
+            self.a_W = a_W
+            self.vid_position = vid_position
+            self.a_in_norm = LayerNorm(size)
+
+    def _project(self, x, lin, norm):
+        """LayerNorm(relu(lin(x))) as one C-ABI call (encoder.py:75,80 / :87,90)."""
+        _lib.require_cuda(x, lin.weight)
+        x = x.detach()
+        if x.dtype != torch.float32:
+            x = x.float()
+        x = x.contiguous()
+        D, d = lin.in_features, lin.out_features
+        N = x.numel() // D
+        cdt = _lib.BF16 if self.precision == "bf16" else _lib.F32
+        out = torch.empty(x.shape[:-1] + (d,), dtype=_TORCH_DTYPE[self.precision], device=x.device)
+        L = _lib.lib()
+        ws = _ws(L.bist_vidproj_workspace_bytes(N, D, d, cdt), x.device)
+        _lib.check(L.bist_vidproj_fwd(_lib.ptr(x), _lib.ptr(lin.weight), _lib.ptr(lin.bias), _lib.ptr(norm.a_2),
+                                      _lib.ptr(norm.b_2), _lib.ptr(out), N, D, d, float(norm.eps), _lib.ptr(ws),
+                                      ws.numel(), cdt, cdt, _lib.stream_ptr()), "bist_vidproj_fwd")
+        return out
+
+    def forward(self, b, ft):
+        _eval_only(self)
+        if self.v_N > 0:
+            if self.vid_position is not None:      # always None in the reference (mtn.py:108)
+                raise NotImplementedError("vid_position is never set by make_model (mtn.py:108)")
+            ft['spatiotemporal_ft'] = self._project(b.fts, self.W, self.in_norm)
+        if self.a_N > 0:
+            if getattr(self.args, 'noW_venc', 0):  # encoder.py:84 (attribute absent from the configs)
+                ft['encoded_audio'] = self.a_in_norm(b.audio_fts)
+            else:
+                ft['encoded_audio'] = self._project(b.audio_fts, self.a_W, self.a_in_norm).float()
+        return ft
+
+
+class VidEncoderLayer4(nn.Module):
+    "encoder.py:95-201 with enc_st_combine == 'none'."
+
+    def __init__(self, size, attn, nb_attn, ff, nb_ff, dropout, args):
+        super(VidEncoderLayer4, self).__init__()
+        self.size = size
+        self.attn = clones(attn, nb_attn)
+        self.ff = clones(ff, nb_ff)
+        self.sublayer = clones(SublayerConnection(size, dropout), nb_attn + nb_ff)
+        self.args = args
+        self.precision = "fp32"
+        if getattr(self.args, 'enc_st_combine', 'none') in ['early_sum', 'early_dyn']:
+            raise NotImplementedError(
+                "enc_st_combine=%r: the early_* modes only run with nb_blocks=1 in the reference "
+                "(SURVEY.md §8 a2) and are not built" % self.args.enc_st_combine)
+        self._packed = None          # (key, tensor)
+
+    def __deepcopy__(self, memo):
+        new = type(self).__new__(type(self))
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            new.__dict__[k] = None if k == "_packed" else copy.deepcopy(v, memo)
+        return new
+
+    # -- parameter hand-over ------------------------------------------------------------------
+    def _dims(self):
+        lin = self.attn[0].linears[0]
+        return lin.out_features, self.ff[0].w_1.out_features, self.attn[0].h
+
+    def _n_dirs(self):
+        if len(self.attn) == 6 and len(self.ff) == 2:
+            return 2
+        if len(self.attn) == 3 and len(self.ff) == 1:
+            return 1
+        raise ValueError("VidEncoderLayer4 needs 6 attn / 2 ff or 3 attn / 1 ff clones (mtn.py:123-128)")
+
+    def packed_weights(self):
+        """Pack (and cache until a parameter changes) the layer weights for the kernels."""
+        params = list(self.parameters())
+        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
+        if self._packed is not None and self._packed[0] == key:
+            return self._packed[1]
+        d, d_ff, h = self._dims()
+        nd = self._n_dirs()
+        dt = _lib.BF16 if self.precision == "bf16" else _lib.F32
+        P = _lib.StLayerParams()
+        for i, a in enumerate(self.attn):
+            for j, lin in enumerate(a.linears):
+                if lin.in_features != d or lin.out_features != d:
+                    raise ValueError("VidEncoderLayer4 kernels need d_in == d_model attention clones")
+                P.attn_w[i][j] = lin.weight.data_ptr()
+                P.attn_b[i][j] = lin.bias.data_ptr()
+        for i, f in enumerate(self.ff):
+            P.ff_w1[i], P.ff_b1[i] = f.w_1.weight.data_ptr(), f.w_1.bias.data_ptr()
+            P.ff_w2[i], P.ff_b2[i] = f.w_2.weight.data_ptr(), f.w_2.bias.data_ptr()
+        for i, s in enumerate(self.sublayer):
+            P.ln_a[i], P.ln_b[i] = s.norm.a_2.data_ptr(), s.norm.b_2.data_ptr()
+        L = _lib.lib()
+        nbytes = L.bist_st_layer_packed_bytes(d, d_ff, nd, dt)
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+        _lib.check(L.bist_st_layer_pack(ctypes.byref(P), _lib.ptr(buf), nbytes, d, d_ff, h, nd, dt,
+                                        _lib.stream_ptr()), "bist_st_layer_pack")
+        self._packed = (key, buf)
+        return buf
+
+    # -- forward ------------------------------------------------------------------------------
+    def forward(self, in_ft, ft, b):
+        _eval_only(self)
+        vft = ft['spatiotemporal_ft']
+        _lib.require_cuda(vft, self.attn[0].linears[0].weight)
+        run_t2s = (not hasattr(self.args, 't2s')) or bool(self.args.t2s)      # encoder.py:174
+        run_s2t = (not hasattr(self.args, 's2t')) or bool(self.args.s2t)      # encoder.py:182
+        dir_mask = (1 if run_t2s else 0) | (2 if run_s2t else 0)
+        if dir_mask == 0:
+            return in_ft
+        vdt = _lib.dtype_code(vft.dtype)
+        want = _lib.BF16 if self.precision == "bf16" else _lib.F32
+        if vdt != want:
+            raise TypeError("ft['spatiotemporal_ft'] is %s but this layer's precision is %s" % (vft.dtype, self.precision))
+        vft = vft.detach().contiguous()
+        B, T, S, d = vft.shape
+        d_model, d_ff, h = self._dims()
+        if d != d_model:
+            raise ValueError("video feature width %d != d_model %d" % (d, d_model))
+        nd = self._n_dirs()
+        x_t2s = in_ft['t2s'].detach().float().contiguous() if run_t2s else None
+        x_s2t = in_ft['s2t'].detach().float().contiguous() if run_s2t else None
+        Lq = (x_t2s if run_t2s else x_s2t).shape[1]
+        qm = _mask_bytes(b.query_mask, B, Lq)
+        tm = _mask_bytes(b.temporal_mask, B, T)
+        o_t2s = torch.empty_like(x_t2s) if run_t2s else None
+        o_s2t = torch.empty_like(x_s2t) if run_s2t else None
+        packed = self.packed_weights()
+        L = _lib.lib()
+        ws = _ws(L.bist_st_layer_workspace_bytes(B, T, S, Lq, d, d_ff, h, nd, vdt), vft.device)
+        _lib.check(L.bist_st_layer_fwd(_lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft), _lib.ptr(qm), _lib.ptr(tm),
+                                       _lib.ptr(packed), _lib.ptr(o_t2s), _lib.ptr(o_s2t), B, T, S, Lq, d, d_ff, h,
+                                       nd, dir_mask, float(self.sublayer[0].norm.eps), _lib.ptr(ws), ws.numel(),
+                                       vdt, _lib.stream_ptr()), "bist_st_layer_fwd")
+        if run_t2s:
+            in_ft['t2s'] = o_t2s
+        if run_s2t:
+            in_ft['s2t'] = o_s2t
+        return in_ft
+
+
+class _DecoderSlice(nn.Module):
+    """The members of MultimodalDecoder8 that belong to the video path (decoder.py:73-77)."""
+
+    def __init__(self, v_layer, v_N, size):
+        super(_DecoderSlice, self).__init__()
+        self.v_layers = clones(v_layer, v_N)
+        self.spatial_out_norm = LayerNorm(size)
+        self.temporal_out_norm = LayerNorm(size)
+
+
+class VideoPath(nn.Module):
+    """vid_encoder + v_layers + output norms, keyed like the reference ``MTN.state_dict()``.
+
+    forward(b, encoded_query) follows mtn.py:49-51 and decoder.py:107-129 and returns ``ft`` with
+    'spatiotemporal_ft', 'temporal_ft' (if s2t) and 'spatial_ft' (if t2s), plus the raw streams
+    under 't2s' / 's2t'.
+    """
+
+    def __init__(self, d_model=512, h=8, n_blocks=3, ft_size=2048, t2s=1, s2t=1, d_ff=None, dropout=0.1,
+                 precision="fp32"):
+        super(VideoPath, self).__init__()
+        from argparse import Namespace
+        from .modules import MultiHeadedAttention, PositionwiseFeedForward
+        args = Namespace(t2s=t2s, s2t=s2t, enc_st_combine='none')
+        self.args = args
+        attn = MultiHeadedAttention(h, d_model)                              # mtn.py:77
+        ff = PositionwiseFeedForward(d_model, d_ff or 4 * d_model, dropout)   # mtn.py:70,78
+        nb_attn, nb_ff = (6, 2) if (t2s and s2t) else (3, 1)                 # mtn.py:123-128
+        self.vid_encoder = VidEncoder8(nn.Linear(ft_size, d_model), None, None, n_blocks, 0, d_model, args)
+        v_layer = VidEncoderLayer4(d_model, attn, nb_attn, ff, nb_ff, dropout, args)
+        self.mutlimodal_decoder = _DecoderSlice(v_layer, n_blocks, d_model)   # (sic) the reference's spelling
+        set_precision(self, precision)
+        self.eval()
+
+    def forward(self, b, encoded_query):
+        ft = {'encoded_query': encoded_query}
+        ft = self.vid_encoder(b, ft)                                          # mtn.py:49-51
+        dec = self.mutlimodal_decoder
+        in_ft = {'t2s': encoded_query, 's2t': encoded_query}                  # decoder.py:109-110
+        for layer in dec.v_layers:
+            in_ft = layer(in_ft, ft, b)                                       # decoder.py:116
+        if self.args.s2t:
+            ft['temporal_ft'] = dec.temporal_out_norm(in_ft['s2t'])           # decoder.py:127
+            ft['s2t'] = in_ft['s2t']
+        if self.args.t2s:
+            ft['spatial_ft'] = dec.spatial_out_norm(in_ft['t2s'])             # decoder.py:129
+            ft['t2s'] = in_ft['t2s']
+        return ft

@@ -1,0 +1,170 @@
+/*
+ * bist_b200.h — C ABI of libbist_b200.so: the B200 (sm_100a) implementation of the BiST
+ * video hot path.  The reference (salesforce/BiST) has no FFI of its own:
+ * its boundary is the Python nn.Module protocol of model/modules.py and model/encoder.py.
+ * Each entry point below therefore replaces the *body* of one reference forward(); the
+ * Python mirror in bist_b200/{modules,encoder}.py keeps the reference's constructor and
+ * forward signatures and calls these functions through ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless it is named host_*; tensors are dense,
+ *     row-major, innermost dimension contiguous; 16-byte aligned base addresses
+ *   - the library never allocates or frees device memory and keeps no pointer after a
+ *     call returns; scratch is passed in (`ws`, sized by the *_workspace_bytes helpers)
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing
+ *     synchronises the host
+ *   - return value: 0 = success, non-zero = bist_status_t error; the message is available
+ *     from bist_last_error() (thread-local).  Nothing throws across the ABI.  There is no
+ *     CPU or eager fallback: unsupported shapes/dtypes are errors.
+ *   - dtype arguments take bist_dtype_t values.  "bf16 mode" (BIST_BF16) stores the large
+ *     activations and the weights in bf16 and accumulates/normalises/softmaxes in fp32;
+ *     LayerNorm gains/offsets and biases are always fp32.
+ */
+#ifndef BIST_B200_H_
+#define BIST_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BIST_B200_VERSION 100 /* 0.1.0 */
+
+typedef enum { BIST_F32 = 0, BIST_BF16 = 1 } bist_dtype_t;
+
+typedef enum {
+  BIST_OK = 0,
+  BIST_ERR_ARG = 1,       /* null pointer, bad shape, bad enum            */
+  BIST_ERR_UNSUPPORTED = 2, /* legal in the reference, not built here     */
+  BIST_ERR_WORKSPACE = 3, /* ws too small                                 */
+  BIST_ERR_CUDA = 4,      /* a CUDA runtime/driver call failed            */
+  BIST_ERR_DEVICE = 5     /* not an sm_100 device                         */
+} bist_status_t;
+
+/* mask_mode of bist_mha_fwd */
+typedef enum {
+  BIST_MASK_NONE = 0, /* mask == NULL                                            */
+  BIST_MASK_KEY = 1,  /* uint8 [Bp, Lk]      (reference mask [Bp,1,Lk])          */
+  BIST_MASK_FULL = 2  /* uint8 [Bp, Lq, Lk]  (reference mask [Bp,Lq,Lk])         */
+} bist_mask_mode_t;
+
+int bist_version(void);
+const char* bist_last_error(void);
+/* 0 when the current CUDA device is compute capability 10.x, BIST_ERR_DEVICE otherwise. */
+int bist_device_check(void);
+/* Number of kernels this library has launched in this process (bench.py "gpu_launches"). */
+int64_t bist_launch_count(void);
+/* Per-launch CUDA-event timing for bench.py's roofline line (off by default, adds two event
+ * records per launch).  bist_prof_collect synchronises the device and writes one
+ * "tag,launches,total_ms\n" line per kernel tag into the HOST buffer `host_buf`. */
+int bist_prof_enable(int on);
+int bist_prof_collect(char* host_buf, size_t cap);
+
+/* ---------------------------------------------------------------------------------------
+ * LayerNorm.forward — /root/reference/model/modules.py:28-31
+ *   y = a_2 * (x - mean) / (std + eps) + b_2, std unbiased (divide by d-1), eps on the std.
+ *   x,y [rows, d]; a_2,b_2 fp32 [d].
+ */
+int bist_ln_fwd(const void* x, const float* a_2, const float* b_2, void* y, int64_t rows,
+                int64_t d, float eps, int x_dtype, int y_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * nn.Linear (+ReLU) (+residual) — the building block of modules.py:74-77,100,106-113
+ *   y[M,N] = act(x[M,K] . w[N,K]^T + bias[N]) (+ residual[M,N]);  bias/residual may be NULL.
+ */
+int bist_linear_fwd(const void* x, const void* w, const float* bias, const void* residual,
+                    void* y, int64_t M, int64_t N, int64_t K, int relu, int x_dtype,
+                    int w_dtype, int y_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * MultiHeadedAttention.forward — modules.py:81-100 (+ attention(), modules.py:54-64), eval
+ * mode (dropout identity).
+ *   query [Bp,Lq,d_in], key/value [Bp,Lk,d_in] (dtype `dtype`); w[0..2] [d,d_in], w[3]
+ *   [d_in,d] (dtype `dtype`), b[0..3] fp32; mask per mask_mode (0 = masked -> -1e9);
+ *   out [Bp,Lq,d_in]; attn_out (may be NULL) fp32 [Bp,h,Lq,Lk] = the reference's `.attn`.
+ */
+typedef struct {
+  const void* w[4];
+  const float* b[4];
+} bist_mha_params_t;
+
+size_t bist_mha_workspace_bytes(int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int64_t d_in,
+                                int64_t h);
+int bist_mha_fwd(const void* query, const void* key, const void* value, const uint8_t* mask,
+                 int mask_mode, const bist_mha_params_t* host_params, void* out,
+                 float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int64_t d_in,
+                 int64_t h, void* ws, size_t ws_bytes, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * PositionwiseFeedForward.forward — modules.py:112-113 (eval): y = w_2(relu(w_1 x)).
+ *   x [rows,d]; w1 [d_ff,d]; w2 [d_out,d_ff]; b1,b2 fp32; y [rows,d_out].
+ *   ws >= rows*d_ff*sizeof(dtype).
+ */
+int bist_ffn_fwd(const void* x, const void* w1, const float* b1, const void* w2,
+                 const float* b2, void* y, int64_t rows, int64_t d, int64_t d_ff,
+                 int64_t d_out, void* ws, size_t ws_bytes, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * VidEncoder8.forward, video branch — /root/reference/model/encoder.py:72-80
+ *   out[n,:] = LayerNorm(relu(fts[n,:] . W^T + bias))       (vid_position is always None)
+ *   fts fp32 [N, D] (N = B*T*S rows of the [B,T,S,D] tensor); W fp32 [d, D]; bias, a_2, b_2
+ *   fp32 [d]; out [N, d] of out_dtype.  compute_dtype BIST_F32: fp32-accurate contraction;
+ *   BIST_BF16: bf16 operands, fp32 accumulate.  The same call serves the audio branch
+ *   (encoder.py:83-91) with D = 128.
+ */
+size_t bist_vidproj_workspace_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype);
+int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const float* a_2,
+                     const float* b_2, void* out, int64_t N, int64_t D, int64_t d, float eps,
+                     void* ws, size_t ws_bytes, int compute_dtype, int out_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * VidEncoderLayer4.forward with enc_st_combine == 'none' — encoder.py:172-201, including
+ * temporal2spatial (encoder.py:109-139) and spatial2temporal (encoder.py:141-170), eval mode.
+ *
+ * Parameters are handed over once per weight update as fp32 device pointers in the
+ * reference's clone order (state_dict names attn.{i}.linears.{j}, ff.{i}.w_{1,2},
+ * sublayer.{i}.norm) and packed by bist_st_layer_pack into `packed` (layout private to the
+ * library: fused QKV rows, pre-scaled transposed key weights for the query-side fold, one
+ * direction after the other at a constant stride).  n_dirs = 2 -> 6 attn / 2 ff / 8 norms
+ * (direction 0 = t2s, 1 = s2t); n_dirs = 1 -> 3 attn / 1 ff / 4 norms (mtn.py:123-128).
+ */
+typedef struct {
+  const float* attn_w[6][4]; /* attn.{i}.linears.{j}.weight [d,d] */
+  const float* attn_b[6][4]; /* attn.{i}.linears.{j}.bias   [d]   */
+  const float* ff_w1[2];     /* ff.{i}.w_1.weight [d_ff,d]        */
+  const float* ff_b1[2];
+  const float* ff_w2[2];     /* ff.{i}.w_2.weight [d,d_ff]        */
+  const float* ff_b2[2];
+  const float* ln_a[8];      /* sublayer.{i}.norm.a_2 [d]         */
+  const float* ln_b[8];
+} bist_st_layer_params_t;
+
+size_t bist_st_layer_packed_bytes(int64_t d, int64_t d_ff, int n_dirs, int dtype);
+int bist_st_layer_pack(const bist_st_layer_params_t* host_params, void* packed,
+                       size_t packed_bytes, int64_t d, int64_t d_ff, int64_t h, int n_dirs,
+                       int dtype, void* stream);
+
+size_t bist_st_layer_workspace_bytes(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d,
+                                     int64_t d_ff, int64_t h, int n_dirs, int dtype);
+/*
+ *   in_t2s / in_s2t   fp32 [B,Lq,d]   in_ft['t2s'], in_ft['s2t'] (may alias each other)
+ *   vft               dtype [B,T,S,d]  ft['spatiotemporal_ft'] (read-only)
+ *   query_mask        uint8 [B,Lq]     b.query_mask [B,1,Lq]
+ *   temporal_mask     uint8 [B,T]      b.temporal_mask [B,1,T]
+ *   out_t2s / out_s2t fp32 [B,Lq,d]    new in_ft['t2s'], in_ft['s2t'] (must not alias inputs)
+ *   dir_mask          bit0 = run t2s, bit1 = run s2t.  With n_dirs == 1 the single packed
+ *                     direction is applied to whichever one bit is set.
+ */
+int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const void* vft,
+                      const uint8_t* query_mask, const uint8_t* temporal_mask,
+                      const void* packed, float* out_t2s, float* out_s2t, int64_t B, int64_t T,
+                      int64_t S, int64_t Lq, int64_t d, int64_t d_ff, int64_t h, int n_dirs,
+                      int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BIST_B200_H_ */
