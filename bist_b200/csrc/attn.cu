@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) softmax_pv_kernel(SoftmaxPvArgs a, int LT
     const uint8_t* mrow = Mg ? Mg + (long long)l * a.m_l : nullptr;
     float mx = -INFINITY;
     for (int k = lane; k < nk; k += 32) {
-      float s = srow[k];
+      float s = srow[(long long)k * a.s_k];
       if (mrow && mrow[k] == 0) s = kMaskFill;
       Ps[(hh * nk + k) * LTP + li] = s;
       mx = fmaxf(mx, s);
@@ -114,9 +114,9 @@ int launch_softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
 
 // ---------------------------------------------------------------------------------------------
 // grid B*Lq; block 256.  smem: qf[h][d] + sc[h][G].
-template <typename TX, int HC>
+template <typename TX, typename TO, int HC>
 __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ qf, const TX* __restrict__ x1,
-                                                     const uint8_t* __restrict__ mask, float* __restrict__ ctxx,
+                                                     const uint8_t* __restrict__ mask, TO* __restrict__ ctxx,
                                                      int B, int G, int Lq, int h, int d) {
   extern __shared__ __align__(16) float sm[];
   float* q = sm;           // [h][d]
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
   }
   __syncthreads();
   // weighted sums: thread per column
-  float* out = ctxx + (long long)blockIdx.x * h * d;
+  TO* out = ctxx + (long long)blockIdx.x * h * d;
   for (int c = threadIdx.x; c < d; c += blockDim.x) {
     for (int h0 = 0; h0 < h; h0 += HC) {
       float acc[HC];
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
       }
 #pragma unroll
       for (int i = 0; i < HC; ++i)
-        if (h0 + i < h) out[(long long)(h0 + i) * d + c] = acc[i];
+        if (h0 + i < h) out[(long long)(h0 + i) * d + c] = from_f32<TO>(acc[i]);
     }
   }
 }
@@ -206,8 +206,20 @@ int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
   return launch_softmax_pv<float, __nv_bfloat16>(a, st);
 }
 
-int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, float* ctxx, int B, int G, int Lq, int h,
-                int d, int x1_dtype, cudaStream_t st) {
+template <typename TX, typename TO>
+int launch_stage2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
+                  size_t smem, cudaStream_t st) {
+  auto kern = stage2_kernel<TX, TO, 8>;
+  if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  ProfScope ps("stage2_attn", st);
+  kern<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), B, G,
+                                                   Lq, h, d);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
+                int x1_dtype, int ctxx_dtype, cudaStream_t st) {
   BIST_CHECK_ARG(qf && x1 && ctxx, "stage2: null pointer");
   BIST_CHECK_ARG(B > 0 && G > 0 && Lq > 0 && h > 0 && d > 0, "stage2: bad shape");
   const size_t smem = ((size_t)h * d + (size_t)h * G) * 4;
@@ -215,19 +227,11 @@ int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, float* ctx
     set_error("stage2: h*(d+G) too large");
     return BIST_ERR_UNSUPPORTED;
   }
-  dim3 grid((unsigned)(B * Lq));
-  ProfScope ps("stage2_attn", st);
-  if (x1_dtype == BIST_BF16) {
-    auto kern = stage2_kernel<__nv_bfloat16, 8>;
-    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    kern<<<grid, 256, smem, st>>>(qf, reinterpret_cast<const __nv_bfloat16*>(x1), mask, ctxx, B, G, Lq, h, d);
-  } else {
-    auto kern = stage2_kernel<float, 8>;
-    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    kern<<<grid, 256, smem, st>>>(qf, reinterpret_cast<const float*>(x1), mask, ctxx, B, G, Lq, h, d);
-  }
-  BIST_LAUNCHED();
-  return 0;
+  const bool xb = x1_dtype == BIST_BF16, ob = ctxx_dtype == BIST_BF16;
+  if (xb && ob) return launch_stage2<__nv_bfloat16, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
+  if (xb) return launch_stage2<__nv_bfloat16, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
+  if (ob) return launch_stage2<float, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
+  return launch_stage2<float, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
 }
 
 int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, float scale, int dst_dtype,

@@ -149,6 +149,7 @@ struct GemmArgs {
   float alpha = 1.f;
   int relu = 0;
   const char* tag = "gemm";  // label for bist_prof_collect
+  int allow_tf32 = 0;        // fp32 operands may be multiplied as tf32 on the tensor cores
   int a_dtype = BIST_F32, w_dtype = BIST_F32, c_dtype = BIST_F32, r_dtype = BIST_F32;
 };
 int gemm(const GemmArgs& g, cudaStream_t st);       // dispatches to the kernels below
@@ -166,7 +167,8 @@ int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t
 struct SoftmaxPvArgs {
   const float* S = nullptr;
   RowMap sg{kNoSplit, 0, 0, kNoSplit};  // group g -> base offset of S
-  long long s_l = 0, s_h = 0;  // strides of the (l, h) row of S; keys contiguous
+  long long s_l = 0, s_h = 0;  // strides of the (l, h) row of S
+  long long s_k = 1;           // stride between consecutive keys of a group
   const uint8_t* mask = nullptr;  // null or uint8, 0 = masked
   int mask_gdiv = 1, mask_gmod = kNoSplit;  // mask batch index = (g / mask_gdiv) % mask_gmod
   long long m_b = 0, m_l = 0;  // mask strides (batch, query row; m_l = 0 for key masks)
@@ -183,8 +185,8 @@ int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st);
 // ---- stage 2 of t2s / s2t: one query row attends over its G stage-1 summaries ---------------------
 // For every (b,l): scores[hh,g] = qf[b,l,hh,:] . X1[b,g,l,:] (qf pre-scaled), optional key mask
 // [B,G], softmax over g, ctxx[b,l,hh,:] = sum_g p[hh,g] X1[b,g,l,:]   (fp32 [B*Lq, h, d]).
-int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, float* ctxx, int B, int G,
-                int Lq, int h, int d, int x1_dtype, cudaStream_t st);
+int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G,
+                int Lq, int h, int d, int x1_dtype, int ctxx_dtype, cudaStream_t st);
 
 // ---- weight packing helpers ------------------------------------------------------------------
 // dst[r, c] = scale * src[r, c] (transpose = 0) or scale * src[c, r] (transpose = 1); dst is

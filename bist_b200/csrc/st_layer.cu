@@ -49,9 +49,10 @@ PackedLayout packed_layout(int64_t d, int64_t dff, int n_dirs, int dtype) {
 }
 
 struct Workspace {
-  float *nbuf, *qkv0, *sc0, *cbuf, *x, *qbuf, *qf, *ctxx2, *ts, *ffh;
+  // query-side activations: `act` buffers are GEMM operands (bf16 in bf16 mode), the rest fp32
+  void *nbuf, *qkv0, *cbuf, *qbuf, *qf1, *ctxx2, *ffh;  // act dtype
+  float *sc0, *x, *qf2, *ts, *sc1;                       // fp32
   void* xv;
-  float* sc1[2];
   void* ctx1[2];
   void* out1[2];
   size_t bytes;
@@ -64,14 +65,15 @@ Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   Workspace W;
   const size_t Q = (size_t)B * Lq, e = dtype_size(dtype);
   auto f = [&](size_t n) { return (float*)A.take(n * 4); };
-  W.nbuf = f(nd * Q * d); W.qkv0 = f(nd * Q * 3 * d); W.sc0 = f(nd * Q * h * Lq); W.cbuf = f(nd * Q * d);
-  W.x = f(nd * Q * d); W.qbuf = f(nd * Q * d); W.qf = f(nd * Q * h * d); W.ctxx2 = f(nd * Q * h * d);
-  W.ts = f(nd * Q * d); W.ffh = f(nd * Q * dff);
+  auto a = [&](size_t n) { return A.take(n * e); };
+  W.nbuf = a(nd * Q * d); W.qkv0 = a(nd * Q * 3 * d); W.cbuf = a(nd * Q * d); W.qbuf = a(nd * Q * d);
+  W.qf1 = a(nd * Q * h * d); W.ctxx2 = a(nd * Q * h * d); W.ffh = a(nd * Q * dff);
+  W.sc0 = f(nd * Q * h * Lq); W.x = f(nd * Q * d); W.qf2 = f(nd * Q * h * d); W.ts = f(nd * Q * d);
+  W.sc1 = f(nd * Q * h * T * S);
   W.xv = A.take((size_t)B * T * S * nd * d * e);
-  for (int u = 0; u < 2; ++u) { W.sc1[u] = nullptr; W.ctx1[u] = W.out1[u] = nullptr; }
+  for (int u = 0; u < 2; ++u) W.ctx1[u] = W.out1[u] = nullptr;
   for (int u = 0; u < nd; ++u) {
     const size_t G = kinds[u] == 0 ? S : T;
-    W.sc1[u] = f(Q * h * T * S);
     W.ctx1[u] = A.take((size_t)B * G * Lq * d * e);
     W.out1[u] = A.take((size_t)B * G * Lq * d * e);
   }
@@ -197,75 +199,79 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   const PackedLayout L = packed_layout(d, dff, n_dirs, dtype);
   const int pu0 = n_dirs == 2 ? kinds[0] : 0;  // packed index of slot 0; slot 1 is pu0 + 1
   const size_t e = dtype_size(dtype);
+  const int adt = dtype;  // dtype of the activations that feed GEMMs
   const char* mat = (const char*)packed + (size_t)pu0 * L.dir_stride * e;
   const float* fs = (const float*)((const char*)packed + L.f_byte_off) + (size_t)pu0 * L.fdir_stride;
   auto Mw = [&](size_t off) { return (const void*)(mat + off * e); };
+  auto act = [&](void* p, long long elems) { return (void*)((char*)p + elems * (long long)e); };
   const long long ms = (long long)L.dir_stride, fsd = (long long)L.fdir_stride;
   const int Q = (int)(B * Lq), dk = (int)(d / h), di = (int)d, hi = (int)h;
   const long long Qd = (long long)Q * d;
 
-  // Batched (over the active directions) linear layer on [Q, K] fp32 activations in the workspace.
-  auto lin = [&](const float* Ain, long long a_dir, size_t w_off, size_t b_off, float* Cout, long long c_dir, int N,
-                 int K, int relu, const float* R, long long r_dir) {
+  // Batched (over the active directions) linear layer  C[u] = act(A[u] . W[u]^T + b[u]) (+ R[u]).
+  auto lin = [&](const void* Ain, long long a_dir, size_t w_off, size_t b_off, void* Cout, long long c_dir, int c_dtype,
+                 int N, int K, int relu, const float* R, long long r_dir) {
     GemmArgs g;
     g.A = Ain; g.W = Mw(w_off); g.C = Cout; g.bias = fs + b_off; g.R = R;
     g.M = Q; g.N = N; g.K = K;
     g.a = rows_dense(K); g.w = rows_dense(K); g.c = rows_dense(N); g.r = rows_dense(N);
     g.Z = nd; g.zin = 1;
     g.az = {a_dir, 0}; g.wz = {ms, 0}; g.cz = {c_dir, 0}; g.rz = {r_dir, 0}; g.bz = {fsd, 0};
-    g.relu = relu; g.w_dtype = dtype; g.tag = "query_side_gemm";
+    g.relu = relu; g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = c_dtype; g.tag = "query_side_gemm";
     return gemm(g, st);
   };
   // Query-side fold of a key projection: qf[u][q,hh,:] = q[u][q, hh*dk:(hh+1)*dk] . WkT[u][:, hh*dk:(hh+1)*dk]^T
-  auto fold = [&](size_t wkt_off) {
+  auto fold = [&](size_t wkt_off, void* out, int out_dtype) {
     GemmArgs g;
-    g.A = W.qbuf; g.W = Mw(wkt_off); g.C = W.qf;
+    g.A = W.qbuf; g.W = Mw(wkt_off); g.C = out;
     g.M = Q; g.N = di; g.K = dk;
     g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(h * d);
     g.Z = nd * hi; g.zin = hi;
     g.az = {Qd, dk}; g.wz = {ms, dk}; g.cz = {Qd * h, d};
-    g.w_dtype = dtype;
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = out_dtype; g.tag = "fold_gemm";
     return gemm(g, st);
   };
 
   // ---- self-attention over the query tokens (encoder.py:176 / :184) -------------------------------
   for (int u = 0; u < nd; ++u)
-    BIST_TRY(layer_norm(x_in[u], fs + u * fsd + L.ln_a, fs + u * fsd + L.ln_b, W.nbuf + u * Qd, Q, d, eps, BIST_F32,
-                        BIST_F32, st));
-  BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, 3 * di, di, 0, nullptr, 0));
+    BIST_TRY(layer_norm(x_in[u], fs + u * fsd + L.ln_a, fs + u * fsd + L.ln_b, act(W.nbuf, u * Qd), Q, d, eps, BIST_F32,
+                        adt, st));
+  BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0));
   {
     GemmArgs g;  // scores[u,b,l,hh,k] = q.k / sqrt(dk)
-    g.A = W.qkv0; g.W = W.qkv0 + d; g.C = W.sc0;
+    g.A = W.qkv0; g.W = act(W.qkv0, d); g.C = W.sc0;
     g.M = (int)Lq; g.N = (int)Lq; g.K = dk;
     g.a = rows_dense(3 * d); g.w = rows_dense(3 * d); g.c = rows_dense(h * Lq);
     g.Z = (int)(nd * B * h); g.zin = hi;
     g.az = {Lq * 3 * d, dk}; g.wz = {Lq * 3 * d, dk}; g.cz = {Lq * h * Lq, Lq};
     g.alpha = 1.f / sqrtf((float)dk);
+    g.a_dtype = adt; g.w_dtype = adt; g.tag = "scores0_gemm";
     BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B*h too large");
-    BIST_TRY(gemm(g, st));
+    BIST_TRY(gemm_simt(g, st));  // 16x16x64 products: CUDA cores
     SoftmaxPvArgs a;
     a.S = W.sc0; a.sg = rows_dense(Lq * h * Lq); a.s_l = h * Lq; a.s_h = Lq;
     a.mask = query_mask; a.mask_gmod = (int)B; a.m_b = Lq; a.m_l = 0;
-    a.V = W.qkv0 + 2 * d; a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
+    a.V = act(W.qkv0, 2 * d); a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
     a.ctx = W.cbuf;
     a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
+    a.v_dtype = adt; a.ctx_dtype = adt;
     BIST_TRY(softmax_pv(a, st));
   }
   // output projection + residual with the (possibly aliased, not strided) layer inputs (modules.py:44)
   for (int u = 0; u < nd; ++u) {
     GemmArgs g;
-    g.A = W.cbuf + u * Qd; g.W = Mw(L.wo0 + (size_t)u * L.dir_stride); g.C = W.x + u * Qd;
+    g.A = act(W.cbuf, u * Qd); g.W = Mw(L.wo0 + (size_t)u * L.dir_stride); g.C = W.x + u * Qd;
     g.bias = fs + u * fsd + L.bo0; g.R = x_in[u];
     g.M = Q; g.N = di; g.K = di;
     g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
-    g.w_dtype = dtype;
+    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "query_side_gemm";
     BIST_TRY(gemm(g, st));
   }
 
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
-  BIST_TRY(layer_norm(W.x, fs + L.ln_a + d, fs + L.ln_b + d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.wq1, L.bq1, W.qbuf, Qd, di, di, 0, nullptr, 0));
-  BIST_TRY(fold(L.wkt1));
+  BIST_TRY(layer_norm(W.x, fs + L.ln_a + d, fs + L.ln_b + d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.wq1, L.bq1, W.qbuf, Qd, adt, di, di, 0, nullptr, 0));
+  BIST_TRY(fold(L.wkt1, W.qf1, adt));
   const long long TS = T * S, xvld = (long long)nd * d;
   {
     GemmArgs g;  // values of every video row for the active directions: XV = vft . [Wv1]^T + bv1
@@ -276,20 +282,24 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
     BIST_TRY(gemm(g, st));
   }
+  {
+    GemmArgs g;  // scores1[u,b,(l,hh),(t,s)] = qf1[u,b,(l,hh),:] . vft[b,t,s,:]  — one launch, video rows in place
+    g.A = W.qf1; g.W = vft; g.C = W.sc1;
+    g.M = (int)(Lq * h); g.N = (int)TS; g.K = di;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(TS);
+    g.Z = (int)(nd * B); g.zin = (int)B;
+    g.az = {Qd * h, Lq * h * d}; g.wz = {0, TS * d}; g.cz = {(long long)Q * h * TS, Lq * h * TS};
+    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
+    BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B too large");
+    BIST_TRY(gemm(g, st));
+  }
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
-    GemmArgs g;  // scores1[b, (l,hh), key-ordered video rows] = qf . x   (keys contiguous per group)
-    g.A = W.qf + u * Qd * h; g.W = vft; g.C = W.sc1[u];
-    g.M = (int)(Lq * h); g.N = (int)TS; g.K = di;
-    g.a = rows_dense(d); g.c = rows_dense(TS);
-    g.w = t2s ? rows_2level((int)T, d, S * d) : rows_dense(d);  // t2s walks rows as (s, t)
-    g.Z = (int)B; g.zin = 1;
-    g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
-    g.w_dtype = dtype; g.tag = "scores1_gemm";
-    BIST_TRY(gemm(g, st));
     SoftmaxPvArgs a;
-    a.S = W.sc1[u]; a.sg = rows_2level(G, Lq * h * TS, nk); a.s_l = h * TS; a.s_h = TS;
+    a.S = W.sc1 + (long long)u * Q * h * TS;
+    // group (b, s) for t2s: keys are the T clips of region s (stride S); group (b, t) for s2t: its S regions
+    a.sg = rows_2level(G, Lq * h * TS, t2s ? 1 : S); a.s_l = h * TS; a.s_h = TS; a.s_k = t2s ? S : 1;
     if (t2s) { a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0; }  // encoder.py:117-121
     a.V = (const char*)W.xv + (size_t)u * d * e;
     a.vg = t2s ? rows_2level((int)S, TS * xvld, xvld) : rows_dense(S * xvld);
@@ -309,13 +319,13 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   }
 
   // ---- stage 2 (encoder.py:125-132 / :152-161) ------------------------------------------------------
-  BIST_TRY(layer_norm(W.x, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.wq2, L.bq2, W.qbuf, Qd, di, di, 0, nullptr, 0));
-  BIST_TRY(fold(L.wkt2));
+  BIST_TRY(layer_norm(W.x, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.wq2, L.bq2, W.qbuf, Qd, adt, di, di, 0, nullptr, 0));
+  BIST_TRY(fold(L.wkt2, W.qf2, BIST_F32));
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
-    BIST_TRY(stage2_attn(W.qf + u * Qd * h, W.out1[u], t2s ? nullptr : temporal_mask, W.ctxx2 + u * Qd * h, (int)B,
-                         (int)(t2s ? S : T), (int)Lq, hi, di, dtype, st));
+    BIST_TRY(stage2_attn(W.qf2 + u * Qd * h, W.out1[u], t2s ? nullptr : temporal_mask, act(W.ctxx2, u * Qd * h), (int)B,
+                         (int)(t2s ? S : T), (int)Lq, hi, di, dtype, adt, st));
   }
   {
     GemmArgs g;  // value projection after the weighted sum: ctx2[q, hh*dk+j] = ctxx2[q,hh,:] . Wv2[hh*dk+j,:] + bv2
@@ -324,21 +334,21 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.a = rows_dense(h * d); g.w = rows_dense(d); g.c = rows_dense(d);
     g.Z = nd * hi; g.zin = hi;
     g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.bz = {fsd, dk};
-    g.w_dtype = dtype;
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "vfold2_gemm";
     BIST_TRY(gemm(g, st));
   }
-  BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, di, di, 0, W.x, Qd));
+  BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd));
 
   // ---- feed-forward (encoder.py:134-135 / :165-166) -----------------------------------------------
-  BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, BIST_F32, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, (int)dff, di, 1, nullptr, 0));
+  BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
+  BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0));
   for (int u = 0; u < nd; ++u) {
     GemmArgs g;
-    g.A = W.ffh + (long long)u * Q * dff; g.W = Mw(L.w2 + (size_t)u * L.dir_stride); g.C = x_out[u];
+    g.A = act(W.ffh, (long long)u * Q * dff); g.W = Mw(L.w2 + (size_t)u * L.dir_stride); g.C = x_out[u];
     g.bias = fs + u * fsd + L.b2; g.R = W.ts + u * Qd;
     g.M = Q; g.N = di; g.K = (int)dff;
     g.a = rows_dense(dff); g.w = rows_dense(dff); g.c = rows_dense(d); g.r = rows_dense(d);
-    g.w_dtype = dtype;
+    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "query_side_gemm";
     BIST_TRY(gemm(g, st));
   }
   return 0;

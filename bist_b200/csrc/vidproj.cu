@@ -24,18 +24,17 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
   float* act = (float*)A.take((size_t)N * d * 4);
   void* wb = compute_dtype == BIST_BF16 ? A.take((size_t)d * D * 2) : nullptr;
   if (!A.ok) { set_error("vidproj: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+  // bf16 mode: the fp32 features are read once from HBM and multiplied as tf32 on the tensor cores
+  // (kind::tf32 reads the fp32 bits directly, so no conversion pass and no bf16 copy of fts exists).
+  (void)wb;
   const void* w_used = W;
-  int w_dtype = BIST_F32;
-  if (compute_dtype == BIST_BF16) {
-    BIST_TRY(pack_matrix(W, wb, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
-    w_used = wb;
-    w_dtype = BIST_BF16;
-  }
+  const int w_dtype = BIST_F32;
   GemmArgs g;  // encoder.py:75 — relu(W fts + b)
   g.A = fts; g.W = w_used; g.C = act; g.bias = bias;
   g.M = (int)N; g.N = (int)d; g.K = (int)D;
   g.a = rows_dense(D); g.w = rows_dense(D); g.c = rows_dense(d);
   g.relu = 1; g.w_dtype = w_dtype; g.tag = "vidproj_gemm";
+  g.allow_tf32 = compute_dtype == BIST_BF16;
   BIST_TRY(gemm(g, st));
   return layer_norm(act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                  // :80
 }
