@@ -1,14 +1,18 @@
 // tcgen05 / TMEM / TMA GEMM for sm_100a:  C = act(alpha * A . W^T + bias) + R
 //   A [M,K] and W [N,K] both K-major (dense rows), bf16 (kind::f16) or fp32 read as tf32
 //   (kind::tf32); fp32 accumulation in tensor memory.
-// One 128 x BN output tile per CTA, 192 threads, warp-specialised:
+// Persistent kernel: each CTA walks 128 x BN output tiles (n fastest, so concurrently resident CTAs
+// share A rows and the whole of W in L2).  320 threads, warp-specialised:
 //   warp 0    TMA producer   cp.async.bulk.tensor (128B-swizzled, 128-byte-wide K slabs) -> smem ring
-//   warp 1    MMA issuer     one elected lane issues tcgen05.mma (UMMA 128 x BN x 16|8) into TMEM;
-//                            tcgen05.commit releases ring slots and publishes the accumulator;
-//                            the warp also owns tcgen05.alloc / dealloc
-//   warps 2-5 epilogue       tcgen05.ld (32 lanes x 32 columns) -> registers -> alpha / bias / ReLU /
-//                            residual -> global; each thread owns one output row
-// The ring is synchronised with mbarriers (full: TMA complete_tx; empty: tcgen05.commit).
+//   warp 1    MMA issuer     one elected lane issues tcgen05.mma (UMMA 128 x BN x 16|8) into one of TWO
+//                            TMEM accumulator stages; tcgen05.commit releases ring slots and publishes
+//                            the accumulator; the warp also owns tcgen05.alloc / dealloc
+//   warps 2-9 epilogue       tcgen05.ld (32 lanes x 32 columns) -> per-warp smem transpose -> alpha / bias /
+//                            ReLU / residual and 16-byte coalesced row stores.  Two warps per TMEM lane
+//                            quarter (half of the columns each).  The epilogue of tile i overlaps the
+//                            MMAs of tile i+1 (other accumulator stage).
+// Barriers: full/empty per ring slot (TMA complete_tx / tcgen05.commit), acc_full/acc_empty per
+// accumulator stage (tcgen05.commit / one arrive per epilogue warp).
 #include "tc_ptx.cuh"
 
 #include <stdlib.h>
@@ -24,19 +28,34 @@ struct TcArgs {
   long long a_ld, w_ld;  // leading dimensions (elements) of the 2-D tensors the TMA maps describe
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
+  int tiles_m, tiles_n, total_tiles;
 };
+
+#ifdef BIST_GEMM_TRACE
+__device__ long long g_trace[3][64];   // CTA 0 only: [role][event]
+#define TRACE(role, idx) do { if (blockIdx.x == 0 && (idx) < 64) g_trace[role][idx] = clock64(); } while (0)
+#else
+#define TRACE(role, idx) do {} while (0)
+#endif
+
+constexpr int STG_LD = 36;  // floats per staging row: 16-byte aligned, conflict-free for float4 in both phases
 
 template <int BN, int STAGES>
 struct Smem {
   static constexpr int A_BYTES = BM * SLAB_BYTES, W_BYTES = BN * SLAB_BYTES;
   static constexpr int STAGE_BYTES = A_BYTES + W_BYTES;
-  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 1) * 8 + 16 + 1024;  // + alignment slack
+  static constexpr int STG_OFF = STAGES * STAGE_BYTES;           // 8 epilogue warps x [32][STG_LD] floats
+  static constexpr int BAR_OFF = STG_OFF + 8 * 32 * STG_LD * 4;
+  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
 };
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 template <int BN, int STAGES, bool TF32>
-__global__ void __launch_bounds__(192) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                      const __grid_constant__ CUtensorMap map_w, const TcArgs t) {
+__global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                         const __grid_constant__ CUtensorMap map_w, const TcArgs t) {
   using S = Smem<BN, STAGES>;
   constexpr int ESZ = TF32 ? 4 : 2;
   constexpr int BKE = SLAB_BYTES / ESZ;        // elements of K per slab: 64 bf16 / 32 tf32
@@ -45,37 +64,44 @@ __global__ void __launch_bounds__(192) gemm_tc_kernel(const __grid_constant__ CU
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + S::BAR_OFF);
   uint64_t* empty = full + STAGES;
-  uint64_t* acc_full = empty + STAGES;
-  uint32_t* tmem_slot = (uint32_t*)(acc_full + 1);
+  uint64_t* acc_full = empty + STAGES;   // [2]
+  uint64_t* acc_empty = acc_full + 2;    // [2]
+  uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
 
   const GemmArgs& g = t.g;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int z = blockIdx.z, m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(acc_full, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, BN);
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int per_z = t.tiles_m * t.tiles_n;
 
   if (warp == 0) {
     if (lane == 0) {
-      // batch offsets become (row, column) coordinates inside the 2-D tensors
-      const long long ao = g.az.off(z, g.zin), wo = g.wz.off(z, g.zin);
-      const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
-      const int w_row = (int)(wo / t.w_ld) + n0, w_col = (int)(wo % t.w_ld);
-      for (int kb = 0; kb < t.nkb; ++kb) {
-        const int s = kb % STAGES;
-        if (kb >= STAGES) mbar_wait(&empty[s], ((kb / STAGES) - 1) & 1);
-        mbar_expect_tx(&full[s], S::STAGE_BYTES);
-        uint8_t* st = smem + s * S::STAGE_BYTES;
-        tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-        tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x) {
+        const int z = tile / per_z, rem = tile - z * per_z;
+        const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
+        // batch offsets become (row, column) coordinates inside the 2-D tensors
+        const long long ao = g.az.off(z, g.zin), wo = g.wz.off(z, g.zin);
+        const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
+        const int w_row = (int)(wo / t.w_ld) + n0, w_col = (int)(wo % t.w_ld);
+        for (int kb = 0; kb < t.nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
+          mbar_expect_tx(&full[s], S::STAGE_BYTES);
+          uint8_t* st = smem + s * S::STAGE_BYTES;
+          tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+          tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          TRACE(0, it);
+        }
       }
     }
   } else if (warp == 1) {
@@ -83,77 +109,155 @@ __global__ void __launch_bounds__(192) gemm_tc_kernel(const __grid_constant__ CU
       // instruction descriptor (cute::UMMA::InstrDescriptor): D = f32, A/B = bf16 | tf32, K-major both
       const uint32_t fmt = TF32 ? 2u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      for (int kb = 0; kb < t.nkb; ++kb) {
-        const int s = kb % STAGES;
-        mbar_wait(&full[s], (kb / STAGES) & 1);
+      int it = 0, tc_ = 0;
+      for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x, ++tc_) {
+        const int a = tc_ & 1;
+        mbar_wait(&acc_empty[a], ((tc_ >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
-        const uint64_t ad = make_desc(sa), wd = make_desc(sa + S::A_BYTES);
+        const uint32_t tacc = tmem_base + (uint32_t)(a * BN);
+        for (int kb = 0; kb < t.nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&full[s], (it / STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+          const uint64_t ad = make_desc(sa), wd = make_desc(sa + S::A_BYTES);
 #pragma unroll
-        for (int k = 0; k < BKE / UMMA_K; ++k)  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
-          tc_mma<TF32>(tmem_base, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
-        tc_commit(&empty[s]);
+          for (int k = 0; k < BKE / UMMA_K; ++k)  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
+            tc_mma<TF32>(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          tc_commit(&empty[s]);
+          TRACE(1, it);
+        }
+        tc_commit(&acc_full[a]);
       }
-      tc_commit(acc_full);
     }
   } else {
-    // ---- epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32) ------------------------
-    const int lg = warp & 3;
-    const int row = m0 + lg * 32 + lane;
-    const bool row_ok = row < g.M;
-    mbar_wait(acc_full, 0);
-    tc_fence_after();
-    const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin) : nullptr;
-    const long long co = row_ok ? g.cz.off(z, g.zin) + g.c.off(row) : 0;
-    const long long ro = (row_ok && g.R) ? g.rz.off(z, g.zin) + g.r.off(row) : 0;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      if (n0 + c0 >= g.N) break;  // warp-uniform
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + c0, r);
-      if (!row_ok) continue;
-      const int col = n0 + c0;
-      if (t.vec_c && col + 32 <= g.N) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          float4 v = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                                 __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
-          v.x *= g.alpha; v.y *= g.alpha; v.z *= g.alpha; v.w *= g.alpha;
-          if (bias) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col + 4 * q));
-            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-          }
-          if (g.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-          if (g.R) {
-            const float4 x = g.r_dtype == BIST_BF16 ? ld4(reinterpret_cast<const __nv_bfloat16*>(g.R) + ro + col + 4 * q)
-                                                    : ld4(reinterpret_cast<const float*>(g.R) + ro + col + 4 * q);
-            v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
-          }
-          if (g.c_dtype == BIST_BF16) st4(reinterpret_cast<__nv_bfloat16*>(g.C) + co + col + 4 * q, v);
-          else st4(reinterpret_cast<float*>(g.C) + co + col + 4 * q, v);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int cc = col + j;
-          if (cc < g.N) {
-            float v = g.alpha * __uint_as_float(r[j]);
-            if (bias) v += bias[cc];
-            if (g.relu) v = fmaxf(v, 0.f);
-            if (g.R) v += g.r_dtype == BIST_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g.R)[ro + cc])
-                                                 : reinterpret_cast<const float*>(g.R)[ro + cc];
-            if (g.c_dtype == BIST_BF16) reinterpret_cast<__nv_bfloat16*>(g.C)[co + cc] = __float2bfloat16_rn(v);
-            else reinterpret_cast<float*>(g.C)[co + cc] = v;
-          }
-        }
+    // ---- epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); two warps per lane quarter,
+    // each owning half of the tile's columns.  All per-element arithmetic happens after the smem transpose,
+    // where a lane's 4 columns are fixed (one bias load per chunk) and rows are addressed through offsets
+    // computed once per tile (no integer division in the loop).
+    const int lg = warp & 3, ch = (warp - 2) >> 2;
+    const uint32_t stg = smem_u32(smem + S::STG_OFF) + (uint32_t)((warp - 2) * 32 * STG_LD * 4);
+    const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;  // phase-2 mapping: 4 rows x 8 float4 per instruction
+    const uint32_t stg_w = stg + (uint32_t)(lane * STG_LD * 4);                 // phase 1: thread = row
+    const uint32_t stg_r = stg + (uint32_t)((sub_r * STG_LD + sub_c) * 4);      // phase 2: + rr * 4 rows
+    constexpr int CH_COLS = BN / 2;
+    const float alpha = g.alpha;
+    const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M, Ntot = g.N;
+    const bool c_bf16 = g.c_dtype == BIST_BF16, r_bf16 = g.r_dtype == BIST_BF16, has_r = g.R != nullptr;
+    int tc_ = 0;
+    for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x, ++tc_) {
+      const int z = tile / per_z, rem = tile - z * per_z;
+      const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
+      const int a = tc_ & 1;
+      const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin) : nullptr;
+      const int row_w0 = m0 + lg * 32;  // first row of this warp
+      // lane i computes the element offsets of row row_w0 + i once per tile; the phase-2 owner of a row
+      // fetches them with shuffles (no integer division inside the chunk loop)
+      const int my_row = row_w0 + lane;
+      long long co_l = 0, ro_l = 0;
+      if (my_row < Mtot) {
+        co_l = g.cz.off(z, g.zin) + g.c.off(my_row);
+        if (has_r) ro_l = g.rz.off(z, g.zin) + g.r.off(my_row);
       }
+      long long co_r[8], ro_r[8];
+      bool ok_r[8];
+#pragma unroll
+      for (int rr = 0; rr < 8; ++rr) {
+        const int lr = rr * 4 + sub_r;
+        co_r[rr] = __shfl_sync(0xffffffffu, co_l, lr);
+        ro_r[rr] = __shfl_sync(0xffffffffu, ro_l, lr);
+        ok_r[rr] = row_w0 + lr < Mtot;
+      }
+      mbar_wait(&acc_full[a], (tc_ >> 1) & 1);
+      tc_fence_after();
+      if (warp == 2 && lane == 0) TRACE(2, 2 * tc_);
+      const uint32_t tacc = tmem_base + (uint32_t)(a * BN) + ((uint32_t)(lg * 32) << 16);
+#pragma unroll 1
+      for (int cj = 0; cj < CH_COLS; cj += 32) {
+        const int c0 = ch * CH_COLS + cj;
+        const int col = n0 + c0;
+        const bool live = col < Ntot;  // warp-uniform
+        uint32_t r[32];
+        if (live) tmem_ld32(tacc + c0, r);
+        if (cj + 32 >= CH_COLS) {  // last chunk of this warp: hand the accumulator stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[a]);
+        }
+        if (!live) continue;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg_w + 16 * q), "r"(r[4 * q]), "r"(r[4 * q + 1]),
+                       "r"(r[4 * q + 2]), "r"(r[4 * q + 3])
+                       : "memory");
+        __syncwarp();
+        if (vec_c && col + 32 <= Ntot) {
+          const int cc = col + sub_c;
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (bias) bv = __ldg(reinterpret_cast<const float4*>(bias + cc));
+          float4 v[8], x[8];
+          if (has_r) {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+              x[rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (ok_r[rr])
+                x[rr] = r_bf16 ? ld4(reinterpret_cast<const __nv_bfloat16*>(g.R) + ro_r[rr] + cc)
+                               : ld4(reinterpret_cast<const float*>(g.R) + ro_r[rr] + cc);
+            }
+          }
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr)
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(v[rr].x), "=f"(v[rr].y), "=f"(v[rr].z), "=f"(v[rr].w)
+                         : "r"(stg_r + (uint32_t)(rr * 4 * STG_LD * 4))
+                         : "memory");
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr) {
+            v[rr].x = fmaf(v[rr].x, alpha, bv.x); v[rr].y = fmaf(v[rr].y, alpha, bv.y);
+            v[rr].z = fmaf(v[rr].z, alpha, bv.z); v[rr].w = fmaf(v[rr].w, alpha, bv.w);
+            if (relu) {
+              v[rr].x = fmaxf(v[rr].x, 0.f); v[rr].y = fmaxf(v[rr].y, 0.f);
+              v[rr].z = fmaxf(v[rr].z, 0.f); v[rr].w = fmaxf(v[rr].w, 0.f);
+            }
+            if (has_r) { v[rr].x += x[rr].x; v[rr].y += x[rr].y; v[rr].z += x[rr].z; v[rr].w += x[rr].w; }
+          }
+          if (c_bf16) {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              if (ok_r[rr]) st4(reinterpret_cast<__nv_bfloat16*>(g.C) + co_r[rr] + cc, v[rr]);
+          } else {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              if (ok_r[rr]) st4(reinterpret_cast<float*>(g.C) + co_r[rr] + cc, v[rr]);
+          }
+        } else {
+          const int cc = col + lane;
+          const float bv = (bias && cc < Ntot) ? bias[cc] : 0.f;
+          for (int lr = 0; lr < 32; ++lr) {
+            const long long co = __shfl_sync(0xffffffffu, co_l, lr), ro = __shfl_sync(0xffffffffu, ro_l, lr);
+            if (row_w0 + lr < Mtot && cc < Ntot) {
+              float sv;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sv) : "r"(stg + (uint32_t)((lr * STG_LD + lane) * 4)) : "memory");
+              float v = fmaf(sv, alpha, bv);
+              if (relu) v = fmaxf(v, 0.f);
+              if (has_r)
+                v += r_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g.R)[ro + cc])
+                            : reinterpret_cast<const float*>(g.R)[ro + cc];
+              if (c_bf16) reinterpret_cast<__nv_bfloat16*>(g.C)[co + cc] = __float2bfloat16_rn(v);
+              else reinterpret_cast<float*>(g.C)[co + cc] = v;
+            }
+          }
+        }
+        __syncwarp();
+      }
+      if (warp == 2 && lane == 0) TRACE(2, 2 * tc_ + 1);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    tmem_dealloc(tmem_base, BN);
+    tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
@@ -191,6 +295,16 @@ int make_map(CUtensorMap* m, const void* base, bool f32, long long ld, long long
   return 0;
 }
 
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
 template <int BN, int STAGES, bool TF32>
 int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
   auto kern = gemm_tc_kernel<BN, STAGES, TF32>;
@@ -200,9 +314,13 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
     BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  dim3 grid((t.g.N + BN - 1) / BN, (t.g.M + BM - 1) / BM, t.g.Z);
+  TcArgs tt = t;
+  tt.tiles_m = (t.g.M + BM - 1) / BM;
+  tt.tiles_n = (t.g.N + BN - 1) / BN;
+  tt.total_tiles = tt.tiles_m * tt.tiles_n * t.g.Z;
+  const int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
   ProfScope ps(t.g.tag, st);
-  kern<<<grid, 192, smem, st>>>(ma, mw, t);
+  kern<<<grid, 320, smem, st>>>(ma, mw, tt);
   BIST_LAUNCHED();
   return 0;
 }
@@ -220,6 +338,12 @@ long long batch_rows(const BatchMap& bm, int Z, int zin, long long ld, int K, in
 }
 
 }  // namespace
+
+#ifdef BIST_GEMM_TRACE
+extern "C" int bist_debug_gemm_trace(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_trace, sizeof(g_trace)) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
   *taken = false;
@@ -251,19 +375,29 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     const int rsz = g.r_dtype == BIST_BF16 ? 2 : 4;
     t.vec_c = t.vec_c && ((uintptr_t)g.R % 16 == 0) && al(g.r.si, rsz) && al(g.r.so, rsz) && al(g.rz.s0, rsz) && al(g.rz.s1, rsz);
   }
-  const long long tiles256 = (long long)((g.M + BM - 1) / BM) * (g.N / 256) * g.Z;
-  const int bn = (g.N % 256 == 0 && tiles256 >= 120) ? 256 : (g.N > 64 ? 128 : 64);
+  // tile width: minimise (waves over the SMs) x (per-tile cost ~ BN + fixed overhead)
+  int bn = 64;
+  {
+    const long long tm = (g.M + BM - 1) / BM, sms = num_sms();
+    long long best = -1;
+    for (int cand : {256, 128, 64}) {
+      if (cand > 64 && g.N <= cand / 2) continue;
+      const long long tiles = tm * ((g.N + cand - 1) / cand) * g.Z;
+      const long long cost = ((tiles + sms - 1) / sms) * (cand + 64);
+      if (best < 0 || cost < best) { best = cost; bn = cand; }
+    }
+  }
   CUtensorMap ma, mw;
   BIST_TRY(make_map(&ma, g.A, !bf, a_ld, a_rows, BM));
   BIST_TRY(make_map(&mw, g.W, !bf, w_ld, w_rows, bn));
   if (bf) {
-    if (bn == 256) return launch<256, 4, false>(t, ma, mw, st);
-    if (bn == 128) return launch<128, 3, false>(t, ma, mw, st);
-    return launch<64, 4, false>(t, ma, mw, st);
+    if (bn == 256) return launch<256, 3, false>(t, ma, mw, st);
+    if (bn == 128) return launch<128, 5, false>(t, ma, mw, st);
+    return launch<64, 7, false>(t, ma, mw, st);
   }
-  if (bn == 256) return launch<256, 4, true>(t, ma, mw, st);
-  if (bn == 128) return launch<128, 3, true>(t, ma, mw, st);
-  return launch<64, 4, true>(t, ma, mw, st);
+  if (bn == 256) return launch<256, 3, true>(t, ma, mw, st);
+  if (bn == 128) return launch<128, 5, true>(t, ma, mw, st);
+  return launch<64, 7, true>(t, ma, mw, st);
 }
 
 }  // namespace bist

@@ -1,8 +1,8 @@
+# Round-trip check on the GPU box: unit tests, parity tests, smoke, bench (bf16 + fp32). Outputs in gpurun_out/.
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x 2>&1 | tail -30 > gpurun_out/pytest_gemm.log; echo "gemm rc=$?" >> gpurun_out/pytest_gemm.log
-tail -15 gpurun_out/pytest_gemm.log
-timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -30 > gpurun_out/pytest.log
-tail -12 gpurun_out/pytest.log
+timeout 300 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x 2>&1 | tail -15 > gpurun_out/pytest_gemm.log; tail -5 gpurun_out/pytest_gemm.log
+timeout 300 python scripts/gemm_bench.py > gpurun_out/gemm_bench.log 2>&1; cat gpurun_out/gemm_bench.log
+timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -30 > gpurun_out/pytest.log; tail -12 gpurun_out/pytest.log
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; tail -3 gpurun_out/smoke.log
 timeout 600 python bench.py --steps 10 --warmup 3 --precision bf16 > gpurun_out/bench_bf16.json 2> gpurun_out/bench_bf16.err; tail -3 gpurun_out/bench_bf16.err
 timeout 600 python bench.py --steps 10 --warmup 3 --precision fp32 --no-cpu-baseline > gpurun_out/bench_fp32.json 2> gpurun_out/bench_fp32.err
