@@ -189,7 +189,7 @@ int bist_mha_fwd(const void* query, const void* key, const void* value, const ui
   a.S = sc; a.sg = rows_dense(Lq * h * Lk); a.s_l = h * Lk; a.s_h = Lk;
   a.mask = mask; a.m_b = (mask_mode == BIST_MASK_FULL) ? Lq * Lk : Lk; a.m_l = (mask_mode == BIST_MASK_FULL) ? Lk : 0;
   a.V = v; a.v = rows_dense(d); a.vg = rows_dense(Lk * d);
-  a.ctx = ctx; a.p_out = attn_out;
+  a.ctx = ctx; a.og = rows_dense(Lq * d); a.o_l = d; a.p_out = attn_out;
   a.G = (int)Bp; a.Lq = (int)Lq; a.h = (int)h; a.dk = dk; a.nk = (int)Lk;
   a.v_dtype = dtype; a.ctx_dtype = dtype;
   BIST_TRY(softmax_pv(a, st));

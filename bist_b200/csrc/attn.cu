@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256) softmax_pv_kernel(SoftmaxPvArgs a, int LT
   // phase 2: ctx[l, c] = sum_k P[l, head(c), k] * V[k, c]
   const int d = h * a.dk;
   const TV* Vg = reinterpret_cast<const TV*>(a.V) + a.vg.off(g);
-  TC* Cg = reinterpret_cast<TC*>(a.ctx) + ((long long)g * a.Lq + l0) * d;
+  TC* Cg = reinterpret_cast<TC*>(a.ctx) + a.og.off(g) + (long long)l0 * a.o_l;
   for (int c = threadIdx.x; c < d; c += blockDim.x) {
     const int hh = c / a.dk;
     for (int lb = 0; lb < nl; lb += 16) {
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) softmax_pv_kernel(SoftmaxPvArgs a, int LT
       }
 #pragma unroll
       for (int i = 0; i < 16; ++i)
-        if (lb + i < nl) Cg[(long long)(lb + i) * d + c] = from_f32<TC>(acc[i]);
+        if (lb + i < nl) Cg[(long long)(lb + i) * a.o_l + c] = from_f32<TC>(acc[i]);
     }
   }
 }
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
 
   // scores: one warp per key g
   for (int g = warp; g < G; g += nwarp) {
-    const TX* xr = x1 + (((long long)b * G + g) * Lq + l) * d;
+    const TX* xr = x1 + (((long long)b * Lq + l) * G + g) * d;
     for (int h0 = 0; h0 < h; h0 += HC) {
       float part[HC];
 #pragma unroll
@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
 #pragma unroll
       for (int i = 0; i < HC; ++i) acc[i] = 0.f;
       for (int g = 0; g < G; ++g) {
-        const float xv = to_f32(x1[(((long long)b * G + g) * Lq + l) * d + c]);
+        const float xv = to_f32(x1[(((long long)b * Lq + l) * G + g) * d + c]);
 #pragma unroll
         for (int i = 0; i < HC; ++i)
           if (h0 + i < h) acc[i] = fmaf(sc[(h0 + i) * G + g], xv, acc[i]);
@@ -199,6 +199,11 @@ __global__ void pack_kernel(const float* __restrict__ src, TD* __restrict__ dst,
 int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
   BIST_CHECK_ARG(a.S && a.V && a.ctx, "softmax_pv: null pointer");
   BIST_CHECK_ARG(a.G > 0 && a.Lq > 0 && a.h > 0 && a.dk > 0 && a.nk > 0, "softmax_pv: bad shape");
+  {
+    bool taken = false;
+    int rc = softmax_pv_mma(a, st, &taken);
+    if (taken) return rc;
+  }
   if (a.v_dtype == BIST_F32 && a.ctx_dtype == BIST_F32) return launch_softmax_pv<float, float>(a, st);
   if (a.v_dtype == BIST_BF16 && a.ctx_dtype == BIST_BF16)
     return launch_softmax_pv<__nv_bfloat16, __nv_bfloat16>(a, st);
@@ -222,6 +227,11 @@ int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx
                 int x1_dtype, int ctxx_dtype, cudaStream_t st) {
   BIST_CHECK_ARG(qf && x1 && ctxx, "stage2: null pointer");
   BIST_CHECK_ARG(B > 0 && G > 0 && Lq > 0 && h > 0 && d > 0, "stage2: bad shape");
+  {
+    bool taken = false;
+    int rc = stage2_v2(qf, x1, mask, ctxx, B, G, Lq, h, d, x1_dtype, ctxx_dtype, st, &taken);
+    if (taken) return rc;
+  }
   const size_t smem = ((size_t)h * d + (size_t)h * G) * 4;
   if (smem > 200 * 1024) {
     set_error("stage2: h*(d+G) too large");

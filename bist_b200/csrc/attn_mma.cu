@@ -1,0 +1,357 @@
+// Tensor-core attention cores of the bf16 path.
+//   softmax_pv_mma : masked softmax over precomputed fp32 scores + P.V with bf16 mma.sync (m16n8k16),
+//                    one CTA per attention group, one warp per head.  V rows are staged once in shared
+//                    memory with cp.async (16-byte coalesced), P never leaves registers, the context
+//                    tile is staged in shared memory and written with 16-byte coalesced stores.
+//                    (attention(), /root/reference/model/modules.py:59-64, after the score GEMM)
+//   stage2_v2      : stage 2 of temporal2spatial / spatial2temporal with key and value projections folded to
+//                    the query side (encoder.py:125-132, 152-161): the G stage-1 summaries of one (b,l) are
+//                    read from HBM/L2 exactly once into shared memory.
+#include "common.cuh"
+
+namespace bist {
+namespace {
+
+constexpr float kMaskFill = -1e9f;  // modules.py:60
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// grid (G, ceil(Lq/16)); block 256 (8 warps; warp w owns heads w, w+8, ...).
+// smem: V tile [16*KS][d+8] bf16 (rows >= nk zero-filled) + context tile [16][d+8] bf16.
+template <int KS, int NT>  // KS = 16-key steps (nk <= 16*KS); NT = 8-column tiles per head (dk = 8*NT, NT even)
+__global__ void __launch_bounds__(256) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int d = a.h * a.dk, ldv = d + 8;  // +8 bf16 = 16 bytes of row padding: ldmatrix rows hit distinct banks
+  __nv_bfloat16* Vs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* Os = Vs + (size_t)16 * KS * ldv;
+  const int g = blockIdx.x, l0 = blockIdx.y * 16;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nk = a.nk;
+
+  // ---- stage the group's V rows (cp.async, 16 B per request), zero the padding rows --------------------
+  {
+    const __nv_bfloat16* Vg = reinterpret_cast<const __nv_bfloat16*>(a.V) + a.vg.off(g);
+    const int cpr = d >> 3;  // 16-byte chunks per row
+    for (int i = threadIdx.x; i < 16 * KS * cpr; i += blockDim.x) {
+      const int k = i / cpr, c = (i - k * cpr) << 3;
+      const uint32_t dst = smem_addr(Vs + (size_t)k * ldv + c);
+      if (k < nk) cp_async16(dst, Vg + a.v.off(k) + c);
+      else *reinterpret_cast<uint4*>(Vs + (size_t)k * ldv + c) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+
+  const float* Sg = a.S + a.sg.off(g);
+  const uint8_t* Mg = a.mask ? a.mask + (long long)((g / a.mask_gdiv) % a.mask_gmod) * a.m_b : nullptr;
+  const int r0 = l0 + (lane >> 2), r1 = r0 + 8;  // the two query rows this thread owns in the fragments
+  const int kq = (lane & 3) * 2;
+  const bool vec2 = (a.s_k == 1) && ((a.s_l | a.s_h) % 2 == 0) && (a.sg.so % 2 == 0) && (a.sg.si % 2 == 0) &&
+                    ((reinterpret_cast<uintptr_t>(a.S) & 7) == 0);
+
+  for (int hh = warp; hh < a.h; hh += 8) {
+    // ---- scores of this head in A-fragment order: s[ks][0..1] row r0 k, [2..3] row r1 k, [4..5] r0 k+8, [6..7] r1 k+8
+    float s[KS][8];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int k = ks * 16 + half * 8 + kq;
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const int row = rr ? r1 : r0;
+          float v0 = -INFINITY, v1 = -INFINITY;
+          if (row < a.Lq && k < nk) {
+            const float* p = Sg + (long long)row * a.s_l + (long long)hh * a.s_h + (long long)k * a.s_k;
+            if (vec2 && k + 1 < nk) {
+              const float2 t = __ldg(reinterpret_cast<const float2*>(p));
+              v0 = t.x; v1 = t.y;
+            } else {
+              v0 = __ldg(p);
+              if (k + 1 < nk) v1 = __ldg(p + a.s_k);
+            }
+            if (Mg) {
+              const uint8_t* mrow = Mg + (long long)row * a.m_l;
+              if (mrow[k] == 0) v0 = kMaskFill;
+              if (k + 1 < nk && mrow[k + 1] == 0) v1 = kMaskFill;
+            }
+          }
+          s[ks][half * 4 + rr * 2 + 0] = v0;
+          s[ks][half * 4 + rr * 2 + 1] = v1;
+        }
+      }
+    }
+    // ---- softmax per row (a row lives in the 4 lanes of a quad) ----------------------------------------------
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      mx0 = fmaxf(mx0, fmaxf(fmaxf(s[ks][0], s[ks][1]), fmaxf(s[ks][4], s[ks][5])));
+      mx1 = fmaxf(mx1, fmaxf(fmaxf(s[ks][2], s[ks][3]), fmaxf(s[ks][6], s[ks][7])));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    if (mx0 == -INFINITY) mx0 = 0.f;  // row beyond Lq: all -inf, keep exp() finite
+    if (mx1 == -INFINITY) mx1 = 0.f;
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const bool row1 = (j & 2) != 0;
+        const float e = __expf(s[ks][j] - (row1 ? mx1 : mx0));
+        s[ks][j] = e;
+        if (row1) sum1 += e; else sum0 += e;
+      }
+    }
+    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+    const float inv0 = sum0 > 0.f ? 1.f / sum0 : 0.f, inv1 = sum1 > 0.f ? 1.f / sum1 : 0.f;
+    uint32_t pa[KS][4];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      pa[ks][0] = pack_bf16(s[ks][0] * inv0, s[ks][1] * inv0);  // (row r0, k..k+1)
+      pa[ks][1] = pack_bf16(s[ks][2] * inv1, s[ks][3] * inv1);  // (row r1, k..k+1)
+      pa[ks][2] = pack_bf16(s[ks][4] * inv0, s[ks][5] * inv0);  // (row r0, k+8..)
+      pa[ks][3] = pack_bf16(s[ks][6] * inv1, s[ks][7] * inv1);  // (row r1, k+8..)
+    }
+    if (hh == warp) {  // first head of this warp: V must have landed
+      cp_async_wait_all();
+      __syncthreads();
+    }
+    // ---- ctx[l, hh*dk + j] = sum_k P[l,k] V[k, hh*dk + j] -----------------------------------------------------
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+    // ldmatrix.x4.trans lane addresses: lanes 0-7 rows k..k+7 @ col n0, 8-15 rows k+8.. @ n0, 16-23 rows k.. @ n0+8, 24-31 rows k+8.. @ n0+8
+    const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
+    const uint32_t vbase = smem_addr(Vs) + (uint32_t)((lrow * ldv + hh * a.dk + lcol) * 2);
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int np = 0; np < NT / 2; ++np) {
+        uint32_t b0, b1, b2, b3;
+        ldmatrix_x4_trans(vbase + (uint32_t)((ks * 16 * ldv + np * 16) * 2), b0, b1, b2, b3);
+        mma_bf16_16816(acc[2 * np], pa[ks], b0, b1);
+        mma_bf16_16816(acc[2 * np + 1], pa[ks], b2, b3);
+      }
+    }
+    // ---- accumulators -> context tile in smem (bf16) ----------------------------------------------------------
+    const int orow = lane >> 2, ocol = hh * a.dk + kq;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      *reinterpret_cast<uint32_t*>(Os + (size_t)orow * ldv + ocol + n * 8) = pack_bf16(acc[n][0], acc[n][1]);
+      *reinterpret_cast<uint32_t*>(Os + (size_t)(orow + 8) * ldv + ocol + n * 8) = pack_bf16(acc[n][2], acc[n][3]);
+    }
+  }
+  if (warp >= a.h) {  // warps without a head still take part in the V barrier
+    cp_async_wait_all();
+    __syncthreads();
+  }
+  __syncthreads();
+  // ---- coalesced 16-byte stores of the context rows ----------------------------------------------------------------
+  {
+    __nv_bfloat16* Cg = reinterpret_cast<__nv_bfloat16*>(a.ctx) + a.og.off(g);
+    const int cpr = d >> 3;
+    const int nl = min(16, a.Lq - l0);
+    for (int i = threadIdx.x; i < nl * cpr; i += blockDim.x) {
+      const int li = i / cpr, c = (i - li * cpr) << 3;
+      *reinterpret_cast<uint4*>(Cg + (long long)(l0 + li) * a.o_l + c) = *reinterpret_cast<const uint4*>(Os + (size_t)li * ldv + c);
+    }
+  }
+}
+
+template <int KS, int NT>
+int launch_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
+  const int d = a.h * a.dk;
+  const size_t smem = (size_t)(16 * KS + 16) * (d + 8) * 2;
+  auto kern = softmax_pv_mma_kernel<KS, NT>;
+  static bool configured = false;
+  if (!configured && smem > 48 * 1024) {
+    BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  dim3 grid(a.G, (a.Lq + 15) / 16);
+  ProfScope ps("softmax_pv_mma", st);
+  kern<<<grid, 256, smem, st>>>(a);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+template <int KS>
+int pick_nt(const SoftmaxPvArgs& a, cudaStream_t st) {
+  switch (a.dk / 8) {
+    case 2: return launch_pv<KS, 2>(a, st);
+    case 4: return launch_pv<KS, 4>(a, st);
+    case 8: return launch_pv<KS, 8>(a, st);
+    case 16: return launch_pv<KS, 16>(a, st);
+    default: return -1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// stage 2: grid B*Lq; block 256.  smem: x1 tile [G][d] (input dtype) + qf [h][d] fp32 + p [h][G] fp32.
+template <typename TX, typename TO, int H>
+__global__ void __launch_bounds__(256) stage2_v2_kernel(const float* __restrict__ qf, const TX* __restrict__ x1,
+                                                        const uint8_t* __restrict__ mask, TO* __restrict__ ctxx,
+                                                        int G, int Lq, int d) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  TX* Xs = reinterpret_cast<TX*>(smem_raw);                                        // [G][d]
+  float* Qs = reinterpret_cast<float*>(smem_raw + (((size_t)G * d * sizeof(TX) + 15) & ~(size_t)15));  // [H][d]
+  float* Ps = Qs + (size_t)H * d;                                                  // [H][G]
+  const int bl = blockIdx.x, b = bl / Lq;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  // ---- one coalesced pass over the (b,l) block of stage-1 summaries and the folded queries ------------------------
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(x1 + (long long)bl * G * d);
+    uint4* dst = reinterpret_cast<uint4*>(Xs);
+    const int n16 = (int)((size_t)G * d * sizeof(TX) / 16);
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) cp_async16(smem_addr(dst + i), src + i);
+    const uint4* qsrc = reinterpret_cast<const uint4*>(qf + (long long)bl * H * d);
+    uint4* qdst = reinterpret_cast<uint4*>(Qs);
+    for (int i = threadIdx.x; i < H * d / 4; i += blockDim.x) cp_async16(smem_addr(qdst + i), qsrc + i);
+    cp_async_wait_all();
+    __syncthreads();
+  }
+  // ---- scores[hh][g] = qf[hh,:] . x1[g,:]   (one warp per key, lanes stride the columns by 4) ------------------------
+  for (int g = warp; g < G; g += nwarp) {
+    float part[H];
+#pragma unroll
+    for (int i = 0; i < H; ++i) part[i] = 0.f;
+    const TX* xr = Xs + (size_t)g * d;
+    for (int c = lane * 4; c < d; c += 128) {
+      const float4 xv = ld4(xr + c);
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const float4 q = *reinterpret_cast<const float4*>(Qs + (size_t)i * d + c);
+        part[i] = fmaf(q.x, xv.x, fmaf(q.y, xv.y, fmaf(q.z, xv.z, fmaf(q.w, xv.w, part[i]))));
+      }
+    }
+    const bool masked = mask && mask[(long long)b * G + g] == 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const float sc = warp_sum(part[i]);
+      if (lane == 0) Ps[i * G + g] = masked ? kMaskFill : sc;
+    }
+  }
+  __syncthreads();
+  // ---- softmax over g: one warp per head -------------------------------------------------------------------------------
+  for (int hh = warp; hh < H; hh += nwarp) {
+    float mx = -INFINITY;
+    for (int g = lane; g < G; g += 32) mx = fmaxf(mx, Ps[hh * G + g]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int g = lane; g < G; g += 32) {
+      const float e = sizeof(TX) == 4 ? expf(Ps[hh * G + g] - mx) : __expf(Ps[hh * G + g] - mx);  // fp32 mode: exact exp
+      Ps[hh * G + g] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    for (int g = lane; g < G; g += 32) Ps[hh * G + g] *= inv;
+  }
+  __syncthreads();
+  // ---- out[hh][c] = sum_g p[hh][g] x1[g][c]: each thread owns 2 columns for all heads -------------------------------------
+  TO* out = ctxx + (long long)bl * H * d;
+  for (int c = threadIdx.x * 2; c < d; c += blockDim.x * 2) {
+    float acc[H][2];
+#pragma unroll
+    for (int i = 0; i < H; ++i) acc[i][0] = acc[i][1] = 0.f;
+    for (int g = 0; g < G; ++g) {
+      const float x0 = to_f32(Xs[(size_t)g * d + c]), x1v = to_f32(Xs[(size_t)g * d + c + 1]);
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const float p = Ps[i * G + g];
+        acc[i][0] = fmaf(p, x0, acc[i][0]);
+        acc[i][1] = fmaf(p, x1v, acc[i][1]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      out[(long long)i * d + c] = from_f32<TO>(acc[i][0]);
+      out[(long long)i * d + c + 1] = from_f32<TO>(acc[i][1]);
+    }
+  }
+}
+
+template <typename TX, typename TO, int H>
+int launch_s2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int d, size_t smem,
+              cudaStream_t st) {
+  auto kern = stage2_v2_kernel<TX, TO, H>;
+  static bool configured = false;
+  if (!configured) {
+    BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  ProfScope ps("stage2_v2", st);
+  kern<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), G, Lq, d);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+template <int H>
+int pick_s2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int d, size_t smem,
+            bool xb, bool ob, cudaStream_t st) {
+  if (xb && ob) return launch_s2<__nv_bfloat16, __nv_bfloat16, H>(qf, x1, mask, ctxx, B, G, Lq, d, smem, st);
+  if (xb) return launch_s2<__nv_bfloat16, float, H>(qf, x1, mask, ctxx, B, G, Lq, d, smem, st);
+  if (ob) return launch_s2<float, __nv_bfloat16, H>(qf, x1, mask, ctxx, B, G, Lq, d, smem, st);
+  return launch_s2<float, float, H>(qf, x1, mask, ctxx, B, G, Lq, d, smem, st);
+}
+
+}  // namespace
+
+// Tensor-core softmax.PV; *taken = false when the shape is left to the CUDA-core kernel (attn.cu).
+int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken) {
+  *taken = false;
+  const int d = a.h * a.dk;
+  if (a.v_dtype != BIST_BF16 || a.ctx_dtype != BIST_BF16 || a.p_out) return 0;
+  if (a.nk > 128 || a.dk % 16 != 0 || a.dk > 128 || d % 8 != 0) return 0;
+  if ((reinterpret_cast<uintptr_t>(a.V) & 15) || (reinterpret_cast<uintptr_t>(a.ctx) & 15)) return 0;
+  if ((a.v.so | a.v.si | a.vg.so | a.vg.si | a.og.so | a.og.si | a.o_l) % 8 != 0) return 0;  // 16-byte row starts
+  if (a.v.inner != kNoSplit && a.v.inner <= 0) return 0;
+  const int ks = (a.nk + 15) / 16;
+  if ((size_t)(16 * ks + 16) * (d + 8) * 2 > 200 * 1024) return 0;
+  int rc = -1;
+  if (ks == 1) rc = pick_nt<1>(a, st);
+  else if (ks == 2) rc = pick_nt<2>(a, st);
+  else if (ks == 3) rc = pick_nt<3>(a, st);
+  else if (ks == 4) rc = pick_nt<4>(a, st);
+  else rc = pick_nt<8>(a, st);
+  if (rc == -1) return 0;
+  *taken = true;
+  return rc;
+}
+
+// Single-pass stage 2 over x1 laid out [B, Lq, G, d]; *taken = false when the tile does not fit in shared memory.
+int stage2_v2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
+              int x1_dtype, int ctxx_dtype, cudaStream_t st, bool* taken) {
+  *taken = false;
+  const bool xb = x1_dtype == BIST_BF16, ob = ctxx_dtype == BIST_BF16;
+  const size_t xbytes = align_up((size_t)G * d * (xb ? 2 : 4), 16);
+  const size_t smem = xbytes + (size_t)h * d * 4 + (size_t)h * G * 4;
+  if (smem > 200 * 1024 || d % 8 != 0 || (h != 8 && h != 4 && h != 2)) return 0;
+  if ((reinterpret_cast<uintptr_t>(x1) & 15) || (reinterpret_cast<uintptr_t>(qf) & 15)) return 0;
+  *taken = true;
+  if (h == 8) return pick_s2<8>(qf, x1, mask, ctxx, B, G, Lq, d, smem, xb, ob, st);
+  if (h == 4) return pick_s2<4>(qf, x1, mask, ctxx, B, G, Lq, d, smem, xb, ob, st);
+  return pick_s2<2>(qf, x1, mask, ctxx, B, G, Lq, d, smem, xb, ob, st);
+}
+
+}  // namespace bist

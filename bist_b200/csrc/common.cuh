@@ -175,18 +175,24 @@ struct SoftmaxPvArgs {
   const void* V = nullptr;
   RowMap v{kNoSplit, 0, 0, kNoSplit};   // key row k -> offset within the group's V
   RowMap vg{kNoSplit, 0, 0, kNoSplit};  // group g  -> base offset of V
-  void* ctx = nullptr;      // [G, Lq, d] dense
+  void* ctx = nullptr;      // element (g, l, c) at og.off(g) + l * o_l + c
+  RowMap og{kNoSplit, 0, 0, kNoSplit};
+  long long o_l = 0;
   float* p_out = nullptr;   // optional fp32 [G, h, Lq, nk]
   int G = 0, Lq = 0, h = 0, dk = 0, nk = 0;
   int v_dtype = BIST_F32, ctx_dtype = BIST_F32;
 };
-int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st);
+int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st);  // tensor-core kernel when the shape allows, else CUDA cores
+int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken);  // attn_mma.cu
 
 // ---- stage 2 of t2s / s2t: one query row attends over its G stage-1 summaries ---------------------
-// For every (b,l): scores[hh,g] = qf[b,l,hh,:] . X1[b,g,l,:] (qf pre-scaled), optional key mask
-// [B,G], softmax over g, ctxx[b,l,hh,:] = sum_g p[hh,g] X1[b,g,l,:]   (fp32 [B*Lq, h, d]).
+// For every (b,l): scores[hh,g] = qf[b,l,hh,:] . X1[b,l,g,:] (qf pre-scaled), optional key mask
+// [B,G], softmax over g, ctxx[b,l,hh,:] = sum_g p[hh,g] X1[b,l,g,:]   (fp32 [B*Lq, h, d]).
+// x1 is laid out [B, Lq, G, d] (the G summaries of one (b,l) are contiguous).
 int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G,
                 int Lq, int h, int d, int x1_dtype, int ctxx_dtype, cudaStream_t st);
+int stage2_v2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
+              int x1_dtype, int ctxx_dtype, cudaStream_t st, bool* taken);  // attn_mma.cu
 
 // ---- weight packing helpers ------------------------------------------------------------------
 // dst[r, c] = scale * src[r, c] (transpose = 0) or scale * src[c, r] (transpose = 1); dst is

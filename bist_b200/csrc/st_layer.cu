@@ -252,7 +252,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     a.S = W.sc0; a.sg = rows_dense(Lq * h * Lq); a.s_l = h * Lq; a.s_h = Lq;
     a.mask = query_mask; a.mask_gmod = (int)B; a.m_b = Lq; a.m_l = 0;
     a.V = act(W.qkv0, 2 * d); a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
-    a.ctx = W.cbuf;
+    a.ctx = W.cbuf; a.og = rows_dense(Lq * d); a.o_l = d;
     a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
     a.v_dtype = adt; a.ctx_dtype = adt;
     BIST_TRY(softmax_pv(a, st));
@@ -282,38 +282,53 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
     BIST_TRY(gemm(g, st));
   }
-  {
-    GemmArgs g;  // scores1[u,b,(l,hh),(t,s)] = qf1[u,b,(l,hh),:] . vft[b,t,s,:]  — one launch, video rows in place
-    g.A = W.qf1; g.W = vft; g.C = W.sc1;
-    g.M = (int)(Lq * h); g.N = (int)TS; g.K = di;
-    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(TS);
-    g.Z = (int)(nd * B); g.zin = (int)B;
-    g.az = {Qd * h, Lq * h * d}; g.wz = {0, TS * d}; g.cz = {(long long)Q * h * TS, Lq * h * TS};
-    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
-    BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B too large");
-    BIST_TRY(gemm(g, st));
-  }
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
+    float* sc = W.sc1 + (long long)u * Q * h * TS;
+    {
+      // Folded stage-1 scores, video rows in place, keys of a group contiguous in the output:
+      //   t2s: one product per (b,s): [Lq*h, d] x [T rows at stride S*d]^T -> sc[b,s,(l,hh),t]
+      //   s2t: one product per b:     [Lq*h, d] x [T*S rows]^T            -> sc[b,(l,hh),(t,s)]
+      GemmArgs g;
+      g.A = act(W.qf1, (long long)u * Qd * h); g.W = vft; g.C = sc;
+      g.M = (int)(Lq * h); g.K = di;
+      g.a = rows_dense(d);
+      g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
+      if (t2s) {
+        g.N = (int)T; g.w = rows_dense(S * d); g.c = rows_dense(T);
+        g.Z = (int)(B * S); g.zin = (int)S;
+        g.az = {Lq * h * d, 0}; g.wz = {TS * d, d}; g.cz = {S * Lq * h * T, Lq * h * T};
+      } else {
+        g.N = (int)TS; g.w = rows_dense(d); g.c = rows_dense(TS);
+        g.Z = (int)B; g.zin = 1;
+        g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
+      }
+      BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B*S too large");
+      BIST_TRY(gemm(g, st));
+    }
     SoftmaxPvArgs a;
-    a.S = W.sc1 + (long long)u * Q * h * TS;
-    // group (b, s) for t2s: keys are the T clips of region s (stride S); group (b, t) for s2t: its S regions
-    a.sg = rows_2level(G, Lq * h * TS, t2s ? 1 : S); a.s_l = h * TS; a.s_h = TS; a.s_k = t2s ? S : 1;
-    if (t2s) { a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0; }  // encoder.py:117-121
+    a.S = sc;
+    if (t2s) {  // group (b,s): keys are its T clips (encoder.py:117-121: temporal mask on the keys)
+      a.sg = rows_dense(Lq * h * T); a.s_l = h * T; a.s_h = T; a.s_k = 1;
+      a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0;
+    } else {    // group (b,t): keys are its S regions, no mask (encoder.py:148)
+      a.sg = rows_2level((int)T, Lq * h * TS, S); a.s_l = h * TS; a.s_h = TS; a.s_k = 1;
+    }
     a.V = (const char*)W.xv + (size_t)u * d * e;
     a.vg = t2s ? rows_2level((int)S, TS * xvld, xvld) : rows_dense(S * xvld);
     a.v = t2s ? rows_dense(S * xvld) : rows_dense(xvld);
-    a.ctx = W.ctx1[u];
+    a.ctx = W.ctx1[u];  // [B, Lq, G, d]: the G summaries of one (b,l) are contiguous for stage 2
+    a.og = rows_2level(G, Lq * G * d, d); a.o_l = (long long)G * d;
     a.G = (int)(B * G); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = nk;
     a.v_dtype = dtype; a.ctx_dtype = dtype;
     BIST_TRY(softmax_pv(a, st));
-    GemmArgs o;  // out1[b,g,l,:] = x[b,l,:] + ctx1[b,g,l,:] . Wo1^T + bo1
+    GemmArgs o;  // out1[b,l,g,:] = x[b,l,:] + ctx1[b,l,g,:] . Wo1^T + bo1
     o.A = W.ctx1[u]; o.W = Mw(L.wo1 + (size_t)u * L.dir_stride); o.C = W.out1[u];
     o.bias = fs + u * fsd + L.bo1; o.R = W.x + u * Qd;
     o.M = (int)(B * G * Lq); o.N = di; o.K = di;
     o.a = rows_dense(d); o.w = rows_dense(d); o.c = rows_dense(d);
-    o.r = rows_bcast((int)(G * Lq), Lq * d, (int)Lq, d);
+    o.r = rows_2level(G, d, 0);
     o.a_dtype = dtype; o.w_dtype = dtype; o.c_dtype = dtype; o.r_dtype = BIST_F32; o.tag = "o1_gemm";
     BIST_TRY(gemm(o, st));
   }
