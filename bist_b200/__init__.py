@@ -11,7 +11,7 @@ _LAZY = {
     "LayerNorm": "modules", "SublayerConnection": "modules", "MultiHeadedAttention": "modules",
     "PositionwiseFeedForward": "modules", "clones": "modules",
     "VidEncoder8": "encoder", "VidEncoderLayer4": "encoder", "VideoPath": "encoder",
-    "set_precision": "encoder",
+    "set_precision": "encoder", "GraphedVideoPath": "encoder",
 }
 
 

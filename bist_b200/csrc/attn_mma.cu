@@ -24,6 +24,12 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, u
                : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
                : "r"(addr));
 }
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+
 __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
       "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
@@ -207,6 +213,122 @@ int pick_nt(const SoftmaxPvArgs& a, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// stage 2 on tensor cores (bf16): grid B*Lq; block 256 (8 warps).  One (b,l) per CTA:
+//   S[hh, g] = q[hh,:] . x1[g,:]        mma.sync, heads padded to one 16-row tile, warp w owns key tiles w, w+8, ..
+//   P = softmax_g(mask(S))              one warp per head
+//   U[hh, :] = sum_g P[hh,g] x1[g,:]    mma.sync, warp w owns columns [w*d/8, (w+1)*d/8)
+// smem: X [Gp][d+8] bf16 (Gp = G rounded up to 16, padding rows zero) | Q/U [16][d+8] bf16 | S [16][Gp] f32 | P [16][Gp+8] bf16
+__global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ x1,
+                                                         const uint8_t* __restrict__ mask, __nv_bfloat16* __restrict__ out,
+                                                         int G, int Gp, int Lq, int h, int d) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int ldx = d + 8, ldp = Gp + 8;
+  __nv_bfloat16* Xs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* Qs = Xs + (size_t)Gp * ldx;
+  float* Ss = reinterpret_cast<float*>(Qs + (size_t)16 * ldx);
+  __nv_bfloat16* Ps = reinterpret_cast<__nv_bfloat16*>(Ss + (size_t)16 * Gp);
+  const int bl = blockIdx.x, b = bl / Lq;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cpr = d >> 3;
+  // ---- stage X (G rows) and Q (h rows); zero the padding rows ---------------------------------------------------
+  {
+    const __nv_bfloat16* xg = x1 + (long long)bl * G * d;
+    for (int i = threadIdx.x; i < Gp * cpr; i += blockDim.x) {
+      const int r = i / cpr, c = (i - r * cpr) << 3;
+      if (r < G) cp_async16(smem_addr(Xs + (size_t)r * ldx + c), xg + (long long)r * d + c);
+      else *reinterpret_cast<uint4*>(Xs + (size_t)r * ldx + c) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    const __nv_bfloat16* qg = q + (long long)bl * h * d;
+    for (int i = threadIdx.x; i < 16 * cpr; i += blockDim.x) {
+      const int r = i / cpr, c = (i - r * cpr) << 3;
+      if (r < h) cp_async16(smem_addr(Qs + (size_t)r * ldx + c), qg + (long long)r * d + c);
+      else *reinterpret_cast<uint4*>(Qs + (size_t)r * ldx + c) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+  }
+  // ---- scores: warp per 8-key tile -----------------------------------------------------------------------------------
+  {
+    const uint32_t qa = smem_addr(Qs) + (uint32_t)(((lane & 15) * ldx + (lane >> 4) * 8) * 2);  // A: rows lane%16, k-half lane/16
+    for (int nt = warp; nt < Gp / 8; nt += 8) {
+      // B[k][n] = X[n][k]: non-transposed 8x8 tiles of X rows nt*8.., four consecutive 8-wide k slices per ldmatrix.x4
+      const uint32_t xb = smem_addr(Xs) + (uint32_t)(((nt * 8 + (lane & 7)) * ldx + (lane >> 3) * 8) * 2);
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int k0 = 0; k0 < d; k0 += 32) {
+        uint32_t a0[4], a1[4], b0, b1, b2, b3;
+        ldmatrix_x4(qa + (uint32_t)(k0 * 2), a0[0], a0[1], a0[2], a0[3]);
+        ldmatrix_x4(xb + (uint32_t)(k0 * 2), b0, b1, b2, b3);
+        mma_bf16_16816(acc, a0, b0, b1);
+        if (k0 + 16 < d) {
+          ldmatrix_x4(qa + (uint32_t)((k0 + 16) * 2), a1[0], a1[1], a1[2], a1[3]);
+          mma_bf16_16816(acc, a1, b2, b3);
+        }
+      }
+      const int r = lane >> 2, c = nt * 8 + (lane & 3) * 2;
+      Ss[r * Gp + c] = acc[0]; Ss[r * Gp + c + 1] = acc[1];
+      Ss[(r + 8) * Gp + c] = acc[2]; Ss[(r + 8) * Gp + c + 1] = acc[3];
+    }
+  }
+  __syncthreads();
+  // ---- masked softmax over g: warp per head row; rows >= h and columns >= G of P are zero -------------------------------
+  for (int hh = warp; hh < 16; hh += 8) {
+    if (hh < h) {
+      float mx = -INFINITY;
+      for (int g = lane; g < G; g += 32) {
+        float sc = Ss[hh * Gp + g];
+        if (mask && mask[(long long)b * G + g] == 0) sc = kMaskFill;
+        Ss[hh * Gp + g] = sc;
+        mx = fmaxf(mx, sc);
+      }
+      mx = warp_max(mx);
+      float sum = 0.f;
+      for (int g = lane; g < G; g += 32) {
+        const float e = __expf(Ss[hh * Gp + g] - mx);
+        Ss[hh * Gp + g] = e;
+        sum += e;
+      }
+      sum = warp_sum(sum);
+      const float inv = 1.f / sum;
+      for (int g = lane; g < Gp; g += 32) Ps[hh * ldp + g] = __float2bfloat16_rn(g < G ? Ss[hh * Gp + g] * inv : 0.f);
+    } else {
+      for (int g = lane; g < Gp; g += 32) Ps[hh * ldp + g] = __float2bfloat16_rn(0.f);
+    }
+  }
+  __syncthreads();
+  // ---- U = P . X: warp owns d/8 columns; result rows < h go to the Q tile (reused as the output stage) ---------------------
+  {
+    const int ncol = d / 8;                       // columns per warp (multiple of 16 by the host check)
+    const uint32_t pa = smem_addr(Ps) + (uint32_t)(((lane & 15) * ldp + (lane >> 4) * 8) * 2);
+    const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
+    const uint32_t xb = smem_addr(Xs) + (uint32_t)((lrow * ldx + warp * ncol + lcol) * 2);
+    for (int n0 = 0; n0 < ncol; n0 += 16) {
+      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int k0 = 0; k0 < Gp; k0 += 16) {
+        uint32_t a[4], b0, b1, b2, b3;
+        ldmatrix_x4(pa + (uint32_t)(k0 * 2), a[0], a[1], a[2], a[3]);
+        ldmatrix_x4_trans(xb + (uint32_t)((k0 * ldx + n0) * 2), b0, b1, b2, b3);
+        mma_bf16_16816(acc0, a, b0, b1);
+        mma_bf16_16816(acc1, a, b2, b3);
+      }
+      const int r = lane >> 2, c = warp * ncol + n0 + (lane & 3) * 2;
+      // Q tile is dead after the score phase (barrier above): stage the 16 x d result there
+      *reinterpret_cast<uint32_t*>(Qs + (size_t)r * ldx + c) = pack_bf16(acc0[0], acc0[1]);
+      *reinterpret_cast<uint32_t*>(Qs + (size_t)(r + 8) * ldx + c) = pack_bf16(acc0[2], acc0[3]);
+      *reinterpret_cast<uint32_t*>(Qs + (size_t)r * ldx + c + 8) = pack_bf16(acc1[0], acc1[1]);
+      *reinterpret_cast<uint32_t*>(Qs + (size_t)(r + 8) * ldx + c + 8) = pack_bf16(acc1[2], acc1[3]);
+    }
+  }
+  __syncthreads();
+  {
+    __nv_bfloat16* og = out + (long long)bl * h * d;
+    for (int i = threadIdx.x; i < h * cpr; i += blockDim.x) {
+      const int r = i / cpr, c = (i - r * cpr) << 3;
+      *reinterpret_cast<uint4*>(og + (long long)r * d + c) = *reinterpret_cast<const uint4*>(Qs + (size_t)r * ldx + c);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // stage 2: grid B*Lq; block 256.  smem: x1 tile [G][d] (input dtype) + qf [h][d] fp32 + p [h][G] fp32.
 template <typename TX, typename TO, int H>
 __global__ void __launch_bounds__(256) stage2_v2_kernel(const float* __restrict__ qf, const TX* __restrict__ x1,
@@ -337,6 +459,192 @@ int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken) {
   if (rc == -1) return 0;
   *taken = true;
   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused self-attention over the query tokens (encoder.py:176,184 -> modules.py:81-100 without the output
+// projection): one CTA per (direction, b); the [Lq, 3d] q|k|v rows are staged once; warp w owns heads w, w+8, ..
+//   S = Q_h K_h^T / sqrt(dk) -> key mask -> softmax -> P V_h, all in registers (C fragments of two adjacent
+//   8-key tiles are the A fragment of the next mma).  KT = ceil(Lq/16) <= 4.
+template <int KT, int DKS>  // DKS = dk / 16
+__global__ void __launch_bounds__(256) self_attn_mma_kernel(const __nv_bfloat16* __restrict__ qkv, const uint8_t* __restrict__ mask,
+                                                            int mask_mod, __nv_bfloat16* __restrict__ ctx, int Lq, int h, float scale) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  constexpr int LP = 16 * KT, dk = 16 * DKS;
+  const int d = h * dk, ld = 3 * d + 8;
+  __nv_bfloat16* Ts = reinterpret_cast<__nv_bfloat16*>(smem_raw);  // [LP][3d+8]; the q columns are reused as the output stage
+  const int g = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  {
+    const __nv_bfloat16* src = qkv + (long long)g * Lq * 3 * d;
+    const int cpr = (3 * d) >> 3;
+    for (int i = threadIdx.x; i < LP * cpr; i += blockDim.x) {
+      const int r = i / cpr, c = (i - r * cpr) << 3;
+      if (r < Lq) cp_async16(smem_addr(Ts + (size_t)r * ld + c), src + (long long)r * 3 * d + c);
+      else *reinterpret_cast<uint4*>(Ts + (size_t)r * ld + c) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+  }
+  const uint8_t* mrow = mask ? mask + (long long)(g % mask_mod) * Lq : nullptr;
+  const int kq = (lane & 3) * 2;
+  for (int hh = warp; hh < h; hh += 8) {
+    const uint32_t qa = smem_addr(Ts) + (uint32_t)(((lane & 15) * ld + hh * dk + (lane >> 4) * 8) * 2);
+    const uint32_t kb = smem_addr(Ts) + (uint32_t)(((lane & 7) * ld + d + hh * dk + (lane >> 3) * 8) * 2);
+    const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
+    const uint32_t vb = smem_addr(Ts) + (uint32_t)((lrow * ld + 2 * d + hh * dk + lcol) * 2);
+    float o[KT][2 * DKS][4];
+#pragma unroll
+    for (int mt = 0; mt < KT; ++mt) {
+      // ---- scores for query rows mt*16.., all LP keys -------------------------------------------------------
+      float sc[2 * KT][4];
+#pragma unroll
+      for (int nt = 0; nt < 2 * KT; ++nt) sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < DKS; ks += 2) {  // one ldmatrix.x4 of K covers two 16-wide k steps
+        uint32_t a0[4], a1[4];
+        ldmatrix_x4(qa + (uint32_t)((mt * 16 * ld + ks * 16) * 2), a0[0], a0[1], a0[2], a0[3]);
+        if (ks + 1 < DKS) ldmatrix_x4(qa + (uint32_t)((mt * 16 * ld + (ks + 1) * 16) * 2), a1[0], a1[1], a1[2], a1[3]);
+#pragma unroll
+        for (int nt = 0; nt < 2 * KT; ++nt) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(kb + (uint32_t)((nt * 8 * ld + ks * 16) * 2), b0, b1, b2, b3);
+          mma_bf16_16816(sc[nt], a0, b0, b1);
+          if (ks + 1 < DKS) mma_bf16_16816(sc[nt], a1, b2, b3);
+        }
+      }
+      // ---- scale, key mask, softmax (rows r = lane/4 and r+8 of this tile) -----------------------------------------
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 2 * KT; ++nt) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int key = nt * 8 + kq + j;
+          const bool valid = key < Lq;
+          const bool masked = valid && mrow && mrow[key] == 0;
+          float v0 = valid ? (masked ? kMaskFill : sc[nt][j] * scale) : -INFINITY;
+          float v1 = valid ? (masked ? kMaskFill : sc[nt][2 + j] * scale) : -INFINITY;
+          sc[nt][j] = v0; sc[nt][2 + j] = v1;
+          mx0 = fmaxf(mx0, v0); mx1 = fmaxf(mx1, v1);
+        }
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 2 * KT; ++nt) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const float e0 = __expf(sc[nt][j] - mx0), e1 = __expf(sc[nt][2 + j] - mx1);
+          sc[nt][j] = e0; sc[nt][2 + j] = e1;
+          s0 += e0; s1 += e1;
+        }
+      }
+      s0 += __shfl_xor_sync(0xffffffffu, s0, 1); s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+      const float i0 = 1.f / s0, i1 = 1.f / s1;
+      // ---- P V --------------------------------------------------------------------------------------------------------
+#pragma unroll
+      for (int n = 0; n < 2 * DKS; ++n) o[mt][n][0] = o[mt][n][1] = o[mt][n][2] = o[mt][n][3] = 0.f;
+#pragma unroll
+      for (int kt = 0; kt < KT; ++kt) {
+        uint32_t pa[4];
+        pa[0] = pack_bf16(sc[2 * kt][0] * i0, sc[2 * kt][1] * i0);
+        pa[1] = pack_bf16(sc[2 * kt][2] * i1, sc[2 * kt][3] * i1);
+        pa[2] = pack_bf16(sc[2 * kt + 1][0] * i0, sc[2 * kt + 1][1] * i0);
+        pa[3] = pack_bf16(sc[2 * kt + 1][2] * i1, sc[2 * kt + 1][3] * i1);
+#pragma unroll
+        for (int np = 0; np < DKS; ++np) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(vb + (uint32_t)((kt * 16 * ld + np * 16) * 2), b0, b1, b2, b3);
+          mma_bf16_16816(o[mt][2 * np], pa, b0, b1);
+          mma_bf16_16816(o[mt][2 * np + 1], pa, b2, b3);
+        }
+      }
+    }
+    // every warp only ever reads its own heads' q columns, so they can be overwritten with the output now
+    __syncwarp();
+#pragma unroll
+    for (int mt = 0; mt < KT; ++mt) {
+      const int r = mt * 16 + (lane >> 2);
+#pragma unroll
+      for (int n = 0; n < 2 * DKS; ++n) {
+        *reinterpret_cast<uint32_t*>(Ts + (size_t)r * ld + hh * dk + n * 8 + kq) = pack_bf16(o[mt][n][0], o[mt][n][1]);
+        *reinterpret_cast<uint32_t*>(Ts + (size_t)(r + 8) * ld + hh * dk + n * 8 + kq) = pack_bf16(o[mt][n][2], o[mt][n][3]);
+      }
+    }
+  }
+  __syncthreads();
+  {
+    __nv_bfloat16* dst = ctx + (long long)g * Lq * d;
+    const int cpr = d >> 3;
+    for (int i = threadIdx.x; i < Lq * cpr; i += blockDim.x) {
+      const int r = i / cpr, c = (i - r * cpr) << 3;
+      *reinterpret_cast<uint4*>(dst + (long long)r * d + c) = *reinterpret_cast<const uint4*>(Ts + (size_t)r * ld + c);
+    }
+  }
+}
+
+template <int KT>
+int launch_self(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, int G, int Lq, int h, int dk, cudaStream_t st) {
+  const int d = h * dk;
+  const size_t smem = (size_t)16 * KT * (3 * d + 8) * 2;
+  const float scale = 1.f / sqrtf((float)dk);
+  auto go = [&](auto kern) -> int {
+    BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    ProfScope ps("self_attn_mma", st);
+    kern<<<dim3((unsigned)G), 256, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), mask, mask_mod,
+                                              reinterpret_cast<__nv_bfloat16*>(ctx), Lq, h, scale);
+    BIST_LAUNCHED();
+    return 0;
+  };
+  switch (dk / 16) {
+    case 1: return go(self_attn_mma_kernel<KT, 1>);
+    case 2: return go(self_attn_mma_kernel<KT, 2>);
+    case 4: return go(self_attn_mma_kernel<KT, 4>);
+    default: return -1;
+  }
+}
+
+int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, int G, int Lq, int h, int dk, cudaStream_t st,
+                  bool* taken) {
+  *taken = false;
+  const int d = h * dk, kt = (Lq + 15) / 16;
+  if (kt > 4 || (dk != 16 && dk != 32 && dk != 64) || (size_t)16 * kt * (3 * d + 8) * 2 > 200 * 1024) return 0;
+  if ((reinterpret_cast<uintptr_t>(qkv) & 15) || (reinterpret_cast<uintptr_t>(ctx) & 15)) return 0;
+  *taken = true;
+  if (kt == 1) return launch_self<1>(qkv, mask, mask_mod, ctx, G, Lq, h, dk, st);
+  if (kt == 2) return launch_self<2>(qkv, mask, mask_mod, ctx, G, Lq, h, dk, st);
+  if (kt == 3) return launch_self<3>(qkv, mask, mask_mod, ctx, G, Lq, h, dk, st);
+  return launch_self<4>(qkv, mask, mask_mod, ctx, G, Lq, h, dk, st);
+}
+
+bool stage2_mma_supported(int G, int h, int d) {
+  const int Gp = (G + 15) / 16 * 16;
+  const size_t smem = (size_t)(Gp + 16) * (d + 8) * 2 + (size_t)16 * Gp * 4 + (size_t)16 * (Gp + 8) * 2;
+  return h <= 16 && d % 128 == 0 && smem <= 200 * 1024;
+}
+
+// bf16 tensor-core stage 2 (q, x1, out all bf16); *taken = false when the shape is left to the other kernels.
+int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d,
+               cudaStream_t st, bool* taken) {
+  *taken = false;
+  const int Gp = (G + 15) / 16 * 16;
+  const size_t smem = (size_t)(Gp + 16) * (d + 8) * 2 + (size_t)16 * Gp * 4 + (size_t)16 * (Gp + 8) * 2;
+  if (h > 16 || d % 128 != 0 || smem > 200 * 1024) return 0;
+  if ((reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(x1) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) return 0;
+  *taken = true;
+  static bool configured = false;
+  if (!configured) {
+    BIST_CUDA(cudaFuncSetAttribute(stage2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  ProfScope ps("stage2_mma", st);
+  stage2_mma_kernel<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(q),
+                                                                reinterpret_cast<const __nv_bfloat16*>(x1), mask,
+                                                                reinterpret_cast<__nv_bfloat16*>(out), G, Gp, Lq, h, d);
+  BIST_LAUNCHED();
+  return 0;
 }
 
 // Single-pass stage 2 over x1 laid out [B, Lq, G, d]; *taken = false when the tile does not fit in shared memory.

@@ -127,11 +127,13 @@ static inline RowMap rows_dense(long long ld) { return RowMap{kNoSplit, 0, ld, k
 static inline RowMap rows_2level(int inner, long long so, long long si) { return RowMap{inner, so, si, kNoSplit}; }
 static inline RowMap rows_bcast(int inner, long long so, int mod, long long si) { return RowMap{inner, so, si, mod}; }
 
-// Batch index z -> (z / zin, z % zin) with one stride each.
+// Batch index z -> inner = z % zin (stride s1), outer = z / zin split once more into outer / zmid (stride s0)
+// and outer % zmid (stride s2).  zmid = 1 (default) gives the plain two-level map.
 struct BatchMap {
-  long long s0, s1;
-  __host__ __device__ __forceinline__ long long off(int z, int zin) const {
-    return (long long)(z / zin) * s0 + (long long)(z % zin) * s1;
+  long long s0, s1, s2 = 0;
+  __host__ __device__ __forceinline__ long long off(int z, int zin, int zmid) const {
+    const int outer = z / zin;
+    return (long long)(outer / zmid) * s0 + (long long)(outer % zmid) * s2 + (long long)(z % zin) * s1;
   }
 };
 
@@ -144,7 +146,7 @@ struct GemmArgs {
   const void* R = nullptr;      // residual rows via `r`, N contiguous, or null
   int M = 0, N = 0, K = 0;
   RowMap a{kNoSplit, 0, 0, kNoSplit}, w{kNoSplit, 0, 0, kNoSplit}, c{kNoSplit, 0, 0, kNoSplit}, r{kNoSplit, 0, 0, kNoSplit};
-  int Z = 1, zin = 1;  // batch count and inner batch extent
+  int Z = 1, zin = 1, zmid = 1;  // batch count, inner batch extent, optional split of the outer index
   BatchMap az{0, 0}, wz{0, 0}, cz{0, 0}, rz{0, 0}, bz{0, 0};
   float alpha = 1.f;
   int relu = 0;
@@ -160,6 +162,10 @@ int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate
 int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d,
                float eps, int x_dtype, int y_dtype, cudaStream_t st, int64_t group_rows = 0,
                int64_t pstride = 0);
+
+int layer_norm2(const float* x, const float* a2a, const float* b2a, const float* a2b, const float* b2b, void* ya, void* yb,
+                void* xc, int64_t rows, int64_t d, float eps, int y_dtype, cudaStream_t st, int64_t group_rows = 0,
+                int64_t pstride = 0);
 
 // ---- softmax + weighted sum over projected values ---------------------------------------------
 // For every group g in [0,G): scores S[g] [Lq*h rows (l-major, h-minor), nk] fp32 (row stride
@@ -191,6 +197,12 @@ int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken);  // at
 // x1 is laid out [B, Lq, G, d] (the G summaries of one (b,l) are contiguous).
 int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G,
                 int Lq, int h, int d, int x1_dtype, int ctxx_dtype, cudaStream_t st);
+int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d,
+               cudaStream_t st, bool* taken);  // bf16 q / x1 / out; attn_mma.cu
+bool stage2_mma_supported(int G, int h, int d);
+// Fused self-attention over the query tokens (bf16): qkv [G*Lq, 3d] -> ctx [G*Lq, d]; key mask uint8 [(g % mask_mod), Lq].
+int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, int G, int Lq, int h, int dk, cudaStream_t st,
+                  bool* taken);
 int stage2_v2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
               int x1_dtype, int ctxx_dtype, cudaStream_t st, bool* taken);  // attn_mma.cu
 

@@ -22,8 +22,8 @@ gemm_simt_kernel(GemmArgs g) {
   const int tid = threadIdx.x;
   const int z = blockIdx.z;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  const TA* A = reinterpret_cast<const TA*>(g.A) + g.az.off(z, g.zin);
-  const TW* W = reinterpret_cast<const TW*>(g.W) + g.wz.off(z, g.zin);
+  const TA* A = reinterpret_cast<const TA*>(g.A) + g.az.off(z, g.zin, g.zmid);
+  const TW* W = reinterpret_cast<const TW*>(g.W) + g.wz.off(z, g.zin, g.zmid);
 
   // rows this thread loads
   long long a_off[A_LD], w_off[W_LD];
@@ -127,8 +127,8 @@ gemm_simt_kernel(GemmArgs g) {
   }
 
   // epilogue
-  const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin) : nullptr;
-  const long long c_base = g.cz.off(z, g.zin), r_base = g.rz.off(z, g.zin);
+  const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin, g.zmid) : nullptr;
+  const long long c_base = g.cz.off(z, g.zin, g.zmid), r_base = g.rz.off(z, g.zin, g.zmid);
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int row = m0 + ty * 4 + (i / 4) * (BM / MC) + (i % 4);
@@ -190,7 +190,7 @@ int gemm_simt(const GemmArgs& g, cudaStream_t st) {
                  g.M, g.N, g.K, g.Z);
   BIST_CHECK_ARG(g.Z <= 65535 && (g.M + 63) / 64 <= 65535, "gemm: grid too large");
   bool vec = mult4(g.K) && mult4(g.a.so) && mult4(g.a.si) && mult4(g.w.so) && mult4(g.w.si) &&
-             mult4(g.az.s0) && mult4(g.az.s1) && mult4(g.wz.s0) && mult4(g.wz.s1) &&
+             mult4(g.az.s0) && mult4(g.az.s1) && mult4(g.az.s2) && mult4(g.wz.s0) && mult4(g.wz.s1) && mult4(g.wz.s2) &&
              ((uintptr_t)g.A % 16 == 0) && ((uintptr_t)g.W % 16 == 0);
   if (g.a_dtype == BIST_F32 && g.w_dtype == BIST_F32) return pick_tile<float, float>(g, vec, st);
   if (g.a_dtype == BIST_BF16 && g.w_dtype == BIST_BF16)

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         const int z = tile / per_z, rem = tile - z * per_z;
         const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
         // batch offsets become (row, column) coordinates inside the 2-D tensors
-        const long long ao = g.az.off(z, g.zin), wo = g.wz.off(z, g.zin);
+        const long long ao = g.az.off(z, g.zin, g.zmid), wo = g.wz.off(z, g.zin, g.zmid);
         const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
         const int w_row = (int)(wo / t.w_ld) + n0, w_col = (int)(wo % t.w_ld);
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
@@ -149,15 +149,15 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
       const int z = tile / per_z, rem = tile - z * per_z;
       const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
       const int a = tc_ & 1;
-      const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin) : nullptr;
+      const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin, g.zmid) : nullptr;
       const int row_w0 = m0 + lg * 32;  // first row of this warp
       // lane i computes the element offsets of row row_w0 + i once per tile; the phase-2 owner of a row
       // fetches them with shuffles (no integer division inside the chunk loop)
       const int my_row = row_w0 + lane;
       long long co_l = 0, ro_l = 0;
       if (my_row < Mtot) {
-        co_l = g.cz.off(z, g.zin) + g.c.off(my_row);
-        if (has_r) ro_l = g.rz.off(z, g.zin) + g.r.off(my_row);
+        co_l = g.cz.off(z, g.zin, g.zmid) + g.c.off(my_row);
+        if (has_r) ro_l = g.rz.off(z, g.zin, g.zmid) + g.r.off(my_row);
       }
       long long co_r[8], ro_r[8];
       bool ok_r[8];
@@ -327,10 +327,10 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
 
 // Can the (row offset, column offset) decomposition of every batch offset be used?  Returns the
 // number of tensor rows needed, or -1.
-long long batch_rows(const BatchMap& bm, int Z, int zin, long long ld, int K, int rows_per_batch) {
+long long batch_rows(const BatchMap& bm, int Z, int zin, int zmid, long long ld, int K, int rows_per_batch) {
   long long max_row = 0;
   for (int z = 0; z < Z; ++z) {
-    const long long off = bm.off(z, zin);
+    const long long off = bm.off(z, zin, zmid);
     if (off < 0 || off % ld + K > ld) return -1;
     max_row = off / ld > max_row ? off / ld : max_row;
   }
@@ -359,8 +359,8 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
   if (a_ld < g.K || w_ld < g.K || (a_ld * esz) % 16 || (w_ld * esz) % 16) return 0;
   if (((uintptr_t)g.A % 16) || ((uintptr_t)g.W % 16)) return 0;
   if ((long long)g.M * g.N * g.Z < 64 * 64) return 0;  // tiny products stay on the CUDA cores
-  const long long a_rows = batch_rows(g.az, g.Z, g.zin, a_ld, g.K, g.M);
-  const long long w_rows = batch_rows(g.wz, g.Z, g.zin, w_ld, g.K, g.N);
+  const long long a_rows = batch_rows(g.az, g.Z, g.zin, g.zmid, a_ld, g.K, g.M);
+  const long long w_rows = batch_rows(g.wz, g.Z, g.zin, g.zmid, w_ld, g.K, g.N);
   if (a_rows < 0 || w_rows < 0) return 0;
   *taken = true;
 
@@ -369,11 +369,11 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
   t.a_ld = a_ld; t.w_ld = w_ld; t.nkb = g.K / bke;
   const int csz = g.c_dtype == BIST_BF16 ? 2 : 4;
   auto al = [&](long long v, int sz) { return (v * sz) % 16 == 0; };
-  t.vec_c = ((uintptr_t)g.C % 16 == 0) && al(g.c.si, csz) && al(g.c.so, csz) && al(g.cz.s0, csz) && al(g.cz.s1, csz) &&
-            (!g.bias || (((uintptr_t)g.bias % 16 == 0) && g.bz.s0 % 4 == 0 && g.bz.s1 % 4 == 0));
+  t.vec_c = ((uintptr_t)g.C % 16 == 0) && al(g.c.si, csz) && al(g.c.so, csz) && al(g.cz.s0, csz) && al(g.cz.s1, csz) && al(g.cz.s2, csz) &&
+            (!g.bias || (((uintptr_t)g.bias % 16 == 0) && g.bz.s0 % 4 == 0 && g.bz.s1 % 4 == 0 && g.bz.s2 % 4 == 0));
   if (g.R) {
     const int rsz = g.r_dtype == BIST_BF16 ? 2 : 4;
-    t.vec_c = t.vec_c && ((uintptr_t)g.R % 16 == 0) && al(g.r.si, rsz) && al(g.r.so, rsz) && al(g.rz.s0, rsz) && al(g.rz.s1, rsz);
+    t.vec_c = t.vec_c && ((uintptr_t)g.R % 16 == 0) && al(g.r.si, rsz) && al(g.r.so, rsz) && al(g.rz.s0, rsz) && al(g.rz.s1, rsz) && al(g.rz.s2, rsz);
   }
   // tile width: minimise (waves over the SMs) x (per-tile cost ~ BN + fixed overhead)
   int bn = 64;

@@ -82,6 +82,57 @@ __global__ void __launch_bounds__(256) ln_rows_any(const TX* __restrict__ x, con
   for (int c = lane; c < d; c += 32) yr[c] = from_f32<TY>(a2[c] * (to_f32(xr[c]) - mean) * inv + b2[c]);
 }
 
+// Two LayerNorms of the same fp32 rows with different gains (the stage-1 and stage-2 query norms of
+// VidEncoderLayer4, encoder.py:121,130 / :148,161 both normalise the same x) plus a raw copy of x in the
+// activation dtype, in one pass.  One warp per row; rows [k*group_rows, (k+1)*group_rows) use the parameter
+// sets at +k*pstride.
+template <typename TY, int MAXV>
+__global__ void __launch_bounds__(256) ln2_rows_vec(const float* __restrict__ x, const float* __restrict__ a2a,
+                                                    const float* __restrict__ b2a, const float* __restrict__ a2b,
+                                                    const float* __restrict__ b2b, TY* __restrict__ ya,
+                                                    TY* __restrict__ yb, TY* __restrict__ xc, long long rows, int d,
+                                                    float eps, long long group_rows, long long pstride) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const long long po = (row / group_rows) * pstride;
+  const float* xr = x + row * d;
+  const int nv = d >> 2;
+  float4 v[MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int c = lane + i * 32;
+    if (c < nv) {
+      v[i] = ld4(xr + c * 4);
+      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+  }
+  const float mean = warp_sum(s) / (float)d;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int c = lane + i * 32;
+    if (c < nv) {
+      float a = v[i].x - mean, b = v[i].y - mean, e = v[i].z - mean, f = v[i].w - mean;
+      q += (a * a + b * b) + (e * e + f * f);
+    }
+  }
+  const float inv = 1.f / (sqrtf(warp_sum(q) / (float)(d - 1)) + eps);
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int c = lane + i * 32;
+    if (c < nv) {
+      const float4 n = make_float4((v[i].x - mean) * inv, (v[i].y - mean) * inv, (v[i].z - mean) * inv, (v[i].w - mean) * inv);
+      float4 g = *reinterpret_cast<const float4*>(a2a + po + c * 4), o = *reinterpret_cast<const float4*>(b2a + po + c * 4);
+      st4(ya + row * d + c * 4, make_float4(g.x * n.x + o.x, g.y * n.y + o.y, g.z * n.z + o.z, g.w * n.w + o.w));
+      g = *reinterpret_cast<const float4*>(a2b + po + c * 4); o = *reinterpret_cast<const float4*>(b2b + po + c * 4);
+      st4(yb + row * d + c * 4, make_float4(g.x * n.x + o.x, g.y * n.y + o.y, g.z * n.z + o.z, g.w * n.w + o.w));
+      if (xc) st4(xc + row * d + c * 4, v[i]);
+    }
+  }
+}
+
 template <typename TX, typename TY>
 int launch(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d, float eps,
            cudaStream_t st, long long group_rows, long long pstride) {
@@ -118,6 +169,28 @@ int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t
   if (x_dtype == BIST_BF16 && y_dtype == BIST_F32)
     return launch<__nv_bfloat16, float>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
   return launch<__nv_bfloat16, __nv_bfloat16>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
+}
+
+// Fused pair of LayerNorms + raw copy (see ln2_rows_vec).  x fp32 [rows, d]; ya, yb, xc of y_dtype; d % 4 == 0, d <= 2048.
+int layer_norm2(const float* x, const float* a2a, const float* b2a, const float* a2b, const float* b2b, void* ya, void* yb,
+                void* xc, int64_t rows, int64_t d, float eps, int y_dtype, cudaStream_t st, int64_t group_rows, int64_t pstride) {
+  BIST_CHECK_ARG(x && a2a && b2a && a2b && b2b && ya && yb, "ln2: null pointer");
+  BIST_CHECK_ARG(rows > 0 && d > 1 && d % 4 == 0 && d <= 2048 && pstride % 4 == 0 && dtype_ok(y_dtype), "ln2: bad argument");
+  if (group_rows <= 0) { group_rows = rows; pstride = 0; }
+  const int wpb = 8;
+  dim3 grid((unsigned)((rows + wpb - 1) / wpb));
+  ProfScope ps("layer_norm", st);
+  if (y_dtype == BIST_BF16) {
+    auto Y = [](void* p) { return reinterpret_cast<__nv_bfloat16*>(p); };
+    if (d <= 512) ln2_rows_vec<__nv_bfloat16, 4><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    else ln2_rows_vec<__nv_bfloat16, 16><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+  } else {
+    auto Y = [](void* p) { return reinterpret_cast<float*>(p); };
+    if (d <= 512) ln2_rows_vec<float, 4><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    else ln2_rows_vec<float, 16><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+  }
+  BIST_LAUNCHED();
+  return 0;
 }
 
 }  // namespace bist

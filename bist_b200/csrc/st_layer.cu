@@ -1,14 +1,19 @@
 // VidEncoderLayer4.forward (enc_st_combine == 'none') — /root/reference/model/encoder.py:172-201 with
 // temporal2spatial (:109-139) and spatial2temporal (:141-170), eval mode.
 //
-// Formulation: the reference copies the query block S (or T) times and projects every
-// video row to keys and values.  Here
-//   * the query-side work (LayerNorm, Q projection) is done once per (b,l) instead of once per copy;
-//   * the key projection is folded into the query:  q_h.(W_k,h x + b_k,h) = (q_h W_k,h).x + const, and
-//     the constant cancels in the softmax, so stage-1 scores are ONE batched GEMM of the folded
-//     queries [Lq*h, d] against the raw video rows, and the key bias never appears;
-//   * stage 2 (one query row against its G stage-1 summaries) folds both key and value projections.
-// Only the stage-1 value projection touches every video row (one GEMM for both directions).
+// Formulation.  The reference copies the query block S (or T) times and projects every video
+// row to keys and values, per direction and per block.  Here
+//   * the query-side work (LayerNorm, Q projection, residual) is done once per (b,l) instead of once per copy;
+//   * the key projection is folded into the query:  q_h.(W_k,h x + b_k,h) = (q_h W_k,h).x + const, and the
+//     constant cancels in the softmax, so stage-1 scores are a product of the folded queries [Lq*h, d] with the
+//     raw video rows, and the key bias never appears;
+//   * the stage-1 output projection W_o1 (applied by the reference to every (b,g,l) row) is folded past stage 2:
+//     with c1 = stage-1 context (before W_o1), out1 = x + b_o1 + c1 W_o1^T, so
+//       stage-2 scores  = (q2_h W_k2,h W_o1) . c1  + terms constant over the keys (cancel in the softmax)
+//       stage-2 context = (x + b_o1) W_v2^T + b_v2 + (sum_g p_g c1_g) (W_v2 W_o1)^T       (sum_g p_g = 1)
+//     W_k2 W_o1 and W_v2 W_o1 are formed once at pack time in fp32.
+// Only the stage-1 value projection touches every video row (one GEMM for both directions); the stage-1 and
+// stage-2 query norms / projections / folds of both directions run as three batched launches.
 #include <math.h>
 
 #include "common.cuh"
@@ -18,12 +23,12 @@ namespace {
 
 struct PackedLayout {
   // matrix section, element offsets relative to the direction base
-  size_t wqkv0, wo0, wq1, wkt1, wo1, wq2, wkt2, wv2, wo2, w1, w2, dir_stride;
+  size_t wqkv0, wo0, wq12x, wkt12, wv2f, wo2, w1, w2, dir_stride;
   size_t wv1cat, mat_elems;
   // fp32 section, float offsets relative to the direction base
-  size_t bqkv0, bo0, bq1, bo1, bq2, bv2, bo2, b1, b2, ln_a, ln_b, fdir_stride;
+  size_t bqkv0, bo0, bq12x, bo2, b1, b2, ln_a, ln_b, fdir_stride;
   size_t bv1cat, f_elems;
-  size_t f_byte_off, total_bytes;
+  size_t f_byte_off, scratch_byte_off, total_bytes;
 };
 
 PackedLayout packed_layout(int64_t d, int64_t dff, int n_dirs, int dtype) {
@@ -31,33 +36,45 @@ PackedLayout packed_layout(int64_t d, int64_t dff, int n_dirs, int dtype) {
   size_t o = 0;
   auto m = [&](size_t n) { size_t r = o; o += n; return r; };
   const size_t dd = (size_t)d * d;
-  L.wqkv0 = m(3 * dd); L.wo0 = m(dd); L.wq1 = m(dd); L.wkt1 = m(dd); L.wo1 = m(dd);
-  L.wq2 = m(dd); L.wkt2 = m(dd); L.wv2 = m(dd); L.wo2 = m(dd);
+  L.wqkv0 = m(3 * dd); L.wo0 = m(dd);
+  L.wq12x = m(3 * dd);  // W_q1 | W_q2 | W_v2          (one batched launch: q1, q2, x W_v2^T)
+  L.wkt12 = m(2 * dd);  // (W_k1)^T/sqrt(dk) | (W_k2 W_o1)^T/sqrt(dk)   (one batched fold)
+  L.wv2f = m(dd);       // W_v2 W_o1
+  L.wo2 = m(dd);
   L.w1 = m((size_t)dff * d); L.w2 = m((size_t)d * dff);
   L.dir_stride = o;
   L.wv1cat = L.dir_stride * n_dirs;
   L.mat_elems = L.wv1cat + (size_t)n_dirs * dd;
   o = 0;
-  L.bqkv0 = m(3 * d); L.bo0 = m(d); L.bq1 = m(d); L.bo1 = m(d); L.bq2 = m(d); L.bv2 = m(d); L.bo2 = m(d);
-  L.b1 = m(dff); L.b2 = m(d); L.ln_a = m(4 * d); L.ln_b = m(4 * d);
+  L.bqkv0 = m(3 * d); L.bo0 = m(d);
+  L.bq12x = m(3 * d);   // b_q1 | b_q2 | b_v2 + W_v2 b_o1
+  L.bo2 = m(d); L.b1 = m(dff); L.b2 = m(d); L.ln_a = m(4 * d); L.ln_b = m(4 * d);
   L.fdir_stride = o;
   L.bv1cat = L.fdir_stride * n_dirs;
   L.f_elems = L.bv1cat + (size_t)n_dirs * d;
   L.f_byte_off = align_up(L.mat_elems * dtype_size(dtype), 256);
-  L.total_bytes = L.f_byte_off + L.f_elems * 4;
+  L.scratch_byte_off = align_up(L.f_byte_off + L.f_elems * 4, 256);
+  L.total_bytes = L.scratch_byte_off + 2 * dd * 4;  // pack-time scratch: W_o1^T and one fp32 product
   return L;
 }
 
 struct Workspace {
-  // query-side activations: `act` buffers are GEMM operands (bf16 in bf16 mode), the rest fp32
-  void *nbuf, *qkv0, *cbuf, *qbuf, *qf1, *ctxx2, *ffh;  // act dtype
-  float *sc0, *x, *qf2, *ts, *sc1;                       // fp32
+  // `act` buffers are GEMM operands (bf16 in bf16 mode), the rest fp32
+  void *nbuf, *qkv0, *cbuf, *n12x, *q12x, *qf12, *u2, *ffh;  // act dtype
+  float *sc0, *x, *ts, *sc1, *qf2f;                           // fp32
   void* xv;
   void* ctx1[2];
-  void* out1[2];
   size_t bytes;
   bool ok;
 };
+
+// Can stage 2 of both active directions run on the bf16 tensor-core kernel?
+bool use_stage2_mma(int dtype, int64_t T, int64_t S, int64_t h, int64_t d, int nd, const int* kinds) {
+  if (dtype != BIST_BF16) return false;
+  for (int u = 0; u < nd; ++u)
+    if (!stage2_mma_supported((int)(kinds[u] == 0 ? S : T), (int)h, (int)d)) return false;
+  return true;
+}
 
 Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t dff,
                 int64_t h, int nd, const int* kinds, int dtype) {
@@ -66,17 +83,15 @@ Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   const size_t Q = (size_t)B * Lq, e = dtype_size(dtype);
   auto f = [&](size_t n) { return (float*)A.take(n * 4); };
   auto a = [&](size_t n) { return A.take(n * e); };
-  W.nbuf = a(nd * Q * d); W.qkv0 = a(nd * Q * 3 * d); W.cbuf = a(nd * Q * d); W.qbuf = a(nd * Q * d);
-  W.qf1 = a(nd * Q * h * d); W.ctxx2 = a(nd * Q * h * d); W.ffh = a(nd * Q * dff);
-  W.sc0 = f(nd * Q * h * Lq); W.x = f(nd * Q * d); W.qf2 = f(nd * Q * h * d); W.ts = f(nd * Q * d);
-  W.sc1 = f(nd * Q * h * T * S);
+  W.nbuf = a(nd * Q * d); W.qkv0 = a(nd * Q * 3 * d); W.cbuf = a(nd * Q * d);
+  W.n12x = a(3 * nd * Q * d); W.q12x = a(3 * nd * Q * d); W.qf12 = a(2 * nd * Q * h * d); W.u2 = a(nd * Q * h * d);
+  W.ffh = a(nd * Q * dff);
+  W.sc0 = f(nd * Q * h * Lq); W.x = f(nd * Q * d); W.ts = f(nd * Q * d);
+  W.sc1 = f(Q * h * T * S);  // one direction at a time
+  W.qf2f = (dtype == BIST_BF16 && !use_stage2_mma(dtype, T, S, h, d, nd, kinds)) ? f(nd * Q * h * d) : nullptr;
   W.xv = A.take((size_t)B * T * S * nd * d * e);
-  for (int u = 0; u < 2; ++u) W.ctx1[u] = W.out1[u] = nullptr;
-  for (int u = 0; u < nd; ++u) {
-    const size_t G = kinds[u] == 0 ? S : T;
-    W.ctx1[u] = A.take((size_t)B * G * Lq * d * e);
-    W.out1[u] = A.take((size_t)B * G * Lq * d * e);
-  }
+  for (int u = 0; u < 2; ++u) W.ctx1[u] = nullptr;
+  for (int u = 0; u < nd; ++u) W.ctx1[u] = A.take((size_t)B * (kinds[u] == 0 ? S : T) * Lq * d * e);
   W.bytes = A.used + 256;
   W.ok = A.ok;
   return W;
@@ -88,6 +103,16 @@ int active_dirs(int n_dirs, int dir_mask, int* kinds) {
   if (dir_mask & 2) kinds[nd++] = 1;
   if (n_dirs == 1 && nd != 1) return -1;
   return nd;
+}
+
+// C[M,N] (fp32) = A[M,K] (fp32) . W[N,K]^T (fp32) (+ bias) on the CUDA-core GEMM (pack-time weight products).
+int fp32_product(const float* A, const float* Wm, const float* bias, float* C, int M, int N, int K, cudaStream_t st) {
+  GemmArgs g;
+  g.A = A; g.W = Wm; g.C = C; g.bias = bias;
+  g.M = M; g.N = N; g.K = K;
+  g.a = rows_dense(K); g.w = rows_dense(K); g.c = rows_dense(N);
+  g.tag = "pack";
+  return gemm_simt(g, st);
 }
 
 }  // namespace
@@ -111,9 +136,11 @@ int bist_st_layer_pack(const bist_st_layer_params_t* P, void* packed, size_t pac
   BIST_CHECK_ARG(d % 4 == 0 && dff % 4 == 0, "pack: d and d_ff must be multiples of 4");
   const PackedLayout L = packed_layout(d, dff, n_dirs, dtype);
   if (packed_bytes < L.total_bytes) { set_error("pack: buffer too small"); return BIST_ERR_WORKSPACE; }
-  const size_t e = dtype_size(dtype);
+  const size_t e = dtype_size(dtype), dd = (size_t)d * d;
   char* mat = (char*)packed;
   float* fs = (float*)((char*)packed + L.f_byte_off);
+  float* tmpT = (float*)((char*)packed + L.scratch_byte_off);  // W_o1^T, then products
+  float* tmpP = tmpT + dd;
   const float rs = 1.f / sqrtf((float)(d / h));
   const int di = (int)d, fi = (int)dff;
   auto M = [&](size_t off) { return (void*)(mat + off * e); };
@@ -123,28 +150,35 @@ int bist_st_layer_pack(const bist_st_layer_params_t* P, void* packed, size_t pac
       for (int j = 0; j < 4; ++j) BIST_CHECK_ARG(P->attn_w[ab + i][j] && P->attn_b[ab + i][j], "pack: null attn parameter");
     BIST_CHECK_ARG(P->ff_w1[u] && P->ff_b1[u] && P->ff_w2[u] && P->ff_b2[u], "pack: null ff parameter");
     const size_t mb = u * L.dir_stride, fb = u * L.fdir_stride;
-    for (int j = 0; j < 3; ++j)
-      BIST_TRY(pack_matrix(P->attn_w[ab][j], M(mb + L.wqkv0 + (size_t)j * d * d), di, di, 0, 1.f, dtype, st));
+    const float *Wk2 = P->attn_w[ab + 2][1], *Wv2 = P->attn_w[ab + 2][2], *Wo1 = P->attn_w[ab + 1][3];
+    auto V = [&](const float* src, size_t off, int n) { return pack_matrix(src, fs + off, 1, n, 0, 1.f, BIST_F32, st); };
+    // query self-attention (encoder.py:176 / :184)
+    for (int j = 0; j < 3; ++j) {
+      BIST_TRY(pack_matrix(P->attn_w[ab][j], M(mb + L.wqkv0 + j * dd), di, di, 0, 1.f, dtype, st));
+      BIST_TRY(V(P->attn_b[ab][j], fb + L.bqkv0 + (size_t)j * d, di));
+    }
     BIST_TRY(pack_matrix(P->attn_w[ab][3], M(mb + L.wo0), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][0], M(mb + L.wq1), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][1], M(mb + L.wkt1), di, di, 1, rs, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][2], M(L.wv1cat + (size_t)u * d * d), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][3], M(mb + L.wo1), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 2][0], M(mb + L.wq2), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 2][1], M(mb + L.wkt2), di, di, 1, rs, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 2][2], M(mb + L.wv2), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(V(P->attn_b[ab][3], fb + L.bo0, di));
+    // stage 1 / stage 2 query projections and the raw-x value term
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][0], M(mb + L.wq12x), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 2][0], M(mb + L.wq12x + dd), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(Wv2, M(mb + L.wq12x + 2 * dd), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(V(P->attn_b[ab + 1][0], fb + L.bq12x, di));
+    BIST_TRY(V(P->attn_b[ab + 2][0], fb + L.bq12x + d, di));
+    BIST_TRY(fp32_product(P->attn_b[ab + 1][3], Wv2, P->attn_b[ab + 2][2], fs + fb + L.bq12x + 2 * d, 1, di, di, st));  // b_v2 + W_v2 b_o1
+    // folds: (W_k1)^T / sqrt(dk) and (W_k2 W_o1)^T / sqrt(dk);  W_v2 W_o1
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][1], M(mb + L.wkt12), di, di, 1, rs, dtype, st));
+    BIST_TRY(pack_matrix(Wo1, tmpT, di, di, 1, 1.f, BIST_F32, st));              // tmpT[i][o] = W_o1[o][i]
+    BIST_TRY(fp32_product(Wk2, tmpT, nullptr, tmpP, di, di, di, st));             // tmpP = W_k2 W_o1
+    BIST_TRY(pack_matrix(tmpP, M(mb + L.wkt12 + dd), di, di, 1, rs, dtype, st));
+    BIST_TRY(fp32_product(Wv2, tmpT, nullptr, tmpP, di, di, di, st));             // tmpP = W_v2 W_o1
+    BIST_TRY(pack_matrix(tmpP, M(mb + L.wv2f), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(pack_matrix(P->attn_w[ab + 1][2], M(L.wv1cat + (size_t)u * dd), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(V(P->attn_b[ab + 1][2], L.bv1cat + (size_t)u * d, di));
     BIST_TRY(pack_matrix(P->attn_w[ab + 2][3], M(mb + L.wo2), di, di, 0, 1.f, dtype, st));
+    BIST_TRY(V(P->attn_b[ab + 2][3], fb + L.bo2, di));
     BIST_TRY(pack_matrix(P->ff_w1[u], M(mb + L.w1), fi, di, 0, 1.f, dtype, st));
     BIST_TRY(pack_matrix(P->ff_w2[u], M(mb + L.w2), di, fi, 0, 1.f, dtype, st));
-    auto V = [&](const float* src, size_t off, int n) { return pack_matrix(src, fs + off, 1, n, 0, 1.f, BIST_F32, st); };
-    for (int j = 0; j < 3; ++j) BIST_TRY(V(P->attn_b[ab][j], fb + L.bqkv0 + (size_t)j * d, di));
-    BIST_TRY(V(P->attn_b[ab][3], fb + L.bo0, di));
-    BIST_TRY(V(P->attn_b[ab + 1][0], fb + L.bq1, di));
-    BIST_TRY(V(P->attn_b[ab + 1][2], L.bv1cat + (size_t)u * d, di));
-    BIST_TRY(V(P->attn_b[ab + 1][3], fb + L.bo1, di));
-    BIST_TRY(V(P->attn_b[ab + 2][0], fb + L.bq2, di));
-    BIST_TRY(V(P->attn_b[ab + 2][2], fb + L.bv2, di));
-    BIST_TRY(V(P->attn_b[ab + 2][3], fb + L.bo2, di));
     BIST_TRY(V(P->ff_b1[u], fb + L.b1, fi));
     BIST_TRY(V(P->ff_b2[u], fb + L.b2, di));
     for (int i = 0; i < 4; ++i) {
@@ -161,9 +195,13 @@ size_t bist_st_layer_workspace_bytes(int64_t B, int64_t T, int64_t S, int64_t Lq
   if (B <= 0 || T <= 0 || S <= 0 || Lq <= 0 || d <= 0 || d_ff <= 0 || h <= 0 || !dtype_ok(dtype)) return 0;
   int kinds[2] = {0, 1};
   const int nd = n_dirs == 2 ? 2 : 1;
-  if (nd == 1) kinds[0] = T > S ? 1 : 0;  // the larger of the two single-direction footprints
-  Workspace W = carve(nullptr, (size_t)-1, B, T, S, Lq, d, d_ff, h, nd, kinds, dtype);
-  return W.bytes;
+  size_t best = 0;
+  for (int k = 0; k < (nd == 1 ? 2 : 1); ++k) {  // a single-direction layer may be applied to either direction
+    if (nd == 1) kinds[0] = k;
+    Workspace W = carve(nullptr, (size_t)-1, B, T, S, Lq, d, d_ff, h, nd, kinds, dtype);
+    best = W.bytes > best ? W.bytes : best;
+  }
+  return best;
 }
 
 }  // extern "C"
@@ -183,6 +221,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   BIST_CHECK_ARG((n_dirs == 1 || n_dirs == 2) && dtype_ok(dtype) && (dir_mask & ~3) == 0 && dir_mask != 0,
                  "st_layer: bad n_dirs/dir_mask/dtype");
   BIST_CHECK_ARG(B * T * S < (1LL << 31) / 2 && B * Lq * h < (1LL << 31), "st_layer: problem too large");
+  BIST_CHECK_ARG(B * S <= 65535 && 2 * B * h <= 65535, "st_layer: batch too large for one call (split B)");
   int kinds[2];
   const int nd = active_dirs(n_dirs, dir_mask, kinds);
   BIST_CHECK_ARG(nd > 0, "st_layer: a single-direction layer needs exactly one bit in dir_mask");
@@ -206,7 +245,8 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   auto act = [&](void* p, long long elems) { return (void*)((char*)p + elems * (long long)e); };
   const long long ms = (long long)L.dir_stride, fsd = (long long)L.fdir_stride;
   const int Q = (int)(B * Lq), dk = (int)(d / h), di = (int)d, hi = (int)h;
-  const long long Qd = (long long)Q * d;
+  const long long Qd = (long long)Q * d, dd = (long long)d * d;
+  const bool s2mma = use_stage2_mma(dtype, T, S, h, d, nd, kinds);
 
   // Batched (over the active directions) linear layer  C[u] = act(A[u] . W[u]^T + b[u]) (+ R[u]).
   auto lin = [&](const void* Ain, long long a_dir, size_t w_off, size_t b_off, void* Cout, long long c_dir, int c_dtype,
@@ -220,17 +260,6 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.relu = relu; g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = c_dtype; g.tag = "query_side_gemm";
     return gemm(g, st);
   };
-  // Query-side fold of a key projection: qf[u][q,hh,:] = q[u][q, hh*dk:(hh+1)*dk] . WkT[u][:, hh*dk:(hh+1)*dk]^T
-  auto fold = [&](size_t wkt_off, void* out, int out_dtype) {
-    GemmArgs g;
-    g.A = W.qbuf; g.W = Mw(wkt_off); g.C = out;
-    g.M = Q; g.N = di; g.K = dk;
-    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(h * d);
-    g.Z = nd * hi; g.zin = hi;
-    g.az = {Qd, dk}; g.wz = {ms, dk}; g.cz = {Qd * h, d};
-    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = out_dtype; g.tag = "fold_gemm";
-    return gemm(g, st);
-  };
 
   // ---- self-attention over the query tokens (encoder.py:176 / :184) -------------------------------
   for (int u = 0; u < nd; ++u)
@@ -238,24 +267,27 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
                         adt, st));
   BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0));
   {
-    GemmArgs g;  // scores[u,b,l,hh,k] = q.k / sqrt(dk)
-    g.A = W.qkv0; g.W = act(W.qkv0, d); g.C = W.sc0;
-    g.M = (int)Lq; g.N = (int)Lq; g.K = dk;
-    g.a = rows_dense(3 * d); g.w = rows_dense(3 * d); g.c = rows_dense(h * Lq);
-    g.Z = (int)(nd * B * h); g.zin = hi;
-    g.az = {Lq * 3 * d, dk}; g.wz = {Lq * 3 * d, dk}; g.cz = {Lq * h * Lq, Lq};
-    g.alpha = 1.f / sqrtf((float)dk);
-    g.a_dtype = adt; g.w_dtype = adt; g.tag = "scores0_gemm";
-    BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B*h too large");
-    BIST_TRY(gemm_simt(g, st));  // 16x16x64 products: CUDA cores
-    SoftmaxPvArgs a;
-    a.S = W.sc0; a.sg = rows_dense(Lq * h * Lq); a.s_l = h * Lq; a.s_h = Lq;
-    a.mask = query_mask; a.mask_gmod = (int)B; a.m_b = Lq; a.m_l = 0;
-    a.V = act(W.qkv0, 2 * d); a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
-    a.ctx = W.cbuf; a.og = rows_dense(Lq * d); a.o_l = d;
-    a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
-    a.v_dtype = adt; a.ctx_dtype = adt;
-    BIST_TRY(softmax_pv(a, st));
+    bool fused = false;
+    if (dtype == BIST_BF16) BIST_TRY(self_attn_mma(W.qkv0, query_mask, (int)B, W.cbuf, (int)(nd * B), (int)Lq, hi, dk, st, &fused));
+    if (!fused) {
+      GemmArgs g;  // scores[u,b,l,hh,k] = q.k / sqrt(dk)
+      g.A = W.qkv0; g.W = act(W.qkv0, d); g.C = W.sc0;
+      g.M = (int)Lq; g.N = (int)Lq; g.K = dk;
+      g.a = rows_dense(3 * d); g.w = rows_dense(3 * d); g.c = rows_dense(h * Lq);
+      g.Z = (int)(nd * B * h); g.zin = hi;
+      g.az = {Lq * 3 * d, dk}; g.wz = {Lq * 3 * d, dk}; g.cz = {Lq * h * Lq, Lq};
+      g.alpha = 1.f / sqrtf((float)dk);
+      g.a_dtype = adt; g.w_dtype = adt; g.tag = "scores0_gemm";
+      BIST_TRY(gemm_simt(g, st));  // 16x16x64 products: CUDA cores
+      SoftmaxPvArgs a;
+      a.S = W.sc0; a.sg = rows_dense(Lq * h * Lq); a.s_l = h * Lq; a.s_h = Lq;
+      a.mask = query_mask; a.mask_gmod = (int)B; a.m_b = Lq; a.m_l = 0;
+      a.V = act(W.qkv0, 2 * d); a.v = rows_dense(3 * d); a.vg = rows_dense(Lq * 3 * d);
+      a.ctx = W.cbuf; a.og = rows_dense(Lq * d); a.o_l = d;
+      a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
+      a.v_dtype = adt; a.ctx_dtype = adt;
+      BIST_TRY(softmax_pv(a, st));
+    }
   }
   // output projection + residual with the (possibly aliased, not strided) layer inputs (modules.py:44)
   for (int u = 0; u < nd; ++u) {
@@ -268,10 +300,42 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     BIST_TRY(gemm(g, st));
   }
 
+  // ---- query side of stage 1 and stage 2 in three launches ------------------------------------------------------
+  // n12x = [LN1(x) | LN2(x) | x] (encoder.py:121,130 / :148,161 norm the same x with different gains)
+  void* xcopy = act(W.n12x, 2 * nd * Qd);
+  BIST_TRY(layer_norm2(W.x, fs + L.ln_a + d, fs + L.ln_b + d, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.n12x,
+                       act(W.n12x, nd * Qd), xcopy, (int64_t)nd * Q, d, eps, adt, st, Q, fsd));
+  {
+    GemmArgs g;  // q12x[which][u] = n12x[which][u] . {W_q1 | W_q2 | W_v2}^T + {b_q1 | b_q2 | b_v2 + W_v2 b_o1}
+    g.A = W.n12x; g.W = Mw(L.wq12x); g.C = W.q12x; g.bias = fs + L.bq12x;
+    g.M = Q; g.N = di; g.K = di;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(d);
+    g.Z = 3 * nd; g.zin = nd;  // z = which * nd + u
+    g.az = {nd * Qd, Qd}; g.wz = {dd, ms}; g.cz = {nd * Qd, Qd}; g.bz = {d, fsd};
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "query_side_gemm";
+    BIST_TRY(gemm(g, st));
+  }
+  {
+    // Query-side folds of the key projections: qf[which][u][q,hh,:] = q[which][u][q, hh*dk:(hh+1)*dk] . WkT[:, hh*dk:(hh+1)*dk]^T
+    GemmArgs g;
+    g.A = W.q12x; g.W = Mw(L.wkt12); g.C = W.qf12;
+    g.M = Q; g.N = di; g.K = dk;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(h * d);
+    g.zin = hi; g.zmid = nd;  // z = (which * nd + u) * h + hh
+    g.az = {nd * Qd, dk, Qd}; g.wz = {dd, dk, ms}; g.cz = {nd * Qd * h, d, Qd * h};
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "fold_gemm";
+    if (dtype == BIST_BF16 && !s2mma) {  // the CUDA-core stage-2 kernels want fp32 folded queries
+      g.Z = nd * hi;
+      BIST_TRY(gemm(g, st));
+      g.A = act(W.q12x, nd * Qd); g.W = Mw(L.wkt12 + dd); g.C = W.qf2f; g.c_dtype = BIST_F32;
+      BIST_TRY(gemm(g, st));
+    } else {
+      g.Z = 2 * nd * hi;
+      BIST_TRY(gemm(g, st));
+    }
+  }
+
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
-  BIST_TRY(layer_norm(W.x, fs + L.ln_a + d, fs + L.ln_b + d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.wq1, L.bq1, W.qbuf, Qd, adt, di, di, 0, nullptr, 0));
-  BIST_TRY(fold(L.wkt1, W.qf1, adt));
   const long long TS = T * S, xvld = (long long)nd * d;
   {
     GemmArgs g;  // values of every video row for the active directions: XV = vft . [Wv1]^T + bv1
@@ -285,13 +349,12 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
-    float* sc = W.sc1 + (long long)u * Q * h * TS;
     {
       // Folded stage-1 scores, video rows in place, keys of a group contiguous in the output:
       //   t2s: one product per (b,s): [Lq*h, d] x [T rows at stride S*d]^T -> sc[b,s,(l,hh),t]
       //   s2t: one product per b:     [Lq*h, d] x [T*S rows]^T            -> sc[b,(l,hh),(t,s)]
       GemmArgs g;
-      g.A = act(W.qf1, (long long)u * Qd * h); g.W = vft; g.C = sc;
+      g.A = act(W.qf12, (long long)u * Qd * h); g.W = vft; g.C = W.sc1;
       g.M = (int)(Lq * h); g.K = di;
       g.a = rows_dense(d);
       g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
@@ -304,11 +367,10 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
         g.Z = (int)B; g.zin = 1;
         g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
       }
-      BIST_CHECK_ARG(g.Z <= 65535, "st_layer: B*S too large");
       BIST_TRY(gemm(g, st));
     }
     SoftmaxPvArgs a;
-    a.S = sc;
+    a.S = W.sc1;
     if (t2s) {  // group (b,s): keys are its T clips (encoder.py:117-121: temporal mask on the keys)
       a.sg = rows_dense(Lq * h * T); a.s_l = h * T; a.s_h = T; a.s_k = 1;
       a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0;
@@ -318,38 +380,35 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     a.V = (const char*)W.xv + (size_t)u * d * e;
     a.vg = t2s ? rows_2level((int)S, TS * xvld, xvld) : rows_dense(S * xvld);
     a.v = t2s ? rows_dense(S * xvld) : rows_dense(xvld);
-    a.ctx = W.ctx1[u];  // [B, Lq, G, d]: the G summaries of one (b,l) are contiguous for stage 2
+    a.ctx = W.ctx1[u];  // c1 [B, Lq, G, d]: the G summaries of one (b,l) are contiguous for stage 2
     a.og = rows_2level(G, Lq * G * d, d); a.o_l = (long long)G * d;
     a.G = (int)(B * G); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = nk;
     a.v_dtype = dtype; a.ctx_dtype = dtype;
     BIST_TRY(softmax_pv(a, st));
-    GemmArgs o;  // out1[b,l,g,:] = x[b,l,:] + ctx1[b,l,g,:] . Wo1^T + bo1
-    o.A = W.ctx1[u]; o.W = Mw(L.wo1 + (size_t)u * L.dir_stride); o.C = W.out1[u];
-    o.bias = fs + u * fsd + L.bo1; o.R = W.x + u * Qd;
-    o.M = (int)(B * G * Lq); o.N = di; o.K = di;
-    o.a = rows_dense(d); o.w = rows_dense(d); o.c = rows_dense(d);
-    o.r = rows_2level(G, d, 0);
-    o.a_dtype = dtype; o.w_dtype = dtype; o.c_dtype = dtype; o.r_dtype = BIST_F32; o.tag = "o1_gemm";
-    BIST_TRY(gemm(o, st));
   }
 
-  // ---- stage 2 (encoder.py:125-132 / :152-161) ------------------------------------------------------
-  BIST_TRY(layer_norm(W.x, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.wq2, L.bq2, W.qbuf, Qd, adt, di, di, 0, nullptr, 0));
-  BIST_TRY(fold(L.wkt2, W.qf2, BIST_F32));
+  // ---- stage 2 (encoder.py:125-132 / :152-161) with W_o1 folded through it ------------------------------------------
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
-    BIST_TRY(stage2_attn(W.qf2 + u * Qd * h, W.out1[u], t2s ? nullptr : temporal_mask, act(W.ctxx2, u * Qd * h), (int)B,
-                         (int)(t2s ? S : T), (int)Lq, hi, di, dtype, adt, st));
+    const int G = (int)(t2s ? S : T);
+    const uint8_t* m2 = t2s ? nullptr : temporal_mask;  // :130 no mask / :157-161 temporal mask
+    if (s2mma) {
+      bool taken = false;
+      BIST_TRY(stage2_mma(act(W.qf12, (nd + u) * Qd * h), W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, st, &taken));
+      BIST_CHECK_ARG(taken, "st_layer: stage2_mma declined a shape it reported as supported");
+    } else {
+      const float* qf = dtype == BIST_BF16 ? W.qf2f + u * Qd * h : (const float*)W.qf12 + (nd + u) * Qd * h;
+      BIST_TRY(stage2_attn(qf, W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, dtype, adt, st));
+    }
   }
   {
-    GemmArgs g;  // value projection after the weighted sum: ctx2[q, hh*dk+j] = ctxx2[q,hh,:] . Wv2[hh*dk+j,:] + bv2
-    g.A = W.ctxx2; g.W = Mw(L.wv2); g.C = W.cbuf; g.bias = fs + L.bv2;
+    GemmArgs g;  // ctx2[q, hh*dk+j] = u2[q,hh,:] . (W_v2 W_o1)[hh*dk+j,:] + (x W_v2^T + b_v2 + W_v2 b_o1)[q, hh*dk+j]
+    g.A = W.u2; g.W = Mw(L.wv2f); g.C = W.cbuf; g.R = act(W.q12x, 2 * nd * Qd);
     g.M = Q; g.N = dk; g.K = di;
-    g.a = rows_dense(h * d); g.w = rows_dense(d); g.c = rows_dense(d);
+    g.a = rows_dense(h * d); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
     g.Z = nd * hi; g.zin = hi;
-    g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.bz = {fsd, dk};
-    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "vfold2_gemm";
+    g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.rz = {Qd, dk};
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.r_dtype = adt; g.tag = "vfold2_gemm";
     BIST_TRY(gemm(g, st));
   }
   BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd));

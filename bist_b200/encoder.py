@@ -229,6 +229,16 @@ class VideoPath(nn.Module):
         set_precision(self, precision)
         self.eval()
 
+    def capture(self, b, encoded_query, warmup=3):
+        """Capture one forward into a CUDA graph and return a ``GraphedVideoPath``.
+
+        The kernels are stream-ordered, never synchronise and take every buffer from torch's caching
+        allocator, so the whole path (projection + all blocks + output norms, ~80 launches) records into
+        one graph.  ``graphed(b, encoded_query)`` copies the new inputs into the static input buffers and
+        replays; ``graphed.replay()`` replays on whatever the static buffers hold.
+        """
+        return GraphedVideoPath(self, b, encoded_query, warmup)
+
     def forward(self, b, encoded_query):
         ft = {'encoded_query': encoded_query}
         ft = self.vid_encoder(b, ft)                                          # mtn.py:49-51
@@ -243,3 +253,40 @@ class VideoPath(nn.Module):
             ft['spatial_ft'] = dec.spatial_out_norm(in_ft['t2s'])             # decoder.py:129
             ft['t2s'] = in_ft['t2s']
         return ft
+
+
+class GraphedVideoPath:
+    """CUDA-graph replay of ``VideoPath.forward`` for a fixed batch shape (launch overhead removed)."""
+
+    def __init__(self, model, b, encoded_query, warmup=3):
+        from types import SimpleNamespace
+        _lib.require_cuda(b.fts, encoded_query)
+        self.model = model
+        self.static_b = SimpleNamespace(fts=b.fts.clone(), query_mask=b.query_mask.clone(),
+                                        temporal_mask=b.temporal_mask.clone())
+        self.static_eq = encoded_query.clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.no_grad(), torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):           # packs weights, sets kernel attributes, warms the allocator
+                model(self.static_b, self.static_eq)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.out = model(self.static_b, self.static_eq)
+
+    def load(self, b, encoded_query, non_blocking=True):
+        "Copy a new batch (host or device tensors of the captured shapes) into the static input buffers."
+        self.static_b.fts.copy_(b.fts, non_blocking=non_blocking)
+        self.static_b.query_mask.copy_(b.query_mask, non_blocking=non_blocking)
+        self.static_b.temporal_mask.copy_(b.temporal_mask, non_blocking=non_blocking)
+        self.static_eq.copy_(encoded_query, non_blocking=non_blocking)
+
+    def replay(self):
+        self.graph.replay()
+        return self.out
+
+    def __call__(self, b, encoded_query):
+        self.load(b, encoded_query)
+        return self.replay()
