@@ -45,7 +45,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // grid (G, ceil(Lq/16)); block 256 (8 warps; warp w owns heads w, w+8, ...).
 // smem: V tile [16*KS][d+8] bf16 (rows >= nk zero-filled) + context tile [16][d+8] bf16.
 template <int KS, int NT>  // KS = 16-key steps (nk <= 16*KS); NT = 8-column tiles per head (dk = 8*NT, NT even)
-__global__ void __launch_bounds__(256) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
+__global__ void __launch_bounds__(256, (KS <= 3 ? 3 : 1)) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int d = a.h * a.dk, ldv = d + 8;  // +8 bf16 = 16 bytes of row padding: ldmatrix rows hit distinct banks
   __nv_bfloat16* Vs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
@@ -54,15 +54,17 @@ __global__ void __launch_bounds__(256) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = a.nk;
 
-  // ---- stage the group's V rows (cp.async, 16 B per request), zero the padding rows --------------------
+  // ---- stage the group's V rows (cp.async, 16 B per request; one warp per row), zero the padding rows ------------
   {
     const __nv_bfloat16* Vg = reinterpret_cast<const __nv_bfloat16*>(a.V) + a.vg.off(g);
-    const int cpr = d >> 3;  // 16-byte chunks per row
-    for (int i = threadIdx.x; i < 16 * KS * cpr; i += blockDim.x) {
-      const int k = i / cpr, c = (i - k * cpr) << 3;
-      const uint32_t dst = smem_addr(Vs + (size_t)k * ldv + c);
-      if (k < nk) cp_async16(dst, Vg + a.v.off(k) + c);
-      else *reinterpret_cast<uint4*>(Vs + (size_t)k * ldv + c) = make_uint4(0u, 0u, 0u, 0u);
+    for (int k = warp; k < 16 * KS; k += 8) {
+      __nv_bfloat16* drow = Vs + (size_t)k * ldv;
+      if (k < nk) {
+        const __nv_bfloat16* srow = Vg + a.v.off(k);
+        for (int c = lane * 8; c < d; c += 256) cp_async16(smem_addr(drow + c), srow + c);
+      } else {
+        for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(drow + c) = make_uint4(0u, 0u, 0u, 0u);
+      }
     }
   }
 
@@ -71,37 +73,63 @@ __global__ void __launch_bounds__(256) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
   const int r0 = l0 + (lane >> 2), r1 = r0 + 8;  // the two query rows this thread owns in the fragments
   const int kq = (lane & 3) * 2;
   const bool vec2 = (a.s_k == 1) && ((a.s_l | a.s_h) % 2 == 0) && (a.sg.so % 2 == 0) && (a.sg.si % 2 == 0) &&
-                    ((reinterpret_cast<uintptr_t>(a.S) & 7) == 0);
+                    ((reinterpret_cast<uintptr_t>(a.S) & 7) == 0) &&
+                    (!a.mask || (a.m_b % 2 == 0 && (reinterpret_cast<uintptr_t>(a.mask) & 1) == 0));
 
   for (int hh = warp; hh < a.h; hh += 8) {
     // ---- scores of this head in A-fragment order: s[ks][0..1] row r0 k, [2..3] row r1 k, [4..5] r0 k+8, [6..7] r1 k+8
     float s[KS][8];
+    if (vec2 && a.m_l == 0) {
+      // fast path: contiguous keys, key mask shared by all query rows
+      const float* p0 = Sg + (long long)r0 * a.s_l + (long long)hh * a.s_h;
+      const float* p1 = p0 + 8 * a.s_l;
+      const bool ok0 = r0 < a.Lq, ok1 = r1 < a.Lq;
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
+      for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int k = ks * 16 + half * 8 + kq;
+        for (int half = 0; half < 2; ++half) {
+          const int k = ks * 16 + half * 8 + kq;
+          float2 t0 = make_float2(-INFINITY, -INFINITY), t1 = t0;
+          if (k + 1 < nk) {
+            if (ok0) t0 = __ldg(reinterpret_cast<const float2*>(p0 + k));
+            if (ok1) t1 = __ldg(reinterpret_cast<const float2*>(p1 + k));
+            if (Mg) {
+              const uchar2 m = *reinterpret_cast<const uchar2*>(Mg + k);  // k even
+              if (m.x == 0) { t0.x = ok0 ? kMaskFill : t0.x; t1.x = ok1 ? kMaskFill : t1.x; }
+              if (m.y == 0) { t0.y = ok0 ? kMaskFill : t0.y; t1.y = ok1 ? kMaskFill : t1.y; }
+            }
+          } else if (k < nk) {
+            if (ok0) t0.x = __ldg(p0 + k);
+            if (ok1) t1.x = __ldg(p1 + k);
+            if (Mg && Mg[k] == 0) { t0.x = ok0 ? kMaskFill : t0.x; t1.x = ok1 ? kMaskFill : t1.x; }
+          }
+          s[ks][half * 4 + 0] = t0.x; s[ks][half * 4 + 1] = t0.y;
+          s[ks][half * 4 + 2] = t1.x; s[ks][half * 4 + 3] = t1.y;
+        }
+      }
+    } else {
 #pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-          const int row = rr ? r1 : r0;
-          float v0 = -INFINITY, v1 = -INFINITY;
-          if (row < a.Lq && k < nk) {
-            const float* p = Sg + (long long)row * a.s_l + (long long)hh * a.s_h + (long long)k * a.s_k;
-            if (vec2 && k + 1 < nk) {
-              const float2 t = __ldg(reinterpret_cast<const float2*>(p));
-              v0 = t.x; v1 = t.y;
-            } else {
+      for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int k = ks * 16 + half * 8 + kq;
+#pragma unroll
+          for (int rr = 0; rr < 2; ++rr) {
+            const int row = rr ? r1 : r0;
+            float v0 = -INFINITY, v1 = -INFINITY;
+            if (row < a.Lq && k < nk) {
+              const float* p = Sg + (long long)row * a.s_l + (long long)hh * a.s_h + (long long)k * a.s_k;
               v0 = __ldg(p);
               if (k + 1 < nk) v1 = __ldg(p + a.s_k);
+              if (Mg) {
+                const uint8_t* mrow = Mg + (long long)row * a.m_l;
+                if (mrow[k] == 0) v0 = kMaskFill;
+                if (k + 1 < nk && mrow[k + 1] == 0) v1 = kMaskFill;
+              }
             }
-            if (Mg) {
-              const uint8_t* mrow = Mg + (long long)row * a.m_l;
-              if (mrow[k] == 0) v0 = kMaskFill;
-              if (k + 1 < nk && mrow[k + 1] == 0) v1 = kMaskFill;
-            }
+            s[ks][half * 4 + rr * 2 + 0] = v0;
+            s[ks][half * 4 + rr * 2 + 1] = v1;
           }
-          s[ks][half * 4 + rr * 2 + 0] = v0;
-          s[ks][half * 4 + rr * 2 + 1] = v1;
         }
       }
     }
@@ -172,14 +200,13 @@ __global__ void __launch_bounds__(256) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
     __syncthreads();
   }
   __syncthreads();
-  // ---- coalesced 16-byte stores of the context rows ----------------------------------------------------------------
+  // ---- coalesced 16-byte stores of the context rows (one warp per row) -----------------------------------------------
   {
     __nv_bfloat16* Cg = reinterpret_cast<__nv_bfloat16*>(a.ctx) + a.og.off(g);
-    const int cpr = d >> 3;
     const int nl = min(16, a.Lq - l0);
-    for (int i = threadIdx.x; i < nl * cpr; i += blockDim.x) {
-      const int li = i / cpr, c = (i - li * cpr) << 3;
-      *reinterpret_cast<uint4*>(Cg + (long long)(l0 + li) * a.o_l + c) = *reinterpret_cast<const uint4*>(Os + (size_t)li * ldv + c);
+    for (int li = warp; li < nl; li += 8) {
+      __nv_bfloat16* crow = Cg + (long long)(l0 + li) * a.o_l;
+      for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(crow + c) = *reinterpret_cast<const uint4*>(Os + (size_t)li * ldv + c);
     }
   }
 }
@@ -233,16 +260,16 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
   // ---- stage X (G rows) and Q (h rows); zero the padding rows ---------------------------------------------------
   {
     const __nv_bfloat16* xg = x1 + (long long)bl * G * d;
-    for (int i = threadIdx.x; i < Gp * cpr; i += blockDim.x) {
-      const int r = i / cpr, c = (i - r * cpr) << 3;
-      if (r < G) cp_async16(smem_addr(Xs + (size_t)r * ldx + c), xg + (long long)r * d + c);
-      else *reinterpret_cast<uint4*>(Xs + (size_t)r * ldx + c) = make_uint4(0u, 0u, 0u, 0u);
+    for (int r = warp; r < Gp; r += 8) {
+      __nv_bfloat16* drow = Xs + (size_t)r * ldx;
+      if (r < G) for (int c = lane * 8; c < d; c += 256) cp_async16(smem_addr(drow + c), xg + (long long)r * d + c);
+      else for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(drow + c) = make_uint4(0u, 0u, 0u, 0u);
     }
     const __nv_bfloat16* qg = q + (long long)bl * h * d;
-    for (int i = threadIdx.x; i < 16 * cpr; i += blockDim.x) {
-      const int r = i / cpr, c = (i - r * cpr) << 3;
-      if (r < h) cp_async16(smem_addr(Qs + (size_t)r * ldx + c), qg + (long long)r * d + c);
-      else *reinterpret_cast<uint4*>(Qs + (size_t)r * ldx + c) = make_uint4(0u, 0u, 0u, 0u);
+    for (int r = warp; r < 16; r += 8) {
+      __nv_bfloat16* drow = Qs + (size_t)r * ldx;
+      if (r < h) for (int c = lane * 8; c < d; c += 256) cp_async16(smem_addr(drow + c), qg + (long long)r * d + c);
+      else for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(drow + c) = make_uint4(0u, 0u, 0u, 0u);
     }
     cp_async_wait_all();
     __syncthreads();
@@ -321,10 +348,9 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
   __syncthreads();
   {
     __nv_bfloat16* og = out + (long long)bl * h * d;
-    for (int i = threadIdx.x; i < h * cpr; i += blockDim.x) {
-      const int r = i / cpr, c = (i - r * cpr) << 3;
-      *reinterpret_cast<uint4*>(og + (long long)r * d + c) = *reinterpret_cast<const uint4*>(Qs + (size_t)r * ldx + c);
-    }
+    for (int r = warp; r < h; r += 8)
+      for (int c = lane * 8; c < d; c += 256)
+        *reinterpret_cast<uint4*>(og + (long long)r * d + c) = *reinterpret_cast<const uint4*>(Qs + (size_t)r * ldx + c);
   }
 }
 

@@ -159,9 +159,11 @@ int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate
 
 // ---- LayerNorm ----------------------------------------------------------------------------
 // Rows [k*group_rows, (k+1)*group_rows) use a2 + k*pstride, b2 + k*pstride (batched directions).
+// With x_strided, group k of x starts at x + k * x_gstride elements (the groups need not be adjacent; the
+// stride may be zero or negative).
 int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d,
                float eps, int x_dtype, int y_dtype, cudaStream_t st, int64_t group_rows = 0,
-               int64_t pstride = 0);
+               int64_t pstride = 0, int64_t x_gstride = 0, bool x_strided = false);
 
 int layer_norm2(const float* x, const float* a2a, const float* b2a, const float* a2b, const float* b2b, void* ya, void* yb,
                 void* xc, int64_t rows, int64_t d, float eps, int y_dtype, cudaStream_t st, int64_t group_rows = 0,

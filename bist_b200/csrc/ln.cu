@@ -10,13 +10,14 @@ template <typename TX, typename TY, int MAXV>  // MAXV float4 per lane cached in
 __global__ void __launch_bounds__(256) ln_rows_vec(const TX* __restrict__ x, const float* __restrict__ a2,
                                                    const float* __restrict__ b2, TY* __restrict__ y,
                                                    long long rows, int d, float eps,
-                                                   long long group_rows, long long pstride) {
+                                                   long long group_rows, long long pstride, long long x_gstride) {
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
-  a2 += (row / group_rows) * pstride;
-  b2 += (row / group_rows) * pstride;
-  const TX* xr = x + row * d;
+  const long long grp = row / group_rows;
+  a2 += grp * pstride;
+  b2 += grp * pstride;
+  const TX* xr = x + grp * x_gstride + (row - grp * group_rows) * d;
   TY* yr = y + row * d;
   const int nv = d >> 2;  // float4 count
   float4 v[MAXV];
@@ -61,13 +62,14 @@ template <typename TX, typename TY>
 __global__ void __launch_bounds__(256) ln_rows_any(const TX* __restrict__ x, const float* __restrict__ a2,
                                                    const float* __restrict__ b2, TY* __restrict__ y,
                                                    long long rows, int d, float eps,
-                                                   long long group_rows, long long pstride) {
+                                                   long long group_rows, long long pstride, long long x_gstride) {
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
-  a2 += (row / group_rows) * pstride;
-  b2 += (row / group_rows) * pstride;
-  const TX* xr = x + row * d;
+  const long long grp = row / group_rows;
+  a2 += grp * pstride;
+  b2 += grp * pstride;
+  const TX* xr = x + grp * x_gstride + (row - grp * group_rows) * d;
   TY* yr = y + row * d;
   float s = 0.f;
   for (int c = lane; c < d; c += 32) s += to_f32(xr[c]);
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(256) ln2_rows_vec(const float* __restrict__ x,
 
 template <typename TX, typename TY>
 int launch(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d, float eps,
-           cudaStream_t st, long long group_rows, long long pstride) {
+           cudaStream_t st, long long group_rows, long long pstride, long long x_gstride) {
   const int wpb = 8;
   dim3 grid((unsigned)((rows + wpb - 1) / wpb));
   const TX* xp = reinterpret_cast<const TX*>(x);
@@ -144,11 +146,11 @@ int launch(const void* x, const float* a2, const float* b2, void* y, int64_t row
                  ((uintptr_t)a2 % 16 == 0) && ((uintptr_t)b2 % 16 == 0);
   ProfScope ps("layer_norm", st);
   if (aligned && d <= 512)
-    ln_rows_vec<TX, TY, 4><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride);
+    ln_rows_vec<TX, TY, 4><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   else if (aligned && d <= 2048)
-    ln_rows_vec<TX, TY, 16><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride);
+    ln_rows_vec<TX, TY, 16><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   else
-    ln_rows_any<TX, TY><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride);
+    ln_rows_any<TX, TY><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   BIST_LAUNCHED();
   return 0;
 }
@@ -156,19 +158,21 @@ int launch(const void* x, const float* a2, const float* b2, void* y, int64_t row
 }  // namespace
 
 int layer_norm(const void* x, const float* a2, const float* b2, void* y, int64_t rows, int64_t d, float eps,
-               int x_dtype, int y_dtype, cudaStream_t st, int64_t group_rows, int64_t pstride) {
+               int x_dtype, int y_dtype, cudaStream_t st, int64_t group_rows, int64_t pstride, int64_t x_gstride, bool x_strided) {
   if (group_rows <= 0) { group_rows = rows; pstride = 0; }
+  if (!x_strided) x_gstride = group_rows * d;
+  BIST_CHECK_ARG(x_gstride % 4 == 0, "ln: group stride of x must be a multiple of 4 elements");
   BIST_CHECK_ARG(pstride % 4 == 0, "ln: parameter stride must be a multiple of 4");
   BIST_CHECK_ARG(x && a2 && b2 && y, "ln: null pointer");
   BIST_CHECK_ARG(rows > 0 && d > 1 && d <= (1 << 20), "ln: bad shape rows=%lld d=%lld", (long long)rows,
                  (long long)d);
   BIST_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(y_dtype), "ln: bad dtype");
-  if (x_dtype == BIST_F32 && y_dtype == BIST_F32) return launch<float, float>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
+  if (x_dtype == BIST_F32 && y_dtype == BIST_F32) return launch<float, float>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride, x_gstride);
   if (x_dtype == BIST_F32 && y_dtype == BIST_BF16)
-    return launch<float, __nv_bfloat16>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
+    return launch<float, __nv_bfloat16>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride, x_gstride);
   if (x_dtype == BIST_BF16 && y_dtype == BIST_F32)
-    return launch<__nv_bfloat16, float>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
-  return launch<__nv_bfloat16, __nv_bfloat16>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride);
+    return launch<__nv_bfloat16, float>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride, x_gstride);
+  return launch<__nv_bfloat16, __nv_bfloat16>(x, a2, b2, y, rows, d, eps, st, group_rows, pstride, x_gstride);
 }
 
 // Fused pair of LayerNorms + raw copy (see ln2_rows_vec).  x fp32 [rows, d]; ya, yb, xc of y_dtype; d % 4 == 0, d <= 2048.

@@ -262,9 +262,11 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   };
 
   // ---- self-attention over the query tokens (encoder.py:176 / :184) -------------------------------
-  for (int u = 0; u < nd; ++u)
-    BIST_TRY(layer_norm(x_in[u], fs + u * fsd + L.ln_a, fs + u * fsd + L.ln_b, act(W.nbuf, u * Qd), Q, d, eps, BIST_F32,
-                        adt, st));
+  // the layer inputs of the two directions are separate (possibly aliased) tensors: address them as a batch
+  // whose stride is the pointer difference (zero when both are ft['encoded_query'], decoder.py:109-110)
+  const long long in_dir = nd == 2 ? (long long)(x_in[1] - x_in[0]) : 0;
+  const long long out_dir = nd == 2 ? (long long)(x_out[1] - x_out[0]) : 0;
+  BIST_TRY(layer_norm(x_in[0], fs + L.ln_a, fs + L.ln_b, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd, in_dir, true));
   BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0));
   {
     bool fused = false;
@@ -289,16 +291,8 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       BIST_TRY(softmax_pv(a, st));
     }
   }
-  // output projection + residual with the (possibly aliased, not strided) layer inputs (modules.py:44)
-  for (int u = 0; u < nd; ++u) {
-    GemmArgs g;
-    g.A = act(W.cbuf, u * Qd); g.W = Mw(L.wo0 + (size_t)u * L.dir_stride); g.C = W.x + u * Qd;
-    g.bias = fs + u * fsd + L.bo0; g.R = x_in[u];
-    g.M = Q; g.N = di; g.K = di;
-    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
-    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "query_side_gemm";
-    BIST_TRY(gemm(g, st));
-  }
+  // output projection + residual with the layer inputs (modules.py:44)
+  BIST_TRY(lin(W.cbuf, Qd, L.wo0, L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir));
 
   // ---- query side of stage 1 and stage 2 in three launches ------------------------------------------------------
   // n12x = [LN1(x) | LN2(x) | x] (encoder.py:121,130 / :148,161 norm the same x with different gains)
@@ -416,14 +410,6 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   // ---- feed-forward (encoder.py:134-135 / :165-166) -----------------------------------------------
   BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
   BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0));
-  for (int u = 0; u < nd; ++u) {
-    GemmArgs g;
-    g.A = act(W.ffh, (long long)u * Q * dff); g.W = Mw(L.w2 + (size_t)u * L.dir_stride); g.C = x_out[u];
-    g.bias = fs + u * fsd + L.b2; g.R = W.ts + u * Qd;
-    g.M = Q; g.N = di; g.K = (int)dff;
-    g.a = rows_dense(dff); g.w = rows_dense(dff); g.c = rows_dense(d); g.r = rows_dense(d);
-    g.a_dtype = adt; g.w_dtype = dtype; g.tag = "query_side_gemm";
-    BIST_TRY(gemm(g, st));
-  }
+  BIST_TRY(lin(W.ffh, (long long)Q * dff, L.w2, L.b2, x_out[0], out_dir, BIST_F32, di, (int)dff, 0, W.ts, Qd));
   return 0;
 }
