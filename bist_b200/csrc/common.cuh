@@ -152,10 +152,14 @@ struct GemmArgs {
   int relu = 0;
   const char* tag = "gemm";  // label for bist_prof_collect
   int allow_tf32 = 0;        // fp32 operands may be multiplied as tf32 on the tensor cores
+  // Region-major W (tensor-core path only): W is a [*, wr_T, wr_S, K] tensor (row (bt, s) at (bt*wr_S + s)*w.si) and
+  // output column n = s*wr_T + t multiplies row (t, s) of the batch's wr_T x wr_S block; N = wr_T*wr_S.
+  int wr_T = 0, wr_S = 0;
   int a_dtype = BIST_F32, w_dtype = BIST_F32, c_dtype = BIST_F32, r_dtype = BIST_F32;
 };
 int gemm(const GemmArgs& g, cudaStream_t st);       // dispatches to the kernels below
 int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate GEMM, any shape
+int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken);  // tcgen05 GEMM; *taken = false when it declines the shape
 
 // ---- LayerNorm ----------------------------------------------------------------------------
 // Rows [k*group_rows, (k+1)*group_rows) use a2 + k*pstride, b2 + k*pstride (batched directions).

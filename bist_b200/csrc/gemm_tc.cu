@@ -29,6 +29,10 @@ struct TcArgs {
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
   int tiles_m, tiles_n, total_tiles;
+  int bn_valid;          // output columns per N tile (== BN except in region mode)
+  int w3d, s_box;        // region mode: W tile = 3-D box [s_box regions][wr_T rows][128 B]; w_stage_bytes of it land per slot
+  int w_stage_bytes;
+  long long w_bt_elems;  // elements per bt row group (wr_S * w_ld)
 };
 
 #ifdef BIST_GEMM_TRACE
@@ -48,10 +52,6 @@ struct Smem {
   static constexpr int BAR_OFF = STG_OFF + 8 * 32 * STG_LD * 4;
   static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
 };
-
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 
 template <int BN, int STAGES, bool TF32>
 __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
       int it = 0;
       for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x) {
         const int z = tile / per_z, rem = tile - z * per_z;
-        const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
+        const int m0 = (rem / t.tiles_n) * BM, nt = rem % t.tiles_n, n0 = nt * BN;
         // batch offsets become (row, column) coordinates inside the 2-D tensors
         const long long ao = g.az.off(z, g.zin, g.zmid), wo = g.wz.off(z, g.zin, g.zmid);
         const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
@@ -96,10 +96,11 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full[s], S::STAGE_BYTES);
+          mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
           uint8_t* st = smem + s * S::STAGE_BYTES;
           tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-          tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
+          else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
           TRACE(0, it);
         }
       }
@@ -142,12 +143,13 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
     const uint32_t stg_r = stg + (uint32_t)((sub_r * STG_LD + sub_c) * 4);      // phase 2: + rr * 4 rows
     constexpr int CH_COLS = BN / 2;
     const float alpha = g.alpha;
-    const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M, Ntot = g.N;
+    const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M;
     const bool c_bf16 = g.c_dtype == BIST_BF16, r_bf16 = g.r_dtype == BIST_BF16, has_r = g.R != nullptr;
     int tc_ = 0;
     for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x, ++tc_) {
       const int z = tile / per_z, rem = tile - z * per_z;
-      const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * BN;
+      const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * t.bn_valid;
+      const int Ntot = min(g.N, n0 + t.bn_valid);  // first column this tile does not own
       const int a = tc_ & 1;
       const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin, g.zmid) : nullptr;
       const int row_w0 = m0 + lg * 32;  // first row of this warp
@@ -262,49 +264,6 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
 }
 
 // ---------------------------------------------------------------------------------- host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  });
-  return fn;
-}
-
-// 2-D tensor [rows, ld] (ld contiguous) with a [box_rows, 128 bytes] box, 128B swizzle, zero OOB fill.
-int make_map(CUtensorMap* m, const void* base, bool f32, long long ld, long long rows, int box_rows) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
-  const int esz = f32 ? 4 : 2;
-  cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
-  cuuint32_t box[2] = {(cuuint32_t)(SLAB_BYTES / esz), (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base),
-                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d): ld=%lld rows=%lld", (int)r, ld, rows); return BIST_ERR_CUDA; }
-  return 0;
-}
-
-int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
-  }
-  return n;
-}
-
 template <int BN, int STAGES, bool TF32>
 int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
   auto kern = gemm_tc_kernel<BN, STAGES, TF32>;
@@ -316,7 +275,8 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
   }
   TcArgs tt = t;
   tt.tiles_m = (t.g.M + BM - 1) / BM;
-  tt.tiles_n = (t.g.N + BN - 1) / BN;
+  if (!tt.w3d) { tt.bn_valid = BN; tt.w_stage_bytes = BN * SLAB_BYTES; }
+  tt.tiles_n = (t.g.N + tt.bn_valid - 1) / tt.bn_valid;
   tt.total_tiles = tt.tiles_m * tt.tiles_n * t.g.Z;
   const int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
   ProfScope ps(t.g.tag, st);
@@ -359,13 +319,26 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
   if (a_ld < g.K || w_ld < g.K || (a_ld * esz) % 16 || (w_ld * esz) % 16) return 0;
   if (((uintptr_t)g.A % 16) || ((uintptr_t)g.W % 16)) return 0;
   if ((long long)g.M * g.N * g.Z < 64 * 64) return 0;  // tiny products stay on the CUDA cores
+  const bool regions = g.wr_T > 0;
+  if (regions && (!bf || g.wr_T > 256 || g.wr_S < 1 || g.N != g.wr_T * g.wr_S || w_ld != g.K)) return 0;
   const long long a_rows = batch_rows(g.az, g.Z, g.zin, g.zmid, a_ld, g.K, g.M);
-  const long long w_rows = batch_rows(g.wz, g.Z, g.zin, g.zmid, w_ld, g.K, g.N);
+  long long w_rows = 0;
+  if (regions) {  // every batch offset must address a whole [wr_T, wr_S] block
+    const long long blk = (long long)g.wr_T * g.wr_S * w_ld;
+    for (int z = 0; z < g.Z; ++z) {
+      const long long off = g.wz.off(z, g.zin, g.zmid);
+      if (off < 0 || off % ((long long)g.wr_S * w_ld) != 0) return 0;
+      w_rows = (off + blk) / w_ld > w_rows ? (off + blk) / w_ld : w_rows;
+    }
+  } else {
+    w_rows = batch_rows(g.wz, g.Z, g.zin, g.zmid, w_ld, g.K, g.N);
+  }
   if (a_rows < 0 || w_rows < 0) return 0;
   *taken = true;
 
   TcArgs t;
   t.g = g;
+  t.w3d = 0; t.s_box = 0; t.bn_valid = 0; t.w_stage_bytes = 0; t.w_bt_elems = 1;
   t.a_ld = a_ld; t.w_ld = w_ld; t.nkb = g.K / bke;
   const int csz = g.c_dtype == BIST_BF16 ? 2 : 4;
   auto al = [&](long long v, int sz) { return (v * sz) % 16 == 0; };
@@ -388,8 +361,28 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     }
   }
   CUtensorMap ma, mw;
-  BIST_TRY(make_map(&ma, g.A, !bf, a_ld, a_rows, BM));
-  BIST_TRY(make_map(&mw, g.W, !bf, w_ld, w_rows, bn));
+  BIST_TRY(make_map_2d(&ma, g.A, !bf, a_ld, a_rows, SLAB_BYTES / esz, BM, 128));
+  if (regions) {
+    // N tiles own whole regions: s_box regions x wr_T rows each (<= BN rows of the MMA tile, the rest is never stored)
+    const long long tm = (g.M + BM - 1) / BM, sms = num_sms();
+    long long best = -1;
+    for (int cand : {256, 128}) {
+      const int sb = cand / g.wr_T < g.wr_S ? cand / g.wr_T : g.wr_S;
+      if (sb < 1) continue;
+      const long long tiles = tm * ((g.wr_S + sb - 1) / sb) * g.Z;
+      const long long cost = ((tiles + sms - 1) / sms) * (cand + 64);
+      if (best < 0 || cost < best) { best = cost; bn = cand; t.s_box = sb; }
+    }
+    t.w3d = 1;
+    t.bn_valid = t.s_box * g.wr_T;
+    t.w_stage_bytes = t.bn_valid * SLAB_BYTES;
+    t.w_bt_elems = (long long)g.wr_S * w_ld;
+    if (t.bn_valid % 4 != 0) t.vec_c = 0;  // N tiles must start on a 16-byte boundary for the vector epilogue
+    BIST_TRY(make_map_3d(&mw, g.W, false, w_ld, w_rows / g.wr_S, g.wr_S, (long long)g.wr_S * w_ld * esz, w_ld * esz, SLAB_BYTES / esz,
+                         g.wr_T, t.s_box));
+  } else {
+    BIST_TRY(make_map_2d(&mw, g.W, !bf, w_ld, w_rows, SLAB_BYTES / esz, bn, 128));
+  }
   if (bf) {
     if (bn == 256) return launch<256, 3, false>(t, ma, mw, st);
     if (bn == 128) return launch<128, 5, false>(t, ma, mw, st);

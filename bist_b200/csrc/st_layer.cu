@@ -343,6 +343,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
+    bool t2s_regions = false;
     {
       // Folded stage-1 scores, video rows in place, keys of a group contiguous in the output:
       //   t2s: one product per (b,s): [Lq*h, d] x [T rows at stride S*d]^T -> sc[b,s,(l,hh),t]
@@ -352,7 +353,18 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       g.M = (int)(Lq * h); g.K = di;
       g.a = rows_dense(d);
       g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
+      bool done = false;
       if (t2s) {
+        if (dtype == BIST_BF16) {
+          // tensor-core path: one product per b with region-major columns n = s*T + t (whole regions per N tile,
+          // the folded queries of b are fetched once per tile instead of once per region) -> sc[b,(l,hh),s,t]
+          GemmArgs r = g;
+          r.N = (int)TS; r.w = rows_dense(d); r.c = rows_dense(TS); r.wr_T = (int)T; r.wr_S = (int)S;
+          r.Z = (int)B; r.zin = 1;
+          r.az = {Lq * h * d, 0}; r.wz = {TS * d, 0}; r.cz = {Lq * h * TS, 0};
+          BIST_TRY(gemm_tc(r, st, &done));
+          t2s_regions = done;
+        }
         g.N = (int)T; g.w = rows_dense(S * d); g.c = rows_dense(T);
         g.Z = (int)(B * S); g.zin = (int)S;
         g.az = {Lq * h * d, 0}; g.wz = {TS * d, d}; g.cz = {S * Lq * h * T, Lq * h * T};
@@ -361,12 +373,13 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
         g.Z = (int)B; g.zin = 1;
         g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
       }
-      BIST_TRY(gemm(g, st));
+      if (!done) BIST_TRY(gemm(g, st));
     }
     SoftmaxPvArgs a;
     a.S = W.sc1;
     if (t2s) {  // group (b,s): keys are its T clips (encoder.py:117-121: temporal mask on the keys)
-      a.sg = rows_dense(Lq * h * T); a.s_l = h * T; a.s_h = T; a.s_k = 1;
+      if (t2s_regions) { a.sg = rows_2level((int)S, Lq * h * TS, T); a.s_l = h * TS; a.s_h = TS; a.s_k = 1; }
+      else { a.sg = rows_dense(Lq * h * T); a.s_l = h * T; a.s_h = T; a.s_k = 1; }
       a.mask = temporal_mask; a.mask_gdiv = (int)S; a.m_b = T; a.m_l = 0;
     } else {    // group (b,t): keys are its S regions, no mask (encoder.py:148)
       a.sg = rows_2level((int)T, Lq * h * TS, S); a.s_l = h * TS; a.s_h = TS; a.s_k = 1;

@@ -2,6 +2,10 @@
 //   out = LayerNorm(relu(fts . W^T + bias)).
 #include "common.cuh"
 
+namespace bist {
+int vidproj_fused(const float* fts, const float* W, const float* bias, const float* a2, const float* b2, void* out, int64_t N,
+                  int64_t D, int64_t d, float eps, void* wb, int out_dtype, cudaStream_t st, bool* taken);  // vidproj_tc.cu
+}
 using namespace bist;
 
 extern "C" {
@@ -24,9 +28,14 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
   float* act = (float*)A.take((size_t)N * d * 4);
   void* wb = compute_dtype == BIST_BF16 ? A.take((size_t)d * D * 2) : nullptr;
   if (!A.ok) { set_error("vidproj: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
-  // bf16 mode: the fp32 features are read once from HBM and multiplied as tf32 on the tensor cores
-  // (kind::tf32 reads the fp32 bits directly, so no conversion pass and no bf16 copy of fts exists).
-  (void)wb;
+  if (compute_dtype == BIST_BF16) {
+    // bf16 mode: one fused kernel (TMA fp32 -> in-smem bf16 -> tcgen05 -> LayerNorm epilogue), see vidproj_tc.cu
+    bool taken = false;
+    int rc = vidproj_fused(fts, W, bias, a_2, b_2, out, N, D, d, eps, wb, out_dtype, st, &taken);
+    if (taken) return rc;
+  }
+  // other shapes in bf16 mode: the fp32 features are multiplied as tf32 on the tensor cores (kind::tf32 reads
+  // the fp32 bits directly), followed by the LayerNorm kernel.
   const void* w_used = W;
   const int w_dtype = BIST_F32;
   GemmArgs g;  // encoder.py:75 — relu(W fts + b)

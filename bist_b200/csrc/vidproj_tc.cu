@@ -1,0 +1,306 @@
+// VidEncoder8.forward, video branch — /root/reference/model/encoder.py:72-80, as ONE kernel (bf16 mode):
+//   out = LayerNorm(relu(fts . W^T + bias))
+// fts is read from HBM exactly once as fp32 (TMA, 128B-swizzled [128 rows x 32 k] slabs), converted to bf16
+// inside shared memory by the worker warps (64B-swizzled K-major tile), multiplied on the tensor cores
+// (tcgen05.mma kind::f16, M = 128, N = d <= 512 as one or two instructions, fp32 accumulation in all 512
+// TMEM columns) against the bf16 weight slab streamed by TMA, and normalised in the epilogue straight out of
+// TMEM: a 128 x d fp32 tile is exactly the full row that the reference's LayerNorm (modules.py:28-31,
+// unbiased std, eps on the std) needs, so the un-normalised projection never goes to memory.
+//
+// Persistent CTAs (one per SM), 320 threads:
+//   warp 0      TMA producer    fts slab (fp32) + W slab (bf16) -> 3-stage ring
+//   warp 1      MMA issuer      waits for the converted A slab, issues the UMMAs, commits ring slots / accumulator
+//   warps 2-9   workers         main loop: fp32 -> bf16 conversion of the A slab (swizzle-aware, conflict-free);
+//                               epilogue: bias + ReLU + single-pass (Chan) row statistics, normalise, smem
+//                               transpose, 16-byte coalesced stores.  Two warps per TMEM lane quarter.
+#include "tc_ptx.cuh"
+
+namespace bist {
+namespace {
+using namespace tc;
+
+constexpr int VP_BK = 32;                      // K elements per ring slot
+constexpr int VP_STAGES = 3;
+constexpr int VP_AF = 128 * VP_BK * 4;         // fp32 A slab   16 KB (SWIZZLE_128B)
+constexpr int VP_AB = 128 * VP_BK * 2;         // bf16 A slab    8 KB (SWIZZLE_64B)
+constexpr int VP_STG_LD = 36;
+
+#ifdef BIST_GEMM_TRACE
+__device__ long long g_vtrace[4][64];   // CTA 0 only: [role][event]
+#define VTRACE(role, idx) do { if (blockIdx.x == 0 && (idx) < 64) g_vtrace[role][idx] = clock64(); } while (0)
+#else
+#define VTRACE(role, idx) do {} while (0)
+#endif
+
+struct VpSmem {
+  int wb_bytes, stage_bytes, stg_off, red_off, bar_off, total;
+};
+__host__ __device__ inline VpSmem vp_smem(int d) {
+  VpSmem s;
+  s.wb_bytes = d * VP_BK * 2;                   // bf16 W slab (SWIZZLE_64B), d rows
+  s.stage_bytes = VP_AF + VP_AB + s.wb_bytes;   // multiple of 1024 for d % 16 == 0
+  s.stg_off = VP_STAGES * s.stage_bytes;        // 8 worker warps x [32][36] floats
+  s.red_off = s.stg_off + 8 * 32 * VP_STG_LD * 4;   // row statistics exchange: [2][128] x (n, mean, M2)
+  s.bar_off = s.red_off + 2 * 128 * 3 * 4;
+  s.total = s.bar_off + (3 * VP_STAGES + 2) * 8 + 16 + 1024;
+  return s;
+}
+
+struct VpArgs {
+  const float* bias;
+  const float* a2;
+  const float* b2;
+  void* out;
+  int N, D, d, out_bf16, tiles, nkb;
+  float eps;
+};
+
+__global__ void __launch_bounds__(320, 1) vidproj_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                         const __grid_constant__ CUtensorMap map_w, const VpArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const VpSmem L = vp_smem(p.d);
+  uint64_t* full = (uint64_t*)(smem + L.bar_off);  // TMA bytes landed (fp32 A + bf16 W)
+  uint64_t* conv = full + VP_STAGES;               // bf16 A written (8 worker-warp arrivals)
+  uint64_t* empty = conv + VP_STAGES;              // UMMAs that read the slot have completed
+  uint64_t* acc_full = empty + VP_STAGES;
+  uint64_t* acc_empty = acc_full + 1;
+  uint32_t* tmem_slot = (uint32_t*)(acc_empty + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.d;
+  const int nhalf = d > 256 ? 2 : 1, nmma = d / nhalf;   // UMMA N <= 256
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < VP_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&conv[s], 8); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, 8);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        const int m0 = tile * 128;
+        for (int kb = 0; kb < p.nkb; ++kb, ++it) {
+          const int s = it % VP_STAGES;
+          mbar_wait(&empty[s], ((it / VP_STAGES) & 1) ^ 1);
+          mbar_expect_tx(&full[s], VP_AF + L.wb_bytes);
+          uint8_t* st = smem + s * L.stage_bytes;
+          tma_load_2d(st, &map_a, &full[s], kb * VP_BK, m0);
+          for (int hN = 0; hN < nhalf; ++hN)
+            tma_load_2d(st + VP_AF + VP_AB + hN * nmma * VP_BK * 2, &map_w, &full[s], kb * VP_BK, hN * nmma);
+          VTRACE(0, it);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nmma >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int it = 0, tc_ = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++tc_) {
+        mbar_wait(acc_empty, (tc_ & 1) ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < p.nkb; ++kb, ++it) {
+          const int s = it % VP_STAGES;
+          mbar_wait(&conv[s], (it / VP_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * L.stage_bytes);
+          const uint64_t ad = make_desc_sw64(sa + VP_AF);
+#pragma unroll
+          for (int k = 0; k < VP_BK / 16; ++k) {
+            for (int hN = 0; hN < nhalf; ++hN) {
+              const uint64_t wd = make_desc_sw64(sa + VP_AF + VP_AB + hN * nmma * VP_BK * 2);
+              tc_mma<false>(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            }
+          }
+          tc_commit(&empty[s]);
+          VTRACE(1, it);
+        }
+        tc_commit(acc_full);
+      }
+    }
+  } else {
+    // ================================ worker warps =====================================================
+    const int wt = threadIdx.x - 64;                 // 0..255
+    const int crow = wt >> 1, chalf = wt & 1;        // conversion: row of the slab, which 16 of its 32 k
+    const int lg = warp & 3, ch = (warp - 2) >> 2;   // epilogue: TMEM lane quarter, column half
+    const int hcols = d >> 1;                        // columns per half (multiple of 32)
+    const uint32_t stg = smem_u32(smem + L.stg_off) + (uint32_t)((warp - 2) * 32 * VP_STG_LD * 4);
+    const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+    const uint32_t stg_w = stg + (uint32_t)(lane * VP_STG_LD * 4);
+    const uint32_t stg_r = stg + (uint32_t)((sub_r * VP_STG_LD + sub_c) * 4);
+    float* red = (float*)(smem + L.red_off);         // [2][128][3]
+    int it = 0, tc_ = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++tc_) {
+      // ---- main loop: fp32 slab -> bf16 slab ------------------------------------------------------------
+      for (int kb = 0; kb < p.nkb; ++kb, ++it) {
+        const int s = it % VP_STAGES;
+        mbar_wait(&full[s], (it / VP_STAGES) & 1);
+        if (warp == 2 && lane == 0) VTRACE(2, it);
+        const uint32_t af = smem_u32(smem + s * L.stage_bytes) + (uint32_t)(crow * 128);
+        const uint32_t ab = smem_u32(smem + s * L.stage_bytes) + VP_AF + (uint32_t)(crow * 64);
+        float4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {   // logical 16-byte chunk 4*chalf + j of a SWIZZLE_128B row
+          const uint32_t a = af + (uint32_t)((((4 * chalf + j) ^ (crow & 7))) << 4);
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[j].x), "=f"(v[j].y), "=f"(v[j].z), "=f"(v[j].w) : "r"(a) : "memory");
+        }
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {  // logical 16-byte chunk 2*chalf + jj of a SWIZZLE_64B row
+          __nv_bfloat162 b0 = __floats2bfloat162_rn(v[2 * jj].x, v[2 * jj].y), b1 = __floats2bfloat162_rn(v[2 * jj].z, v[2 * jj].w);
+          __nv_bfloat162 b2 = __floats2bfloat162_rn(v[2 * jj + 1].x, v[2 * jj + 1].y), b3 = __floats2bfloat162_rn(v[2 * jj + 1].z, v[2 * jj + 1].w);
+          const uint32_t a = ab + (uint32_t)((((2 * chalf + jj) ^ ((crow >> 1) & 3))) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(*reinterpret_cast<uint32_t*>(&b0)),
+                       "r"(*reinterpret_cast<uint32_t*>(&b1)), "r"(*reinterpret_cast<uint32_t*>(&b2)),
+                       "r"(*reinterpret_cast<uint32_t*>(&b3))
+                       : "memory");
+        }
+        fence_proxy_async_smem();   // make the generic-proxy writes visible to the tensor core's async proxy
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&conv[s]);
+        if (warp == 2 && lane == 0) VTRACE(3, it);
+      }
+      // ---- epilogue -------------------------------------------------------------------------------------------
+      const int m0 = tile * 128;
+      const int row_w0 = m0 + lg * 32;
+      mbar_wait(acc_full, tc_ & 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * hcols);
+      // pass 1: row statistics of relu(acc + bias) over this warp's column half (Chan's parallel update per 32 columns)
+      float cnt = 0.f, mean = 0.f, m2 = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < hcols; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tacc + c0, r);
+        const float* bp = p.bias + ch * hcols + c0;
+        float sum = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(bp + 4 * q));
+          float x0 = fmaxf(__uint_as_float(r[4 * q]) + b.x, 0.f), x1 = fmaxf(__uint_as_float(r[4 * q + 1]) + b.y, 0.f);
+          float x2 = fmaxf(__uint_as_float(r[4 * q + 2]) + b.z, 0.f), x3 = fmaxf(__uint_as_float(r[4 * q + 3]) + b.w, 0.f);
+          r[4 * q] = __float_as_uint(x0); r[4 * q + 1] = __float_as_uint(x1);
+          r[4 * q + 2] = __float_as_uint(x2); r[4 * q + 3] = __float_as_uint(x3);
+          sum += (x0 + x1) + (x2 + x3);
+        }
+        const float mc = sum * (1.f / 32.f);
+        float qc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { const float t = __uint_as_float(r[j]) - mc; qc = fmaf(t, t, qc); }
+        const float ncnt = cnt + 32.f, delta = mc - mean;
+        mean += delta * (32.f / ncnt);
+        m2 += qc + delta * delta * (cnt * 32.f / ncnt);
+        cnt = ncnt;
+      }
+      {
+        float* mine = red + (ch * 128 + lg * 32 + lane) * 3;
+        mine[0] = cnt; mine[1] = mean; mine[2] = m2;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float* oth = red + ((ch ^ 1) * 128 + lg * 32 + lane) * 3;
+        const float on = oth[0], om = oth[1], oq = oth[2];
+        const float ncnt = cnt + on, delta = om - mean;
+        mean += delta * (on / ncnt);
+        m2 += oq + delta * delta * (cnt * on / ncnt);
+      }
+      const float inv = 1.f / (sqrtf(m2 / (float)(d - 1)) + p.eps);   // modules.py:30-31: unbiased std, eps on the std
+      // pass 2: normalise, transpose through smem, gains + coalesced stores
+#pragma unroll 1
+      for (int c0 = 0; c0 < hcols; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tacc + c0, r);
+        if (c0 + 32 >= hcols) {  // accumulator fully read by this warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty);
+        }
+        const int col = ch * hcols + c0;
+        const float* bp = p.bias + col;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(bp + 4 * q));
+          const float x0 = (fmaxf(__uint_as_float(r[4 * q]) + b.x, 0.f) - mean) * inv;
+          const float x1 = (fmaxf(__uint_as_float(r[4 * q + 1]) + b.y, 0.f) - mean) * inv;
+          const float x2 = (fmaxf(__uint_as_float(r[4 * q + 2]) + b.z, 0.f) - mean) * inv;
+          const float x3 = (fmaxf(__uint_as_float(r[4 * q + 3]) + b.w, 0.f) - mean) * inv;
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stg_w + 16 * q), "f"(x0), "f"(x1), "f"(x2), "f"(x3) : "memory");
+        }
+        __syncwarp();
+        const int cc = col + sub_c;
+        const float4 ga = __ldg(reinterpret_cast<const float4*>(p.a2 + cc)), gb = __ldg(reinterpret_cast<const float4*>(p.b2 + cc));
+        float4 y[8];
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr)
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(y[rr].x), "=f"(y[rr].y), "=f"(y[rr].z), "=f"(y[rr].w)
+                       : "r"(stg_r + (uint32_t)(rr * 4 * VP_STG_LD * 4))
+                       : "memory");
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+          const int row = row_w0 + rr * 4 + sub_r;
+          if (row < p.N) {
+            const float4 o = make_float4(fmaf(y[rr].x, ga.x, gb.x), fmaf(y[rr].y, ga.y, gb.y), fmaf(y[rr].z, ga.z, gb.z),
+                                         fmaf(y[rr].w, ga.w, gb.w));
+            if (p.out_bf16) st4(reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * d + cc, o);
+            else st4(reinterpret_cast<float*>(p.out) + (long long)row * d + cc, o);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+#ifdef BIST_GEMM_TRACE
+extern "C" int bist_debug_vp_trace(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_vtrace, sizeof(g_vtrace)) == cudaSuccess ? 0 : 1;
+}
+#endif
+
+// Fused bf16-mode projection; *taken = false when the shape is left to the GEMM + LayerNorm pair (vidproj.cu).
+// wb: bf16 copy of W [d, D] (workspace).
+int vidproj_fused(const float* fts, const float* W, const float* bias, const float* a2, const float* b2, void* out, int64_t N,
+                  int64_t D, int64_t d, float eps, void* wb, int out_dtype, cudaStream_t st, bool* taken) {
+  *taken = false;
+  if (d % 64 != 0 || d > 512 || D % VP_BK != 0 || N < 1 || N >= (1LL << 31) - 128) return 0;
+  if ((reinterpret_cast<uintptr_t>(fts) & 15) || (reinterpret_cast<uintptr_t>(wb) & 15) || (reinterpret_cast<uintptr_t>(out) & 15) ||
+      (reinterpret_cast<uintptr_t>(bias) & 15) || (reinterpret_cast<uintptr_t>(a2) & 15) || (reinterpret_cast<uintptr_t>(b2) & 15))
+    return 0;
+  const VpSmem L = vp_smem((int)d);
+  if (L.total > 227 * 1024) return 0;
+  *taken = true;
+  BIST_TRY(pack_matrix(W, wb, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
+  const int nmma = (int)(d > 256 ? d / 2 : d);
+  CUtensorMap ma, mw;
+  BIST_TRY(make_map_2d(&ma, fts, true, D, N, VP_BK, 128, 128));
+  BIST_TRY(make_map_2d(&mw, wb, false, D, d, VP_BK, nmma, 64));
+  static bool configured = false;
+  if (!configured) {
+    BIST_CUDA(cudaFuncSetAttribute(vidproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  VpArgs p;
+  p.bias = bias; p.a2 = a2; p.b2 = b2; p.out = out;
+  p.N = (int)N; p.D = (int)D; p.d = (int)d; p.out_bf16 = out_dtype == BIST_BF16;
+  p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
+  const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+  ProfScope ps("vidproj_fused", st);
+  vidproj_kernel<<<grid, 320, L.total, st>>>(ma, mw, p);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+}  // namespace bist
