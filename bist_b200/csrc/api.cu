@@ -4,6 +4,7 @@
 // live in st_layer.cu.
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <map>
@@ -23,6 +24,10 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+bool pdl_enabled() {
+  static const bool on = getenv("BIST_NO_PDL") == nullptr;
+  return on;
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 

@@ -15,6 +15,8 @@ constexpr float kMaskFill = -1e9f;  // modules.py:60
 template <typename TV, typename TC>
 __global__ void __launch_bounds__(256) softmax_pv_kernel(SoftmaxPvArgs a, int LT, int LTP) {
   extern __shared__ __align__(16) float Ps[];
+  pdl_trigger();
+  pdl_wait();
   const int g = blockIdx.x;
   const int l0 = blockIdx.y * LT;
   const int nl = min(LT, a.Lq - l0);
@@ -107,7 +109,7 @@ int launch_softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
     BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   dim3 grid(a.G, (a.Lq + LT - 1) / LT);
   ProfScope ps("softmax_pv", st);
-  kern<<<grid, 256, smem, st>>>(a, LT, LTP);
+  BIST_LAUNCH(kern, grid, 256, smem, st, a, LT, LTP);
   BIST_LAUNCHED();
   return 0;
 }
@@ -119,6 +121,8 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
                                                      const uint8_t* __restrict__ mask, TO* __restrict__ ctxx,
                                                      int B, int G, int Lq, int h, int d) {
   extern __shared__ __align__(16) float sm[];
+  pdl_trigger();
+  pdl_wait();
   float* q = sm;           // [h][d]
   float* sc = sm + h * d;  // [h][G]
   const int b = blockIdx.x / Lq, l = blockIdx.x % Lq;
@@ -187,6 +191,8 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
 template <typename TD>
 __global__ void pack_kernel(const float* __restrict__ src, TD* __restrict__ dst, int rows, int cols,
                             int transpose, float scale) {
+  pdl_trigger();
+  pdl_wait();
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)rows * cols) return;
   int r = (int)(i / cols), c = (int)(i % cols);
@@ -217,7 +223,7 @@ int launch_stage2(const float* qf, const void* x1, const uint8_t* mask, void* ct
   auto kern = stage2_kernel<TX, TO, 8>;
   if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   ProfScope ps("stage2_attn", st);
-  kern<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), B, G,
+  BIST_LAUNCH(kern, dim3((unsigned)(B * Lq)), 256, smem, st, qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), B, G,
                                                    Lq, h, d);
   BIST_LAUNCHED();
   return 0;
@@ -251,9 +257,9 @@ int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, 
   unsigned grid = (unsigned)((n + 255) / 256);
   ProfScope ps("pack", st);
   if (dst_dtype == BIST_BF16)
-    pack_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, transpose, scale);
+    BIST_LAUNCH((pack_kernel<__nv_bfloat16>), grid, 256, 0, st, src, reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, transpose, scale);
   else
-    pack_kernel<float><<<grid, 256, 0, st>>>(src, reinterpret_cast<float*>(dst), rows, cols, transpose, scale);
+    BIST_LAUNCH((pack_kernel<float>), grid, 256, 0, st, src, reinterpret_cast<float*>(dst), rows, cols, transpose, scale);
   BIST_LAUNCHED();
   return 0;
 }

@@ -47,6 +47,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 template <int KS, int NT>  // KS = 16-key steps (nk <= 16*KS); NT = 8-column tiles per head (dk = 8*NT, NT even)
 __global__ void __launch_bounds__(256, (KS <= 3 ? 3 : 1)) softmax_pv_mma_kernel(SoftmaxPvArgs a) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
+  pdl_trigger();
+  pdl_wait();
   const int d = a.h * a.dk, ldv = d + 8;  // +8 bf16 = 16 bytes of row padding: ldmatrix rows hit distinct banks
   __nv_bfloat16* Vs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   __nv_bfloat16* Os = Vs + (size_t)16 * KS * ldv;
@@ -223,7 +225,7 @@ int launch_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
   }
   dim3 grid(a.G, (a.Lq + 15) / 16);
   ProfScope ps("softmax_pv_mma", st);
-  kern<<<grid, 256, smem, st>>>(a);
+  BIST_LAUNCH(kern, grid, 256, smem, st, a);
   BIST_LAUNCHED();
   return 0;
 }
@@ -249,6 +251,8 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
                                                          const uint8_t* __restrict__ mask, __nv_bfloat16* __restrict__ out,
                                                          int G, int Gp, int Lq, int h, int d) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
+  pdl_trigger();
+  pdl_wait();
   const int ldx = d + 8, ldp = Gp + 8;
   __nv_bfloat16* Xs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   __nv_bfloat16* Qs = Xs + (size_t)Gp * ldx;
@@ -361,6 +365,8 @@ __global__ void __launch_bounds__(256) stage2_v2_kernel(const float* __restrict_
                                                         const uint8_t* __restrict__ mask, TO* __restrict__ ctxx,
                                                         int G, int Lq, int d) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
+  pdl_trigger();
+  pdl_wait();
   TX* Xs = reinterpret_cast<TX*>(smem_raw);                                        // [G][d]
   float* Qs = reinterpret_cast<float*>(smem_raw + (((size_t)G * d * sizeof(TX) + 15) & ~(size_t)15));  // [H][d]
   float* Ps = Qs + (size_t)H * d;                                                  // [H][G]
@@ -449,7 +455,7 @@ int launch_s2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, 
     configured = true;
   }
   ProfScope ps("stage2_v2", st);
-  kern<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), G, Lq, d);
+  BIST_LAUNCH(kern, dim3((unsigned)(B * Lq)), 256, smem, st, qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), G, Lq, d);
   BIST_LAUNCHED();
   return 0;
 }
@@ -496,6 +502,8 @@ template <int KT, int DKS>  // DKS = dk / 16
 __global__ void __launch_bounds__(256) self_attn_mma_kernel(const __nv_bfloat16* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                             int mask_mod, __nv_bfloat16* __restrict__ ctx, int Lq, int h, float scale) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
+  pdl_trigger();
+  pdl_wait();
   constexpr int LP = 16 * KT, dk = 16 * DKS;
   const int d = h * dk, ld = 3 * d + 8;
   __nv_bfloat16* Ts = reinterpret_cast<__nv_bfloat16*>(smem_raw);  // [LP][3d+8]; the q columns are reused as the output stage
@@ -619,7 +627,7 @@ int launch_self(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, i
   auto go = [&](auto kern) -> int {
     BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     ProfScope ps("self_attn_mma", st);
-    kern<<<dim3((unsigned)G), 256, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), mask, mask_mod,
+    BIST_LAUNCH(kern, dim3((unsigned)G), 256, smem, st, reinterpret_cast<const __nv_bfloat16*>(qkv), mask, mask_mod,
                                               reinterpret_cast<__nv_bfloat16*>(ctx), Lq, h, scale);
     BIST_LAUNCHED();
     return 0;
@@ -666,7 +674,7 @@ int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, in
     configured = true;
   }
   ProfScope ps("stage2_mma", st);
-  stage2_mma_kernel<<<dim3((unsigned)(B * Lq)), 256, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(q),
+  BIST_LAUNCH(stage2_mma_kernel, dim3((unsigned)(B * Lq)), 256, smem, st, reinterpret_cast<const __nv_bfloat16*>(q),
                                                                 reinterpret_cast<const __nv_bfloat16*>(x1), mask,
                                                                 reinterpret_cast<__nv_bfloat16*>(out), G, Gp, Lq, h, d);
   BIST_LAUNCHED();

@@ -50,6 +50,30 @@ struct ProfScope {
     BIST_CUDA(cudaGetLastError());          \
   } while (0)
 
+// ---- launches: programmatic dependent launch (PDL) ------------------------------------------------------------
+// Every kernel of the library is launched with programmatic stream serialization allowed: it calls
+// pdl_trigger() first (the next kernel in the stream may start launching once all CTAs of this one have
+// started) and pdl_wait() before its first access to global memory (blocks until the previous kernel has
+// completed and flushed).  Prologues (barrier init, TMEM allocation, smem carve-up) therefore overlap the tail
+// of the previous kernel, inside CUDA graphs too.  BIST_NO_PDL=1 turns the attribute off.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... P, typename... A>
+inline cudaError_t launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, P(args)...);
+}
+#endif
+#define BIST_LAUNCH(kern, grid, block, smem, st, ...) \
+  BIST_CUDA(::bist::launch_pdl(kern, dim3(grid), dim3(block), (size_t)(smem), st, __VA_ARGS__))
+
 static inline size_t dtype_size(int dt) { return dt == BIST_BF16 ? 2 : 4; }
 static inline bool dtype_ok(int dt) { return dt == BIST_F32 || dt == BIST_BF16; }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

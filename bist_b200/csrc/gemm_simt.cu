@@ -19,6 +19,8 @@ gemm_simt_kernel(GemmArgs g) {
   constexpr int W_LD = BN * BK / 4 / NT;
   static_assert(A_LD >= 1 && W_LD >= 1, "tile too small for the thread count");
 
+  pdl_trigger();
+  pdl_wait();
   const int tid = threadIdx.x;
   const int z = blockIdx.z;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
@@ -165,9 +167,9 @@ int launch(const GemmArgs& g, bool vec, cudaStream_t st) {
   constexpr int NT = (BM / TM) * (BN / TN);
   ProfScope ps(g.tag, st);
   if (vec)
-    gemm_simt_kernel<BM, BN, TM, TN, TA, TW, true><<<grid, NT, 0, st>>>(g);
+    BIST_LAUNCH((gemm_simt_kernel<BM, BN, TM, TN, TA, TW, true>), grid, NT, 0, st, g);
   else
-    gemm_simt_kernel<BM, BN, TM, TN, TA, TW, false><<<grid, NT, 0, st>>>(g);
+    BIST_LAUNCH((gemm_simt_kernel<BM, BN, TM, TN, TA, TW, false>), grid, NT, 0, st, g);
   BIST_LAUNCHED();
   return 0;
 }

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
   constexpr int ESZ = TF32 ? 4 : 2;
   constexpr int BKE = SLAB_BYTES / ESZ;        // elements of K per slab: 64 bf16 / 32 tf32
   constexpr int UMMA_K = 32 / ESZ;             // 16 bf16 / 8 tf32 (32 bytes of K per instruction)
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + S::BAR_OFF);
@@ -81,6 +82,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the tail of the previous kernel
   const int per_z = t.tiles_m * t.tiles_n;
 
   if (warp == 0) {
@@ -280,7 +282,7 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
   tt.total_tiles = tt.tiles_m * tt.tiles_n * t.g.Z;
   const int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
   ProfScope ps(t.g.tag, st);
-  kern<<<grid, 320, smem, st>>>(ma, mw, tt);
+  BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, tt);
   BIST_LAUNCHED();
   return 0;
 }

@@ -11,6 +11,8 @@ __global__ void __launch_bounds__(256) ln_rows_vec(const TX* __restrict__ x, con
                                                    const float* __restrict__ b2, TY* __restrict__ y,
                                                    long long rows, int d, float eps,
                                                    long long group_rows, long long pstride, long long x_gstride) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -63,6 +65,8 @@ __global__ void __launch_bounds__(256) ln_rows_any(const TX* __restrict__ x, con
                                                    const float* __restrict__ b2, TY* __restrict__ y,
                                                    long long rows, int d, float eps,
                                                    long long group_rows, long long pstride, long long x_gstride) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -94,6 +98,8 @@ __global__ void __launch_bounds__(256) ln2_rows_vec(const float* __restrict__ x,
                                                     const float* __restrict__ b2b, TY* __restrict__ ya,
                                                     TY* __restrict__ yb, TY* __restrict__ xc, long long rows, int d,
                                                     float eps, long long group_rows, long long pstride) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -146,11 +152,11 @@ int launch(const void* x, const float* a2, const float* b2, void* y, int64_t row
                  ((uintptr_t)a2 % 16 == 0) && ((uintptr_t)b2 % 16 == 0);
   ProfScope ps("layer_norm", st);
   if (aligned && d <= 512)
-    ln_rows_vec<TX, TY, 4><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
+    BIST_LAUNCH((ln_rows_vec<TX, TY, 4>), grid, wpb * 32, 0, st, xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   else if (aligned && d <= 2048)
-    ln_rows_vec<TX, TY, 16><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
+    BIST_LAUNCH((ln_rows_vec<TX, TY, 16>), grid, wpb * 32, 0, st, xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   else
-    ln_rows_any<TX, TY><<<grid, wpb * 32, 0, st>>>(xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
+    BIST_LAUNCH((ln_rows_any<TX, TY>), grid, wpb * 32, 0, st, xp, a2, b2, yp, rows, (int)d, eps, group_rows, pstride, x_gstride);
   BIST_LAUNCHED();
   return 0;
 }
@@ -186,12 +192,12 @@ int layer_norm2(const float* x, const float* a2a, const float* b2a, const float*
   ProfScope ps("layer_norm", st);
   if (y_dtype == BIST_BF16) {
     auto Y = [](void* p) { return reinterpret_cast<__nv_bfloat16*>(p); };
-    if (d <= 512) ln2_rows_vec<__nv_bfloat16, 4><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
-    else ln2_rows_vec<__nv_bfloat16, 16><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    if (d <= 512) BIST_LAUNCH((ln2_rows_vec<__nv_bfloat16, 4>), grid, wpb * 32, 0, st, x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    else BIST_LAUNCH((ln2_rows_vec<__nv_bfloat16, 16>), grid, wpb * 32, 0, st, x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
   } else {
     auto Y = [](void* p) { return reinterpret_cast<float*>(p); };
-    if (d <= 512) ln2_rows_vec<float, 4><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
-    else ln2_rows_vec<float, 16><<<grid, wpb * 32, 0, st>>>(x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    if (d <= 512) BIST_LAUNCH((ln2_rows_vec<float, 4>), grid, wpb * 32, 0, st, x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
+    else BIST_LAUNCH((ln2_rows_vec<float, 16>), grid, wpb * 32, 0, st, x, a2a, b2a, a2b, b2b, Y(ya), Y(yb), Y(xc), rows, (int)d, eps, group_rows, pstride);
   }
   BIST_LAUNCHED();
   return 0;

@@ -57,6 +57,7 @@ struct VpArgs {
 
 __global__ void __launch_bounds__(320, 1) vidproj_kernel(const __grid_constant__ CUtensorMap map_a,
                                                          const __grid_constant__ CUtensorMap map_w, const VpArgs p) {
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const VpSmem L = vp_smem(p.d);
@@ -81,6 +82,7 @@ __global__ void __launch_bounds__(320, 1) vidproj_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the tail of the previous kernel
 
   if (warp == 0) {
     if (lane == 0) {
@@ -298,7 +300,7 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   ProfScope ps("vidproj_fused", st);
-  vidproj_kernel<<<grid, 320, L.total, st>>>(ma, mw, p);
+  BIST_LAUNCH(vidproj_kernel, grid, 320, L.total, st, ma, mw, p);
   BIST_LAUNCHED();
   return 0;
 }
