@@ -215,3 +215,43 @@ int bist_ffn_fwd(const void* x, const void* w1, const float* b1, const void* w2,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------- backward building blocks
+extern "C" {
+
+int bist_ln_bwd(const void* dy, const void* x, const float* a_2, void* dx, float* da_2, float* db_2, int64_t rows, int64_t d,
+                float eps, int dy_dtype, int x_dtype, int dx_dtype, void* stream) {
+  BIST_CHECK_ARG(dtype_ok(dy_dtype) && dtype_ok(x_dtype) && dtype_ok(dx_dtype), "ln_bwd: bad dtype");
+  LnBwdArgs a;
+  a.dy = dy; a.x = x; a.a2 = a_2; a.dx = dx; a.da = da_2; a.db = db_2;
+  a.rows = rows; a.d = d; a.eps = eps;
+  a.dy_dtype = dy_dtype; a.x_dtype = x_dtype; a.dx_dtype = dx_dtype;
+  return layer_norm_bwd(a, (cudaStream_t)stream);
+}
+
+int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, float* dw, float* db, int64_t M, int64_t N,
+                    int64_t K, int dy_dtype, int x_dtype, int w_dtype, int dx_dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(dy && M > 0 && N > 0 && K > 0 && M < (1LL << 31), "linear_bwd: bad argument");
+  BIST_CHECK_ARG(dtype_ok(dy_dtype) && dtype_ok(x_dtype) && dtype_ok(w_dtype) && dtype_ok(dx_dtype), "linear_bwd: bad dtype");
+  if (dx) {
+    BIST_CHECK_ARG(wT, "linear_bwd: dx needs the transposed weight");
+    GemmArgs g;
+    g.A = dy; g.W = wT; g.C = dx;
+    g.M = (int)M; g.N = (int)K; g.K = (int)N;
+    g.a = rows_dense(N); g.w = rows_dense(N); g.c = rows_dense(K);
+    g.a_dtype = dy_dtype; g.w_dtype = w_dtype; g.c_dtype = dx_dtype; g.tag = "bwd_dx_gemm";
+    BIST_TRY(gemm(g, st));
+  }
+  if (dw) {
+    BIST_CHECK_ARG(x, "linear_bwd: dw needs x");
+    WgradArgs w;
+    w.A = dy; w.B = x; w.C = dw; w.colsum = db;
+    w.M = (int)M; w.N = (int)N; w.K = (int)K; w.lda = N; w.ldb = K; w.ldc = K;
+    w.a_dtype = dy_dtype; w.b_dtype = x_dtype; w.tag = "wgrad";
+    BIST_TRY(wgrad(w, st));
+  }
+  return 0;
+}
+
+}  // extern "C"

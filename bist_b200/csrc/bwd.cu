@@ -1,0 +1,812 @@
+// Backward-pass kernels of the BiST video hot path (training step).
+//   wgrad           weight / bias gradients: C[n,k] += sum_m A[m,n] B[m,k]   (nn.Linear backward w.r.t. weight)
+//   layer_norm_bwd  LayerNorm backward (modules.py:28-31: unbiased std, eps added to the std)
+//   attn_core_bwd   attention() backward with projected q,k,v (modules.py:54-64)       -> query self-attention
+//   stage1_bwd      softmax / weighted-sum backward of stage 1 over the folded scores   (encoder.py:111-121 / 143-148)
+//   stage2_bwd      stage-2 backward, projections folded to the query side            (encoder.py:125-132 / 152-161)
+//   relu_gate, group_sum, cast_copy   small element-wise helpers
+// All probabilities are recomputed from saved scores / operands; nothing here allocates.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace bist {
+namespace {
+
+constexpr float kMaskFill = -1e9f;  // modules.py:60
+
+template <typename T>
+__device__ __forceinline__ float ldf(const T* p) { return to_f32(*p); }
+
+// ------------------------------------------------------------------------------------------------ wgrad (CUDA cores)
+// grid (tiles_n * tiles_k, splits, Z); block 256 = 16 x 16 threads, 4 x 4 outputs each; tile 64 x 64, 16 rows per step.
+constexpr int WG_T = 64, WG_R = 16;
+
+template <typename TA, typename TB>
+__global__ void __launch_bounds__(256) wgrad_simt_kernel(WgradArgs w, int tiles_k, int rows_per_split) {
+  __shared__ __align__(16) float As[2][WG_R][WG_T];
+  __shared__ __align__(16) float Bs[2][WG_R][WG_T];
+  pdl_trigger();
+  pdl_wait();
+  const int z = blockIdx.z;
+  const int tn = blockIdx.x / tiles_k, tk = blockIdx.x % tiles_k;
+  const int n0 = tn * WG_T, k0 = tk * WG_T;
+  const int m_begin = blockIdx.y * rows_per_split;
+  const int m_end = min(w.M, m_begin + rows_per_split);
+  if (m_begin >= m_end) return;
+  const TA* A = reinterpret_cast<const TA*>(w.A) + w.az.off(z, w.zin, 1);
+  const TB* B = reinterpret_cast<const TB*>(w.B) + w.bz.off(z, w.zin, 1);
+  const int t = threadIdx.x;
+  const int lc = t & 63, lr = t >> 6;  // loader: column lc, rows lr + 4*i
+  const int ty = t >> 4, tx = t & 15;  // compute: n = n0 + ty*4 + i, k = k0 + tx*4 + j
+  const bool do_cs = w.colsum != nullptr && tk == 0;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  float cs = 0.f;
+  float ra[4], rb[4];
+  auto gload = [&](int m0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + lr + 4 * i;
+      ra[i] = (m < m_end && n0 + lc < w.N) ? ldf(A + (long long)m * w.lda + n0 + lc) : 0.f;
+      rb[i] = (m < m_end && k0 + lc < w.K) ? ldf(B + (long long)m * w.ldb + k0 + lc) : 0.f;
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      As[buf][lr + 4 * i][lc] = ra[i];
+      Bs[buf][lr + 4 * i][lc] = rb[i];
+    }
+  };
+  gload(m_begin);
+  sstore(0);
+  __syncthreads();
+  const int steps = (m_end - m_begin + WG_R - 1) / WG_R;
+  for (int s = 0; s < steps; ++s) {
+    const int buf = s & 1;
+    if (s + 1 < steps) gload(m_begin + (s + 1) * WG_R);
+#pragma unroll
+    for (int mm = 0; mm < WG_R; ++mm) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[buf][mm][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[buf][mm][tx * 4]);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (do_cs && t < WG_T) {
+#pragma unroll
+      for (int mm = 0; mm < WG_R; ++mm) cs += As[buf][mm][t];
+    }
+    if (s + 1 < steps) {
+      sstore(buf ^ 1);
+      __syncthreads();
+    }
+  }
+  float* C = w.C + w.cz.off(z, w.zin, 1);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int n = n0 + ty * 4 + i;
+    if (n >= w.N) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + tx * 4 + j;
+      if (k < w.K) atomicAdd(C + (long long)n * w.ldc + k, w.alpha * acc[i][j]);
+    }
+  }
+  if (do_cs && t < WG_T && n0 + t < w.N) atomicAdd(w.colsum + w.sz.off(z, w.zin, 1) + n0 + t, cs);
+}
+
+// ------------------------------------------------------------------------------------------------ wgrad (tensor cores)
+// bf16 x bf16 (B may also be fp32, converted while staging) -> fp32, mma.sync.m16n8k16.  The contraction runs over
+// the rows of both operands, so both fragments come out of row-major smem tiles through ldmatrix.trans.
+// CTA tile 128 (n) x 128 (k), 32 rows per step, 8 warps as 4 (n) x 2 (k): warp tile 32 x 64.
+constexpr int WM_TN = 128, WM_TK = 128, WM_R = 32, WM_LD = 136;  // smem row stride in bf16 (272 B: conflict-free ldmatrix)
+
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ uint4 load8_bf16(const __nv_bfloat16* p) { return *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ uint4 load8_bf16(const float* p) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  __nv_bfloat162 v0 = __floats2bfloat162_rn(a.x, a.y), v1 = __floats2bfloat162_rn(a.z, a.w);
+  __nv_bfloat162 v2 = __floats2bfloat162_rn(b.x, b.y), v3 = __floats2bfloat162_rn(b.z, b.w);
+  uint4 u;
+  u.x = *reinterpret_cast<uint32_t*>(&v0); u.y = *reinterpret_cast<uint32_t*>(&v1);
+  u.z = *reinterpret_cast<uint32_t*>(&v2); u.w = *reinterpret_cast<uint32_t*>(&v3);
+  return u;
+}
+
+template <typename TB>
+__global__ void __launch_bounds__(256) wgrad_mma_kernel(WgradArgs w, int tiles_k, int rows_per_split) {
+  __shared__ __align__(16) __nv_bfloat16 As[2][WM_R][WM_LD];
+  __shared__ __align__(16) __nv_bfloat16 Bs[2][WM_R][WM_LD];
+  pdl_trigger();
+  pdl_wait();
+  const int z = blockIdx.z;
+  const int tn = blockIdx.x / tiles_k, tk = blockIdx.x % tiles_k;
+  const int n0 = tn * WM_TN, k0 = tk * WM_TK;
+  const int m_begin = blockIdx.y * rows_per_split;
+  const int m_end = min(w.M, m_begin + rows_per_split);
+  if (m_begin >= m_end) return;
+  const __nv_bfloat16* A = reinterpret_cast<const __nv_bfloat16*>(w.A) + w.az.off(z, w.zin, 1);
+  const TB* B = reinterpret_cast<const TB*>(w.B) + w.bz.off(z, w.zin, 1);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int wn = warp >> 1, wk = warp & 1;  // warp tile: n in [wn*32, +32), k in [wk*64, +64)
+  // loader: 32 rows x 128 cols = 512 chunks of 8 elements; thread t takes chunks t and t + 256
+  const int lrow = t >> 4, lcol = (t & 15) * 8;
+  const bool do_cs = w.colsum != nullptr && tk == 0;
+  uint4 ra[2], rb[2];
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  auto gload = [&](int m0) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int m = m0 + lrow + 16 * i;
+      // N and K are multiples of 8 (checked by the host), so a chunk is either fully inside or fully outside
+      ra[i] = (m < m_end && n0 + lcol < w.N) ? load8_bf16(A + (long long)m * w.lda + n0 + lcol) : zero4;
+      rb[i] = (m < m_end && k0 + lcol < w.K) ? load8_bf16(B + (long long)m * w.ldb + k0 + lcol) : zero4;
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      *reinterpret_cast<uint4*>(&As[buf][lrow + 16 * i][lcol]) = ra[i];
+      *reinterpret_cast<uint4*>(&Bs[buf][lrow + 16 * i][lcol]) = rb[i];
+    }
+  };
+  float acc[2][8][4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.f;
+  float cs = 0.f;
+  gload(m_begin);
+  sstore(0);
+  __syncthreads();
+  const int steps = (m_end - m_begin + WM_R - 1) / WM_R;
+  const int lm = lane & 7, lq = lane >> 3;  // ldmatrix: lane supplies row lm of 8x8 matrix number lq
+  for (int s = 0; s < steps; ++s) {
+    const int buf = s & 1;
+    if (s + 1 < steps) gload(m_begin + (s + 1) * WM_R);
+#pragma unroll
+    for (int ks = 0; ks < WM_R / 16; ++ks) {
+      // A fragments (mma "row" operand [16 n x 16 m]) from As[m][n] via .trans:
+      //   matrix 0: n 0-7,  m 0-7 ; 1: n 8-15, m 0-7 ; 2: n 0-7, m 8-15 ; 3: n 8-15, m 8-15
+      uint32_t af[2][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int mrow = ks * 16 + (lq >> 1) * 8 + lm;
+        const int ncol = wn * 32 + i * 16 + (lq & 1) * 8;
+        ldsm_x4_t((uint32_t)__cvta_generic_to_shared(&As[buf][mrow][ncol]), af[i][0], af[i][1], af[i][2], af[i][3]);
+      }
+      // B fragments (mma "col" operand [16 m x 8 k]) from Bs[m][k] via .trans: matrices (m 0-7 | m 8-15) x (k 0-7 | k 8-15)
+#pragma unroll
+      for (int jp = 0; jp < 4; ++jp) {
+        const int mrow = ks * 16 + (lq & 1) * 8 + lm;
+        const int kcol = wk * 64 + jp * 16 + (lq >> 1) * 8;
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t((uint32_t)__cvta_generic_to_shared(&Bs[buf][mrow][kcol]), b0, b1, b2, b3);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          mma_bf16(acc[i][jp * 2], af[i], b0, b1);
+          mma_bf16(acc[i][jp * 2 + 1], af[i], b2, b3);
+        }
+      }
+    }
+    if (do_cs && t < WM_TN) {
+#pragma unroll 8
+      for (int mm = 0; mm < WM_R; ++mm) cs += __bfloat162float(As[buf][mm][t]);
+    }
+    if (s + 1 < steps) {
+      sstore(buf ^ 1);
+      __syncthreads();
+    }
+  }
+  float* C = w.C + w.cz.off(z, w.zin, 1);
+  const int gr = lane >> 2, gc = (lane & 3) * 2;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int n = n0 + wn * 32 + i * 16 + gr + (q >> 1) * 8;
+        const int k = k0 + wk * 64 + j * 8 + gc + (q & 1);
+        if (n < w.N && k < w.K) atomicAdd(C + (long long)n * w.ldc + k, w.alpha * acc[i][j][q]);
+      }
+  if (do_cs && t < WM_TN && n0 + t < w.N) atomicAdd(w.colsum + w.sz.off(z, w.zin, 1) + n0 + t, cs);
+}
+
+int num_sms_cached() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <typename TA, typename TB>
+int launch_wgrad_simt(const WgradArgs& w, cudaStream_t st) {
+  const int tiles_n = (w.N + WG_T - 1) / WG_T, tiles_k = (w.K + WG_T - 1) / WG_T;
+  const long long base = (long long)tiles_n * tiles_k * w.Z;
+  long long splits = (2LL * num_sms_cached() + base - 1) / base;
+  const long long max_splits = (w.M + 4 * WG_R - 1) / (4 * WG_R);
+  splits = splits < 1 ? 1 : (splits > max_splits ? max_splits : splits);
+  if (splits > 65535) splits = 65535;
+  int rows = (int)((w.M + splits - 1) / splits);
+  rows = (rows + WG_R - 1) / WG_R * WG_R;
+  splits = (w.M + rows - 1) / rows;
+  dim3 grid(tiles_n * tiles_k, (unsigned)splits, w.Z);
+  ProfScope ps(w.tag, st);
+  BIST_LAUNCH((wgrad_simt_kernel<TA, TB>), grid, 256, 0, st, w, tiles_k, rows);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+template <typename TB>
+int launch_wgrad_mma(const WgradArgs& w, cudaStream_t st) {
+  const int tiles_n = (w.N + WM_TN - 1) / WM_TN, tiles_k = (w.K + WM_TK - 1) / WM_TK;
+  const long long base = (long long)tiles_n * tiles_k * w.Z;
+  long long splits = (2LL * num_sms_cached() + base - 1) / base;
+  const long long max_splits = (w.M + 2 * WM_R - 1) / (2 * WM_R);
+  splits = splits < 1 ? 1 : (splits > max_splits ? max_splits : splits);
+  if (splits > 65535) splits = 65535;
+  int rows = (int)((w.M + splits - 1) / splits);
+  rows = (rows + WM_R - 1) / WM_R * WM_R;
+  splits = (w.M + rows - 1) / rows;
+  dim3 grid(tiles_n * tiles_k, (unsigned)splits, w.Z);
+  ProfScope ps(w.tag, st);
+  BIST_LAUNCH((wgrad_mma_kernel<TB>), grid, 256, 0, st, w, tiles_k, rows);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+}  // namespace
+
+int wgrad(const WgradArgs& w, cudaStream_t st) {
+  BIST_CHECK_ARG(w.A && w.B && w.C && w.M > 0 && w.N > 0 && w.K > 0 && w.Z > 0 && w.Z <= 65535, "wgrad: bad argument");
+  static const bool no_mma = getenv("BIST_DISABLE_TC") != nullptr;
+  // tensor-core path: bf16 A, bf16 or fp32 B, 16-byte aligned 8-element chunks everywhere
+  auto al = [](long long v, int esz) { return (v * esz) % 16 == 0; };
+  const int bsz = w.b_dtype == BIST_BF16 ? 2 : 4;
+  bool mma_ok = !no_mma && w.a_dtype == BIST_BF16 && w.N % 8 == 0 && w.K % 8 == 0 && w.M >= 64 &&
+                ((uintptr_t)w.A % 16 == 0) && ((uintptr_t)w.B % 16 == 0) && al(w.lda, 2) && al(w.ldb, bsz) &&
+                al(w.az.s0, 2) && al(w.az.s1, 2) && al(w.bz.s0, bsz) && al(w.bz.s1, bsz);
+  if (mma_ok) return w.b_dtype == BIST_BF16 ? launch_wgrad_mma<__nv_bfloat16>(w, st) : launch_wgrad_mma<float>(w, st);
+  if (w.a_dtype == BIST_F32 && w.b_dtype == BIST_F32) return launch_wgrad_simt<float, float>(w, st);
+  if (w.a_dtype == BIST_BF16 && w.b_dtype == BIST_BF16) return launch_wgrad_simt<__nv_bfloat16, __nv_bfloat16>(w, st);
+  if (w.a_dtype == BIST_BF16 && w.b_dtype == BIST_F32) return launch_wgrad_simt<__nv_bfloat16, float>(w, st);
+  return launch_wgrad_simt<float, __nv_bfloat16>(w, st);
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm backward
+namespace {
+
+// grid: ceil(rows / rows_per_cta) CTAs inside one parameter group each; block 256 (8 warps, one row per warp at a time).
+template <typename TDY, typename TX, typename TDX>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(LnBwdArgs a, int rows_per_cta, int ctas_per_group) {
+  extern __shared__ float sacc[];  // [2][d]: da, db partial sums of this CTA
+  pdl_trigger();
+  pdl_wait();
+  const int d = (int)a.d;
+  const int grp = blockIdx.x / ctas_per_group, cg = blockIdx.x % ctas_per_group;
+  const int64_t grows = a.group_rows > 0 ? a.group_rows : a.rows;
+  const int64_t r_begin = grp * grows + (int64_t)cg * rows_per_cta;
+  const int64_t r_end = min(grp * grows + grows, r_begin + rows_per_cta);
+  const bool want_p = a.da != nullptr;
+  if (want_p)
+    for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float* a2 = a.a2 + grp * a.pstride;
+  for (int64_t r = r_begin + warp; r < r_end; r += 8) {
+    const TX* x = reinterpret_cast<const TX*>(a.x) + r * d;
+    const TDY* dy = reinterpret_cast<const TDY*>(a.dy) + r * d;
+    float s = 0.f;
+    for (int c = lane; c < d; c += 32) s += to_f32(x[c]);
+    const float mu = warp_sum(s) / (float)d;
+    float ss = 0.f, sg = 0.f, sgc = 0.f;
+    for (int c = lane; c < d; c += 32) {
+      const float cc = to_f32(x[c]) - mu, g = to_f32(dy[c]) * a2[c];
+      ss = fmaf(cc, cc, ss);
+      sg += g;
+      sgc = fmaf(g, cc, sgc);
+    }
+    ss = warp_sum(ss); sg = warp_sum(sg); sgc = warp_sum(sgc);
+    const float sd = sqrtf(ss / (float)(d - 1));
+    const float rinv = 1.f / (sd + a.eps);
+    const float mg = sg / (float)d;
+    const float k2 = sd > 0.f ? rinv * rinv * sgc / ((float)(d - 1) * sd) : 0.f;
+    TDX* dx = reinterpret_cast<TDX*>(a.dx) + r * d;
+    for (int c = lane; c < d; c += 32) {
+      const float xv = to_f32(x[c]), cc = xv - mu, dyv = to_f32(dy[c]);
+      float v = rinv * (dyv * a2[c] - mg) - k2 * cc;
+      if (a.relu_gate && !(xv > 0.f)) v = 0.f;
+      if (a.accumulate) v += to_f32(dx[c]);
+      dx[c] = from_f32<TDX>(v);
+      if (want_p) {
+        atomicAdd(&sacc[c], dyv * cc * rinv);
+        atomicAdd(&sacc[d + c], dyv);
+      }
+    }
+  }
+  if (want_p) {
+    __syncthreads();
+    float* da = a.da + grp * a.gstride;
+    float* db = a.db + grp * a.gstride;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+      atomicAdd(da + i, sacc[i]);
+      atomicAdd(db + i, sacc[d + i]);
+    }
+  }
+}
+
+template <typename TDY, typename TX, typename TDX>
+int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
+  const int64_t grows = a.group_rows > 0 ? a.group_rows : a.rows;
+  const int64_t groups = a.rows / grows;
+  // enough CTAs to fill the machine, at least 8 rows (one per warp) each
+  int64_t per = (a.rows + 4LL * num_sms_cached() - 1) / (4LL * num_sms_cached());
+  per = per < 8 ? 8 : (per + 7) / 8 * 8;
+  const int64_t cpg = (grows + per - 1) / per;
+  ProfScope ps("ln_bwd", st);
+  BIST_LAUNCH((ln_bwd_kernel<TDY, TX, TDX>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+}  // namespace
+
+int layer_norm_bwd(const LnBwdArgs& a, cudaStream_t st) {
+  BIST_CHECK_ARG(a.dy && a.x && a.a2 && a.dx && a.rows > 0 && a.d > 1 && a.d <= 8192, "ln_bwd: bad argument");
+  BIST_CHECK_ARG((a.da == nullptr) == (a.db == nullptr), "ln_bwd: da and db go together");
+  const int64_t grows = a.group_rows > 0 ? a.group_rows : a.rows;
+  BIST_CHECK_ARG(a.rows % grows == 0, "ln_bwd: rows must be a multiple of group_rows");
+  const int key = a.dy_dtype * 4 + a.x_dtype * 2 + a.dx_dtype;
+  switch (key) {
+    case 0: return launch_ln_bwd<float, float, float>(a, st);
+    case 1: return launch_ln_bwd<float, float, __nv_bfloat16>(a, st);
+    case 2: return launch_ln_bwd<float, __nv_bfloat16, float>(a, st);
+    case 3: return launch_ln_bwd<float, __nv_bfloat16, __nv_bfloat16>(a, st);
+    case 4: return launch_ln_bwd<__nv_bfloat16, float, float>(a, st);
+    case 5: return launch_ln_bwd<__nv_bfloat16, float, __nv_bfloat16>(a, st);
+    case 6: return launch_ln_bwd<__nv_bfloat16, __nv_bfloat16, float>(a, st);
+    default: return launch_ln_bwd<__nv_bfloat16, __nv_bfloat16, __nv_bfloat16>(a, st);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ element-wise helpers
+namespace {
+
+template <typename T>
+__global__ void relu_gate_kernel(T* __restrict__ dy, const T* __restrict__ y, int64_t n) {
+  pdl_trigger();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    if (!(to_f32(y[i]) > 0.f)) dy[i] = from_f32<T>(0.f);
+}
+
+template <typename T>
+__global__ void group_sum_kernel(const T* __restrict__ in, float* __restrict__ out, int64_t Qrows, int G, int d) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = Qrows * d;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t q = i / d;
+    const int c = (int)(i % d);
+    const T* p = in + q * G * d + c;
+    float s = 0.f;
+    for (int g = 0; g < G; ++g) s += to_f32(p[(int64_t)g * d]);
+    out[i] += s;
+  }
+}
+
+template <typename TS, typename TD>
+__global__ void cast_kernel(const TS* __restrict__ src, TD* __restrict__ dst, int64_t n) {
+  pdl_trigger();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = from_f32<TD>(to_f32(src[i]));
+}
+
+inline unsigned ew_grid(int64_t n) {
+  int64_t g = (n + 255) / 256;
+  const int64_t cap = 8LL * num_sms_cached();
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st) {
+  ProfScope ps("relu_gate", st);
+  if (dtype == BIST_BF16) BIST_LAUNCH(relu_gate_kernel<__nv_bfloat16>, ew_grid(n), 256, 0, st, (__nv_bfloat16*)dy, (const __nv_bfloat16*)y, n);
+  else BIST_LAUNCH(relu_gate_kernel<float>, ew_grid(n), 256, 0, st, (float*)dy, (const float*)y, n);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int group_sum(const void* in, float* out, int64_t Qrows, int64_t G, int64_t d, int in_dtype, cudaStream_t st) {
+  ProfScope ps("group_sum", st);
+  if (in_dtype == BIST_BF16) BIST_LAUNCH(group_sum_kernel<__nv_bfloat16>, ew_grid(Qrows * d), 256, 0, st, (const __nv_bfloat16*)in, out, Qrows, (int)G, (int)d);
+  else BIST_LAUNCH(group_sum_kernel<float>, ew_grid(Qrows * d), 256, 0, st, (const float*)in, out, Qrows, (int)G, (int)d);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int cast_copy(const void* src, void* dst, int64_t n, int src_dtype, int dst_dtype, cudaStream_t st) {
+  ProfScope ps("cast", st);
+  const unsigned g = ew_grid(n);
+  if (src_dtype == BIST_F32 && dst_dtype == BIST_BF16) BIST_LAUNCH((cast_kernel<float, __nv_bfloat16>), g, 256, 0, st, (const float*)src, (__nv_bfloat16*)dst, n);
+  else if (src_dtype == BIST_BF16 && dst_dtype == BIST_F32) BIST_LAUNCH((cast_kernel<__nv_bfloat16, float>), g, 256, 0, st, (const __nv_bfloat16*)src, (float*)dst, n);
+  else if (src_dtype == BIST_F32) BIST_LAUNCH((cast_kernel<float, float>), g, 256, 0, st, (const float*)src, (float*)dst, n);
+  else BIST_LAUNCH((cast_kernel<__nv_bfloat16, __nv_bfloat16>), g, 256, 0, st, (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, n);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ attention() backward
+namespace {
+
+// grid (Bp * h); block 256.  smem (floats): Q[Lq][dkp] K[Lk][dkp] V[Lk][dkp] dC[Lq][dkp] P[Lq][Lkp] dS[Lq][Lkp]
+template <typename T>
+__global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  pdl_trigger();
+  pdl_wait();
+  const int b = blockIdx.x / a.h, hh = blockIdx.x % a.h;
+  const int Lq = a.Lq, Lk = a.Lk, dk = a.dk, dkp = dk + 1, Lkp = Lk + 1;
+  float* Qs = sm;
+  float* Ks = Qs + Lq * dkp;
+  float* Vs = Ks + Lk * dkp;
+  float* Cs = Vs + Lk * dkp;
+  float* Ps = Cs + Lq * dkp;
+  float* Ds = Ps + Lq * Lkp;
+  const T* q = reinterpret_cast<const T*>(a.q) + b * a.q_b + hh * dk;
+  const T* k = reinterpret_cast<const T*>(a.k) + b * a.k_b + hh * dk;
+  const T* v = reinterpret_cast<const T*>(a.v) + b * a.k_b + hh * dk;
+  const T* dc = reinterpret_cast<const T*>(a.dctx) + b * a.c_b + hh * dk;
+  const int t = threadIdx.x, nt = blockDim.x;
+  for (int i = t; i < Lq * dk; i += nt) {
+    const int l = i / dk, j = i % dk;
+    Qs[l * dkp + j] = to_f32(q[l * a.q_l + j]);
+    Cs[l * dkp + j] = to_f32(dc[l * a.c_l + j]);
+  }
+  for (int i = t; i < Lk * dk; i += nt) {
+    const int kk = i / dk, j = i % dk;
+    Ks[kk * dkp + j] = to_f32(k[kk * a.k_l + j]);
+    Vs[kk * dkp + j] = to_f32(v[kk * a.k_l + j]);
+  }
+  __syncthreads();
+  const float scale = rsqrtf((float)dk);
+  const uint8_t* mb = a.mask ? a.mask + (long long)(b % a.mask_mod) * a.m_b : nullptr;
+  for (int i = t; i < Lq * Lk; i += nt) {
+    const int l = i / Lk, kk = i % Lk;
+    float s = 0.f, dp = 0.f;
+    for (int j = 0; j < dk; ++j) {
+      s = fmaf(Qs[l * dkp + j], Ks[kk * dkp + j], s);
+      dp = fmaf(Cs[l * dkp + j], Vs[kk * dkp + j], dp);
+    }
+    s *= scale;
+    if (mb && mb[l * a.m_l + kk] == 0) s = kMaskFill;
+    Ps[l * Lkp + kk] = s;
+    Ds[l * Lkp + kk] = dp;
+  }
+  __syncthreads();
+  const int lane = t & 31, warp = t >> 5, nw = nt >> 5;
+  for (int l = warp; l < Lq; l += nw) {
+    float mx = -INFINITY;
+    for (int kk = lane; kk < Lk; kk += 32) mx = fmaxf(mx, Ps[l * Lkp + kk]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int kk = lane; kk < Lk; kk += 32) {
+      const float e = expf(Ps[l * Lkp + kk] - mx);
+      Ps[l * Lkp + kk] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    float dot = 0.f;
+    for (int kk = lane; kk < Lk; kk += 32) {
+      const float p = Ps[l * Lkp + kk] * inv;
+      Ps[l * Lkp + kk] = p;
+      dot = fmaf(p, Ds[l * Lkp + kk], dot);
+    }
+    dot = warp_sum(dot);
+    for (int kk = lane; kk < Lk; kk += 32) Ds[l * Lkp + kk] = Ps[l * Lkp + kk] * (Ds[l * Lkp + kk] - dot) * scale;
+  }
+  __syncthreads();
+  T* dq = reinterpret_cast<T*>(a.dq) + b * a.q_b + hh * dk;
+  T* dkk = reinterpret_cast<T*>(a.dk_) + b * a.k_b + hh * dk;
+  T* dv = reinterpret_cast<T*>(a.dv) + b * a.k_b + hh * dk;
+  for (int i = t; i < Lq * dk; i += nt) {
+    const int l = i / dk, j = i % dk;
+    float s = 0.f;
+    for (int kk = 0; kk < Lk; ++kk) s = fmaf(Ds[l * Lkp + kk], Ks[kk * dkp + j], s);
+    dq[l * a.q_l + j] = from_f32<T>(s);
+  }
+  for (int i = t; i < Lk * dk; i += nt) {
+    const int kk = i / dk, j = i % dk;
+    float sk = 0.f, sv = 0.f;
+    for (int l = 0; l < Lq; ++l) {
+      sk = fmaf(Ds[l * Lkp + kk], Qs[l * dkp + j], sk);
+      sv = fmaf(Ps[l * Lkp + kk], Cs[l * dkp + j], sv);
+    }
+    dkk[kk * a.k_l + j] = from_f32<T>(sk);
+    dv[kk * a.k_l + j] = from_f32<T>(sv);
+  }
+}
+
+}  // namespace
+
+int attn_core_bwd(const AttnBwdArgs& a, cudaStream_t st) {
+  BIST_CHECK_ARG(a.q && a.k && a.v && a.dctx && a.dq && a.dk_ && a.dv, "attn_bwd: null pointer");
+  BIST_CHECK_ARG(a.Bp > 0 && a.Lq > 0 && a.Lk > 0 && a.h > 0 && a.dk > 0, "attn_bwd: bad shape");
+  const size_t smem = ((size_t)(2 * a.Lq + 2 * a.Lk) * (a.dk + 1) + 2 * (size_t)a.Lq * (a.Lk + 1)) * 4;
+  if (smem > 200 * 1024) {
+    set_error("attn_bwd: Lq=%d Lk=%d dk=%d does not fit one CTA", a.Lq, a.Lk, a.dk);
+    return BIST_ERR_UNSUPPORTED;
+  }
+  ProfScope ps("attn_bwd", st);
+  if (a.dtype == BIST_BF16) {
+    auto kern = attn_bwd_kernel<__nv_bfloat16>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)(a.Bp * a.h), 256, smem, st, a);
+  } else {
+    auto kern = attn_bwd_kernel<float>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)(a.Bp * a.h), 256, smem, st, a);
+  }
+  BIST_LAUNCHED();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ stage-1 backward
+namespace {
+
+// grid G groups; block 256.  smem floats: P[Lq*h][nkp] (probabilities, then ds), dC[Lq][dkp], Vh[nk][dkp]
+template <typename TV, typename TS>
+__global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  pdl_trigger();
+  pdl_wait();
+  const SoftmaxPvArgs& f = a.f;
+  const int g = blockIdx.x;
+  const int h = f.h, nk = f.nk, Lq = f.Lq, dk = f.dk, dkp = dk + 1, nkp = nk + 1;
+  float* Ps = sm;                      // [Lq*h][nkp], row = l*h + hh
+  float* Cs = Ps + Lq * h * nkp;       // [Lq][dkp]
+  float* Vs = Cs + Lq * dkp;           // [nk][dkp]
+  const int t = threadIdx.x, nt = blockDim.x, lane = t & 31, warp = t >> 5, nw = nt >> 5;
+
+  // phase 1: probabilities of every (l, hh) row of this group, recomputed from the saved scores
+  const float* Sg = f.S + f.sg.off(g);
+  const uint8_t* Mg = f.mask ? f.mask + (long long)((g / f.mask_gdiv) % f.mask_gmod) * f.m_b : nullptr;
+  for (int r = warp; r < Lq * h; r += nw) {
+    const int l = r / h, hh = r % h;
+    const float* srow = Sg + (long long)l * f.s_l + (long long)hh * f.s_h;
+    const uint8_t* mrow = Mg ? Mg + (long long)l * f.m_l : nullptr;
+    float mx = -INFINITY;
+    for (int k = lane; k < nk; k += 32) {
+      float s = srow[(long long)k * f.s_k];
+      if (mrow && mrow[k] == 0) s = kMaskFill;
+      Ps[r * nkp + k] = s;
+      mx = fmaxf(mx, s);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int k = lane; k < nk; k += 32) {
+      const float e = expf(Ps[r * nkp + k] - mx);
+      Ps[r * nkp + k] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    for (int k = lane; k < nk; k += 32) Ps[r * nkp + k] *= inv;
+  }
+  __syncthreads();
+
+  const TV* Vg = reinterpret_cast<const TV*>(f.V) + f.vg.off(g);
+  TV* dVg = reinterpret_cast<TV*>(a.dV) + f.vg.off(g);
+  const TV* dCg = reinterpret_cast<const TV*>(a.dctx) + f.og.off(g);
+  for (int hh = 0; hh < h; ++hh) {
+    for (int i = t; i < Lq * dk; i += nt) {
+      const int l = i / dk, j = i % dk;
+      Cs[l * dkp + j] = to_f32(dCg[(long long)l * f.o_l + hh * dk + j]);
+    }
+    for (int i = t; i < nk * dk; i += nt) {
+      const int k = i / dk, j = i % dk;
+      Vs[k * dkp + j] = to_f32(Vg[f.v.off(k) + hh * dk + j]);
+    }
+    __syncthreads();
+    // dV[k, j] = sum_l p[l,hh,k] dC[l, j]   (uses p before it is overwritten by ds below)
+    for (int i = t; i < nk * dk; i += nt) {
+      const int k = i / dk, j = i % dk;
+      float s = 0.f;
+      for (int l = 0; l < Lq; ++l) s = fmaf(Ps[(l * h + hh) * nkp + k], Cs[l * dkp + j], s);
+      dVg[f.v.off(k) + hh * dk + j] = from_f32<TV>(s);
+    }
+    __syncthreads();
+    // dP[l,k] = dC[l,:] . V[k,:] ;  ds = p * (dP - sum_k p dP): one warp per row l
+    for (int l = warp; l < Lq; l += nw) {
+      float* prow = Ps + (l * h + hh) * nkp;
+      float dpv[8];  // nk <= 256
+      float dot = 0.f;
+      int c = 0;
+      for (int k = lane; k < nk; k += 32, ++c) {
+        float s = 0.f;
+        for (int j = 0; j < dk; ++j) s = fmaf(Cs[l * dkp + j], Vs[k * dkp + j], s);
+        dpv[c] = s;
+        dot = fmaf(prow[k], s, dot);
+      }
+      dot = warp_sum(dot);
+      c = 0;
+      for (int k = lane; k < nk; k += 32, ++c) prow[k] = prow[k] * (dpv[c] - dot);
+    }
+    __syncthreads();
+  }
+
+  // phase 3: write ds in both layouts
+  const int b = g / a.gdiv, gi = g % a.gdiv;
+  const int R = Lq * h;
+  TS* ds = reinterpret_cast<TS*>(a.ds) + (long long)b * R * a.TS;
+  TS* dsT = reinterpret_cast<TS*>(a.dsT) + (long long)b * a.TS * R;
+  for (int i = t; i < R * nk; i += nt) {  // k fastest: ds[b][r][ts]
+    const int r = i / nk, k = i % nk;
+    ds[(long long)r * a.TS + gi * a.ts_g + k * a.ts_k] = from_f32<TS>(Ps[r * nkp + k]);
+  }
+  for (int i = t; i < R * nk; i += nt) {  // r fastest: dsT[b][ts][r]
+    const int k = i / R, r = i % R;
+    dsT[((long long)gi * a.ts_g + k * a.ts_k) * R + r] = from_f32<TS>(Ps[r * nkp + k]);
+  }
+}
+
+}  // namespace
+
+int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st) {
+  const SoftmaxPvArgs& f = a.f;
+  BIST_CHECK_ARG(f.S && f.V && a.dctx && a.dV && a.ds && a.dsT, "stage1_bwd: null pointer");
+  BIST_CHECK_ARG(f.G > 0 && f.Lq > 0 && f.h > 0 && f.dk > 0 && f.nk > 0 && f.nk <= 256, "stage1_bwd: bad shape (nk <= 256)");
+  BIST_CHECK_ARG(a.ds_dtype == f.v_dtype, "stage1_bwd: ds dtype must equal the value dtype");
+  const size_t smem = ((size_t)f.Lq * f.h * (f.nk + 1) + (size_t)(f.Lq + f.nk) * (f.dk + 1)) * 4;
+  if (smem > 200 * 1024) {
+    set_error("stage1_bwd: Lq*h*nk = %d*%d*%d too large for one CTA", f.Lq, f.h, f.nk);
+    return BIST_ERR_UNSUPPORTED;
+  }
+  ProfScope ps("stage1_bwd", st);
+  if (f.v_dtype == BIST_BF16) {
+    auto kern = stage1_bwd_kernel<__nv_bfloat16, __nv_bfloat16>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)f.G, 256, smem, st, a);
+  } else {
+    auto kern = stage1_bwd_kernel<float, float>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)f.G, 256, smem, st, a);
+  }
+  BIST_LAUNCHED();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ stage-2 backward
+namespace {
+
+// grid B*Lq; block 256.  smem floats: QF[h][d], DU[h][d], P[h][Gp], DS[h][Gp]
+template <typename T>
+__global__ void __launch_bounds__(256) stage2_bwd_kernel(Stage2BwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  pdl_trigger();
+  pdl_wait();
+  const int q = blockIdx.x, b = q / a.Lq;
+  const int h = a.h, d = a.d, G = a.G, Gp = G + 1;
+  float* QF = sm;
+  float* DU = QF + h * d;
+  float* Ps = DU + h * d;
+  float* Ds = Ps + h * Gp;
+  const int t = threadIdx.x, nt = blockDim.x, lane = t & 31, warp = t >> 5, nw = nt >> 5;
+  const T* qf = reinterpret_cast<const T*>(a.qf) + (long long)q * h * d;
+  const T* du = reinterpret_cast<const T*>(a.du) + (long long)q * h * d;
+  const T* x1 = reinterpret_cast<const T*>(a.x1) + (long long)q * G * d;
+  for (int i = t; i < h * d; i += nt) {
+    QF[i] = to_f32(qf[i]);
+    DU[i] = to_f32(du[i]);
+  }
+  __syncthreads();
+  // scores and dP: one warp per key row g
+  for (int g = warp; g < G; g += nw) {
+    const T* xr = x1 + (long long)g * d;
+    for (int hh = 0; hh < h; ++hh) {
+      float s = 0.f, dp = 0.f;
+      for (int c = lane; c < d; c += 32) {
+        const float xv = to_f32(xr[c]);
+        s = fmaf(QF[hh * d + c], xv, s);
+        dp = fmaf(DU[hh * d + c], xv, dp);
+      }
+      s = warp_sum(s);
+      dp = warp_sum(dp);
+      if (lane == 0) {
+        if (a.mask && a.mask[(long long)b * G + g] == 0) s = kMaskFill;
+        Ps[hh * Gp + g] = s;
+        Ds[hh * Gp + g] = dp;
+      }
+    }
+  }
+  __syncthreads();
+  for (int hh = warp; hh < h; hh += nw) {
+    float mx = -INFINITY;
+    for (int g = lane; g < G; g += 32) mx = fmaxf(mx, Ps[hh * Gp + g]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int g = lane; g < G; g += 32) {
+      const float e = expf(Ps[hh * Gp + g] - mx);
+      Ps[hh * Gp + g] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    float dot = 0.f;
+    for (int g = lane; g < G; g += 32) {
+      const float p = Ps[hh * Gp + g] * inv;
+      Ps[hh * Gp + g] = p;
+      dot = fmaf(p, Ds[hh * Gp + g], dot);
+    }
+    dot = warp_sum(dot);
+    for (int g = lane; g < G; g += 32) Ds[hh * Gp + g] = Ps[hh * Gp + g] * (Ds[hh * Gp + g] - dot);
+  }
+  __syncthreads();
+  // dx1[g, c] = sum_hh p[hh,g] du[hh,c] + ds[hh,g] qf[hh,c]
+  T* dx1 = reinterpret_cast<T*>(a.dx1) + (long long)q * G * d;
+  for (int i = t; i < G * d; i += nt) {
+    const int g = i / d, c = i % d;
+    float s = 0.f;
+    for (int hh = 0; hh < h; ++hh) s = fmaf(Ps[hh * Gp + g], DU[hh * d + c], fmaf(Ds[hh * Gp + g], QF[hh * d + c], s));
+    dx1[i] = from_f32<T>(s);
+  }
+  // dqf[hh, c] = sum_g ds[hh,g] x1[g,c]
+  T* dqf = reinterpret_cast<T*>(a.dqf) + (long long)q * h * d;
+  for (int i = t; i < h * d; i += nt) {
+    const int hh = i / d, c = i % d;
+    float s = 0.f;
+    for (int g = 0; g < G; ++g) s = fmaf(Ds[hh * Gp + g], to_f32(x1[(long long)g * d + c]), s);
+    dqf[i] = from_f32<T>(s);
+  }
+}
+
+}  // namespace
+
+int stage2_bwd(const Stage2BwdArgs& a, cudaStream_t st) {
+  BIST_CHECK_ARG(a.qf && a.x1 && a.du && a.dx1 && a.dqf, "stage2_bwd: null pointer");
+  BIST_CHECK_ARG(a.B > 0 && a.G > 0 && a.Lq > 0 && a.h > 0 && a.d > 0, "stage2_bwd: bad shape");
+  const size_t smem = ((size_t)2 * a.h * a.d + 2 * (size_t)a.h * (a.G + 1)) * 4;
+  if (smem > 200 * 1024) {
+    set_error("stage2_bwd: h*d = %d*%d too large for one CTA", a.h, a.d);
+    return BIST_ERR_UNSUPPORTED;
+  }
+  ProfScope ps("stage2_bwd", st);
+  if (a.dtype == BIST_BF16) {
+    auto kern = stage2_bwd_kernel<__nv_bfloat16>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)(a.B * a.Lq), 256, smem, st, a);
+  } else {
+    auto kern = stage2_bwd_kernel<float>;
+    if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    BIST_LAUNCH(kern, (unsigned)(a.B * a.Lq), 256, smem, st, a);
+  }
+  BIST_LAUNCHED();
+  return 0;
+}
+
+}  // namespace bist

@@ -243,3 +243,95 @@ int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, 
                 int dst_dtype, cudaStream_t st);
 
 }  // namespace bist
+
+// =============================================================================================
+// Backward-pass building blocks (bwd.cu)
+// =============================================================================================
+namespace bist {
+
+// Weight-gradient product (contraction over the ROWS of two row-major operands):
+//   C[z][n,k] += alpha * sum_m A[z][m,n] * B[z][m,k]          C fp32, accumulated with red.global.add
+//   colsum[z][n] += sum_m A[z][m,n]                            (optional: bias gradients)
+// The row range is split across CTAs; C (and colsum) must hold the running sum (zero for a fresh gradient).
+struct WgradArgs {
+  const void* A = nullptr;
+  const void* B = nullptr;
+  float* C = nullptr;
+  float* colsum = nullptr;
+  int M = 0, N = 0, K = 0;
+  long long lda = 0, ldb = 0, ldc = 0;
+  int Z = 1, zin = 1;
+  BatchMap az{0, 0}, bz{0, 0}, cz{0, 0}, sz{0, 0};
+  float alpha = 1.f;
+  int a_dtype = BIST_F32, b_dtype = BIST_F32;
+  const char* tag = "wgrad";
+};
+int wgrad(const WgradArgs& w, cudaStream_t st);
+
+// LayerNorm backward (modules.py:28-31: unbiased std, eps on the std).
+//   dx = [accumulate ? dx : 0] + dLN(dy; x)         (optionally gated by x > 0: the ReLU in front of in_norm)
+//   da += sum_rows dy * xhat, db += sum_rows dy     (atomics; rows [k*group_rows, ..) use a2 + k*pstride, da/db + k*gstride)
+struct LnBwdArgs {
+  const void* dy = nullptr;
+  const void* x = nullptr;
+  const float* a2 = nullptr;
+  void* dx = nullptr;
+  float* da = nullptr;
+  float* db = nullptr;
+  int64_t rows = 0, d = 0, group_rows = 0, pstride = 0, gstride = 0;
+  float eps = 1e-6f;
+  int dy_dtype = BIST_F32, x_dtype = BIST_F32, dx_dtype = BIST_F32;
+  int accumulate = 0, relu_gate = 0;
+};
+int layer_norm_bwd(const LnBwdArgs& a, cudaStream_t st);
+
+// dy[i] = y[i] > 0 ? dy[i] : 0   (in place; y and dy of dtype `dtype`)
+int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st);
+// out[q, c] (fp32) += sum_g in[q, g, c]
+int group_sum(const void* in, float* out, int64_t Qrows, int64_t G, int64_t d, int in_dtype, cudaStream_t st);
+// dst (dst_dtype) = src (src_dtype), n elements
+int cast_copy(const void* src, void* dst, int64_t n, int src_dtype, int dst_dtype, cudaStream_t st);
+
+// Backward of scaled-dot-product attention with projected q, k, v (attention(), modules.py:54-64); probabilities are
+// recomputed.  Element (b, row, hh*dk + j) of q / dq / dctx at  b*q_b + row*q_l + hh*dk + j  (k, v, dk, dv: k_b, k_l).
+struct AttnBwdArgs {
+  const void *q = nullptr, *k = nullptr, *v = nullptr, *dctx = nullptr;
+  void *dq = nullptr, *dk_ = nullptr, *dv = nullptr;
+  long long q_b = 0, q_l = 0, k_b = 0, k_l = 0, c_b = 0, c_l = 0;  // strides of q/dq, k/v/dk/dv, dctx
+  const uint8_t* mask = nullptr;
+  int mask_mod = kNoSplit;
+  long long m_b = 0, m_l = 0;  // mask[(b % mask_mod)*m_b + l*m_l + k]
+  int Bp = 0, Lq = 0, Lk = 0, h = 0, dk = 0;
+  int dtype = BIST_F32;  // of q, k, v, dctx, dq, dk, dv
+};
+int attn_core_bwd(const AttnBwdArgs& a, cudaStream_t st);
+
+// Backward of stage 1 (softmax over precomputed folded scores + weighted sum of projected values).
+// `f` is the forward's argument block (S = raw scores, mask, V, group/row maps); dctx is addressed like f.ctx.
+//   dV  (same addressing as f.V, dtype f.v_dtype)   = sum_l p[l,hh,k] dctx[l, hh-slice]
+//   ds  [b][(l*h+hh)][ts]  and  dsT [b][ts][(l*h+hh)]   (dtype ds_dtype), ts = (g % gdiv)*ts_g + k*ts_k, b = g / gdiv
+struct Stage1BwdArgs {
+  SoftmaxPvArgs f;
+  const void* dctx = nullptr;
+  void* dV = nullptr;
+  void* ds = nullptr;
+  void* dsT = nullptr;
+  int gdiv = 1, TS = 0;
+  long long ts_g = 0, ts_k = 0;
+  int ds_dtype = BIST_F32;
+};
+int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st);
+
+// Backward of stage 2: per (b,l) one folded query row per head against its G summaries x1[b,l,g,:].
+//   scores s[hh,g] = qf[q,hh,:].x1[q,g,:] (recomputed), p = softmax_g(mask), u[hh,:] = sum_g p x1[g,:]
+//   in : du [Q,h,d];  out: dx1 [Q,G,d] = sum_hh p du + ds qf ;  dqf [Q,h,d] = sum_g ds x1
+struct Stage2BwdArgs {
+  const void *qf = nullptr, *x1 = nullptr, *du = nullptr;
+  const uint8_t* mask = nullptr;  // [B, G] or null
+  void *dx1 = nullptr, *dqf = nullptr;
+  int B = 0, G = 0, Lq = 0, h = 0, d = 0;
+  int dtype = BIST_F32;  // of all six tensors
+};
+int stage2_bwd(const Stage2BwdArgs& a, cudaStream_t st);
+
+}  // namespace bist

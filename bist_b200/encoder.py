@@ -18,7 +18,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .modules import LayerNorm, SublayerConnection, clones, _eval_only, _ws
+from .modules import LayerNorm, SublayerConnection, clones, _eval_only, _no_dropout, _needs_grad, _ws
 
 _TORCH_DTYPE = {"fp32": torch.float32, "bf16": torch.bfloat16}
 
@@ -37,6 +37,148 @@ def _mask_bytes(mask, B, L):
     m = mask.reshape(B, L)
     m = m if m.dtype == torch.bool else (m != 0)
     return m.contiguous().view(torch.uint8)
+
+
+class _GradBox:
+    """fp32 accumulator for d(ft['spatiotemporal_ft']) shared by the projection and the layers that read it.
+
+    The layers' backward adds into ``acc`` in place (fp32, one buffer for all blocks and directions) instead of
+    returning bf16 gradients for autograd to sum; the projection's backward consumes it.
+    """
+
+    def __init__(self):
+        self.acc = None
+
+    def get(self, like):
+        if self.acc is None:
+            self.acc = torch.zeros(like.shape, dtype=torch.float32, device=like.device)
+        return self.acc
+
+
+class _VidProjFn(torch.autograd.Function):
+    """LayerNorm(relu(W fts + b)) with a backward (encoder.py:75,80) — bist_vidproj_train_fwd / bist_vidproj_bwd."""
+
+    @staticmethod
+    def forward(ctx, fts, W, bias, a_2, b_2, eps, precision, box):
+        D, d = W.shape[1], W.shape[0]
+        N = fts.numel() // D
+        cdt = _lib.BF16 if precision == "bf16" else _lib.F32
+        out = torch.empty(fts.shape[:-1] + (d,), dtype=_TORCH_DTYPE[precision], device=fts.device)
+        act = torch.empty((N, d), dtype=torch.float32, device=fts.device)
+        _lib.check(_lib.lib().bist_vidproj_train_fwd(_lib.ptr(fts), _lib.ptr(W), _lib.ptr(bias), _lib.ptr(a_2),
+                                                     _lib.ptr(b_2), _lib.ptr(out), _lib.ptr(act), N, D, d, float(eps),
+                                                     cdt, cdt, _lib.stream_ptr()), "bist_vidproj_train_fwd")
+        handle = torch.zeros(1, dtype=torch.float32, device=fts.device)
+        ctx.save_for_backward(fts, act, a_2, W)
+        ctx.box, ctx.eps, ctx.cdt = box, float(eps), cdt
+        ctx.set_materialize_grads(False)
+        return out, handle
+
+    @staticmethod
+    def backward(ctx, g_out, g_handle):
+        fts, act, a_2, W = ctx.saved_tensors
+        acc = ctx.box.acc
+        ctx.box.acc = None
+        if g_out is not None:                       # some other consumer differentiated the tensor directly
+            acc = g_out.float().reshape(act.shape) if acc is None else acc.add_(g_out.float().reshape(acc.shape))
+        if acc is None:
+            return (None,) * 8
+        d, D = W.shape
+        N = act.shape[0]
+        dW = torch.zeros_like(W)
+        vec = torch.zeros((3, d), dtype=torch.float32, device=W.device)
+        L = _lib.lib()
+        ws = _ws(L.bist_vidproj_bwd_workspace_bytes(N, D, d, ctx.cdt), W.device)
+        _lib.check(L.bist_vidproj_bwd(_lib.ptr(acc), _lib.ptr(fts), _lib.ptr(act), _lib.ptr(a_2), _lib.ptr(dW),
+                                      _lib.ptr(vec[0]), _lib.ptr(vec[1]), _lib.ptr(vec[2]), N, D, d, ctx.eps,
+                                      _lib.ptr(ws), ws.numel(), ctx.cdt, _lib.stream_ptr()), "bist_vidproj_bwd")
+        return None, dW, vec[0], vec[1], vec[2], None, None, None
+
+
+def _layer_grad_offsets(layer, d, d_ff, n_dirs):
+    """(offset, numel) of every parameter of a VidEncoderLayer4 inside the library's gradient block
+    (layout documented in include/bist_b200.h), in ``layer.named_parameters()`` order."""
+    dd = d * d
+    attn_stride = 4 * dd + 4 * d
+    ff = 3 * attn_stride
+    ln = ff + 2 * d * d_ff + d_ff + d
+    gdir = ln + 8 * d
+    out = []
+    for name, p in layer.named_parameters():
+        parts = name.split(".")
+        if parts[0] == "attn":
+            i, j = int(parts[1]), int(parts[3])
+            base = (i // 3) * gdir + (i % 3) * attn_stride
+            off = base + (j * dd if parts[4] == "weight" else 4 * dd + j * d)
+        elif parts[0] == "ff":
+            base = int(parts[1]) * gdir + ff
+            off = base + {"w_1.weight": 0, "w_1.bias": d_ff * d, "w_2.weight": d_ff * d + d_ff,
+                          "w_2.bias": 2 * d_ff * d + d_ff}[parts[2] + "." + parts[3]]
+        elif parts[0] == "sublayer":
+            i = int(parts[1])
+            off = (i // 4) * gdir + ln + (i % 4) * 2 * d + (0 if parts[3] == "a_2" else d)
+        else:
+            raise ValueError("unexpected VidEncoderLayer4 parameter %r" % name)
+        out.append((off, p.numel()))
+    assert max(o + n for o, n in out) <= n_dirs * gdir
+    return out, n_dirs * gdir
+
+
+class _StLayerFn(torch.autograd.Function):
+    """VidEncoderLayer4.forward with a backward — bist_st_layer_train_fwd / bist_st_layer_bwd."""
+
+    @staticmethod
+    def forward(ctx, layer, vft, handle, box, qm, tm, dir_mask, x_t2s, x_s2t, *params):
+        B, T, S, d = vft.shape
+        d_model, d_ff, h = layer._dims()
+        nd = layer._n_dirs()
+        run_t2s, run_s2t = bool(dir_mask & 1), bool(dir_mask & 2)
+        Lq = (x_t2s if run_t2s else x_s2t).shape[1]
+        vdt = _lib.dtype_code(vft.dtype)
+        o_t2s = torch.empty_like(x_t2s) if run_t2s else None
+        o_s2t = torch.empty_like(x_s2t) if run_s2t else None
+        packed = layer.train_packed_weights()
+        L = _lib.lib()
+        tape = _ws(L.bist_st_layer_tape_bytes(B, T, S, Lq, d, d_ff, h, nd, vdt), vft.device)
+        eps = float(layer.sublayer[0].norm.eps)
+        _lib.check(L.bist_st_layer_train_fwd(_lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft), _lib.ptr(qm), _lib.ptr(tm),
+                                             _lib.ptr(packed), _lib.ptr(o_t2s), _lib.ptr(o_s2t), B, T, S, Lq, d, d_ff, h,
+                                             nd, dir_mask, eps, _lib.ptr(tape), tape.numel(), vdt, _lib.stream_ptr()),
+                   "bist_st_layer_train_fwd")
+        ctx.save_for_backward(vft, qm, tm, packed, tape, x_t2s, x_s2t)
+        ctx.layer, ctx.box, ctx.dims = layer, box, (B, T, S, Lq, d, d_ff, h, nd, dir_mask, eps, vdt)
+        ctx.vft_needs_grad = vft.requires_grad
+        return tuple(o for o in (o_t2s, o_s2t) if o is not None)
+
+    @staticmethod
+    def backward(ctx, *g_outs):
+        vft, qm, tm, packed, tape, x_t2s, x_s2t = ctx.saved_tensors
+        B, T, S, Lq, d, d_ff, h, nd, dir_mask, eps, vdt = ctx.dims
+        run_t2s, run_s2t = bool(dir_mask & 1), bool(dir_mask & 2)
+        g_outs = list(g_outs)
+        g_t2s = g_outs.pop(0).float().contiguous() if run_t2s else None
+        g_s2t = g_outs.pop(0).float().contiguous() if run_s2t else None
+        if run_t2s and run_s2t and g_t2s.data_ptr() == g_s2t.data_ptr():
+            g_s2t = g_s2t.clone()
+        d_t2s = torch.empty_like(x_t2s) if run_t2s else None
+        d_s2t = torch.empty_like(x_s2t) if run_s2t else None
+        shared = ctx.box is not None
+        acc = ctx.box.get(vft) if shared else torch.zeros(vft.shape, dtype=torch.float32, device=vft.device)
+        offs, total = _layer_grad_offsets(ctx.layer, d, d_ff, nd)
+        L = _lib.lib()
+        if total != L.bist_st_layer_grad_elems(d, d_ff, nd):
+            raise RuntimeError("gradient block layout mismatch between bist_b200/encoder.py and libbist_b200.so")
+        grads = torch.zeros(total, dtype=torch.float32, device=vft.device)
+        ws = _ws(L.bist_st_layer_bwd_workspace_bytes(B, T, S, Lq, d, d_ff, h, nd, vdt), vft.device)
+        _lib.check(L.bist_st_layer_bwd(_lib.ptr(g_t2s), _lib.ptr(g_s2t), _lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft),
+                                       _lib.ptr(qm), _lib.ptr(tm), _lib.ptr(packed), _lib.ptr(tape), tape.numel(),
+                                       _lib.ptr(d_t2s), _lib.ptr(d_s2t), _lib.ptr(acc), _lib.ptr(grads), B, T, S, Lq, d,
+                                       d_ff, h, nd, dir_mask, eps, _lib.ptr(ws), ws.numel(), vdt, _lib.stream_ptr()),
+                   "bist_st_layer_bwd")
+        pg = tuple(grads[o:o + n].view(p.shape) for (o, n), p in zip(offs, ctx.layer.parameters()))
+        g_vft = None if shared or not ctx.vft_needs_grad else acc.to(vft.dtype)
+        g_handle = torch.zeros(1, dtype=torch.float32, device=vft.device) if shared else None
+        return (None, g_vft, g_handle, None, None, None, None, d_t2s, d_s2t) + pg
 
 
 class VidEncoder8(nn.Module):
@@ -64,6 +206,11 @@ class VidEncoder8(nn.Module):
         if x.dtype != torch.float32:
             x = x.float()
         x = x.contiguous()
+        if _needs_grad(lin.weight, lin.bias, norm.a_2, norm.b_2):
+            box = _GradBox()
+            out, handle = _VidProjFn.apply(x, lin.weight, lin.bias, norm.a_2, norm.b_2, norm.eps, self.precision, box)
+            out._bist_box, out._bist_handle = box, handle      # picked up by VidEncoderLayer4.forward
+            return out
         D, d = lin.in_features, lin.out_features
         N = x.numel() // D
         cdt = _lib.BF16 if self.precision == "bf16" else _lib.F32
@@ -76,7 +223,6 @@ class VidEncoder8(nn.Module):
         return out
 
     def forward(self, b, ft):
-        _eval_only(self)
         if self.v_N > 0:
             if self.vid_position is not None:      # always None in the reference (mtn.py:108)
                 raise NotImplementedError("vid_position is never set by make_model (mtn.py:108)")
@@ -110,7 +256,7 @@ class VidEncoderLayer4(nn.Module):
         new = type(self).__new__(type(self))
         memo[id(self)] = new
         for k, v in self.__dict__.items():
-            new.__dict__[k] = None if k == "_packed" else copy.deepcopy(v, memo)
+            new.__dict__[k] = None if k in ("_packed", "_train_packed") else copy.deepcopy(v, memo)
         return new
 
     # -- parameter hand-over ------------------------------------------------------------------
@@ -125,15 +271,7 @@ class VidEncoderLayer4(nn.Module):
             return 1
         raise ValueError("VidEncoderLayer4 needs 6 attn / 2 ff or 3 attn / 1 ff clones (mtn.py:123-128)")
 
-    def packed_weights(self):
-        """Pack (and cache until a parameter changes) the layer weights for the kernels."""
-        params = list(self.parameters())
-        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
-        if self._packed is not None and self._packed[0] == key:
-            return self._packed[1]
-        d, d_ff, h = self._dims()
-        nd = self._n_dirs()
-        dt = _lib.BF16 if self.precision == "bf16" else _lib.F32
+    def _param_struct(self, d):
         P = _lib.StLayerParams()
         for i, a in enumerate(self.attn):
             for j, lin in enumerate(a.linears):
@@ -146,6 +284,18 @@ class VidEncoderLayer4(nn.Module):
             P.ff_w2[i], P.ff_b2[i] = f.w_2.weight.data_ptr(), f.w_2.bias.data_ptr()
         for i, s in enumerate(self.sublayer):
             P.ln_a[i], P.ln_b[i] = s.norm.a_2.data_ptr(), s.norm.b_2.data_ptr()
+        return P
+
+    def packed_weights(self):
+        """Pack (and cache until a parameter changes) the layer weights for the kernels."""
+        params = list(self.parameters())
+        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
+        if self._packed is not None and self._packed[0] == key:
+            return self._packed[1]
+        d, d_ff, h = self._dims()
+        nd = self._n_dirs()
+        dt = _lib.BF16 if self.precision == "bf16" else _lib.F32
+        P = self._param_struct(d)
         L = _lib.lib()
         nbytes = L.bist_st_layer_packed_bytes(d, d_ff, nd, dt)
         buf = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
@@ -154,9 +304,28 @@ class VidEncoderLayer4(nn.Module):
         self._packed = (key, buf)
         return buf
 
+    def train_packed_weights(self):
+        """Packed weights of the training formulation (both operand orientations), cached per weight version."""
+        params = list(self.parameters())
+        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
+        hit = getattr(self, "_train_packed", None)
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        d, d_ff, h = self._dims()
+        nd = self._n_dirs()
+        dt = _lib.BF16 if self.precision == "bf16" else _lib.F32
+        P = self._param_struct(d)
+        L = _lib.lib()
+        nbytes = L.bist_st_layer_train_packed_bytes(d, d_ff, nd, dt)
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+        _lib.check(L.bist_st_layer_train_pack(ctypes.byref(P), _lib.ptr(buf), nbytes, d, d_ff, h, nd, dt,
+                                              _lib.stream_ptr()), "bist_st_layer_train_pack")
+        self._train_packed = (key, buf)
+        return buf
+
     # -- forward ------------------------------------------------------------------------------
     def forward(self, in_ft, ft, b):
-        _eval_only(self)
+        _no_dropout(self, self.sublayer[0].dropout.p, self.attn[0].dropout.p, self.ff[0].dropout.p)
         vft = ft['spatiotemporal_ft']
         _lib.require_cuda(vft, self.attn[0].linears[0].weight)
         run_t2s = (not hasattr(self.args, 't2s')) or bool(self.args.t2s)      # encoder.py:174
@@ -168,12 +337,26 @@ class VidEncoderLayer4(nn.Module):
         want = _lib.BF16 if self.precision == "bf16" else _lib.F32
         if vdt != want:
             raise TypeError("ft['spatiotemporal_ft'] is %s but this layer's precision is %s" % (vft.dtype, self.precision))
-        vft = vft.detach().contiguous()
         B, T, S, d = vft.shape
         d_model, d_ff, h = self._dims()
         if d != d_model:
             raise ValueError("video feature width %d != d_model %d" % (d, d_model))
         nd = self._n_dirs()
+        params = list(self.parameters())
+        if _needs_grad(vft, in_ft.get('t2s') if run_t2s else None, in_ft.get('s2t') if run_s2t else None, *params):
+            x_t2s = in_ft['t2s'].float().contiguous() if run_t2s else None
+            x_s2t = in_ft['s2t'].float().contiguous() if run_s2t else None
+            Lq = (x_t2s if run_t2s else x_s2t).shape[1]
+            qm = _mask_bytes(b.query_mask, B, Lq)
+            tm = _mask_bytes(b.temporal_mask, B, T)
+            box, handle = getattr(vft, "_bist_box", None), getattr(vft, "_bist_handle", None)
+            outs = list(_StLayerFn.apply(self, vft.contiguous(), handle, box, qm, tm, dir_mask, x_t2s, x_s2t, *params))
+            if run_t2s:
+                in_ft['t2s'] = outs.pop(0)
+            if run_s2t:
+                in_ft['s2t'] = outs.pop(0)
+            return in_ft
+        vft = vft.detach().contiguous()
         x_t2s = in_ft['t2s'].detach().float().contiguous() if run_t2s else None
         x_s2t = in_ft['s2t'].detach().float().contiguous() if run_s2t else None
         Lq = (x_t2s if run_t2s else x_s2t).shape[1]

@@ -6,8 +6,9 @@ Same constructor signatures, forward signatures and parameter names as the refer
 loads with ``strict=True`` and ``model/mtn.py`` can build its model from these classes.
 The forward bodies call the C ABI (include/bist_b200.h) on torch's current CUDA stream.
 
-This round the CUDA path is forward-only (eval mode): calling a module in ``train()`` mode
-raises, and outputs carry no autograd graph.  Inputs may be float32 or bfloat16 ("bf16
+``LayerNorm`` (and the video modules of encoder.py) carry autograd through the library's backward
+entry points; ``MultiHeadedAttention`` / ``PositionwiseFeedForward`` / ``SublayerConnection`` used on
+their own are still forward-only (eval mode).  Inputs may be float32 or bfloat16 ("bf16
 mode": bf16 storage, fp32 accumulation / statistics); parameters stay fp32 masters.
 """
 import copy
@@ -27,8 +28,49 @@ def clones(module, N):
 def _eval_only(m):
     if m.training:
         raise NotImplementedError(
-            "%s: the bist_b200 CUDA path is forward-only this round (dropout + backward land later); "
-            "call .eval()" % type(m).__name__)
+            "%s: this module of the bist_b200 CUDA path is forward-only this round; call .eval()" % type(m).__name__)
+
+
+def _no_dropout(m, *ps):
+    """Training mode is supported by the CUDA path only with dropout probability 0 (dropout kernels land next)."""
+    if m.training and any(p > 0 for p in ps):
+        raise NotImplementedError(
+            "%s: train() with dropout p > 0 is not built yet on the bist_b200 CUDA path; use dropout=0 or .eval() "
+            "(gradients flow in both modes)" % type(m).__name__)
+
+
+def _needs_grad(*tensors):
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
+
+
+class _LayerNormFn(torch.autograd.Function):
+    """LayerNorm forward/backward through the C ABI (modules.py:28-31)."""
+
+    @staticmethod
+    def forward(ctx, x, a_2, b_2, eps):
+        x = x.contiguous()
+        d = x.shape[-1]
+        y = torch.empty_like(x)
+        dt = _lib.dtype_code(x.dtype)
+        _lib.check(_lib.lib().bist_ln_fwd(_lib.ptr(x), _lib.ptr(a_2), _lib.ptr(b_2), _lib.ptr(y), x.numel() // d, d,
+                                          float(eps), dt, dt, _lib.stream_ptr()), "bist_ln_fwd")
+        ctx.save_for_backward(x, a_2)
+        ctx.eps = float(eps)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, a_2 = ctx.saved_tensors
+        gy = gy.contiguous()
+        d = x.shape[-1]
+        dx = torch.empty_like(x)
+        da = torch.zeros_like(a_2, dtype=torch.float32)
+        db = torch.zeros_like(a_2, dtype=torch.float32)
+        _lib.check(_lib.lib().bist_ln_bwd(_lib.ptr(gy), _lib.ptr(x), _lib.ptr(a_2), _lib.ptr(dx), _lib.ptr(da),
+                                          _lib.ptr(db), x.numel() // d, d, ctx.eps, _lib.dtype_code(gy.dtype),
+                                          _lib.dtype_code(x.dtype), _lib.dtype_code(dx.dtype), _lib.stream_ptr()),
+                   "bist_ln_bwd")
+        return dx, da, db, None
 
 
 def _ws(nbytes, device):
@@ -68,6 +110,8 @@ class LayerNorm(nn.Module):
 
     def forward(self, x):
         _lib.require_cuda(x, self.a_2)
+        if _needs_grad(x, self.a_2, self.b_2):
+            return _LayerNormFn.apply(x, self.a_2, self.b_2, self.eps)
         x = x.detach().contiguous()
         d = x.shape[-1]
         y = torch.empty_like(x)

@@ -164,6 +164,81 @@ int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const void* vft,
                       int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype,
                       void* stream);
 
+/* =======================================================================================
+ * Training step: forward with a tape + backward.
+ *
+ * The reference trains through torch autograd over the modules of model/modules.py and
+ * model/encoder.py; these entry points replace the autograd graph of the same forward()s.
+ * Gradients are fp32 and ACCUMULATED (+=) into caller-owned buffers (zero them for a fresh
+ * gradient).  Parity is against torch.autograd over the oracle (tests/test_gpu_backward.py).
+ * ======================================================================================= */
+
+/* VidEncoder8.forward for training — encoder.py:72-80.  Same output as bist_vidproj_fwd;
+ * `act` fp32 [N, d] receives relu(fts W^T + b) and is the tape of bist_vidproj_bwd. */
+int bist_vidproj_train_fwd(const float* fts, const float* W, const float* bias, const float* a_2,
+                           const float* b_2, void* out, float* act, int64_t N, int64_t D, int64_t d,
+                           float eps, int compute_dtype, int out_dtype, void* stream);
+size_t bist_vidproj_bwd_workspace_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype);
+/*   d_out fp32 [N, d]: gradient w.r.t. ft['spatiotemporal_ft'] (summed over blocks/directions);
+ *   dW [d, D], dbias [d], da_2 [d], db_2 [d] fp32, accumulated.  fts is data: no gradient. */
+int bist_vidproj_bwd(const float* d_out, const float* fts, const float* act, const float* a_2,
+                     float* dW, float* dbias, float* da_2, float* db_2, int64_t N, int64_t D, int64_t d,
+                     float eps, void* ws, size_t ws_bytes, int compute_dtype, void* stream);
+
+/* VidEncoderLayer4 for training — encoder.py:172-201 (+ :109-170), enc_st_combine == 'none'.
+ *
+ * bist_st_layer_train_pack: like bist_st_layer_pack, for the training formulation (the stage-1
+ * output projection is applied explicitly because the reference's sublayer dropout,
+ * modules.py:44, sits between it and stage 2), plus the transposed operands of the backward.
+ * `tape` (bist_st_layer_tape_bytes) is written by the forward and must reach the backward
+ * unchanged together with the same inputs, masks and packed weights.
+ *
+ * Gradient block `grads` (fp32, bist_st_layer_grad_elems floats), per packed direction u
+ * (0 = t2s, 1 = s2t for n_dirs == 2), in the reference's parameter order:
+ *     attn.{3u+i}, i = 0..2 :  linears.{0..3}.weight [4][d,d], then linears.{0..3}.bias [4][d]
+ *     ff.{u}                :  w_1.weight [d_ff,d], w_1.bias [d_ff], w_2.weight [d,d_ff], w_2.bias [d]
+ *     sublayer.{4u+i}.norm, i = 0..3 : a_2 [d], b_2 [d]
+ * Key-projection biases (linears.1.bias of the stage-1 / stage-2 attentions) get exactly zero:
+ * their score contribution is constant over the keys and cancels in the softmax.
+ */
+size_t bist_st_layer_train_packed_bytes(int64_t d, int64_t d_ff, int n_dirs, int dtype);
+int bist_st_layer_train_pack(const bist_st_layer_params_t* host_params, void* packed, size_t packed_bytes,
+                             int64_t d, int64_t d_ff, int64_t h, int n_dirs, int dtype, void* stream);
+size_t bist_st_layer_grad_elems(int64_t d, int64_t d_ff, int n_dirs);
+size_t bist_st_layer_tape_bytes(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t d_ff,
+                                int64_t h, int n_dirs, int dtype);
+size_t bist_st_layer_bwd_workspace_bytes(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d,
+                                         int64_t d_ff, int64_t h, int n_dirs, int dtype);
+/* Arguments as bist_st_layer_fwd; `packed` from bist_st_layer_train_pack. */
+int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t, const void* vft,
+                            const uint8_t* query_mask, const uint8_t* temporal_mask, const void* packed,
+                            float* out_t2s, float* out_s2t, int64_t B, int64_t T, int64_t S, int64_t Lq,
+                            int64_t d, int64_t d_ff, int64_t h, int n_dirs, int dir_mask, float eps,
+                            void* tape, size_t tape_bytes, int dtype, void* stream);
+/*   d_out_*   fp32 [B,Lq,d]  gradients of the layer outputs (separate tensors per direction)
+ *   d_in_*    fp32 [B,Lq,d]  gradients of the layer inputs (written, not accumulated)
+ *   d_vft     fp32 [B,T,S,d] gradient of ft['spatiotemporal_ft'], ACCUMULATED
+ *   grads     the gradient block described above, ACCUMULATED */
+int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t, const float* in_t2s,
+                      const float* in_s2t, const void* vft, const uint8_t* query_mask,
+                      const uint8_t* temporal_mask, const void* packed, const void* tape,
+                      size_t tape_bytes, float* d_in_t2s, float* d_in_s2t, float* d_vft, float* grads,
+                      int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t d_ff, int64_t h,
+                      int n_dirs, int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype,
+                      void* stream);
+
+/* LayerNorm backward — modules.py:28-31.  dx (dx_dtype) written; da_2/db_2 fp32 accumulated
+ * (both may be NULL). */
+int bist_ln_bwd(const void* dy, const void* x, const float* a_2, void* dx, float* da_2, float* db_2,
+                int64_t rows, int64_t d, float eps, int dy_dtype, int x_dtype, int dx_dtype, void* stream);
+
+/* nn.Linear backward: dx[M,K] = dy[M,N] . w[N,K] (dx may be NULL), dw[N,K] += dy^T x,
+ * db[N] += colsum(dy) (dw/db fp32, accumulated, may be NULL together).  wT is w transposed
+ * ([K,N], dtype w_dtype), needed only when dx != NULL. */
+int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, float* dw, float* db,
+                    int64_t M, int64_t N, int64_t K, int dy_dtype, int x_dtype, int w_dtype, int dx_dtype,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

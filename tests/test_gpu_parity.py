@@ -30,6 +30,7 @@ def _run_path(c, precision, P=None):
     m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], t2s=c.get("t2s", 1), s2t=c.get("s2t", 1),
                   precision=precision).to(DEV)
     m.load_state_dict(P, strict=True)
+    m.requires_grad_(False)          # inference path (the training path is covered by test_gpu_backward.py)
     b = synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"]).to(DEV)
     eq = synth.make_encoded_query(c["seed"], c["B"], c["Lq"], c["d"]).to(DEV)
     return m, b, eq
