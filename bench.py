@@ -300,6 +300,39 @@ def run_ours(args):
         roof["peak_source"] = peaks["src"] + " (sustained bf16 / copy bandwidth, MEASURED_PEAKS.json)"
     whole = algorithmic_bytes(c, e_act) / (ms_step * 1e-3) / 1e9
 
+    # ---- training step of the video path (forward with tape + backward + grad all-reduce + Adam) ------------
+    train = None
+    if not args.no_train:
+        from bist_b200.dist import allreduce_grads
+        tm = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.0, precision=args.precision).to(dev)
+        tm.load_state_dict(synth.make_params(0, c["d"], c["D"], c["n_blocks"]), strict=True)
+        tm.eval()                                        # dropout identity (dropout kernels are not built yet)
+        opt = torch.optim.Adam(tm.parameters(), lr=1e-4, fused=True)
+        tgt = torch.randn(c["B"], c["Lq"], c["d"], device=dev)
+        plist = list(tm.parameters())
+        ncoll = [0]
+
+        def train_step():
+            opt.zero_grad(set_to_none=True)
+            out = tm(db, deq)
+            loss = ((out["temporal_ft"] - tgt) ** 2).mean() + ((out["spatial_ft"] - tgt) ** 2).mean()
+            loss.backward()
+            ncoll[0] = allreduce_grads(plist)
+            opt.step()
+
+        for _ in range(3):
+            train_step()
+        n0 = L.bist_launch_count()
+        tsteps = max(3, min(args.steps, 10))
+        tms = timed(train_step, tsteps) / tsteps
+        train = {"metric": "video_path_train_turns_per_sec", "value": world * c["B"] / (tms * 1e-3), "unit": UNIT,
+                 "ms_per_step": tms, "gpu_launches_per_step": (L.bist_launch_count() - n0) // tsteps,
+                 "collectives_per_step": ncoll[0],
+                 "what": "video path only (projection + 3 blocks + out norms): forward with tape, MSE loss, backward "
+                         "through libbist_b200, gradient all-reduce (NCCL, N>1), fused Adam; dropout off; the rest of "
+                         "the BiST model (text encoders, decoder, generator, label-smoothed loss) is not built"}
+        del tm, opt
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -322,6 +355,7 @@ def run_ours(args):
                 "roofline": roof,
                 "encoder_algorithmic_gbs": whole, "encoder_frac_of_hbm_peak": whole / peaks["hbm"],
                 "kernels": kern, "kernel_rooflines": per_kernel,
+                "train": train,
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -337,6 +371,7 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("BIST_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement of the video path")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

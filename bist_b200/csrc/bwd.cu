@@ -425,6 +425,21 @@ __global__ void cast_kernel(const TS* __restrict__ src, TD* __restrict__ dst, in
     dst[i] = from_f32<TD>(to_f32(src[i]));
 }
 
+// 32 x 32 tiles through shared memory; grid (ceil(cols/32), ceil(rows/32), Z), block (32, 8)
+template <typename T>
+__global__ void transpose_kernel(const T* __restrict__ src, T* __restrict__ dst, int rows, int cols) {
+  __shared__ T tile[32][33];
+  pdl_trigger();
+  pdl_wait();
+  const long long zoff = (long long)blockIdx.z * rows * cols;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8)
+    if (r0 + i < rows && c0 + threadIdx.x < cols) tile[i][threadIdx.x] = src[zoff + (long long)(r0 + i) * cols + c0 + threadIdx.x];
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8)
+    if (c0 + i < cols && r0 + threadIdx.x < rows) dst[zoff + (long long)(c0 + i) * rows + r0 + threadIdx.x] = tile[threadIdx.x][i];
+}
+
 inline unsigned ew_grid(int64_t n) {
   int64_t g = (n + 255) / 256;
   const int64_t cap = 8LL * num_sms_cached();
@@ -445,6 +460,16 @@ int group_sum(const void* in, float* out, int64_t Qrows, int64_t G, int64_t d, i
   ProfScope ps("group_sum", st);
   if (in_dtype == BIST_BF16) BIST_LAUNCH(group_sum_kernel<__nv_bfloat16>, ew_grid(Qrows * d), 256, 0, st, (const __nv_bfloat16*)in, out, Qrows, (int)G, (int)d);
   else BIST_LAUNCH(group_sum_kernel<float>, ew_grid(Qrows * d), 256, 0, st, (const float*)in, out, Qrows, (int)G, (int)d);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int transpose_batched(const void* src, void* dst, int64_t Z, int64_t rows, int64_t cols, int dtype, cudaStream_t st) {
+  BIST_CHECK_ARG(src && dst && Z > 0 && Z <= 65535 && rows > 0 && cols > 0, "transpose: bad argument");
+  dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32), (unsigned)Z), block(32, 8);
+  ProfScope ps("transpose", st);
+  if (dtype == BIST_BF16) BIST_LAUNCH(transpose_kernel<__nv_bfloat16>, grid, block, 0, st, (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, (int)rows, (int)cols);
+  else BIST_LAUNCH(transpose_kernel<float>, grid, block, 0, st, (const float*)src, (float*)dst, (int)rows, (int)cols);
   BIST_LAUNCHED();
   return 0;
 }
@@ -665,10 +690,11 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
   const int R = Lq * h;
   TS* ds = reinterpret_cast<TS*>(a.ds) + (long long)b * R * a.TS;
   TS* dsT = reinterpret_cast<TS*>(a.dsT) + (long long)b * a.TS * R;
-  for (int i = t; i < R * nk; i += nt) {  // k fastest: ds[b][r][ts]
-    const int r = i / nk, k = i % nk;
-    ds[(long long)r * a.TS + gi * a.ts_g + k * a.ts_k] = from_f32<TS>(Ps[r * nkp + k]);
-  }
+  if (a.ds)
+    for (int i = t; i < R * nk; i += nt) {  // k fastest: ds[b][r][ts]
+      const int r = i / nk, k = i % nk;
+      ds[(long long)r * a.TS + gi * a.ts_g + k * a.ts_k] = from_f32<TS>(Ps[r * nkp + k]);
+    }
   for (int i = t; i < R * nk; i += nt) {  // r fastest: dsT[b][ts][r]
     const int k = i / R, r = i % R;
     dsT[((long long)gi * a.ts_g + k * a.ts_k) * R + r] = from_f32<TS>(Ps[r * nkp + k]);
@@ -679,7 +705,12 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
 
 int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st) {
   const SoftmaxPvArgs& f = a.f;
-  BIST_CHECK_ARG(f.S && f.V && a.dctx && a.dV && a.ds && a.dsT, "stage1_bwd: null pointer");
+  BIST_CHECK_ARG(f.S && f.V && a.dctx && a.dV && a.dsT, "stage1_bwd: null pointer");
+  {
+    bool taken = false;
+    int rc = stage1_bwd_mma(a, st, &taken);
+    if (taken) return rc;
+  }
   BIST_CHECK_ARG(f.G > 0 && f.Lq > 0 && f.h > 0 && f.dk > 0 && f.nk > 0 && f.nk <= 256, "stage1_bwd: bad shape (nk <= 256)");
   BIST_CHECK_ARG(a.ds_dtype == f.v_dtype, "stage1_bwd: ds dtype must equal the value dtype");
   const size_t smem = ((size_t)f.Lq * f.h * (f.nk + 1) + (size_t)(f.Lq + f.nk) * (f.dk + 1)) * 4;
@@ -790,6 +821,11 @@ __global__ void __launch_bounds__(256) stage2_bwd_kernel(Stage2BwdArgs a) {
 int stage2_bwd(const Stage2BwdArgs& a, cudaStream_t st) {
   BIST_CHECK_ARG(a.qf && a.x1 && a.du && a.dx1 && a.dqf, "stage2_bwd: null pointer");
   BIST_CHECK_ARG(a.B > 0 && a.G > 0 && a.Lq > 0 && a.h > 0 && a.d > 0, "stage2_bwd: bad shape");
+  {
+    bool taken = false;
+    int rc = stage2_bwd_mma(a, st, &taken);
+    if (taken) return rc;
+  }
   const size_t smem = ((size_t)2 * a.h * a.d + 2 * (size_t)a.h * (a.G + 1)) * 4;
   if (smem > 200 * 1024) {
     set_error("stage2_bwd: h*d = %d*%d too large for one CTA", a.h, a.d);

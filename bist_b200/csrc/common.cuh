@@ -320,7 +320,8 @@ struct Stage1BwdArgs {
   long long ts_g = 0, ts_k = 0;
   int ds_dtype = BIST_F32;
 };
-int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st);
+int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st);      // a.ds may be null (only dsT is written); tensor cores when possible
+int stage1_bwd_mma(const Stage1BwdArgs& a, cudaStream_t st, bool* taken);  // bwd_mma.cu
 
 // Backward of stage 2: per (b,l) one folded query row per head against its G summaries x1[b,l,g,:].
 //   scores s[hh,g] = qf[q,hh,:].x1[q,g,:] (recomputed), p = softmax_g(mask), u[hh,:] = sum_g p x1[g,:]
@@ -333,5 +334,8 @@ struct Stage2BwdArgs {
   int dtype = BIST_F32;  // of all six tensors
 };
 int stage2_bwd(const Stage2BwdArgs& a, cudaStream_t st);
+int stage2_bwd_mma(const Stage2BwdArgs& a, cudaStream_t st, bool* taken);  // bwd_mma.cu
+// dst[z][c][r] = src[z][r][c]  (Z matrices of [rows, cols], dense)
+int transpose_batched(const void* src, void* dst, int64_t Z, int64_t rows, int64_t cols, int dtype, cudaStream_t st);
 
 }  // namespace bist

@@ -112,7 +112,7 @@ Tape carve_tape(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
 }
 
 struct BwdWs {
-  void *a_dout, *a_dts, *a_dx, *dffh, *dn, *dc, *du2, *dqf12, *dq12, *dxv, *ds, *dsT, *dqkv0;  // compute dtype
+  void *a_dout, *a_dts, *a_dx, *dffh, *dn, *dc, *du2, *dqf12, *dq12, *dxv, *qf1T, *dsT, *dqkv0;  // compute dtype
   void* dout1[2];
   void* dc1[2];
   float *dts, *dqf1;
@@ -132,7 +132,7 @@ BwdWs carve_bwd(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   W.dffh = a(nd * Q * dff); W.dn = a(2 * nd * Q * d); W.dc = a(nd * Q * d); W.du2 = a(nd * Q * h * d);
   W.dqf12 = a(2 * nd * Q * h * d); W.dq12 = a(2 * nd * Q * d);
   W.dxv = a((size_t)B * T * S * nd * d);
-  W.ds = a(Q * h * T * S); W.dsT = a(Q * h * T * S);
+  W.qf1T = a(Q * h * d); W.dsT = a(Q * h * T * S);
   W.dqkv0 = a(nd * Q * 3 * d);
   for (int u = 0; u < 2; ++u) { W.dout1[u] = nullptr; W.dc1[u] = nullptr; }
   for (int u = 0; u < nd; ++u) {
@@ -670,19 +670,22 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     a.f = stage1_args(t2s, t2s && c.regions, W.sc1[u], temporal_mask, c.act(W.xv, (long long)u * d), nullptr, B, T, S, Lq, d, h, nd, dtype);
     a.dctx = D.dc1[u];
     a.dV = c.act(D.dxv, (long long)u * d);
-    a.ds = D.ds; a.dsT = D.dsT; a.gdiv = G; a.TS = (int)TS;
+    a.ds = nullptr; a.dsT = D.dsT; a.gdiv = G; a.TS = (int)TS;
     a.ts_g = t2s ? 1 : S; a.ts_k = t2s ? S : 1;
     a.ds_dtype = adt;
     BIST_TRY(stage1_bwd(a, st));
     const int R = (int)(Lq * h);
     {
-      WgradArgs w;  // d_vft[b][ts, :] += sum_r ds[b][r, ts] qf1[b][r, :]
-      w.A = D.ds; w.B = c.act(W.qf12, (long long)u * Qd * h); w.C = d_vft;
-      w.M = R; w.N = (int)TS; w.K = di; w.lda = TS; w.ldb = d; w.ldc = d;
-      w.Z = (int)B; w.zin = 1;
-      w.az = {(long long)R * TS, 0}; w.bz = {(long long)R * d, 0}; w.cz = {TS * d, 0};
-      w.a_dtype = adt; w.b_dtype = adt; w.tag = "bwd_scores_dvft";
-      BIST_TRY(wgrad(w, st));
+      // d_vft[b][ts, :] += sum_r dsT[b][ts, r] qf1[b][r, :]  as an NT product against qf1^T [d, R]
+      BIST_TRY(transpose_batched(c.act(W.qf12, (long long)u * Qd * h), D.qf1T, B, R, d, adt, st));
+      GemmArgs g;
+      g.A = D.dsT; g.W = D.qf1T; g.C = d_vft; g.R = d_vft;
+      g.M = (int)TS; g.N = di; g.K = R;
+      g.a = rows_dense(R); g.w = rows_dense(R); g.c = rows_dense(d); g.r = rows_dense(d);
+      g.Z = (int)B; g.zin = 1;
+      g.az = {TS * R, 0}; g.wz = {(long long)d * R, 0}; g.cz = {TS * d, 0}; g.rz = {TS * d, 0};
+      g.a_dtype = adt; g.w_dtype = adt; g.c_dtype = BIST_F32; g.r_dtype = BIST_F32; g.tag = "bwd_scores_dvft";
+      BIST_TRY(gemm(g, st));
       WgradArgs v;  // dqf1[b][r, :] += sum_ts dsT[b][ts, r] vft[b][ts, :]
       v.A = D.dsT; v.B = vft; v.C = D.dqf1 + u * Qd * h;
       v.M = (int)TS; v.N = R; v.K = di; v.lda = R; v.ldb = d; v.ldc = d;

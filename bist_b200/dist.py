@@ -2,7 +2,8 @@
 
 Dialogue turns (batch rows) are independent on the whole video path — attention never mixes samples and
 LayerNorm is per row — so the path shards by rows with NO data-path collective.  The only communication is
-bookkeeping: the max-over-ranks step time of bench.py and, in tests, gathering the shards back.
+bookkeeping (the max-over-ranks step time of bench.py and, in tests, gathering the shards back) and, for the
+training step, ONE gradient all-reduce per step (`allreduce_grads`).
 """
 import torch
 import torch.distributed as dist
@@ -42,3 +43,46 @@ def gather_rows(local, n_rows):
         dist.broadcast(buf, src=r)
         out.append(buf)
     return torch.cat(out, 0)
+
+
+def allreduce_grads(params, average=True):
+    """Sum (or average) the gradients of `params` over all ranks with as few collectives as possible.
+
+    The backward of a VidEncoderLayer4 writes all of its parameter gradients into one flat fp32 block
+    (include/bist_b200.h, "Gradient block") and hands out views, so every layer is ONE all-reduce over the
+    views' common base; stand-alone gradients are flattened into one extra bucket.  Returns the number of
+    collectives issued.  A no-op (returns 0) without an initialised process group or with world_size 1.
+    """
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return 0
+    world = dist.get_world_size()
+    blocks, loose = {}, []
+    for p in params:
+        g = p.grad
+        if g is None:
+            continue
+        base = g._base if g._is_view() and g._base is not None and g._base.is_contiguous() else None
+        if base is not None:
+            blocks.setdefault(id(base), [base, 0])[1] += g.numel()
+        else:
+            loose.append(g)
+    n = 0
+    for base, covered in blocks.values():
+        if covered == base.numel():          # the block holds nothing but gradients: reduce it in place
+            dist.all_reduce(base)
+            if average:
+                base.div_(world)
+            n += 1
+        else:                                # partially used base: fall back to its views
+            loose.extend(p.grad for p in params if p.grad is not None and p.grad._is_view() and p.grad._base is base)
+    if loose:
+        flat = torch.cat([g.reshape(-1) for g in loose])
+        dist.all_reduce(flat)
+        if average:
+            flat.div_(world)
+        off = 0
+        for g in loose:
+            g.copy_(flat[off:off + g.numel()].view_as(g))
+            off += g.numel()
+        n += 1
+    return n

@@ -18,7 +18,8 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .modules import LayerNorm, SublayerConnection, clones, _eval_only, _no_dropout, _needs_grad, _ws
+from .modules import (LayerNorm, SublayerConnection, clones, _eval_only, _no_dropout, _needs_grad, _ws, _WEIGHT_EPOCH,
+                      _reg_hook, weights_updated)
 
 _TORCH_DTYPE = {"fp32": torch.float32, "bf16": torch.bfloat16}
 
@@ -175,6 +176,8 @@ class _StLayerFn(torch.autograd.Function):
                                        _lib.ptr(d_t2s), _lib.ptr(d_s2t), _lib.ptr(acc), _lib.ptr(grads), B, T, S, Lq, d,
                                        d_ff, h, nd, dir_mask, eps, _lib.ptr(ws), ws.numel(), vdt, _lib.stream_ptr()),
                    "bist_st_layer_bwd")
+        if _reg_hook is None:
+            weights_updated()
         pg = tuple(grads[o:o + n].view(p.shape) for (o, n), p in zip(offs, ctx.layer.parameters()))
         g_vft = None if shared or not ctx.vft_needs_grad else acc.to(vft.dtype)
         g_handle = torch.zeros(1, dtype=torch.float32, device=vft.device) if shared else None
@@ -289,7 +292,8 @@ class VidEncoderLayer4(nn.Module):
     def packed_weights(self):
         """Pack (and cache until a parameter changes) the layer weights for the kernels."""
         params = list(self.parameters())
-        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
+        key = (self.precision, params[0].device, _WEIGHT_EPOCH[0], tuple(p._version for p in params),
+               tuple(p.data_ptr() for p in params))
         if self._packed is not None and self._packed[0] == key:
             return self._packed[1]
         d, d_ff, h = self._dims()
@@ -307,7 +311,8 @@ class VidEncoderLayer4(nn.Module):
     def train_packed_weights(self):
         """Packed weights of the training formulation (both operand orientations), cached per weight version."""
         params = list(self.parameters())
-        key = (self.precision, params[0].device, tuple(p._version for p in params), tuple(p.data_ptr() for p in params))
+        key = (self.precision, params[0].device, _WEIGHT_EPOCH[0], tuple(p._version for p in params),
+               tuple(p.data_ptr() for p in params))
         hit = getattr(self, "_train_packed", None)
         if hit is not None and hit[0] == key:
             return hit[1]

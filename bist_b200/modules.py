@@ -84,6 +84,27 @@ def _mask_u8(mask, shape):
     return m.contiguous().view(torch.uint8)
 
 
+# Packed-weight caches are keyed on the parameters' version counters, which fused optimizers (torch._fused_adam_)
+# do not bump; a global optimizer-step hook therefore advances an epoch that is part of every cache key.
+_WEIGHT_EPOCH = [0]
+
+
+def _on_optimizer_step(*_args, **_kwargs):
+    _WEIGHT_EPOCH[0] += 1
+
+
+try:
+    from torch.optim.optimizer import register_optimizer_step_post_hook as _reg_hook
+    _reg_hook(_on_optimizer_step)
+except ImportError:                                   # very old torch: fall back to invalidating after every backward
+    _reg_hook = None
+
+
+def weights_updated():
+    """Call after changing parameters in a way torch cannot see (custom in-place kernels): drops packed caches."""
+    _WEIGHT_EPOCH[0] += 1
+
+
 class _BF16Cache:
     """bf16 copies of fp32 parameters, refreshed when a parameter is updated in place."""
 
@@ -93,8 +114,9 @@ class _BF16Cache:
     def get(self, p):
         key = id(p)
         hit = self._store.get(key)
-        if hit is None or hit[0] != p._version or hit[1].device != p.device:
-            hit = (p._version, p.detach().to(torch.bfloat16).contiguous())
+        ver = (p._version, _WEIGHT_EPOCH[0])
+        if hit is None or hit[0] != ver or hit[1].device != p.device:
+            hit = (ver, p.detach().to(torch.bfloat16).contiguous())
             self._store[key] = hit
         return hit[1]
 

