@@ -28,6 +28,12 @@ class MhaParams(ctypes.Structure):
     _fields_ = [("w", c_p * 4), ("b", c_p * 4)]
 
 
+class Dropout(ctypes.Structure):
+    "bist_dropout_t"
+    _fields_ = [("p_attn", ctypes.c_float), ("p_sublayer", ctypes.c_float), ("p_ffn", ctypes.c_float),
+                ("seed", ctypes.c_uint64)]
+
+
 class StLayerParams(ctypes.Structure):
     _fields_ = [("attn_w", (c_p * 4) * 6), ("attn_b", (c_p * 4) * 6),
                 ("ff_w1", c_p * 2), ("ff_b1", c_p * 2), ("ff_w2", c_p * 2), ("ff_b2", c_p * 2),
@@ -67,8 +73,10 @@ SIGNATURES = {
     "bist_st_layer_bwd_workspace_bytes": (c_sz, [c_i64] * 7 + [c_i, c_i]),
     "bist_st_layer_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p,
                                       c_i64, c_i64, c_i64, c_i64, c_i64, c_i64, c_i64,
-                                      c_i, c_i, c_f, c_p, c_sz, c_i, c_p]),
-    "bist_st_layer_bwd": (c_i, [c_p] * 9 + [c_sz] + [c_p] * 4 + [c_i64] * 7 + [c_i, c_i, c_f, c_p, c_sz, c_i, c_p]),
+                                      c_i, c_i, c_f, c_p, c_sz, c_i, ctypes.POINTER(Dropout), c_p]),
+    "bist_st_layer_bwd": (c_i, [c_p] * 9 + [c_sz] + [c_p] * 4 + [c_i64] * 7 +
+                          [c_i, c_i, c_f, c_p, c_sz, c_i, ctypes.POINTER(Dropout), c_p]),
+    "bist_dropout_mask": (c_i, [ctypes.c_uint64, ctypes.c_uint32, c_f, c_i64, c_p, c_p]),
     "bist_ln_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_f, c_i, c_i, c_i, c_p]),
     "bist_linear_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i, c_i, c_i, c_i, c_p]),
 }

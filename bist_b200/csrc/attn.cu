@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(256) softmax_pv_kernel(SoftmaxPvArgs a, int LT
     const float inv = 1.f / sum;
     for (int k = lane; k < nk; k += 32) {
       float p = Ps[(hh * nk + k) * LTP + li] * inv;
+      p *= drop_mul(a.drop, (((unsigned long long)g * h + hh) * a.Lq + l) * nk + k);
       Ps[(hh * nk + k) * LTP + li] = p;
       if (a.p_out) a.p_out[(((long long)g * h + hh) * a.Lq + l) * nk + k] = p;
     }
@@ -119,7 +120,7 @@ int launch_softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
 template <typename TX, typename TO, int HC>
 __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ qf, const TX* __restrict__ x1,
                                                      const uint8_t* __restrict__ mask, TO* __restrict__ ctxx,
-                                                     int B, int G, int Lq, int h, int d) {
+                                                     int B, int G, int Lq, int h, int d, DropCfg drop, float* __restrict__ rsum) {
   extern __shared__ __align__(16) float sm[];
   pdl_trigger();
   pdl_wait();
@@ -165,7 +166,16 @@ __global__ void __launch_bounds__(256) stage2_kernel(const float* __restrict__ q
     }
     sum = warp_sum(sum);
     const float inv = 1.f / sum;
-    for (int g = lane; g < G; g += 32) sc[hh * G + g] *= inv;
+    float rs = 0.f;
+    for (int g = lane; g < G; g += 32) {
+      const float pv = sc[hh * G + g] * inv * drop_mul(drop, ((unsigned long long)blockIdx.x * h + hh) * G + g);
+      sc[hh * G + g] = pv;
+      rs += pv;
+    }
+    if (rsum) {
+      rs = warp_sum(rs);
+      if (lane == 0) rsum[(long long)blockIdx.x * h + hh] = rs;
+    }
   }
   __syncthreads();
   // weighted sums: thread per column
@@ -219,21 +229,21 @@ int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
 
 template <typename TX, typename TO>
 int launch_stage2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
-                  size_t smem, cudaStream_t st) {
+                  size_t smem, cudaStream_t st, const Stage2Extra* ex) {
   auto kern = stage2_kernel<TX, TO, 8>;
   if (smem > 48 * 1024) BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   ProfScope ps("stage2_attn", st);
   BIST_LAUNCH(kern, dim3((unsigned)(B * Lq)), 256, smem, st, qf, reinterpret_cast<const TX*>(x1), mask, reinterpret_cast<TO*>(ctxx), B, G,
-                                                   Lq, h, d);
+                                                   Lq, h, d, ex ? ex->drop : DropCfg(), ex ? ex->rsum : nullptr);
   BIST_LAUNCHED();
   return 0;
 }
 
 int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
-                int x1_dtype, int ctxx_dtype, cudaStream_t st) {
+                int x1_dtype, int ctxx_dtype, cudaStream_t st, const Stage2Extra* ex) {
   BIST_CHECK_ARG(qf && x1 && ctxx, "stage2: null pointer");
   BIST_CHECK_ARG(B > 0 && G > 0 && Lq > 0 && h > 0 && d > 0, "stage2: bad shape");
-  {
+  if (!ex) {  // the training extras (dropout, rsum) live in the plain kernel below
     bool taken = false;
     int rc = stage2_v2(qf, x1, mask, ctxx, B, G, Lq, h, d, x1_dtype, ctxx_dtype, st, &taken);
     if (taken) return rc;
@@ -244,10 +254,10 @@ int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx
     return BIST_ERR_UNSUPPORTED;
   }
   const bool xb = x1_dtype == BIST_BF16, ob = ctxx_dtype == BIST_BF16;
-  if (xb && ob) return launch_stage2<__nv_bfloat16, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
-  if (xb) return launch_stage2<__nv_bfloat16, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
-  if (ob) return launch_stage2<float, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
-  return launch_stage2<float, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st);
+  if (xb && ob) return launch_stage2<__nv_bfloat16, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st, ex);
+  if (xb) return launch_stage2<__nv_bfloat16, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st, ex);
+  if (ob) return launch_stage2<float, __nv_bfloat16>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st, ex);
+  return launch_stage2<float, float>(qf, x1, mask, ctxx, B, G, Lq, h, d, smem, st, ex);
 }
 
 int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, float scale, int dst_dtype,

@@ -160,6 +160,17 @@ __global__ void __launch_bounds__(256, (KS <= 3 ? 3 : 1)) softmax_pv_mma_kernel(
     sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
     sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
     const float inv0 = sum0 > 0.f ? 1.f / sum0 : 0.f, inv1 = sum1 > 0.f ? 1.f / sum1 : 0.f;
+    if (a.drop.thresh != 0u) {  // dropout on the probabilities: element ((g*h + hh)*Lq + row)*nk + key
+      const unsigned long long base0 = (((unsigned long long)g * a.h + hh) * a.Lq + r0) * nk;
+      const unsigned long long base1 = (((unsigned long long)g * a.h + hh) * a.Lq + r1) * nk;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int key = ks * 16 + (j >> 2) * 8 + kq + (j & 1);
+          s[ks][j] *= drop_mul(a.drop, ((j & 2) ? base1 : base0) + key);
+        }
+    }
     uint32_t pa[KS][4];
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
@@ -249,7 +260,7 @@ int pick_nt(const SoftmaxPvArgs& a, cudaStream_t st) {
 // smem: X [Gp][d+8] bf16 (Gp = G rounded up to 16, padding rows zero) | Q/U [16][d+8] bf16 | S [16][Gp] f32 | P [16][Gp+8] bf16
 __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ x1,
                                                          const uint8_t* __restrict__ mask, __nv_bfloat16* __restrict__ out,
-                                                         int G, int Gp, int Lq, int h, int d) {
+                                                         int G, int Gp, int Lq, int h, int d, DropCfg drop, float* __restrict__ rsum) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   pdl_trigger();
   pdl_wait();
@@ -320,7 +331,18 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
       }
       sum = warp_sum(sum);
       const float inv = 1.f / sum;
-      for (int g = lane; g < Gp; g += 32) Ps[hh * ldp + g] = __float2bfloat16_rn(g < G ? Ss[hh * Gp + g] * inv : 0.f);
+      float rs = 0.f;
+      for (int g = lane; g < Gp; g += 32) {
+        float pv = 0.f;
+        if (g < G) pv = Ss[hh * Gp + g] * inv * drop_mul(drop, ((unsigned long long)bl * h + hh) * G + g);
+        const __nv_bfloat16 pb = __float2bfloat16_rn(pv);
+        Ps[hh * ldp + g] = pb;
+        rs += __bfloat162float(pb);
+      }
+      if (rsum) {
+        rs = warp_sum(rs);
+        if (lane == 0) rsum[(long long)bl * h + hh] = rs;
+      }
     } else {
       for (int g = lane; g < Gp; g += 32) Ps[hh * ldp + g] = __float2bfloat16_rn(0.f);
     }
@@ -661,7 +683,7 @@ bool stage2_mma_supported(int G, int h, int d) {
 
 // bf16 tensor-core stage 2 (q, x1, out all bf16); *taken = false when the shape is left to the other kernels.
 int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d,
-               cudaStream_t st, bool* taken) {
+               cudaStream_t st, bool* taken, const Stage2Extra* ex) {
   *taken = false;
   const int Gp = (G + 15) / 16 * 16;
   const size_t smem = (size_t)(Gp + 16) * (d + 8) * 2 + (size_t)16 * Gp * 4 + (size_t)16 * (Gp + 8) * 2;
@@ -676,7 +698,8 @@ int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, in
   ProfScope ps("stage2_mma", st);
   BIST_LAUNCH(stage2_mma_kernel, dim3((unsigned)(B * Lq)), 256, smem, st, reinterpret_cast<const __nv_bfloat16*>(q),
                                                                 reinterpret_cast<const __nv_bfloat16*>(x1), mask,
-                                                                reinterpret_cast<__nv_bfloat16*>(out), G, Gp, Lq, h, d);
+                                                                reinterpret_cast<__nv_bfloat16*>(out), G, Gp, Lq, h, d,
+                                                                ex ? ex->drop : DropCfg(), ex ? ex->rsum : nullptr);
   BIST_LAUNCHED();
   return 0;
 }

@@ -395,11 +395,98 @@ int layer_norm_bwd(const LnBwdArgs& a, cudaStream_t st) {
 namespace {
 
 template <typename T>
-__global__ void relu_gate_kernel(T* __restrict__ dy, const T* __restrict__ y, int64_t n) {
+__global__ void relu_gate_kernel(T* __restrict__ dy, const T* __restrict__ y, int64_t n, float scale) {
   pdl_trigger();
   pdl_wait();
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     if (!(to_f32(y[i]) > 0.f)) dy[i] = from_f32<T>(0.f);
+    else if (scale != 1.f) dy[i] = from_f32<T>(to_f32(dy[i]) * scale);
+  }
+}
+
+__device__ __forceinline__ int64_t ref_row(int64_t r, int perm_L, int perm_G) {
+  if (perm_L <= 0) return r;
+  const int64_t g = r % perm_G, bl = r / perm_G;
+  const int64_t l = bl % perm_L, b = bl / perm_L;
+  return (b * perm_G + g) * perm_L + l;
+}
+
+template <typename T>
+__global__ void dropout_add_kernel(T* __restrict__ out, const float* __restrict__ res, int64_t rows, int d, int64_t res_div,
+                                   DropCfg drop, int perm_L, int perm_G, int64_t row0) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = rows * d;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / d;
+    const int c = (int)(i % d);
+    float v = to_f32(out[i]) * drop_mul(drop, (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c));
+    if (res) v += res[(r / res_div) * d + c];
+    out[i] = from_f32<T>(v);
+  }
+}
+
+template <typename TS, typename TD>
+__global__ void dropout_scale_kernel(const TS* __restrict__ src, TD* __restrict__ dst, int64_t rows, int d, DropCfg drop, int perm_L,
+                                     int perm_G, int64_t row0) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = rows * d;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / d;
+    const int c = (int)(i % d);
+    dst[i] = from_f32<TD>(to_f32(src[i]) * drop_mul(drop, (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c)));
+  }
+}
+
+template <typename T>
+__global__ void bias_rsum_fwd_kernel(T* __restrict__ c2, const float* __restrict__ bv, const float* __restrict__ rsum, int64_t Q, int h,
+                                     int dk) {
+  pdl_trigger();
+  pdl_wait();
+  const int d = h * dk;
+  const int64_t total = Q * d;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t q = i / d;
+    const int c = (int)(i % d);
+    c2[i] = from_f32<T>(to_f32(c2[i]) + bv[c] * (rsum[q * h + c / dk] - 1.f));
+  }
+}
+
+// grid: ceil(Q / 32) CTAs of 256 threads (8 warps x 4 rows each); per-CTA dbv partial sums in smem
+template <typename T>
+__global__ void __launch_bounds__(256) bias_rsum_bwd_kernel(const T* __restrict__ dc2, const float* __restrict__ bv,
+                                                            const float* __restrict__ rsum, float* __restrict__ drsum,
+                                                            float* __restrict__ dbv, int64_t Q, int h, int dk) {
+  extern __shared__ float sdb[];  // [d]
+  pdl_trigger();
+  pdl_wait();
+  const int d = h * dk;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) sdb[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int rr = 0; rr < 4; ++rr) {
+    const int64_t q = (int64_t)blockIdx.x * 32 + warp * 4 + rr;
+    if (q >= Q) break;
+    for (int hh = 0; hh < h; ++hh) {
+      const float rs = rsum[q * h + hh];
+      float part = 0.f;
+      for (int j = lane; j < dk; j += 32) {
+        const float g = to_f32(dc2[q * d + hh * dk + j]);
+        part = fmaf(g, bv[hh * dk + j], part);
+        atomicAdd(&sdb[hh * dk + j], g * rs);
+      }
+      part = warp_sum(part);
+      if (lane == 0) drsum[q * h + hh] = part;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < d; i += blockDim.x) atomicAdd(dbv + i, sdb[i]);
+}
+
+__global__ void dropout_mask_kernel(float* __restrict__ out, int64_t n, DropCfg drop) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = drop_mul(drop, (unsigned long long)i);
 }
 
 template <typename T>
@@ -448,10 +535,60 @@ inline unsigned ew_grid(int64_t n) {
 
 }  // namespace
 
-int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st) {
+int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st, float scale) {
   ProfScope ps("relu_gate", st);
-  if (dtype == BIST_BF16) BIST_LAUNCH(relu_gate_kernel<__nv_bfloat16>, ew_grid(n), 256, 0, st, (__nv_bfloat16*)dy, (const __nv_bfloat16*)y, n);
-  else BIST_LAUNCH(relu_gate_kernel<float>, ew_grid(n), 256, 0, st, (float*)dy, (const float*)y, n);
+  if (dtype == BIST_BF16) BIST_LAUNCH(relu_gate_kernel<__nv_bfloat16>, ew_grid(n), 256, 0, st, (__nv_bfloat16*)dy, (const __nv_bfloat16*)y, n, scale);
+  else BIST_LAUNCH(relu_gate_kernel<float>, ew_grid(n), 256, 0, st, (float*)dy, (const float*)y, n, scale);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int dropout_add(void* out, const float* res, int64_t rows, int64_t d, int64_t res_div, const DropCfg& drop, int perm_L, int perm_G,
+                int out_dtype, cudaStream_t st, int64_t row0) {
+  BIST_CHECK_ARG(out && rows > 0 && d > 0 && res_div > 0, "dropout_add: bad argument");
+  ProfScope ps("dropout", st);
+  if (out_dtype == BIST_BF16) BIST_LAUNCH(dropout_add_kernel<__nv_bfloat16>, ew_grid(rows * d), 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  else BIST_LAUNCH(dropout_add_kernel<float>, ew_grid(rows * d), 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int dropout_scale(const void* src, void* dst, int64_t rows, int64_t d, const DropCfg& drop, int perm_L, int perm_G, int src_dtype,
+                  int dst_dtype, cudaStream_t st, int64_t row0) {
+  BIST_CHECK_ARG(src && dst && rows > 0 && d > 0, "dropout_scale: bad argument");
+  ProfScope ps("dropout", st);
+  const unsigned g = ew_grid(rows * d);
+  const int di = (int)d;
+  if (src_dtype == BIST_F32 && dst_dtype == BIST_BF16) BIST_LAUNCH((dropout_scale_kernel<float, __nv_bfloat16>), g, 256, 0, st, (const float*)src, (__nv_bfloat16*)dst, rows, di, drop, perm_L, perm_G, row0);
+  else if (src_dtype == BIST_F32) BIST_LAUNCH((dropout_scale_kernel<float, float>), g, 256, 0, st, (const float*)src, (float*)dst, rows, di, drop, perm_L, perm_G, row0);
+  else if (dst_dtype == BIST_BF16) BIST_LAUNCH((dropout_scale_kernel<__nv_bfloat16, __nv_bfloat16>), g, 256, 0, st, (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, rows, di, drop, perm_L, perm_G, row0);
+  else BIST_LAUNCH((dropout_scale_kernel<__nv_bfloat16, float>), g, 256, 0, st, (const __nv_bfloat16*)src, (float*)dst, rows, di, drop, perm_L, perm_G, row0);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int bias_rsum_fwd(void* c2, const float* bv, const float* rsum, int64_t Q, int h, int dk, int dtype, cudaStream_t st) {
+  ProfScope ps("dropout", st);
+  if (dtype == BIST_BF16) BIST_LAUNCH(bias_rsum_fwd_kernel<__nv_bfloat16>, ew_grid(Q * h * dk), 256, 0, st, (__nv_bfloat16*)c2, bv, rsum, Q, h, dk);
+  else BIST_LAUNCH(bias_rsum_fwd_kernel<float>, ew_grid(Q * h * dk), 256, 0, st, (float*)c2, bv, rsum, Q, h, dk);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int bias_rsum_bwd(const void* dc2, const float* bv, const float* rsum, float* drsum, float* dbv, int64_t Q, int h, int dk, int dtype,
+                  cudaStream_t st) {
+  ProfScope ps("dropout", st);
+  const unsigned grid = (unsigned)((Q + 31) / 32);
+  const size_t smem = (size_t)h * dk * 4;
+  if (dtype == BIST_BF16) BIST_LAUNCH(bias_rsum_bwd_kernel<__nv_bfloat16>, grid, 256, smem, st, (const __nv_bfloat16*)dc2, bv, rsum, drsum, dbv, Q, h, dk);
+  else BIST_LAUNCH(bias_rsum_bwd_kernel<float>, grid, 256, smem, st, (const float*)dc2, bv, rsum, drsum, dbv, Q, h, dk);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+int dropout_mask(float* out, int64_t n, const DropCfg& drop, cudaStream_t st) {
+  BIST_CHECK_ARG(out && n > 0, "dropout_mask: bad argument");
+  BIST_LAUNCH(dropout_mask_kernel, ew_grid(n), 256, 0, st, out, n, drop);
   BIST_LAUNCHED();
   return 0;
 }
@@ -547,13 +684,20 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
     sum = warp_sum(sum);
     const float inv = 1.f / sum;
     float dot = 0.f;
+    const unsigned long long ibase = (((unsigned long long)b * a.h + hh) * Lq + l) * Lk;
     for (int kk = lane; kk < Lk; kk += 32) {
       const float p = Ps[l * Lkp + kk] * inv;
+      const float dpv = Ds[l * Lkp + kk] * drop_mul(a.drop, ibase + kk);  // dP = m o dP'
       Ps[l * Lkp + kk] = p;
-      dot = fmaf(p, Ds[l * Lkp + kk], dot);
+      Ds[l * Lkp + kk] = dpv;
+      dot = fmaf(p, dpv, dot);
     }
     dot = warp_sum(dot);
-    for (int kk = lane; kk < Lk; kk += 32) Ds[l * Lkp + kk] = Ps[l * Lkp + kk] * (Ds[l * Lkp + kk] - dot) * scale;
+    for (int kk = lane; kk < Lk; kk += 32) {
+      const float p = Ps[l * Lkp + kk];
+      Ds[l * Lkp + kk] = p * (Ds[l * Lkp + kk] - dot) * scale;
+      Ps[l * Lkp + kk] = p * drop_mul(a.drop, ibase + kk);                 // p' for dV below
+    }
   }
   __syncthreads();
   T* dq = reinterpret_cast<T*>(a.dq) + b * a.q_b + hh * dk;
@@ -616,6 +760,7 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
   float* Ps = sm;                      // [Lq*h][nkp], row = l*h + hh
   float* Cs = Ps + Lq * h * nkp;       // [Lq][dkp]
   float* Vs = Cs + Lq * dkp;           // [nk][dkp]
+  float* Pd = Vs + nk * dkp;           // [Lq][nkp] dropped probabilities of the current head
   const int t = threadIdx.x, nt = blockDim.x, lane = t & 31, warp = t >> 5, nw = nt >> 5;
 
   // phase 1: probabilities of every (l, hh) row of this group, recomputed from the saved scores
@@ -657,15 +802,18 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
       const int k = i / dk, j = i % dk;
       Vs[k * dkp + j] = to_f32(Vg[f.v.off(k) + hh * dk + j]);
     }
+    for (int i = t; i < Lq * nk; i += nt) {
+      const int l = i / nk, k = i % nk;
+      Pd[l * nkp + k] = Ps[(l * h + hh) * nkp + k] * drop_mul(f.drop, (((unsigned long long)g * h + hh) * Lq + l) * nk + k);
+    }
     __syncthreads();
-    // dV[k, j] = sum_l p[l,hh,k] dC[l, j]   (uses p before it is overwritten by ds below)
+    // dV[k, j] = sum_l p'[l,hh,k] dC[l, j]
     for (int i = t; i < nk * dk; i += nt) {
       const int k = i / dk, j = i % dk;
       float s = 0.f;
-      for (int l = 0; l < Lq; ++l) s = fmaf(Ps[(l * h + hh) * nkp + k], Cs[l * dkp + j], s);
+      for (int l = 0; l < Lq; ++l) s = fmaf(Pd[l * nkp + k], Cs[l * dkp + j], s);
       dVg[f.v.off(k) + hh * dk + j] = from_f32<TV>(s);
     }
-    __syncthreads();
     // dP[l,k] = dC[l,:] . V[k,:] ;  ds = p * (dP - sum_k p dP): one warp per row l
     for (int l = warp; l < Lq; l += nw) {
       float* prow = Ps + (l * h + hh) * nkp;
@@ -675,6 +823,7 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
       for (int k = lane; k < nk; k += 32, ++c) {
         float s = 0.f;
         for (int j = 0; j < dk; ++j) s = fmaf(Cs[l * dkp + j], Vs[k * dkp + j], s);
+        s *= drop_mul(f.drop, (((unsigned long long)g * h + hh) * Lq + l) * nk + k);   // dP = m o dP'
         dpv[c] = s;
         dot = fmaf(prow[k], s, dot);
       }
@@ -713,7 +862,7 @@ int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st) {
   }
   BIST_CHECK_ARG(f.G > 0 && f.Lq > 0 && f.h > 0 && f.dk > 0 && f.nk > 0 && f.nk <= 256, "stage1_bwd: bad shape (nk <= 256)");
   BIST_CHECK_ARG(a.ds_dtype == f.v_dtype, "stage1_bwd: ds dtype must equal the value dtype");
-  const size_t smem = ((size_t)f.Lq * f.h * (f.nk + 1) + (size_t)(f.Lq + f.nk) * (f.dk + 1)) * 4;
+  const size_t smem = ((size_t)f.Lq * f.h * (f.nk + 1) + (size_t)(f.Lq + f.nk) * (f.dk + 1) + (size_t)f.Lq * (f.nk + 1)) * 4;
   if (smem > 200 * 1024) {
     set_error("stage1_bwd: Lq*h*nk = %d*%d*%d too large for one CTA", f.Lq, f.h, f.nk);
     return BIST_ERR_UNSUPPORTED;
@@ -770,8 +919,9 @@ __global__ void __launch_bounds__(256) stage2_bwd_kernel(Stage2BwdArgs a) {
       dp = warp_sum(dp);
       if (lane == 0) {
         if (a.mask && a.mask[(long long)b * G + g] == 0) s = kMaskFill;
+        if (a.drsum) dp += a.drsum[(long long)q * h + hh];
         Ps[hh * Gp + g] = s;
-        Ds[hh * Gp + g] = dp;
+        Ds[hh * Gp + g] = dp * drop_mul(a.drop, ((unsigned long long)q * h + hh) * G + g);   // dP = m o dP'
       }
     }
   }
@@ -795,10 +945,14 @@ __global__ void __launch_bounds__(256) stage2_bwd_kernel(Stage2BwdArgs a) {
       dot = fmaf(p, Ds[hh * Gp + g], dot);
     }
     dot = warp_sum(dot);
-    for (int g = lane; g < G; g += 32) Ds[hh * Gp + g] = Ps[hh * Gp + g] * (Ds[hh * Gp + g] - dot);
+    for (int g = lane; g < G; g += 32) {
+      const float p = Ps[hh * Gp + g];
+      Ds[hh * Gp + g] = p * (Ds[hh * Gp + g] - dot);
+      Ps[hh * Gp + g] = p * drop_mul(a.drop, ((unsigned long long)q * h + hh) * G + g);       // p' for dx1 below
+    }
   }
   __syncthreads();
-  // dx1[g, c] = sum_hh p[hh,g] du[hh,c] + ds[hh,g] qf[hh,c]
+  // dx1[g, c] = sum_hh p'[hh,g] du[hh,c] + ds[hh,g] qf[hh,c]
   T* dx1 = reinterpret_cast<T*>(a.dx1) + (long long)q * G * d;
   for (int i = t; i < G * d; i += nt) {
     const int g = i / d, c = i % d;

@@ -139,12 +139,18 @@ __global__ void __launch_bounds__(256) stage1_bwd_mma_kernel(Stage1BwdArgs a) {
     for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) s[ks][j] *= (j & 2) ? inv1 : inv0;
-      // P (bf16) into this warp's [16 l][keys] tile for the transposed product below
+      // P' = m o P (bf16; m = the forward's dropout multipliers) into this warp's [16 l][keys] tile for the transposed product below
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int k = ks * 16 + half * 8 + kq;
-        *reinterpret_cast<uint32_t*>(Pw + (size_t)r0 * ldp + k) = pack2(s[ks][half * 4 + 0], s[ks][half * 4 + 1]);
-        *reinterpret_cast<uint32_t*>(Pw + (size_t)r1 * ldp + k) = pack2(s[ks][half * 4 + 2], s[ks][half * 4 + 3]);
+        float m[4] = {1.f, 1.f, 1.f, 1.f};
+        if (f.drop.thresh != 0u) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            m[e] = drop_mul(f.drop, (((unsigned long long)g * h + hh) * Lq + ((e & 2) ? r1 : r0)) * nk + k + (e & 1));
+        }
+        *reinterpret_cast<uint32_t*>(Pw + (size_t)r0 * ldp + k) = pack2(s[ks][half * 4 + 0] * m[0], s[ks][half * 4 + 1] * m[1]);
+        *reinterpret_cast<uint32_t*>(Pw + (size_t)r1 * ldp + k) = pack2(s[ks][half * 4 + 2] * m[2], s[ks][half * 4 + 3] * m[3]);
       }
     }
     if (!staged) {  // first head of this warp: the staged tiles must have landed
@@ -180,7 +186,16 @@ __global__ void __launch_bounds__(256) stage1_bwd_mma_kernel(Stage1BwdArgs a) {
         }
       }
     }
-    // ---- dS = P o (dP - rowsum(P o dP))
+    // ---- dS = P o (dP - rowsum(P o dP)), dP = m o dP'
+    if (f.drop.thresh != 0u) {
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int key = ks * 16 + (j >> 2) * 8 + kq + (j & 1);
+          dp[ks][j] *= drop_mul(f.drop, (((unsigned long long)g * h + hh) * Lq + ((j & 2) ? r1 : r0)) * nk + key);
+        }
+    }
     float dot0 = 0.f, dot1 = 0.f;
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks)
@@ -414,13 +429,17 @@ __global__ void __launch_bounds__(256) stage2_bwd_mma_kernel(Stage2BwdArgs a) {
     sum = warp_sum(sum);
     const float inv = 1.f / sum;
     float dot = 0.f;
-    for (int g = lane; g < G; g += 32) dot = fmaf(srow[g] * inv, drow[g], dot);
+    const float dr = (a.drsum && hh < h) ? a.drsum[(long long)q * h + hh] : 0.f;
+    const unsigned long long ibase = ((unsigned long long)q * h + hh) * G;
+    for (int g = lane; g < G; g += 32) dot = fmaf(srow[g] * inv, (drow[g] + dr) * drop_mul(a.drop, ibase + g), dot);
     dot = warp_sum(dot);
     for (int g = lane; g < Gp; g += 32) {
       float p = 0.f, ds = 0.f;
       if (g < G && hh < h) {
+        const float m = drop_mul(a.drop, ibase + g);
         p = srow[g] * inv;
-        ds = p * (drow[g] - dot);
+        ds = p * ((drow[g] + dr) * m - dot);
+        p *= m;                                    // p' multiplies du in dx1
       }
       W2[(size_t)hh * ldw + g] = __float2bfloat16_rn(ds);
       W2[(size_t)(8 + hh) * ldw + g] = __float2bfloat16_rn(p);

@@ -133,6 +133,41 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// ---- dropout (training mode, modules.py:44,62-63,113) --------------------------------------------
+// Counter-based: element `idx` of dropout site `site` is kept iff hash(seed, site, idx) >= thresh; kept values are
+// scaled by 1/(1-p).  Forward and backward regenerate the same mask; nothing is stored.  `idx` is the flat index of
+// the element in the REFERENCE's tensor at that site (so that tests can inject identical masks into the oracle
+// through bist_dropout_mask).  p == 0 (thresh == 0) disables a site.
+struct DropCfg {
+  unsigned long long seed = 0;
+  uint32_t thresh = 0;   // floor(p * 2^32)
+  uint32_t site = 0;
+  float scale = 1.f;     // 1 / (1 - p)
+};
+static inline DropCfg make_drop(float p, unsigned long long seed, uint32_t site) {
+  DropCfg c;
+  if (p > 0.f) {
+    double t = (double)p * 4294967296.0;
+    c.thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+    c.scale = 1.f / (1.f - p);
+    c.seed = seed; c.site = site;
+  }
+  return c;
+}
+#ifdef __CUDACC__
+__host__ __device__ __forceinline__ uint32_t drop_hash(unsigned long long seed, uint32_t site, unsigned long long idx) {
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (idx + 1ull) + ((unsigned long long)site << 52);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (uint32_t)(z >> 32);
+}
+// multiplier of element idx: 0 (dropped) or 1/(1-p)
+__device__ __forceinline__ float drop_mul(const DropCfg& c, unsigned long long idx) {
+  return (c.thresh == 0u || drop_hash(c.seed, c.site, idx) >= c.thresh) ? c.scale : 0.f;
+}
+#endif
+
 // ---- two-level row addressing -----------------------------------------------------------
 // Element offset of logical row r: (r / inner) * outer_stride + (r % inner) * inner_stride.
 // Lets one GEMM / attention kernel walk [B,T,S,d] as rows (b,t,s) or (b,s,t), broadcast a
@@ -217,6 +252,7 @@ struct SoftmaxPvArgs {
   float* p_out = nullptr;   // optional fp32 [G, h, Lq, nk]
   int G = 0, Lq = 0, h = 0, dk = 0, nk = 0;
   int v_dtype = BIST_F32, ctx_dtype = BIST_F32;
+  DropCfg drop;  // dropout on the probabilities (modules.py:62-63); element index ((g*h + hh)*Lq + l)*nk + k
 };
 int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st);  // tensor-core kernel when the shape allows, else CUDA cores
 int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken);  // attn_mma.cu
@@ -225,10 +261,16 @@ int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken);  // at
 // For every (b,l): scores[hh,g] = qf[b,l,hh,:] . X1[b,l,g,:] (qf pre-scaled), optional key mask
 // [B,G], softmax over g, ctxx[b,l,hh,:] = sum_g p[hh,g] X1[b,l,g,:]   (fp32 [B*Lq, h, d]).
 // x1 is laid out [B, Lq, G, d] (the G summaries of one (b,l) are contiguous).
+// Training-mode extras of stage 2: dropout on the probabilities (element index (q*h + hh)*G + g) and, because the
+// dropped probabilities no longer sum to one, rsum[q,hh] = sum_g p'[hh,g] (fp32 [B*Lq, h]) for the value bias.
+struct Stage2Extra {
+  DropCfg drop;
+  float* rsum = nullptr;
+};
 int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G,
-                int Lq, int h, int d, int x1_dtype, int ctxx_dtype, cudaStream_t st);
+                int Lq, int h, int d, int x1_dtype, int ctxx_dtype, cudaStream_t st, const Stage2Extra* ex = nullptr);
 int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d,
-               cudaStream_t st, bool* taken);  // bf16 q / x1 / out; attn_mma.cu
+               cudaStream_t st, bool* taken, const Stage2Extra* ex = nullptr);  // bf16 q / x1 / out; attn_mma.cu
 bool stage2_mma_supported(int G, int h, int d);
 // Fused self-attention over the query tokens (bf16): qkv [G*Lq, 3d] -> ctx [G*Lq, d]; key mask uint8 [(g % mask_mod), Lq].
 int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, int G, int Lq, int h, int dk, cudaStream_t st,
@@ -285,8 +327,24 @@ struct LnBwdArgs {
 };
 int layer_norm_bwd(const LnBwdArgs& a, cudaStream_t st);
 
-// dy[i] = y[i] > 0 ? dy[i] : 0   (in place; y and dy of dtype `dtype`)
-int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st);
+// dy[i] = y[i] > 0 ? scale * dy[i] : 0   (in place; y and dy of dtype `dtype`).  With dropout after the ReLU, y is the
+// dropped activation (positive only where the unit was active AND kept) and scale = 1/(1-p).
+int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st, float scale = 1.f);
+// Sublayer / hidden dropout, forward (modules.py:44,113):  out[r,c] = (res ? res[r / res_div, c] : 0) + out[r,c] * m(idx),
+// idx = ref_row(r) * d + c.  ref_row(r) = r, or with perm_L > 0 the reference's row of our (b, l, g) row:
+// r = (b*perm_L + l)*perm_G + g  ->  (b*perm_G + g)*perm_L + l   (stage-1 outputs are kept [B,Lq,G,d], the reference's are [B*G,Lq,d]).
+int dropout_add(void* out, const float* res, int64_t rows, int64_t d, int64_t res_div, const DropCfg& drop, int perm_L, int perm_G,
+                int out_dtype, cudaStream_t st, int64_t row0 = 0);   // row0: offset added to ref_row (per-direction calls of a batched site)
+// Backward of the same: dst[r,c] = src[r,c] * m(idx)  (also the fp32 -> compute-dtype cast when drop is off; src may equal dst).
+int dropout_scale(const void* src, void* dst, int64_t rows, int64_t d, const DropCfg& drop, int perm_L, int perm_G, int src_dtype,
+                  int dst_dtype, cudaStream_t st, int64_t row0 = 0);
+// Stage-2 value bias under dropout: c2[q, hh*dk + j] += bv[hh*dk + j] * (rsum[q,hh] - 1)   (the GEMM already added bv once)
+int bias_rsum_fwd(void* c2, const float* bv, const float* rsum, int64_t Q, int h, int dk, int dtype, cudaStream_t st);
+// and its backward: drsum[q,hh] = sum_j dc2[q, hh*dk+j] bv[hh*dk+j];  dbv[hh*dk+j] += sum_q dc2[q, hh*dk+j] rsum[q,hh]
+int bias_rsum_bwd(const void* dc2, const float* bv, const float* rsum, float* drsum, float* dbv, int64_t Q, int h, int dk, int dtype,
+                  cudaStream_t st);
+// out[i] = keep ? 1/(1-p) : 0 for i in [0, n): the multipliers of one dropout site (tests / bist_dropout_mask)
+int dropout_mask(float* out, int64_t n, const DropCfg& drop, cudaStream_t st);
 // out[q, c] (fp32) += sum_g in[q, g, c]
 int group_sum(const void* in, float* out, int64_t Qrows, int64_t G, int64_t d, int in_dtype, cudaStream_t st);
 // dst (dst_dtype) = src (src_dtype), n elements
@@ -303,6 +361,7 @@ struct AttnBwdArgs {
   long long m_b = 0, m_l = 0;  // mask[(b % mask_mod)*m_b + l*m_l + k]
   int Bp = 0, Lq = 0, Lk = 0, h = 0, dk = 0;
   int dtype = BIST_F32;  // of q, k, v, dctx, dq, dk, dv
+  DropCfg drop;          // dropout that the forward applied to the probabilities: element ((b*h + hh)*Lq + l)*Lk + k
 };
 int attn_core_bwd(const AttnBwdArgs& a, cudaStream_t st);
 
@@ -332,6 +391,8 @@ struct Stage2BwdArgs {
   void *dx1 = nullptr, *dqf = nullptr;
   int B = 0, G = 0, Lq = 0, h = 0, d = 0;
   int dtype = BIST_F32;  // of all six tensors
+  DropCfg drop;                  // dropout of the forward's probabilities (Stage2Extra)
+  const float* drsum = nullptr;  // fp32 [Q,h] gradient of rsum (added to every dP'[hh,g]) or null
 };
 int stage2_bwd(const Stage2BwdArgs& a, cudaStream_t st);
 int stage2_bwd_mma(const Stage2BwdArgs& a, cudaStream_t st, bool* taken);  // bwd_mma.cu

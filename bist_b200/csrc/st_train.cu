@@ -77,7 +77,7 @@ bool stage2_on_mma(int dtype, int64_t T, int64_t S, int64_t h, int64_t d, int nd
 
 struct Tape {
   void *n0, *qkv0, *c0, *n12, *q12, *qf12, *xv, *u2, *c2, *n3, *ffh;  // compute dtype
-  float *x, *ts, *qf2f, *sc0;
+  float *x, *ts, *qf2f, *sc0, *rsum;
   float* sc1[2];
   void* ctx1[2];
   void* out1[2];
@@ -99,6 +99,7 @@ Tape carve_tape(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   W.x = f(nd * Q * d); W.ts = f(nd * Q * d);
   W.qf2f = (dtype == BIST_BF16 && !stage2_on_mma(dtype, T, S, h, d, nd, kinds)) ? f(nd * Q * h * d) : nullptr;
   W.sc0 = f(nd * Q * h * Lq);
+  W.rsum = f(nd * Q * h);
   for (int u = 0; u < 2; ++u) { W.sc1[u] = nullptr; W.ctx1[u] = nullptr; W.out1[u] = nullptr; }
   for (int u = 0; u < nd; ++u) {
     const size_t G = kinds[u] == 0 ? S : T;
@@ -115,7 +116,7 @@ struct BwdWs {
   void *a_dout, *a_dts, *a_dx, *dffh, *dn, *dc, *du2, *dqf12, *dq12, *dxv, *qf1T, *dsT, *dqkv0;  // compute dtype
   void* dout1[2];
   void* dc1[2];
-  float *dts, *dqf1;
+  float *dts, *dqf1, *drsum;
   size_t bytes;
   bool ok;
 };
@@ -127,8 +128,7 @@ BwdWs carve_bwd(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   const size_t Q = (size_t)B * Lq, e = dtype_size(dtype);
   auto f = [&](size_t n) { return (float*)A.take(n * 4); };
   auto a = [&](size_t n) { return A.take(n * e); };
-  const bool cast = dtype == BIST_BF16;
-  W.a_dout = cast ? a(nd * Q * d) : nullptr; W.a_dts = cast ? a(nd * Q * d) : nullptr; W.a_dx = cast ? a(nd * Q * d) : nullptr;
+  W.a_dout = a(nd * Q * d); W.a_dts = a(nd * Q * d); W.a_dx = a(nd * Q * d);
   W.dffh = a(nd * Q * dff); W.dn = a(2 * nd * Q * d); W.dc = a(nd * Q * d); W.du2 = a(nd * Q * h * d);
   W.dqf12 = a(2 * nd * Q * h * d); W.dq12 = a(2 * nd * Q * d);
   W.dxv = a((size_t)B * T * S * nd * d);
@@ -140,11 +140,15 @@ BwdWs carve_bwd(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
     W.dout1[u] = a(Q * G * d);
     W.dc1[u] = a(Q * G * d);
   }
-  W.dts = f(nd * Q * d); W.dqf1 = f(nd * Q * h * d);
+  W.dts = f(nd * Q * d); W.dqf1 = f(nd * Q * h * d); W.drsum = f(nd * Q * h);
   W.bytes = A.used + 256;
   W.ok = A.ok;
   return W;
 }
+
+// Dropout sites of one layer call (DropCfg::site); u = slot of the active direction.
+enum : uint32_t { S_SELF_P = 0, S_SELF_OUT = 1, S_ST1_P = 2 /* +u */, S_ST1_OUT = 4 /* +u */, S_ST2_P = 6 /* +u */, S_ST2_OUT = 8,
+                  S_FF_HID = 9, S_FF_OUT = 10 };
 
 int active(int n_dirs, int dir_mask, int* kinds) {
   int nd = 0;
@@ -156,7 +160,7 @@ int active(int n_dirs, int dir_mask, int* kinds) {
 
 // Stage-1 argument block shared by the forward (softmax_pv) and the backward (stage1_bwd).
 SoftmaxPvArgs stage1_args(bool t2s, bool regions, const float* sc1, const uint8_t* temporal_mask, const void* xv_u, void* ctx,
-                          int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h, int nd, int dtype) {
+                          int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h, int nd, int dtype, const DropCfg& drop) {
   const long long TS = T * S, xvld = (long long)nd * d;
   const int G = (int)(t2s ? S : T);
   SoftmaxPvArgs a;
@@ -175,6 +179,7 @@ SoftmaxPvArgs stage1_args(bool t2s, bool regions, const float* sc1, const uint8_
   a.og = rows_2level(G, Lq * G * d, d); a.o_l = (long long)G * d;
   a.G = (int)(B * G); a.Lq = (int)Lq; a.h = (int)h; a.dk = (int)(d / h); a.nk = (int)(t2s ? T : S);
   a.v_dtype = dtype; a.ctx_dtype = dtype;
+  a.drop = drop;
   return a;
 }
 
@@ -316,6 +321,9 @@ struct Ctx {
   int Q, dk, di, hi;
   long long Qd, dd, ms, fsd, TS;
   bool s2mma, regions;
+  float p_attn = 0.f, p_sub = 0.f, p_ffn = 0.f;
+  unsigned long long seed = 0;
+  DropCfg drop(uint32_t site, float p) const { return make_drop(p, seed, site); }
   const void* Mw(size_t off) const { return mat + off * e; }
   const void* Mshared(size_t off) const { return mat - (size_t)pu0 * L.dir_stride * e + off * e; }
   const float* Fshared(size_t off) const { return fs - (size_t)pu0 * L.fdir_stride + off; }
@@ -324,7 +332,12 @@ struct Ctx {
 };
 
 int make_ctx(Ctx& c, const void* packed, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t dff, int64_t h, int n_dirs,
-             int dir_mask, float eps, int dtype, cudaStream_t st) {
+             int dir_mask, float eps, int dtype, cudaStream_t st, const bist_dropout_t* dropout) {
+  if (dropout) {
+    BIST_CHECK_ARG(dropout->p_attn >= 0.f && dropout->p_attn < 1.f && dropout->p_sublayer >= 0.f && dropout->p_sublayer < 1.f &&
+                       dropout->p_ffn >= 0.f && dropout->p_ffn < 1.f, "st_layer(train): dropout probabilities must be in [0, 1)");
+    c.p_attn = dropout->p_attn; c.p_sub = dropout->p_sublayer; c.p_ffn = dropout->p_ffn; c.seed = dropout->seed;
+  }
   BIST_CHECK_ARG(B > 0 && T > 0 && S > 0 && Lq > 0 && d > 0 && dff > 0 && h > 0 && d % h == 0, "st_layer(train): bad shape");
   BIST_CHECK_ARG(d % 4 == 0 && dff % 4 == 0, "st_layer(train): d and d_ff must be multiples of 4");
   BIST_CHECK_ARG((n_dirs == 1 || n_dirs == 2) && dtype_ok(dtype) && (dir_mask & ~3) == 0 && dir_mask != 0, "st_layer(train): bad n_dirs/dir_mask/dtype");
@@ -366,11 +379,11 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
                                        const uint8_t* temporal_mask, const void* packed, float* out_t2s, float* out_s2t,
                                        int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t dff, int64_t h,
                                        int n_dirs, int dir_mask, float eps, void* tape, size_t tape_bytes, int dtype,
-                                       void* stream) {
+                                       const bist_dropout_t* dropout, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   BIST_CHECK_ARG(vft && query_mask && temporal_mask && packed && tape, "st_layer_train_fwd: null pointer");
   Ctx c;
-  BIST_TRY(make_ctx(c, packed, B, T, S, Lq, d, dff, h, n_dirs, dir_mask, eps, dtype, st));
+  BIST_TRY(make_ctx(c, packed, B, T, S, Lq, d, dff, h, n_dirs, dir_mask, eps, dtype, st, dropout));
   const int nd = c.nd;
   const float* x_in[2];
   float* x_out[2];
@@ -393,7 +406,8 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
   BIST_TRY(lin(c, W.n0, Qd, adt, L.wqkv0, fs + L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0, adt, "query_side_gemm"));
   {
     bool fused = false;
-    if (dtype == BIST_BF16) BIST_TRY(self_attn_mma(W.qkv0, query_mask, (int)B, W.c0, (int)(nd * B), (int)Lq, hi, dk, st, &fused));
+    if (dtype == BIST_BF16 && c.p_attn == 0.f)
+      BIST_TRY(self_attn_mma(W.qkv0, query_mask, (int)B, W.c0, (int)(nd * B), (int)Lq, hi, dk, st, &fused));
     if (!fused) {
       GemmArgs g;
       g.A = W.qkv0; g.W = c.act(W.qkv0, d); g.C = W.sc0;
@@ -411,10 +425,18 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
       a.ctx = W.c0; a.og = rows_dense(Lq * d); a.o_l = d;
       a.G = (int)(nd * B); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = (int)Lq;
       a.v_dtype = adt; a.ctx_dtype = adt;
+      a.drop = c.drop(S_SELF_P, c.p_attn);
       BIST_TRY(softmax_pv(a, st));
     }
   }
-  BIST_TRY(lin(c, W.c0, Qd, adt, L.wo0, fs + L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir, BIST_F32, "query_side_gemm"));
+  // x = x_in + dropout(c0 W_o0^T + b_o0)   (modules.py:44)
+  if (c.p_sub > 0.f) {
+    BIST_TRY(lin(c, W.c0, Qd, adt, L.wo0, fs + L.bo0, W.x, Qd, BIST_F32, di, di, 0, nullptr, 0, BIST_F32, "query_side_gemm"));
+    for (int u = 0; u < nd; ++u)
+      BIST_TRY(dropout_add(W.x + u * Qd, x_in[u], Q, d, 1, c.drop(S_SELF_OUT, c.p_sub), 0, 0, BIST_F32, st, (int64_t)u * Q));
+  } else {
+    BIST_TRY(lin(c, W.c0, Qd, adt, L.wo0, fs + L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir, BIST_F32, "query_side_gemm"));
+  }
 
   // ---- query side of stage 1 / stage 2: n12 = [LN1(x) | LN2(x)], q12 = n12 . {W_q1 | W_q2}^T + b, folds
   BIST_TRY(layer_norm2(W.x, fs + L.ln_a + d, fs + L.ln_b + d, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.n12, c.act(W.n12, nd * Qd),
@@ -487,16 +509,19 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
       }
       if (!done) BIST_TRY(gemm(g, st));
     }
-    SoftmaxPvArgs a = stage1_args(t2s, regions, W.sc1[u], temporal_mask, c.act(W.xv, (long long)u * d), W.ctx1[u], B, T, S, Lq, d, h, nd, dtype);
+    SoftmaxPvArgs a = stage1_args(t2s, regions, W.sc1[u], temporal_mask, c.act(W.xv, (long long)u * d), W.ctx1[u], B, T, S, Lq, d, h, nd, dtype,
+                                  c.drop(S_ST1_P + u, c.p_attn));
     BIST_TRY(softmax_pv(a, st));
     {
       GemmArgs g;  // out1[b,l,g,:] = x[b,l,:] + c1[b,l,g,:] W_o1^T + b_o1   (modules.py:44 around encoder.py:121 / :148)
       g.A = W.ctx1[u]; g.W = c.Mw(L.wo1 + (size_t)u * ms); g.C = W.out1[u]; g.bias = fs + L.bo1 + u * fsd;
-      g.R = W.x + u * Qd;
+      g.R = c.p_sub > 0.f ? nullptr : W.x + u * Qd;
       g.M = Q * G; g.N = di; g.K = di;
       g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_2level(G, d, 0);
       g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.r_dtype = BIST_F32; g.tag = "o1_gemm";
       BIST_TRY(gemm(g, st));
+      if (c.p_sub > 0.f)  // the reference drops elements of its [B*G, Lq, d] tensor: index through the (b,l,g) -> (b,g,l) row map
+        BIST_TRY(dropout_add(W.out1[u], W.x + u * Qd, (int64_t)Q * G, d, G, c.drop(S_ST1_OUT + u, c.p_sub), (int)Lq, G, adt, st));
     }
   }
 
@@ -505,13 +530,16 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
     const bool t2s = c.kinds[u] == 0;
     const int G = (int)(t2s ? S : T);
     const uint8_t* m2 = t2s ? nullptr : temporal_mask;
+    Stage2Extra ex;
+    ex.drop = c.drop(S_ST2_P + u, c.p_attn); ex.rsum = W.rsum + (long long)u * Q * h;
+    const Stage2Extra* exp = c.p_attn > 0.f ? &ex : nullptr;
     if (c.s2mma) {
       bool taken = false;
-      BIST_TRY(stage2_mma(c.act(W.qf12, (nd + u) * Qd * h), W.out1[u], m2, c.act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, st, &taken));
+      BIST_TRY(stage2_mma(c.act(W.qf12, (nd + u) * Qd * h), W.out1[u], m2, c.act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, st, &taken, exp));
       BIST_CHECK_ARG(taken, "st_layer_train_fwd: stage2_mma declined a shape it reported as supported");
     } else {
       const float* qf = dtype == BIST_BF16 ? W.qf2f + u * Qd * h : (const float*)W.qf12 + (nd + u) * Qd * h;
-      BIST_TRY(stage2_attn(qf, W.out1[u], m2, c.act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, dtype, adt, st));
+      BIST_TRY(stage2_attn(qf, W.out1[u], m2, c.act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, dtype, adt, st, exp));
     }
   }
   {
@@ -523,13 +551,29 @@ extern "C" int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t,
     g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.bz = {fsd, dk};
     g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "vfold2_gemm";
     BIST_TRY(gemm(g, st));
+    if (c.p_attn > 0.f)  // dropped probabilities do not sum to one: the value bias enters with weight rsum (modules.py:62-64)
+      for (int u = 0; u < nd; ++u)
+        BIST_TRY(bias_rsum_fwd(c.act(W.c2, u * Qd), fs + u * fsd + L.bv2, W.rsum + (long long)u * Q * h, Q, hi, dk, adt, st));
   }
-  BIST_TRY(lin(c, W.c2, Qd, adt, L.wo2, fs + L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd, BIST_F32, "query_side_gemm"));
+  if (c.p_sub > 0.f) {
+    BIST_TRY(lin(c, W.c2, Qd, adt, L.wo2, fs + L.bo2, W.ts, Qd, BIST_F32, di, di, 0, nullptr, 0, BIST_F32, "query_side_gemm"));
+    BIST_TRY(dropout_add(W.ts, W.x, (int64_t)nd * Q, d, 1, c.drop(S_ST2_OUT, c.p_sub), 0, 0, BIST_F32, st));
+  } else {
+    BIST_TRY(lin(c, W.c2, Qd, adt, L.wo2, fs + L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd, BIST_F32, "query_side_gemm"));
+  }
 
   // ---- feed-forward (encoder.py:134-135 / :165-166)
   BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.n3, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
   BIST_TRY(lin(c, W.n3, Qd, adt, L.w1, fs + L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0, adt, "query_side_gemm"));
-  BIST_TRY(lin(c, W.ffh, (long long)Q * dff, adt, L.w2, fs + L.b2, x_out[0], out_dir, BIST_F32, di, (int)dff, 0, W.ts, Qd, BIST_F32, "query_side_gemm"));
+  if (c.p_ffn > 0.f)   // modules.py:113
+    BIST_TRY(dropout_add(W.ffh, nullptr, (int64_t)nd * Q, dff, 1, c.drop(S_FF_HID, c.p_ffn), 0, 0, adt, st));
+  if (c.p_sub > 0.f) {
+    BIST_TRY(lin(c, W.ffh, (long long)Q * dff, adt, L.w2, fs + L.b2, x_out[0], out_dir, BIST_F32, di, (int)dff, 0, nullptr, 0, BIST_F32, "query_side_gemm"));
+    for (int u = 0; u < nd; ++u)
+      BIST_TRY(dropout_add(x_out[u], W.ts + u * Qd, Q, d, 1, c.drop(S_FF_OUT, c.p_sub), 0, 0, BIST_F32, st, (int64_t)u * Q));
+  } else {
+    BIST_TRY(lin(c, W.ffh, (long long)Q * dff, adt, L.w2, fs + L.b2, x_out[0], out_dir, BIST_F32, di, (int)dff, 0, W.ts, Qd, BIST_F32, "query_side_gemm"));
+  }
   return 0;
 }
 
@@ -538,11 +582,12 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
                                  const void* vft, const uint8_t* query_mask, const uint8_t* temporal_mask, const void* packed,
                                  const void* tape, size_t tape_bytes, float* d_in_t2s, float* d_in_s2t, float* d_vft,
                                  float* grads, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t dff, int64_t h,
-                                 int n_dirs, int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype, void* stream) {
+                                 int n_dirs, int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype,
+                                 const bist_dropout_t* dropout, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   BIST_CHECK_ARG(vft && query_mask && temporal_mask && packed && tape && ws && d_vft && grads, "st_layer_bwd: null pointer");
   Ctx c;
-  BIST_TRY(make_ctx(c, packed, B, T, S, Lq, d, dff, h, n_dirs, dir_mask, eps, dtype, st));
+  BIST_TRY(make_ctx(c, packed, B, T, S, Lq, d, dff, h, n_dirs, dir_mask, eps, dtype, st, dropout));
   const int nd = c.nd;
   const float *x_in[2], *g_out[2];
   float* g_in[2];
@@ -593,14 +638,13 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
   };
 
   // ---- feed-forward backward: out = ts + relu(n3 W1^T + b1) W2^T + b2
-  const void* a_dout = g_out[0];
-  long long a_dout_dir = go_dir;
-  if (bf) {
-    for (int u = 0; u < nd; ++u) BIST_TRY(cast_copy(g_out[u], c.act(D.a_dout, u * Qd), Qd, BIST_F32, BIST_BF16, st));
-    a_dout = D.a_dout; a_dout_dir = Qd;
-  }
+  // gradient of the dropped sublayer output, in the compute dtype: a_dout = m o d_out   (plain cast/copy without dropout)
+  for (int u = 0; u < nd; ++u)
+    BIST_TRY(dropout_scale(g_out[u], c.act(D.a_dout, u * Qd), Q, d, c.drop(S_FF_OUT, c.p_sub), 0, 0, BIST_F32, adt, st, (int64_t)u * Q));
+  const void* a_dout = D.a_dout;
+  const long long a_dout_dir = Qd;
   BIST_TRY(lin(c, a_dout, a_dout_dir, adt, L.w2T, nullptr, D.dffh, Qf, adt, fi, di, 0, nullptr, 0, adt, "bwd_dx_gemm"));
-  BIST_TRY(relu_gate(D.dffh, W.ffh, (int64_t)nd * Qf, adt, st));
+  BIST_TRY(relu_gate(D.dffh, W.ffh, (int64_t)nd * Qf, adt, st, c.p_ffn > 0.f ? 1.f / (1.f - c.p_ffn) : 1.f));
   BIST_TRY(wg(a_dout, a_dout_dir, d, adt, W.ffh, Qf, dff, adt, GL.ff + (size_t)d * dff + dff, GL.ff + 2 * (size_t)d * dff + dff, true, di, fi, "wgrad_q"));
   BIST_TRY(lin(c, D.dffh, Qf, adt, L.w1T, nullptr, D.dn, Qd, adt, di, fi, 0, nullptr, 0, adt, "bwd_dx_gemm"));
   BIST_TRY(wg(D.dffh, Qf, dff, adt, W.n3, Qd, d, adt, GL.ff, GL.ff + (size_t)d * dff, true, fi, di, "wgrad_q"));
@@ -609,8 +653,8 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
   BIST_TRY(lnb(D.dn, W.ts, 0, 3, D.dts, 1));
 
   // ---- ts = x + c2 W_o2^T + b_o2
-  const void* a_dts = D.dts;
-  if (bf) { BIST_TRY(cast_copy(D.dts, D.a_dts, nd * Qd, BIST_F32, BIST_BF16, st)); a_dts = D.a_dts; }
+  BIST_TRY(dropout_scale(D.dts, D.a_dts, (int64_t)nd * Q, d, c.drop(S_ST2_OUT, c.p_sub), 0, 0, BIST_F32, adt, st));
+  const void* a_dts = D.a_dts;
   BIST_TRY(lin(c, a_dts, Qd, adt, L.wo2T, nullptr, D.dc, Qd, adt, di, di, 0, nullptr, 0, adt, "bwd_dx_gemm"));   // dc2
   BIST_TRY(wg(a_dts, Qd, d, adt, W.c2, Qd, d, adt, GL.W(2, 3, sdd), GL.b(2, 3, sdd, d), true, di, di, "wgrad_q"));
   // from here on D.dts is the running gradient of x (dx): x feeds ts directly (residual)
@@ -626,15 +670,19 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "bwd_fold_gemm";
     BIST_TRY(gemm(g, st));
     WgradArgs w;  // dW_v2[hh-slice, :] += dc2[:, hh-slice]^T u2[:, hh, :] ; db_v2 += colsum(dc2)
-    w.A = D.dc; w.B = W.u2; w.C = G0 + GL.W(2, 2, sdd); w.colsum = G0 + GL.b(2, 2, sdd, d);
+    w.A = D.dc; w.B = W.u2; w.C = G0 + GL.W(2, 2, sdd); w.colsum = c.p_attn > 0.f ? nullptr : G0 + GL.b(2, 2, sdd, d);
     w.M = Q; w.N = dk; w.K = di; w.lda = d; w.ldb = h * d; w.ldc = d;
     w.Z = nd * hi; w.zin = hi;
     w.az = {Qd, dk}; w.bz = {Qd * h, d}; w.cz = {gd, (long long)dk * d}; w.sz = {gd, dk};
     w.a_dtype = adt; w.b_dtype = adt; w.tag = "wgrad_q";
     BIST_TRY(wgrad(w, st));
+    if (c.p_attn > 0.f)  // c2 += b_v2 * rsum: db_v2 += sum_q dc2 * rsum, drsum = dc2 . b_v2
+      for (int u = 0; u < nd; ++u)
+        BIST_TRY(bias_rsum_bwd(c.act(D.dc, u * Qd), fs + u * fsd + L.bv2, W.rsum + (long long)u * Q * h, D.drsum + (long long)u * Q * h,
+                               G0 + u * gd + GL.b(2, 2, sdd, d), Q, hi, dk, adt, st));
   }
 
-  // ---- stage 2 backward, then out1 = x + c1 W_o1^T + b_o1
+  // ---- stage 2 backward, then out1 = x + dropout(c1 W_o1^T + b_o1)
   for (int u = 0; u < nd; ++u) {
     const bool t2s = c.kinds[u] == 0;
     const int G = (int)(t2s ? S : T);
@@ -643,8 +691,12 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     a.mask = t2s ? nullptr : temporal_mask;
     a.dx1 = D.dout1[u]; a.dqf = c.act(D.dqf12, (nd + u) * Qd * h);
     a.B = (int)B; a.G = G; a.Lq = (int)Lq; a.h = hi; a.d = di; a.dtype = adt;
+    a.drop = c.drop(S_ST2_P + u, c.p_attn);
+    a.drsum = c.p_attn > 0.f ? D.drsum + (long long)u * Q * h : nullptr;
     BIST_TRY(stage2_bwd(a, st));
-    BIST_TRY(group_sum(D.dout1[u], D.dts + u * Qd, Q, G, d, adt, st));  // dx += sum_g dout1
+    BIST_TRY(group_sum(D.dout1[u], D.dts + u * Qd, Q, G, d, adt, st));  // dx += sum_g dout1 (residual branch, not dropped)
+    if (c.p_sub > 0.f)
+      BIST_TRY(dropout_scale(D.dout1[u], D.dout1[u], (int64_t)Q * G, d, c.drop(S_ST1_OUT + u, c.p_sub), (int)Lq, G, adt, adt, st));
     {
       GemmArgs g;  // dc1 = dout1 . W_o1
       g.A = D.dout1[u]; g.W = c.Mw(L.wo1T + (size_t)u * ms); g.C = D.dc1[u];
@@ -667,7 +719,8 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     const bool t2s = c.kinds[u] == 0;
     const int G = (int)(t2s ? S : T);
     Stage1BwdArgs a;
-    a.f = stage1_args(t2s, t2s && c.regions, W.sc1[u], temporal_mask, c.act(W.xv, (long long)u * d), nullptr, B, T, S, Lq, d, h, nd, dtype);
+    a.f = stage1_args(t2s, t2s && c.regions, W.sc1[u], temporal_mask, c.act(W.xv, (long long)u * d), nullptr, B, T, S, Lq, d, h, nd, dtype,
+                      c.drop(S_ST1_P + u, c.p_attn));
     a.dctx = D.dc1[u];
     a.dV = c.act(D.dxv, (long long)u * d);
     a.ds = nullptr; a.dsT = D.dsT; a.gdiv = G; a.TS = (int)TS;
@@ -754,8 +807,8 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
   BIST_TRY(lnb(c.act(D.dn, nd * Qd), W.x, 0, 2, D.dts, 1));
 
   // ---- x = x0 + c0 W_o0^T + b_o0
-  const void* a_dx = D.dts;
-  if (bf) { BIST_TRY(cast_copy(D.dts, D.a_dx, nd * Qd, BIST_F32, BIST_BF16, st)); a_dx = D.a_dx; }
+  BIST_TRY(dropout_scale(D.dts, D.a_dx, (int64_t)nd * Q, d, c.drop(S_SELF_OUT, c.p_sub), 0, 0, BIST_F32, adt, st));
+  const void* a_dx = D.a_dx;
   BIST_TRY(lin(c, a_dx, Qd, adt, L.wo0T, nullptr, D.dc, Qd, adt, di, di, 0, nullptr, 0, adt, "bwd_dx_gemm"));  // dc0
   BIST_TRY(wg(a_dx, Qd, d, adt, W.c0, Qd, d, adt, GL.W(0, 3, sdd), GL.b(0, 3, sdd, d), true, di, di, "wgrad_q"));
   {
@@ -765,6 +818,7 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     a.q_b = Lq * 3 * d; a.q_l = 3 * d; a.k_b = Lq * 3 * d; a.k_l = 3 * d; a.c_b = Lq * d; a.c_l = d;
     a.mask = query_mask; a.mask_mod = (int)B; a.m_b = Lq; a.m_l = 0;
     a.Bp = (int)(nd * B); a.Lq = (int)Lq; a.Lk = (int)Lq; a.h = hi; a.dk = dk; a.dtype = adt;
+    a.drop = c.drop(S_SELF_P, c.p_attn);
     BIST_TRY(attn_core_bwd(a, st));
   }
   // dn0 = sum_j dqkv0[:, j-block] . W_j   (three accumulating products against the transposed weights)
@@ -789,6 +843,13 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
     a.dy_dtype = adt; a.x_dtype = BIST_F32; a.dx_dtype = BIST_F32; a.accumulate = 1;
     BIST_TRY(layer_norm_bwd(a, st));
   }
-  (void)in_dir; (void)bf;
+  (void)in_dir; (void)bf; (void)go_dir;
   return 0;
+}
+
+/* The multipliers (0 or 1/(1-p)) that the kernels apply at one dropout site, for tests that inject the same masks into
+ * the oracle.  out fp32 [n]. */
+extern "C" int bist_dropout_mask(uint64_t seed, uint32_t site, float p, int64_t n, float* out, void* stream) {
+  BIST_CHECK_ARG(p >= 0.f && p < 1.f, "dropout_mask: p must be in [0, 1)");
+  return dropout_mask(out, n, make_drop(p, seed, site), (cudaStream_t)stream);
 }

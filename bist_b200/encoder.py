@@ -18,7 +18,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .modules import (LayerNorm, SublayerConnection, clones, _eval_only, _no_dropout, _needs_grad, _ws, _WEIGHT_EPOCH,
+from .modules import (LayerNorm, SublayerConnection, clones, _eval_only, _needs_grad, _ws, _WEIGHT_EPOCH,
                       _reg_hook, weights_updated)
 
 _TORCH_DTYPE = {"fp32": torch.float32, "bf16": torch.bfloat16}
@@ -129,7 +129,7 @@ class _StLayerFn(torch.autograd.Function):
     """VidEncoderLayer4.forward with a backward — bist_st_layer_train_fwd / bist_st_layer_bwd."""
 
     @staticmethod
-    def forward(ctx, layer, vft, handle, box, qm, tm, dir_mask, x_t2s, x_s2t, *params):
+    def forward(ctx, layer, vft, handle, box, qm, tm, dir_mask, dropout, x_t2s, x_s2t, *params):
         B, T, S, d = vft.shape
         d_model, d_ff, h = layer._dims()
         nd = layer._n_dirs()
@@ -144,8 +144,10 @@ class _StLayerFn(torch.autograd.Function):
         eps = float(layer.sublayer[0].norm.eps)
         _lib.check(L.bist_st_layer_train_fwd(_lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft), _lib.ptr(qm), _lib.ptr(tm),
                                              _lib.ptr(packed), _lib.ptr(o_t2s), _lib.ptr(o_s2t), B, T, S, Lq, d, d_ff, h,
-                                             nd, dir_mask, eps, _lib.ptr(tape), tape.numel(), vdt, _lib.stream_ptr()),
+                                             nd, dir_mask, eps, _lib.ptr(tape), tape.numel(), vdt,
+                                             ctypes.byref(dropout) if dropout is not None else None, _lib.stream_ptr()),
                    "bist_st_layer_train_fwd")
+        ctx.dropout = dropout
         ctx.save_for_backward(vft, qm, tm, packed, tape, x_t2s, x_s2t)
         ctx.layer, ctx.box, ctx.dims = layer, box, (B, T, S, Lq, d, d_ff, h, nd, dir_mask, eps, vdt)
         ctx.vft_needs_grad = vft.requires_grad
@@ -174,14 +176,15 @@ class _StLayerFn(torch.autograd.Function):
         _lib.check(L.bist_st_layer_bwd(_lib.ptr(g_t2s), _lib.ptr(g_s2t), _lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft),
                                        _lib.ptr(qm), _lib.ptr(tm), _lib.ptr(packed), _lib.ptr(tape), tape.numel(),
                                        _lib.ptr(d_t2s), _lib.ptr(d_s2t), _lib.ptr(acc), _lib.ptr(grads), B, T, S, Lq, d,
-                                       d_ff, h, nd, dir_mask, eps, _lib.ptr(ws), ws.numel(), vdt, _lib.stream_ptr()),
+                                       d_ff, h, nd, dir_mask, eps, _lib.ptr(ws), ws.numel(), vdt,
+                                       ctypes.byref(ctx.dropout) if ctx.dropout is not None else None, _lib.stream_ptr()),
                    "bist_st_layer_bwd")
         if _reg_hook is None:
             weights_updated()
         pg = tuple(grads[o:o + n].view(p.shape) for (o, n), p in zip(offs, ctx.layer.parameters()))
         g_vft = None if shared or not ctx.vft_needs_grad else acc.to(vft.dtype)
         g_handle = torch.zeros(1, dtype=torch.float32, device=vft.device) if shared else None
-        return (None, g_vft, g_handle, None, None, None, None, d_t2s, d_s2t) + pg
+        return (None, g_vft, g_handle, None, None, None, None, None, d_t2s, d_s2t) + pg
 
 
 class VidEncoder8(nn.Module):
@@ -308,6 +311,19 @@ class VidEncoderLayer4(nn.Module):
         self._packed = (key, buf)
         return buf
 
+    def _dropout_cfg(self):
+        """bist_dropout_t of this call: the three probabilities of the reference's nn.Dropout members (modules.py:40,79,
+        109) and a fresh seed from torch's CPU generator (so torch.manual_seed reproduces a run); None in eval mode."""
+        self.last_dropout = None
+        if not self.training:
+            return None
+        p_sub, p_attn, p_ffn = self.sublayer[0].dropout.p, self.attn[0].dropout.p, self.ff[0].dropout.p
+        if p_sub == 0 and p_attn == 0 and p_ffn == 0:
+            return None
+        cfg = _lib.Dropout(float(p_attn), float(p_sub), float(p_ffn), int(torch.randint(0, 2 ** 62, (1,)).item()))
+        self.last_dropout = cfg            # tests read the seed back to rebuild the masks
+        return cfg
+
     def train_packed_weights(self):
         """Packed weights of the training formulation (both operand orientations), cached per weight version."""
         params = list(self.parameters())
@@ -330,7 +346,6 @@ class VidEncoderLayer4(nn.Module):
 
     # -- forward ------------------------------------------------------------------------------
     def forward(self, in_ft, ft, b):
-        _no_dropout(self, self.sublayer[0].dropout.p, self.attn[0].dropout.p, self.ff[0].dropout.p)
         vft = ft['spatiotemporal_ft']
         _lib.require_cuda(vft, self.attn[0].linears[0].weight)
         run_t2s = (not hasattr(self.args, 't2s')) or bool(self.args.t2s)      # encoder.py:174
@@ -348,14 +363,17 @@ class VidEncoderLayer4(nn.Module):
             raise ValueError("video feature width %d != d_model %d" % (d, d_model))
         nd = self._n_dirs()
         params = list(self.parameters())
-        if _needs_grad(vft, in_ft.get('t2s') if run_t2s else None, in_ft.get('s2t') if run_s2t else None, *params):
+        dropout = self._dropout_cfg()
+        if dropout is not None or _needs_grad(vft, in_ft.get('t2s') if run_t2s else None,
+                                              in_ft.get('s2t') if run_s2t else None, *params):
             x_t2s = in_ft['t2s'].float().contiguous() if run_t2s else None
             x_s2t = in_ft['s2t'].float().contiguous() if run_s2t else None
             Lq = (x_t2s if run_t2s else x_s2t).shape[1]
             qm = _mask_bytes(b.query_mask, B, Lq)
             tm = _mask_bytes(b.temporal_mask, B, T)
             box, handle = getattr(vft, "_bist_box", None), getattr(vft, "_bist_handle", None)
-            outs = list(_StLayerFn.apply(self, vft.contiguous(), handle, box, qm, tm, dir_mask, x_t2s, x_s2t, *params))
+            outs = list(_StLayerFn.apply(self, vft.contiguous(), handle, box, qm, tm, dir_mask, dropout,
+                                         x_t2s, x_s2t, *params))
             if run_t2s:
                 in_ft['t2s'] = outs.pop(0)
             if run_s2t:

@@ -201,6 +201,22 @@ int bist_vidproj_bwd(const float* d_out, const float* fts, const float* act, con
  * Key-projection biases (linears.1.bias of the stage-1 / stage-2 attentions) get exactly zero:
  * their score contribution is constant over the keys and cancels in the softmax.
  */
+/* Dropout of the training forward (model.train()): p_attn on the attention probabilities (modules.py:62-63, fixed 0.1
+ * by mtn.py:77), p_sublayer on every sublayer output (modules.py:44), p_ffn on the FFN hidden layer (modules.py:113).
+ * Masks are counter-based — keep(seed, site, element index in the REFERENCE's tensor at that site) — regenerated by
+ * the backward from the same struct, never stored.  Sites of one layer call (u = slot of the active direction, 0 or 1):
+ *   0 self-attention probabilities [nd*B, h, Lq, Lq]     1 self-attention sublayer output [nd*B*Lq, d]
+ *   2+u stage-1 probabilities [B*G, h, Lq, nk]            4+u stage-1 sublayer output [B*G, Lq, d]
+ *   6+u stage-2 probabilities [B*Lq, h, 1, G]             8 stage-2 sublayer output [nd*B*Lq, d]
+ *   9 FFN hidden [nd*B*Lq, d_ff]                          10 FFN sublayer output [nd*B*Lq, d]
+ * NULL (or all p == 0) = eval mode.  The stream of random numbers differs from torch's; the distribution is the same. */
+typedef struct {
+  float p_attn, p_sublayer, p_ffn;
+  uint64_t seed;
+} bist_dropout_t;
+/* out[i] = multiplier (0 or 1/(1-p)) of element i of `site`, fp32 [n] (tests inject these into the oracle). */
+int bist_dropout_mask(uint64_t seed, uint32_t site, float p, int64_t n, float* out, void* stream);
+
 size_t bist_st_layer_train_packed_bytes(int64_t d, int64_t d_ff, int n_dirs, int dtype);
 int bist_st_layer_train_pack(const bist_st_layer_params_t* host_params, void* packed, size_t packed_bytes,
                              int64_t d, int64_t d_ff, int64_t h, int n_dirs, int dtype, void* stream);
@@ -214,7 +230,7 @@ int bist_st_layer_train_fwd(const float* in_t2s, const float* in_s2t, const void
                             const uint8_t* query_mask, const uint8_t* temporal_mask, const void* packed,
                             float* out_t2s, float* out_s2t, int64_t B, int64_t T, int64_t S, int64_t Lq,
                             int64_t d, int64_t d_ff, int64_t h, int n_dirs, int dir_mask, float eps,
-                            void* tape, size_t tape_bytes, int dtype, void* stream);
+                            void* tape, size_t tape_bytes, int dtype, const bist_dropout_t* dropout, void* stream);
 /*   d_out_*   fp32 [B,Lq,d]  gradients of the layer outputs (separate tensors per direction)
  *   d_in_*    fp32 [B,Lq,d]  gradients of the layer inputs (written, not accumulated)
  *   d_vft     fp32 [B,T,S,d] gradient of ft['spatiotemporal_ft'], ACCUMULATED
@@ -225,7 +241,7 @@ int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t, const floa
                       size_t tape_bytes, float* d_in_t2s, float* d_in_s2t, float* d_vft, float* grads,
                       int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t d_ff, int64_t h,
                       int n_dirs, int dir_mask, float eps, void* ws, size_t ws_bytes, int dtype,
-                      void* stream);
+                      const bist_dropout_t* dropout, void* stream);
 
 /* LayerNorm backward — modules.py:28-31.  dx (dx_dtype) written; da_2/db_2 fp32 accumulated
  * (both may be NULL). */

@@ -62,16 +62,21 @@ def linear(x, w, b=None):
     return y if b is None else y + b
 
 
-def sdp_attention(q, k, v, mask=None):
-    """modules.py:54-64 (dropout is identity in eval).  mask==0 -> score := -1e9."""
+def _apply(drop, site, x):
+    """Dropout site hook: `drop(site, x) -> x'` (training-mode tests inject explicit masks); None = eval mode."""
+    return x if drop is None else drop(site, x)
+
+
+def sdp_attention(q, k, v, mask=None, drop=None, site=None):
+    """modules.py:54-64.  mask==0 -> score := -1e9; dropout on the probabilities (:62-63)."""
     s = q.matmul(k.transpose(-2, -1)) / math.sqrt(q.shape[-1])
     if mask is not None:
         s = s.masked_fill(mask == 0, -1e9)
-    p = torch.softmax(s, dim=-1)
+    p = _apply(drop, site, torch.softmax(s, dim=-1))
     return p.matmul(v), p
 
 
-def mha(P, pre, h, query, key, value, mask=None):
+def mha(P, pre, h, query, key, value, mask=None, drop=None):
     """modules.py:81-100.  P[pre+'linears.{0..3}.{weight,bias}'].  Returns (out, attn)."""
     if mask is not None:
         mask = mask.unsqueeze(1)                                   # :85 same mask for all heads
@@ -84,20 +89,20 @@ def mha(P, pre, h, query, key, value, mask=None):
         return y.view(nb, -1, h, dk).transpose(1, 2)               # :89-91
 
     q, k, v = split(0, query), split(1, key), split(2, value)
-    ctx, p = sdp_attention(q, k, v, mask)                          # :94
+    ctx, p = sdp_attention(q, k, v, mask, drop, pre + "p")         # :94
     ctx = ctx.transpose(1, 2).contiguous().view(nb, -1, h * dk)    # :98-99
     return linear(ctx, P[pre + "linears.3.weight"], P[pre + "linears.3.bias"]), p
 
 
-def ffn(P, pre, x):
-    """modules.py:112-113 (dropout identity)."""
-    hid = torch.relu(linear(x, P[pre + "w_1.weight"], P[pre + "w_1.bias"]))
+def ffn(P, pre, x, drop=None):
+    """modules.py:112-113: w_2(dropout(relu(w_1 x)))."""
+    hid = _apply(drop, pre + "hidden", torch.relu(linear(x, P[pre + "w_1.weight"], P[pre + "w_1.bias"])))
     return linear(hid, P[pre + "w_2.weight"], P[pre + "w_2.bias"])
 
 
-def sublayer(P, pre, x, fn):
-    """modules.py:42-44: x + sublayer(norm(x)); only x is normed."""
-    return x + fn(layer_norm(x, P[pre + "norm.a_2"], P[pre + "norm.b_2"]))
+def sublayer(P, pre, x, fn, drop=None):
+    """modules.py:42-44: x + dropout(sublayer(norm(x))); only x is normed."""
+    return x + _apply(drop, pre + "out", fn(layer_norm(x, P[pre + "norm.a_2"], P[pre + "norm.b_2"])))
 
 
 # ----------------------------------------------------------------------------- a1
@@ -117,7 +122,7 @@ def vid_encoder8(P, pre, fts, audio_fts=None, no_w_audio=False):
 
 
 # ----------------------------------------------------------------------------- a3 / a4
-def temporal2spatial(P, pre, h, x, vft, temporal_mask, ai, fi, si):
+def temporal2spatial(P, pre, h, x, vft, temporal_mask, ai, fi, si, drop=None):
     """encoder.py:109-139.  x [B,Lq,d]; vft [B,T,S,d]; temporal_mask [B,1,T] bool.
 
     ai/fi/si = indices of the first attn / ff / sublayer clone used (reference keeps
@@ -129,37 +134,37 @@ def temporal2spatial(P, pre, h, x, vft, temporal_mask, ai, fi, si):
     xe = x.unsqueeze(1).expand(B, S, Lq, d).reshape(B * S, Lq, d)                  # :114-115
     me = temporal_mask.unsqueeze(1).expand(B, S, 1, T).reshape(B * S, 1, T)        # :117-119
     t_out = sublayer(P, f"{pre}sublayer.{si}.", xe,
-                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, me)[0])    # :121
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, me, drop)[0], drop)    # :121
     kv2 = t_out.reshape(B, S, Lq, d).permute(0, 2, 1, 3).reshape(B * Lq, S, d)     # :125-126
     x1 = x.reshape(B * Lq, 1, d)                                                   # :128
     ts = sublayer(P, f"{pre}sublayer.{si + 1}.", x1,
-                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, None)[0])  # :130
+                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, None, drop)[0], drop)  # :130
     ts = ts.reshape(B, Lq, d)                                                      # :134
     return sublayer(P, f"{pre}sublayer.{si + 2}.", ts,
-                    lambda z: ffn(P, f"{pre}ff.{fi}.", z))                         # :135
+                    lambda z: ffn(P, f"{pre}ff.{fi}.", z, drop), drop)             # :135
 
 
-def spatial2temporal(P, pre, h, x, vft, temporal_mask, ai, fi, si):
+def spatial2temporal(P, pre, h, x, vft, temporal_mask, ai, fi, si, drop=None):
     """encoder.py:141-170 (mirror order: over S per clip without mask, then over T with mask)."""
     B, T, S, d = vft.shape
     Lq = x.shape[1]
     kv = vft.reshape(B * T, S, d)                                                  # :143
     xe = x.unsqueeze(1).expand(B, T, Lq, d).reshape(B * T, Lq, d)                  # :145-146
     s_out = sublayer(P, f"{pre}sublayer.{si}.", xe,
-                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, None)[0])  # :148
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, kv, kv, None, drop)[0], drop)  # :148
     kv2 = s_out.reshape(B, T, Lq, d).permute(0, 2, 1, 3).reshape(B * Lq, T, d)     # :152-153
     x1 = x.reshape(B * Lq, 1, d)                                                   # :155
     me = temporal_mask.unsqueeze(1).expand(B, Lq, 1, T).reshape(B * Lq, 1, T)      # :157-159
     st = sublayer(P, f"{pre}sublayer.{si + 1}.", x1,
-                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, me)[0])  # :161
+                  lambda z: mha(P, f"{pre}attn.{ai + 1}.", h, z, kv2, kv2, me, drop)[0], drop)  # :161
     st = st.reshape(B, Lq, d)                                                      # :165
     return sublayer(P, f"{pre}sublayer.{si + 2}.", st,
-                    lambda z: ffn(P, f"{pre}ff.{fi}.", z))                         # :166
+                    lambda z: ffn(P, f"{pre}ff.{fi}.", z, drop), drop)             # :166
 
 
 # ----------------------------------------------------------------------------- a2
 def vid_encoder_layer4(P, pre, h, in_t2s, in_s2t, vft, query_mask, temporal_mask,
-                       t2s=True, s2t=True):
+                       t2s=True, s2t=True, drop=None):
     """encoder.py:172-201 with enc_st_combine == 'none'.  Returns (t2s_out, s2t_out).
 
     Clone indexing follows the reference cursors: with both directions on, t2s uses
@@ -170,21 +175,21 @@ def vid_encoder_layer4(P, pre, h, in_t2s, in_s2t, vft, query_mask, temporal_mask
     o_t2s, o_s2t = in_t2s, in_s2t
     if t2s:
         x = sublayer(P, f"{pre}sublayer.{si}.", in_t2s,
-                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, z, z, query_mask)[0])  # :176
-        o_t2s = temporal2spatial(P, pre, h, x, vft, temporal_mask, ai + 1, fi, si + 1)  # :179
+                     lambda z: mha(P, f"{pre}attn.{ai}.", h, z, z, z, query_mask, drop)[0], drop)  # :176
+        o_t2s = temporal2spatial(P, pre, h, x, vft, temporal_mask, ai + 1, fi, si + 1, drop)  # :179
         ai, fi, si = ai + 3, fi + 1, si + 4
     if s2t:
         a0, f0, s0 = ai, fi, si
         x = sublayer(P, f"{pre}sublayer.{s0}.", in_s2t,
-                     lambda z: mha(P, f"{pre}attn.{a0}.", h, z, z, z, query_mask)[0])  # :184
-        o_s2t = spatial2temporal(P, pre, h, x, vft, temporal_mask, a0 + 1, f0, s0 + 1)  # :187
+                     lambda z: mha(P, f"{pre}attn.{a0}.", h, z, z, z, query_mask, drop)[0], drop)  # :184
+        o_s2t = spatial2temporal(P, pre, h, x, vft, temporal_mask, a0 + 1, f0, s0 + 1, drop)  # :187
     return o_t2s, o_s2t
 
 
 # ----------------------------------------------------------------------------- a1 + L x a2 + a10
 def video_path(P, h, fts, encoded_query, query_mask, temporal_mask, n_blocks,
                t2s=True, s2t=True,
-               enc_pre="vid_encoder.", dec_pre="mutlimodal_decoder."):
+               enc_pre="vid_encoder.", dec_pre="mutlimodal_decoder.", drop=None):
     """The slice of MTN.forward that is the hot path (mtn.py:49-51, decoder.py:107-129).
 
     Returns dict(spatiotemporal_ft, t2s, s2t, temporal_ft, spatial_ft) where t2s/s2t are
@@ -197,7 +202,7 @@ def video_path(P, h, fts, encoded_query, query_mask, temporal_mask, n_blocks,
     for blk in range(n_blocks):
         cur_t2s, cur_s2t = vid_encoder_layer4(
             P, f"{dec_pre}v_layers.{blk}.", h, cur_t2s, cur_s2t, vft,
-            query_mask, temporal_mask, t2s=t2s, s2t=s2t)                           # decoder.py:116
+            query_mask, temporal_mask, t2s=t2s, s2t=s2t, drop=drop)                # decoder.py:116
     out["t2s"], out["s2t"] = cur_t2s, cur_s2t
     if s2t:
         out["temporal_ft"] = layer_norm(cur_s2t, P[dec_pre + "temporal_out_norm.a_2"],

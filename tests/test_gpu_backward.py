@@ -168,3 +168,108 @@ def test_optimizer_step_refreshes_packed_weights():
     for k in ("temporal_ft", "spatial_ft"):
         assert O.norm_err(got_inf[k], want[k]) < 1e-6, k
         assert O.norm_err(got_train[k], want[k]) < 1e-5, k
+
+
+# ----------------------------------------------------------------------------------------------- dropout (train mode)
+def _site_map(layer_pre, u, B, Lq, h, d, d_ff):
+    """reference dropout site (oracle name) -> (library site id, flat offset inside that site) for direction slot u."""
+    Q = B * Lq
+    return {
+        f"{layer_pre}attn.{3 * u}.p": (0, u * B * h * Lq * Lq),
+        f"{layer_pre}sublayer.{4 * u}.out": (1, u * Q * d),
+        f"{layer_pre}attn.{3 * u + 1}.p": (2 + u, 0),
+        f"{layer_pre}sublayer.{4 * u + 1}.out": (4 + u, 0),
+        f"{layer_pre}attn.{3 * u + 2}.p": (6 + u, 0),
+        f"{layer_pre}sublayer.{4 * u + 2}.out": (8, u * Q * d),
+        f"{layer_pre}ff.{u}.hidden": (9, u * Q * d_ff),
+        f"{layer_pre}sublayer.{4 * u + 3}.out": (10, u * Q * d),
+    }
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("c", [
+    dict(seed=211, B=3, T=5, S=4, D=48, d=64, h=4, Lq=5, n_blocks=2, t2s=1, s2t=1),
+    dict(seed=212, B=2, T=6, S=16, D=128, d=128, h=8, Lq=7, n_blocks=1, t2s=1, s2t=1),
+], ids=lambda c: "seed%d" % c["seed"])
+def test_train_mode_dropout_matches_oracle_with_the_same_masks(c, precision):
+    """model.train() with dropout 0.2 / attention dropout 0.1 (exec.sh:35, mtn.py:77): the kernels' counter-based masks
+    are read back through bist_dropout_mask and injected into the oracle, so forward AND gradients must agree."""
+    import ctypes
+    p_sub, p_attn = 0.2, 0.1
+    P = synth.make_params(c["seed"], c["d"], c["D"], c["n_blocks"])
+    b = synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"])
+    eq = synth.make_encoded_query(c["seed"], c["B"], c["Lq"], c["d"])
+    m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=p_sub, precision=precision).to(DEV)
+    m.load_state_dict(P, strict=True)
+    m.train()
+    torch.manual_seed(1234)
+    eqd = eq.to(DEV).requires_grad_(True)
+    out = m(b.to(DEV), eqd)
+    (out["temporal_ft"].float() * _loss_weights(11, out["temporal_ft"].shape).to(DEV)).sum().add(
+        (out["spatial_ft"].float() * _loss_weights(12, out["spatial_ft"].shape).to(DEV)).sum()).backward()
+    torch.cuda.synchronize()
+
+    d_ff = 4 * c["d"]
+    table, cache = {}, {}
+    for blk, layer in enumerate(m.mutlimodal_decoder.v_layers):
+        cfg = layer.last_dropout
+        assert cfg is not None and abs(cfg.p_attn - p_attn) < 1e-7 and abs(cfg.p_sublayer - p_sub) < 1e-7
+        for u in range(2):
+            for name, (site, off) in _site_map(f"mutlimodal_decoder.v_layers.{blk}.", u, c["B"], c["Lq"], c["h"], c["d"], d_ff).items():
+                p = p_attn if name.endswith(".p") else p_sub
+                table[name] = (int(cfg.seed), site, off, p)
+
+    def drop(name, x):
+        seed, site, off, p = table[name]
+        n = off + x.numel()
+        key = (seed, site, n)
+        if key not in cache:
+            buf = torch.empty(n, dtype=torch.float32, device=DEV)
+            _lib.check(_lib.lib().bist_dropout_mask(seed, site, p, n, _lib.ptr(buf), _lib.stream_ptr()), "bist_dropout_mask")
+            cache[key] = buf.cpu()
+        mul = cache[key][off:off + x.numel()].view(x.shape)
+        frac = float((mul == 0).float().mean())
+        assert abs(frac - p) < 0.08, (name, frac)             # the masks drop about p of the elements
+        return x * mul
+
+    Pg = {k: v.clone().requires_grad_(True) for k, v in P.items()}
+    eqg = eq.clone().requires_grad_(True)
+    ref = O.video_path(Pg, c["h"], b.fts, eqg, b.query_mask, b.temporal_mask, c["n_blocks"], drop=drop)
+    ((ref["temporal_ft"] * _loss_weights(11, ref["temporal_ft"].shape)).sum()
+     + (ref["spatial_ft"] * _loss_weights(12, ref["spatial_ft"].shape)).sum()).backward()
+    for k in ("temporal_ft", "spatial_ft"):
+        assert O.norm_err(out[k].float(), ref[k]) < TOL_FWD[precision], (precision, k)
+    with torch.no_grad():                                    # and dropout really changed the result
+        assert O.norm_err(ref["temporal_ft"], O.video_path(P, c["h"], b.fts, eq, b.query_mask, b.temporal_mask,
+                                                           c["n_blocks"])["temporal_ft"]) > 1e-2
+    if precision == "fp32":
+        for name, prm in m.named_parameters():
+            r = Pg[name].grad
+            scale = max(float(g.abs().max()) for g in (v.grad for v in Pg.values()) if g is not None)
+            if float(r.abs().max()) < 1e-6 * scale:
+                assert float(prm.grad.abs().max()) <= 1e-5 * scale, name
+                continue
+            assert O.norm_err(prm.grad, r) < 1e-4, (name, O.norm_err(prm.grad, r))
+        assert O.norm_err(eqd.grad, eqg.grad) < 1e-4
+    else:
+        scale = max(float(v.grad.abs().max()) for v in Pg.values() if v.grad is not None)
+        for name, prm in m.named_parameters():
+            r = Pg[name].grad
+            if float(r.abs().max()) < 1e-6 * scale:          # key biases: mathematically zero
+                continue
+            l2 = float((prm.grad.float().cpu() - r).norm() / r.norm())
+            assert l2 < (TOL_BWD_L2_RELU if any(t in name for t in RELU_ADJACENT) else TOL_BWD_L2), (name, l2)
+
+
+def test_train_mode_dropout_is_seeded_by_torch():
+    c = dict(seed=213, B=2, T=4, S=3, D=40, d=32, h=4, Lq=3, n_blocks=1)
+    m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.3, precision="fp32").to(DEV)
+    m.load_state_dict(synth.make_params(c["seed"], c["d"], c["D"], c["n_blocks"]), strict=True)
+    m.train().requires_grad_(False)
+    b = synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"]).to(DEV)
+    eq = synth.make_encoded_query(c["seed"], c["B"], c["Lq"], c["d"]).to(DEV)
+    torch.manual_seed(7); a1 = m(b, eq)["temporal_ft"].clone()
+    torch.manual_seed(7); a2 = m(b, eq)["temporal_ft"].clone()
+    a3 = m(b, eq)["temporal_ft"].clone()
+    assert torch.equal(a1, a2) and not torch.equal(a1, a3)
+    assert torch.equal(m.eval()(b, eq)["temporal_ft"], m(b, eq)["temporal_ft"])      # eval mode: no dropout

@@ -166,5 +166,6 @@ def test_errors_are_loud():
     ft["spatiotemporal_ft"] = ft["spatiotemporal_ft"].to(torch.bfloat16)
     with pytest.raises(TypeError):
         m.mutlimodal_decoder.v_layers[0]({"t2s": eq, "s2t": eq}, ft, b)
-    with pytest.raises(NotImplementedError):
-        m.train()(b, eq)
+    # a non-CUDA input is an error, never a CPU fallback
+    with pytest.raises(RuntimeError):
+        m(synth.make_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"]), eq.cpu())
