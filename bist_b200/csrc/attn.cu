@@ -210,7 +210,64 @@ __global__ void pack_kernel(const float* __restrict__ src, TD* __restrict__ dst,
   dst[i] = from_f32<TD>(v * scale);
 }
 
+struct PackTable {
+  PackItem it[kMaxPackItems];
+  int n;
+};
+
+// grid = total 32x32 destination tiles over all items; block (32, 8).  Both directions of the copy are coalesced
+// (transposes go through a padded shared-memory tile).
+template <typename TD>
+__global__ void __launch_bounds__(256) pack_many_kernel(const __grid_constant__ PackTable tab, TD* __restrict__ base, float* __restrict__ fbase) {
+  __shared__ float tile[32][33];
+  pdl_trigger();
+  pdl_wait();
+  int i = 0;
+  while (i + 1 < tab.n && (int)blockIdx.x >= tab.it[i + 1].tile_begin) ++i;
+  const PackItem& p = tab.it[i];
+  const int t = blockIdx.x - p.tile_begin;
+  const int tiles_c = (p.cols + 31) / 32;
+  const int r0 = (t / tiles_c) * 32, c0 = (t % tiles_c) * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  if (p.transpose) {  // src is [cols, rows]: read rows c0.. of src (contiguous in r), write rows r0.. of dst (contiguous in c)
+    for (int j = ty; j < 32; j += 8)
+      if (c0 + j < p.cols && r0 + tx < p.rows) tile[j][tx] = p.src[(long long)(c0 + j) * p.rows + r0 + tx];
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8)
+      if (r0 + j < p.rows && c0 + tx < p.cols) {
+        const float v = tile[tx][j] * p.scale;
+        const long long o = p.dst_off + (long long)(r0 + j) * p.cols + c0 + tx;
+        if (p.to_f32) fbase[o] = v; else base[o] = from_f32<TD>(v);
+      }
+  } else {
+    for (int j = ty; j < 32; j += 8)
+      if (r0 + j < p.rows && c0 + tx < p.cols) {
+        const float v = p.src[(long long)(r0 + j) * p.cols + c0 + tx] * p.scale;
+        const long long o = p.dst_off + (long long)(r0 + j) * p.cols + c0 + tx;
+        if (p.to_f32) fbase[o] = v; else base[o] = from_f32<TD>(v);
+      }
+  }
+}
+
 }  // namespace
+
+int pack_many(const PackItem* items, int n, void* base, float* f32_base, int dtype, cudaStream_t st) {
+  BIST_CHECK_ARG(items && n > 0 && n <= kMaxPackItems && base && f32_base, "pack_many: bad argument");
+  PackTable tab;
+  tab.n = n;
+  int tiles = 0;
+  for (int i = 0; i < n; ++i) {
+    tab.it[i] = items[i];
+    BIST_CHECK_ARG(items[i].src && items[i].rows > 0 && items[i].cols > 0, "pack_many: bad item");
+    tab.it[i].tile_begin = tiles;
+    tiles += ((items[i].rows + 31) / 32) * ((items[i].cols + 31) / 32);
+  }
+  ProfScope ps("pack", st);
+  if (dtype == BIST_BF16) BIST_LAUNCH(pack_many_kernel<__nv_bfloat16>, dim3((unsigned)tiles), dim3(32, 8), 0, st, tab, (__nv_bfloat16*)base, f32_base);
+  else BIST_LAUNCH(pack_many_kernel<float>, dim3((unsigned)tiles), dim3(32, 8), 0, st, tab, (float*)base, f32_base);
+  BIST_LAUNCHED();
+  return 0;
+}
 
 int softmax_pv(const SoftmaxPvArgs& a, cudaStream_t st) {
   BIST_CHECK_ARG(a.S && a.V && a.ctx, "softmax_pv: null pointer");

@@ -281,6 +281,11 @@ int launch_wgrad_mma(const WgradArgs& w, cudaStream_t st) {
 
 int wgrad(const WgradArgs& w, cudaStream_t st) {
   BIST_CHECK_ARG(w.A && w.B && w.C && w.M > 0 && w.N > 0 && w.K > 0 && w.Z > 0 && w.Z <= 65535, "wgrad: bad argument");
+  {
+    bool taken = false;
+    int rc = wgrad_tc(w, st, &taken);
+    if (taken) return rc;
+  }
   static const bool no_mma = getenv("BIST_DISABLE_TC") != nullptr;
   // tensor-core path: bf16 A, bf16 or fp32 B, 16-byte aligned 8-element chunks everywhere
   auto al = [](long long v, int esz) { return (v * esz) % 16 == 0; };
@@ -411,18 +416,25 @@ __device__ __forceinline__ int64_t ref_row(int64_t r, int perm_L, int perm_G) {
   return (b * perm_G + g) * perm_L + l;
 }
 
+// Four consecutive elements per thread (d % 4 == 0): one row/column split and one vector access per four hashes.
 template <typename T>
 __global__ void dropout_add_kernel(T* __restrict__ out, const float* __restrict__ res, int64_t rows, int d, int64_t res_div,
                                    DropCfg drop, int perm_L, int perm_G, int64_t row0) {
   pdl_trigger();
   pdl_wait();
-  const int64_t total = rows * d;
+  const int d4 = d >> 2;
+  const int64_t total = rows * d4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / d;
-    const int c = (int)(i % d);
-    float v = to_f32(out[i]) * drop_mul(drop, (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c));
-    if (res) v += res[(r / res_div) * d + c];
-    out[i] = from_f32<T>(v);
+    const int64_t r = i / d4;
+    const int c = (int)(i - r * d4) * 4;
+    const unsigned long long ib = (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c);
+    float4 v = ld4(out + r * d + c);
+    v.x *= drop_mul(drop, ib); v.y *= drop_mul(drop, ib + 1); v.z *= drop_mul(drop, ib + 2); v.w *= drop_mul(drop, ib + 3);
+    if (res) {
+      const float4 x = ld4(res + (r / res_div) * d + c);
+      v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+    }
+    st4(out + r * d + c, v);
   }
 }
 
@@ -431,11 +443,17 @@ __global__ void dropout_scale_kernel(const TS* __restrict__ src, TD* __restrict_
                                      int perm_G, int64_t row0) {
   pdl_trigger();
   pdl_wait();
-  const int64_t total = rows * d;
+  const int d4 = d >> 2;
+  const int64_t total = rows * d4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / d;
-    const int c = (int)(i % d);
-    dst[i] = from_f32<TD>(to_f32(src[i]) * drop_mul(drop, (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c)));
+    const int64_t r = i / d4;
+    const int c = (int)(i - r * d4) * 4;
+    float4 v = ld4(src + r * d + c);
+    if (drop.thresh != 0u) {
+      const unsigned long long ib = (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c);
+      v.x *= drop_mul(drop, ib); v.y *= drop_mul(drop, ib + 1); v.z *= drop_mul(drop, ib + 2); v.w *= drop_mul(drop, ib + 3);
+    }
+    st4(dst + r * d + c, v);
   }
 }
 
@@ -545,19 +563,23 @@ int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st, fl
 
 int dropout_add(void* out, const float* res, int64_t rows, int64_t d, int64_t res_div, const DropCfg& drop, int perm_L, int perm_G,
                 int out_dtype, cudaStream_t st, int64_t row0) {
-  BIST_CHECK_ARG(out && rows > 0 && d > 0 && res_div > 0, "dropout_add: bad argument");
+  BIST_CHECK_ARG(out && rows > 0 && d > 0 && d % 4 == 0 && res_div > 0, "dropout_add: bad argument (d %% 4 == 0)");
+  BIST_CHECK_ARG(((uintptr_t)out % 16 == 0 || (out_dtype == BIST_BF16 && (uintptr_t)out % 8 == 0)) && (!res || (uintptr_t)res % 16 == 0),
+                 "dropout_add: misaligned pointer");
   ProfScope ps("dropout", st);
-  if (out_dtype == BIST_BF16) BIST_LAUNCH(dropout_add_kernel<__nv_bfloat16>, ew_grid(rows * d), 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
-  else BIST_LAUNCH(dropout_add_kernel<float>, ew_grid(rows * d), 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  if (out_dtype == BIST_BF16) BIST_LAUNCH(dropout_add_kernel<__nv_bfloat16>, ew_grid(rows * d / 4), 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  else BIST_LAUNCH(dropout_add_kernel<float>, ew_grid(rows * d / 4), 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
   BIST_LAUNCHED();
   return 0;
 }
 
 int dropout_scale(const void* src, void* dst, int64_t rows, int64_t d, const DropCfg& drop, int perm_L, int perm_G, int src_dtype,
                   int dst_dtype, cudaStream_t st, int64_t row0) {
-  BIST_CHECK_ARG(src && dst && rows > 0 && d > 0, "dropout_scale: bad argument");
+  BIST_CHECK_ARG(src && dst && rows > 0 && d > 0 && d % 4 == 0, "dropout_scale: bad argument (d %% 4 == 0)");
+  BIST_CHECK_ARG((uintptr_t)src % 8 == 0 && (uintptr_t)dst % 8 == 0 && (src_dtype == BIST_BF16 || (uintptr_t)src % 16 == 0) &&
+                     (dst_dtype == BIST_BF16 || (uintptr_t)dst % 16 == 0), "dropout_scale: misaligned pointer");
   ProfScope ps("dropout", st);
-  const unsigned g = ew_grid(rows * d);
+  const unsigned g = ew_grid(rows * d / 4);
   const int di = (int)d;
   if (src_dtype == BIST_F32 && dst_dtype == BIST_BF16) BIST_LAUNCH((dropout_scale_kernel<float, __nv_bfloat16>), g, 256, 0, st, (const float*)src, (__nv_bfloat16*)dst, rows, di, drop, perm_L, perm_G, row0);
   else if (src_dtype == BIST_F32) BIST_LAUNCH((dropout_scale_kernel<float, float>), g, 256, 0, st, (const float*)src, (float*)dst, rows, di, drop, perm_L, perm_G, row0);

@@ -283,6 +283,19 @@ int stage2_v2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, 
 // [rows, cols] dense of dst_dtype, src fp32 dense.
 int pack_matrix(const float* src, void* dst, int rows, int cols, int transpose, float scale,
                 int dst_dtype, cudaStream_t st);
+// Many pack_matrix calls as ONE launch (weights are re-packed after every optimizer step): item i writes
+// dst_i[r, c] = scale_i * (transpose_i ? src_i[c, r] : src_i[r, c]) with dst_i = (to_f32_i ? f32_base : base of dtype) + dst_off_i.
+struct PackItem {
+  const float* src;
+  long long dst_off;   // element offset from the destination base
+  int rows, cols;      // of the destination
+  int transpose;
+  int to_f32;          // destination is the fp32 vector section
+  float scale;
+  int tile_begin;      // filled in by pack_many
+};
+constexpr int kMaxPackItems = 72;
+int pack_many(const PackItem* items, int n, void* base, float* f32_base, int dtype, cudaStream_t st);
 
 }  // namespace bist
 
@@ -309,6 +322,7 @@ struct WgradArgs {
   const char* tag = "wgrad";
 };
 int wgrad(const WgradArgs& w, cudaStream_t st);
+int wgrad_tc(const WgradArgs& w, cudaStream_t st, bool* taken);  // tcgen05 path (wgrad_tc.cu)
 
 // LayerNorm backward (modules.py:28-31: unbiased std, eps on the std).
 //   dx = [accumulate ? dx : 0] + dLN(dy; x)         (optionally gated by x > 0: the ReLU in front of in_norm)

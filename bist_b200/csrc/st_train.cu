@@ -217,63 +217,64 @@ int bist_st_layer_train_pack(const bist_st_layer_params_t* P, void* packed, size
   BIST_CHECK_ARG(d % 4 == 0 && dff % 4 == 0, "train_pack: d and d_ff must be multiples of 4");
   const TrainLayout L = train_layout(d, dff, n_dirs, dtype);
   if (packed_bytes < L.total_bytes) { set_error("train_pack: buffer too small"); return BIST_ERR_WORKSPACE; }
-  const size_t e = dtype_size(dtype), dd = (size_t)d * d;
-  char* mat = (char*)packed;
+  const size_t dd = (size_t)d * d;
   float* fs = (float*)((char*)packed + L.f_byte_off);
   const float rs = 1.f / sqrtf((float)(d / h));
   const int di = (int)d, fi = (int)dff;
-  auto M = [&](size_t off) { return (void*)(mat + off * e); };
-  for (int u = 0; u < n_dirs; ++u) {
+  for (int u = 0; u < n_dirs; ++u) {   // one launch per direction (the item table travels as a kernel argument)
     const int ab = 3 * u;
     for (int i = 0; i < 3; ++i)
       for (int j = 0; j < 4; ++j) BIST_CHECK_ARG(P->attn_w[ab + i][j] && P->attn_b[ab + i][j], "train_pack: null attn parameter");
     BIST_CHECK_ARG(P->ff_w1[u] && P->ff_b1[u] && P->ff_w2[u] && P->ff_b2[u], "train_pack: null ff parameter");
+    for (int i = 0; i < 4; ++i) BIST_CHECK_ARG(P->ln_a[4 * u + i] && P->ln_b[4 * u + i], "train_pack: null norm parameter");
     const size_t mb = u * L.dir_stride, fb = u * L.fdir_stride;
-    auto V = [&](const float* src, size_t off, int n) { return pack_matrix(src, fs + off, 1, n, 0, 1.f, BIST_F32, st); };
-    // both orientations of a [rows, cols] weight: dst = W, dstT = W^T
+    PackItem items[kMaxPackItems];
+    int n = 0;
+    // dst [rows, cols] at matrix offset `off`: W (transpose = 0, src [rows, cols]) or W^T (transpose = 1, src [cols, rows])
+    auto Mx = [&](const float* src, size_t off, int rows, int cols, int transpose, float scale) {
+      items[n++] = PackItem{src, (long long)off, rows, cols, transpose, 0, scale, 0};
+    };
+    auto V = [&](const float* src, size_t off, int len) { items[n++] = PackItem{src, (long long)off, 1, len, 0, 1, 1.f, 0}; };
     auto both = [&](const float* src, size_t off, size_t offT, int rows, int cols) {
-      BIST_TRY(pack_matrix(src, M(mb + off), rows, cols, 0, 1.f, dtype, st));
-      return pack_matrix(src, M(mb + offT), cols, rows, 1, 1.f, dtype, st);
+      Mx(src, mb + off, rows, cols, 0, 1.f);
+      Mx(src, mb + offT, cols, rows, 1, 1.f);
     };
     for (int j = 0; j < 3; ++j) {
-      BIST_TRY(pack_matrix(P->attn_w[ab][j], M(mb + L.wqkv0 + j * dd), di, di, 0, 1.f, dtype, st));
-      BIST_TRY(V(P->attn_b[ab][j], fb + L.bqkv0 + (size_t)j * d, di));
+      Mx(P->attn_w[ab][j], mb + L.wqkv0 + j * dd, di, di, 0, 1.f);
+      // W_j^T of the self-attention q/k/v projections: dn0 = sum_j dqkv0[:, j-th block] . W_j runs as three accumulating products
+      Mx(P->attn_w[ab][j], mb + L.wqkv0T + j * dd, di, di, 1, 1.f);
+      V(P->attn_b[ab][j], fb + L.bqkv0 + (size_t)j * d, di);
     }
-    BIST_TRY(both(P->attn_w[ab][3], L.wo0, L.wo0T, di, di));
-    BIST_TRY(V(P->attn_b[ab][3], fb + L.bo0, di));
-    BIST_TRY(both(P->attn_w[ab + 1][0], L.wq12, L.wq12T, di, di));
-    BIST_TRY(both(P->attn_w[ab + 2][0], L.wq12 + dd, L.wq12T + dd, di, di));
-    BIST_TRY(V(P->attn_b[ab + 1][0], fb + L.bq12, di));
-    BIST_TRY(V(P->attn_b[ab + 2][0], fb + L.bq12 + d, di));
+    both(P->attn_w[ab][3], L.wo0, L.wo0T, di, di);
+    V(P->attn_b[ab][3], fb + L.bo0, di);
+    both(P->attn_w[ab + 1][0], L.wq12, L.wq12T, di, di);
+    both(P->attn_w[ab + 2][0], L.wq12 + dd, L.wq12T + dd, di, di);
+    V(P->attn_b[ab + 1][0], fb + L.bq12, di);
+    V(P->attn_b[ab + 2][0], fb + L.bq12 + d, di);
     // key folds: forward operand (W_k)^T / sqrt(dk), backward operand W_k / sqrt(dk)
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][1], M(mb + L.wkt12), di, di, 1, rs, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 2][1], M(mb + L.wkt12 + dd), di, di, 1, rs, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][1], M(mb + L.wks12), di, di, 0, rs, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 2][1], M(mb + L.wks12 + dd), di, di, 0, rs, dtype, st));
-    BIST_TRY(both(P->attn_w[ab + 2][2], L.wv2, L.wv2T, di, di));
-    BIST_TRY(V(P->attn_b[ab + 2][2], fb + L.bv2, di));
-    BIST_TRY(both(P->attn_w[ab + 1][3], L.wo1, L.wo1T, di, di));
-    BIST_TRY(V(P->attn_b[ab + 1][3], fb + L.bo1, di));
-    BIST_TRY(both(P->attn_w[ab + 2][3], L.wo2, L.wo2T, di, di));
-    BIST_TRY(V(P->attn_b[ab + 2][3], fb + L.bo2, di));
-    BIST_TRY(both(P->ff_w1[u], L.w1, L.w1T, fi, di));
-    BIST_TRY(both(P->ff_w2[u], L.w2, L.w2T, di, fi));
-    BIST_TRY(V(P->ff_b1[u], fb + L.b1, fi));
-    BIST_TRY(V(P->ff_b2[u], fb + L.b2, di));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][2], M(L.wv1 + (size_t)u * dd), di, di, 0, 1.f, dtype, st));
-    BIST_TRY(pack_matrix(P->attn_w[ab + 1][2], M(L.wv1T + (size_t)u * dd), di, di, 1, 1.f, dtype, st));
-    BIST_TRY(V(P->attn_b[ab + 1][2], L.bv1 + (size_t)u * d, di));
+    Mx(P->attn_w[ab + 1][1], mb + L.wkt12, di, di, 1, rs);
+    Mx(P->attn_w[ab + 2][1], mb + L.wkt12 + dd, di, di, 1, rs);
+    Mx(P->attn_w[ab + 1][1], mb + L.wks12, di, di, 0, rs);
+    Mx(P->attn_w[ab + 2][1], mb + L.wks12 + dd, di, di, 0, rs);
+    both(P->attn_w[ab + 2][2], L.wv2, L.wv2T, di, di);
+    V(P->attn_b[ab + 2][2], fb + L.bv2, di);
+    both(P->attn_w[ab + 1][3], L.wo1, L.wo1T, di, di);
+    V(P->attn_b[ab + 1][3], fb + L.bo1, di);
+    both(P->attn_w[ab + 2][3], L.wo2, L.wo2T, di, di);
+    V(P->attn_b[ab + 2][3], fb + L.bo2, di);
+    both(P->ff_w1[u], L.w1, L.w1T, fi, di);
+    both(P->ff_w2[u], L.w2, L.w2T, di, fi);
+    V(P->ff_b1[u], fb + L.b1, fi);
+    V(P->ff_b2[u], fb + L.b2, di);
+    Mx(P->attn_w[ab + 1][2], L.wv1 + (size_t)u * dd, di, di, 0, 1.f);
+    Mx(P->attn_w[ab + 1][2], L.wv1T + (size_t)u * dd, di, di, 1, 1.f);
+    V(P->attn_b[ab + 1][2], L.bv1 + (size_t)u * d, di);
     for (int i = 0; i < 4; ++i) {
-      BIST_CHECK_ARG(P->ln_a[4 * u + i] && P->ln_b[4 * u + i], "train_pack: null norm parameter");
-      BIST_TRY(V(P->ln_a[4 * u + i], fb + L.ln_a + (size_t)i * d, di));
-      BIST_TRY(V(P->ln_b[4 * u + i], fb + L.ln_b + (size_t)i * d, di));
+      V(P->ln_a[4 * u + i], fb + L.ln_a + (size_t)i * d, di);
+      V(P->ln_b[4 * u + i], fb + L.ln_b + (size_t)i * d, di);
     }
+    BIST_TRY(pack_many(items, n, packed, fs, dtype, st));
   }
-  // W_j^T of the self-attention q/k/v projections as three [d, d] blocks: dn0 = sum_j dqkv0[:, j-th block] . W_j runs as
-  // three accumulating products.
-  for (int u = 0; u < n_dirs; ++u)
-    for (int j = 0; j < 3; ++j)
-      BIST_TRY(pack_matrix(P->attn_w[3 * u][j], M(u * L.dir_stride + L.wqkv0T + j * dd), di, di, 1, 1.f, dtype, st));
   return 0;
 }
 

@@ -9,16 +9,18 @@ ap.add_argument("--precision", default="bf16")
 ap.add_argument("--steps", type=int, default=10)
 ap.add_argument("--B", type=int, default=64)
 ap.add_argument("--no-adam", action="store_true")
+ap.add_argument("--dropout", type=float, default=0.1)
 a = ap.parse_args()
 c = dict(B=a.B, T=40, S=16, D=2048, d=512, h=8, Lq=16, n_blocks=3)
 dev = torch.device("cuda:0")
 L = _lib.lib()
-m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.0, precision=a.precision).to(dev)
+m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=a.dropout, precision=a.precision).to(dev)
 m.load_state_dict(synth.make_params(0, c["d"], c["D"], c["n_blocks"]), strict=True)
 m.train()
-for mod in m.modules():
-    if isinstance(mod, torch.nn.Dropout):
-        mod.p = 0.0
+if a.dropout == 0:
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.Dropout):
+            mod.p = 0.0
 b = synth.make_batch(1, c["B"], c["T"], c["S"], c["D"], c["Lq"]).to(dev)
 eq = synth.make_encoded_query(1, c["B"], c["Lq"], c["d"]).to(dev)
 tgt = torch.randn(c["B"], c["Lq"], c["d"], device=dev)
@@ -43,7 +45,7 @@ for _ in range(a.steps):
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / a.steps
-print("train step %.3f ms  -> %.0f turns/s (%s, B=%d)" % (ms, c["B"] / ms * 1e3, a.precision, c["B"]))
+print("train step %.3f ms  -> %.0f turns/s (%s, B=%d, dropout %.2f)" % (ms, c["B"] / ms * 1e3, a.precision, c["B"], a.dropout))
 # phases
 def t(fn, n=5):
     torch.cuda.synchronize(); e0.record()
