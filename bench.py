@@ -304,9 +304,9 @@ def run_ours(args):
     train = None
     if not args.no_train:
         from bist_b200.dist import allreduce_grads
-        tm = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.0, precision=args.precision).to(dev)
+        tm = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.1, precision=args.precision).to(dev)
         tm.load_state_dict(synth.make_params(0, c["d"], c["D"], c["n_blocks"]), strict=True)
-        tm.eval()                                        # dropout identity (dropout kernels are not built yet)
+        tm.train()                                       # dropout on: 0.1 sublayer/FFN (train_configs.py:34), 0.1 attention (mtn.py:77)
         opt = torch.optim.Adam(tm.parameters(), lr=1e-4, fused=True)
         tgt = torch.randn(c["B"], c["Lq"], c["d"], device=dev)
         plist = list(tm.parameters())
@@ -329,7 +329,7 @@ def run_ours(args):
                  "ms_per_step": tms, "gpu_launches_per_step": (L.bist_launch_count() - n0) // tsteps,
                  "collectives_per_step": ncoll[0],
                  "what": "video path only (projection + 3 blocks + out norms): forward with tape, MSE loss, backward "
-                         "through libbist_b200, gradient all-reduce (NCCL, N>1), fused Adam; dropout off; the rest of "
+                         "through libbist_b200, gradient all-reduce (NCCL, N>1), fused Adam; train() mode, dropout 0.1; the rest of "
                          "the BiST model (text encoders, decoder, generator, label-smoothed loss) is not built"}
         del tm, opt
 

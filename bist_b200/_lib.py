@@ -63,9 +63,10 @@ SIGNATURES = {
                                 c_i64, c_i64, c_i64, c_i64, c_i64, c_i64, c_i64,
                                 c_i, c_i, c_f, c_p, c_sz, c_i, c_p]),
     # training step
-    "bist_vidproj_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_f, c_i, c_i, c_p]),
+    "bist_vidproj_tape_bytes": (c_sz, [c_i64, c_i64, c_i64, c_i]),
+    "bist_vidproj_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_i64, c_i64, c_i64, c_f, c_i, c_i, c_p]),
     "bist_vidproj_bwd_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64, c_i]),
-    "bist_vidproj_bwd": (c_i, [c_p] * 8 + [c_i64, c_i64, c_i64, c_f, c_p, c_sz, c_i, c_p]),
+    "bist_vidproj_bwd": (c_i, [c_p, c_p, c_p, c_sz] + [c_p] * 5 + [c_i64, c_i64, c_i64, c_f, c_p, c_sz, c_i, c_p]),
     "bist_st_layer_train_packed_bytes": (c_sz, [c_i64, c_i64, c_i, c_i]),
     "bist_st_layer_train_pack": (c_i, [ctypes.POINTER(StLayerParams), c_p, c_sz, c_i64, c_i64, c_i64, c_i, c_i, c_p]),
     "bist_st_layer_grad_elems": (c_sz, [c_i64, c_i64, c_i]),

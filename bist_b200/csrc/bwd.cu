@@ -263,7 +263,7 @@ template <typename TB>
 int launch_wgrad_mma(const WgradArgs& w, cudaStream_t st) {
   const int tiles_n = (w.N + WM_TN - 1) / WM_TN, tiles_k = (w.K + WM_TK - 1) / WM_TK;
   const long long base = (long long)tiles_n * tiles_k * w.Z;
-  long long splits = (2LL * num_sms_cached() + base - 1) / base;
+  long long splits = (1LL * num_sms_cached() + base - 1) / base;   // every split costs a full tile of reductions
   const long long max_splits = (w.M + 2 * WM_R - 1) / (2 * WM_R);
   splits = splits < 1 ? 1 : (splits > max_splits ? max_splits : splits);
   if (splits > 65535) splits = 65535;
@@ -409,51 +409,53 @@ __global__ void relu_gate_kernel(T* __restrict__ dy, const T* __restrict__ y, in
   }
 }
 
-__device__ __forceinline__ int64_t ref_row(int64_t r, int perm_L, int perm_G) {
+// Index arithmetic in 32 bits whenever the tensor has fewer than 2^31 elements (64-bit division costs ~100 instructions).
+template <typename I>
+__device__ __forceinline__ I ref_row(I r, int perm_L, int perm_G) {
   if (perm_L <= 0) return r;
-  const int64_t g = r % perm_G, bl = r / perm_G;
-  const int64_t l = bl % perm_L, b = bl / perm_L;
-  return (b * perm_G + g) * perm_L + l;
+  const I g = r % (I)perm_G, bl = r / (I)perm_G;
+  const I l = bl % (I)perm_L, b = bl / (I)perm_L;
+  return (b * (I)perm_G + g) * (I)perm_L + l;
 }
 
 // Four consecutive elements per thread (d % 4 == 0): one row/column split and one vector access per four hashes.
-template <typename T>
+template <typename T, typename I>
 __global__ void dropout_add_kernel(T* __restrict__ out, const float* __restrict__ res, int64_t rows, int d, int64_t res_div,
                                    DropCfg drop, int perm_L, int perm_G, int64_t row0) {
   pdl_trigger();
   pdl_wait();
-  const int d4 = d >> 2;
-  const int64_t total = rows * d4;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / d4;
+  const I d4 = (I)(d >> 2);
+  const I total = (I)rows * d4;
+  for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+    const I r = i / d4;
     const int c = (int)(i - r * d4) * 4;
-    const unsigned long long ib = (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c);
-    float4 v = ld4(out + r * d + c);
+    const unsigned long long ib = (unsigned long long)((int64_t)(ref_row<I>(r, perm_L, perm_G)) + row0) * d + c;
+    float4 v = ld4(out + (int64_t)r * d + c);
     v.x *= drop_mul(drop, ib); v.y *= drop_mul(drop, ib + 1); v.z *= drop_mul(drop, ib + 2); v.w *= drop_mul(drop, ib + 3);
     if (res) {
-      const float4 x = ld4(res + (r / res_div) * d + c);
+      const float4 x = ld4(res + (int64_t)(r / (I)res_div) * d + c);
       v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
     }
-    st4(out + r * d + c, v);
+    st4(out + (int64_t)r * d + c, v);
   }
 }
 
-template <typename TS, typename TD>
+template <typename TS, typename TD, typename I>
 __global__ void dropout_scale_kernel(const TS* __restrict__ src, TD* __restrict__ dst, int64_t rows, int d, DropCfg drop, int perm_L,
                                      int perm_G, int64_t row0) {
   pdl_trigger();
   pdl_wait();
-  const int d4 = d >> 2;
-  const int64_t total = rows * d4;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / d4;
+  const I d4 = (I)(d >> 2);
+  const I total = (I)rows * d4;
+  for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+    const I r = i / d4;
     const int c = (int)(i - r * d4) * 4;
-    float4 v = ld4(src + r * d + c);
+    float4 v = ld4(src + (int64_t)r * d + c);
     if (drop.thresh != 0u) {
-      const unsigned long long ib = (unsigned long long)((ref_row(r, perm_L, perm_G) + row0) * d + c);
+      const unsigned long long ib = (unsigned long long)((int64_t)(ref_row<I>(r, perm_L, perm_G)) + row0) * d + c;
       v.x *= drop_mul(drop, ib); v.y *= drop_mul(drop, ib + 1); v.z *= drop_mul(drop, ib + 2); v.w *= drop_mul(drop, ib + 3);
     }
-    st4(dst + r * d + c, v);
+    st4(dst + (int64_t)r * d + c, v);
   }
 }
 
@@ -567,8 +569,15 @@ int dropout_add(void* out, const float* res, int64_t rows, int64_t d, int64_t re
   BIST_CHECK_ARG(((uintptr_t)out % 16 == 0 || (out_dtype == BIST_BF16 && (uintptr_t)out % 8 == 0)) && (!res || (uintptr_t)res % 16 == 0),
                  "dropout_add: misaligned pointer");
   ProfScope ps("dropout", st);
-  if (out_dtype == BIST_BF16) BIST_LAUNCH(dropout_add_kernel<__nv_bfloat16>, ew_grid(rows * d / 4), 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
-  else BIST_LAUNCH(dropout_add_kernel<float>, ew_grid(rows * d / 4), 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  const bool small = rows * d < (1LL << 31) - (1LL << 24);
+  const unsigned grid = ew_grid(rows * d / 4);
+  if (out_dtype == BIST_BF16) {
+    if (small) BIST_LAUNCH((dropout_add_kernel<__nv_bfloat16, uint32_t>), grid, 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+    else BIST_LAUNCH((dropout_add_kernel<__nv_bfloat16, int64_t>), grid, 256, 0, st, (__nv_bfloat16*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  } else {
+    if (small) BIST_LAUNCH((dropout_add_kernel<float, uint32_t>), grid, 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+    else BIST_LAUNCH((dropout_add_kernel<float, int64_t>), grid, 256, 0, st, (float*)out, res, rows, (int)d, res_div, drop, perm_L, perm_G, row0);
+  }
   BIST_LAUNCHED();
   return 0;
 }
@@ -581,10 +590,17 @@ int dropout_scale(const void* src, void* dst, int64_t rows, int64_t d, const Dro
   ProfScope ps("dropout", st);
   const unsigned g = ew_grid(rows * d / 4);
   const int di = (int)d;
-  if (src_dtype == BIST_F32 && dst_dtype == BIST_BF16) BIST_LAUNCH((dropout_scale_kernel<float, __nv_bfloat16>), g, 256, 0, st, (const float*)src, (__nv_bfloat16*)dst, rows, di, drop, perm_L, perm_G, row0);
-  else if (src_dtype == BIST_F32) BIST_LAUNCH((dropout_scale_kernel<float, float>), g, 256, 0, st, (const float*)src, (float*)dst, rows, di, drop, perm_L, perm_G, row0);
-  else if (dst_dtype == BIST_BF16) BIST_LAUNCH((dropout_scale_kernel<__nv_bfloat16, __nv_bfloat16>), g, 256, 0, st, (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, rows, di, drop, perm_L, perm_G, row0);
-  else BIST_LAUNCH((dropout_scale_kernel<__nv_bfloat16, float>), g, 256, 0, st, (const __nv_bfloat16*)src, (float*)dst, rows, di, drop, perm_L, perm_G, row0);
+  const bool small = rows * d < (1LL << 31) - (1LL << 24);
+#define BIST_DS(TS_, TD_)                                                                                                               \
+  do {                                                                                                                                  \
+    if (small) BIST_LAUNCH((dropout_scale_kernel<TS_, TD_, uint32_t>), g, 256, 0, st, (const TS_*)src, (TD_*)dst, rows, di, drop, perm_L, perm_G, row0); \
+    else BIST_LAUNCH((dropout_scale_kernel<TS_, TD_, int64_t>), g, 256, 0, st, (const TS_*)src, (TD_*)dst, rows, di, drop, perm_L, perm_G, row0);        \
+  } while (0)
+  if (src_dtype == BIST_F32 && dst_dtype == BIST_BF16) BIST_DS(float, __nv_bfloat16);
+  else if (src_dtype == BIST_F32) BIST_DS(float, float);
+  else if (dst_dtype == BIST_BF16) BIST_DS(__nv_bfloat16, __nv_bfloat16);
+  else BIST_DS(__nv_bfloat16, float);
+#undef BIST_DS
   BIST_LAUNCHED();
   return 0;
 }

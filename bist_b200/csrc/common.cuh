@@ -155,12 +155,16 @@ static inline DropCfg make_drop(float p, unsigned long long seed, uint32_t site)
   return c;
 }
 #ifdef __CUDACC__
+// 32-bit avalanche mixer ("lowbias32"): a handful of integer instructions per element instead of 64-bit multiplies.
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du;
+  x ^= x >> 15; x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
 __host__ __device__ __forceinline__ uint32_t drop_hash(unsigned long long seed, uint32_t site, unsigned long long idx) {
-  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (idx + 1ull) + ((unsigned long long)site << 52);
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z ^= z >> 31;
-  return (uint32_t)(z >> 32);
+  const uint32_t key = mix32((uint32_t)(seed >> 32) + (uint32_t)(idx >> 32) * 0x9E3779B9u + site * 0x85EBCA6Bu) ^ (uint32_t)seed;
+  return mix32((uint32_t)idx ^ key);
 }
 // multiplier of element idx: 0 (dropped) or 1/(1-p)
 __device__ __forceinline__ float drop_mul(const DropCfg& c, unsigned long long idx) {

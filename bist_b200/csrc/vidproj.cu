@@ -49,23 +49,56 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
 }
 
 
-/* Training forward: same result as bist_vidproj_fwd, and the post-ReLU activations h = relu(fts W^T + b) are kept as
- * fp32 [N, d] in `act` (caller-owned) for the backward (the LayerNorm cannot be inverted through a bf16 output). */
+/* Tape of the training forward: h = relu(fts W^T + b) as fp32 [N, d] (the LayerNorm cannot be inverted through a bf16
+ * output) and, in bf16 mode, bf16 copies of fts [N, D] and W [d, D]: the forward contraction and the weight gradient
+ * dW = dh^T fts both read the 2-byte copy (168 MB instead of 335 MB at config 2) on the tcgen05 kernels. */
+namespace {
+struct VpTape {
+  float* act;
+  void* fts16;
+  void* w16;
+  size_t bytes;
+  bool ok;
+};
+VpTape vp_tape(void* base, size_t cap, int64_t N, int64_t D, int64_t d, int compute_dtype) {
+  Arena A(base, cap);
+  VpTape t;
+  t.act = (float*)A.take((size_t)N * d * 4);
+  t.fts16 = compute_dtype == BIST_BF16 ? A.take((size_t)N * D * 2) : nullptr;
+  t.w16 = compute_dtype == BIST_BF16 ? A.take((size_t)d * D * 2) : nullptr;
+  t.bytes = A.used + 256;
+  t.ok = A.ok;
+  return t;
+}
+}  // namespace
+
+size_t bist_vidproj_tape_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype) {
+  if (N <= 0 || D <= 0 || d <= 0 || !dtype_ok(compute_dtype)) return 0;
+  return vp_tape(nullptr, (size_t)-1, N, D, d, compute_dtype).bytes;
+}
+
 int bist_vidproj_train_fwd(const float* fts, const float* W, const float* bias, const float* a_2, const float* b_2,
-                           void* out, float* act, int64_t N, int64_t D, int64_t d, float eps, int compute_dtype,
-                           int out_dtype, void* stream) {
+                           void* out, void* tape, size_t tape_bytes, int64_t N, int64_t D, int64_t d, float eps,
+                           int compute_dtype, int out_dtype, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  BIST_CHECK_ARG(fts && W && bias && a_2 && b_2 && out && act, "vidproj_train: null pointer");
+  BIST_CHECK_ARG(fts && W && bias && a_2 && b_2 && out && tape, "vidproj_train: null pointer");
   BIST_CHECK_ARG(N > 0 && D > 0 && d > 1 && N < (1LL << 31), "vidproj_train: bad shape");
   BIST_CHECK_ARG(dtype_ok(compute_dtype) && dtype_ok(out_dtype), "vidproj_train: bad dtype");
-  GemmArgs g;  // encoder.py:75 — relu(W fts + b); bf16 mode multiplies the fp32 operands as tf32 on the tensor cores
-  g.A = fts; g.W = W; g.C = act; g.bias = bias;
+  const VpTape T = vp_tape(tape, tape_bytes, N, D, d, compute_dtype);
+  if (!T.ok) { set_error("vidproj_train: tape too small (%zu bytes)", tape_bytes); return BIST_ERR_WORKSPACE; }
+  GemmArgs g;  // encoder.py:75 — relu(W fts + b)
+  g.A = fts; g.W = W; g.C = T.act; g.bias = bias;
   g.M = (int)N; g.N = (int)d; g.K = (int)D;
   g.a = rows_dense(D); g.w = rows_dense(D); g.c = rows_dense(d);
   g.relu = 1; g.tag = "vidproj_gemm";
-  g.allow_tf32 = compute_dtype == BIST_BF16;
+  if (compute_dtype == BIST_BF16) {
+    if (D % 4 == 0) BIST_TRY(dropout_scale(fts, T.fts16, N, D, DropCfg(), 0, 0, BIST_F32, BIST_BF16, st));  // vectorised cast
+    else BIST_TRY(cast_copy(fts, T.fts16, N * D, BIST_F32, BIST_BF16, st));
+    BIST_TRY(pack_matrix(W, T.w16, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
+    g.A = T.fts16; g.W = T.w16; g.a_dtype = BIST_BF16; g.w_dtype = BIST_BF16;
+  }
   BIST_TRY(gemm(g, st));
-  return layer_norm(act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                  // :80
+  return layer_norm(T.act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                // :80
 }
 
 size_t bist_vidproj_bwd_workspace_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype) {
@@ -75,25 +108,27 @@ size_t bist_vidproj_bwd_workspace_bytes(int64_t N, int64_t D, int64_t d, int com
 
 /* Backward of LayerNorm(relu(fts W^T + b)) w.r.t. W, bias, a_2, b_2 (fts is data: no gradient).
  *   d_out fp32 [N, d] (gradient of the projected video tensor, accumulated over blocks and directions);
- *   act = the tape of bist_vidproj_train_fwd; dW [d, D], dbias, da_2, db_2 fp32, accumulated (+=). */
-int bist_vidproj_bwd(const float* d_out, const float* fts, const float* act, const float* a_2, float* dW, float* dbias,
-                     float* da_2, float* db_2, int64_t N, int64_t D, int64_t d, float eps, void* ws, size_t ws_bytes,
-                     int compute_dtype, void* stream) {
+ *   tape = what bist_vidproj_train_fwd wrote; dW [d, D], dbias, da_2, db_2 fp32, accumulated (+=). */
+int bist_vidproj_bwd(const float* d_out, const float* fts, const void* tape, size_t tape_bytes, const float* a_2, float* dW,
+                     float* dbias, float* da_2, float* db_2, int64_t N, int64_t D, int64_t d, float eps, void* ws,
+                     size_t ws_bytes, int compute_dtype, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  BIST_CHECK_ARG(d_out && fts && act && a_2 && dW && dbias && da_2 && db_2 && ws, "vidproj_bwd: null pointer");
+  BIST_CHECK_ARG(d_out && fts && tape && a_2 && dW && dbias && da_2 && db_2 && ws, "vidproj_bwd: null pointer");
   BIST_CHECK_ARG(N > 0 && D > 0 && d > 1 && N < (1LL << 31) && dtype_ok(compute_dtype), "vidproj_bwd: bad argument");
+  const VpTape T = vp_tape(const_cast<void*>(tape), tape_bytes, N, D, d, compute_dtype);
+  if (!T.ok) { set_error("vidproj_bwd: tape too small (%zu bytes)", tape_bytes); return BIST_ERR_WORKSPACE; }
   Arena A(ws, ws_bytes);
   void* dh = A.take((size_t)N * d * dtype_size(compute_dtype));
   if (!A.ok) { set_error("vidproj_bwd: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
   LnBwdArgs l;  // dh = relu'(h) * dLN(d_out; h)
-  l.dy = d_out; l.x = act; l.a2 = a_2; l.dx = dh; l.da = da_2; l.db = db_2;
+  l.dy = d_out; l.x = T.act; l.a2 = a_2; l.dx = dh; l.da = da_2; l.db = db_2;
   l.rows = N; l.d = d; l.eps = eps;
   l.dy_dtype = BIST_F32; l.x_dtype = BIST_F32; l.dx_dtype = compute_dtype; l.relu_gate = 1;
   BIST_TRY(layer_norm_bwd(l, st));
   WgradArgs w;  // dW += dh^T fts ; dbias += colsum(dh)
-  w.A = dh; w.B = fts; w.C = dW; w.colsum = dbias;
+  w.A = dh; w.B = compute_dtype == BIST_BF16 ? T.fts16 : (const void*)fts; w.C = dW; w.colsum = dbias;
   w.M = (int)N; w.N = (int)d; w.K = (int)D; w.lda = d; w.ldb = D; w.ldc = D;
-  w.a_dtype = compute_dtype; w.b_dtype = BIST_F32; w.tag = "wgrad_vidproj";
+  w.a_dtype = compute_dtype; w.b_dtype = compute_dtype; w.tag = "wgrad_vidproj";
   return wgrad(w, st);
 }
 

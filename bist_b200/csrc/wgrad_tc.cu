@@ -144,20 +144,35 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
   }
 }
 
-// colsum[z][n] += sum_m A[z][m,n]   (bias gradients); bf16 A, N % 8 == 0, N / 8 <= 256
+// colsum[z][n] += sum_m A[z][m,n]   (bias gradients); bf16 A, N % 8 == 0, N / 8 <= 256.  grid (row chunks, Z).
 __global__ void __launch_bounds__(256) colsum_kernel(WgradArgs w, int rows_per_cta) {
-  __shared__ float red[256][8];
+  __shared__ float red[256][9];
   pdl_trigger();
   pdl_wait();
   const int z = blockIdx.y;
   const int ncg = w.N / 8, rl = 256 / ncg;  // column groups, row lanes
   const int cg = threadIdx.x % ncg, lane_r = threadIdx.x / ncg;
-  const __nv_bfloat16* A = reinterpret_cast<const __nv_bfloat16*>(w.A) + w.az.off(z, w.zin, 1);
+  const __nv_bfloat16* A = reinterpret_cast<const __nv_bfloat16*>(w.A) + w.az.off(z, w.zin, 1) + cg * 8;
   const int m0 = blockIdx.x * rows_per_cta, m1 = min(w.M, m0 + rows_per_cta);
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  if (lane_r < rl)
-    for (int m = m0 + lane_r; m < m1; m += rl) {
-      const uint4 u = *reinterpret_cast<const uint4*>(A + (long long)m * w.lda + cg * 8);
+  if (lane_r < rl) {
+    int m = m0 + lane_r;
+    for (; m + 3 * rl < m1; m += 4 * rl) {  // four independent 16-byte loads in flight
+      uint4 u[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) u[q] = *reinterpret_cast<const uint4*>(A + (long long)(m + q * rl) * w.lda);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u[q]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = __bfloat1622float2(p[j]);
+          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+        }
+      }
+    }
+    for (; m < m1; m += rl) {
+      const uint4 u = *reinterpret_cast<const uint4*>(A + (long long)m * w.lda);
       const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -165,6 +180,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(WgradArgs w, int rows_per_c
         acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
       }
     }
+  }
 #pragma unroll
   for (int j = 0; j < 8; ++j) red[threadIdx.x][j] = acc[j];
   __syncthreads();
@@ -213,7 +229,10 @@ int wgrad_tc(const WgradArgs& w, cudaStream_t st, bool* taken) {
   static const bool disabled = getenv("BIST_DISABLE_TC") != nullptr || getenv("BIST_DISABLE_WGRAD_TC") != nullptr;
   if (disabled) return 0;
   if (w.a_dtype != BIST_BF16 || w.b_dtype != BIST_BF16) return 0;
-  if (w.M % WT_R != 0 || w.M < 4 * WT_R || w.N < 16 || w.K < 64 || w.N % 8 != 0 || w.K % 8 != 0) return 0;
+  if (w.M % WT_R != 0 || w.M < 8 * WT_R || w.N < 16 || w.K < 64 || w.N % 8 != 0 || w.K % 8 != 0) return 0;
+  // small products are launch/latency-bound: the lighter mma.sync kernel (one launch, fused bias sums) wins there
+  static const long long min_macs = getenv("BIST_WGRAD_TC_MIN") ? atoll(getenv("BIST_WGRAD_TC_MIN")) : (1LL << 31);
+  if ((long long)w.M * w.N * w.K * w.Z < min_macs) return 0;
   if ((w.lda * 2) % 16 || (w.ldb * 2) % 16 || ((uintptr_t)w.A % 16) || ((uintptr_t)w.B % 16)) return 0;
   if (w.colsum && (w.N / 8 > 256)) return 0;
   bool ok = true;
@@ -248,7 +267,7 @@ int wgrad_tc(const WgradArgs& w, cudaStream_t st, bool* taken) {
   const long long ctas = items * t.splits;
   if (ctas > 0x7fffffffLL) { *taken = false; return 0; }
   if (w.colsum) {
-    const int rows_per_cta = 512;
+    const int rows_per_cta = 128;
     ProfScope ps("colsum", st);
     BIST_LAUNCH(colsum_kernel, dim3((unsigned)((w.M + rows_per_cta - 1) / rows_per_cta), (unsigned)w.Z), 256, 0, st, w, rows_per_cta);
     BIST_LAUNCHED();

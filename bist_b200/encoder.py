@@ -65,32 +65,34 @@ class _VidProjFn(torch.autograd.Function):
         N = fts.numel() // D
         cdt = _lib.BF16 if precision == "bf16" else _lib.F32
         out = torch.empty(fts.shape[:-1] + (d,), dtype=_TORCH_DTYPE[precision], device=fts.device)
-        act = torch.empty((N, d), dtype=torch.float32, device=fts.device)
-        _lib.check(_lib.lib().bist_vidproj_train_fwd(_lib.ptr(fts), _lib.ptr(W), _lib.ptr(bias), _lib.ptr(a_2),
-                                                     _lib.ptr(b_2), _lib.ptr(out), _lib.ptr(act), N, D, d, float(eps),
-                                                     cdt, cdt, _lib.stream_ptr()), "bist_vidproj_train_fwd")
+        L = _lib.lib()
+        tape = _ws(L.bist_vidproj_tape_bytes(N, D, d, cdt), fts.device)
+        _lib.check(L.bist_vidproj_train_fwd(_lib.ptr(fts), _lib.ptr(W), _lib.ptr(bias), _lib.ptr(a_2), _lib.ptr(b_2),
+                                            _lib.ptr(out), _lib.ptr(tape), tape.numel(), N, D, d, float(eps), cdt, cdt,
+                                            _lib.stream_ptr()), "bist_vidproj_train_fwd")
         handle = torch.zeros(1, dtype=torch.float32, device=fts.device)
-        ctx.save_for_backward(fts, act, a_2, W)
+        ctx.save_for_backward(fts, tape, a_2, W)
+        ctx.N = N
         ctx.box, ctx.eps, ctx.cdt = box, float(eps), cdt
         ctx.set_materialize_grads(False)
         return out, handle
 
     @staticmethod
     def backward(ctx, g_out, g_handle):
-        fts, act, a_2, W = ctx.saved_tensors
+        fts, tape, a_2, W = ctx.saved_tensors
+        d, D = W.shape
+        N = ctx.N
         acc = ctx.box.acc
         ctx.box.acc = None
         if g_out is not None:                       # some other consumer differentiated the tensor directly
-            acc = g_out.float().reshape(act.shape) if acc is None else acc.add_(g_out.float().reshape(acc.shape))
+            acc = g_out.float().reshape(N, d) if acc is None else acc.add_(g_out.float().reshape(acc.shape))
         if acc is None:
             return (None,) * 8
-        d, D = W.shape
-        N = act.shape[0]
         dW = torch.zeros_like(W)
         vec = torch.zeros((3, d), dtype=torch.float32, device=W.device)
         L = _lib.lib()
         ws = _ws(L.bist_vidproj_bwd_workspace_bytes(N, D, d, ctx.cdt), W.device)
-        _lib.check(L.bist_vidproj_bwd(_lib.ptr(acc), _lib.ptr(fts), _lib.ptr(act), _lib.ptr(a_2), _lib.ptr(dW),
+        _lib.check(L.bist_vidproj_bwd(_lib.ptr(acc), _lib.ptr(fts), _lib.ptr(tape), tape.numel(), _lib.ptr(a_2), _lib.ptr(dW),
                                       _lib.ptr(vec[0]), _lib.ptr(vec[1]), _lib.ptr(vec[2]), N, D, d, ctx.eps,
                                       _lib.ptr(ws), ws.numel(), ctx.cdt, _lib.stream_ptr()), "bist_vidproj_bwd")
         return None, dW, vec[0], vec[1], vec[2], None, None, None

@@ -173,17 +173,20 @@ int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const void* vft,
  * gradient).  Parity is against torch.autograd over the oracle (tests/test_gpu_backward.py).
  * ======================================================================================= */
 
-/* VidEncoder8.forward for training — encoder.py:72-80.  Same output as bist_vidproj_fwd;
- * `act` fp32 [N, d] receives relu(fts W^T + b) and is the tape of bist_vidproj_bwd. */
+/* VidEncoder8.forward for training — encoder.py:72-80.  Same output as bist_vidproj_fwd; `tape`
+ * (bist_vidproj_tape_bytes) receives relu(fts W^T + b) as fp32 [N, d] and, in bf16 mode, bf16
+ * copies of fts and W that the forward contraction and the weight gradient both read. */
+size_t bist_vidproj_tape_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype);
 int bist_vidproj_train_fwd(const float* fts, const float* W, const float* bias, const float* a_2,
-                           const float* b_2, void* out, float* act, int64_t N, int64_t D, int64_t d,
-                           float eps, int compute_dtype, int out_dtype, void* stream);
+                           const float* b_2, void* out, void* tape, size_t tape_bytes, int64_t N, int64_t D,
+                           int64_t d, float eps, int compute_dtype, int out_dtype, void* stream);
 size_t bist_vidproj_bwd_workspace_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype);
 /*   d_out fp32 [N, d]: gradient w.r.t. ft['spatiotemporal_ft'] (summed over blocks/directions);
  *   dW [d, D], dbias [d], da_2 [d], db_2 [d] fp32, accumulated.  fts is data: no gradient. */
-int bist_vidproj_bwd(const float* d_out, const float* fts, const float* act, const float* a_2,
-                     float* dW, float* dbias, float* da_2, float* db_2, int64_t N, int64_t D, int64_t d,
-                     float eps, void* ws, size_t ws_bytes, int compute_dtype, void* stream);
+int bist_vidproj_bwd(const float* d_out, const float* fts, const void* tape, size_t tape_bytes,
+                     const float* a_2, float* dW, float* dbias, float* da_2, float* db_2, int64_t N,
+                     int64_t D, int64_t d, float eps, void* ws, size_t ws_bytes, int compute_dtype,
+                     void* stream);
 
 /* VidEncoderLayer4 for training — encoder.py:172-201 (+ :109-170), enc_st_combine == 'none'.
  *
