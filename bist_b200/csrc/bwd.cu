@@ -362,6 +362,107 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(LnBwdArgs a, int rows_per_c
   }
 }
 
+// d % 4 == 0, d <= 128 * MAXV: a row lives in registers (one vector load of x and dy per lane and column group), and the
+// lane keeps the gain/offset gradients of its own columns in registers over all rows of the warp.
+template <typename TDY, typename TX, typename TDX, int MAXV>
+__global__ void __launch_bounds__(256) ln_bwd_vec_kernel(LnBwdArgs a, int rows_per_cta, int ctas_per_group) {
+  extern __shared__ float sacc[];  // [2][d]
+  pdl_trigger();
+  pdl_wait();
+  const int d = (int)a.d, nv = d >> 2;
+  const int grp = blockIdx.x / ctas_per_group, cg = blockIdx.x % ctas_per_group;
+  const int64_t grows = a.group_rows > 0 ? a.group_rows : a.rows;
+  const int64_t r_begin = grp * grows + (int64_t)cg * rows_per_cta;
+  const int64_t r_end = min(grp * grows + grows, r_begin + rows_per_cta);
+  const bool want_p = a.da != nullptr;
+  if (want_p)
+    for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float* a2 = a.a2 + grp * a.pstride;
+  float4 ga[MAXV], pa[MAXV], pb[MAXV];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = lane + i * 32;
+    ga[i] = c < nv ? *reinterpret_cast<const float4*>(a2 + c * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    pa[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    pb[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int64_t r = r_begin + warp; r < r_end; r += 8) {
+    const TX* x = reinterpret_cast<const TX*>(a.x) + r * d;
+    const TDY* dy = reinterpret_cast<const TDY*>(a.dy) + r * d;
+    float4 xv[MAXV], gv[MAXV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        xv[i] = ld4(x + c * 4);
+        gv[i] = ld4(dy + c * 4);
+        s += (xv[i].x + xv[i].y) + (xv[i].z + xv[i].w);
+      }
+    }
+    const float mu = warp_sum(s) / (float)d;
+    float ss = 0.f, sg = 0.f, sgc = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        const float c0 = xv[i].x - mu, c1 = xv[i].y - mu, c2 = xv[i].z - mu, c3 = xv[i].w - mu;
+        const float g0 = gv[i].x * ga[i].x, g1 = gv[i].y * ga[i].y, g2 = gv[i].z * ga[i].z, g3 = gv[i].w * ga[i].w;
+        ss += (c0 * c0 + c1 * c1) + (c2 * c2 + c3 * c3);
+        sg += (g0 + g1) + (g2 + g3);
+        sgc += (g0 * c0 + g1 * c1) + (g2 * c2 + g3 * c3);
+      }
+    }
+    ss = warp_sum(ss); sg = warp_sum(sg); sgc = warp_sum(sgc);
+    const float sd = sqrtf(ss / (float)(d - 1));
+    const float rinv = 1.f / (sd + a.eps);
+    const float mg = sg / (float)d;
+    const float k2 = sd > 0.f ? rinv * rinv * sgc / ((float)(d - 1) * sd) : 0.f;
+    TDX* dx = reinterpret_cast<TDX*>(a.dx) + r * d;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        const float c0 = xv[i].x - mu, c1 = xv[i].y - mu, c2 = xv[i].z - mu, c3 = xv[i].w - mu;
+        float4 v = make_float4(rinv * (gv[i].x * ga[i].x - mg) - k2 * c0, rinv * (gv[i].y * ga[i].y - mg) - k2 * c1,
+                               rinv * (gv[i].z * ga[i].z - mg) - k2 * c2, rinv * (gv[i].w * ga[i].w - mg) - k2 * c3);
+        if (a.relu_gate) {
+          if (!(xv[i].x > 0.f)) v.x = 0.f;
+          if (!(xv[i].y > 0.f)) v.y = 0.f;
+          if (!(xv[i].z > 0.f)) v.z = 0.f;
+          if (!(xv[i].w > 0.f)) v.w = 0.f;
+        }
+        if (a.accumulate) {
+          const float4 o = ld4(dx + c * 4);
+          v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+        }
+        st4(dx + c * 4, v);
+        pa[i].x += gv[i].x * c0 * rinv; pa[i].y += gv[i].y * c1 * rinv; pa[i].z += gv[i].z * c2 * rinv; pa[i].w += gv[i].w * c3 * rinv;
+        pb[i].x += gv[i].x; pb[i].y += gv[i].y; pb[i].z += gv[i].z; pb[i].w += gv[i].w;
+      }
+    }
+  }
+  if (want_p) {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = (lane + i * 32) * 4;
+      if (c < d) {
+        atomicAdd(&sacc[c], pa[i].x); atomicAdd(&sacc[c + 1], pa[i].y); atomicAdd(&sacc[c + 2], pa[i].z); atomicAdd(&sacc[c + 3], pa[i].w);
+        atomicAdd(&sacc[d + c], pb[i].x); atomicAdd(&sacc[d + c + 1], pb[i].y); atomicAdd(&sacc[d + c + 2], pb[i].z); atomicAdd(&sacc[d + c + 3], pb[i].w);
+      }
+    }
+    __syncthreads();
+    float* da = a.da + grp * a.gstride;
+    float* db = a.db + grp * a.gstride;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+      atomicAdd(da + i, sacc[i]);
+      atomicAdd(db + i, sacc[d + i]);
+    }
+  }
+}
+
 template <typename TDY, typename TX, typename TDX>
 int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
   const int64_t grows = a.group_rows > 0 ? a.group_rows : a.rows;
@@ -369,9 +470,15 @@ int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
   // enough CTAs to fill the machine, at least 8 rows (one per warp) each
   int64_t per = (a.rows + 4LL * num_sms_cached() - 1) / (4LL * num_sms_cached());
   per = per < 8 ? 8 : (per + 7) / 8 * 8;
+  const bool vec = a.d % 4 == 0 && a.d <= 512 && ((uintptr_t)a.x % 16 == 0) && ((uintptr_t)a.dy % 16 == 0) && ((uintptr_t)a.dx % 16 == 0) &&
+                   ((uintptr_t)a.a2 % 16 == 0) && a.pstride % 4 == 0;
+  if (vec && per < 32) per = 32;   // four rows per warp: the per-lane gradient sums amortise their atomics
   const int64_t cpg = (grows + per - 1) / per;
   ProfScope ps("ln_bwd", st);
-  BIST_LAUNCH((ln_bwd_kernel<TDY, TX, TDX>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
+  if (vec)
+    BIST_LAUNCH((ln_bwd_vec_kernel<TDY, TX, TDX, 4>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
+  else
+    BIST_LAUNCH((ln_bwd_kernel<TDY, TX, TDX>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
   BIST_LAUNCHED();
   return 0;
 }

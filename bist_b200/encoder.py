@@ -10,6 +10,12 @@ Constructor and forward signatures, the ``b`` / ``ft`` / ``in_ft`` dict protocol
 state_dict key names are the reference's.  ``precision`` ("fp32" | "bf16") selects the storage
 type of the projected video tensor and of the weights inside the kernels; parameters stay
 fp32 masters and the [B,Lq,d] query streams stay fp32 in both modes.
+
+Autograd: when a gradient is required (or the module is in ``train()`` mode with dropout) the
+modules run the library's training forward (``bist_vidproj_train_fwd`` /
+``bist_st_layer_train_fwd``: tape + dropout) and ``loss.backward()`` runs its hand-written
+backward (``bist_st_layer_bwd`` / ``bist_vidproj_bwd``); under ``torch.no_grad()`` in eval mode
+they run the inference forward (folded formulation, CUDA-graph capturable).
 """
 import copy
 import ctypes
