@@ -303,7 +303,7 @@ def run_ours(args):
     # ---- training step of the video path (forward with tape + backward + grad all-reduce + Adam) ------------
     train = None
     if not args.no_train:
-        from bist_b200.dist import allreduce_grads
+        from bist_b200.dist import allreduce_grads, overlap_grad_allreduce
         tm = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], dropout=0.1, precision=args.precision).to(dev)
         tm.load_state_dict(synth.make_params(0, c["d"], c["D"], c["n_blocks"]), strict=True)
         tm.train()                                       # dropout on: 0.1 sublayer/FFN (train_configs.py:34), 0.1 attention (mtn.py:77)
@@ -316,7 +316,8 @@ def run_ours(args):
             opt.zero_grad(set_to_none=True)
             out = tm(db, deq)
             loss = ((out["temporal_ft"] - tgt) ** 2).mean() + ((out["spatial_ft"] - tgt) ** 2).mean()
-            loss.backward()
+            with overlap_grad_allreduce():               # each block's all-reduce starts as its backward is enqueued
+                loss.backward()
             ncoll[0] = allreduce_grads(plist)
             opt.step()
 
@@ -373,6 +374,11 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement of the video path")
     args = ap.parse_args()
+    # stdout carries exactly ONE line (the JSON): libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -45,40 +45,97 @@ def gather_rows(local, n_rows):
     return torch.cat(out, 0)
 
 
+_pending = None          # [(work, storage_ptr)] while overlap_grad_allreduce() is active, else None
+
+
+class overlap_grad_allreduce:
+    """``with overlap_grad_allreduce(): loss.backward()`` — every VidEncoderLayer4 starts the all-reduce of its
+    gradient block as soon as its backward kernels are enqueued (NCCL runs it on its own stream, behind the
+    kernels that write the block and beside the backward of the earlier layers); ``allreduce_grads`` afterwards
+    waits for those and reduces only what is left.  A no-op without a process group or with world_size 1."""
+
+    def __enter__(self):
+        global _pending
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            _pending = []
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def _reduce_op():
+    # NCCL averages inside the collective; gloo has no AVG, so sum and divide afterwards.
+    return dist.ReduceOp.AVG if dist.get_backend() == "nccl" else dist.ReduceOp.SUM
+
+
+def grad_block_ready(block, average=True):
+    """Called by the layer backward (encoder.py) with its freshly written gradient block."""
+    if _pending is None:
+        return
+    op = _reduce_op() if average else dist.ReduceOp.SUM
+    work = dist.all_reduce(block, op=op, async_op=True)
+    _pending.append((work, block.untyped_storage().data_ptr(), block, average and op == dist.ReduceOp.SUM))
+
+
 def allreduce_grads(params, average=True):
     """Sum (or average) the gradients of `params` over all ranks with as few collectives as possible.
 
     The backward of a VidEncoderLayer4 writes all of its parameter gradients into one flat fp32 block
-    (include/bist_b200.h, "Gradient block") and hands out views, so every layer is ONE all-reduce over the
-    views' common base; stand-alone gradients are flattened into one extra bucket.  Returns the number of
-    collectives issued.  A no-op (returns 0) without an initialised process group or with world_size 1.
+    (include/bist_b200.h, "Gradient block") and returns slices of it; autograd adopts those slices as the
+    parameters' ``.grad`` without copying (they keep sharing the block's storage, though they are no longer
+    autograd views), so every layer is ONE all-reduce over that storage; stand-alone gradients are flattened
+    into one extra bucket.  Blocks already started by ``overlap_grad_allreduce`` are only waited for.  Returns
+    the number of collectives issued (started ones included).  A no-op (returns 0) without an initialised
+    process group or with world_size 1.
     """
+    global _pending
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
         return 0
     world = dist.get_world_size()
+    op = _reduce_op() if average else dist.ReduceOp.SUM
+    div = average and op == dist.ReduceOp.SUM
+    started = {}
+    n = 0
+    for work, sp, block, need_div in (_pending or []):
+        work.wait()
+        if need_div:
+            block.div_(world)
+        started[sp] = True
+        n += 1
+    _pending = None
     blocks, loose = {}, []
     for p in params:
         g = p.grad
         if g is None:
             continue
-        base = g._base if g._is_view() and g._base is not None and g._base.is_contiguous() else None
-        if base is not None:
-            blocks.setdefault(id(base), [base, 0])[1] += g.numel()
+        st = g.untyped_storage()
+        if st.data_ptr() in started:
+            continue
+        if g.dtype == torch.float32 and g.is_contiguous() and st.nbytes() > g.numel() * 4:
+            blocks.setdefault(st.data_ptr(), [st, 0, []])
+            blocks[st.data_ptr()][1] += g.numel() * 4
+            blocks[st.data_ptr()][2].append(g)
         else:
             loose.append(g)
-    n = 0
-    for base, covered in blocks.values():
-        if covered == base.numel():          # the block holds nothing but gradients: reduce it in place
-            dist.all_reduce(base)
-            if average:
-                base.div_(world)
+    for st, covered, gs in blocks.values():
+        if covered == st.nbytes():           # the storage holds nothing but these gradients: reduce it in place
+            flat = torch.empty(0, dtype=torch.float32, device=gs[0].device).set_(st, 0, (st.nbytes() // 4,))
+            dist.all_reduce(flat, op=op)
+            if div:
+                flat.div_(world)
             n += 1
-        else:                                # partially used base: fall back to its views
-            loose.extend(p.grad for p in params if p.grad is not None and p.grad._is_view() and p.grad._base is base)
-    if loose:
-        flat = torch.cat([g.reshape(-1) for g in loose])
-        dist.all_reduce(flat)
-        if average:
+        else:                                # partially used storage: treat its gradients one by one
+            loose.extend(gs)
+    if len(loose) == 1:
+        dist.all_reduce(loose[0], op=op)
+        if div:
+            loose[0].div_(world)
+        n += 1
+    elif loose:
+        flat = torch.cat([g.reshape(-1).float() for g in loose])
+        dist.all_reduce(flat, op=op)
+        if div:
             flat.div_(world)
         off = 0
         for g in loose:

@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from . import dist as _dist
 from .modules import (LayerNorm, SublayerConnection, clones, _eval_only, _needs_grad, _ws, _WEIGHT_EPOCH,
                       _reg_hook, weights_updated)
 
@@ -189,6 +190,8 @@ class _StLayerFn(torch.autograd.Function):
                    "bist_st_layer_bwd")
         if _reg_hook is None:
             weights_updated()
+        if all(p.grad is None for p in ctx.layer.parameters()):     # autograd will adopt the slices: the block IS .grad
+            _dist.grad_block_ready(grads)
         pg = tuple(grads[o:o + n].view(p.shape) for (o, n), p in zip(offs, ctx.layer.parameters()))
         g_vft = None if shared or not ctx.vft_needs_grad else acc.to(vft.dtype)
         g_handle = torch.zeros(1, dtype=torch.float32, device=vft.device) if shared else None

@@ -58,18 +58,43 @@ def test_row_sharding_two_ranks_gloo():
     assert n0 == 3                # 5 rows over 2 ranks: 3 + 2
 
 
+class _BlockFn(torch.autograd.Function):
+    """What the layer backward does: one flat gradient block, slices of it returned as the parameter gradients."""
+
+    @staticmethod
+    def forward(ctx, x, a, b, scale):
+        ctx.scale = scale
+        return x * 1.0
+
+    @staticmethod
+    def backward(ctx, g):
+        from bist_b200.dist import grad_block_ready
+        block = torch.arange(10, dtype=torch.float32) * ctx.scale
+        grad_block_ready(block)
+        return g, block[:4].view(4), block[4:].view(2, 3), None
+
+
 def _grad_worker(rank, world, port, q):
+    from bist_b200.dist import overlap_grad_allreduce
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    # one flat gradient block handed out as views (what the layer backward does) + two stand-alone gradients
-    block = torch.arange(10, dtype=torch.float32) * (rank + 1)
-    ps = [torch.nn.Parameter(torch.zeros(4)), torch.nn.Parameter(torch.zeros(2, 3)),
-          torch.nn.Parameter(torch.zeros(5)), torch.nn.Parameter(torch.zeros(1))]
-    ps[0].grad, ps[1].grad = block[:4].view(4), block[4:].view(2, 3)
-    ps[2].grad, ps[3].grad = torch.full((5,), float(rank + 1)), torch.full((1,), 10.0 * (rank + 1))
-    n = allreduce_grads(ps, average=True)
+    res = []
+    for overlap in (False, True):
+        ps = [torch.nn.Parameter(torch.zeros(4)), torch.nn.Parameter(torch.zeros(2, 3)),
+              torch.nn.Parameter(torch.zeros(5)), torch.nn.Parameter(torch.zeros(1))]
+        x = torch.ones(3, requires_grad=True)
+        loss = _BlockFn.apply(x, ps[0], ps[1], float(rank + 1)).sum() + (ps[2] * (rank + 1)).sum() + ps[3][0] * 10 * (rank + 1)
+        if overlap:
+            with overlap_grad_allreduce():
+                loss.backward()
+        else:
+            loss.backward()
+        # autograd adopts the slices without copying: both gradients still live in the block's storage
+        shared = ps[0].grad.untyped_storage().data_ptr() == ps[1].grad.untyped_storage().data_ptr()
+        n = allreduce_grads(ps, average=True)
+        res.append((n, shared, [p.grad.clone() for p in ps]))
     if rank == 0:
-        q.put((n, [p.grad.clone() for p in ps]))
+        q.put(res)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -81,11 +106,13 @@ def test_gradient_allreduce_two_ranks_gloo():
     procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    n, grads = q.get(timeout=120)
+    res = q.get(timeout=120)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    assert n == 2                                            # one collective for the block, one for the loose bucket
     mean = torch.arange(10, dtype=torch.float32) * 1.5       # mean of 1x and 2x
-    assert torch.equal(grads[0], mean[:4]) and torch.equal(grads[1], mean[4:].view(2, 3))
-    assert torch.equal(grads[2], torch.full((5,), 1.5)) and torch.equal(grads[3], torch.full((1,), 15.0))
+    for n, shared, grads in res:                             # plain, then with the block's all-reduce started in backward
+        assert shared
+        assert n == 2                                        # one collective for the block, one for the loose bucket
+        assert torch.equal(grads[0], mean[:4]) and torch.equal(grads[1], mean[4:].view(2, 3))
+        assert torch.equal(grads[2], torch.full((5,), 1.5)) and torch.equal(grads[3], torch.full((1,), 15.0))
