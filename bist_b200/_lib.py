@@ -80,6 +80,16 @@ SIGNATURES = {
     "bist_dropout_mask": (c_i, [ctypes.c_uint64, ctypes.c_uint32, c_f, c_i64, c_p, c_p]),
     "bist_ln_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_f, c_i, c_i, c_i, c_p]),
     "bist_linear_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i, c_i, c_i, c_i, c_p]),
+    "bist_dropout_fwd": (c_i, [c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
+    "bist_mha_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, ctypes.POINTER(MhaParams), c_p, c_p,
+                                 c_i64, c_i64, c_i64, c_i64, c_i64, c_i64, c_p, c_sz, c_i,
+                                 c_f, ctypes.c_uint64, ctypes.c_uint32, c_p]),
+    "bist_mha_bwd_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64, c_i64, c_i]),
+    "bist_mha_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, ctypes.POINTER(MhaParams), c_p, c_sz, c_p, c_p, c_p,
+                           ctypes.POINTER(c_p), ctypes.POINTER(c_p), c_i64, c_i64, c_i64, c_i64, c_i64, c_i64,
+                           c_p, c_sz, c_i, c_f, ctypes.c_uint64, ctypes.c_uint32, c_p]),
+    "bist_ffn_train_fwd": (c_i, [c_p] * 7 + [c_i64] * 4 + [c_i, c_f, ctypes.c_uint64, ctypes.c_uint32, c_p]),
+    "bist_ffn_bwd": (c_i, [c_p] * 10 + [c_i64] * 4 + [c_p, c_sz, c_i, c_f, c_p]),
 }
 
 

@@ -150,9 +150,30 @@ size_t bist_mha_workspace_bytes(int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, i
   return n + 1024;
 }
 
-int bist_mha_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
-                 const bist_mha_params_t* P, void* out, float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk,
-                 int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype, void* stream) {
+}  // extern "C"
+
+namespace {
+
+// Carving of the MultiHeadedAttention workspace; the training forward leaves q, k, v, ctx there for the backward.
+struct MhaWs {
+  void *q, *k, *v, *ctx;
+  float* sc;
+  bool ok;
+  MhaWs(void* ws, size_t ws_bytes, int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int64_t h, size_t e) {
+    Arena A(ws, ws_bytes);
+    q = A.take((size_t)Bp * Lq * d * e);
+    k = A.take((size_t)Bp * Lk * d * e);
+    v = A.take((size_t)Bp * Lk * d * e);
+    ctx = A.take((size_t)Bp * Lq * d * e);
+    sc = (float*)A.take((size_t)Bp * Lq * h * Lk * 4);
+    ok = A.ok;
+  }
+};
+
+int mha_forward(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
+                const bist_mha_params_t* P, void* out, float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk,
+                int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype, const DropCfg& drop,
+                void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   BIST_CHECK_ARG(query && key && value && P && out && ws, "mha: null pointer");
   BIST_CHECK_ARG(Bp > 0 && Lq > 0 && Lk > 0 && d > 0 && d_in > 0 && h > 0 && d % h == 0, "mha: bad shape");
@@ -163,13 +184,10 @@ int bist_mha_fwd(const void* query, const void* key, const void* value, const ui
   BIST_CHECK_ARG(Bp * h <= 65535 * 1LL, "mha: Bp*h too large");
   const int dk = (int)(d / h);
   const size_t e = dtype_size(dtype);
-  Arena A(ws, ws_bytes);
-  void* q = A.take((size_t)Bp * Lq * d * e);
-  void* k = A.take((size_t)Bp * Lk * d * e);
-  void* v = A.take((size_t)Bp * Lk * d * e);
-  void* ctx = A.take((size_t)Bp * Lq * d * e);
-  float* sc = (float*)A.take((size_t)Bp * Lq * h * Lk * 4);
-  if (!A.ok) { set_error("mha: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+  MhaWs W(ws, ws_bytes, Bp, Lq, Lk, d, h, e);
+  if (!W.ok) { set_error("mha: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+  void *q = W.q, *k = W.k, *v = W.v, *ctx = W.ctx;
+  float* sc = W.sc;
 
   // modules.py:89-91 — the three input projections
   const void* in[3] = {query, key, value};
@@ -197,10 +215,22 @@ int bist_mha_fwd(const void* query, const void* key, const void* value, const ui
   a.ctx = ctx; a.og = rows_dense(Lq * d); a.o_l = d; a.p_out = attn_out;
   a.G = (int)Bp; a.Lq = (int)Lq; a.h = (int)h; a.dk = dk; a.nk = (int)Lk;
   a.v_dtype = dtype; a.ctx_dtype = dtype;
+  a.drop = drop;                      // modules.py:62-63 (element ((b*h + hh)*Lq + l)*Lk + k of p_attn)
   BIST_TRY(softmax_pv(a, st));
 
   // modules.py:98-100 — output projection
   return bist_linear_fwd(ctx, P->w[3], P->b[3], nullptr, out, Bp * Lq, d_in, d, 0, dtype, dtype, dtype, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int bist_mha_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
+                 const bist_mha_params_t* P, void* out, float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk,
+                 int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype, void* stream) {
+  return mha_forward(query, key, value, mask, mask_mode, P, out, attn_out, Bp, Lq, Lk, d, d_in, h, ws, ws_bytes, dtype,
+                     DropCfg(), stream);
 }
 
 // ----------------------------------------------------------------------------- PositionwiseFeedForward
@@ -252,6 +282,111 @@ int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, flo
     BIST_TRY(wgrad(w, st));
   }
   return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------- stand-alone modules, training
+// MultiHeadedAttention / PositionwiseFeedForward / nn.Dropout of /root/reference/model/modules.py used on their own
+// (the decoder, caption and audio layers are built from them: decoder.py:11-60, encoder.py:203-235).
+extern "C" {
+
+int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, uint64_t seed, uint32_t site, int dtype,
+                     void* stream) {
+  BIST_CHECK_ARG(x && y && rows > 0 && d > 0, "dropout: bad argument");
+  BIST_CHECK_ARG(dtype_ok(dtype) && p >= 0.f && p < 1.f, "dropout: bad dtype or probability");
+  return dropout_scale(x, y, rows, d, make_drop(p, seed, site), 0, 0, dtype, dtype, (cudaStream_t)stream);
+}
+
+int bist_mha_train_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
+                       const bist_mha_params_t* P, void* out, float* attn_out, int64_t Bp, int64_t Lq, int64_t Lk,
+                       int64_t d, int64_t d_in, int64_t h, void* tape, size_t tape_bytes, int dtype, float p_drop,
+                       uint64_t seed, uint32_t site, void* stream) {
+  BIST_CHECK_ARG(p_drop >= 0.f && p_drop < 1.f, "mha(train): dropout probability must be in [0, 1)");
+  return mha_forward(query, key, value, mask, mask_mode, P, out, attn_out, Bp, Lq, Lk, d, d_in, h, tape, tape_bytes, dtype,
+                     make_drop(p_drop, seed, site), stream);
+}
+
+size_t bist_mha_bwd_workspace_bytes(int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int dtype) {
+  const size_t e = dtype_size(dtype);
+  return 2 * align_up((size_t)Bp * Lq * d * e, 256) + 2 * align_up((size_t)Bp * Lk * d * e, 256) + 1024;
+}
+
+// PT->w[i] = linears[i].weight transposed ([in, out] row-major, dtype `dtype`); PT->b is not read.
+// dW[i] / db[i] (fp32, zero-initialised or holding a running sum) are accumulated into; any of d_query / d_key /
+// d_value may be null (that input needs no gradient).
+int bist_mha_bwd(const void* d_out, const void* query, const void* key, const void* value, const uint8_t* mask,
+                 int mask_mode, const bist_mha_params_t* PT, const void* tape, size_t tape_bytes, void* d_query,
+                 void* d_key, void* d_value, float* const* dW, float* const* db, int64_t Bp, int64_t Lq, int64_t Lk,
+                 int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype, float p_drop, uint64_t seed,
+                 uint32_t site, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(d_out && query && key && value && PT && tape && dW && db && ws, "mha_bwd: null pointer");
+  BIST_CHECK_ARG(Bp > 0 && Lq > 0 && Lk > 0 && d > 0 && d_in > 0 && h > 0 && d % h == 0, "mha_bwd: bad shape");
+  BIST_CHECK_ARG(dtype_ok(dtype), "mha_bwd: bad dtype");
+  BIST_CHECK_ARG((mask_mode == BIST_MASK_NONE) == (mask == nullptr) && mask_mode >= 0 && mask_mode <= 2,
+                 "mha_bwd: mask and mask_mode disagree");
+  for (int i = 0; i < 4; ++i) BIST_CHECK_ARG(PT->w[i] && dW[i] && db[i], "mha_bwd: null parameter %d", i);
+  const size_t e = dtype_size(dtype);
+  MhaWs T(const_cast<void*>(tape), tape_bytes, Bp, Lq, Lk, d, h, e);
+  if (!T.ok) { set_error("mha_bwd: tape too small (%zu bytes)", tape_bytes); return BIST_ERR_WORKSPACE; }
+  Arena A(ws, ws_bytes);
+  void* dctx = A.take((size_t)Bp * Lq * d * e);
+  void* dq = A.take((size_t)Bp * Lq * d * e);
+  void* dk = A.take((size_t)Bp * Lk * d * e);
+  void* dv = A.take((size_t)Bp * Lk * d * e);
+  if (!A.ok) { set_error("mha_bwd: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+
+  // modules.py:98-100 backwards: dctx = d_out W_o ; dW_o += d_out^T ctx ; db_o += colsum(d_out)
+  BIST_TRY(bist_linear_bwd(d_out, T.ctx, PT->w[3], dctx, dW[3], db[3], Bp * Lq, d_in, d, dtype, dtype, dtype, dtype, st));
+
+  // modules.py:54-64 backwards (probabilities recomputed from the saved q, k)
+  AttnBwdArgs a;
+  a.q = T.q; a.k = T.k; a.v = T.v; a.dctx = dctx; a.dq = dq; a.dk_ = dk; a.dv = dv;
+  a.q_b = Lq * d; a.q_l = d; a.k_b = Lk * d; a.k_l = d; a.c_b = Lq * d; a.c_l = d;
+  a.mask = mask;
+  a.m_b = (mask_mode == BIST_MASK_FULL) ? Lq * Lk : Lk;
+  a.m_l = (mask_mode == BIST_MASK_FULL) ? Lk : 0;
+  a.Bp = (int)Bp; a.Lq = (int)Lq; a.Lk = (int)Lk; a.h = (int)h; a.dk = (int)(d / h);
+  a.dtype = dtype;
+  a.drop = make_drop(p_drop, seed, site);
+  BIST_TRY(attn_core_bwd(a, st));
+
+  // modules.py:89-91 backwards: the three input projections
+  const void* in[3] = {query, key, value};
+  const void* dproj[3] = {dq, dk, dv};
+  void* din[3] = {d_query, d_key, d_value};
+  const int64_t rows[3] = {Bp * Lq, Bp * Lk, Bp * Lk};
+  for (int i = 0; i < 3; ++i)
+    BIST_TRY(bist_linear_bwd(dproj[i], in[i], PT->w[i], din[i], dW[i], db[i], rows[i], d, d_in, dtype, dtype, dtype, dtype, st));
+  return 0;
+}
+
+// hidden [rows, d_ff] (dtype) is the tape: relu(x W1^T + b1) after dropout (modules.py:113).
+int bist_ffn_train_fwd(const void* x, const void* w1, const float* b1, const void* w2, const float* b2, void* y,
+                       void* hidden, int64_t rows, int64_t d, int64_t d_ff, int64_t d_out, int dtype, float p_drop,
+                       uint64_t seed, uint32_t site, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(x && w1 && w2 && y && hidden, "ffn(train): null pointer");
+  BIST_CHECK_ARG(dtype_ok(dtype) && p_drop >= 0.f && p_drop < 1.f, "ffn(train): bad dtype or dropout probability");
+  BIST_TRY(bist_linear_fwd(x, w1, b1, nullptr, hidden, rows, d_ff, d, 1, dtype, dtype, dtype, st));
+  if (p_drop > 0.f)
+    BIST_TRY(dropout_add(hidden, nullptr, rows, d_ff, 1, make_drop(p_drop, seed, site), 0, 0, dtype, st));
+  return bist_linear_fwd(hidden, w2, b2, nullptr, y, rows, d_out, d_ff, 0, dtype, dtype, dtype, st);
+}
+
+// w1T [d, d_ff], w2T [d_ff, d_out] (dtype); ws >= rows*d_ff*sizeof(dtype); dW / db fp32, accumulated into; dx may be null.
+int bist_ffn_bwd(const void* dy, const void* x, const void* w1T, const void* w2T, const void* hidden, void* dx, float* dW1,
+                 float* db1, float* dW2, float* db2, int64_t rows, int64_t d, int64_t d_ff, int64_t d_out, void* ws,
+                 size_t ws_bytes, int dtype, float p_drop, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(dy && x && w1T && w2T && hidden && dW1 && db1 && dW2 && db2 && ws, "ffn_bwd: null pointer");
+  BIST_CHECK_ARG(dtype_ok(dtype) && p_drop >= 0.f && p_drop < 1.f, "ffn_bwd: bad dtype or dropout probability");
+  if (ws_bytes < (size_t)rows * d_ff * dtype_size(dtype)) { set_error("ffn_bwd: workspace too small"); return BIST_ERR_WORKSPACE; }
+  // d(hidden') = dy W2 ; dW2 += dy^T hidden' ; then through the dropout multiplier and the ReLU gate in one pass
+  BIST_TRY(bist_linear_bwd(dy, hidden, w2T, ws, dW2, db2, rows, d_out, d_ff, dtype, dtype, dtype, dtype, st));
+  BIST_TRY(relu_gate(ws, hidden, rows * d_ff, dtype, st, p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f));
+  return bist_linear_bwd(ws, x, w1T, dx, dW1, db1, rows, d_ff, d, dtype, dtype, dtype, dtype, st);
 }
 
 }  // extern "C"

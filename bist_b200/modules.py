@@ -6,10 +6,12 @@ Same constructor signatures, forward signatures and parameter names as the refer
 loads with ``strict=True`` and ``model/mtn.py`` can build its model from these classes.
 The forward bodies call the C ABI (include/bist_b200.h) on torch's current CUDA stream.
 
-``LayerNorm`` (and the video modules of encoder.py) carry autograd through the library's backward
-entry points; ``MultiHeadedAttention`` / ``PositionwiseFeedForward`` / ``SublayerConnection`` used on
-their own are still forward-only (eval mode).  Inputs may be float32 or bfloat16 ("bf16
-mode": bf16 storage, fp32 accumulation / statistics); parameters stay fp32 masters.
+Every module carries autograd through the library's backward entry points (``bist_ln_bwd``, ``bist_mha_bwd``,
+``bist_ffn_bwd``, ``bist_dropout_fwd``) and honours ``train()`` mode: dropout at the reference's three sites
+(modules.py:44,62-63,113) with counter-based masks, a fresh seed per call drawn from torch's CPU generator
+(``torch.manual_seed`` reproduces a run; ``module.last_dropout`` = (p, seed, site) lets a test rebuild the mask
+with ``bist_dropout_mask``).  Inputs may be float32 or bfloat16 ("bf16 mode": bf16 storage, fp32 accumulation /
+statistics); parameters stay fp32 masters and their gradients are fp32.
 """
 import copy
 import ctypes
@@ -29,14 +31,6 @@ def _eval_only(m):
     if m.training:
         raise NotImplementedError(
             "%s: this module of the bist_b200 CUDA path is forward-only this round; call .eval()" % type(m).__name__)
-
-
-def _no_dropout(m, *ps):
-    """Training mode is supported by the CUDA path only with dropout probability 0 (dropout kernels land next)."""
-    if m.training and any(p > 0 for p in ps):
-        raise NotImplementedError(
-            "%s: train() with dropout p > 0 is not built yet on the bist_b200 CUDA path; use dropout=0 or .eval() "
-            "(gradients flow in both modes)" % type(m).__name__)
 
 
 def _needs_grad(*tensors):
@@ -106,19 +100,153 @@ def weights_updated():
 
 
 class _BF16Cache:
-    """bf16 copies of fp32 parameters, refreshed when a parameter is updated in place."""
+    """Copies of fp32 parameters in the compute dtype (bf16 copies; transposed copies for the backward GEMMs),
+    refreshed when a parameter is updated in place."""
 
     def __init__(self):
         self._store = {}
 
-    def get(self, p):
-        key = id(p)
+    def get(self, p, dtype=torch.bfloat16, transposed=False):
+        key = (id(p), dtype, transposed)
         hit = self._store.get(key)
         ver = (p._version, _WEIGHT_EPOCH[0])
         if hit is None or hit[0] != ver or hit[1].device != p.device:
-            hit = (ver, p.detach().to(torch.bfloat16).contiguous())
+            w = p.detach().t() if transposed else p.detach()
+            hit = (ver, w.to(dtype).contiguous())
             self._store[key] = hit
         return hit[1]
+
+
+# dropout sites of the stand-alone modules (the video path's sites 0-10 are listed in include/bist_b200.h)
+SITE_MHA, SITE_FFN, SITE_SUBLAYER = 100, 101, 102
+
+
+def _draw_seed():
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+
+class _DropoutFn(torch.autograd.Function):
+    """y = x o m / (1 - p) with the library's counter-based mask; the backward is the same call on dy."""
+
+    @staticmethod
+    def forward(ctx, x, p, seed, site):
+        x = x.contiguous()
+        d = x.shape[-1]
+        y = torch.empty_like(x)
+        _lib.check(_lib.lib().bist_dropout_fwd(_lib.ptr(x), _lib.ptr(y), x.numel() // d, d, float(p), seed, site,
+                                               _lib.dtype_code(x.dtype), _lib.stream_ptr()), "bist_dropout_fwd")
+        ctx.cfg = (float(p), seed, site)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        gy = gy.contiguous()
+        d = gy.shape[-1]
+        gx = torch.empty_like(gy)
+        p, seed, site = ctx.cfg
+        _lib.check(_lib.lib().bist_dropout_fwd(_lib.ptr(gy), _lib.ptr(gx), gy.numel() // d, d, p, seed, site,
+                                               _lib.dtype_code(gy.dtype), _lib.stream_ptr()), "bist_dropout_fwd")
+        return gx, None, None, None
+
+
+def _ptr_array(tensors):
+    arr = (ctypes.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
+
+
+class _MhaFn(torch.autograd.Function):
+    """MultiHeadedAttention forward/backward (modules.py:81-100) — bist_mha_train_fwd / bist_mha_bwd."""
+
+    @staticmethod
+    def forward(ctx, mod, query, key, value, m8, mask_mode, p_drop, seed, *params):
+        dt = _lib.dtype_code(query.dtype)
+        query, key, value = query.contiguous(), key.contiguous(), value.contiguous()
+        Bp, Lq, d_in = query.shape
+        Lk = key.shape[1]
+        d = mod.h * mod.d_k
+        P, keep = mod._param_struct(dt, transposed=False)
+        out = torch.empty((Bp, Lq, d_in), dtype=query.dtype, device=query.device)
+        attn = torch.empty((Bp, mod.h, Lq, Lk), dtype=torch.float32, device=query.device) if mod.store_attn else None
+        L = _lib.lib()
+        tape = _ws(L.bist_mha_workspace_bytes(Bp, Lq, Lk, d, d_in, mod.h), query.device)
+        _lib.check(L.bist_mha_train_fwd(_lib.ptr(query), _lib.ptr(key), _lib.ptr(value), _lib.ptr(m8), mask_mode,
+                                        ctypes.byref(P), _lib.ptr(out), _lib.ptr(attn), Bp, Lq, Lk, d, d_in, mod.h,
+                                        _lib.ptr(tape), tape.numel(), dt, float(p_drop), seed, SITE_MHA,
+                                        _lib.stream_ptr()), "bist_mha_train_fwd")
+        ctx.save_for_backward(query, key, value, m8, tape)
+        ctx.mod, ctx.cfg = mod, (Bp, Lq, Lk, d, d_in, mask_mode, float(p_drop), seed, dt)
+        if attn is None:
+            attn = torch.empty(0, device=query.device)
+        ctx.mark_non_differentiable(attn)
+        return out, attn
+
+    @staticmethod
+    def backward(ctx, g_out, _g_attn):
+        query, key, value, m8, tape = ctx.saved_tensors
+        mod = ctx.mod
+        Bp, Lq, Lk, d, d_in, mask_mode, p_drop, seed, dt = ctx.cfg
+        g_out = g_out.to(query.dtype).contiguous()
+        PT, keep = mod._param_struct(dt, transposed=True)
+        # one flat fp32 block for the eight parameter gradients (one all-reduce per module, dist.allreduce_grads)
+        nw, nb = d * d_in, (d, d, d, d_in)
+        block = torch.zeros(4 * nw + sum(nb), dtype=torch.float32, device=query.device)
+        dW = [block[i * nw:(i + 1) * nw] for i in range(4)]
+        db, off = [], 4 * nw
+        for n in nb:
+            db.append(block[off:off + n])
+            off += n
+        d_in_t = [torch.empty_like(t) if need else None for t, need in zip((query, key, value), ctx.needs_input_grad[1:4])]
+        L = _lib.lib()
+        ws = _ws(L.bist_mha_bwd_workspace_bytes(Bp, Lq, Lk, d, dt), query.device)
+        _lib.check(L.bist_mha_bwd(_lib.ptr(g_out), _lib.ptr(query), _lib.ptr(key), _lib.ptr(value), _lib.ptr(m8),
+                                  mask_mode, ctypes.byref(PT), _lib.ptr(tape), tape.numel(), _lib.ptr(d_in_t[0]),
+                                  _lib.ptr(d_in_t[1]), _lib.ptr(d_in_t[2]), _ptr_array(dW), _ptr_array(db), Bp, Lq, Lk,
+                                  d, d_in, mod.h, _lib.ptr(ws), ws.numel(), dt, p_drop, seed, SITE_MHA,
+                                  _lib.stream_ptr()), "bist_mha_bwd")
+        grads = []
+        for i, lin in enumerate(mod.linears):
+            grads += [dW[i].view(lin.weight.shape), db[i]]
+        return (None, d_in_t[0], d_in_t[1], d_in_t[2], None, None, None, None) + tuple(grads)
+
+
+class _FfnFn(torch.autograd.Function):
+    """PositionwiseFeedForward forward/backward (modules.py:112-113) — bist_ffn_train_fwd / bist_ffn_bwd."""
+
+    @staticmethod
+    def forward(ctx, mod, x, p_drop, seed, w1, b1, w2, b2):
+        dt = _lib.dtype_code(x.dtype)
+        x = x.contiguous()
+        d, d_ff, d_out = w1.shape[1], w1.shape[0], w2.shape[0]
+        rows = x.numel() // d
+        cw1, cw2 = (w1.detach(), w2.detach()) if dt == _lib.F32 else (mod._bf16.get(w1), mod._bf16.get(w2))
+        y = torch.empty(x.shape[:-1] + (d_out,), dtype=x.dtype, device=x.device)
+        hidden = torch.empty((rows, d_ff), dtype=x.dtype, device=x.device)
+        _lib.check(_lib.lib().bist_ffn_train_fwd(_lib.ptr(x), _lib.ptr(cw1), _lib.ptr(b1), _lib.ptr(cw2), _lib.ptr(b2),
+                                                 _lib.ptr(y), _lib.ptr(hidden), rows, d, d_ff, d_out, dt, float(p_drop),
+                                                 seed, SITE_FFN, _lib.stream_ptr()), "bist_ffn_train_fwd")
+        ctx.save_for_backward(x, hidden, w1, w2)
+        ctx.mod, ctx.cfg = mod, (rows, d, d_ff, d_out, float(p_drop), dt)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, hidden, w1, w2 = ctx.saved_tensors
+        rows, d, d_ff, d_out, p_drop, dt = ctx.cfg
+        gy = gy.to(x.dtype).contiguous()
+        w1T = ctx.mod._bf16.get(ctx.mod.w_1.weight, x.dtype, transposed=True)
+        w2T = ctx.mod._bf16.get(ctx.mod.w_2.weight, x.dtype, transposed=True)
+        o1, o2, o3 = d_ff * d, d_ff * d + d_ff, d_ff * d + d_ff + d_out * d_ff
+        block = torch.zeros(o3 + d_out, dtype=torch.float32, device=x.device)     # one block: one all-reduce per module
+        dW1, db1, dW2, db2 = block[:o1], block[o1:o2], block[o2:o3], block[o3:]
+        dx = torch.empty_like(x) if ctx.needs_input_grad[1] else None
+        ws = _ws(rows * d_ff * x.element_size() + 256, x.device)
+        _lib.check(_lib.lib().bist_ffn_bwd(_lib.ptr(gy), _lib.ptr(x), _lib.ptr(w1T), _lib.ptr(w2T), _lib.ptr(hidden),
+                                           _lib.ptr(dx), _lib.ptr(dW1), _lib.ptr(db1), _lib.ptr(dW2), _lib.ptr(db2), rows,
+                                           d, d_ff, d_out, _lib.ptr(ws), ws.numel(), dt, p_drop, _lib.stream_ptr()),
+                   "bist_ffn_bwd")
+        return None, dx, None, None, dW1.view(w1.shape), db1, dW2.view(w2.shape), db2
 
 
 class LayerNorm(nn.Module):
@@ -153,8 +281,14 @@ class SublayerConnection(nn.Module):
         self.dropout = nn.Dropout(dropout)
 
     def forward(self, x, sublayer):
-        _eval_only(self)
-        return x + sublayer(self.norm(x))
+        y = sublayer(self.norm(x))
+        self.last_dropout = None
+        if self.training and self.dropout.p > 0:                       # modules.py:44
+            _lib.require_cuda(y)
+            seed = _draw_seed()
+            self.last_dropout = (self.dropout.p, seed, SITE_SUBLAYER)
+            y = _DropoutFn.apply(y, self.dropout.p, seed, SITE_SUBLAYER)
+        return x + y
 
 
 class MultiHeadedAttention(nn.Module):
@@ -181,34 +315,51 @@ class MultiHeadedAttention(nn.Module):
             new.__dict__[k] = _BF16Cache() if k == "_bf16" else copy.deepcopy(v, memo)
         return new
 
-    def forward(self, query, key, value, mask=None):
-        _eval_only(self)
-        _lib.require_cuda(query, key, value, self.linears[0].weight)
-        dt = _lib.dtype_code(query.dtype)
-        query, key, value = (t.detach().contiguous() for t in (query, key, value))
-        Bp, Lq, d_in = query.shape
-        Lk = key.shape[1]
-        d = self.h * self.d_k
-        P = _lib.MhaParams()
-        keep = []
+    def _param_struct(self, dt, transposed):
+        """bist_mha_params_t over the compute-dtype (optionally transposed) copies of the four Linear weights."""
+        P, keep = _lib.MhaParams(), []
+        tdt = torch.float32 if dt == _lib.F32 else torch.bfloat16
         for i, lin in enumerate(self.linears):
-            w = lin.weight.detach() if dt == _lib.F32 else self._bf16.get(lin.weight)
+            if transposed or dt != _lib.F32:
+                w = self._bf16.get(lin.weight, tdt, transposed)
+            else:
+                w = lin.weight.detach()
             keep.append(w)
             P.w[i] = w.data_ptr()
             P.b[i] = lin.bias.data_ptr()
+        return P, keep
+
+    def forward(self, query, key, value, mask=None):
+        _lib.require_cuda(query, key, value, self.linears[0].weight)
+        dt = _lib.dtype_code(query.dtype)
+        Bp, Lq, d_in = query.shape
+        Lk = key.shape[1]
+        d = self.h * self.d_k
         mask_mode, m8 = _lib.MASK_NONE, None
         if mask is not None:
             if mask.dim() == 3 and mask.shape[1] == 1:
                 mask_mode, m8 = _lib.MASK_KEY, _mask_u8(mask, (Bp, 1, Lk))
             else:
                 mask_mode, m8 = _lib.MASK_FULL, _mask_u8(mask, (Bp, Lq, Lk))
-        out = torch.empty((Bp, Lq, d_in), dtype=query.dtype, device=query.device)
-        attn = torch.empty((Bp, self.h, Lq, Lk), dtype=torch.float32, device=query.device) if self.store_attn else None
-        L = _lib.lib()
-        ws = _ws(L.bist_mha_workspace_bytes(Bp, Lq, Lk, d, d_in, self.h), query.device)
-        _lib.check(L.bist_mha_fwd(_lib.ptr(query), _lib.ptr(key), _lib.ptr(value), _lib.ptr(m8), mask_mode,
-                                  ctypes.byref(P), _lib.ptr(out), _lib.ptr(attn), Bp, Lq, Lk, d, d_in, self.h,
-                                  _lib.ptr(ws), ws.numel(), dt, _lib.stream_ptr()), "bist_mha_fwd")
+        p_drop = self.dropout.p if self.training else 0.0
+        self.last_dropout = None
+        params = [t for lin in self.linears for t in (lin.weight, lin.bias)]
+        if p_drop > 0 or _needs_grad(query, key, value, *params):
+            seed = _draw_seed() if p_drop > 0 else 0
+            if p_drop > 0:
+                self.last_dropout = (p_drop, seed, SITE_MHA)
+            out, attn = _MhaFn.apply(self, query, key, value, m8, mask_mode, p_drop, seed, *params)
+            attn = attn if self.store_attn else None
+        else:
+            query, key, value = (t.detach().contiguous() for t in (query, key, value))
+            P, keep = self._param_struct(dt, transposed=False)
+            out = torch.empty((Bp, Lq, d_in), dtype=query.dtype, device=query.device)
+            attn = torch.empty((Bp, self.h, Lq, Lk), dtype=torch.float32, device=query.device) if self.store_attn else None
+            L = _lib.lib()
+            ws = _ws(L.bist_mha_workspace_bytes(Bp, Lq, Lk, d, d_in, self.h), query.device)
+            _lib.check(L.bist_mha_fwd(_lib.ptr(query), _lib.ptr(key), _lib.ptr(value), _lib.ptr(m8), mask_mode,
+                                      ctypes.byref(P), _lib.ptr(out), _lib.ptr(attn), Bp, Lq, Lk, d, d_in, self.h,
+                                      _lib.ptr(ws), ws.numel(), dt, _lib.stream_ptr()), "bist_mha_fwd")
         self.attn = attn if attn is None or dt == _lib.F32 else attn.to(query.dtype)
         return out
 
@@ -228,9 +379,16 @@ class PositionwiseFeedForward(nn.Module):
     __deepcopy__ = MultiHeadedAttention.__deepcopy__
 
     def forward(self, x):
-        _eval_only(self)
         _lib.require_cuda(x, self.w_1.weight)
         dt = _lib.dtype_code(x.dtype)
+        p_drop = self.dropout.p if self.training else 0.0
+        self.last_dropout = None
+        params = (self.w_1.weight, self.w_1.bias, self.w_2.weight, self.w_2.bias)
+        if p_drop > 0 or _needs_grad(x, *params):
+            seed = _draw_seed() if p_drop > 0 else 0
+            if p_drop > 0:
+                self.last_dropout = (p_drop, seed, SITE_FFN)
+            return _FfnFn.apply(self, x, p_drop, seed, *params)
         x = x.detach().contiguous()
         d, d_ff, d_out = self.w_1.in_features, self.w_1.out_features, self.w_2.out_features
         rows = x.numel() // d

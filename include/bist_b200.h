@@ -258,6 +258,42 @@ int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, flo
                     int64_t M, int64_t N, int64_t K, int dy_dtype, int x_dtype, int w_dtype, int dx_dtype,
                     void* stream);
 
+/* ---- stand-alone modules, training (modules.py:33-113 used outside VidEncoderLayer4: the decoder, caption and audio
+ * layers of decoder.py:11-60 / encoder.py:203-235 are compositions of these) ----------------------------------------
+ * Dropout masks are counter based, as on the video path: element i of the reference's tensor at a site is kept iff
+ * hash(seed, site, i) >= p * 2^32; the backward regenerates them from the same (seed, site).
+ *
+ * bist_dropout_fwd: y = x o m / (1 - p) over a dense [rows, d] tensor (nn.Dropout of SublayerConnection,
+ * modules.py:44); its own backward is the same call on dy. */
+int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, uint64_t seed, uint32_t site,
+                     int dtype, void* stream);
+
+/* MultiHeadedAttention.forward in train() mode (modules.py:81-100): as bist_mha_fwd, with dropout p_drop on the
+ * probabilities (modules.py:62-63; attn_out receives the dropped probabilities, as self.attn does) and the workspace
+ * kept as the tape of bist_mha_bwd (tape_bytes = bist_mha_workspace_bytes). */
+int bist_mha_train_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,
+                       const bist_mha_params_t* params, void* out, float* attn_out, int64_t Bp, int64_t Lq,
+                       int64_t Lk, int64_t d, int64_t d_in, int64_t h, void* tape, size_t tape_bytes, int dtype,
+                       float p_drop, uint64_t seed, uint32_t site, void* stream);
+size_t bist_mha_bwd_workspace_bytes(int64_t Bp, int64_t Lq, int64_t Lk, int64_t d, int dtype);
+/* Backward of the same.  params_T->w[i] = linears[i].weight TRANSPOSED ([in, out], dtype); params_T->b is not read.
+ * dW[i] ([out, in]) and db[i] are fp32 and accumulated into.  d_query / d_key / d_value ([Bp, L, d_in], dtype) may
+ * each be NULL.  Limits: (2 Lq + 2 Lk)(d_k + 1) + 2 Lq (Lk + 1) floats must fit 200 KB of shared memory. */
+int bist_mha_bwd(const void* d_out, const void* query, const void* key, const void* value, const uint8_t* mask,
+                 int mask_mode, const bist_mha_params_t* params_T, const void* tape, size_t tape_bytes,
+                 void* d_query, void* d_key, void* d_value, float* const* dW, float* const* db, int64_t Bp,
+                 int64_t Lq, int64_t Lk, int64_t d, int64_t d_in, int64_t h, void* ws, size_t ws_bytes, int dtype,
+                 float p_drop, uint64_t seed, uint32_t site, void* stream);
+
+/* PositionwiseFeedForward in train() mode (modules.py:112-113).  hidden [rows, d_ff] (dtype) is written by the
+ * forward (the ReLU output after dropout) and read by the backward.  w1T [d, d_ff], w2T [d_ff, d_out]. */
+int bist_ffn_train_fwd(const void* x, const void* w1, const float* b1, const void* w2, const float* b2, void* y,
+                       void* hidden, int64_t rows, int64_t d, int64_t d_ff, int64_t d_out, int dtype, float p_drop,
+                       uint64_t seed, uint32_t site, void* stream);
+int bist_ffn_bwd(const void* dy, const void* x, const void* w1T, const void* w2T, const void* hidden, void* dx,
+                 float* dW1, float* db1, float* dW2, float* db2, int64_t rows, int64_t d, int64_t d_ff,
+                 int64_t d_out, void* ws, size_t ws_bytes, int dtype, float p_drop, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
