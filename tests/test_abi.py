@@ -77,8 +77,8 @@ def test_no_cpu_fallback():
         m(b, synth.make_encoded_query(1, 2, 5, 64))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         LayerNorm(8)(torch.zeros(2, 8))
-    with pytest.raises(NotImplementedError):
-        LayerNorm(8).train() and SublayerConnection(8, 0.1).train()(torch.zeros(2, 8), lambda x: x)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):       # train() mode runs the CUDA path too, never torch's
+        SublayerConnection(8, 0.1).train()(torch.zeros(2, 8), lambda x: x)
 
 
 def test_shard_rows_covers_batch_exactly():
