@@ -141,3 +141,48 @@ def shard_rows(n_rows, world_size, rank):
     base, rem = divmod(n_rows, world_size)
     start = rank * base + min(rank, rem)
     return start, start + base + (1 if rank < rem else 0)
+
+
+# ---------------------------------------------------------------------------------------------- decoder side (§8(f) row 1)
+def fill_params(shapes, seed):
+    """Seeded values for a {name: shape} table (a ``state_dict`` of the decoder side), drawn in sorted-name order
+    so that the reference model in oracle/make_golden.py and the mirror modules in tests/ get the same weights:
+    matrices xavier-uniform, LayerNorm gains 1 + N(0, 0.1), offsets N(0, 0.1), other vectors N(0, 0.02)."""
+    rs = np.random.RandomState(seed)
+    out = {}
+    for name in sorted(shapes):
+        shp = tuple(shapes[name])
+        if len(shp) > 1:
+            a = math.sqrt(6.0 / (shp[0] + shp[1]))
+            v = rs.uniform(-a, a, size=shp)
+        elif name.endswith("a_2"):
+            v = 1.0 + 0.1 * rs.standard_normal(shp)
+        elif name.endswith("b_2"):
+            v = 0.1 * rs.standard_normal(shp)
+        else:
+            v = 0.02 * rs.standard_normal(shp)
+        out[name] = torch.from_numpy(v.astype(np.float32))
+    return out
+
+
+def _pad_mask(rs, B, L):
+    n = rs.randint(int(math.ceil(L / 2)), L + 1, size=B)
+    n[0] = L
+    return torch.from_numpy(np.arange(L)[None, :] < n[:, None]).unsqueeze(1)       # [B,1,L] bool
+
+
+def make_decoder_inputs(seed, B, Lq, Lh, Lc, Lt, Ta, T, S, d):
+    """Seeded inputs of MultimodalDecoder8.forward (decoder.py:107): a batch with the masks of data/dataset.py:59-99
+    (trg_mask = pad & causal, make_std_mask :101-104) and the ft dict the text / video encoders would have filled
+    (N(0,1) activations).  Returns (batch, ft, encoded_tgt)."""
+    rs = np.random.RandomState(seed)
+    b = SynthBatch()
+    b.query_mask, b.his_mask, b.cap_mask = _pad_mask(rs, B, Lq), _pad_mask(rs, B, Lh), _pad_mask(rs, B, Lc)
+    b.audio_mask, b.temporal_mask = _pad_mask(rs, B, Ta), _pad_mask(rs, B, T)
+    b.trg_mask = _pad_mask(rs, B, Lt) & torch.tril(torch.ones(Lt, Lt, dtype=torch.bool)).unsqueeze(0)   # [B,Lt,Lt]
+
+    def act(*shape):
+        return torch.from_numpy(rs.standard_normal(shape).astype(np.float32))
+    ft = {"encoded_query": act(B, Lq, d), "encoded_his": act(B, Lh, d), "encoded_cap": act(B, Lc, d),
+          "encoded_audio": act(B, Ta, d), "spatiotemporal_ft": act(B, T, S, d)}
+    return b, ft, act(B, Lt, d)

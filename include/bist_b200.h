@@ -294,6 +294,14 @@ int bist_ffn_bwd(const void* dy, const void* x, const void* w1T, const void* w2T
                  float* dW1, float* db1, float* dW2, float* db2, int64_t rows, int64_t d, int64_t d_ff,
                  int64_t d_out, void* ws, size_t ws_bytes, int dtype, float p_drop, void* stream);
 
+/* Softmax gate of MultimodalDecoder8 (decoder.py:150-181): out[r,:] = sum_k softmax(logits[r,0:K])_k * src[k][r,:],
+ * K <= 4 streams of [R, d] (dtype); logits fp32 [R, K] come from the gate Linear (bist_linear_fwd with an fp32
+ * output).  Backward: d_src[k] = p_k * d_out, d_logits = softmax backward of dp_k = <d_out, src[k]>. */
+int bist_gate_combine_fwd(const void* const* src, const float* logits, void* out, int64_t R, int64_t d, int K,
+                          int dtype, void* stream);
+int bist_gate_combine_bwd(const void* d_out, const void* const* src, const float* logits, void* const* d_src,
+                          float* d_logits, int64_t R, int64_t d, int K, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

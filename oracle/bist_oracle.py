@@ -211,3 +211,123 @@ def video_path(P, h, fts, encoded_query, query_mask, temporal_mask, n_blocks,
         out["spatial_ft"] = layer_norm(cur_t2s, P[dec_pre + "spatial_out_norm.a_2"],
                                        P[dec_pre + "spatial_out_norm.b_2"])        # decoder.py:129
     return out
+
+
+# ----------------------------------------------------------------------------- §8(f) row 1: decoder-side layers
+# Functional restatement of CapEncoderLayer / AudioEncoderLayer (encoder.py:203-235), MultimodalDecoderLayer12
+# (decoder.py:11-60) and MultimodalDecoder8 (decoder.py:62-186) for enc_st_combine == 'none' (the configuration of
+# train_configs.py:40 / exec.sh; the other modes overwrite ft['spatiotemporal_ft'] and only run with one block,
+# SURVEY.md §8 a2).  `cfg` carries the args fields the reference reads: nb_venc_blocks, nb_cenc_blocks,
+# nb_aenc_blocks, enc_vc_combine, include_caption, dec_st_combine, t2s, s2t.  `masks`: trg, his, query, cap, audio,
+# temporal.  Pinned by tests/golden/decoder_*.npz (outputs of the unmodified reference, oracle/make_golden.py).
+def memory_encoder_layer(P, pre, h, x, mem, self_mask, mem_mask, drop=None):
+    """CapEncoderLayer.forward / AudioEncoderLayer.forward: self attention, attention over the memory, FFN."""
+    x = sublayer(P, pre + "sublayer.0.", x, lambda z: mha(P, pre + "attn.0.", h, z, z, z, self_mask, drop)[0], drop)
+    x = sublayer(P, pre + "sublayer.1.", x, lambda z: mha(P, pre + "attn.1.", h, z, mem, mem, mem_mask, drop)[0], drop)
+    return sublayer(P, pre + "sublayer.2.", x, lambda z: ffn(P, pre + "ff.", z, drop), drop)
+
+
+def decoder_memories(cfg):
+    """The attention memories MultimodalDecoderLayer12 walks after self / history / query attention, as
+    (ft key, mask name) in order, and whether the two video streams are attended in parallel (decoder.py:27-57)."""
+    v, c, a = cfg["nb_venc_blocks"] > 0, cfg["nb_cenc_blocks"] > 0, cfg.get("nb_aenc_blocks", 0) > 0
+    if v and c and cfg.get("enc_vc_combine", "none") != "none":
+        return [("encoded_ft", "query")], False                                    # :28-30
+    mems = []
+    if cfg["include_caption"] != "none":                                           # :32-37
+        mems.append(("cap_ft", "query") if c else ("encoded_cap", "cap"))
+    parallel = False
+    if v:                                                                          # :38-54 (enc_st_combine == 'none')
+        if cfg["dec_st_combine"] == "seq":
+            if cfg["s2t"]:
+                mems.append(("temporal_ft", "query"))
+            if cfg["t2s"]:
+                mems.append(("spatial_ft", "query"))
+        else:
+            mems += [("temporal_ft", "query"), ("spatial_ft", "query")]
+            parallel = True
+    if a:                                                                          # :55-57
+        mems.append(("audio_ft", "query"))
+    return mems, parallel
+
+
+def decoder_layer12(P, pre, h, cfg, x, ft, masks, drop=None):
+    """MultimodalDecoderLayer12.forward (decoder.py:20-60)."""
+    def att(i, z, mem, mask):
+        return sublayer(P, f"{pre}sublayer.{i}.", z,
+                        lambda y: mha(P, f"{pre}attn.{i}.", h, y, y if mem is None else mem, y if mem is None else mem,
+                                      mask, drop)[0], drop)
+    x = att(0, x, None, masks["trg"])                                              # :21
+    x = att(1, x, ft["encoded_his"], masks["his"])                                 # :22
+    x = att(2, x, ft["encoded_query"], masks["query"])                             # :23
+    mems, parallel = decoder_memories(cfg)
+    i = 3
+    for key, mname in mems:
+        if parallel and key == "temporal_ft":                                      # :47-52 both from the same input
+            t_x = att(i, x, ft["temporal_ft"], masks["query"])
+            s_x = att(i + 1, x, ft["spatial_ft"], masks["query"])
+            x = t_x + s_x
+            i += 2
+        elif parallel and key == "spatial_ft":
+            continue
+        else:
+            x = att(i, x, ft[key], masks[mname])
+            i += 1
+    return sublayer(P, f"{pre}sublayer.{i}.", x, lambda z: ffn(P, pre + "ff.", z, drop), drop)   # :58
+
+
+def vc_combine(P, pre, cfg, ft):
+    """encoded_ft of decoder.py:137-167 (enc_st_combine == 'none'): sum, or softmax gate over the streams."""
+    mode = cfg.get("enc_vc_combine", "none")
+    a = cfg.get("nb_aenc_blocks", 0) > 0
+    if mode == "sum":
+        return ft["temporal_ft"] + ft["spatial_ft"] + ft["cap_ft"]                 # :141
+    temp = [ft["encoded_query"], ft["cap_ft"]]                                     # :148
+    if cfg["t2s"]:
+        temp.append(ft["spatial_ft"])
+    if cfg["s2t"]:
+        temp.append(ft["temporal_ft"])
+    if a:
+        temp.append(ft["audio_ft"])
+    score = torch.softmax(linear(torch.cat(temp, dim=-1), P[pre + "vc_combine_W.weight"], P[pre + "vc_combine_W.bias"]), dim=-1)
+    if cfg["t2s"] and cfg["s2t"]:
+        streams = ["temporal_ft", "spatial_ft", "cap_ft"]                          # :157-160
+    elif not cfg["t2s"]:
+        streams = ["temporal_ft", "cap_ft"]
+    else:
+        streams = ["spatial_ft", "cap_ft"]
+    out = sum(score[:, :, i:i + 1] * ft[k] for i, k in enumerate(streams))
+    if a:
+        out = out + score[:, :, 3:4] * ft["audio_ft"]                              # :167 (index 3, as the reference)
+    return out
+
+
+def multimodal_decoder8(P, pre, h, cfg, ft, x, masks, n_blocks, drop=None):
+    """MultimodalDecoder8.forward (decoder.py:107-186), enc_st_combine == 'none'.  ft must hold encoded_query,
+    encoded_his, (encoded_cap), (spatiotemporal_ft), (encoded_audio); returns ft with decoded_text added."""
+    ft = dict(ft)
+    eq = ft["encoded_query"]
+    cur = {"t2s": eq, "s2t": eq, "audio": eq, "cap": eq}                           # :108-112
+    v, c, a = cfg["nb_venc_blocks"] > 0, cfg["nb_cenc_blocks"] > 0, cfg.get("nb_aenc_blocks", 0) > 0
+    for blk in range(n_blocks):
+        if v:                                                                      # :115-129
+            cur["t2s"], cur["s2t"] = vid_encoder_layer4(
+                P, f"{pre}v_layers.{blk}.", h, cur["t2s"], cur["s2t"], ft["spatiotemporal_ft"], masks["query"],
+                masks["temporal"], t2s=bool(cfg["t2s"]), s2t=bool(cfg["s2t"]), drop=drop)
+            if cfg["s2t"]:
+                ft["temporal_ft"] = layer_norm(cur["s2t"], P[pre + "temporal_out_norm.a_2"], P[pre + "temporal_out_norm.b_2"])
+            if cfg["t2s"]:
+                ft["spatial_ft"] = layer_norm(cur["t2s"], P[pre + "spatial_out_norm.a_2"], P[pre + "spatial_out_norm.b_2"])
+        if c:                                                                      # :130-132
+            cur["cap"] = memory_encoder_layer(P, f"{pre}c_layers.{blk}.", h, cur["cap"], ft["encoded_cap"],
+                                              masks["query"], masks["cap"], drop)
+            ft["cap_ft"] = layer_norm(cur["cap"], P[pre + "cap_out_norm.a_2"], P[pre + "cap_out_norm.b_2"])
+        if a:                                                                      # :133-135
+            cur["audio"] = memory_encoder_layer(P, f"{pre}a_layers.{blk}.", h, cur["audio"], ft["encoded_audio"],
+                                                masks["query"], masks["audio"], drop)
+            ft["audio_ft"] = layer_norm(cur["audio"], P[pre + "a_out_norm.a_2"], P[pre + "a_out_norm.b_2"])
+        if v and c and cfg.get("enc_vc_combine", "none") in ("sum", "dyn"):        # :137-167
+            ft["encoded_ft"] = vc_combine(P, pre, cfg, ft)
+        x = decoder_layer12(P, f"{pre}layers.{blk}.", h, cfg, x, ft, masks, drop)  # :182
+    ft["decoded_text"] = layer_norm(x, P[pre + "norm.a_2"], P[pre + "norm.b_2"])   # :185
+    return ft

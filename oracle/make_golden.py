@@ -150,6 +150,51 @@ def run_modules_fixture(modules):
     return out
 
 
+# ---- decoder side: MultimodalDecoder8 with its caption / audio / decoder layers ----------
+DEC_CASES = {
+    # exec.sh-like AVSD setting: caption encoder + softmax gate over (temporal, spatial, caption)
+    "avsd_dyn":     dict(seed=31, B=2, Lq=5, Lh=9, Lc=7, Lt=6, Ta=4, T=4, S=3, d=64, h=4, n_blocks=2, nb_cenc=2, nb_aenc=0,
+                         vc="dyn", cap="summary", dec_st="seq", t2s=1, s2t=1),
+    "audio_dyn":    dict(seed=32, B=2, Lq=4, Lh=6, Lc=5, Lt=5, Ta=6, T=3, S=4, d=64, h=4, n_blocks=2, nb_cenc=2, nb_aenc=2,
+                         vc="dyn", cap="summary", dec_st="seq", t2s=1, s2t=1),
+    "vc_sum":       dict(seed=33, B=2, Lq=4, Lh=6, Lc=5, Lt=5, Ta=3, T=3, S=4, d=32, h=2, n_blocks=1, nb_cenc=1, nb_aenc=0,
+                         vc="sum", cap="summary", dec_st="seq", t2s=1, s2t=1),
+    "nocap_seq":    dict(seed=34, B=3, Lq=5, Lh=7, Lc=4, Lt=6, Ta=3, T=4, S=3, d=64, h=8, n_blocks=2, nb_cenc=0, nb_aenc=0,
+                         vc="none", cap="none", dec_st="seq", t2s=1, s2t=1),
+    # (include_caption != 'none' with nb_cenc_blocks == 0 and video blocks indexes one attention past what
+    #  mtn.py:139-150 allocates: the reference itself raises IndexError, so there is no such case)
+    "nocap_par":    dict(seed=35, B=2, Lq=5, Lh=7, Lc=6, Lt=4, Ta=3, T=4, S=3, d=64, h=4, n_blocks=1, nb_cenc=0, nb_aenc=0,
+                         vc="none", cap="none", dec_st="par", t2s=1, s2t=1),
+    "cenc_aenc":    dict(seed=36, B=2, Lq=5, Lh=7, Lc=6, Lt=4, Ta=5, T=4, S=3, d=64, h=4, n_blocks=1, nb_cenc=1, nb_aenc=1,
+                         vc="none", cap="summary", dec_st="seq", t2s=1, s2t=1),
+    "s2t_only_dyn": dict(seed=37, B=2, Lq=5, Lh=7, Lc=6, Lt=4, Ta=5, T=4, S=3, d=64, h=4, n_blocks=1, nb_cenc=1, nb_aenc=0,
+                         vc="dyn", cap="summary", dec_st="seq", t2s=0, s2t=1),
+}
+
+
+def dec_args(c):
+    return argparse.Namespace(
+        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=c["nb_aenc"],
+        d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft="query", auto_encoder=0,
+        t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none", enc_vc_combine=c["vc"],
+        dec_st_combine=c["dec_st"], include_caption=c["cap"], mask_unk=1)
+
+
+def run_decoder_case(mtn, c):
+    torch.manual_seed(0)
+    model = mtn.make_model(64, 64, dec_args(c), ft_sizes=[48, 16]).eval()
+    dec = model.mutlimodal_decoder
+    shapes = {k: tuple(v.shape) for k, v in dec.state_dict().items()}
+    dec.load_state_dict(synth.fill_params(shapes, c["seed"]), strict=True)
+    b, ft, x = synth.make_decoder_inputs(c["seed"], c["B"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["Ta"], c["T"], c["S"], c["d"])
+    with torch.no_grad():
+        out_ft = dec(b, dict(ft), x)                                   # decoder.py:107-186, as mtn.py:61 calls it
+    out = {k: out_ft[k].numpy().copy() for k in ("decoded_text", "temporal_ft", "spatial_ft", "cap_ft", "audio_ft",
+                                                  "encoded_ft") if k in out_ft}
+    out["param_shapes"] = np.array(json.dumps(sorted([k, list(v)] for k, v in shapes.items())))
+    return out
+
+
 def main():
     mtn, modules = import_reference()
     gold = os.path.join(ROOT, "tests", "golden")
@@ -160,6 +205,12 @@ def main():
         path = os.path.join(gold, f"path_{name}.npz")
         np.savez_compressed(path, **out)
         print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")
+    for name, c in DEC_CASES.items():
+        out = run_decoder_case(mtn, c)
+        out["meta"] = np.array(json.dumps(c))
+        path = os.path.join(gold, f"decoder_{name}.npz")
+        np.savez_compressed(path, **out)
+        print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB", sorted(k for k in out if k not in ("meta", "param_shapes")))
     path = os.path.join(gold, "modules.npz")
     np.savez_compressed(path, **run_modules_fixture(modules))
     print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")
