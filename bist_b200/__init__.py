@@ -12,6 +12,8 @@ _LAZY = {
     "PositionwiseFeedForward": "modules", "clones": "modules",
     "VidEncoder8": "encoder", "VidEncoderLayer4": "encoder", "VideoPath": "encoder",
     "set_precision": "encoder", "GraphedVideoPath": "encoder",
+    "CapEncoderLayer": "encoder", "AudioEncoderLayer": "encoder",
+    "MultimodalDecoderLayer12": "decoder", "MultimodalDecoder8": "decoder", "make_decoder": "decoder",
 }
 
 

@@ -507,3 +507,34 @@ class GraphedVideoPath:
     def __call__(self, b, encoded_query):
         self.load(b, encoded_query)
         return self.replay()
+
+
+class _MemoryEncoderLayer(nn.Module):
+    """Self attention over the query-length stream, attention over one encoded memory, FFN — the common body of
+    CapEncoderLayer and AudioEncoderLayer (encoder.py:203-235); compositions of the library-backed blocks."""
+    stream, memory, memory_mask = None, None, None
+
+    def __init__(self, size, attn, nb_attn, ff, dropout):
+        super(_MemoryEncoderLayer, self).__init__()
+        self.size = size
+        self.attn = clones(attn, nb_attn)
+        self.ff = ff
+        self.sublayer = clones(SublayerConnection(size, dropout), nb_attn + 1)
+
+    def forward(self, in_ft, ft, b):
+        x = in_ft[self.stream]
+        mem, mem_mask = ft[self.memory], getattr(b, self.memory_mask)
+        x = self.sublayer[0](x, lambda y: self.attn[0](y, y, y, b.query_mask))
+        x = self.sublayer[1](x, lambda y: self.attn[1](y, mem, mem, mem_mask))
+        in_ft[self.stream] = self.sublayer[2](x, self.ff)
+        return in_ft
+
+
+class CapEncoderLayer(_MemoryEncoderLayer):
+    "encoder.py:203-218 — in_ft['cap'] attends over ft['encoded_cap'] (b.cap_mask)."
+    stream, memory, memory_mask = 'cap', 'encoded_cap', 'cap_mask'
+
+
+class AudioEncoderLayer(_MemoryEncoderLayer):
+    "encoder.py:220-235 — in_ft['audio'] attends over ft['encoded_audio'] (b.audio_mask)."
+    stream, memory, memory_mask = 'audio', 'encoded_audio', 'audio_mask'

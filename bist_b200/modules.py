@@ -332,6 +332,10 @@ class MultiHeadedAttention(nn.Module):
     def forward(self, query, key, value, mask=None):
         _lib.require_cuda(query, key, value, self.linears[0].weight)
         dt = _lib.dtype_code(query.dtype)
+        if key.dtype != query.dtype:                 # e.g. fp32 video streams attended by a bf16 decoder state
+            key = key.to(query.dtype)
+        if value.dtype != query.dtype:
+            value = value.to(query.dtype)
         Bp, Lq, d_in = query.shape
         Lk = key.shape[1]
         d = self.h * self.d_k
@@ -400,3 +404,77 @@ class PositionwiseFeedForward(nn.Module):
                                            _lib.ptr(self.w_2.bias), _lib.ptr(y), rows, d, d_ff, d_out,
                                            _lib.ptr(ws), ws.numel(), dt, _lib.stream_ptr()), "bist_ffn_fwd")
         return y
+
+
+class _LinearFn(torch.autograd.Function):
+    """nn.Linear through the library (bist_linear_fwd / bist_linear_bwd): y = x W^T + b in x's dtype."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, cache):
+        x = x.contiguous()
+        dt = _lib.dtype_code(x.dtype)
+        N, K = weight.shape
+        M = x.numel() // K
+        w = weight.detach() if dt == _lib.F32 else cache.get(weight)
+        y = torch.empty(x.shape[:-1] + (N,), dtype=x.dtype, device=x.device)
+        _lib.check(_lib.lib().bist_linear_fwd(_lib.ptr(x), _lib.ptr(w), _lib.ptr(bias), None, _lib.ptr(y), M, N, K, 0,
+                                              dt, dt, dt, _lib.stream_ptr()), "bist_linear_fwd")
+        ctx.save_for_backward(x, weight)
+        ctx.cache = cache
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        dt = _lib.dtype_code(x.dtype)
+        N, K = weight.shape
+        M = x.numel() // K
+        gy = gy.to(x.dtype).contiguous()
+        wT = ctx.cache.get(weight, x.dtype, transposed=True)
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        block = torch.zeros(N * K + N, dtype=torch.float32, device=x.device)
+        _lib.check(_lib.lib().bist_linear_bwd(_lib.ptr(gy), _lib.ptr(x), _lib.ptr(wT), _lib.ptr(dx), _lib.ptr(block),
+                                              _lib.ptr(block[N * K:]), M, N, K, dt, dt, dt, dt, _lib.stream_ptr()),
+                   "bist_linear_bwd")
+        return dx, block[:N * K].view(N, K), block[N * K:], None
+
+
+class _GateFn(torch.autograd.Function):
+    """out = sum_k softmax(logits)_k * src_k (decoder.py:155-167) — bist_gate_combine_fwd / bwd."""
+
+    @staticmethod
+    def forward(ctx, logits, *srcs):
+        logits = logits.float().contiguous()
+        srcs = tuple(s.contiguous() for s in srcs)
+        d = srcs[0].shape[-1]
+        R = srcs[0].numel() // d
+        out = torch.empty_like(srcs[0])
+        _lib.check(_lib.lib().bist_gate_combine_fwd(_ptr_array(srcs), _lib.ptr(logits), _lib.ptr(out), R, d, len(srcs),
+                                                    _lib.dtype_code(out.dtype), _lib.stream_ptr()), "bist_gate_combine_fwd")
+        ctx.save_for_backward(logits, *srcs)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        logits, *srcs = ctx.saved_tensors
+        g = g.to(srcs[0].dtype).contiguous()
+        d = srcs[0].shape[-1]
+        R = srcs[0].numel() // d
+        dsrc = [torch.empty_like(s) for s in srcs]
+        dlog = torch.empty_like(logits)
+        _lib.check(_lib.lib().bist_gate_combine_bwd(_lib.ptr(g), _ptr_array(srcs), _lib.ptr(logits), _ptr_array(dsrc),
+                                                    _lib.ptr(dlog), R, d, len(srcs), _lib.dtype_code(g.dtype),
+                                                    _lib.stream_ptr()), "bist_gate_combine_bwd")
+        return (dlog,) + tuple(dsrc)
+
+
+def linear(x, lin, cache):
+    """``lin(x)`` for an nn.Linear through the library, with autograd."""
+    _lib.require_cuda(x, lin.weight)
+    return _LinearFn.apply(x, lin.weight, lin.bias, cache)
+
+
+def gate_combine(logits, srcs):
+    """softmax(logits) over the last dim, then the weighted sum of the K streams (each [..., d])."""
+    _lib.require_cuda(logits, *srcs)
+    return _GateFn.apply(logits, *srcs)
