@@ -30,6 +30,8 @@ bool pdl_enabled() {
   return on;
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static std::atomic<const unsigned long long*> g_drop_step{nullptr};
+const unsigned long long* dropout_step_ptr() { return g_drop_step.load(std::memory_order_relaxed); }
 
 // ---- per-launch event timing (off by default) ---------------------------------------------
 struct ProfRec { const char* tag; cudaEvent_t e0, e1; };
@@ -70,6 +72,11 @@ extern "C" {
 int bist_version(void) { return BIST_B200_VERSION; }
 const char* bist_last_error(void) { return g_err; }
 int64_t bist_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int bist_set_dropout_step(const uint64_t* device_counter) {
+  g_drop_step.store(reinterpret_cast<const unsigned long long*>(device_counter));
+  return 0;
+}
 
 int bist_prof_enable(int on) {
   g_prof_on.store(on ? 1 : 0);

@@ -140,10 +140,12 @@ __device__ __forceinline__ float warp_max(float v) {
 // through bist_dropout_mask).  p == 0 (thresh == 0) disables a site.
 struct DropCfg {
   unsigned long long seed = 0;
+  const unsigned long long* step = nullptr;  // optional device counter added to the seed at run time (bist_set_dropout_step)
   uint32_t thresh = 0;   // floor(p * 2^32)
   uint32_t site = 0;
   float scale = 1.f;     // 1 / (1 - p)
 };
+const unsigned long long* dropout_step_ptr();   // api.cu
 static inline DropCfg make_drop(float p, unsigned long long seed, uint32_t site) {
   DropCfg c;
   if (p > 0.f) {
@@ -151,6 +153,7 @@ static inline DropCfg make_drop(float p, unsigned long long seed, uint32_t site)
     c.thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
     c.scale = 1.f / (1.f - p);
     c.seed = seed; c.site = site;
+    c.step = dropout_step_ptr();
   }
   return c;
 }
@@ -168,7 +171,9 @@ __host__ __device__ __forceinline__ uint32_t drop_hash(unsigned long long seed, 
 }
 // multiplier of element idx: 0 (dropped) or 1/(1-p)
 __device__ __forceinline__ float drop_mul(const DropCfg& c, unsigned long long idx) {
-  return (c.thresh == 0u || drop_hash(c.seed, c.site, idx) >= c.thresh) ? c.scale : 0.f;
+  if (c.thresh == 0u) return c.scale;
+  const unsigned long long seed = c.step ? c.seed + __ldg(c.step) : c.seed;   // a CUDA-graph replay advances *step
+  return drop_hash(seed, c.site, idx) >= c.thresh ? c.scale : 0.f;
 }
 #endif
 

@@ -217,6 +217,11 @@ typedef struct {
   float p_attn, p_sublayer, p_ffn;
   uint64_t seed;
 } bist_dropout_t;
+
+/* Dropout under CUDA-graph replay: when a device counter is registered, every dropout site hashes with
+ * seed + *device_counter, read by the kernels at run time — a captured training step that increments the counter as
+ * its first node draws fresh masks on every replay (bist_b200/graph.py).  NULL unregisters.  Process-wide. */
+int bist_set_dropout_step(const uint64_t* device_counter);
 /* out[i] = multiplier (0 or 1/(1-p)) of element i of `site`, fp32 [n] (tests inject these into the oracle). */
 int bist_dropout_mask(uint64_t seed, uint32_t site, float p, int64_t n, float* out, void* stream);
 

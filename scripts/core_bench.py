@@ -1,0 +1,81 @@
+"""Training step of the model core at config-3 shapes: VidEncoder8 projection + MultimodalDecoder8
+(3 video blocks, 3 caption-encoder blocks, softmax gate, 3 decoder layers) — everything MTN.forward runs except the
+embeddings / text encoder (their outputs are synthetic leaf tensors here) and the generator + loss (an MSE stand-in).
+
+    python scripts/core_bench.py [--precision bf16|fp32] [--steps 10] [--tags]
+"""
+import argparse
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bist_b200 import _lib, synth  # noqa: E402
+from bist_b200.core import BiSTCore, core_inputs  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--eval", action="store_true")
+    ap.add_argument("--tags", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="forward+loss+backward as one CUDA graph (bist_b200/graph.py)")
+    a = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    m = BiSTCore(precision=a.precision).to(dev)
+    m.train(not a.eval)
+    b, ft, x, tgt = core_inputs(1, dev, a.precision)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-4, fused=True)
+    L = _lib.lib()
+
+    def loss_fn():
+        out = m(b, dict(ft), x)
+        return ((out["decoded_text"].float() - tgt) ** 2).mean()
+
+    if a.graph:
+        from bist_b200.graph import GraphedTrainStep
+        graphed = GraphedTrainStep(loss_fn, list(m.parameters()) + list(ft.values()) + [x])
+
+        def step():
+            graphed()
+            opt.step()
+    else:
+        def step():
+            opt.zero_grad(set_to_none=True)
+            loss_fn().backward()
+            opt.step()
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    n0 = L.bist_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / a.steps
+    print("core train step: %.3f ms (%d turns/s), host enqueue %.3f ms, %d library launches/step" % (
+        ms, 64 / ms * 1e3, (t1 - t0) / a.steps * 1e3, (L.bist_launch_count() - n0) // a.steps))
+    if a.tags:
+        import ctypes
+        L.bist_prof_enable(1)
+        for _ in range(3):
+            step()
+        buf = ctypes.create_string_buffer(1 << 16)
+        _lib.check(L.bist_prof_collect(buf, len(buf)), "prof")
+        L.bist_prof_enable(0)
+        rows = [ln.split(",") for ln in buf.value.decode().strip().splitlines()]
+        for tag, n, tot in sorted(rows, key=lambda r: -float(r[2])):
+            print("%-22s n=%6.1f  ms/step=%.4f  us/launch=%.1f" % (tag, int(n) / 3, float(tot) / 3, 1e3 * float(tot) / int(n)))
+
+
+if __name__ == "__main__":
+    main()
