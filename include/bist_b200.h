@@ -307,6 +307,36 @@ int bist_gate_combine_fwd(const void* const* src, const float* logits, void* out
 int bist_gate_combine_bwd(const void* d_out, const void* const* src, const float* logits, void* const* d_src,
                           float* d_logits, int64_t R, int64_t d, int K, int dtype, void* stream);
 
+/* ---- text side and generator ------------------------------------------------------------
+ * Embeddings + PositionalEncoding (modules.py:115-141): out[r,:] = dropout(lut[idx[r],:] * sqrt(d) + pe[r % L,:]),
+ * rows = B*L token positions, lut fp32 [vocab, d], pe fp32 [>= L, d], out in out_dtype.  Backward scatter-adds
+ * sqrt(d) * mask * dy[r,:] into dlut[idx[r],:] (fp32, accumulated). */
+int bist_embed_fwd(const int64_t* idx, const float* lut, const float* pe, void* out, int64_t rows, int64_t L,
+                   int64_t d, int64_t vocab, float p_drop, uint64_t seed, uint32_t site, int out_dtype, void* stream);
+int bist_embed_bwd(const int64_t* idx, const void* dy, float* dlut, int64_t rows, int64_t d, float p_drop,
+                   uint64_t seed, uint32_t site, int dy_dtype, void* stream);
+
+/* Pointer attention of the generators (generator.py:62-63,104-114): one head over projected q [B,Lt,d] / k [B,Ls,d]
+ * (scale 1/sqrt(d)), key mask [B,Ls] (0 = masked -> -1e9) or NULL; P [B,Lt,Ls] fp32 are the pointer probabilities,
+ * tvec [B,Lt,d] = P . v with v the RAW encoded text.  Backward takes dP and dtvec, returns dq, dk, dv. */
+int bist_ptr_attn_fwd(const void* q, const void* k, const void* v, const uint8_t* mask, float* P, void* tvec,
+                      int64_t B, int64_t Lt, int64_t Ls, int64_t d, int dtype, void* stream);
+int bist_ptr_attn_bwd(const float* dP, const void* dtvec, const void* q, const void* k, const void* v, const float* P,
+                      void* dq, void* dk, void* dv, int64_t B, int64_t Lt, int64_t Ls, int64_t d, int dtype,
+                      void* stream);
+
+/* Generator + label-smoothed loss, forward AND gradient in one pass over the logits (generator.py:11-127,
+ * label_smoothing.py:20-30, optimize.py:46-82).  Z [R, V] (dtype) = decoded_text . E^T on entry; when want_grad it is
+ * overwritten with d(sum_r row_loss[r]) / dZ.  n_ptr in {0,1,2} pointer sources: P[i] [R, Ls[i]] fp32 (from
+ * bist_ptr_attn_fwd), text[i] [R / Lt, Ls[i]] token ids, dP[i] out; sw [R, n_ptr+1] fp32 switch logits (softmax inside,
+ * the vocabulary distribution's weight LAST), dsw out; both NULL with n_ptr == 0 (plain log_softmax: the auto-encoder
+ * heads).  target [R] (pad rows contribute nothing; NULL = inference), row_loss [R] fp32 un-normalised KL per row
+ * with smoothing mass smoothing/(V-2) and the pad column zeroed; logp (optional) [R, V] fp32 = log p_out. */
+int bist_genloss_fwd_bwd(void* Z, float* logp, int n_ptr, const float* const* P, float* const* dP,
+                         const int64_t* const* text, const int64_t* Ls, const float* sw, float* dsw,
+                         const int64_t* target, float* row_loss, int64_t R, int64_t V, int64_t Lt, int64_t pad,
+                         float smoothing, int want_grad, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
