@@ -186,3 +186,30 @@ def make_decoder_inputs(seed, B, Lq, Lh, Lc, Lt, Ta, T, S, d):
     ft = {"encoded_query": act(B, Lq, d), "encoded_his": act(B, Lh, d), "encoded_cap": act(B, Lc, d),
           "encoded_audio": act(B, Ta, d), "spatiotemporal_ft": act(B, T, S, d)}
     return b, ft, act(B, Lt, d)
+
+
+def _tokens(rs, B, L, vocab, unk_rate=0.0):
+    ids = rs.randint(4, vocab, size=(B, L)).astype(np.int64)
+    if unk_rate > 0:
+        ids[rs.uniform(size=(B, L)) < unk_rate] = 0                   # <unk>: masked out of the pointers (mask_unk)
+    n = rs.randint(int(math.ceil(L / 2)), L + 1, size=B)
+    n[0] = L
+    ids[np.arange(L)[None, :] >= n[:, None]] = PAD_ID
+    return torch.from_numpy(ids)
+
+
+def make_full_batch(seed, B, T, S, D, Lq, Lh, Lc, Lt, vocab):
+    """Seeded batch with every field MTN.forward and SimpleLossCompute read (data/dataset.py:59-104): token ids of the
+    query / history / caption / shifted target (pad id 1 on the tails, a few <unk>=0 in the sources), their masks,
+    trg_mask = pad & causal, ntokens / qntokens, and the video features of make_batch."""
+    vb = make_batch(seed, B, T, S, D, Lq)
+    rs = np.random.RandomState(seed + 7919)
+    b = SynthBatch()
+    b.fts, b.temporal_mask = vb.fts, vb.temporal_mask
+    b.query, b.his, b.cap = _tokens(rs, B, Lq, vocab, 0.1), _tokens(rs, B, Lh, vocab, 0.05), _tokens(rs, B, Lc, vocab, 0.05)
+    tgt = _tokens(rs, B, Lt + 1, vocab)
+    b.trg, b.trg_y = tgt[:, :-1].contiguous(), tgt[:, 1:].contiguous()
+    b.query_mask, b.his_mask, b.cap_mask = ((t != PAD_ID).unsqueeze(-2) for t in (b.query, b.his, b.cap))
+    b.trg_mask = (b.trg != PAD_ID).unsqueeze(-2) & torch.tril(torch.ones(Lt, Lt, dtype=torch.bool)).unsqueeze(0)
+    b.ntokens, b.qntokens = (b.trg_y != PAD_ID).sum(), (b.query != PAD_ID).sum()
+    return b

@@ -331,3 +331,102 @@ def multimodal_decoder8(P, pre, h, cfg, ft, x, masks, n_blocks, drop=None):
         x = decoder_layer12(P, f"{pre}layers.{blk}.", h, cfg, x, ft, masks, drop)  # :182
     ft["decoded_text"] = layer_norm(x, P[pre + "norm.a_2"], P[pre + "norm.b_2"])   # :185
     return ft
+
+
+# ----------------------------------------------------------------------------- §8(f) row 2: text side, generators, loss
+# Embeddings / PositionalEncoding (modules.py:115-141), the LayerNorm-only text Encoder (encoder.py:11-40),
+# Generator / PointerGenerator / MultiPointerGenerator (generator.py), LabelSmoothing (label_smoothing.py),
+# SimpleLossCompute (optimize.py:36-94) and MTN.forward (mtn.py:31-61).  Pinned by tests/golden/model_*.npz.
+def positional_table(max_len, d):
+    """modules.py:127-136 (the registered buffer ``pe`` without its batch dimension)."""
+    pe = torch.zeros(max_len, d)
+    position = torch.arange(0., max_len).unsqueeze(1)
+    div_term = torch.exp(torch.arange(0., d, 2) * -(math.log(10000.0) / d))
+    pe[:, 0::2] = torch.sin(position * div_term)
+    pe[:, 1::2] = torch.cos(position * div_term)
+    return pe
+
+
+def embed(P, pre, ids, drop=None, site=None):
+    """query_embed = Sequential(Embeddings, PositionalEncoding) (mtn.py:78-80): lut(x) * sqrt(d) + pe, then dropout."""
+    lut = P[pre + "0.lut.weight"]
+    d = lut.shape[1]
+    x = lut[ids] * math.sqrt(d) + positional_table(ids.shape[1], d).unsqueeze(0)
+    return _apply(drop, site, x)
+
+
+def pointer_probs(P, pre, x, encoded_text, text_mask):
+    """pointer_attn(x, text, text, mask).attn of a 1-head MultiHeadedAttention (generator.py:62-63): [B, Lt, Ls]."""
+    q = linear(x, P[pre + "linears.0.weight"], P[pre + "linears.0.bias"])
+    k = linear(encoded_text, P[pre + "linears.1.weight"], P[pre + "linears.1.bias"])
+    s = q.matmul(k.transpose(-2, -1)) / math.sqrt(q.shape[-1])
+    return torch.softmax(s.masked_fill(text_mask == 0, -1e9), dim=-1)
+
+
+def _pointer_source(name, b, ft):
+    return {"query": (b.query, ft["encoded_query"], b.query_mask), "his": (b.his, ft["encoded_his"], b.his_mask),
+            "cap": (b.cap, ft["encoded_cap"], b.cap_mask)}[name]
+
+
+def generator_logp(P, pre, ft, b, ptr_ft, mask_unk=1):
+    """log p_out of PointerGenerator (one source, sigmoid switch, generator.py:29-75) or MultiPointerGenerator
+    (several sources, softmax switch, generator.py:77-127) with the tied embedding ``vocab_gen``."""
+    x = ft["decoded_text"]
+    p_vocab = torch.softmax(x.matmul(P[pre + "vocab_gen"].t()), dim=-1)
+    names = ptr_ft.split(",")
+    multi = len(names) > 1
+    ptrs, vecs = [], []
+    for i, name in enumerate(names):
+        text, enc, mask = _pointer_source(name, b, ft)
+        if mask_unk:
+            mask = mask & (text != 0).unsqueeze(-2)
+        ap = pointer_probs(P, pre + (f"pointer_attn.{i}." if multi else "pointer_attn."), x, enc, mask)
+        idx = text.unsqueeze(1).expand_as(ap)
+        ptrs.append(torch.zeros_like(p_vocab).scatter_add(2, idx, ap))
+        vecs.append(ap.matmul(enc))
+    W, bias = P[pre + "pointer_gen_W.weight"], P[pre + "pointer_gen_W.bias"]
+    if multi:
+        sw = torch.softmax(linear(torch.cat([x, ft["encoded_tgt"]] + vecs, -1), W, bias), dim=-1)
+        p_out = sum(sw[:, :, i:i + 1] * ptrs[i] for i in range(len(names))) + sw[:, :, -1:] * p_vocab
+    else:
+        s = torch.sigmoid(linear(torch.cat([x, vecs[0], ft["encoded_tgt"]], -1), W, bias))
+        p_out = (1 - s) * ptrs[0] + s * p_vocab
+    return torch.log(p_out)
+
+
+def label_smoothing_kl(logp, target, pad, smoothing):
+    """LabelSmoothing.forward (label_smoothing.py:20-30): summed KL(true_dist || exp(logp)); logp [R, V]."""
+    V = logp.shape[1]
+    t = torch.full_like(logp, smoothing / (V - 2))
+    t.scatter_(1, target.unsqueeze(1), 1.0 - smoothing)
+    t[:, pad] = 0
+    t[target == pad] = 0
+    return torch.where(t > 0, t * (t.clamp_min(1e-38).log() - logp), torch.zeros_like(t)).sum()
+
+
+def loss_compute(P, args, ft, b, pad, smoothing=0.1):
+    """SimpleLossCompute.__call__ (optimize.py:46-82) for enc_st_combine == 'none'.  Returns (loss, parts)."""
+    V = P["generator.vocab_gen"].shape[0]
+    out = generator_logp(P, "generator.", ft, b, args["ptr_ft"], args.get("mask_unk", 1))
+    parts = {"out": label_smoothing_kl(out.reshape(-1, V), b.trg_y.reshape(-1), pad, smoothing) / b.ntokens.float()}
+    if args.get("auto_encoder", 0):
+        keys = (["cap_ft"] if args["nb_cenc_blocks"] > 0 else []) + (["audio_ft"] if args.get("nb_aenc_blocks", 0) > 0 else [])
+        if args["nb_venc_blocks"] > 0:
+            keys += (["temporal_ft"] if args["s2t"] else []) + (["spatial_ft"] if args["t2s"] else [])
+        for k in keys:
+            lp = torch.log_softmax(ft[k].matmul(P["ae_generator.proj"].t()), dim=-1)        # generator.py:22-25
+            parts[k + "_ae"] = label_smoothing_kl(lp.reshape(-1, V), b.query.reshape(-1), pad, smoothing) / b.qntokens.float()
+    return sum(parts.values()), parts
+
+
+def mtn_forward(P, args, b, h, n_blocks, drop=None):
+    """MTN.forward (mtn.py:31-61): embeddings -> text encoder norms -> video encoder -> multimodal decoder."""
+    ft = {}
+    eq, ec, eh = (embed(P, "query_embed.", ids, drop, f"query_embed.{n}") for n, ids in (("query", b.query), ("cap", b.cap), ("his", b.his)))
+    for i, (key, x) in enumerate((("encoded_query", eq), ("encoded_cap", ec), ("encoded_his", eh))):   # encoder.py:19-40
+        ft[key] = layer_norm(x, P[f"text_encoder.norm.{i}.a_2"], P[f"text_encoder.norm.{i}.b_2"])
+    ft["spatiotemporal_ft"], _ = vid_encoder8(P, "vid_encoder.", b.fts)
+    ft["encoded_tgt"] = embed(P, "tgt_embed.", b.trg, drop, "tgt_embed.trg")
+    masks = dict(trg=b.trg_mask, his=b.his_mask, query=b.query_mask, cap=b.cap_mask, audio=getattr(b, "audio_mask", None),
+                 temporal=b.temporal_mask)
+    return multimodal_decoder8(P, "mutlimodal_decoder.", h, args, ft, ft["encoded_tgt"], masks, n_blocks, drop)

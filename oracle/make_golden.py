@@ -195,6 +195,70 @@ def run_decoder_case(mtn, c):
     return out
 
 
+# ---- full model: MTN.forward + SimpleLossCompute of the unmodified reference --------------
+MODEL_CASES = {
+    # exec.sh-like: caption encoder, softmax gate, two pointer sources, auto-encoder heads
+    "avsd_full":   dict(seed=41, B=3, T=4, S=3, D=40, d=64, h=4, Lq=6, Lh=9, Lc=7, Lt=5, V=97, n_blocks=2, nb_cenc=2,
+                        vc="dyn", cap="summary", ptr_ft="query,cap", ae=1, t2s=1, s2t=1),
+    "single_ptr":  dict(seed=42, B=2, T=3, S=4, D=32, d=32, h=2, Lq=5, Lh=6, Lc=4, Lt=4, V=50, n_blocks=1, nb_cenc=0,
+                        vc="none", cap="none", ptr_ft="query", ae=1, t2s=1, s2t=1),
+    "his_ptr_noae": dict(seed=43, B=2, T=3, S=4, D=32, d=32, h=4, Lq=5, Lh=8, Lc=4, Lt=6, V=64, n_blocks=1, nb_cenc=1,
+                         vc="sum", cap="summary", ptr_ft="his,query", ae=0, t2s=1, s2t=1),
+}
+PAD, SMOOTHING = 1, 0.1          # train.py:93 (vocab['<blank>'] is the collate pad id, data/dataset.py)
+
+
+def model_args(c):
+    return argparse.Namespace(
+        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=0,
+        d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft=c["ptr_ft"], auto_encoder=c["ae"],
+        t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none", enc_vc_combine=c["vc"],
+        dec_st_combine="seq", include_caption=c["cap"], mask_unk=1)
+
+
+TIED = ("tgt_embed.0.lut.weight", "generator.vocab_gen", "ae_generator.proj")
+
+
+def model_params(shapes, seed):
+    """fill_params over the whole state_dict; the tied copies of the embedding take the query_embed values and the
+    positional tables (buffers) are left to the model."""
+    P = synth.fill_params({k: v for k, v in shapes.items() if not k.endswith(".pe")}, seed)
+    for k in TIED:
+        if k in P:
+            P[k] = P["query_embed.0.lut.weight"]
+    return P
+
+
+def run_model_case(mtn, c):
+    import model.label_smoothing as ls
+    import model.optimize as opt
+    torch.Tensor.cuda = lambda self, *a, **k: self        # generator.py:66,113 hard-code .cuda() (harness shim, §8(c))
+    torch.manual_seed(0)
+    args = model_args(c)
+    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=[c["D"]]).eval()
+    shapes = {k: tuple(v.shape) for k, v in model.state_dict().items()}
+    model.load_state_dict(model_params(shapes, c["seed"]), strict=False)
+    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    crit = ls.LabelSmoothing(size=c["V"], padding_idx=PAD, smoothing=SMOOTHING)
+    with torch.no_grad():
+        ft = model.forward(b)
+        logp = model.generator(ft, b, args)
+        lc = opt.SimpleLossCompute(model.generator, model.ae_generator, crit, opt=None, args=args)
+        losses = lc(ft, b)
+        # total normalised loss exactly as optimize.py:48-82 sums it
+        total = crit(logp.contiguous().view(-1, c["V"]), b.trg_y.contiguous().view(-1)) / b.ntokens.float()
+        if c["ae"]:
+            for k in (["cap_ft"] if c["nb_cenc"] > 0 else []) + ["temporal_ft", "spatial_ft"]:
+                ae = model.ae_generator(ft, b, args, k)
+                total = total + crit(ae.contiguous().view(-1, c["V"]), b.query.contiguous().view(-1)) / b.qntokens.float()
+    out = {k: ft[k].numpy().copy() for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text")}
+    out["logp"] = logp.numpy().copy()
+    out["loss_out_sum"] = np.array(float(losses["out"]))
+    out["loss_total"] = np.array(float(total))
+    out["param_shapes"] = np.array(json.dumps(sorted([k, list(v)] for k, v in shapes.items())))
+    return out
+
+
 def main():
     mtn, modules = import_reference()
     gold = os.path.join(ROOT, "tests", "golden")
@@ -211,6 +275,12 @@ def main():
         path = os.path.join(gold, f"decoder_{name}.npz")
         np.savez_compressed(path, **out)
         print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB", sorted(k for k in out if k not in ("meta", "param_shapes")))
+    for name, c in MODEL_CASES.items():
+        out = run_model_case(mtn, c)
+        out["meta"] = np.array(json.dumps(c))
+        path = os.path.join(gold, f"model_{name}.npz")
+        np.savez_compressed(path, **out)
+        print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB  loss_total={float(out['loss_total']):.6f}")
     path = os.path.join(gold, "modules.npz")
     np.savez_compressed(path, **run_modules_fixture(modules))
     print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")

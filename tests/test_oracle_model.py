@@ -1,0 +1,51 @@
+"""CPU: the oracle's restatement of the whole forward + loss (SURVEY.md §8(f) rows 1-2 — embeddings, positional
+encoding, text-encoder norms, video encoder, multimodal decoder, pointer generators, label-smoothed KL and the
+auto-encoder heads) against tests/golden/model_*.npz: outputs of the UNMODIFIED reference (``MTN.forward``,
+``generator`` and ``SimpleLossCompute``) on the same seeded batch and weights (oracle/make_golden.py)."""
+import glob
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from bist_b200 import synth
+from oracle import bist_oracle as O
+
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "model_*.npz")))
+PAD, SMOOTHING = 1, 0.1
+TIED = ("tgt_embed.0.lut.weight", "generator.vocab_gen", "ae_generator.proj")
+
+
+def load_model_case(path):
+    z = np.load(path)
+    c = json.loads(str(z["meta"]))
+    shapes = {k: tuple(v) for k, v in json.loads(str(z["param_shapes"]))}
+    P = synth.fill_params({k: v for k, v in shapes.items() if not k.endswith(".pe")}, c["seed"])
+    for k in TIED:
+        if k in P:
+            P[k] = P["query_embed.0.lut.weight"]
+    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    args = dict(nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=0, enc_vc_combine=c["vc"],
+                include_caption=c["cap"], dec_st_combine="seq", t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none",
+                ptr_ft=c["ptr_ft"], auto_encoder=c["ae"], mask_unk=1)
+    gold = {k: torch.from_numpy(z[k]) for k in z.files if k not in ("meta", "param_shapes")}
+    return c, args, P, shapes, b, gold
+
+
+def test_fixtures_present():
+    assert len(GOLD) >= 3
+
+
+@pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-4])
+def test_oracle_model_matches_reference(path):
+    c, args, P, shapes, b, gold = load_model_case(path)
+    ft = O.mtn_forward(P, args, b, c["h"], c["n_blocks"])
+    for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text"):
+        assert O.norm_err(ft[k], gold[k]) < 2e-6, (k, O.norm_err(ft[k], gold[k]))
+    logp = O.generator_logp(P, "generator.", ft, b, c["ptr_ft"], 1)
+    assert O.norm_err(logp, gold["logp"]) < 5e-6
+    total, parts = O.loss_compute(P, args, ft, b, PAD, SMOOTHING)
+    assert abs(float(total) - float(gold["loss_total"])) < 2e-5 * abs(float(gold["loss_total"]))
+    assert abs(float(parts["out"] * b.ntokens) - float(gold["loss_out_sum"])) < 2e-5 * abs(float(gold["loss_out_sum"]))
