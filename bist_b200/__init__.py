@@ -13,6 +13,9 @@ _LAZY = {
     "VidEncoder8": "encoder", "VidEncoderLayer4": "encoder", "VideoPath": "encoder",
     "set_precision": "encoder", "GraphedVideoPath": "encoder",
     "CapEncoderLayer": "encoder", "AudioEncoderLayer": "encoder",
+    "Encoder": "encoder", "Embeddings": "modules", "PositionalEncoding": "modules", "EmbedSequence": "modules",
+    "Generator": "generator", "PointerGenerator": "generator", "MultiPointerGenerator": "generator",
+    "LabelSmoothing": "generator", "MTN": "mtn", "make_model": "mtn", "SimpleLossCompute": "optimize", "NoamOpt": "optimize",
     "MultimodalDecoderLayer12": "decoder", "MultimodalDecoder8": "decoder", "make_decoder": "decoder",
 }
 

@@ -538,3 +538,23 @@ class CapEncoderLayer(_MemoryEncoderLayer):
 class AudioEncoderLayer(_MemoryEncoderLayer):
     "encoder.py:220-235 — in_ft['audio'] attends over ft['encoded_audio'] (b.audio_mask)."
     stream, memory, memory_mask = 'audio', 'encoded_audio', 'audio_mask'
+
+
+class Encoder(nn.Module):
+    """The text "encoder" of encoder.py:11-40: one LayerNorm per sequence, consumed in order (lists of sequences take
+    one norm per element, None passes through)."""
+
+    def __init__(self, size, nb_layers):
+        super(Encoder, self).__init__()
+        self.norm = nn.ModuleList(LayerNorm(size) for _ in range(nb_layers))
+        self.nb_layers = nb_layers
+
+    def forward(self, *seqs):
+        norms = iter(self.norm)
+        out = []
+        for s in seqs:
+            if isinstance(s, list):
+                out.append([next(norms)(t) for t in s])
+            else:
+                out.append(None if s is None else next(norms)(s))
+        return out

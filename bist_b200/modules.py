@@ -478,3 +478,81 @@ def gate_combine(logits, srcs):
     """softmax(logits) over the last dim, then the weighted sum of the K streams (each [..., d])."""
     _lib.require_cuda(logits, *srcs)
     return _GateFn.apply(logits, *srcs)
+
+
+# ---------------------------------------------------------------------------------------------- text side (modules.py:115-141)
+SITE_EMBED = 103
+
+
+class _EmbedFn(torch.autograd.Function):
+    """dropout(lut(ids) * sqrt(d) + pe) in one kernel — bist_embed_fwd / bist_embed_bwd."""
+
+    @staticmethod
+    def forward(ctx, ids, lut, pe, p_drop, seed, dtype):
+        ids = ids.contiguous()
+        B, L = ids.shape
+        V, d = lut.shape
+        out = torch.empty((B, L, d), dtype=dtype, device=lut.device)
+        _lib.check(_lib.lib().bist_embed_fwd(_lib.ptr(ids), _lib.ptr(lut), _lib.ptr(pe), _lib.ptr(out), B * L, L, d, V,
+                                             float(p_drop), seed, SITE_EMBED, _lib.dtype_code(dtype), _lib.stream_ptr()),
+                   "bist_embed_fwd")
+        ctx.save_for_backward(ids)
+        ctx.cfg = (V, d, float(p_drop), seed)
+        return out
+
+    @staticmethod
+    def backward(ctx, gy):
+        (ids,) = ctx.saved_tensors
+        V, d, p_drop, seed = ctx.cfg
+        gy = gy.contiguous()
+        dlut = torch.zeros((V, d), dtype=torch.float32, device=gy.device)
+        _lib.check(_lib.lib().bist_embed_bwd(_lib.ptr(ids), _lib.ptr(gy), _lib.ptr(dlut), ids.numel(), d, p_drop, seed,
+                                             SITE_EMBED, _lib.dtype_code(gy.dtype), _lib.stream_ptr()), "bist_embed_bwd")
+        return None, dlut, None, None, None, None
+
+
+class Embeddings(nn.Module):
+    "modules.py:115-123 — lut(x) * sqrt(d_model).  Used through ``EmbedSequence`` (fused with the positional encoding)."
+
+    def __init__(self, d_model, vocab):
+        super(Embeddings, self).__init__()
+        self.lut = nn.Embedding(vocab, d_model)
+        self.d_model = d_model
+
+    def forward(self, x):
+        raise NotImplementedError("Embeddings runs fused with PositionalEncoding: call the EmbedSequence that holds both")
+
+
+class PositionalEncoding(nn.Module):
+    "modules.py:125-141 — the sinusoidal table ``pe`` (buffer, same construction) and the dropout after the sum."
+
+    def __init__(self, d_model, dropout, max_len=5000):
+        super(PositionalEncoding, self).__init__()
+        self.dropout = nn.Dropout(p=dropout)
+        import math
+        pe = torch.zeros(max_len, d_model)
+        position = torch.arange(0., max_len).unsqueeze(1)
+        div_term = torch.exp(torch.arange(0., d_model, 2) * -(math.log(10000.0) / d_model))
+        pe[:, 0::2] = torch.sin(position * div_term)
+        pe[:, 1::2] = torch.cos(position * div_term)
+        self.register_buffer('pe', pe.unsqueeze(0))
+
+    def forward(self, x):
+        raise NotImplementedError("PositionalEncoding runs fused with Embeddings: call the EmbedSequence that holds both")
+
+
+class EmbedSequence(nn.Sequential):
+    """``nn.Sequential(Embeddings, PositionalEncoding)`` of mtn.py:78-80 (same children, same state_dict keys
+    ``0.lut.weight`` / ``1.pe``) whose forward is ONE kernel: lookup, scale, add the table, dropout."""
+    precision = "fp32"
+
+    def forward(self, ids):
+        if ids is None:
+            return None
+        emb, pos = self[0], self[1]
+        _lib.require_cuda(ids, emb.lut.weight)
+        p_drop = pos.dropout.p if self.training else 0.0
+        seed = _draw_seed() if p_drop > 0 else 0
+        self.last_dropout = (p_drop, seed, SITE_EMBED) if p_drop > 0 else None
+        dtype = torch.float32 if self.precision == "fp32" else torch.bfloat16
+        return _EmbedFn.apply(ids, emb.lut.weight, pos.pe[0], p_drop, seed, dtype)
