@@ -118,15 +118,32 @@ def allreduce_grads(params, average=True):
             blocks[st.data_ptr()][2].append(g)
         else:
             loose.append(g)
+    flats = []
     for st, covered, gs in blocks.values():
         if covered == st.nbytes():           # the storage holds nothing but these gradients: reduce it in place
-            flat = torch.empty(0, dtype=torch.float32, device=gs[0].device).set_(st, 0, (st.nbytes() // 4,))
-            dist.all_reduce(flat, op=op)
-            if div:
-                flat.div_(world)
-            n += 1
+            flats.append(torch.empty(0, dtype=torch.float32, device=gs[0].device).set_(st, 0, (st.nbytes() // 4,)))
         else:                                # partially used storage: treat its gradients one by one
             loose.extend(gs)
+    if dist.get_backend() == "nccl":
+        # every block and every stand-alone gradient in place, as ONE grouped NCCL launch (ncclGroupStart/End)
+        tensors = flats + [g for g in loose if g.is_contiguous()]
+        odd = [g for g in loose if not g.is_contiguous()]
+        if tensors:
+            with dist._coalescing_manager(device=tensors[0].device, async_ops=False):
+                for t in tensors:
+                    dist.all_reduce(t, op=op)
+            n += 1
+        for g in odd:
+            c = g.contiguous()
+            dist.all_reduce(c, op=op)
+            g.copy_(c)
+            n += 1
+        return n
+    for flat in flats:
+        dist.all_reduce(flat, op=op)
+        if div:
+            flat.div_(world)
+        n += 1
     if len(loose) == 1:
         dist.all_reduce(loose[0], op=op)
         if div:

@@ -1,6 +1,6 @@
-"""Training step of the model core at config-3 shapes: VidEncoder8 projection + MultimodalDecoder8
-(3 video blocks, 3 caption-encoder blocks, softmax gate, 3 decoder layers) — everything MTN.forward runs except the
-embeddings / text encoder (their outputs are synthetic leaf tensors here) and the generator + loss (an MSE stand-in).
+"""Full BiST training step at config-3 shapes: embeddings, text-encoder norms, VidEncoder8,
+MultimodalDecoder8 (3 video / 3 caption / 3 decoder blocks, softmax gate), pointer generator over query + caption,
+auto-encoder heads, label-smoothed loss, backward, fused Adam — per-step time, host enqueue time, per-tag kernel times.
 
     python scripts/core_bench.py [--precision bf16|fp32] [--steps 10] [--tags]
 """
@@ -13,7 +13,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bist_b200 import _lib, synth  # noqa: E402
-from bist_b200.core import BiSTCore, core_inputs  # noqa: E402
+from bist_b200.core import full_batch, full_model  # noqa: E402
 
 
 def main():
@@ -26,19 +26,19 @@ def main():
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
-    m = BiSTCore(precision=a.precision).to(dev)
+    m, lc = full_model(a.precision)
+    m = m.to(dev)
     m.train(not a.eval)
-    b, ft, x, tgt = core_inputs(1, dev, a.precision)
+    b = full_batch(1, dev)
     opt = torch.optim.Adam(m.parameters(), lr=1e-4, fused=True)
     L = _lib.lib()
 
     def loss_fn():
-        out = m(b, dict(ft), x)
-        return ((out["decoded_text"].float() - tgt) ** 2).mean()
+        return lc.loss(m(b), b)[0]
 
     if a.graph:
         from bist_b200.graph import GraphedTrainStep
-        graphed = GraphedTrainStep(loss_fn, list(m.parameters()) + list(ft.values()) + [x])
+        graphed = GraphedTrainStep(loss_fn, list(m.parameters()))
 
         def step():
             graphed()
@@ -62,7 +62,7 @@ def main():
     t1 = time.perf_counter()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / a.steps
-    print("core train step: %.3f ms (%d turns/s), host enqueue %.3f ms, %d library launches/step" % (
+    print("full train step: %.3f ms (%d turns/s), host enqueue %.3f ms, %d library launches/step" % (
         ms, 64 / ms * 1e3, (t1 - t0) / a.steps * 1e3, (L.bist_launch_count() - n0) // a.steps))
     if a.tags:
         import ctypes
