@@ -25,7 +25,7 @@ import torch.nn as nn
 
 from . import _lib
 from . import dist as _dist
-from .modules import (LayerNorm, SublayerConnection, clones, _eval_only, _needs_grad, _ws, _WEIGHT_EPOCH,
+from .modules import (LayerNorm, SublayerConnection, clones, _needs_grad, _ws, _WEIGHT_EPOCH,
                       _reg_hook, weights_updated)
 
 _TORCH_DTYPE = {"fp32": torch.float32, "bf16": torch.bfloat16}

@@ -27,12 +27,6 @@ def clones(module, N):
     return nn.ModuleList([copy.deepcopy(module) for _ in range(N)])
 
 
-def _eval_only(m):
-    if m.training:
-        raise NotImplementedError(
-            "%s: this module of the bist_b200 CUDA path is forward-only this round; call .eval()" % type(m).__name__)
-
-
 def _needs_grad(*tensors):
     return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
 
