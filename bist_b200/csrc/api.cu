@@ -6,6 +6,7 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <algorithm>
 #include <atomic>
 #include <map>
 #include <mutex>
@@ -61,6 +62,48 @@ int gemm(const GemmArgs& g, cudaStream_t st) {
   int rc = gemm_tc(g, st, &taken);
   if (taken) return rc;
   return gemm_simt(g, st);
+}
+
+// ---- skinny Linear (the gate / switch heads: a handful of outputs per row, decoder.py:147-167, generator.py:71,120) ----
+// N <= 8 outputs: one warp per row keeps the row of A in flight once and reduces N dot products with shuffles.
+template <typename T>
+__global__ void __launch_bounds__(256) skinny_fwd_kernel(const T* __restrict__ A, const T* __restrict__ W, const float* __restrict__ bias,
+                                                         T* __restrict__ C, int64_t M, int N, int K) {
+  pdl_trigger();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int64_t m = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (m >= M) return;
+  float acc[8];
+#pragma unroll
+  for (int n = 0; n < 8; ++n) acc[n] = 0.f;
+  const T* a = A + m * K;
+  for (int k = lane; k < K; k += 32) {
+    const float x = to_f32(a[k]);
+#pragma unroll
+    for (int n = 0; n < 8; ++n)
+      if (n < N) acc[n] = fmaf(x, to_f32(W[(int64_t)n * K + k]), acc[n]);
+  }
+#pragma unroll
+  for (int n = 0; n < 8; ++n) {
+    const float v = warp_sum(acc[n]);
+    if (n < N && lane == 0) C[m * N + n] = from_f32<T>(v + (bias ? bias[n] : 0.f));
+  }
+}
+// dx[m,k] = sum_n dy[m,n] wT[k,n] with N <= 8: one thread per output element.
+template <typename T>
+__global__ void __launch_bounds__(256) skinny_dx_kernel(const T* __restrict__ dy, const T* __restrict__ wT, T* __restrict__ dx, int64_t M,
+                                                        int N, int K) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = M * K;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = i / K;
+    const int k = (int)(i - m * K);
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc = fmaf(to_f32(dy[m * N + n]), to_f32(wT[(int64_t)k * N + n]), acc);
+    dx[i] = from_f32<T>(acc);
+  }
 }
 
 }  // namespace bist
@@ -136,6 +179,17 @@ int bist_linear_fwd(const void* x, const void* w, const float* bias, const void*
   BIST_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31),
                  "linear: bad shape");
   BIST_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(w_dtype) && dtype_ok(y_dtype), "linear: bad dtype");
+  if (N <= 8 && !relu && !residual && x_dtype == w_dtype && x_dtype == y_dtype) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ProfScope ps("skinny_linear", st);
+    const unsigned grid = (unsigned)((M + 7) / 8);
+    if (x_dtype == BIST_BF16)
+      BIST_LAUNCH(skinny_fwd_kernel<__nv_bfloat16>, grid, 256, 0, st, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, bias, (__nv_bfloat16*)y, M, (int)N, (int)K);
+    else
+      BIST_LAUNCH(skinny_fwd_kernel<float>, grid, 256, 0, st, (const float*)x, (const float*)w, bias, (float*)y, M, (int)N, (int)K);
+    BIST_LAUNCHED();
+    return 0;
+  }
   GemmArgs g;
   g.A = x; g.W = w; g.C = y; g.bias = bias; g.R = residual;
   g.M = (int)M; g.N = (int)N; g.K = (int)K;
@@ -271,7 +325,16 @@ int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, flo
   cudaStream_t st = (cudaStream_t)stream;
   BIST_CHECK_ARG(dy && M > 0 && N > 0 && K > 0 && M < (1LL << 31), "linear_bwd: bad argument");
   BIST_CHECK_ARG(dtype_ok(dy_dtype) && dtype_ok(x_dtype) && dtype_ok(w_dtype) && dtype_ok(dx_dtype), "linear_bwd: bad dtype");
-  if (dx) {
+  if (dx && N <= 8 && dy_dtype == w_dtype && dy_dtype == dx_dtype) {
+    BIST_CHECK_ARG(wT, "linear_bwd: dx needs the transposed weight");
+    ProfScope ps("skinny_linear_dx", st);
+    const unsigned grid = (unsigned)std::min<int64_t>((M * K + 255) / 256, 148 * 8);
+    if (dy_dtype == BIST_BF16)
+      BIST_LAUNCH(skinny_dx_kernel<__nv_bfloat16>, grid, 256, 0, st, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)wT, (__nv_bfloat16*)dx, M, (int)N, (int)K);
+    else
+      BIST_LAUNCH(skinny_dx_kernel<float>, grid, 256, 0, st, (const float*)dy, (const float*)wT, (float*)dx, M, (int)N, (int)K);
+    BIST_LAUNCHED();
+  } else if (dx) {
     BIST_CHECK_ARG(wT, "linear_bwd: dx needs the transposed weight");
     GemmArgs g;
     g.A = dy; g.W = wT; g.C = dx;

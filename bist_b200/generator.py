@@ -252,6 +252,8 @@ class Generator(nn.Module):
 
     def loss_rows(self, ft, batch, args, target, pad, smoothing, ft_key='decoded_text'):
         x = ft[ft_key]
+        if 'decoded_text' in ft and x.dtype != ft['decoded_text'].dtype:
+            x = x.to(ft['decoded_text'].dtype)           # the video streams leave VidEncoderLayer4 in fp32
         _lib.require_cuda(x, self._weight())
         return _GenLossFn.apply(x, self._weight(), self._cache, target, pad, smoothing, [], None)
 

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--eval", action="store_true")
     ap.add_argument("--tags", action="store_true")
+    ap.add_argument("--ncu", action="store_true", help="bracket the timed steps with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--graph", action="store_true", help="forward+loss+backward as one CUDA graph (bist_b200/graph.py)")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
@@ -55,10 +56,15 @@ def main():
     n0 = L.bist_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
+    if a.ncu:
+        torch.cuda.profiler.start()
     e0.record()
     for _ in range(a.steps):
         step()
     e1.record()
+    if a.ncu:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     t1 = time.perf_counter()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / a.steps
