@@ -158,29 +158,53 @@ class MultimodalDecoder8(nn.Module):
             raise RuntimeError("vc_combine_W has %d outputs for %d streams" % (logits.shape[-1], len(streams)))
         return gate_combine(logits, streams)
 
-    def forward(self, b, ft, x):
+    def _block_memories(self, count, in_ft, ft, b):
+        """Block `count` of the query-conditioned encoders (decoder.py:115-167): video, caption and audio layers, their
+        output norms and the gate.  None of it depends on the target sequence."""
         args = self.args
+        if self.v_N > 0:
+            in_ft = self.v_layers[count](in_ft, ft, b)
+            if _opt(args, "s2t", 1):
+                ft['temporal_ft'] = self.temporal_out_norm(in_ft['s2t'])
+            if _opt(args, "t2s", 1):
+                ft['spatial_ft'] = self.spatial_out_norm(in_ft['t2s'])
+        if self.c_N > 0:
+            in_ft = self.c_layers[count](in_ft, ft, b)
+            ft['cap_ft'] = self.cap_out_norm(in_ft['cap'])
+        if self.a_N > 0:
+            in_ft = self.a_layers[count](in_ft, ft, b)
+            ft['audio_ft'] = self.a_out_norm(in_ft['audio'])
+        if self.v_N > 0 and self.c_N > 0 and _opt(args, "enc_vc_combine", "none") in ('sum', 'dyn'):
+            ft['encoded_ft'] = self._combine(ft)
+        return in_ft
+
+    def forward(self, b, ft, x):
         eq = ft['encoded_query']
         in_ft = {'t2s': eq, 's2t': eq, 'audio': eq, 'cap': eq}
-        vc = _opt(args, "enc_vc_combine", "none")
         for count, layer in enumerate(self.layers):
-            if self.v_N > 0:
-                in_ft = self.v_layers[count](in_ft, ft, b)
-                if _opt(args, "s2t", 1):
-                    ft['temporal_ft'] = self.temporal_out_norm(in_ft['s2t'])
-                if _opt(args, "t2s", 1):
-                    ft['spatial_ft'] = self.spatial_out_norm(in_ft['t2s'])
-            if self.c_N > 0:
-                in_ft = self.c_layers[count](in_ft, ft, b)
-                ft['cap_ft'] = self.cap_out_norm(in_ft['cap'])
-            if self.a_N > 0:
-                in_ft = self.a_layers[count](in_ft, ft, b)
-                ft['audio_ft'] = self.a_out_norm(in_ft['audio'])
-            if self.v_N > 0 and self.c_N > 0 and vc in ('sum', 'dyn'):
-                ft['encoded_ft'] = self._combine(ft)
+            in_ft = self._block_memories(count, in_ft, ft, b)
             x = layer(b, ft, x)
         ft['decoded_text'] = self.norm(x)
         return ft
+
+    # ---- decoding with the target-independent part cached (SURVEY.md §8(f) row 3) ----------------------------------
+    def encode_memories(self, b, ft):
+        """Run every block's video / caption / audio layers and gate ONCE and return one ft snapshot per block — what
+        each decoder layer attends over.  The reference recomputes all of this for every hypothesis at every step of
+        ``beam_search_decode`` (decode.py:63-66 calls the whole ``MultimodalDecoder8.forward``)."""
+        eq = ft['encoded_query']
+        in_ft = {'t2s': eq, 's2t': eq, 'audio': eq, 'cap': eq}
+        snaps = []
+        for count in range(len(self.layers)):
+            in_ft = self._block_memories(count, in_ft, ft, b)
+            snaps.append(dict(ft))
+        return snaps
+
+    def decode_with_memories(self, b, snaps, x):
+        """``decoded_text`` for target embeddings x given the cached per-block memories (decoder.py:182-185)."""
+        for layer, ft_k in zip(self.layers, snaps):
+            x = layer(b, ft_k, x)
+        return self.norm(x)
 
 
 def make_decoder(args, precision="fp32"):

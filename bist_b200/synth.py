@@ -213,3 +213,12 @@ def make_full_batch(seed, B, T, S, D, Lq, Lh, Lc, Lt, vocab):
     b.trg_mask = (b.trg != PAD_ID).unsqueeze(-2) & torch.tril(torch.ones(Lt, Lt, dtype=torch.bool)).unsqueeze(0)
     b.ntokens, b.qntokens = (b.trg_y != PAD_ID).sum(), (b.query != PAD_ID).sum()
     return b
+
+
+def batch_rows(b, lo, hi):
+    """Rows [lo, hi) of a batch as a new batch (dialogue turns are independent)."""
+    n = b.query.shape[0] if hasattr(b, "query") else b.fts.shape[0]
+    out = SynthBatch()
+    for k, v in b.__dict__.items():
+        setattr(out, k, v[lo:hi] if torch.is_tensor(v) and v.dim() > 0 and v.shape[0] == n else v)
+    return out

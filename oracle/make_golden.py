@@ -259,6 +259,37 @@ def run_model_case(mtn, c):
     return out
 
 
+# ---- beam search: decode.py:53-104 of the unmodified reference, one turn at a time ----------
+BEAM = dict(beam=3, max_len=6, nbest=3, min_len=1, penalty=1.0, start=2, unk=0, end=3, pad=1)
+BEAM_CASES = ("avsd_full", "single_ptr")
+
+
+def run_beam_case(mtn, c):
+    import model.decode as dec
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.manual_seed(0)
+    args = model_args(c)
+    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=[c["D"]]).eval()
+    shapes = {k: tuple(v.shape) for k, v in model.state_dict().items()}
+    model.load_state_dict(model_params(shapes, c["seed"]), strict=False)
+    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    out = {}
+    g = BEAM
+    with torch.no_grad():
+        for i in range(c["B"]):
+            bi = synth.batch_rows(b, i, i + 1)
+            hyps, best = dec.beam_search_decode(model, bi, g["max_len"], g["start"], g["unk"], g["end"], g["pad"], beam=g["beam"],
+                                                penalty=g["penalty"], nbest=g["nbest"], min_len=g["min_len"], train_args=args)
+            toks = np.full((g["nbest"], g["max_len"]), -1, dtype=np.int64)
+            for j, (seq, _s) in enumerate(hyps):
+                toks[j, :len(seq)] = [int(t) for t in seq]
+            out[f"tokens_{i}"] = toks
+            out[f"scores_{i}"] = np.array([float(s) for _seq, s in hyps], dtype=np.float64)
+            out[f"best_{i}"] = np.array(float(best))
+    out["beam"] = np.array(json.dumps(g))
+    return out
+
+
 def main():
     mtn, modules = import_reference()
     gold = os.path.join(ROOT, "tests", "golden")
@@ -281,6 +312,13 @@ def main():
         path = os.path.join(gold, f"model_{name}.npz")
         np.savez_compressed(path, **out)
         print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB  loss_total={float(out['loss_total']):.6f}")
+    for name in BEAM_CASES:
+        c = MODEL_CASES[name]
+        out = run_beam_case(mtn, c)
+        out["meta"] = np.array(json.dumps(c))
+        path = os.path.join(gold, f"beam_{name}.npz")
+        np.savez_compressed(path, **out)
+        print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB", out["tokens_0"].tolist(), out["scores_0"].tolist())
     path = os.path.join(gold, "modules.npz")
     np.savez_compressed(path, **run_modules_fixture(modules))
     print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB")
