@@ -81,6 +81,7 @@ SIGNATURES = {
     "bist_ln_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_f, c_i, c_i, c_i, c_p]),
     "bist_linear_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i, c_i, c_i, c_i, c_p]),
     "bist_dropout_fwd": (c_i, [c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
+    "bist_dropout_add_fwd": (c_i, [c_p, c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
     "bist_mha_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, ctypes.POINTER(MhaParams), c_p, c_p,
                                  c_i64, c_i64, c_i64, c_i64, c_i64, c_i64, c_p, c_sz, c_i,
                                  c_f, ctypes.c_uint64, ctypes.c_uint32, c_p]),

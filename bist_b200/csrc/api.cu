@@ -106,6 +106,16 @@ __global__ void __launch_bounds__(256) skinny_dx_kernel(const T* __restrict__ dy
   }
 }
 
+// out = x + y * m(idx): the residual add of SublayerConnection fused with its dropout (modules.py:44)
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_residual_kernel(const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ out,
+                                                               int64_t n, DropCfg drop) {
+  pdl_trigger();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = from_f32<T>(fmaf(to_f32(y[i]), drop_mul(drop, (unsigned long long)i), to_f32(x[i])));
+}
+
 }  // namespace bist
 
 using namespace bist;
@@ -366,6 +376,23 @@ int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, u
   BIST_CHECK_ARG(x && y && rows > 0 && d > 0, "dropout: bad argument");
   BIST_CHECK_ARG(dtype_ok(dtype) && p >= 0.f && p < 1.f, "dropout: bad dtype or probability");
   return dropout_scale(x, y, rows, d, make_drop(p, seed, site), 0, 0, dtype, dtype, (cudaStream_t)stream);
+}
+
+int bist_dropout_add_fwd(const void* y, const void* x, void* out, int64_t rows, int64_t d, float p, uint64_t seed,
+                         uint32_t site, int dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(y && x && out && rows > 0 && d > 0, "dropout_add: bad argument");
+  BIST_CHECK_ARG(dtype_ok(dtype) && p >= 0.f && p < 1.f, "dropout_add: bad dtype or probability");
+  const int64_t n = rows * d;
+  const DropCfg drop = make_drop(p, seed, site);
+  ProfScope ps("dropout", st);
+  const unsigned grid = (unsigned)std::min<int64_t>((n + 255) / 256, 148 * 8);
+  if (dtype == BIST_BF16)
+    BIST_LAUNCH(dropout_residual_kernel<__nv_bfloat16>, grid, 256, 0, st, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, n, drop);
+  else
+    BIST_LAUNCH(dropout_residual_kernel<float>, grid, 256, 0, st, (const float*)y, (const float*)x, (float*)out, n, drop);
+  BIST_LAUNCHED();
+  return 0;
 }
 
 int bist_mha_train_fwd(const void* query, const void* key, const void* value, const uint8_t* mask, int mask_mode,

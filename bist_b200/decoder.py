@@ -231,5 +231,8 @@ def make_decoder(args, precision="fp32"):
     layer = MultimodalDecoderLayer12(d_model, c(attn), nb_attn, c(ff), dropout, args)
     dec = MultimodalDecoder8(v_layer, c_layer, a_layer, layer, args.nb_venc_blocks, args.nb_cenc_blocks,
                              _opt(args, "nb_aenc_blocks", 0), args.nb_blocks, args)
+    for m in dec.modules():                        # nobody reads .attn of these attentions (only the generator's pointer
+        if isinstance(m, MultiHeadedAttention):    # attention is read, generator.py:62-63): skip storing the probabilities
+            m.store_attn = False
     set_precision(dec, precision)
     return dec

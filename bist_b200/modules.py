@@ -143,6 +143,30 @@ class _DropoutFn(torch.autograd.Function):
         return gx, None, None, None
 
 
+class _DropoutAddFn(torch.autograd.Function):
+    """x + dropout(y) in one kernel (modules.py:44); backward: dx = g, dy = g o m."""
+
+    @staticmethod
+    def forward(ctx, y, x, p, seed, site):
+        y, x = y.contiguous(), x.contiguous()
+        d = x.shape[-1]
+        out = torch.empty_like(x)
+        _lib.check(_lib.lib().bist_dropout_add_fwd(_lib.ptr(y), _lib.ptr(x), _lib.ptr(out), x.numel() // d, d, float(p), seed,
+                                                   site, _lib.dtype_code(x.dtype), _lib.stream_ptr()), "bist_dropout_add_fwd")
+        ctx.cfg = (float(p), seed, site)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.contiguous()
+        d = g.shape[-1]
+        gy = torch.empty_like(g)
+        p, seed, site = ctx.cfg
+        _lib.check(_lib.lib().bist_dropout_fwd(_lib.ptr(g), _lib.ptr(gy), g.numel() // d, d, p, seed, site,
+                                               _lib.dtype_code(g.dtype), _lib.stream_ptr()), "bist_dropout_fwd")
+        return gy, g, None, None, None
+
+
 def _ptr_array(tensors):
     arr = (ctypes.c_void_p * len(tensors))()
     for i, t in enumerate(tensors):
@@ -281,6 +305,8 @@ class SublayerConnection(nn.Module):
             _lib.require_cuda(y)
             seed = _draw_seed()
             self.last_dropout = (self.dropout.p, seed, SITE_SUBLAYER)
+            if y.dtype == x.dtype and y.shape == x.shape:
+                return _DropoutAddFn.apply(y, x, self.dropout.p, seed, SITE_SUBLAYER)
             y = _DropoutFn.apply(y, self.dropout.p, seed, SITE_SUBLAYER)
         return x + y
 

@@ -273,6 +273,10 @@ int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, flo
 int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, uint64_t seed, uint32_t site,
                      int dtype, void* stream);
 
+/* SublayerConnection's residual fused with its dropout: out = x + y o m / (1 - p) (modules.py:44), dense [rows, d]. */
+int bist_dropout_add_fwd(const void* y, const void* x, void* out, int64_t rows, int64_t d, float p, uint64_t seed,
+                         uint32_t site, int dtype, void* stream);
+
 /* MultiHeadedAttention.forward in train() mode (modules.py:81-100): as bist_mha_fwd, with dropout p_drop on the
  * probabilities (modules.py:62-63; attn_out receives the dropped probabilities, as self.attn does) and the workspace
  * kept as the tape of bist_mha_bwd (tape_bytes = bist_mha_workspace_bytes). */
