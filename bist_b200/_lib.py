@@ -24,6 +24,11 @@ MASK_NONE, MASK_KEY, MASK_FULL = 0, 1, 2
 c_p, c_i, c_i64, c_f, c_sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
 
 
+class PackItem(ctypes.Structure):
+    _fields_ = [("src", ctypes.c_void_p), ("dst_off", ctypes.c_int64), ("rows", ctypes.c_int32), ("cols", ctypes.c_int32),
+                ("transpose", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
 class MhaParams(ctypes.Structure):
     _fields_ = [("w", c_p * 4), ("b", c_p * 4)]
 
@@ -81,6 +86,7 @@ SIGNATURES = {
     "bist_ln_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_f, c_i, c_i, c_i, c_p]),
     "bist_linear_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i, c_i, c_i, c_i, c_p]),
     "bist_dropout_fwd": (c_i, [c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
+    "bist_pack_params": (c_i, [ctypes.POINTER(PackItem), c_i64, c_p, c_i, c_p]),
     "bist_dropout_add_fwd": (c_i, [c_p, c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
     "bist_mha_train_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, ctypes.POINTER(MhaParams), c_p, c_p,
                                  c_i64, c_i64, c_i64, c_i64, c_i64, c_i64, c_p, c_sz, c_i,

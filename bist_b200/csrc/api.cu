@@ -378,6 +378,26 @@ int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, u
   return dropout_scale(x, y, rows, d, make_drop(p, seed, site), 0, 0, dtype, dtype, (cudaStream_t)stream);
 }
 
+// Compute-dtype (optionally transposed) copies of many fp32 parameters into ONE destination buffer, in as few launches
+// as the 72-item table of pack_many allows (the stand-alone modules refresh all their weight copies together after an
+// optimizer step, bist_b200/modules.py: _CopyArena).
+int bist_pack_params(const bist_pack_item_t* items, int64_t n, void* base, int dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(items && n > 0 && base && dtype_ok(dtype), "pack_params: bad argument");
+  PackItem tab[kMaxPackItems];
+  static float dummy_f32;   // pack_many wants a non-null fp32 base; no item here targets it
+  for (int64_t i0 = 0; i0 < n; i0 += kMaxPackItems) {
+    const int m = (int)std::min<int64_t>(kMaxPackItems, n - i0);
+    for (int i = 0; i < m; ++i) {
+      const bist_pack_item_t& it = items[i0 + i];
+      BIST_CHECK_ARG(it.src && it.rows > 0 && it.cols > 0 && it.dst_off >= 0, "pack_params: bad item %lld", (long long)(i0 + i));
+      tab[i] = PackItem{it.src, (long long)it.dst_off, (int)it.rows, (int)it.cols, it.transpose ? 1 : 0, 0, 1.f, 0};
+    }
+    BIST_TRY(pack_many(tab, m, base, &dummy_f32, dtype, st));
+  }
+  return 0;
+}
+
 int bist_dropout_add_fwd(const void* y, const void* x, void* out, int64_t rows, int64_t d, float p, uint64_t seed,
                          uint32_t site, int dtype, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;

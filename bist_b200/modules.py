@@ -15,6 +15,7 @@ statistics); parameters stay fp32 masters and their gradients are fp32.
 """
 import copy
 import ctypes
+import weakref
 
 import torch
 import torch.nn as nn
@@ -93,14 +94,84 @@ def weights_updated():
     _WEIGHT_EPOCH[0] += 1
 
 
+class _CopyArena:
+    """Compute-dtype (and transposed) copies of fp32 weight matrices for one (device, dtype), kept in ONE buffer and
+    refreshed TOGETHER — ceil(n / 72) launches of ``bist_pack_params`` after an optimizer step instead of one or two
+    torch kernels per copy (a full model asks for ~200 copies per step).  A copy requested for the first time in the
+    middle of a step is made on the spot and joins the arena at the next refresh."""
+
+    def __init__(self, device, dtype):
+        self.device, self.dtype = device, dtype
+        self.slots = {}              # (id(param), transposed) -> [weakref, offset, rows, cols, version, view]
+        self.size, self.buf = 0, None
+        self.refreshed_epoch = None
+        self.stale_layout = True
+        self.extra = {}
+
+    def get(self, p, transposed):
+        key = (id(p), transposed)
+        slot = self.slots.get(key)
+        if slot is None or slot[0]() is not p:
+            rows, cols = (p.shape[1], p.shape[0]) if transposed else (p.shape[0], p.shape[1])
+            slot = [weakref.ref(p), 0, rows, cols, None, None]
+            self.slots[key] = slot
+            self.stale_layout = True
+            self.extra.pop(key, None)        # ids are recycled: never hand out a dead parameter's copy
+        cur = _WEIGHT_EPOCH[0]
+        if self.refreshed_epoch == cur and slot[5] is not None and slot[4] == p._version:
+            return slot[5]
+        if self.refreshed_epoch == cur and slot[5] is None:          # new this step: one-off copy, arena next time
+            e = self.extra.get(key)
+            if e is None or e[0] != p._version:
+                w = p.detach().t() if transposed else p.detach()
+                e = (p._version, w.to(self.dtype).contiguous())
+                self.extra[key] = e
+            return e[1]
+        self.refresh()
+        return self.slots[key][5]
+
+    def refresh(self):
+        live = {k: s for k, s in self.slots.items() if s[0]() is not None}
+        if len(live) != len(self.slots):
+            self.slots, self.stale_layout = live, True
+        if self.stale_layout or self.buf is None:
+            off = 0
+            for s in self.slots.values():
+                s[1] = off
+                off += (s[2] * s[3] + 63) // 64 * 64                # 128-byte aligned slots
+            self.size = off
+            self.buf = torch.empty(max(off, 64), dtype=self.dtype, device=self.device)
+            self.stale_layout = False
+        items = (_lib.PackItem * len(self.slots))()
+        for it, (key, s) in zip(items, self.slots.items()):
+            p = s[0]()
+            it.src, it.dst_off, it.rows, it.cols, it.transpose = p.data_ptr(), s[1], s[2], s[3], int(key[1])
+            s[4] = p._version
+            s[5] = self.buf[s[1]:s[1] + s[2] * s[3]].view(s[2], s[3])
+        _lib.check(_lib.lib().bist_pack_params(items, len(self.slots), _lib.ptr(self.buf), _lib.dtype_code(self.dtype),
+                                               _lib.stream_ptr()), "bist_pack_params")
+        self.refreshed_epoch = _WEIGHT_EPOCH[0]
+        self.extra.clear()
+
+
+_ARENAS = {}
+
+
 class _BF16Cache:
     """Copies of fp32 parameters in the compute dtype (bf16 copies; transposed copies for the backward GEMMs),
-    refreshed when a parameter is updated in place."""
+    refreshed when a parameter is updated in place.  Weight matrices on a CUDA device live in the shared ``_CopyArena``
+    of their (device, dtype); anything else is copied on its own."""
 
     def __init__(self):
         self._store = {}
 
     def get(self, p, dtype=torch.bfloat16, transposed=False):
+        if p.is_cuda and p.dim() == 2 and p.dtype == torch.float32 and p.is_contiguous():
+            ak = (p.device, dtype)
+            arena = _ARENAS.get(ak)
+            if arena is None:
+                arena = _ARENAS[ak] = _CopyArena(p.device, dtype)
+            return arena.get(p, transposed)
         key = (id(p), dtype, transposed)
         hit = self._store.get(key)
         ver = (p._version, _WEIGHT_EPOCH[0])

@@ -273,6 +273,17 @@ int bist_linear_bwd(const void* dy, const void* x, const void* wT, void* dx, flo
 int bist_dropout_fwd(const void* x, void* y, int64_t rows, int64_t d, float p, uint64_t seed, uint32_t site,
                      int dtype, void* stream);
 
+/* Refresh many weight copies at once: item i writes dst[dst_off + r*cols + c] = transpose ? src[c*rows + r] : src[r*cols + c]
+ * (rows x cols = shape of the DESTINATION; src fp32 parameters, dst of `dtype`), 72 items per launch. */
+typedef struct {
+  const float* src;
+  int64_t dst_off;
+  int32_t rows, cols;
+  int32_t transpose;
+  int32_t reserved;
+} bist_pack_item_t;
+int bist_pack_params(const bist_pack_item_t* items, int64_t n, void* base, int dtype, void* stream);
+
 /* SublayerConnection's residual fused with its dropout: out = x + y o m / (1 - p) (modules.py:44), dense [rows, d]. */
 int bist_dropout_add_fwd(const void* y, const void* x, void* out, int64_t rows, int64_t d, float p, uint64_t seed,
                          uint32_t site, int dtype, void* stream);
