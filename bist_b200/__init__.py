@@ -11,7 +11,7 @@ _LAZY = {
     "LayerNorm": "modules", "SublayerConnection": "modules", "MultiHeadedAttention": "modules",
     "PositionwiseFeedForward": "modules", "clones": "modules",
     "VidEncoder8": "encoder", "VidEncoderLayer4": "encoder", "VideoPath": "encoder",
-    "set_precision": "encoder", "GraphedVideoPath": "encoder",
+    "set_precision": "encoder", "GraphedVideoPath": "encoder", "PipelinedVideoPath": "encoder",
     "CapEncoderLayer": "encoder", "AudioEncoderLayer": "encoder",
     "Encoder": "encoder", "Embeddings": "modules", "PositionalEncoding": "modules", "EmbedSequence": "modules",
     "Generator": "generator", "PointerGenerator": "generator", "MultiPointerGenerator": "generator",

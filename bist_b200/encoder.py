@@ -509,6 +509,49 @@ class GraphedVideoPath:
         return self.replay()
 
 
+class PipelinedVideoPath:
+    """Host -> device -> host pipeline over ``depth`` captured copies of the forward: while one copy's graph runs, the
+    next batch's pinned-host inputs are already crossing PCIe into the other copy's static buffers on a copy stream
+    (H2D, compute and D2H use different engines).  Every submitted batch is still copied in, computed and copied out;
+    only the waiting is overlapped, so the steady-state step time is max(H2D, compute) instead of their sum.
+
+        pipe = PipelinedVideoPath(model, device_batch, device_eq)
+        for host_batch, host_eq in loader:
+            pipe.submit(host_batch, host_eq, out_temporal_pinned, out_spatial_pinned)
+        pipe.drain()
+    """
+
+    def __init__(self, model, b, encoded_query, depth=2, warmup=3):
+        self.slots = [GraphedVideoPath(model, b, encoded_query, warmup) for _ in range(depth)]
+        self.copy_stream = torch.cuda.Stream()
+        self.loaded = [torch.cuda.Event() for _ in range(depth)]
+        self.free = [torch.cuda.Event() for _ in range(depth)]
+        for e in self.free:
+            e.record()
+        self.n = 0
+
+    def submit(self, b, encoded_query, out_temporal=None, out_spatial=None):
+        k = self.n % len(self.slots)
+        g = self.slots[k]
+        cur = torch.cuda.current_stream()
+        self.copy_stream.wait_event(self.free[k])          # slot k's previous replay and read-back are done
+        with torch.cuda.stream(self.copy_stream):
+            g.load(b, encoded_query, non_blocking=True)
+            self.loaded[k].record(self.copy_stream)
+        cur.wait_event(self.loaded[k])
+        out = g.replay()
+        if out_temporal is not None:
+            out_temporal.copy_(out['temporal_ft'], non_blocking=True)
+        if out_spatial is not None:
+            out_spatial.copy_(out['spatial_ft'], non_blocking=True)
+        self.free[k].record(cur)
+        self.n += 1
+        return out
+
+    def drain(self):
+        torch.cuda.current_stream().synchronize()
+
+
 class _MemoryEncoderLayer(nn.Module):
     """Self attention over the query-length stream, attention over one encoded memory, FFN — the common body of
     CapEncoderLayer and AudioEncoderLayer (encoder.py:203-235); compositions of the library-backed blocks."""

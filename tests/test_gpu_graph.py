@@ -38,7 +38,7 @@ def test_graphed_step_equals_eager_and_follows_weight_updates():
     try:
         loss_g = step()
         torch.cuda.synchronize()
-        assert abs(float(loss_g) - float(loss_e)) <= 1e-5 * abs(float(loss_e))
+        assert abs(float(loss_g.detach()) - float(loss_e)) <= 1e-5 * abs(float(loss_e))
         for p, g in zip(params, eager):
             assert O.norm_err(p.grad.cpu(), g.cpu()) < 1e-5
         opt = torch.optim.SGD(params, lr=5e-3)
@@ -66,3 +66,29 @@ def test_graphed_step_draws_fresh_dropout_masks_per_replay():
         assert float(step()) == b
     finally:
         step.close()
+
+
+def test_pipelined_forward_equals_direct_forward_for_every_batch():
+    """PipelinedVideoPath overlaps the next batch's H2D with the current replay: every batch's outputs must still be
+    exactly those of a direct forward on that batch."""
+    from bist_b200 import PipelinedVideoPath
+    c = dict(seed=411, B=4, T=6, S=4, D=64, d=64, h=4, Lq=5, n_blocks=2)
+    m = VideoPath(c["d"], c["h"], c["n_blocks"], c["D"], precision="fp32").to(DEV)
+    m.load_state_dict(synth.make_params(c["seed"], c["d"], c["D"], c["n_blocks"]), strict=True)
+    m.eval()
+    batches = []
+    for i in range(5):
+        hb = synth.make_batch(500 + i, c["B"], c["T"], c["S"], c["D"], c["Lq"], full_clips=True)
+        hb.fts, hb.query_mask, hb.temporal_mask = hb.fts.pin_memory(), hb.query_mask.pin_memory(), hb.temporal_mask.pin_memory()
+        batches.append((hb, synth.make_encoded_query(500 + i, c["B"], c["Lq"], c["d"]).pin_memory()))
+    with torch.no_grad():
+        direct = [m(hb.to(DEV), heq.to(DEV)) for hb, heq in batches]
+        direct = [(o["temporal_ft"].cpu(), o["spatial_ft"].cpu()) for o in direct]
+    pipe = PipelinedVideoPath(m, batches[0][0].to(DEV), batches[0][1].to(DEV), depth=2)
+    outs = [(torch.empty(c["B"], c["Lq"], c["d"]).pin_memory(), torch.empty(c["B"], c["Lq"], c["d"]).pin_memory())
+            for _ in batches]
+    for (hb, heq), (ot, os_) in zip(batches, outs):
+        pipe.submit(hb, heq, ot, os_)
+    pipe.drain()
+    for (ot, os_), (dt_, ds_) in zip(outs, direct):
+        assert torch.equal(ot, dt_) and torch.equal(os_, ds_)
