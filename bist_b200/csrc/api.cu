@@ -55,6 +55,26 @@ ProfScope::~ProfScope() {
   g_prof_recs.push_back(r);
 }
 
+bool overlap_enabled() {
+  static const bool on = getenv("BIST_NO_OVERLAP") == nullptr;
+  return on;
+}
+int side_stream(SideStream** out) {
+  static thread_local std::map<int, SideStream> tab;
+  int dev = 0;
+  BIST_CUDA(cudaGetDevice(&dev));
+  auto it = tab.find(dev);
+  if (it == tab.end()) {
+    SideStream ss{};
+    BIST_CUDA(cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking));
+    BIST_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
+    BIST_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+    it = tab.emplace(dev, ss).first;
+  }
+  *out = &it->second;
+  return 0;
+}
+
 int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken);  // gemm_tc.cu
 
 int gemm(const GemmArgs& g, cudaStream_t st) {

@@ -220,11 +220,21 @@ struct GemmArgs {
   int relu = 0;
   const char* tag = "gemm";  // label for bist_prof_collect
   int allow_tf32 = 0;        // fp32 operands may be multiplied as tf32 on the tensor cores
+  int max_ctas = 0;          // persistent tensor-core GEMM: cap on the grid (0 = one CTA per SM); a GEMM forked onto the side
+                             // stream leaves some SMs to the serial chain it overlaps with
   // Region-major W (tensor-core path only): W is a [*, wr_T, wr_S, K] tensor (row (bt, s) at (bt*wr_S + s)*w.si) and
   // output column n = s*wr_T + t multiplies row (t, s) of the batch's wr_T x wr_S block; N = wr_T*wr_S.
   int wr_T = 0, wr_S = 0;
   int a_dtype = BIST_F32, w_dtype = BIST_F32, c_dtype = BIST_F32, r_dtype = BIST_F32;
 };
+// One internal non-blocking stream (+ fork / join events) per host thread and device, for fork-join overlap INSIDE one
+// entry point: work that does not depend on the call's serial chain is launched there between an event recorded on the
+// caller's stream and an event the caller's stream waits for before the call returns.  Capturable (the side stream joins
+// the caller's capture through the fork event).  BIST_NO_OVERLAP=1 disables it.
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join; };
+int side_stream(SideStream** out);
+bool overlap_enabled();
+
 int gemm(const GemmArgs& g, cudaStream_t st);       // dispatches to the kernels below
 int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate GEMM, any shape
 int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken);  // tcgen05 GEMM; *taken = false when it declines the shape

@@ -280,7 +280,8 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
   if (!tt.w3d) { tt.bn_valid = BN; tt.w_stage_bytes = BN * SLAB_BYTES; }
   tt.tiles_n = (t.g.N + tt.bn_valid - 1) / tt.bn_valid;
   tt.total_tiles = tt.tiles_m * tt.tiles_n * t.g.Z;
-  const int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
+  int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
+  if (t.g.max_ctas > 0 && grid > t.g.max_ctas) grid = t.g.max_ctas;
   ProfScope ps(t.g.tag, st);
   BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, tt);
   BIST_LAUNCHED();

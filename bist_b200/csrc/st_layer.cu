@@ -115,6 +115,15 @@ int fp32_product(const float* A, const float* Wm, const float* bias, float* C, i
   return gemm_simt(g, st);
 }
 
+// CTAs of the forked stage-1 value GEMM: the rest of the SMs stay free for the query-side chain it runs beside.
+int xv_side_ctas() {
+  static const int n = [] {
+    const char* e = getenv("BIST_XV_CTAS");
+    return e ? atoi(e) : 100;   // measured optimum at config 2 (sweep 56..148: 96-112 best)
+  }();
+  return n;
+}
+
 }  // namespace
 }  // namespace bist
 
@@ -261,6 +270,31 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     return gemm(g, st);
   };
 
+  // The stage-1 values XV = vft . [Wv1]^T + bv1 (the one big GEMM of the block) depend only on the video tensor: launch
+  // them on the side stream now, so they run beside the serial query-side chain below; joined before the first P.XV.
+  const long long TS = T * S, xvld = (long long)nd * d;
+  auto launch_xv = [&](cudaStream_t s) {
+    GemmArgs g;
+    g.A = vft; g.W = (const char*)packed + (L.wv1cat + (size_t)pu0 * d * d) * e; g.C = W.xv;
+    g.bias = (const float*)((const char*)packed + L.f_byte_off) + L.bv1cat + (size_t)pu0 * d;
+    g.M = (int)(B * TS); g.N = nd * di; g.K = di;
+    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(xvld);
+    g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
+    if (s != st) g.max_ctas = xv_side_ctas();
+    return gemm(g, s);
+  };
+  SideStream* side = nullptr;
+  bool xv_forked = false, xv_joined = false;
+  if (overlap_enabled()) {
+    BIST_TRY(side_stream(&side));
+    BIST_CUDA(cudaEventRecord(side->fork, st));
+    BIST_CUDA(cudaStreamWaitEvent(side->s, side->fork, 0));
+    const int rc = launch_xv(side->s);
+    BIST_CUDA(cudaEventRecord(side->join, side->s));
+    if (rc != 0) { cudaStreamWaitEvent(st, side->join, 0); return rc; }
+    xv_forked = true;
+  }
+
   // ---- self-attention over the query tokens (encoder.py:176 / :184) -------------------------------
   // the layer inputs of the two directions are separate (possibly aliased) tensors: address them as a batch
   // whose stride is the pointer difference (zero when both are ft['encoded_query'], decoder.py:109-110)
@@ -330,16 +364,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   }
 
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
-  const long long TS = T * S, xvld = (long long)nd * d;
-  {
-    GemmArgs g;  // values of every video row for the active directions: XV = vft . [Wv1]^T + bv1
-    g.A = vft; g.W = (const char*)packed + (L.wv1cat + (size_t)pu0 * d * d) * e; g.C = W.xv;
-    g.bias = (const float*)((const char*)packed + L.f_byte_off) + L.bv1cat + (size_t)pu0 * d;
-    g.M = (int)(B * TS); g.N = nd * di; g.K = di;
-    g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(xvld);
-    g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
-    BIST_TRY(gemm(g, st));
-  }
+  if (!xv_forked) BIST_TRY(launch_xv(st));
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
@@ -391,8 +416,13 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     a.og = rows_2level(G, Lq * G * d, d); a.o_l = (long long)G * d;
     a.G = (int)(B * G); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = nk;
     a.v_dtype = dtype; a.ctx_dtype = dtype;
+    if (xv_forked && !xv_joined) {
+      BIST_CUDA(cudaStreamWaitEvent(st, side->join, 0));
+      xv_joined = true;
+    }
     BIST_TRY(softmax_pv(a, st));
   }
+  if (xv_forked && !xv_joined) BIST_CUDA(cudaStreamWaitEvent(st, side->join, 0));
 
   // ---- stage 2 (encoder.py:125-132 / :152-161) with W_o1 folded through it ------------------------------------------
   for (int u = 0; u < nd; ++u) {
