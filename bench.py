@@ -108,6 +108,40 @@ def cpu_oracle_turns_per_sec(c, rows, reps, threads):
     return rows / best, best
 
 
+def cpu_oracle_train_turns_per_sec(model, rows, reps, threads):
+    """Time the CPU oracle's full training step (forward + label-smoothed losses + autograd backward, fp32; no
+    optimizer) on `rows` dialogue turns of config 3, with the model's own weights."""
+    from bist_b200 import synth
+    from bist_b200.core import FULL_SHAPES, PAD, SMOOTHING
+    from oracle import bist_oracle as O
+    torch.set_num_threads(threads)
+    c = FULL_SHAPES
+    leaves, P = {}, {}
+    for k, v in model.state_dict().items():
+        if k.endswith(".pe"):
+            continue
+        key = v.data_ptr()
+        if key not in leaves:
+            leaves[key] = v.detach().float().cpu().clone().requires_grad_(True)
+        P[k] = leaves[key]
+    a = model.args
+    args = dict(nb_venc_blocks=a.nb_venc_blocks, nb_cenc_blocks=a.nb_cenc_blocks, nb_aenc_blocks=0,
+                enc_vc_combine=a.enc_vc_combine, include_caption=a.include_caption, dec_st_combine=a.dec_st_combine,
+                t2s=a.t2s, s2t=a.s2t, enc_st_combine="none", ptr_ft=a.ptr_ft, auto_encoder=a.auto_encoder, mask_unk=1)
+    b = synth.make_full_batch(1, rows, c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    best = float("inf")
+    for i in range(reps + 1):              # first pass is the warm-up
+        for v in leaves.values():
+            v.grad = None
+        t0 = time.perf_counter()
+        ft = O.mtn_forward(P, args, b, a.att_h, a.nb_blocks)
+        O.loss_compute(P, args, ft, b, PAD, SMOOTHING)[0].backward()
+        dt = time.perf_counter() - t0
+        if i > 0:
+            best = min(best, dt)
+    return rows / best, best
+
+
 def kernel_model(c, e_act, nd=2):
     """Algorithmic (flops, bytes) per step summed over the launches of each kernel tag."""
     B, T, S, D, d, h, Lq, L = c["B"], c["T"], c["S"], c["D"], c["d"], c["h"], c["Lq"], c["n_blocks"]
@@ -379,6 +413,12 @@ def run_ours(args):
                                    "spatial, label smoothing 0.1, backward, gradient all-reduce (NCCL, N>1), fused Adam; train() "
                                    "mode, dropout 0.1; all arithmetic in libbist_b200 (no audio branch)")
         train_full["metric"] = "bist_train_turns_per_sec"
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, best = cpu_oracle_train_turns_per_sec(fm, 8, 2, threads)
+            train_full["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                          "sample": "8 dialogue turns of config 3, forward + losses + autograd backward "
+                                                    "(no optimizer), best of 2 after 1 warm-up (%.2f s each), fp32 torch CPU" % best}
         del fm
 
     # ---- beam-search decode at BASELINE config 5 (long video: S=49, T=128; beam 5, max_len 12), B=8 turns per GPU ---

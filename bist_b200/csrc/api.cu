@@ -55,9 +55,9 @@ ProfScope::~ProfScope() {
   g_prof_recs.push_back(r);
 }
 
-bool overlap_enabled() {
+bool overlap_enabled() {   // off while per-launch timing is on: a kernel timed beside another is not its own duration
   static const bool on = getenv("BIST_NO_OVERLAP") == nullptr;
-  return on;
+  return on && !g_prof_on.load(std::memory_order_relaxed);
 }
 int side_stream(SideStream** out) {
   static thread_local std::map<int, SideStream> tab;
