@@ -136,6 +136,41 @@ __global__ void __launch_bounds__(256) dropout_residual_kernel(const T* __restri
     out[i] = from_f32<T>(fmaf(to_f32(y[i]), drop_mul(drop, (unsigned long long)i), to_f32(x[i])));
 }
 
+// Ingest gather: the zero-padded device batch is written by ONE kernel whose threads read the page-locked host rows of
+// each video directly over PCIe (unified addressing maps pinned host memory into the device's address space) — every
+// video's transfer is in flight at once, instead of one DMA descriptor after the other with a set-up gap between them.
+constexpr int kIngestMax = 64;
+struct IngestTable {
+  const uint4* src[kIngestMax];
+  long long chunks[kIngestMax];     // 16-byte chunks of real data per video
+  int n;
+  long long slot_chunks;            // 16-byte chunks per batch row (T * S * D * elem / 16)
+};
+__global__ void __launch_bounds__(256) ingest_gather_kernel(const __grid_constant__ IngestTable tab, uint4* __restrict__ dst) {
+  const long long total = (long long)tab.n * tab.slot_chunks;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  // four independent 16-byte host reads in flight per thread: a few CTAs keep PCIe busy and the SMs stay free for the
+  // forward that runs beside this kernel
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += 4 * stride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * stride;
+      v[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (i < total) {
+        const int b = (int)(i / tab.slot_chunks);
+        const long long c = i - (long long)b * tab.slot_chunks;
+        if (c < tab.chunks[b]) v[u] = __ldcs(tab.src[b] + c);      // streaming read from host memory
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < total) dst[i] = v[u];
+    }
+  }
+}
+
 }  // namespace bist
 
 using namespace bist;
@@ -415,6 +450,47 @@ int bist_pack_params(const bist_pack_item_t* items, int64_t n, void* base, int d
     }
     BIST_TRY(pack_many(tab, m, base, &dummy_f32, dtype, st));
   }
+  return 0;
+}
+
+// Ingest: n ragged host->device row copies and the zero fill of each video's padding, issued back to back on one stream
+// (bist_b200/ingest.py: FeatureCache.collate).  src[i]: page-locked host rows; offsets in bytes from dst_base.
+int bist_ingest_gather(const void* const* src, void* dst_base, const int64_t* dst_off, const int64_t* nbytes,
+                       const int64_t* pad_off, const int64_t* pad_nbytes, int64_t n, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(src && dst_base && dst_off && nbytes && pad_off && pad_nbytes && n > 0, "ingest_gather: bad argument");
+  char* base = (char*)dst_base;
+  // Fast path: dense batch rows of equal size, 16-byte granularity -> one gather kernel per 64 videos (see above).
+  {
+    static const bool kernel_on = getenv("BIST_INGEST_DMA") == nullptr;
+    bool dense = kernel_on && ((uintptr_t)dst_base % 16 == 0);
+    const int64_t slot = n > 0 ? nbytes[0] + pad_nbytes[0] : 0;
+    for (int64_t i = 0; i < n && dense; ++i)
+      dense = src[i] && ((uintptr_t)src[i] % 16 == 0) && nbytes[i] % 16 == 0 && nbytes[i] + pad_nbytes[i] == slot &&
+              dst_off[i] == i * slot && (pad_nbytes[i] == 0 || pad_off[i] == i * slot + nbytes[i]);
+    if (dense && slot > 0 && slot % 16 == 0) {
+      for (int64_t i0 = 0; i0 < n; i0 += kIngestMax) {
+        IngestTable tab{};
+        tab.n = (int)std::min<int64_t>(kIngestMax, n - i0);
+        tab.slot_chunks = slot / 16;
+        for (int i = 0; i < tab.n; ++i) { tab.src[i] = (const uint4*)src[i0 + i]; tab.chunks[i] = nbytes[i0 + i] / 16; }
+        const long long total = (long long)tab.n * tab.slot_chunks;
+        static const int max_ctas = [] { const char* e = getenv("BIST_INGEST_CTAS"); return e ? atoi(e) : 64; }();
+        const unsigned grid = (unsigned)std::min<long long>((total + 1023) / 1024, (long long)max_ctas);
+        ProfScope ps("ingest_gather", st);
+        BIST_LAUNCH(ingest_gather_kernel, grid, 256, 0, st, tab, (uint4*)(base + i0 * slot));
+        BIST_LAUNCHED();
+      }
+      return 0;
+    }
+  }
+  // General path (BIST_INGEST_DMA=1 forces it): copy-engine transfers, all fills first, then the copies back to back.
+  for (int64_t i = 0; i < n; ++i) {
+    BIST_CHECK_ARG(src[i] && nbytes[i] >= 0 && pad_nbytes[i] >= 0, "ingest_gather: bad item %lld", (long long)i);
+    if (pad_nbytes[i] > 0) BIST_CUDA(cudaMemsetAsync(base + pad_off[i], 0, (size_t)pad_nbytes[i], st));
+  }
+  for (int64_t i = 0; i < n; ++i)
+    if (nbytes[i] > 0) BIST_CUDA(cudaMemcpyAsync(base + dst_off[i], src[i], (size_t)nbytes[i], cudaMemcpyHostToDevice, st));
   return 0;
 }
 

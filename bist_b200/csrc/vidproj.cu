@@ -49,6 +49,31 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
 }
 
 
+/* The same projection for features that are ALREADY bf16 (the ingest cache of bist_b200/ingest.py keeps them in 2 bytes
+ * on the host and on the device: half the PCIe and HBM traffic of the fp32 array the reference loads).  Rounding the fp32
+ * features to bf16 is exactly what the fused kernel above does in shared memory, so the result is the same; with a 2-byte
+ * A operand the plain tcgen05 GEMM (bias + ReLU epilogue, fp32 activations) followed by the LayerNorm kernel is faster than
+ * the fused fp32-input kernel (the contraction reads 168 MB instead of 335 MB at config 2).
+ * W16: bf16 [d, D]; ws >= N*d*4 bytes. */
+int bist_vidproj_fwd_bf16in(const void* fts16, const void* W16, const float* bias, const float* a_2, const float* b_2,
+                            void* out, int64_t N, int64_t D, int64_t d, float eps, void* ws, size_t ws_bytes,
+                            int out_dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(fts16 && W16 && bias && a_2 && b_2 && out && ws, "vidproj(bf16 in): null pointer");
+  BIST_CHECK_ARG(N > 0 && D > 0 && d > 1 && N < (1LL << 31), "vidproj(bf16 in): bad shape");
+  BIST_CHECK_ARG(dtype_ok(out_dtype), "vidproj(bf16 in): bad dtype");
+  if (ws_bytes < (size_t)N * d * 4) { set_error("vidproj(bf16 in): workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
+  float* act = (float*)ws;
+  GemmArgs g;  // encoder.py:75 — relu(W fts + b)
+  g.A = fts16; g.W = W16; g.C = act; g.bias = bias;
+  g.M = (int)N; g.N = (int)d; g.K = (int)D;
+  g.a = rows_dense(D); g.w = rows_dense(D); g.c = rows_dense(d);
+  g.relu = 1; g.a_dtype = BIST_BF16; g.w_dtype = BIST_BF16; g.tag = "vidproj_gemm";
+  BIST_TRY(gemm(g, st));
+  return layer_norm(act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                  // :80
+}
+
+
 /* Tape of the training forward: h = relu(fts W^T + b) as fp32 [N, d] (the LayerNorm cannot be inverted through a bf16
  * output) and, in bf16 mode, bf16 copies of fts [N, D] and W [d, D]: the forward contraction and the weight gradient
  * dW = dh^T fts both read the 2-byte copy (168 MB instead of 335 MB at config 2) on the tcgen05 kernels. */

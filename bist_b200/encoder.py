@@ -220,10 +220,25 @@ class VidEncoder8(nn.Module):
         """LayerNorm(relu(lin(x))) as one C-ABI call (encoder.py:75,80 / :87,90)."""
         _lib.require_cuda(x, lin.weight)
         x = x.detach()
+        needs_grad = _needs_grad(lin.weight, lin.bias, norm.a_2, norm.b_2)
+        if x.dtype == torch.bfloat16 and self.precision == "bf16" and not needs_grad:
+            # features held in bf16 by the ingest cache (ingest.py): the projection reads 2 bytes per value
+            from .modules import _BF16Cache
+            cache = self.__dict__.setdefault("_wcache", _BF16Cache())
+            x = x.contiguous()
+            D, d = lin.in_features, lin.out_features
+            N = x.numel() // D
+            out = torch.empty(x.shape[:-1] + (d,), dtype=torch.bfloat16, device=x.device)
+            ws = _ws(N * d * 4 + 256, x.device)
+            _lib.check(_lib.lib().bist_vidproj_fwd_bf16in(_lib.ptr(x), _lib.ptr(cache.get(lin.weight)), _lib.ptr(lin.bias),
+                                                          _lib.ptr(norm.a_2), _lib.ptr(norm.b_2), _lib.ptr(out), N, D, d,
+                                                          float(norm.eps), _lib.ptr(ws), ws.numel(), _lib.BF16,
+                                                          _lib.stream_ptr()), "bist_vidproj_fwd_bf16in")
+            return out
         if x.dtype != torch.float32:
             x = x.float()
         x = x.contiguous()
-        if _needs_grad(lin.weight, lin.bias, norm.a_2, norm.b_2):
+        if needs_grad:
             box = _GradBox()
             out, handle = _VidProjFn.apply(x, lin.weight, lin.bias, norm.a_2, norm.b_2, norm.eps, self.precision, box)
             out._bist_box, out._bist_handle = box, handle      # picked up by VidEncoderLayer4.forward
@@ -530,13 +545,19 @@ class PipelinedVideoPath:
             e.record()
         self.n = 0
 
-    def submit(self, b, encoded_query, out_temporal=None, out_spatial=None):
+    def submit(self, b, encoded_query, out_temporal=None, out_spatial=None, fill=None):
+        """``fill(slot)``: optional callable that writes the slot's static inputs itself (e.g. ``FeatureCache.collate``
+        into ``slot.static_b.fts`` / ``.temporal_mask``); it runs on the copy stream.  Otherwise ``b`` and
+        ``encoded_query`` (host or device tensors of the captured shapes) are copied in."""
         k = self.n % len(self.slots)
         g = self.slots[k]
         cur = torch.cuda.current_stream()
         self.copy_stream.wait_event(self.free[k])          # slot k's previous replay and read-back are done
         with torch.cuda.stream(self.copy_stream):
-            g.load(b, encoded_query, non_blocking=True)
+            if fill is not None:
+                fill(g)
+            else:
+                g.load(b, encoded_query, non_blocking=True)
             self.loaded[k].record(self.copy_stream)
         cur.wait_event(self.loaded[k])
         out = g.replay()

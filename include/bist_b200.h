@@ -322,6 +322,19 @@ int bist_gate_combine_fwd(const void* const* src, const float* logits, void* out
 int bist_gate_combine_bwd(const void* d_out, const void* const* src, const float* logits, void* const* d_src,
                           float* d_logits, int64_t R, int64_t d, int K, int dtype, void* stream);
 
+/* ---- feature ingest ------------------------------------------------------------------------
+ * VidEncoder8's projection (encoder.py:72-80) for features already held in bf16 (bist_b200/ingest.py keeps the feature
+ * cache in 2 bytes per value on the host and the device): fts16 bf16 [N, D], W16 bf16 [d, D], ws >= N*d*4 bytes. */
+int bist_vidproj_fwd_bf16in(const void* fts16, const void* W16, const float* bias, const float* a_2, const float* b_2,
+                            void* out, int64_t N, int64_t D, int64_t d, float eps, void* ws, size_t ws_bytes,
+                            int out_dtype, void* stream);
+
+/* n ragged host->device copies (src[i]: page-locked host rows, nbytes[i] to dst_base + dst_off[i]) each followed by the
+ * zero fill of that video's padding (pad_nbytes[i] at dst_base + pad_off[i]), all on `stream`: the collate of
+ * data/dataset.py:164-174 without a padded host copy. */
+int bist_ingest_gather(const void* const* src, void* dst_base, const int64_t* dst_off, const int64_t* nbytes,
+                       const int64_t* pad_off, const int64_t* pad_nbytes, int64_t n, void* stream);
+
 /* ---- text side and generator ------------------------------------------------------------
  * Embeddings + PositionalEncoding (modules.py:115-141): out[r,:] = dropout(lut[idx[r],:] * sqrt(d) + pe[r % L,:]),
  * rows = B*L token positions, lut fp32 [vocab, d], pe fp32 [>= L, d], out in out_dtype.  Backward scatter-adds
