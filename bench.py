@@ -142,6 +142,29 @@ def cpu_oracle_train_turns_per_sec(model, rows, reps, threads):
     return rows / best, best
 
 
+def cpu_oracle_decode_turns_per_sec(model, shapes, max_len_sample, max_len, beam, threads):
+    """Time the CPU oracle's beam search (the reference's procedure: every hypothesis of every step re-runs the whole
+    decoder, video blocks included) on ONE dialogue turn of config 5 for `max_len_sample` of the `max_len` steps, and
+    scale by the count of hypothesis-decodes (1 at step 0, `beam` afterwards)."""
+    from bist_b200 import synth
+    from bist_b200.core import FULL_SHAPES
+    from oracle import bist_oracle as O
+    torch.set_num_threads(threads)
+    c = dict(FULL_SHAPES, **shapes)
+    P = {k: v.detach().float().cpu() for k, v in model.state_dict().items() if not k.endswith(".pe")}
+    a = model.args
+    args = dict(nb_venc_blocks=a.nb_venc_blocks, nb_cenc_blocks=a.nb_cenc_blocks, nb_aenc_blocks=0,
+                enc_vc_combine=a.enc_vc_combine, include_caption=a.include_caption, dec_st_combine=a.dec_st_combine,
+                t2s=a.t2s, s2t=a.s2t, enc_st_combine="none", ptr_ft=a.ptr_ft, auto_encoder=a.auto_encoder, mask_unk=1)
+    b = synth.make_full_batch(5, 1, c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        O.beam_search(P, args, b, a.att_h, a.nb_blocks, max_len_sample, 2, 0, 3, beam=beam, penalty=1.0, nbest=5, min_len=1)
+        dt = time.perf_counter() - t0
+    done, full = 1 + beam * (max_len_sample - 1), 1 + beam * (max_len - 1)
+    return 1.0 / (dt * full / done), dt, done, full
+
+
 def kernel_model(c, e_act, nd=2):
     """Algorithmic (flops, bytes) per step summed over the launches of each kernel tag."""
     B, T, S, D, d, h, Lq, L = c["B"], c["T"], c["S"], c["D"], c["d"], c["h"], c["Lq"], c["n_blocks"]
@@ -486,6 +509,13 @@ def run_ours(args):
                           "dialogue turns per GPU over long videos (T=128 clips x S=49 regions x 2048), whole model in "
                           "libbist_b200; the video / caption blocks run once per turn and all hypotheses of all turns go "
                           "through the decoder layers as one batch (the reference re-runs everything per hypothesis per step)"}
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, dt, done, full = cpu_oracle_decode_turns_per_sec(dm, dshape, 12, 12, 5, threads)
+            decode["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                      "sample": "1 dialogue turn of config 5, the whole search (beam 5, max_len 12: %d of %d "
+                                                "hypothesis decodes) in %.1f s, fp32 torch CPU, the reference's procedure "
+                                                "(whole decoder incl. video blocks per hypothesis per step)" % (done, full, dt)}
         del dm
 
     cpu = None

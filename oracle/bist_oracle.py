@@ -419,14 +419,73 @@ def loss_compute(P, args, ft, b, pad, smoothing=0.1):
     return sum(parts.values()), parts
 
 
-def mtn_forward(P, args, b, h, n_blocks, drop=None):
-    """MTN.forward (mtn.py:31-61): embeddings -> text encoder norms -> video encoder -> multimodal decoder."""
+def mtn_encode(P, b, drop=None):
+    """MTN.encode (mtn.py:36-52): embeddings -> text-encoder norms -> video projection; target-independent."""
     ft = {}
     eq, ec, eh = (embed(P, "query_embed.", ids, drop, f"query_embed.{n}") for n, ids in (("query", b.query), ("cap", b.cap), ("his", b.his)))
     for i, (key, x) in enumerate((("encoded_query", eq), ("encoded_cap", ec), ("encoded_his", eh))):   # encoder.py:19-40
         ft[key] = layer_norm(x, P[f"text_encoder.norm.{i}.a_2"], P[f"text_encoder.norm.{i}.b_2"])
     ft["spatiotemporal_ft"], _ = vid_encoder8(P, "vid_encoder.", b.fts)
+    return ft
+
+
+def mtn_decode(P, args, b, ft, h, n_blocks, drop=None):
+    """MTN.decode (mtn.py:54-62): target embedding -> multimodal decoder (which re-runs its video / caption blocks)."""
+    ft = dict(ft)
     ft["encoded_tgt"] = embed(P, "tgt_embed.", b.trg, drop, "tgt_embed.trg")
     masks = dict(trg=b.trg_mask, his=b.his_mask, query=b.query_mask, cap=b.cap_mask, audio=getattr(b, "audio_mask", None),
                  temporal=b.temporal_mask)
     return multimodal_decoder8(P, "mutlimodal_decoder.", h, args, ft, ft["encoded_tgt"], masks, n_blocks, drop)
+
+
+def mtn_forward(P, args, b, h, n_blocks, drop=None):
+    """MTN.forward (mtn.py:31-34): encode, then decode."""
+    return mtn_decode(P, args, b, mtn_encode(P, b, drop), h, n_blocks, drop)
+
+
+# ----------------------------------------------------------------------------- §8(f) row 3: beam search
+def beam_search(P, args, b, h, n_blocks, max_len, start_symbol, unk_symbol, end_symbol, beam=5, penalty=1.0, nbest=5,
+                min_len=1, dec_eos=False):
+    """beam_search_decode (decode.py:53-104) for ONE dialogue turn, in the reference's order of operations: one
+    encode, then per step and per live hypothesis one full decode (video / caption blocks included) + generator on the
+    last position, the completed-hypothesis list scored with the end symbol, and the fill-then-replace-the-minimum
+    candidate selection over the descending argsort of the [V] scores.  Returns (n-best [(tokens, score)], best_state).
+    Pinned by tests/golden/beam_*.npz (the unmodified reference's hypotheses)."""
+    import copy
+    import numpy as np
+    ft = mtn_encode(P, b)
+    hyps, comp, best = [([], 0., [int(start_symbol)])], [], None
+    skip = (unk_symbol,) if dec_eos else (unk_symbol, end_symbol)
+    for l in range(max_len):
+        new, argmin = [], 0
+        for out, lp, st in hyps:
+            bb = copy.copy(b)
+            bb.trg = torch.tensor([st], dtype=torch.long)
+            bb.trg_mask = torch.tril(torch.ones(1, len(st), len(st), dtype=torch.bool))      # subsequent_mask
+            f = mtn_decode(P, args, bb, ft, h, n_blocks)
+            f["decoded_text"], f["encoded_tgt"] = f["decoded_text"][:, -1:], f["encoded_tgt"][:, -1:]
+            logp = generator_logp(P, "generator.", f, bb, args["ptr_ft"], args.get("mask_unk", 1))
+            lp_vec = np.squeeze(logp.detach().numpy() + lp)
+            if l >= min_len:
+                new_lp = lp_vec[end_symbol] + penalty * (len(out) + 1)
+                comp.append((out, new_lp))
+                if best is None or best < new_lp:
+                    best = new_lp
+            for o in np.argsort(lp_vec)[::-1]:
+                if o in skip:
+                    continue
+                new_lp = lp_vec[o]
+                if len(new) == beam:
+                    if new[argmin][1] < new_lp:
+                        new[argmin] = (out + [o], new_lp, st + [int(o)])
+                        argmin = min(enumerate(new), key=lambda e: e[1][1])[0]
+                    else:
+                        break
+                else:
+                    new.append((out + [o], new_lp, st + [int(o)]))
+                    if len(new) == beam:
+                        argmin = min(enumerate(new), key=lambda e: e[1][1])[0]
+        hyps = new
+    if comp:
+        return sorted(comp, key=lambda e: -e[1])[:nbest], best
+    return [([], 0)], None
