@@ -23,7 +23,7 @@ namespace {
 using namespace tc;
 
 constexpr int VP_BK = 32;                      // K elements per ring slot
-constexpr int VP_STAGES = 3;                   // MMA ring: bf16 A slab + W slab
+constexpr int VP_STAGES = 6;                   // MMA ring (bf16 A slab + W slab): barrier slots; L.ms of them are used
 constexpr int VP_MAX_A = 8;                    // fp32 A ring: at most this many slabs
 constexpr int VP_AF = 128 * VP_BK * 4;         // fp32 A slab   16 KB (SWIZZLE_128B)
 constexpr int VP_AB = 128 * VP_BK * 2;         // bf16 A slab    8 KB (SWIZZLE_64B)
@@ -36,18 +36,75 @@ __device__ long long g_vtrace[4][64];   // CTA 0 only: [role][event]
 #define VTRACE(role, idx) do {} while (0)
 #endif
 
+// ---- CTA-pair (cta_group::2) variants of the wrappers in tc_ptx.cuh ------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Arrive on the barrier at the same offset in CTA `cta` of the cluster.  RELAXED on purpose: the release form stalls the
+// arriving warp for about a microsecond per slab (253 vs 140 us for the whole kernel).  What the arrive publishes are
+// this warp's st.shared writes to its OWN shared memory, already ordered by fence.proxy.async + __syncwarp before this
+// instruction issues; the leader reads them only through the tensor core after it has observed the arrival.
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(bar)), "r"(cta));
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(r) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  const uint32_t addr = smem_u32(bar);
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void tc_mma2(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+// completion of the pair's UMMAs -> the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit2(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* slot_in_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+#ifndef VP_PAIR_STAGES
+#define VP_PAIR_STAGES 5
+#endif
+__host__ __device__ inline int vp_pair_stages() { return VP_PAIR_STAGES; }
 struct VpSmem {
-  int wb_bytes, stage_bytes, na, mma_off, stg_off, red_off, bar_off, total;
+  int wb_bytes, stage_bytes, na, ms, mma_off, stg_off, red_off, bar_off, total;
 };
-__host__ __device__ inline VpSmem vp_smem(int d) {
+__host__ __device__ inline VpSmem vp_smem(int d, int ncta) {
   VpSmem s;
-  s.wb_bytes = d * VP_BK * 2;                   // bf16 W slab (SWIZZLE_64B), d rows
+  s.wb_bytes = d * VP_BK * 2 / ncta;            // bf16 W slab (SWIZZLE_64B): d rows, or this CTA's half of each UMMA's N
   s.stage_bytes = VP_AB + s.wb_bytes;           // MMA-ring slot; multiple of 1024 for d % 16 == 0
-  const int fixed = VP_STAGES * s.stage_bytes + 8 * 32 * VP_STG_LD * 4 + 2 * 128 * 3 * 4 + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
+  // a CTA pair hands slots back and forth across two SMs (multicast commit, remote arrive): its MMA ring is deeper
+  s.ms = ncta == 2 ? vp_pair_stages() : 3;
+  const int fixed = s.ms * s.stage_bytes + 8 * 32 * VP_STG_LD * 4 + 2 * 128 * 3 * 4 + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
   int na = (227 * 1024 - fixed) / VP_AF;        // every byte left over goes to fp32 slabs in flight
   s.na = na > VP_MAX_A ? VP_MAX_A : na;
   s.mma_off = s.na * VP_AF;
-  s.stg_off = s.mma_off + VP_STAGES * s.stage_bytes;   // 8 worker warps x [32][36] floats
+  s.stg_off = s.mma_off + s.ms * s.stage_bytes;        // 8 worker warps x [32][36] floats
   s.red_off = s.stg_off + 8 * 32 * VP_STG_LD * 4;      // row statistics exchange: [2][128] x (n, mean, M2)
   s.bar_off = s.red_off + 2 * 128 * 3 * 4;
   s.total = s.bar_off + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
@@ -63,16 +120,17 @@ struct VpArgs {
   float eps;
 };
 
+template <int NCTA>
 __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__ CUtensorMap map_a,
                                                          const __grid_constant__ CUtensorMap map_w, const VpArgs p) {
   pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const VpSmem L = vp_smem(p.d);
+  const VpSmem L = vp_smem(p.d, NCTA);
   uint64_t* afull = (uint64_t*)(smem + L.bar_off);  // fp32 A slab landed
   uint64_t* aempty = afull + VP_MAX_A;              // fp32 A slab converted (8 worker-warp arrivals)
   uint64_t* wfull = aempty + VP_MAX_A;              // bf16 W slab landed
-  uint64_t* conv = wfull + VP_STAGES;               // bf16 A written (8 worker-warp arrivals)
+  uint64_t* conv = wfull + VP_STAGES;               // bf16 A written (8 worker-warp arrivals per CTA, counted at the leader)
   uint64_t* empty = conv + VP_STAGES;               // UMMAs that read the MMA-ring slot have completed
   uint64_t* acc_full = empty + VP_STAGES;
   uint64_t* acc_empty = acc_full + 1;
@@ -80,17 +138,29 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.d;
   const int nhalf = d > 256 ? 2 : 1, nmma = d / nhalf;   // UMMA N <= 256
+  // NCTA == 2: the two CTAs of a cluster work on a PAIR of row tiles with one UMMA of M = 256; each holds its own 128
+  // rows of A and HALF of each W slab (the B operand of a cta_group::2 UMMA is split over the pair), so every SM pulls
+  // half the weight bytes from L2 and the tensor core reads half the B bytes from each shared memory.
+  const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
+  const int unit0 = NCTA == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int ustep = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int units = NCTA == 2 ? (p.tiles + 1) >> 1 : p.tiles;
+  const int wrows = nmma / NCTA;                         // W rows per UMMA held by this CTA
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < VP_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 8); }
-    for (int s = 0; s < VP_STAGES; ++s) { mbar_init(&wfull[s], 1); mbar_init(&conv[s], 8); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < VP_STAGES; ++s) { mbar_init(&wfull[s], 1); mbar_init(&conv[s], 8 * NCTA); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
-    mbar_init(acc_empty, 8);
+    mbar_init(acc_empty, 8 * NCTA);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) {
+    if (NCTA == 2) tmem_alloc2(tmem_slot, 512);
+    else tmem_alloc(tmem_slot, 512);
+  }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();   // the peer's barriers exist before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything above overlapped the tail of the previous kernel
@@ -98,8 +168,8 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   if (warp == 0) {
     if (lane == 0) {
       int sa = 0, pa = 0, it = 0;
-      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-        const int m0 = tile * 128;
+      for (int u = unit0; u < units; u += ustep) {
+        const int m0 = (NCTA * u + rank) * 128;   // a tile past the end (odd tile count) loads zeros
         // two slabs (adjacent 128-byte segments of the same 128 feature rows) are requested back to back, so the second
         // finds the DRAM pages the first opened: 154.7 -> 144.9 us at config 2
         const int grp = L.na >= 4 ? 2 : 1;
@@ -122,42 +192,47 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   } else if (warp == 10) {
     if (lane == 0) {
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+      for (int u = unit0; u < units; u += ustep) {
         for (int kb = 0; kb < p.nkb; ++kb, ++it) {
-          const int s = it % VP_STAGES;
-          mbar_wait(&empty[s], ((it / VP_STAGES) & 1) ^ 1);
+          const int s = it % L.ms;
+          mbar_wait(&empty[s], ((it / L.ms) & 1) ^ 1);
           mbar_expect_tx(&wfull[s], L.wb_bytes);
           uint8_t* st = smem + L.mma_off + s * L.stage_bytes + VP_AB;
           for (int hN = 0; hN < nhalf; ++hN)
-            tma_load_2d(st + hN * nmma * VP_BK * 2, &map_w, &wfull[s], kb * VP_BK, hN * nmma);
+            tma_load_2d(st + hN * wrows * VP_BK * 2, &map_w, &wfull[s], kb * VP_BK, hN * nmma + rank * wrows);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nmma >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    if (lane == 0 && rank == 0) {   // the leader CTA issues for the pair
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nmma >> 3) << 17) | ((uint32_t)((128 * NCTA) >> 4) << 24);
       int it = 0, tc_ = 0;
-      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++tc_) {
-        mbar_wait(acc_empty, (tc_ & 1) ^ 1);
+      for (int u = unit0; u < units; u += ustep, ++tc_) {
+        if (NCTA == 2) mbar_wait_cluster(acc_empty, (tc_ & 1) ^ 1);
+        else mbar_wait(acc_empty, (tc_ & 1) ^ 1);
         tc_fence_after();
         for (int kb = 0; kb < p.nkb; ++kb, ++it) {
-          const int s = it % VP_STAGES;
-          mbar_wait(&wfull[s], (it / VP_STAGES) & 1);
-          mbar_wait(&conv[s], (it / VP_STAGES) & 1);
+          const int s = it % L.ms;
+          mbar_wait(&wfull[s], (it / L.ms) & 1);
+          if (NCTA == 2) mbar_wait_cluster(&conv[s], (it / L.ms) & 1);   // both A slabs converted, the peer's W half landed
+          else mbar_wait(&conv[s], (it / L.ms) & 1);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + L.mma_off + s * L.stage_bytes);
           const uint64_t ad = make_desc_sw64(sa);
 #pragma unroll
           for (int k = 0; k < VP_BK / 16; ++k) {
             for (int hN = 0; hN < nhalf; ++hN) {
-              const uint64_t wd = make_desc_sw64(sa + VP_AB + hN * nmma * VP_BK * 2);
-              tc_mma<false>(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+              const uint64_t wd = make_desc_sw64(sa + VP_AB + hN * wrows * VP_BK * 2);
+              if (NCTA == 2) tc_mma2(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+              else tc_mma<false>(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
             }
           }
-          tc_commit(&empty[s]);
+          if (NCTA == 2) tc_commit2(&empty[s]);
+          else tc_commit(&empty[s]);
           VTRACE(1, it);
         }
-        tc_commit(acc_full);
+        if (NCTA == 2) tc_commit2(acc_full);
+        else tc_commit(acc_full);
       }
     }
   } else {
@@ -172,10 +247,11 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
     const uint32_t stg_r = stg + (uint32_t)((sub_r * VP_STG_LD + sub_c) * 4);
     float* red = (float*)(smem + L.red_off);         // [2][128][3]
     int it = 0, tc_ = 0, sa = 0, pa = 0;
-    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++tc_) {
+    for (int u = unit0; u < units; u += ustep, ++tc_) {
+      const int tile = NCTA * u + rank;
       // ---- main loop: fp32 slab -> bf16 slab ------------------------------------------------------------
       for (int kb = 0; kb < p.nkb; ++kb, ++it) {
-        const int s = it % VP_STAGES;
+        const int s = it % L.ms;
         mbar_wait(&afull[sa], pa);
         if (warp == 2 && lane == 0) VTRACE(2, it);
         const uint32_t af = smem_u32(smem + sa * VP_AF) + (uint32_t)(crow * 128);
@@ -196,7 +272,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         __syncwarp();
         if (lane == 0) mbar_arrive(&aempty[sa]);     // the fp32 slot is in registers: the next slab may land
         if (++sa == L.na) { sa = 0; pa ^= 1; }
-        mbar_wait(&empty[s], ((it / VP_STAGES) & 1) ^ 1);   // the UMMAs that read this bf16 slot have retired
+        mbar_wait(&empty[s], ((it / L.ms) & 1) ^ 1);   // the UMMAs that read this bf16 slot have retired
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {  // logical 16-byte chunk 2*chalf + jj of a SWIZZLE_64B row
           const uint32_t a = ab + (uint32_t)((((2 * chalf + jj) ^ ((crow >> 1) & 3))) << 4);
@@ -206,7 +282,14 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         }
         fence_proxy_async_smem();   // make the generic-proxy writes visible to the tensor core's async proxy
         __syncwarp();
-        if (lane == 0) mbar_arrive(&conv[s]);
+        if (lane == 0) {
+          if (rank == 0) {
+            mbar_arrive(&conv[s]);
+          } else {
+            mbar_wait(&wfull[s], (it / L.ms) & 1);   // this CTA's half of the W slab has landed too
+            mbar_arrive_cta(&conv[s], 0);
+          }
+        }
         if (warp == 2 && lane == 0) VTRACE(3, it);
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
@@ -260,7 +343,10 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         if (c0 + 32 >= hcols) {  // accumulator fully read by this warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(acc_empty);
+          if (lane == 0) {
+            if (rank == 0) mbar_arrive(acc_empty);
+            else mbar_arrive_cta(acc_empty, 0);
+          }
         }
         const int col = ch * hcols + c0;
         const float* bp = p.bias + col;
@@ -299,9 +385,11 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();   // the peer may still be signalled by / read through this CTA until here
   if (warp == 1) {
     __syncwarp();
-    tmem_dealloc(tmem_base, 512);
+    if (NCTA == 2) tmem_dealloc2(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -322,26 +410,43 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   if ((reinterpret_cast<uintptr_t>(fts) & 15) || (reinterpret_cast<uintptr_t>(wb) & 15) || (reinterpret_cast<uintptr_t>(out) & 15) ||
       (reinterpret_cast<uintptr_t>(bias) & 15) || (reinterpret_cast<uintptr_t>(a2) & 15) || (reinterpret_cast<uintptr_t>(b2) & 15))
     return 0;
-  const VpSmem L = vp_smem((int)d);
+  static const int pair = getenv("BIST_VP_2CTA") ? atoi(getenv("BIST_VP_2CTA")) : 1;   // 0: one CTA per tile
+  const int ncta = (pair && (d / (d > 256 ? 2 : 1)) % 32 == 0) ? 2 : 1;   // cta_group::2: UMMA N a multiple of 16 per CTA
+  const VpSmem L = vp_smem((int)d, ncta);
   if (L.total > 227 * 1024 || L.na < 2) return 0;
   *taken = true;
   BIST_TRY(pack_matrix(W, wb, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
   const int nmma = (int)(d > 256 ? d / 2 : d);
   CUtensorMap ma, mw;
   BIST_TRY(make_map_2d(&ma, fts, true, D, N, VP_BK, 128, 128));
-  BIST_TRY(make_map_2d(&mw, wb, false, D, d, VP_BK, nmma, 64));
+  BIST_TRY(make_map_2d(&mw, wb, false, D, d, VP_BK, nmma / ncta, 64));
   static bool configured = false;
   if (!configured) {
-    BIST_CUDA(cudaFuncSetAttribute(vidproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    BIST_CUDA(cudaFuncSetAttribute(vidproj_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    BIST_CUDA(cudaFuncSetAttribute(vidproj_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   VpArgs p;
   p.bias = bias; p.a2 = a2; p.b2 = b2; p.out = out;
   p.N = (int)N; p.D = (int)D; p.d = (int)d; p.out_bf16 = out_dtype == BIST_BF16;
   p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
-  const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   ProfScope ps("vidproj_fused", st);
-  BIST_LAUNCH(vidproj_kernel, grid, 352, L.total, st, ma, mw, p);
+  if (ncta == 2) {
+    const int pairs = (p.tiles + 1) / 2, max_pairs = num_sms() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * (pairs < max_pairs ? pairs : max_pairs)); cfg.blockDim = dim3(352);
+    cfg.dynamicSmemBytes = (size_t)L.total; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 2;
+    BIST_CUDA(cudaLaunchKernelEx(&cfg, vidproj_kernel<2>, ma, mw, p));
+  } else {
+    const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+    BIST_LAUNCH(vidproj_kernel<1>, grid, 352, L.total, st, ma, mw, p);
+  }
   BIST_LAUNCHED();
   return 0;
 }
