@@ -44,19 +44,24 @@ __device__ long long g_trace[3][64];   // CTA 0 only: [role][event]
 
 constexpr int STG_LD = 36;  // floats per staging row: 16-byte aligned, conflict-free for float4 in both phases
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int NCTA = 1>
 struct Smem {
-  static constexpr int A_BYTES = BM * SLAB_BYTES, W_BYTES = BN * SLAB_BYTES;
+  static constexpr int A_BYTES = BM * SLAB_BYTES, W_BYTES = BN * SLAB_BYTES / NCTA;   // a CTA pair splits the W tile
   static constexpr int STAGE_BYTES = A_BYTES + W_BYTES;
   static constexpr int STG_OFF = STAGES * STAGE_BYTES;           // 8 epilogue warps x [32][STG_LD] floats
   static constexpr int BAR_OFF = STG_OFF + 8 * 32 * STG_LD * 4;
   static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
 };
 
-template <int BN, int STAGES, bool TF32>
+// NCTA == 2 (bf16, plain W tiles, BN = 256): the two CTAs of a cluster compute two vertically adjacent 128 x 256 tiles
+// with ONE cta_group::2 UMMA of M = 256.  Each CTA loads its own 128 rows of A and 128 of the 256 W rows, so an SM pulls
+// 32 KB instead of 48 KB per K slab from L2 and the tensor core reads half of B from each shared memory; the ring is 5
+// slots deep instead of 3.  All TMA bytes are counted on the leader's `full` barriers, tcgen05.commit multicasts `empty`
+// and `acc_full` to both CTAs, the peer's epilogue warps hand the accumulator back with remote arrives.
+template <int BN, int STAGES, bool TF32, int NCTA = 1>
 __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                          const __grid_constant__ CUtensorMap map_w, const TcArgs t) {
-  using S = Smem<BN, STAGES>;
+  using S = Smem<BN, STAGES, NCTA>;
   constexpr int ESZ = TF32 ? 4 : 2;
   constexpr int BKE = SLAB_BYTES / ESZ;        // elements of K per slab: 64 bf16 / 32 tf32
   constexpr int UMMA_K = 32 / ESZ;             // 16 bf16 / 8 tf32 (32 bytes of K per instruction)
@@ -74,23 +79,30 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8 * NCTA); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  if (warp == 1) {
+    if (NCTA == 2) tmem_alloc2(tmem_slot, 2 * BN);
+    else tmem_alloc(tmem_slot, 2 * BN);
+  }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything above overlapped the tail of the previous kernel
-  const int per_z = t.tiles_m * t.tiles_n;
+  const int per_z = t.tiles_m * t.tiles_n;   // NCTA == 2: tiles_m counts PAIRS of row tiles
+  const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
+  const int unit0 = NCTA == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int ustep = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0) {
     if (lane == 0) {
       int it = 0;
-      for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x) {
+      for (int tile = unit0; tile < t.total_tiles; tile += ustep) {
         const int z = tile / per_z, rem = tile - z * per_z;
-        const int m0 = (rem / t.tiles_n) * BM, nt = rem % t.tiles_n, n0 = nt * BN;
+        const int m0 = (NCTA * (rem / t.tiles_n) + rank) * BM, nt = rem % t.tiles_n, n0 = nt * BN + rank * (BN / 2);
         // batch offsets become (row, column) coordinates inside the 2-D tensors
         const long long ao = g.az.off(z, g.zin, g.zmid), wo = g.wz.off(z, g.zin, g.zmid);
         const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
@@ -98,24 +110,31 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
           uint8_t* st = smem + s * S::STAGE_BYTES;
-          tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-          if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
-          else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          if (NCTA == 2) {
+            if (rank == 0) mbar_expect_tx(&full[s], 2 * S::STAGE_BYTES);   // both CTAs' A and W bytes land on the leader's barrier
+            tma_load_2d_pair(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+            tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          } else {
+            mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
+            tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+            if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
+            else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          }
           TRACE(0, it);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {
       // instruction descriptor (cute::UMMA::InstrDescriptor): D = f32, A/B = bf16 | tf32, K-major both
       const uint32_t fmt = TF32 ? 2u : 1u;
-      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
       int it = 0, tc_ = 0;
-      for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x, ++tc_) {
+      for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
         const int a = tc_ & 1;
-        mbar_wait(&acc_empty[a], ((tc_ >> 1) & 1) ^ 1);
+        if (NCTA == 2) mbar_wait_cluster(&acc_empty[a], ((tc_ >> 1) & 1) ^ 1);
+        else mbar_wait(&acc_empty[a], ((tc_ >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(a * BN);
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
@@ -125,12 +144,16 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
           const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
           const uint64_t ad = make_desc(sa), wd = make_desc(sa + S::A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BKE / UMMA_K; ++k)  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
-            tc_mma<TF32>(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
-          tc_commit(&empty[s]);
+          for (int k = 0; k < BKE / UMMA_K; ++k) {  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
+            if (NCTA == 2) tc_mma2(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            else tc_mma<TF32>(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          }
+          if (NCTA == 2) tc_commit2(&empty[s]);
+          else tc_commit(&empty[s]);
           TRACE(1, it);
         }
-        tc_commit(&acc_full[a]);
+        if (NCTA == 2) tc_commit2(&acc_full[a]);
+        else tc_commit(&acc_full[a]);
       }
     }
   } else {
@@ -148,9 +171,9 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
     const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M;
     const bool c_bf16 = g.c_dtype == BIST_BF16, r_bf16 = g.r_dtype == BIST_BF16, has_r = g.R != nullptr;
     int tc_ = 0;
-    for (int tile = blockIdx.x; tile < t.total_tiles; tile += gridDim.x, ++tc_) {
+    for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
       const int z = tile / per_z, rem = tile - z * per_z;
-      const int m0 = (rem / t.tiles_n) * BM, n0 = (rem % t.tiles_n) * t.bn_valid;
+      const int m0 = (NCTA * (rem / t.tiles_n) + rank) * BM, n0 = (rem % t.tiles_n) * t.bn_valid;
       const int Ntot = min(g.N, n0 + t.bn_valid);  // first column this tile does not own
       const int a = tc_ & 1;
       const float* bias = g.bias ? g.bias + g.bz.off(z, g.zin, g.zmid) : nullptr;
@@ -186,7 +209,10 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         if (cj + 32 >= CH_COLS) {  // last chunk of this warp: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[a]);
+          if (lane == 0) {
+            if (rank == 0) mbar_arrive(&acc_empty[a]);
+            else mbar_arrive_cta(&acc_empty[a], 0);
+          }
         }
         if (!live) continue;
 #pragma unroll
@@ -259,9 +285,11 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();
   if (warp == 1) {
     __syncwarp();
-    tmem_dealloc(tmem_base, 2 * BN);
+    if (NCTA == 2) tmem_dealloc2(tmem_base, 2 * BN);
+    else tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
@@ -284,6 +312,36 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
   if (t.g.max_ctas > 0 && grid > t.g.max_ctas) grid = t.g.max_ctas;
   ProfScope ps(t.g.tag, st);
   BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, tt);
+  BIST_LAUNCHED();
+  return 0;
+}
+
+// CTA-pair form (bf16, BN = 256, plain W tiles): units are pairs of vertically adjacent row tiles, clusters of two CTAs.
+int launch_pair(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
+  auto kern = gemm_tc_kernel<256, 5, false, 2>;
+  constexpr int smem = Smem<256, 5, 2>::TOTAL;
+  static bool configured = false;
+  if (!configured) {
+    BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  TcArgs tt = t;
+  tt.tiles_m = ((t.g.M + BM - 1) / BM + 1) / 2;
+  tt.bn_valid = 256; tt.w_stage_bytes = 128 * SLAB_BYTES;
+  tt.tiles_n = (t.g.N + 255) / 256;
+  tt.total_tiles = tt.tiles_m * tt.tiles_n * t.g.Z;
+  int pairs = tt.total_tiles < num_sms() / 2 ? tt.total_tiles : num_sms() / 2;
+  if (t.g.max_ctas > 1 && pairs > t.g.max_ctas / 2) pairs = t.g.max_ctas / 2;
+  ProfScope ps(t.g.tag, st);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(320); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  at[1].id = cudaLaunchAttributeClusterDimension;
+  at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 2;
+  BIST_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, tt));
   BIST_LAUNCHED();
   return 0;
 }
@@ -384,6 +442,11 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     BIST_TRY(make_map_3d(&mw, g.W, false, w_ld, w_rows / g.wr_S, g.wr_S, (long long)g.wr_S * w_ld * esz, w_ld * esz, SLAB_BYTES / esz,
                          g.wr_T, t.s_box));
   } else {
+    static const int pair_rows = getenv("BIST_GEMM_2CTA") ? atoi(getenv("BIST_GEMM_2CTA")) : 0;   // min M for the CTA-pair form; 0 = off
+    if (bf && bn == 256 && pair_rows > 0 && g.M >= pair_rows) {
+      BIST_TRY(make_map_2d(&mw, g.W, false, w_ld, w_rows, SLAB_BYTES / esz, 128, 128));
+      return launch_pair(t, ma, mw, st);
+    }
     BIST_TRY(make_map_2d(&mw, g.W, !bf, w_ld, w_rows, SLAB_BYTES / esz, bn, 128));
   }
   if (bf) {
