@@ -125,10 +125,12 @@ def cpu_oracle_train_turns_per_sec(model, rows, reps, threads):
             leaves[key] = v.detach().float().cpu().clone().requires_grad_(True)
         P[k] = leaves[key]
     a = model.args
-    args = dict(nb_venc_blocks=a.nb_venc_blocks, nb_cenc_blocks=a.nb_cenc_blocks, nb_aenc_blocks=0,
+    audio = getattr(a, "nb_aenc_blocks", 0) > 0
+    args = dict(nb_venc_blocks=a.nb_venc_blocks, nb_cenc_blocks=a.nb_cenc_blocks, nb_aenc_blocks=a.nb_aenc_blocks if audio else 0,
                 enc_vc_combine=a.enc_vc_combine, include_caption=a.include_caption, dec_st_combine=a.dec_st_combine,
                 t2s=a.t2s, s2t=a.s2t, enc_st_combine="none", ptr_ft=a.ptr_ft, auto_encoder=a.auto_encoder, mask_unk=1)
-    b = synth.make_full_batch(1, rows, c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    b = synth.make_full_batch(1, rows, c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"],
+                              Ta=c["Ta"] if audio else 0, Da=c["Da"] if audio else 0)
     best = float("inf")
     for i in range(reps + 1):              # first pass is the warm-up
         for v in leaves.values():
@@ -430,7 +432,7 @@ def run_ours(args):
     # ---- training steps (forward with tape + backward + grad all-reduce + Adam) ------------------------------
     # forward + loss + backward replay as ONE CUDA graph (bist_b200/graph.py: weights re-packed and dropout masks
     # re-drawn inside the graph); the gradient all-reduce (NCCL, N>1) and the fused Adam step run eagerly after it.
-    train = train_full = None
+    train = train_full = train_full_audio = None
     if not args.no_train:
         from bist_b200.dist import allreduce_grads, overlap_grad_allreduce
         from bist_b200.graph import GraphedTrainStep
@@ -498,7 +500,8 @@ def run_ours(args):
                                    "blocks): embeddings + positional encoding, text-encoder norms, VidEncoder8, MultimodalDecoder8 "
                                    "with softmax gate, pointer generator over query and caption, auto-encoder heads on cap/temporal/"
                                    "spatial, label smoothing 0.1, backward, gradient all-reduce (NCCL, N>1), fused Adam; train() "
-                                   "mode, dropout 0.1; all arithmetic in libbist_b200 (no audio branch)")
+                                   "mode, dropout 0.1; all arithmetic in libbist_b200 (exec.sh's configuration: nb_aenc_blocks=0, "
+                                   "train_configs.py:30; the audio encoder is the train_full_audio leg)")
         train_full["metric"] = "bist_train_turns_per_sec"
         if rank == 0 and world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
@@ -506,7 +509,28 @@ def run_ours(args):
             train_full["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                           "sample": "8 dialogue turns of config 3, forward + losses + autograd backward "
                                                     "(no optimizer), best of 2 after 1 warm-up (%.2f s each), fp32 torch CPU" % best}
-        del fm
+        del fm, fb
+
+        # config 3 with the audio encoder it names: ft_sizes=[2048, 128], three AudioEncoderLayer blocks over Ta=40 VGGish-like
+        # frames, a fourth gate column and the audio auto-encoder head (encoder.py:83-91,220-235; decoder.py:154,167)
+        am, alc = full_model(args.precision, audio=True)
+        am = am.to(dev).train()
+        ab = full_batch(1 + rank, dev, audio=True)
+
+        def audio_loss():
+            return alc.loss(am(ab), ab)[0]
+
+        train_full_audio = measure_train(am, audio_loss, [],
+                                         "train_full plus the audio stream of BASELINE config 3: audio features [B, Ta=40, 128] "
+                                         "through VidEncoder8.a_W + a_in_norm, 3 AudioEncoderLayer blocks, audio column of the "
+                                         "softmax gate, audio auto-encoder head; same step otherwise")
+        train_full_audio["metric"] = "bist_train_turns_per_sec"
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            v, best = cpu_oracle_train_turns_per_sec(am, 8, 1, threads)
+            train_full_audio["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                                "sample": "8 dialogue turns, forward + losses + autograd backward (no optimizer), "
+                                                          "1 pass after 1 warm-up (%.2f s), fp32 torch CPU" % best}
+        del am, ab
 
     # ---- beam-search decode at BASELINE config 5 (long video: S=49, T=128; beam 5, max_len 12), B=8 turns per GPU ---
     decode = None
@@ -563,7 +587,7 @@ def run_ours(args):
                 "roofline": roof,
                 "encoder_algorithmic_gbs": whole, "encoder_frac_of_hbm_peak": whole / peaks["hbm"],
                 "kernels": kern, "kernel_rooflines": per_kernel,
-                "train": train, "train_full": train_full, "decode": decode,
+                "train": train, "train_full": train_full, "train_full_audio": train_full_audio, "decode": decode,
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -69,8 +69,11 @@ def make_model(src_vocab, tgt_vocab, args, ft_sizes=None, embeddings=None, preci
     "mtn.py:63-167."
     if not args.ptr_gen:
         raise NotImplementedError("ptr_gen=0 raises NameError in the reference (mtn.py:95); only ptr_gen=1 is built")
-    if len(ft_sizes or []) != 1:
-        raise NotImplementedError("ft_sizes must hold the video feature size only (the audio projection is not built)")
+    ft_sizes = list(ft_sizes or [])
+    if len(ft_sizes) not in (1, 2):
+        raise NotImplementedError("ft_sizes = [video feature size] or [video, audio feature size] (mtn.py:110-115)")
+    if getattr(args, "nb_aenc_blocks", 0) > 0 and len(ft_sizes) != 2:
+        raise ValueError("nb_aenc_blocks > 0 needs the audio feature size: ft_sizes=[2048, 128] (mtn.py:112-113)")
     d_model, dropout = args.d_model, args.dropout
     position = PositionalEncoding(d_model, dropout)
     query_embed = EmbedSequence(Embeddings(d_model, src_vocab), copy.deepcopy(position))
@@ -83,8 +86,9 @@ def make_model(src_vocab, tgt_vocab, args, ft_sizes=None, embeddings=None, preci
         generator = PointerGenerator(d_model, tgt_embed[0].lut.weight, MultiHeadedAttention(1, d_model, dropout=0))
     ae_generator = Generator(d_model, tgt_vocab, tgt_embed[0].lut.weight) if args.auto_encoder else None
     text_encoder = Encoder(d_model, nb_layers=3)
-    vid_encoder = VidEncoder8(nn.Linear(ft_sizes[0], d_model), None, None, args.nb_venc_blocks, args.nb_aenc_blocks,
-                              d_model, args)
+    a_W = nn.Linear(ft_sizes[1], d_model) if len(ft_sizes) > 1 else None          # mtn.py:112-115
+    vid_encoder = VidEncoder8(nn.Linear(ft_sizes[0], d_model), a_W, None, args.nb_venc_blocks,
+                              getattr(args, "nb_aenc_blocks", 0), d_model, args)
     model = MTN(text_encoder, vid_encoder, None, make_decoder(args, precision), query_embed, None, None, tgt_embed,
                 generator, ae_generator, args.ptr_gen, args)
     for p in model.parameters():                       # mtn.py:163-165

@@ -198,10 +198,12 @@ def _tokens(rs, B, L, vocab, unk_rate=0.0):
     return torch.from_numpy(ids)
 
 
-def make_full_batch(seed, B, T, S, D, Lq, Lh, Lc, Lt, vocab):
+def make_full_batch(seed, B, T, S, D, Lq, Lh, Lc, Lt, vocab, Ta=0, Da=0):
     """Seeded batch with every field MTN.forward and SimpleLossCompute read (data/dataset.py:59-104): token ids of the
     query / history / caption / shifted target (pad id 1 on the tails, a few <unk>=0 in the sources), their masks,
-    trg_mask = pad & causal, ntokens / qntokens, and the video features of make_batch."""
+    trg_mask = pad & causal, ntokens / qntokens, and the video features of make_batch.  With ``Ta, Da > 0`` the batch
+    also carries the audio stream of data/dataset.py:83-87: ``audio_fts`` [B,Ta,Da] (VGGish-like, non-negative, zero
+    rows past each sample's length) and ``audio_mask`` = (audio_fts.sum(-1) != 0) [B,1,Ta]."""
     vb = make_batch(seed, B, T, S, D, Lq)
     rs = np.random.RandomState(seed + 7919)
     b = SynthBatch()
@@ -212,6 +214,14 @@ def make_full_batch(seed, B, T, S, D, Lq, Lh, Lc, Lt, vocab):
     b.query_mask, b.his_mask, b.cap_mask = ((t != PAD_ID).unsqueeze(-2) for t in (b.query, b.his, b.cap))
     b.trg_mask = (b.trg != PAD_ID).unsqueeze(-2) & torch.tril(torch.ones(Lt, Lt, dtype=torch.bool)).unsqueeze(0)
     b.ntokens, b.qntokens = (b.trg_y != PAD_ID).sum(), (b.query != PAD_ID).sum()
+    if Ta > 0 and Da > 0:
+        ra = np.random.RandomState(seed + 104729)
+        aud = ra.uniform(0.05, 1.0, size=(B, Ta, Da)).astype(np.float32)
+        n = ra.randint(int(math.ceil(Ta / 2)), Ta + 1, size=B)
+        n[0] = Ta
+        aud[np.arange(Ta)[None, :] >= n[:, None]] = 0.0
+        b.audio_fts = torch.from_numpy(aud)
+        b.audio_mask = (b.audio_fts.sum(-1) != 0).unsqueeze(-2)
     return b
 
 

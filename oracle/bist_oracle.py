@@ -425,7 +425,10 @@ def mtn_encode(P, b, drop=None):
     eq, ec, eh = (embed(P, "query_embed.", ids, drop, f"query_embed.{n}") for n, ids in (("query", b.query), ("cap", b.cap), ("his", b.his)))
     for i, (key, x) in enumerate((("encoded_query", eq), ("encoded_cap", ec), ("encoded_his", eh))):   # encoder.py:19-40
         ft[key] = layer_norm(x, P[f"text_encoder.norm.{i}.a_2"], P[f"text_encoder.norm.{i}.b_2"])
-    ft["spatiotemporal_ft"], _ = vid_encoder8(P, "vid_encoder.", b.fts)
+    audio = getattr(b, "audio_fts", None) if "vid_encoder.a_W.weight" in P else None      # a_N > 0, encoder.py:83
+    ft["spatiotemporal_ft"], enc_audio = vid_encoder8(P, "vid_encoder.", b.fts, audio)
+    if enc_audio is not None:
+        ft["encoded_audio"] = enc_audio
     return ft
 
 

@@ -204,16 +204,32 @@ MODEL_CASES = {
                         vc="none", cap="none", ptr_ft="query", ae=1, t2s=1, s2t=1),
     "his_ptr_noae": dict(seed=43, B=2, T=3, S=4, D=32, d=32, h=4, Lq=5, Lh=8, Lc=4, Lt=6, V=64, n_blocks=1, nb_cenc=1,
                          vc="sum", cap="summary", ptr_ft="his,query", ae=0, t2s=1, s2t=1),
+    # BASELINE config 3 names the audio encoder: ft_sizes=[D, Da] builds VidEncoder8.a_W / a_in_norm (mtn.py:112-113,
+    # encoder.py:83-91, with args.noW_venc=0 injected), AudioEncoderLayer blocks, a fourth gate column
+    # (decoder.py:154,167) and the audio auto-encoder head (optimize.py:61-65)
+    "avsd_audio":  dict(seed=44, B=3, T=4, S=3, D=40, d=64, h=4, Lq=6, Lh=8, Lc=7, Lt=5, V=83, n_blocks=2, nb_cenc=2,
+                        nb_aenc=2, Ta=6, Da=12, vc="dyn", cap="summary", ptr_ft="query,cap", ae=1, t2s=1, s2t=1),
+    "audio_seq":   dict(seed=45, B=2, T=3, S=4, D=32, d=32, h=2, Lq=5, Lh=6, Lc=4, Lt=4, V=50, n_blocks=1, nb_cenc=0,
+                        nb_aenc=1, Ta=5, Da=10, vc="none", cap="none", ptr_ft="query", ae=1, t2s=1, s2t=1),
 }
 PAD, SMOOTHING = 1, 0.1          # train.py:93 (vocab['<blank>'] is the collate pad id, data/dataset.py)
 
 
 def model_args(c):
     return argparse.Namespace(
-        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=0,
+        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=c.get("nb_aenc", 0),
         d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft=c["ptr_ft"], auto_encoder=c["ae"],
         t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none", enc_vc_combine=c["vc"],
-        dec_st_combine="seq", include_caption=c["cap"], mask_unk=1)
+        dec_st_combine="seq", include_caption=c["cap"], mask_unk=1, noW_venc=0)
+
+
+def model_ft_sizes(c):
+    return [c["D"]] + ([c["Da"]] if c.get("nb_aenc", 0) > 0 else [])
+
+
+def model_batch(c):
+    return synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"],
+                                 Ta=c.get("Ta", 0), Da=c.get("Da", 0))
 
 
 TIED = ("tgt_embed.0.lut.weight", "generator.vocab_gen", "ae_generator.proj")
@@ -235,10 +251,10 @@ def run_model_case(mtn, c):
     torch.Tensor.cuda = lambda self, *a, **k: self        # generator.py:66,113 hard-code .cuda() (harness shim, §8(c))
     torch.manual_seed(0)
     args = model_args(c)
-    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=[c["D"]]).eval()
+    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=model_ft_sizes(c)).eval()
     shapes = {k: tuple(v.shape) for k, v in model.state_dict().items()}
     model.load_state_dict(model_params(shapes, c["seed"]), strict=False)
-    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    b = model_batch(c)
     crit = ls.LabelSmoothing(size=c["V"], padding_idx=PAD, smoothing=SMOOTHING)
     with torch.no_grad():
         ft = model.forward(b)
@@ -248,10 +264,13 @@ def run_model_case(mtn, c):
         # total normalised loss exactly as optimize.py:48-82 sums it
         total = crit(logp.contiguous().view(-1, c["V"]), b.trg_y.contiguous().view(-1)) / b.ntokens.float()
         if c["ae"]:
-            for k in (["cap_ft"] if c["nb_cenc"] > 0 else []) + ["temporal_ft", "spatial_ft"]:
+            for k in (["cap_ft"] if c["nb_cenc"] > 0 else []) + (["audio_ft"] if c.get("nb_aenc", 0) > 0 else []) + ["temporal_ft", "spatial_ft"]:
                 ae = model.ae_generator(ft, b, args, k)
                 total = total + crit(ae.contiguous().view(-1, c["V"]), b.query.contiguous().view(-1)) / b.qntokens.float()
     out = {k: ft[k].numpy().copy() for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text")}
+    for k in ("encoded_audio", "audio_ft"):
+        if k in ft:
+            out[k] = ft[k].numpy().copy()
     out["logp"] = logp.numpy().copy()
     out["loss_out_sum"] = np.array(float(losses["out"]))
     out["loss_total"] = np.array(float(total))
@@ -269,10 +288,10 @@ def run_beam_case(mtn, c):
     torch.Tensor.cuda = lambda self, *a, **k: self
     torch.manual_seed(0)
     args = model_args(c)
-    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=[c["D"]]).eval()
+    model = mtn.make_model(c["V"], c["V"], args, ft_sizes=model_ft_sizes(c)).eval()
     shapes = {k: tuple(v.shape) for k, v in model.state_dict().items()}
     model.load_state_dict(model_params(shapes, c["seed"]), strict=False)
-    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
+    b = model_batch(c)
     out = {}
     g = BEAM
     with torch.no_grad():
@@ -294,6 +313,16 @@ def main():
     mtn, modules = import_reference()
     gold = os.path.join(ROOT, "tests", "golden")
     os.makedirs(gold, exist_ok=True)
+    only = set(sys.argv[1:])      # e.g. `make_golden.py model_avsd_audio`: (re)generate the named model fixtures only
+    if only:
+        for name, c in MODEL_CASES.items():
+            if f"model_{name}" in only:
+                out = run_model_case(mtn, c)
+                out["meta"] = np.array(json.dumps(c))
+                path = os.path.join(gold, f"model_{name}.npz")
+                np.savez_compressed(path, **out)
+                print(f"{path}: {os.path.getsize(path) / 1024:.1f} KiB  loss_total={float(out['loss_total']):.6f}")
+        return
     for name, c in CASES.items():
         out = run_reference_case(mtn, c)
         out["meta"] = np.array(json.dumps(c))

@@ -26,14 +26,14 @@ GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "model
 
 def _args(c):
     return argparse.Namespace(
-        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=0,
-        d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft=c["ptr_ft"], auto_encoder=c["ae"],
+        nb_blocks=c["n_blocks"], nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"],
+        nb_aenc_blocks=c.get("nb_aenc", 0), noW_venc=0, d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, ptr_ft=c["ptr_ft"], auto_encoder=c["ae"],
         t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none", enc_vc_combine=c["vc"],
         dec_st_combine="seq", include_caption=c["cap"], mask_unk=1)
 
 
 def _build(c, P, shapes, precision):
-    m = make_model(c["V"], c["V"], _args(c), ft_sizes=[c["D"]], precision=precision)
+    m = make_model(c["V"], c["V"], _args(c), ft_sizes=[c["D"]] + ([c["Da"]] if c.get("nb_aenc", 0) else []), precision=precision)
     sd = m.state_dict()
     assert sorted(sd) == sorted(shapes), set(sd) ^ set(shapes)             # the reference's keys, buffers included
     assert all(tuple(sd[k].shape) == tuple(shapes[k]) for k in shapes)
@@ -56,7 +56,9 @@ def test_model_forward_logits_and_loss_match_reference(path, precision):
     torch.cuda.synchronize()
     assert _lib.lib().bist_launch_count() > n0
     tol = 1e-4 if precision == "fp32" else 2e-2
-    for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text"):
+    for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text", "encoded_audio", "audio_ft"):
+        if k not in gold:
+            continue
         assert O.norm_err(ft[k].float().cpu(), gold[k]) < tol, (k, O.norm_err(ft[k].float().cpu(), gold[k]))
     assert O.norm_err(logp.cpu(), gold["logp"]) < tol, O.norm_err(logp.cpu(), gold["logp"])
     assert abs(float(total) - float(gold["loss_total"])) < tol * abs(float(gold["loss_total"]))

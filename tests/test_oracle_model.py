@@ -26,8 +26,9 @@ def load_model_case(path):
     for k in TIED:
         if k in P:
             P[k] = P["query_embed.0.lut.weight"]
-    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"])
-    args = dict(nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=0, enc_vc_combine=c["vc"],
+    b = synth.make_full_batch(c["seed"], c["B"], c["T"], c["S"], c["D"], c["Lq"], c["Lh"], c["Lc"], c["Lt"], c["V"],
+                              Ta=c.get("Ta", 0), Da=c.get("Da", 0))
+    args = dict(nb_venc_blocks=c["n_blocks"], nb_cenc_blocks=c["nb_cenc"], nb_aenc_blocks=c.get("nb_aenc", 0), enc_vc_combine=c["vc"],
                 include_caption=c["cap"], dec_st_combine="seq", t2s=c["t2s"], s2t=c["s2t"], enc_st_combine="none",
                 ptr_ft=c["ptr_ft"], auto_encoder=c["ae"], mask_unk=1)
     gold = {k: torch.from_numpy(z[k]) for k in z.files if k not in ("meta", "param_shapes")}
@@ -35,15 +36,17 @@ def load_model_case(path):
 
 
 def test_fixtures_present():
-    assert len(GOLD) >= 3
+    assert len(GOLD) >= 5
+    assert sum("audio" in os.path.basename(p) for p in GOLD) >= 2        # config 3's audio encoder is pinned too
 
 
 @pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-4])
 def test_oracle_model_matches_reference(path):
     c, args, P, shapes, b, gold = load_model_case(path)
     ft = O.mtn_forward(P, args, b, c["h"], c["n_blocks"])
-    for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text"):
-        assert O.norm_err(ft[k], gold[k]) < 2e-6, (k, O.norm_err(ft[k], gold[k]))
+    for k in ("encoded_query", "encoded_his", "encoded_cap", "encoded_tgt", "decoded_text", "encoded_audio", "audio_ft"):
+        if k in gold:
+            assert O.norm_err(ft[k], gold[k]) < 2e-6, (k, O.norm_err(ft[k], gold[k]))
     logp = O.generator_logp(P, "generator.", ft, b, c["ptr_ft"], 1)
     assert O.norm_err(logp, gold["logp"]) < 5e-6
     total, parts = O.loss_compute(P, args, ft, b, PAD, SMOOTHING)
