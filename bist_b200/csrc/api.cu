@@ -59,6 +59,10 @@ bool overlap_enabled() {   // off while per-launch timing is on: a kernel timed 
   static const bool on = getenv("BIST_NO_OVERLAP") == nullptr;
   return on && !g_prof_on.load(std::memory_order_relaxed);
 }
+bool dir_overlap_enabled() {
+  static const bool on = [] { const char* v = getenv("BIST_DIR_OVERLAP"); return v ? atoi(v) != 0 : true; }();
+  return on && overlap_enabled();
+}
 int side_stream(SideStream** out) {
   static thread_local std::map<int, SideStream> tab;
   int dev = 0;
@@ -69,6 +73,8 @@ int side_stream(SideStream** out) {
     BIST_CUDA(cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking));
     BIST_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
     BIST_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+    BIST_CUDA(cudaEventCreateWithFlags(&ss.fork2, cudaEventDisableTiming));
+    BIST_CUDA(cudaEventCreateWithFlags(&ss.join2, cudaEventDisableTiming));
     it = tab.emplace(dev, ss).first;
   }
   *out = &it->second;

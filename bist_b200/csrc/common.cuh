@@ -231,7 +231,8 @@ struct GemmArgs {
 // entry point: work that does not depend on the call's serial chain is launched there between an event recorded on the
 // caller's stream and an event the caller's stream waits for before the call returns.  Capturable (the side stream joins
 // the caller's capture through the fork event).  BIST_NO_OVERLAP=1 disables it.
-struct SideStream { cudaStream_t s; cudaEvent_t fork, join; };
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join, fork2, join2; };
+bool dir_overlap_enabled();  // second direction's stage-1/stage-2 kernels on the side stream (BIST_DIR_OVERLAP)
 int side_stream(SideStream** out);
 bool overlap_enabled();
 

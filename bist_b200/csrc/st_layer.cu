@@ -61,7 +61,7 @@ PackedLayout packed_layout(int64_t d, int64_t dff, int n_dirs, int dtype) {
 struct Workspace {
   // `act` buffers are GEMM operands (bf16 in bf16 mode), the rest fp32
   void *nbuf, *qkv0, *cbuf, *n12x, *q12x, *qf12, *u2, *ffh;  // act dtype
-  float *sc0, *x, *ts, *sc1, *qf2f;                           // fp32
+  float *sc0, *x, *ts, *sc1, *sc1b, *qf2f;                    // fp32
   void* xv;
   void* ctx1[2];
   size_t bytes;
@@ -87,7 +87,8 @@ Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   W.n12x = a(3 * nd * Q * d); W.q12x = a(3 * nd * Q * d); W.qf12 = a(2 * nd * Q * h * d); W.u2 = a(nd * Q * h * d);
   W.ffh = a(nd * Q * dff);
   W.sc0 = f(nd * Q * h * Lq); W.x = f(nd * Q * d); W.ts = f(nd * Q * d);
-  W.sc1 = f(Q * h * T * S);  // one direction at a time
+  W.sc1 = f(Q * h * T * S);  // one direction at a time ...
+  W.sc1b = nd == 2 ? f(Q * h * T * S) : nullptr;  // ... or the second direction's, when it runs beside the first
   W.qf2f = (dtype == BIST_BF16 && !use_stage2_mma(dtype, T, S, h, d, nd, kinds)) ? f(nd * Q * h * d) : nullptr;
   W.xv = A.take((size_t)B * T * S * nd * d * e);
   for (int u = 0; u < 2; ++u) W.ctx1[u] = nullptr;
@@ -365,8 +366,21 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
 
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
   if (!xv_forked) BIST_TRY(launch_xv(st));
+  // The two directions are independent from here to the stage-2 outputs: the second one's three kernels can run on the
+  // side stream (behind the value GEMM it needs anyway) beside the first one's, with its own score buffer.
+  const bool dir_ovl = xv_forked && nd == 2 && dir_overlap_enabled();
+  if (dir_ovl) {
+    BIST_CUDA(cudaEventRecord(side->fork2, st));  // the folded queries are ready
+    BIST_CUDA(cudaStreamWaitEvent(side->s, side->fork2, 0));
+  }
+  auto stream_of = [&](int u) { return dir_ovl && u == 1 ? side->s : st; };
+  auto join_dirs = [&]() {
+    if (dir_ovl) { cudaEventRecord(side->join2, side->s); cudaStreamWaitEvent(st, side->join2, 0); }
+  };
   for (int u = 0; u < nd; ++u) {
     const bool t2s = kinds[u] == 0;
+    cudaStream_t su = stream_of(u);
+    float* sc1 = dir_ovl && u == 1 ? W.sc1b : W.sc1;
     const int G = (int)(t2s ? S : T), nk = (int)(t2s ? T : S);
     bool t2s_regions = false;
     {
@@ -374,7 +388,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       //   t2s: one product per (b,s): [Lq*h, d] x [T rows at stride S*d]^T -> sc[b,s,(l,hh),t]
       //   s2t: one product per b:     [Lq*h, d] x [T*S rows]^T            -> sc[b,(l,hh),(t,s)]
       GemmArgs g;
-      g.A = act(W.qf12, (long long)u * Qd * h); g.W = vft; g.C = W.sc1;
+      g.A = act(W.qf12, (long long)u * Qd * h); g.W = vft; g.C = sc1;
       g.M = (int)(Lq * h); g.K = di;
       g.a = rows_dense(d);
       g.a_dtype = adt; g.w_dtype = dtype; g.tag = "scores1_gemm";
@@ -387,7 +401,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
           r.N = (int)TS; r.w = rows_dense(d); r.c = rows_dense(TS); r.wr_T = (int)T; r.wr_S = (int)S;
           r.Z = (int)B; r.zin = 1;
           r.az = {Lq * h * d, 0}; r.wz = {TS * d, 0}; r.cz = {Lq * h * TS, 0};
-          BIST_TRY(gemm_tc(r, st, &done));
+          { const int rc = gemm_tc(r, su, &done); if (rc != 0) { join_dirs(); return rc; } }
           t2s_regions = done;
         }
         g.N = (int)T; g.w = rows_dense(S * d); g.c = rows_dense(T);
@@ -398,10 +412,10 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
         g.Z = (int)B; g.zin = 1;
         g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
       }
-      if (!done) BIST_TRY(gemm(g, st));
+      if (!done) { const int rc = gemm(g, su); if (rc != 0) { join_dirs(); return rc; } }
     }
     SoftmaxPvArgs a;
-    a.S = W.sc1;
+    a.S = sc1;
     if (t2s) {  // group (b,s): keys are its T clips (encoder.py:117-121: temporal mask on the keys)
       if (t2s_regions) { a.sg = rows_2level((int)S, Lq * h * TS, T); a.s_l = h * TS; a.s_h = TS; a.s_k = 1; }
       else { a.sg = rows_dense(Lq * h * T); a.s_l = h * T; a.s_h = T; a.s_k = 1; }
@@ -416,11 +430,11 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     a.og = rows_2level(G, Lq * G * d, d); a.o_l = (long long)G * d;
     a.G = (int)(B * G); a.Lq = (int)Lq; a.h = hi; a.dk = dk; a.nk = nk;
     a.v_dtype = dtype; a.ctx_dtype = dtype;
-    if (xv_forked && !xv_joined) {
+    if (xv_forked && !xv_joined && su == st) {  // (the side stream is ordered behind the value GEMM by itself)
       BIST_CUDA(cudaStreamWaitEvent(st, side->join, 0));
       xv_joined = true;
     }
-    BIST_TRY(softmax_pv(a, st));
+    { const int rc = softmax_pv(a, su); if (rc != 0) { join_dirs(); return rc; } }
   }
   if (xv_forked && !xv_joined) BIST_CUDA(cudaStreamWaitEvent(st, side->join, 0));
 
@@ -431,13 +445,19 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     const uint8_t* m2 = t2s ? nullptr : temporal_mask;  // :130 no mask / :157-161 temporal mask
     if (s2mma) {
       bool taken = false;
-      BIST_TRY(stage2_mma(act(W.qf12, (nd + u) * Qd * h), W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, st, &taken));
+      const int rc = stage2_mma(act(W.qf12, (nd + u) * Qd * h), W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di,
+                                stream_of(u), &taken);
+      if (rc != 0 || !taken) join_dirs();
+      BIST_TRY(rc);
       BIST_CHECK_ARG(taken, "st_layer: stage2_mma declined a shape it reported as supported");
     } else {
       const float* qf = dtype == BIST_BF16 ? W.qf2f + u * Qd * h : (const float*)W.qf12 + (nd + u) * Qd * h;
-      BIST_TRY(stage2_attn(qf, W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, dtype, adt, st));
+      const int rc = stage2_attn(qf, W.ctx1[u], m2, act(W.u2, u * Qd * h), (int)B, G, (int)Lq, hi, di, dtype, adt, stream_of(u));
+      if (rc != 0) join_dirs();
+      BIST_TRY(rc);
     }
   }
+  join_dirs();
   {
     GemmArgs g;  // ctx2[q, hh*dk+j] = u2[q,hh,:] . (W_v2 W_o1)[hh*dk+j,:] + (x W_v2^T + b_v2 + W_v2 b_o1)[q, hh*dk+j]
     g.A = W.u2; g.W = Mw(L.wv2f); g.C = W.cbuf; g.R = act(W.q12x, 2 * nd * Qd);
