@@ -17,7 +17,23 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .modules import LayerNorm, SublayerConnection, clones, gate_combine, linear, _BF16Cache
+import os
+
+from .modules import LayerNorm, SublayerConnection, clones, gate_combine, linear, refresh_weight_copies, _BF16Cache
+
+_BRANCH = {}
+
+
+def _branch_streams_enabled():
+    return os.environ.get("BIST_BRANCH_STREAMS", "1") != "0"
+
+
+def _branch_streams(device):
+    """Two long-lived streams per device for the caption and audio layers of a block (``_block_memories``)."""
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    if key not in _BRANCH:
+        _BRANCH[key] = (torch.cuda.Stream(device=device), torch.cuda.Stream(device=device))
+    return _BRANCH[key]
 
 
 def _opt(args, name, default):
@@ -160,20 +176,51 @@ class MultimodalDecoder8(nn.Module):
 
     def _block_memories(self, count, in_ft, ft, b):
         """Block `count` of the query-conditioned encoders (decoder.py:115-167): video, caption and audio layers, their
-        output norms and the gate.  None of it depends on the target sequence."""
+        output norms and the gate.  None of it depends on the target sequence.
+
+        The three layers of a block read different streams of ``in_ft`` and never each other's outputs (they meet in the
+        gate), so on a CUDA device the caption and audio layers are enqueued on two branch streams beside the video layer
+        — their ~20 small launches each hide behind the video layer's large kernels, in eager mode and as parallel
+        branches of a captured CUDA graph alike (autograd runs each backward on its forward's stream).  The branches are
+        joined before the gate.  ``BIST_BRANCH_STREAMS=0`` keeps everything on the current stream."""
         args = self.args
+        eq = ft['encoded_query']
+        side = (self.v_N > 0 and (self.c_N > 0 or self.a_N > 0) and eq.is_cuda and _branch_streams_enabled())
+        if side:
+            main = torch.cuda.current_stream(eq.device)
+            s_cap, s_aud = _branch_streams(eq.device)
+            refresh_weight_copies(eq.device)        # on the main stream, before any branch reads the shared arena
+            made = []
+            if self.c_N > 0:
+                s_cap.wait_stream(main)
+                with torch.cuda.stream(s_cap):
+                    in_ft = self.c_layers[count](in_ft, ft, b)
+                    ft['cap_ft'] = self.cap_out_norm(in_ft['cap'])
+                made += [(s_cap, in_ft['cap']), (s_cap, ft['cap_ft'])]
+            if self.a_N > 0:
+                s_aud.wait_stream(main)
+                with torch.cuda.stream(s_aud):
+                    in_ft = self.a_layers[count](in_ft, ft, b)
+                    ft['audio_ft'] = self.a_out_norm(in_ft['audio'])
+                made += [(s_aud, in_ft['audio']), (s_aud, ft['audio_ft'])]
         if self.v_N > 0:
             in_ft = self.v_layers[count](in_ft, ft, b)
             if _opt(args, "s2t", 1):
                 ft['temporal_ft'] = self.temporal_out_norm(in_ft['s2t'])
             if _opt(args, "t2s", 1):
                 ft['spatial_ft'] = self.spatial_out_norm(in_ft['t2s'])
-        if self.c_N > 0:
-            in_ft = self.c_layers[count](in_ft, ft, b)
-            ft['cap_ft'] = self.cap_out_norm(in_ft['cap'])
-        if self.a_N > 0:
-            in_ft = self.a_layers[count](in_ft, ft, b)
-            ft['audio_ft'] = self.a_out_norm(in_ft['audio'])
+        if side:
+            for s in {id(st): st for st, _ in made}.values():
+                main.wait_stream(s)
+            for _, t in made:                       # allocated on a branch stream, read on the main one from here on
+                t.record_stream(main)
+        else:
+            if self.c_N > 0:
+                in_ft = self.c_layers[count](in_ft, ft, b)
+                ft['cap_ft'] = self.cap_out_norm(in_ft['cap'])
+            if self.a_N > 0:
+                in_ft = self.a_layers[count](in_ft, ft, b)
+                ft['audio_ft'] = self.a_out_norm(in_ft['audio'])
         if self.v_N > 0 and self.c_N > 0 and _opt(args, "enc_vc_combine", "none") in ('sum', 'dyn'):
             ft['encoded_ft'] = self._combine(ft)
         return in_ft

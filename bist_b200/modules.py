@@ -157,6 +157,23 @@ class _CopyArena:
 _ARENAS = {}
 
 
+def refresh_weight_copies(device):
+    """Bring the shared weight-copy arenas of `device` up to date on the CURRENT stream.  Callers that are about to run
+    modules on several streams do this first, so that no stream reads a slot another stream is still writing."""
+    for (dev, _dtype), arena in _ARENAS.items():
+        if dev != device or not arena.slots:
+            continue
+        stale = arena.refreshed_epoch != _WEIGHT_EPOCH[0]
+        if not stale:                                # a parameter changed in place without an optimizer step
+            for s in arena.slots.values():
+                p = s[0]()
+                if p is not None and s[5] is not None and s[4] != p._version:
+                    stale = True
+                    break
+        if stale:
+            arena.refresh()
+
+
 class _BF16Cache:
     """Copies of fp32 parameters in the compute dtype (bf16 copies; transposed copies for the backward GEMMs),
     refreshed when a parameter is updated in place.  Weight matrices on a CUDA device live in the shared ``_CopyArena``

@@ -99,3 +99,34 @@ def test_model_loss_gradients_match_oracle(path):
         assert O.norm_err(p.grad.cpu(), ref) < 1e-4, (name, O.norm_err(p.grad.cpu(), ref))
         checked += 1
     assert checked > 50
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_branch_streams_equal_single_stream(monkeypatch, precision):
+    """The caption / audio layers of a block run on branch streams beside the video layer (decoder.py
+    ``_block_memories``): outputs, loss and every gradient equal the single-stream run (same kernels, same operands;
+    only atomically accumulated gradients may differ in the last bits), eagerly and over repeated steps."""
+    path = [p for p in GOLD if p.endswith("model_avsd_audio.npz")][0]
+    c, args, P, shapes, b, gold = load_model_case(path)
+    bd = b.to(DEV)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("BIST_BRANCH_STREAMS", mode)
+        m = _build(c, P, shapes, precision).eval()
+        lc = SimpleLossCompute(m.generator, m.ae_generator, LabelSmoothing(c["V"], PAD, SMOOTHING), args=m.args)
+        for _ in range(3):                               # repeated steps: allocator reuse across the branch streams
+            for p in m.parameters():
+                p.grad = None
+            ft = m(bd)
+            total, _ = lc.loss(ft, bd)
+            total.backward()
+        torch.cuda.synchronize()
+        res[mode] = (ft["decoded_text"].float().cpu(), float(total), {n: p.grad.cpu() for n, p in m.named_parameters() if p.grad is not None})
+    assert torch.equal(res["0"][0], res["1"][0])
+    assert res["0"][1] == res["1"][1]
+    assert res["0"][2].keys() == res["1"][2].keys()
+    tol = 1e-5 if precision == "fp32" else 1e-3
+    for n, g0 in res["0"][2].items():
+        if n.endswith("linears.1.bias"):                 # zero up to rounding noise (softmax shift invariance)
+            continue
+        assert O.norm_err(res["1"][2][n], g0) <= tol, (n, O.norm_err(res["1"][2][n], g0))
