@@ -134,6 +134,9 @@ class _CopyArena:
         live = {k: s for k, s in self.slots.items() if s[0]() is not None}
         if len(live) != len(self.slots):
             self.slots, self.stale_layout = live, True
+        if not self.slots:
+            self.refreshed_epoch = _WEIGHT_EPOCH[0]
+            return
         if self.stale_layout or self.buf is None:
             off = 0
             for s in self.slots.values():
