@@ -37,6 +37,15 @@ def _decoder_stream(device):
     return _BRANCH[key]
 
 
+def _loss_streams(device, n):
+    """Streams for the auto-encoder heads of ``SimpleLossCompute.loss``."""
+    key = ("loss", torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
+    have = _BRANCH.setdefault(key, [])
+    while len(have) < n:
+        have.append(torch.cuda.Stream(device=device))
+    return have[:n]
+
+
 def _branch_streams(device):
     """Two long-lived streams per device for the caption and audio layers of a block (``_block_memories``)."""
     key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()

@@ -3,7 +3,8 @@
 auto-encoder heads on ``cap_ft`` / ``temporal_ft`` / ``spatial_ft`` (/ ``audio_ft``) against the query — goes through
 ``generator.loss_rows``: one fused kernel pass per vocabulary row that yields the label-smoothed KL and its gradient
 (bist_genloss_fwd_bwd), normalised by ``ntokens`` / ``qntokens`` on the device (no host synchronisation).
-"""
+ """
+import torch
 
 
 class NoamOpt:
@@ -52,12 +53,37 @@ class SimpleLossCompute:
         return keys
 
     def loss(self, ft, batch):
-        """(total normalised loss, {'out': ..., '<key>_ae': ...}) as device tensors (optimize.py:47-82)."""
+        """(total normalised loss, {'out': ..., '<key>_ae': ...}) as device tensors (optimize.py:47-82).
+
+        The auto-encoder heads and the generator loss are independent chains (vocabulary GEMM + fused loss kernel each,
+        pointer attentions for the generator): on a CUDA device each head is enqueued on its own branch stream beside
+        the generator's chain and joined before the sum (``BIST_BRANCH_STREAMS=0``: one stream)."""
+        from .decoder import _branch_streams_enabled, _loss_streams
+        from .modules import refresh_weight_copies
         pad, eps = self.criterion.padding_idx, self.criterion.smoothing
         norm, ae_norm = batch.ntokens.float(), batch.qntokens.float()
+        keys = self.ae_keys()
+        x = ft['decoded_text']
+        side = bool(keys) and x.is_cuda and _branch_streams_enabled()
+        heads = {}
+        if side:
+            main = torch.cuda.current_stream(x.device)
+            refresh_weight_copies(x.device)
+            streams = _loss_streams(x.device, len(keys))
+            for key, s in zip(keys, streams):
+                s.wait_stream(main)
+                with torch.cuda.stream(s):
+                    heads[key] = self.ae_generator.loss_rows(ft, batch, self.args, batch.query, pad, eps, key).sum() / ae_norm
+        else:
+            for key in keys:
+                heads[key] = self.ae_generator.loss_rows(ft, batch, self.args, batch.query, pad, eps, key).sum() / ae_norm
         parts = {'out': self.generator.loss_rows(ft, batch, self.args, batch.trg_y, pad, eps).sum() / norm}
-        for key in self.ae_keys():
-            parts[key + '_ae'] = self.ae_generator.loss_rows(ft, batch, self.args, batch.query, pad, eps, key).sum() / ae_norm
+        if side:
+            for key, s in zip(keys, streams):
+                main.wait_stream(s)
+                heads[key].record_stream(main)
+        for key in keys:
+            parts[key + '_ae'] = heads[key]
         total = parts['out']
         for key, v in parts.items():
             if key != 'out':
