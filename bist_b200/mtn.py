@@ -38,7 +38,24 @@ class MTN(nn.Module):
         return self.decode(b, self.encode(b))
 
     def encode(self, b):
-        return self.encode_vid(b, self.encode_text(b, {}))
+        """mtn.py:36-52.  The text side (three embedding lookups and norms: small kernels) is enqueued on a branch stream
+        beside the video projection (decoder.py has the rest of the model's stream branches); joined before the decoder."""
+        from .decoder import _branch_streams_enabled, _loss_streams
+        from .modules import refresh_weight_copies
+        if not (b.fts.is_cuda and _branch_streams_enabled()):
+            return self.encode_vid(b, self.encode_text(b, {}))
+        main = torch.cuda.current_stream(b.fts.device)
+        refresh_weight_copies(b.fts.device)
+        s = _loss_streams(b.fts.device, 1)[0]
+        s.wait_stream(main)
+        with torch.cuda.stream(s):
+            ft = self.encode_text(b, {})
+        made = list(ft.values())
+        ft = self.encode_vid(b, ft)
+        main.wait_stream(s)
+        for t in made:
+            t.record_stream(main)
+        return ft
 
     def encode_text(self, b, ft):
         ft['encoded_query'], ft['encoded_cap'], ft['encoded_his'] = self.text_encoder(

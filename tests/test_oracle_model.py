@@ -52,3 +52,25 @@ def test_oracle_model_matches_reference(path):
     total, parts = O.loss_compute(P, args, ft, b, PAD, SMOOTHING)
     assert abs(float(total) - float(gold["loss_total"])) < 2e-5 * abs(float(gold["loss_total"]))
     assert abs(float(parts["out"] * b.ntokens) - float(gold["loss_out_sum"])) < 2e-5 * abs(float(gold["loss_out_sum"]))
+
+
+@pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-4])
+def test_mirror_state_dict_matches_reference_keys(path):
+    """Host logic, no GPU: bist_b200.make_model builds the reference's state_dict keys and shapes for every golden
+    configuration (with ft_sizes=[D, Da] and the audio encoder where the case has one), so a reference checkpoint
+    loads strict=True; the synthetic audio stream follows data/dataset.py:83-87."""
+    import argparse
+    from bist_b200 import make_model
+    c, args, P, shapes, b, gold = load_model_case(path)
+    ns = argparse.Namespace(nb_blocks=c["n_blocks"], d_model=c["d"], att_h=c["h"], dropout=0.1, ptr_gen=1, **args)
+    m = make_model(c["V"], c["V"], ns, ft_sizes=[c["D"]] + ([c["Da"]] if c.get("nb_aenc", 0) else []))
+    sd = m.state_dict()
+    assert sorted(sd) == sorted(shapes)
+    assert all(tuple(sd[k].shape) == tuple(shapes[k]) for k in shapes)
+    if c.get("nb_aenc", 0):
+        assert "vid_encoder.a_W.weight" in sd and sd["vid_encoder.a_W.weight"].shape == (c["d"], c["Da"])
+        assert b.audio_fts.shape == (c["B"], c["Ta"], c["Da"])
+        assert torch.equal(b.audio_mask, (b.audio_fts.sum(-1) != 0).unsqueeze(-2))
+        assert bool(b.audio_mask[0].all()) and not bool(b.audio_mask.all())          # ragged, first sample full
+    else:
+        assert not any(k.startswith("vid_encoder.a_") for k in sd)
