@@ -453,12 +453,13 @@ def run_ours(args):
                     train_step()
                 per_step = (L.bist_launch_count() - n0) // 3
             else:
-                gstep = GraphedTrainStep(loss_fn, plist + extra_leaves, warmup=3)
+                in_graph = world > 1 and os.environ.get("BIST_GRAPH_ALLREDUCE", "0") == "1"
+                gstep = GraphedTrainStep(loss_fn, plist + extra_leaves, warmup=3, allreduce=in_graph)
                 per_step = (L.bist_launch_count() - n0) // 4   # 3 warm-up steps + the captured one
 
                 def train_step():
                     gstep()
-                    ncoll[0] = allreduce_grads(plist)
+                    ncoll[0] = gstep.collectives if in_graph else allreduce_grads(plist)
                     opt.step()
                 for _ in range(3):
                     train_step()

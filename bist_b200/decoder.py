@@ -26,7 +26,15 @@ _BRANCH = {}
 
 
 def _branch_streams_enabled():
-    return os.environ.get("BIST_BRANCH_STREAMS", "1") != "0"
+    on = os.environ.get("BIST_BRANCH_STREAMS", "1") != "0"
+    if on and not _BRANCH.get("quiet"):
+        # parameters shared by modules on different branches (the tied embedding, the text norms) accumulate gradients
+        # that arrive from several streams: intended here, autograd synchronises them
+        quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+        if quiet is not None:
+            quiet(False)
+        _BRANCH["quiet"] = True
+    return on
 
 
 def _decoder_stream(device):

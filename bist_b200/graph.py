@@ -27,7 +27,22 @@ class GraphedTrainStep:
     AccumulateGrad nodes on the stream they were created on, which invalidates a capture.
     """
 
-    def __init__(self, loss_fn, params, warmup=3):
+    def __init__(self, loss_fn, params, warmup=3, allreduce=False):
+        """``allreduce=True`` (N > 1): the gradient all-reduce is captured too — each video layer's block starts its
+        NCCL all-reduce as soon as its backward is enqueued (``dist.overlap_grad_allreduce``), the rest follows the
+        backward as one grouped launch, all inside the graph; the caller then only runs the optimizer.
+        ``self.collectives`` is the number of NCCL launches per replay."""
+        from . import dist as _dist
+        self.collectives = 0
+
+        def backward(loss):
+            if not allreduce:
+                loss.backward()
+                return
+            with _dist.overlap_grad_allreduce():
+                loss.backward()
+            self.collectives = _dist.allreduce_grads(self.params)
+
         self.params = [p for p in params if p.requires_grad]
         dev = self.params[0].device
         _lib.require_cuda(self.params[0])
@@ -40,7 +55,7 @@ class GraphedTrainStep:
             for _ in range(max(1, warmup)):            # sets kernel attributes, warms the allocator
                 for p in self.params:
                     p.grad = None
-                loss_fn().backward()
+                backward(loss_fn())
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         for p in self.params:
@@ -50,7 +65,7 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph):
             self.counter.add_(1)
             self.loss = loss_fn()
-            self.loss.backward()
+            backward(self.loss)
         weights_updated()                              # the copies made during capture are not valid eager caches
 
     def __call__(self):
