@@ -24,7 +24,9 @@ for precision in ("fp32", "bf16"):
     del loss
     for p in m.parameters():
         p.grad = None
+    print(f"[rank {rank}] {precision}: eager mean gradients done, capturing", flush=True)
     step = GraphedTrainStep(lambda: lc.loss(m(b), b)[0], list(m.parameters()), warmup=2, allreduce=True)
+    print(f"[rank {rank}] {precision}: captured, {step.collectives} collectives", flush=True)
     worst = 0.0
     for _ in range(3):
         step()
@@ -32,6 +34,9 @@ for precision in ("fp32", "bf16"):
         for p, s in zip(params, mean_g):
             worst = max(worst, float((p.grad - s).abs().max() / s.abs().max().clamp_min(1e-20)))
     step.close()
+    del step                                               # graphs holding NCCL kernels must go before the process group
+    print(f"[rank {rank}] {precision}: worst {worst:.3e}", flush=True)
     if rank == 0:
         print(precision, "collectives per replay", step.collectives, "params", len(params), "worst rel err vs mean of ranks", worst)
-dist.destroy_process_group()
+import gc; gc.collect(); torch.cuda.synchronize()
+os._exit(0)                                                # destroy_process_group() after NCCL graph capture hangs at exit
