@@ -108,6 +108,9 @@ SIGNATURES = {
     "bist_genloss_fwd_bwd": (c_i, [c_p, c_p, c_i, ctypes.POINTER(c_p), ctypes.POINTER(c_p), ctypes.POINTER(c_p),
                                    ctypes.POINTER(c_i64), c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i64, c_f, c_i, c_i, c_p]),
     "bist_gate_combine_fwd": (c_i, [ctypes.POINTER(c_p), c_p, c_p, c_i64, c_i64, c_i, c_i, c_p]),
+    "bist_stage1_fused_supported": (c_i, [c_i64] * 6),
+    "bist_stage1_fused": (c_i, [c_p, c_p, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_p), ctypes.POINTER(c_p),
+                                ctypes.POINTER(c_p), ctypes.POINTER(c_p)] + [c_i64] * 6 + [c_p, c_p]),
     "bist_gate_combine_bwd": (c_i, [c_p, ctypes.POINTER(c_p), c_p, ctypes.POINTER(c_p), c_p, c_i64, c_i64, c_i, c_i, c_p]),
 }
 

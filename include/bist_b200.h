@@ -365,6 +365,19 @@ int bist_genloss_fwd_bwd(void* Z, float* logp, int n_ptr, const float* const* P,
                          const int64_t* target, float* row_loss, int64_t R, int64_t V, int64_t Lt, int64_t pad,
                          float smoothing, int want_grad, int dtype, void* stream);
 
+/* Stage 1 of temporal2spatial / spatial2temporal for up to two directions as ONE launch (bf16; the video tensor is read
+ * once per launch, projected values and scores stay on chip) — encoder.py:109-121 (t2s) and :143-148 (s2t), attention()
+ * of modules.py:54-64.  bist_st_layer_fwd calls it when bist_stage1_fused_supported(); exported for the kernel-level tests.
+ *   vft [B,T,S,d] bf16; temporal_mask uint8 [B,T] (0 = padded clip; used by t2s);  per direction u < nd:
+ *   kinds[u]  0 = t2s (groups = S regions, keys = T clips, key mask), 1 = s2t (groups = T clips, keys = S regions)
+ *   qf[u]     bf16 [B*Lq, h, d]  folded queries (q_hh W_k,hh / sqrt(dk)), wv[u] bf16 [d,d] value weight (rows = outputs),
+ *   bv[u]     fp32 [d], c1[u] out bf16 [B, Lq, G, d] (G = S for t2s, T for s2t): sum_k softmax_k(qf.x_k) (W_v x_k + b_v)
+ *   kinds / qf / wv / bv / c1 are HOST arrays (of device pointers).  dbg: NULL, or fp32 [units, h, 128, 80] raw tiles. */
+int bist_stage1_fused_supported(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h);
+int bist_stage1_fused(const void* vft, const uint8_t* temporal_mask, int nd, const int* kinds, const void* const* qf,
+                      const void* const* wv, const float* const* bv, void* const* c1, int64_t B, int64_t T, int64_t S,
+                      int64_t Lq, int64_t d, int64_t h, float* dbg, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
