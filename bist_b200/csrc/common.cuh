@@ -298,6 +298,14 @@ int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx,
 int stage2_v2(const float* qf, const void* x1, const uint8_t* mask, void* ctxx, int B, int G, int Lq, int h, int d,
               int x1_dtype, int ctxx_dtype, cudaStream_t st, bool* taken);  // attn_mma.cu
 
+// ---- stage 1 of both directions as one kernel (stage1_fused.cu; bf16, d_k = 64, Lq <= 16, T, S <= 128) ----------------------
+// kinds[u]: 0 = t2s (groups = regions, keys = clips, temporal key mask), 1 = s2t.  qf[u] bf16 [B*Lq, h, d] folded queries,
+// wv[u] bf16 [d, d], bv[u] fp32 [d], c1[u] bf16 [B, Lq, G, d].  Host arrays of device pointers.
+bool stage1_fused_supported(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h);
+int stage1_fused(const void* vft, const uint8_t* tmask, int nd, const int* kinds, const void* const* qf, const void* const* wv,
+                 const float* const* bv, void* const* c1, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h,
+                 float* dbg, cudaStream_t st);
+
 // ---- weight packing helpers ------------------------------------------------------------------
 // dst[r, c] = scale * src[r, c] (transpose = 0) or scale * src[c, r] (transpose = 1); dst is
 // [rows, cols] dense of dst_dtype, src fp32 dense.

@@ -284,9 +284,12 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     if (s != st) g.max_ctas = xv_side_ctas();
     return gemm(g, s);
   };
+  // bf16 mode, d_k = 64, Lq <= 16, T and S <= 128: stage 1 of both directions is ONE kernel that reads the video tensor once
+  // and keeps projected values and scores on chip (stage1_fused.cu); otherwise the value GEMM + score GEMM + softmax.V chain.
+  const bool fused1 = dtype == BIST_BF16 && stage1_fused_supported(B, T, S, Lq, d, h);
   SideStream* side = nullptr;
   bool xv_forked = false, xv_joined = false;
-  if (overlap_enabled()) {
+  if (overlap_enabled() && !fused1) {
     BIST_TRY(side_stream(&side));
     BIST_CUDA(cudaEventRecord(side->fork, st));
     BIST_CUDA(cudaStreamWaitEvent(side->s, side->fork, 0));
@@ -365,10 +368,24 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   }
 
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
-  if (!xv_forked) BIST_TRY(launch_xv(st));
-  // The two directions are independent from here to the stage-2 outputs: the second one's three kernels can run on the
+  if (fused1) {
+    const void *qfp[2], *wvp[2];
+    const float* bvp[2];
+    void* c1p[2];
+    for (int u = 0; u < nd; ++u) {
+      qfp[u] = act(W.qf12, (long long)u * Qd * h);
+      wvp[u] = (const char*)packed + (L.wv1cat + (size_t)(pu0 + u) * d * d) * e;
+      bvp[u] = (const float*)((const char*)packed + L.f_byte_off) + L.bv1cat + (size_t)(pu0 + u) * d;
+      c1p[u] = W.ctx1[u];
+    }
+    BIST_TRY(stage1_fused(vft, temporal_mask, nd, kinds, qfp, wvp, bvp, c1p, B, T, S, Lq, d, h, nullptr, st));
+    if (overlap_enabled() && nd == 2 && dir_overlap_enabled()) BIST_TRY(side_stream(&side));
+  } else if (!xv_forked) {
+    BIST_TRY(launch_xv(st));
+  }
+  // The two directions are independent from here to the stage-2 outputs: the second one's kernels can run on the
   // side stream (behind the value GEMM it needs anyway) beside the first one's, with its own score buffer.
-  const bool dir_ovl = xv_forked && nd == 2 && dir_overlap_enabled();
+  const bool dir_ovl = (fused1 ? side != nullptr : xv_forked) && nd == 2 && dir_overlap_enabled();
   if (dir_ovl) {
     BIST_CUDA(cudaEventRecord(side->fork2, st));  // the folded queries are ready
     BIST_CUDA(cudaStreamWaitEvent(side->s, side->fork2, 0));
@@ -377,7 +394,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   auto join_dirs = [&]() {
     if (dir_ovl) { cudaEventRecord(side->join2, side->s); cudaStreamWaitEvent(st, side->join2, 0); }
   };
-  for (int u = 0; u < nd; ++u) {
+  for (int u = 0; u < nd && !fused1; ++u) {
     const bool t2s = kinds[u] == 0;
     cudaStream_t su = stream_of(u);
     float* sc1 = dir_ovl && u == 1 ? W.sc1b : W.sc1;

@@ -4,94 +4,119 @@
 //
 // Per (sample b, group g, head hh) the reference computes  softmax_k(q_hh . K_k / sqrt(dk)) . V_k  with K, V linear
 // projections of the group's video rows.  With the key projection folded into the query the video rows
-// x_k enter through ONE product against [W_v,hh ; qf_hh]:
-//     D[k, :] = x_k . [W_v,hh (64 rows) ; qf[b,:,hh,:] (Lq rows)]^T      (K = d)
-// whose first 64 columns are the head's projected values and whose last Lq columns are its folded scores.  Neither the
+// x_k enter through ONE product against [qf_hh ; W_v,hh]:
+//     D[k, :] = x_k . [qf[b,:,hh,:] (16 rows) ; W_v,hh (64 rows)]^T      (K = d)
+// whose first 16 columns are the head's folded scores and whose last 64 columns are its projected values.  Neither the
 // projected values [N, 2d] nor the scores [B*Lq*h, T*S] ever go to global memory.
 //
-// Layout of the machine: a cluster of h CTAs (one per head) works on one direction; all of them need the same video
-// rows, so every [128 keys x 64 k] slab is fetched from L2/HBM ONCE per cluster and multicast by TMA into the h shared
-// memories (each CTA issues 1/h of the pieces).  The head's W_v slice (64 x d bf16) stays resident in shared memory for
-// the whole kernel, the folded queries of the current sample sit beside it (double buffered), so one UMMA per 16 k
-// (M = 128 keys, N = 64 + 16) produces values and scores of a tile together, fp32 in tensor memory.
-// A tile is a run of whole groups (R groups x Kp8 keys <= 128 lanes): 8 clips x 16 regions for s2t, 3 regions x 40 clips
-// for t2s at config 2 — the t2s tile is gathered by the TMA unit itself from rows at stride S*d (box 1 x 8 of the
-// (d, S, T, B) view), so the softmax over T completes inside the tile like the softmax over S does.
-//
-// Warp roles (384 threads):
-//   warp 0      producer: W_v slice once, folded queries per sample, this CTA's share of the multicast video pieces
-//   warp 1      UMMA issuer: 4 x d/64 main UMMAs per tile into one of two TMEM accumulators, then the P.V UMMAs of
-//               the previous tile (A = staged values, MN-major; B = staged probabilities, K-major; N = 2 groups x 16)
-//   warp 2      TMEM allocation
-//   warps 4-7 / 8-11   two epilogue groups on alternating tiles: TMEM -> registers, values -> bf16 staging (UMMA
-//               MN-major SW128 layout), scores -> smem, masked softmax over the keys of each (group, query token)
-//               (modules.py:60-61), probabilities -> bf16 staging, wait for P.V, + b_v, bf16 stores of
-//               c1[b, l, g, hh*64 .. +64) (the layout stage 2 reads: the G summaries of one (b,l) contiguous).
+// The kernel is shaped like a GEMM with an attention epilogue; its shape follows three measurements on B200
+// (scripts/ubench.cu): an SM takes in at most ~59 bytes per clock through TMA whatever the ring depth, so every SM must
+// see its video rows ONCE; tcgen05.mma with M = 128 runs at 52 clocks for N = 80 (full rate from N = 128); and mma.sync
+// is starved (10 -> 180+ clocks per instruction) while a tcgen05 stream keeps the tensor pipe busy, so the small P.V
+// products are tcgen05 instructions too.
+//   * One CTA per SM owns a tile of 128 video rows of one sample — a run of whole groups: 8 clips x 16 regions for s2t,
+//     3 regions x 40 clips for t2s at config 2; the t2s tile is gathered by the TMA unit itself from rows at stride S*d
+//     (a box of the (d, S, T, B) view), so the softmax over T completes inside the tile like the softmax over S does.
+//     The tile stays RESIDENT in shared memory (A operand, d/64 k-slabs of 16 KB) for all heads.
+//   * [qf_hh ; W_v,hh] (80 rows) streams through a 4-slot ring as the B operand, one head per pass: 4 UMMAs (M = 128,
+//     N = 80, K = 16) per k-slab into one of two TMEM accumulators.
+//   * Two epilogue groups take alternate passes: TMEM -> registers; values -> bf16 tile in the UMMA MN-major SWIZZLE_128B
+//     layout, scores -> shared memory (transposed); masked softmax over the keys of each (group, query token)
+//     (modules.py:57-61; a team of threads per row, warp-shuffle max / sum); probabilities -> bf16 K-major core-matrix
+//     layout; the UMMA issuer then multiplies P.V for two groups per instruction (A = staged values of groups r, r+1 as the
+//     two 64-row atoms, B = their probabilities, N = 32: lanes 0-63 x columns 0-15 and lanes 64-127 x columns 16-31 are the
+//     two results); the group reads them back, adds b_v and assembles the [l][group][64] output tile in place of the dead
+//     staged values; ONE TMA store writes it into c1[b, l, g, hh*64 .. +64) — the layout stage 2 reads.
+// Warps: 0 video-tile producer, 1 UMMA issuer, 2 TMEM allocation + [qf ; W_v] producer, 4-7 / 8-11 epilogue groups.
 #include <stdlib.h>
 
 #include "tc_ptx.cuh"
 
 namespace bist {
+__device__ long long g_s1trace[6][256];   // optional timeline of CTA 0 (bist_debug_s1_trace): [role][event] clock64 stamps
 namespace {
 using namespace tc;
 
-constexpr int S1_STAGES = 4;                 // video slab ring
-constexpr int S1_XSLAB = 128 * 128;          // 128 keys x 64 k bf16
-constexpr int S1_LQP = 16;                   // folded-query rows per head (Lq <= 16)
-constexpr int S1_BROWS = 64 + 2 * S1_LQP;    // rows of the B operand per k slab: qf buffer 0 | W_v | qf buffer 1
-constexpr int S1_BSLAB = S1_BROWS * 128;
 constexpr int S1_MAXKS = 8;                  // d <= 512
-constexpr int S1_XV_ROWS = 160;              // staged value rows per epilogue group (max of R * Kp16)
-constexpr int S1_XV_BYTES = S1_XV_ROWS * 128;
-constexpr int S1_SC_BYTES = 128 * S1_LQP * 4;
-constexpr int S1_P_BYTES = S1_LQP * S1_XV_ROWS * 2;
-constexpr int S1_MAXR = 8;                   // groups per tile (TMEM columns of the P.V accumulator: 8 x 16)
+constexpr int S1_XSLAB = 128 * 128;          // 128 video rows x 64 k bf16 (SWIZZLE_128B)
+constexpr int S1_LQP = 16;                   // folded-query rows per head (Lq <= 16)
+constexpr int S1_BROWS = 2 * (S1_LQP + 64);  // B rows of a pass (two heads): 32 qf rows (l-major, head-minor) | 2 x 64 W_v rows
+constexpr int S1_BSLAB = S1_BROWS * 64;      // half-slab: 160 rows x 32 k bf16 (SWIZZLE_64B) = 10 KB
+constexpr int S1_BSTAGES = 5;
+constexpr int S1_XV_BYTES = 128 * 128;       // staged values of one head [row][64] bf16 (UMMA MN-major SWIZZLE_128B)
+constexpr int S1_SC_BYTES = 128 * S1_LQP * 4;   // scores [row][l] fp32 (chunk-swizzled); the bf16 probabilities take their place
+constexpr int S1_MAXR = 8;                   // groups per tile
 constexpr float kMaskFill = -1e9f;           // modules.py:60
 
-constexpr int OFF_B = 0;
-constexpr int OFF_X = OFF_B + S1_MAXKS * S1_BSLAB;          //  98304
-constexpr int OFF_XV = OFF_X + S1_STAGES * S1_XSLAB;        // 163840
-constexpr int OFF_P = OFF_XV + 2 * S1_XV_BYTES;             // 204800
-constexpr int OFF_SC = OFF_P + 2 * S1_P_BYTES;              // 215040
-constexpr int OFF_BAR = OFF_SC + 2 * S1_SC_BYTES;           // 231424
-constexpr int S1_NBAR = 2 * S1_STAGES + 13;
+constexpr int OFF_X = 0;
+constexpr int OFF_B = OFF_X + S1_MAXKS * S1_XSLAB;            // 131072
+constexpr int OFF_XV = OFF_B + S1_BSTAGES * S1_BSLAB;         // 182272
+constexpr int OFF_SC = OFF_XV + 2 * S1_XV_BYTES;              // 215040
+constexpr int OFF_MB = OFF_SC + 2 * S1_SC_BYTES;              // 231424: temporal-mask bits, 2 x 16 bytes
+constexpr int OFF_BAR = OFF_MB + 64;
+constexpr int S1_NBAR = 2 * S1_MAXKS + 2 * S1_BSTAGES + 9;
 constexpr int S1_SMEM = OFF_BAR + S1_NBAR * 8 + 16;
+static_assert(S1_SMEM <= 227 * 1024, "stage1_fused: shared memory budget");
+static_assert(OFF_B % 1024 == 0 && OFF_XV % 1024 == 0 && S1_BSLAB % 1024 == 0, "swizzled tiles must be 1024-byte aligned");
+constexpr uint32_t TM_ACC = 0, TM_ACC_STRIDE = S1_BROWS, TM_PV = 2 * S1_BROWS;   // TMEM columns: two accumulators, one P.V window (128)
+
+// float4 (query tokens 4*lq .. 4*lq+3) of tile row `row` in the score tile [row][16 l]: 64-byte rows, 16-byte chunks
+// XOR-swizzled by (row >> 1) & 3 (conflict-free row-wise writes, at most 2-way conflicts on column-wise reads)
+__device__ __forceinline__ int sc_f4(int row, int lq) { return row * 4 + (lq ^ ((row >> 1) & 3)); }
+
+#define S1FINE(k) do { if (p.trace && blockIdx.x == 0 && e == 0 && wt == 0 && pc < 25) g_s1trace[5][pc * 10 + (k)] = clock64(); } while (0)
+#define S1TRACE(role, idx) do { if (p.trace && blockIdx.x == 0 && (idx) < 256) g_s1trace[role][idx] = clock64(); } while (0)
 
 struct S1Dir {
   const float* bv;        // [d] value-projection bias
-  __nv_bfloat16* c1;      // [B, Lq, G, d]
   int G, Kn;              // groups per sample, keys per group
-  int Kp8, Kp16, R;       // keys padded to 8 (tile lanes) / 16 (staging, UMMA K); groups per tile
-  int tiles_per_b, units; // ceil(G / R); B * tiles_per_b
-  int use_mask;           // keys are clips: temporal_mask[b][k]
-  int cl_begin, cl_end;   // clusters [cl_begin, cl_end) work on this direction
+  int Kp8, Kp16, R;       // keys padded to 8 (tile rows) / 16 (UMMA K of P.V); groups per tile
+  int tpb, units;         // tiles per sample; B * tpb
+  int kclips;             // keys are clips (t2s): temporal_mask[b][k], tile rows are key-major (k * R + group)
+  int parts, kpp;         // softmax team: `parts` threads per (group, 4 query tokens), kpp keys each (key = part + j * parts)
 };
 struct S1Args {
   S1Dir dir[2];
   const uint8_t* tmask;   // [B, T]
-  float* dbg;             // optional [dir][unit][head][128][80] raw accumulator dump (tests)
-  int B, T, S, Lq, d, h, nks;
+  float* dbg;             // optional [unit][head][128][80] raw accumulator dump (tests)
+  int B, T, S, Lq, d, nh, nks, trace;
+  int total_units;
 };
 
-__device__ __forceinline__ void tma_load_4d_mc(uint32_t dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3,
-                                               uint16_t mask) {
+// ---- PTX -------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
   asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
-      ::"r"(dst), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(mask)
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
-__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return done != 0;
+}
+// sixteen 32-bit columns of 32 lanes; no wait (pair with tmem_ld_wait)
+__device__ __forceinline__ void tmem_ld16_nw(uint32_t taddr, uint32_t* r) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // MN-major SWIZZLE_128B: LBO = bytes between 64-element MN atoms, SBO = bytes between 8-row K groups (both >> 4)
 __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t addr, uint32_t lbo16, uint32_t sbo16) {
   return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)lbo16 << 16) | ((uint64_t)sbo16 << 32) | (1ull << 46) | (2ull << 61);
@@ -108,25 +133,31 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 __device__ __forceinline__ void st_shared_v4(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
-__device__ __forceinline__ float ld_shared_f32(uint32_t a) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
-  return v;
+// true in exactly one lane of a converged warp (the compiler keeps issue instructions under it on the uniform datapath)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-// scores of tile lane `row`, query token l: 16-byte chunks of the 64-byte row XOR-swizzled by (row >> 1) & 3
-__device__ __forceinline__ uint32_t sc_addr(uint32_t base, int row, int l) {
-  return base + (uint32_t)(row * (S1_LQP * 4) + ((((l >> 2) ^ (row >> 1)) & 3) << 4) + ((l & 3) << 2));
+// unit (tile) -> direction, sample, first group, valid groups
+struct Unit { int di, b, g0, rv; };
+__device__ __forceinline__ Unit decode_unit(const S1Args& p, int u) {
+  Unit x;
+  x.di = u >= p.dir[0].units ? 1 : 0;
+  const S1Dir& D = p.dir[x.di];
+  const int uu = u - (x.di ? p.dir[0].units : 0);
+  x.b = uu / D.tpb;
+  x.g0 = (uu - x.b * D.tpb) * D.R;
+  const int left = D.G - x.g0;
+  x.rv = left < D.R ? left : D.R;
+  return x;
 }
 
-struct Unit { int b, g0, rv; };
-__device__ __forceinline__ Unit decode_unit(const S1Dir& D, int u) {
-  Unit x;
-  x.b = u / D.tiles_per_b;
-  x.g0 = (u - x.b * D.tiles_per_b) * D.R;
-  x.rv = min(D.R, D.G - x.g0);
-  return x;
+// MN-major SWIZZLE_64B operand (32 bf16 of N per 64-byte row, K along the rows): SBO = bytes between 8-row K groups (>> 4)
+__device__ __forceinline__ uint64_t desc_mn_sw64(uint32_t addr, uint32_t sbo16) {
+  return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)sbo16 << 32) | (1ull << 46) | (4ull << 61);
 }
 
 __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_constant__ CUtensorMap map_x0,
@@ -134,274 +165,371 @@ __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_const
                                                               const __grid_constant__ CUtensorMap map_w0,
                                                               const __grid_constant__ CUtensorMap map_w1,
                                                               const __grid_constant__ CUtensorMap map_q0,
-                                                              const __grid_constant__ CUtensorMap map_q1, const S1Args p) {
+                                                              const __grid_constant__ CUtensorMap map_q1,
+                                                              const __grid_constant__ CUtensorMap map_c0,
+                                                              const __grid_constant__ CUtensorMap map_c1, const S1Args p) {
   pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = (uint64_t*)(smem + OFF_BAR);
-  uint64_t* full = bars;                       // [STAGES] video slab landed (TMA bytes from all producers of the cluster)
-  uint64_t* empty = full + S1_STAGES;          // [STAGES] slab consumed by the UMMAs of ALL CTAs (h multicast commits)
-  uint64_t* acc_full = empty + S1_STAGES;      // [2]
-  uint64_t* acc_empty = acc_full + 2;          // [2] 4 epilogue-warp arrivals
-  uint64_t* stg_full = acc_empty + 2;          // [2] staged values + probabilities of a tile are in shared memory
-  uint64_t* pv_full = stg_full + 2;            // [2]
-  uint64_t* qf_full = pv_full + 2;             // [2]
-  uint64_t* qf_empty = qf_full + 2;            // [2]
-  uint64_t* w_full = qf_empty + 2;             // [1]
-  uint32_t* tmem_slot = (uint32_t*)(w_full + 1);
+  uint64_t* xfull = bars;                       // [8]  k-slab of the video tile landed
+  uint64_t* xempty = xfull + S1_MAXKS;          // [8]  the last head pass has consumed the k-slab
+  uint64_t* bfull = xempty + S1_MAXKS;          // [5]  a [qf ; W_v] half-slab landed
+  uint64_t* bempty = bfull + S1_BSTAGES;        // [5]
+  uint64_t* acc_full = bempty + S1_BSTAGES;     // [2]
+  uint64_t* acc_empty = acc_full + 2;           // [2]  8 epilogue-warp arrivals
+  uint64_t* stg_full = acc_empty + 2;           // [2]  staged values + probabilities of a head are in shared memory
+  uint64_t* pv_full = stg_full + 2;             // [2]
+  uint64_t* pv_empty = pv_full + 2;             // [1]  the P.V window of TMEM has been read out (4 warp arrivals)
+  uint32_t* tmem_slot = (uint32_t*)(pv_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int h = p.h, nks = p.nks;
-  const int hh = (int)cluster_ctarank();       // this CTA's head
-  const int ci = (int)blockIdx.x / h;          // cluster index
-  const int di = (p.dir[0].cl_end > ci) ? 0 : 1;
-  const S1Dir& D = p.dir[di];
-  const CUtensorMap* map_x = di == 0 ? &map_x0 : &map_x1;
-  const CUtensorMap* map_w = di == 0 ? &map_w0 : &map_w1;
-  const CUtensorMap* map_q = di == 0 ? &map_q0 : &map_q1;
-  const int ncl = D.cl_end - D.cl_begin, lc = ci - D.cl_begin;
-  const int u_begin = (int)((long long)D.units * lc / ncl), u_end = (int)((long long)D.units * (lc + 1) / ncl);
-  const int n_units = u_end - u_begin;
-  const uint16_t mc_mask = (uint16_t)((1u << h) - 1u);
-  const int ppg = D.Kp8 >> 3;                  // 8-key pieces per group
-  const int npieces = D.R * ppg;               // per slab
+  const int u_begin = (int)((long long)p.total_units * blockIdx.x / gridDim.x);
+  const int u_end = (int)((long long)p.total_units * (blockIdx.x + 1) / gridDim.x);
+  const int nks = p.nks, nh = p.nh, npass = p.nh >> 1;   // k-slabs per tile, heads, passes (two heads each)
 
   if ((smem_u32(smem) & 1023u) != 0u) __trap();   // SWIZZLE_128B operands need 1024-byte aligned tiles
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < S1_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)h); }
+    for (int s = 0; s < S1_MAXKS; ++s) { mbar_init(&xfull[s], 1); mbar_init(&xempty[s], 1); }
+    for (int s = 0; s < S1_BSTAGES; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
     for (int a = 0; a < 2; ++a) {
-      mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4);
+      mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8);
       mbar_init(&stg_full[a], 1); mbar_init(&pv_full[a], 1);
-      mbar_init(&qf_full[a], 1); mbar_init(&qf_empty[a], 1);
     }
-    mbar_init(w_full, 1);
+    mbar_init(pv_empty, 4);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 512);
-  // staged-value rows that no tile lane maps to (keys Kp8..Kp16 of a group) must be finite zeros: P is zero there
-  for (int i = threadIdx.x; i < (2 * S1_XV_BYTES + 2 * S1_P_BYTES) / 16; i += blockDim.x)
+  // staged values: rows nobody writes (past the tile's keys; the last group's K padding reads up to 8 of them) must be finite
+  for (int i = threadIdx.x; i < (2 * S1_XV_BYTES + 2 * S1_SC_BYTES) / 16; i += blockDim.x)
     *reinterpret_cast<uint4*>(smem + OFF_XV + i * 16) = make_uint4(0u, 0u, 0u, 0u);
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();   // every CTA's barriers exist before a peer multicasts into it
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
 
   if (warp == 0) {
-    if (lane == 0 && n_units > 0) {
-      // ---- producer -------------------------------------------------------------------------------------------------
-      mbar_expect_tx(w_full, (uint32_t)(nks * 64 * 128));
-      for (int j = 0; j < nks; ++j) tma_load_2d(smem + OFF_B + j * S1_BSLAB + S1_LQP * 128, map_w, w_full, j * 64, hh * 64);
-      int it = 0, cur_b = -1, nsamp = 0;
-      for (int ui = 0; ui < n_units; ++ui) {
-        const Unit U = decode_unit(D, u_begin + ui);
-        if (U.b != cur_b) {
-          const int qb = nsamp & 1;
-          mbar_wait(&qf_empty[qb], ((nsamp >> 1) & 1) ^ 1);
-          mbar_expect_tx(&qf_full[qb], (uint32_t)(nks * S1_LQP * 128));
-          for (int j = 0; j < nks; ++j)
-            tma_load_3d(smem + OFF_B + j * S1_BSLAB + (qb ? (S1_LQP + 64) * 128 : 0), map_q, &qf_full[qb], j * 64, hh, U.b * p.Lq);
-          cur_b = U.b; ++nsamp;
+    // ---- video-tile producer (whole warp converged; the TMA issue sits under elect.sync) ----------------------------------
+    for (int u = u_begin, ui = 0; u < u_end; ++u, ++ui) {
+      const Unit U = decode_unit(p, u);
+      const S1Dir& D = p.dir[U.di];
+      const CUtensorMap* mx = U.di ? &map_x1 : &map_x0;
+      const uint32_t slab_bytes = (uint32_t)(D.R * D.Kp8 * 128);
+      for (int ks = 0; ks < nks; ++ks) {
+        mbar_wait(&xempty[ks], (ui & 1) ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(&xfull[ks], slab_bytes);
+          // one box = R groups x Kp8 keys x 64 k; out-of-range groups / keys are zero-filled
+          if (D.kclips) tma_load_4d(smem + OFF_X + ks * S1_XSLAB, mx, &xfull[ks], ks * 64, U.g0, 0, U.b);
+          else tma_load_4d(smem + OFF_X + ks * S1_XSLAB, mx, &xfull[ks], ks * 64, 0, U.g0, U.b);
+          S1TRACE(0, ui * nks + ks);
         }
-        for (int ks = 0; ks < nks; ++ks, ++it) {
-          const int s = it % S1_STAGES;
-          mbar_wait_cluster(&empty[s], ((it / S1_STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full[s], (uint32_t)(npieces * 1024));
-          const uint32_t dst = smem_u32(smem + OFF_X + s * S1_XSLAB);
-          for (int pc = hh; pc < npieces; pc += h) {
-            const int grp = pc / ppg, kk = (pc - grp * ppg) * 8;
-            if (D.use_mask)   // keys are clips (t2s): (d, s = group, t = key, b)
-              tma_load_4d_mc(dst + pc * 1024, map_x, &full[s], ks * 64, U.g0 + grp, kk, U.b, mc_mask);
-            else                                                     // keys are regions (s2t): (d, s = key, t = group, b)
-              tma_load_4d_mc(dst + pc * 1024, map_x, &full[s], ks * 64, kk, U.g0 + grp, U.b, mc_mask);
+        __syncwarp();
+      }
+    }
+  } else if (warp == 2) {
+    // ---- [qf ; W_v] producer: two heads per pass, half-slabs of 32 k ----------------------------------------------------------
+    int it = 0;
+    for (int u = u_begin; u < u_end; ++u) {
+      const Unit U = decode_unit(p, u);
+      const CUtensorMap* mw = U.di ? &map_w1 : &map_w0;
+      const CUtensorMap* mq = U.di ? &map_q1 : &map_q0;
+      for (int pr = 0; pr < npass; ++pr) {
+        for (int kh = 0; kh < 2 * nks; ++kh, ++it) {
+          const int s = it % S1_BSTAGES;
+          mbar_wait(&bempty[s], ((it / S1_BSTAGES) & 1) ^ 1);
+          if (elect_one()) {
+            S1TRACE(2, it);
+            mbar_expect_tx(&bfull[s], S1_BSLAB);
+            uint8_t* dst = smem + OFF_B + s * S1_BSLAB;
+            tma_load_3d(dst, mq, &bfull[s], kh * 32, 2 * pr, U.b * p.Lq);              // 16 folded-query rows x 2 heads: row l*2 + head
+            tma_load_2d(dst + 2 * S1_LQP * 64, mw, &bfull[s], kh * 32, pr * 128);      // the two heads' 2 x 64 value-weight rows
           }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && n_units > 0) {
-      // ---- UMMA issuer ----------------------------------------------------------------------------------------------
-      const uint32_t idesc_main = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((64 + S1_LQP) >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-      const uint32_t idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(2 * S1_LQP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-      const uint32_t b_base = smem_u32(smem + OFF_B);
-      const int ncore = D.Kp16 >> 3;                       // 8-key cores per probability row
-      auto issue_pv = [&](int ui) {
-        const int e = ui & 1;
-        const Unit U = decode_unit(D, u_begin + ui);
-        mbar_wait(&stg_full[e], (ui >> 1) & 1);
-        tc_fence_after();
-        const uint32_t xv = smem_u32(smem + OFF_XV + e * S1_XV_BYTES), pp = smem_u32(smem + OFF_P + e * S1_P_BYTES);
-        for (int r = 0; r < U.rv; r += 2) {
-          for (int kk = 0; kk < D.Kp16; kk += 16) {
-            // A: values of groups r (feature atom 0) and r+1 (atom 1, LBO = one group of staged rows), 16 keys = two 8-row groups
-            const uint64_t ad = desc_mn_sw128(xv + (uint32_t)((r * D.Kp16 + kk) * 128), (uint32_t)(D.Kp16 * 128) >> 4, 1024u >> 4);
-            // B: probabilities, rows (group r, l = 0..15), (group r+1, l = 0..15): 8-row groups ncore*128 bytes apart
-            const uint64_t bd = desc_k_none(pp + (uint32_t)(2 * r * ncore * 128 + (kk >> 3) * 128), 128u >> 4, (uint32_t)(ncore * 128) >> 4);
-            tc_mma<false>(tmem_base + 256u + (uint32_t)(e * 128 + (r >> 1) * 32), ad, bd, idesc_pv, kk ? 1u : 0u);
+    if (u_end > u_begin) {
+      // ---- UMMA issuer (whole warp converged; issue under elect.sync) --------------------------------------------------------
+      const uint32_t idesc_main = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(S1_BROWS >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int it = 0, pc = 0;
+      for (int u = u_begin, ui = 0; u < u_end; ++u, ++ui) {
+        for (int pr = 0; pr < npass; ++pr, ++pc) {
+          const int a = pc & 1;
+          mbar_wait(&acc_empty[a], ((pc >> 1) & 1) ^ 1);
+          tc_fence_after();
+          for (int ks = 0; ks < nks; ++ks, it += 2) {
+            const int s0 = it % S1_BSTAGES, s1 = (it + 1) % S1_BSTAGES;
+            if (pr == 0) mbar_wait(&xfull[ks], ui & 1);
+            mbar_wait(&bfull[s0], (it / S1_BSTAGES) & 1);
+            mbar_wait(&bfull[s1], ((it + 1) / S1_BSTAGES) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+              S1TRACE(1, it >> 1);
+              const uint64_t ad = make_desc(smem_u32(smem + OFF_X + ks * S1_XSLAB));
+              const uint64_t b0 = make_desc_sw64(smem_u32(smem + OFF_B + s0 * S1_BSLAB)), b1 = make_desc_sw64(smem_u32(smem + OFF_B + s1 * S1_BSLAB));
+              const uint32_t d = tmem_base + TM_ACC + (uint32_t)a * TM_ACC_STRIDE;
+              tc_mma<false>(d, ad, b0, idesc_main, ks ? 1u : 0u);
+              tc_mma<false>(d, ad + 2, b0 + 2, idesc_main, 1u);
+              tc_commit(&bempty[s0]);
+              tc_mma<false>(d, ad + 4, b1, idesc_main, 1u);
+              tc_mma<false>(d, ad + 6, b1 + 2, idesc_main, 1u);
+              tc_commit(&bempty[s1]);
+              if (pr == npass - 1) tc_commit(&xempty[ks]);   // the video slab may be replaced by the next tile's
+              if (ks == nks - 1) tc_commit(&acc_full[a]);
+            }
+            __syncwarp();
           }
         }
-        tc_commit(&pv_full[e]);
-      };
-      mbar_wait(w_full, 0);
-      int it = 0, cur_b = -1, nsamp = 0, qb = 0;
-      for (int ui = 0; ui < n_units; ++ui) {
-        const Unit U = decode_unit(D, u_begin + ui);
-        if (U.b != cur_b) {
-          qb = nsamp & 1;
-          mbar_wait(&qf_full[qb], (nsamp >> 1) & 1);
-          cur_b = U.b; ++nsamp;
-        }
-        const int a = ui & 1;
-        mbar_wait(&acc_empty[a], ((ui >> 1) & 1) ^ 1);
-        tc_fence_after();
-        for (int ks = 0; ks < nks; ++ks, ++it) {
-          const int s = it % S1_STAGES;
-          mbar_wait(&full[s], (it / S1_STAGES) & 1);
-          tc_fence_after();
-          const uint64_t ad = make_desc(smem_u32(smem + OFF_X + s * S1_XSLAB));
-          const uint64_t bd = make_desc(b_base + (uint32_t)(ks * S1_BSLAB + (qb ? S1_LQP * 128 : 0)));
-#pragma unroll
-          for (int k = 0; k < 4; ++k) tc_mma<false>(tmem_base + (uint32_t)(a * 128), ad + 2 * k, bd + 2 * k, idesc_main, (ks | k) ? 1u : 0u);
-          tc_commit_mc(&empty[s], mc_mask);   // the slot is free once EVERY CTA of the cluster has consumed it
-        }
-        tc_commit(&acc_full[a]);
-        const bool last_of_sample = (ui + 1 == n_units) || (decode_unit(D, u_begin + ui + 1).b != U.b);
-        if (last_of_sample) tc_commit(&qf_empty[qb]);
-        if (ui >= 1) issue_pv(ui - 1);
       }
-      issue_pv(n_units - 1);
+    }
+  } else if (warp == 3) {
+    // ---- P.V issuer: as soon as an epilogue group has staged values and probabilities of a head, multiply two groups per UMMA
+    //      (A = staged values of groups r, r+1 as the two 64-row atoms, MN-major; B = their probabilities [key][2 x 16 l], MN-major).
+    //      The two heads of a pass share ONE window of tensor memory: each product waits until the previous one has been read out.
+    const uint32_t idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(2 * S1_LQP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    int pvc = 0, pc = 0;
+    for (int u = u_begin; u < u_end; ++u) {
+      const Unit U = decode_unit(p, u);
+      const S1Dir& D = p.dir[U.di];
+      for (int pr = 0; pr < npass; ++pr, ++pc) {
+        for (int e = 0; e < 2; ++e, ++pvc) {
+          mbar_wait(&stg_full[e], pc & 1);
+          mbar_wait(pv_empty, (pvc & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t xv = smem_u32(smem + OFF_XV + e * S1_XV_BYTES), pp = smem_u32(smem + OFF_SC + e * S1_SC_BYTES);
+          if (elect_one()) {
+            for (int r = 0; r < U.rv; r += 2) {
+              for (int kk = 0; kk < D.Kp16; kk += 16) {
+                // (an odd last group has no partner: its second atom aliases the first, lanes 64-127 are ignored)
+                const uint64_t ad = desc_mn_sw128(xv + (uint32_t)((r * D.Kp8 + kk) * 128), r + 1 < U.rv ? (uint32_t)(D.Kp8 * 128) >> 4 : 0u, 1024u >> 4);
+                const uint64_t bd = desc_mn_sw64(pp + (uint32_t)(((r >> 1) * D.Kp16 + kk) * 64), 512u >> 4);
+                tc_mma<false>(tmem_base + TM_PV + (uint32_t)((r >> 1) * 32), ad, bd, idesc_pv, kk ? 1u : 0u);
+              }
+            }
+            tc_commit(&pv_full[e]);
+          }
+          __syncwarp();
+        }
+      }
     }
   } else if (warp >= 4) {
-    // ---- epilogue groups ----------------------------------------------------------------------------------------------
-    const int e = (warp - 4) >> 2;                 // group 0: warps 4-7, group 1: warps 8-11
+    // ---- epilogue groups: group e handles head 2*pass + e of every pass ----------------------------------------------------
+    const int e = (warp - 4) >> 2;
     const int q = warp & 3;                        // TMEM lane quarter
-    const int row = q * 32 + lane;                 // tile lane = key slot
+    const int row = q * 32 + lane;                 // tile row = TMEM lane
     const int wt = (warp - 4 - 4 * e) * 32 + lane; // thread index inside the group
-    const uint32_t xv = smem_u32(smem + OFF_XV + e * S1_XV_BYTES), pp = smem_u32(smem + OFF_P + e * S1_P_BYTES);
-    const uint32_t sc = smem_u32(smem + OFF_SC + e * S1_SC_BYTES);
-    const int grp = row / D.Kp8, kin = row - grp * D.Kp8;          // this lane's group / key within the tile
-    const bool lane_used = grp < D.R;
-    const uint32_t my_xv = xv + (uint32_t)((grp * D.Kp16 + kin) * 128);
-    const int sw = (grp * D.Kp16 + kin) & 7;
-    const int sgrp = wt >> 4, sl = wt & 15;                         // softmax role: (group, query token)
-    const int ncore = D.Kp16 >> 3;
-    const float bias_v = __ldg(D.bv + hh * 64 + (q & 1) * 32 + lane);
-    int cur_b = -1, nsamp = 0, qb = 0;
-    for (int ui = 0; ui < n_units; ++ui) {
-      const Unit U = decode_unit(D, u_begin + ui);
-      if (U.b != cur_b) { qb = nsamp & 1; cur_b = U.b; ++nsamp; }
-      if ((ui & 1) != e) continue;
-      mbar_wait(&acc_full[e], (ui >> 1) & 1);
-      tc_fence_after();
-      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(e * 128);
-      float* dbg = p.dbg ? p.dbg + ((((long long)di * p.dir[0].units + (u_begin + ui)) * h + hh) * 128 + row) * 80 : nullptr;
-#pragma unroll
-      for (int j = 0; j < 5; ++j) {   // five 16-column chunks: one of scores, four of projected values
-        uint32_t r[16];
-        tmem_ld16(tacc + (uint32_t)(16 * j), r);
-        if (j == 4) {   // accumulator fully read by this warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[e]);
+    uint8_t* xvp = smem + OFF_XV + e * S1_XV_BYTES;
+    const uint32_t xv = smem_u32(xvp), pp = smem_u32(smem + OFF_SC + e * S1_SC_BYTES);
+    float* scT = reinterpret_cast<float*>(smem + OFF_SC + e * S1_SC_BYTES);   // [l][row] swizzled; later the probabilities
+    uint32_t* mbits = reinterpret_cast<uint32_t*>(smem + OFF_MB + e * 16);
+    int pc = 0;
+    bool store_pending = false;
+    const bool store_leader = elect_one() && wt < 32;   // the one thread of the group that issues (and waits for) its TMA stores
+    for (int u = u_begin; u < u_end; ++u) {
+      const Unit U = decode_unit(p, u);
+      const S1Dir& D = p.dir[U.di];
+      const CUtensorMap* mc = U.di ? &map_c1 : &map_c0;
+      const bool kclips = D.kclips != 0;
+      // this row's group / key inside the tile: group-major rows for s2t, key-major rows for t2s; staged group-major
+      const int grp = kclips ? row % D.R : row / D.Kp8, kin = kclips ? row / D.R : row - (row / D.Kp8) * D.Kp8;
+      const bool row_used = row < D.R * D.Kp8;
+      const int srow = grp * D.Kp8 + kin;
+      const uint32_t my_xv = xv + (uint32_t)(srow * 128);
+      // softmax role: `parts` threads per (group, 4 query tokens); this one takes keys part, part + parts, ...
+      const int team = wt / D.parts, part = wt - team * D.parts;
+      const int sgrp = team >> 2, slq = team & 3;
+      for (int pr = 0; pr < npass; ++pr, ++pc) {
+        const int a = pc & 1, hd = 2 * pr + e;
+        if (wt == 0) S1TRACE(3 + e, (pc % 40) * 6 + 0);
+        mbar_wait(&acc_full[a], (pc >> 1) & 1);
+        if (wt == 0) S1TRACE(3 + e, (pc % 40) * 6 + 1);
+        if (store_pending) { if (store_leader) tma_store_wait_read(); store_pending = false; }   // the previous output tile has left the staging buffer
+        if (kclips && pr == 0) {   // temporal-mask bits of this sample (once per tile)
+          const uint32_t bits = __ballot_sync(0xffffffffu, wt < p.T && p.tmask[(long long)U.b * p.T + wt] != 0);
+          if (lane == 0) mbits[wt >> 5] = bits;
         }
-        const bool is_sc = qb ? (j == 4) : (j == 0);
-        if (is_sc) {
-          if (lane_used) {
+        S1FINE(0);
+        bar_sync(1 + e, 128);
+        S1FINE(1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + TM_ACC + (uint32_t)a * TM_ACC_STRIDE;
+        float* dbg = p.dbg ? p.dbg + (((long long)u * nh + hd) * 128 + row) * 80 : nullptr;
+        {
+          // accumulator columns: [0,32) scores (column 2*l + head of the pass), [32,96) values of the even head, [96,160) of the odd one
+          uint32_t r[32];
+          tmem_ld16_nw(tacc, r);
+          tmem_ld16_nw(tacc + 16, r + 16);
+          tmem_ld_wait();
+          S1FINE(2);
+          // keys past Kn (zero-filled padding rows) never take part; masked clips get exactly -1e9 (modules.py:60)
+          const bool key_pad = kin >= D.Kn;
+          const bool key_masked = kclips && kin < D.Kn && ((mbits[kin >> 5] >> (kin & 31)) & 1u) == 0u;
+          float sv[S1_LQP];   // this key's scores against the 16 query tokens of head 2*pass + e
+#pragma unroll
+          for (int l = 0; l < S1_LQP; ++l) {
+            const float x = __uint_as_float(e ? r[2 * l + 1] : r[2 * l]);
+            sv[l] = key_pad ? -INFINITY : (key_masked ? kMaskFill : x);
+          }
+          {
+            float4* s4 = reinterpret_cast<float4*>(scT);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) s4[sc_f4(row, c)] = make_float4(sv[4 * c], sv[4 * c + 1], sv[4 * c + 2], sv[4 * c + 3]);
+          }
+          if (dbg) for (int i = 0; i < 16; ++i) dbg[i] = __uint_as_float(e ? r[2 * i + 1] : r[2 * i]);
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t r[32];
+          tmem_ld16_nw(tacc + (uint32_t)(32 + 64 * e + 32 * half), r);
+          tmem_ld16_nw(tacc + (uint32_t)(48 + 64 * e + 32 * half), r + 16);
+          tmem_ld_wait();
+          if (half == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[a]);   // this warp has read its part of the accumulator
+          }
+          if (row_used) {
 #pragma unroll
             for (int c = 0; c < 4; ++c)
-              st_shared_v4(sc + (uint32_t)(row * 64 + (((c ^ (row >> 1)) & 3) << 4)), r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
-          }
-          if (dbg) for (int i = 0; i < 16; ++i) dbg[i] = __uint_as_float(r[i]);
-        } else {
-          const int vc = qb ? j : j - 1;   // 16-feature chunk of the head's 64 projected values
-          if (lane_used) {
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-              const int chunk = vc * 2 + c;
-              st_shared_v4(my_xv + (uint32_t)(((chunk ^ sw) & 7) << 4),
+              st_shared_v4(my_xv + (uint32_t)((((4 * half + c) ^ srow) & 7) << 4),
                            pack2(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])),
                            pack2(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
                            pack2(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])),
                            pack2(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
-            }
           }
-          if (dbg) for (int i = 0; i < 16; ++i) dbg[16 + vc * 16 + i] = __uint_as_float(r[i]);
+          if (dbg) for (int i = 0; i < 32; ++i) dbg[16 + 32 * half + i] = __uint_as_float(r[i]);
         }
-      }
-      bar_sync(1 + e, 128);
-      // ---- masked softmax over the keys of (group sgrp, query token sl) — modules.py:57-61 -------------------------
-      if (sgrp < U.rv && sl < p.Lq) {
-        const int row0 = sgrp * D.Kp8;
-        const uint8_t* mk = D.use_mask ? p.tmask + (long long)U.b * p.T : nullptr;
-        float mx = -INFINITY;
-        for (int k = 0; k < D.Kn; ++k) {
-          float v = ld_shared_f32(sc_addr(sc, row0 + k, sl));
-          if (mk && mk[k] == 0) v = kMaskFill;
-          mx = fmaxf(mx, v);
-        }
-        float sum = 0.f;
-        for (int k = 0; k < D.Kn; ++k) {
-          float v = ld_shared_f32(sc_addr(sc, row0 + k, sl));
-          if (mk && mk[k] == 0) v = kMaskFill;
-          sum += __expf(v - mx);
-        }
-        const float inv = 1.f / sum;
-        const uint32_t prow = pp + (uint32_t)(((2 * sgrp + (sl >> 3)) * ncore) * 128 + (sl & 7) * 16);
-        for (int c = 0; c < ncore; ++c) {
-          float pv[8];
+        S1FINE(3);
+        bar_sync(1 + e, 128);
+        if (wt == 0) S1TRACE(3 + e, (pc % 40) * 6 + 2);
+        // ---- masked softmax over the keys of group sgrp for query tokens 4*slq .. 4*slq+3 — modules.py:57-61 ------------------
+        {
+          const bool act = sgrp < U.rv;
+          const float4* s4 = reinterpret_cast<const float4*>(scT);
+          float4 x[8];
+          float4 mx = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const int k = c * 8 + j;
-            float v = 0.f;
-            if (k < D.Kn) {
-              v = ld_shared_f32(sc_addr(sc, row0 + k, sl));
-              if (mk && mk[k] == 0) v = kMaskFill;
-              v = __expf(v - mx) * inv;
-            }
-            pv[j] = v;
+            const int k = part + j * D.parts;
+            x[j] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+            if (j < D.kpp && act && k < D.Kp8) x[j] = s4[sc_f4(kclips ? k * D.R + sgrp : sgrp * D.Kp8 + k, slq)];
+            mx.x = fmaxf(mx.x, x[j].x); mx.y = fmaxf(mx.y, x[j].y); mx.z = fmaxf(mx.z, x[j].z); mx.w = fmaxf(mx.w, x[j].w);
           }
-          st_shared_v4(prow + (uint32_t)(c * 128), pack2(pv[0], pv[1]), pack2(pv[2], pv[3]), pack2(pv[4], pv[5]), pack2(pv[6], pv[7]));
-        }
-      }
-      fence_proxy_async_smem();   // generic-proxy writes of values and probabilities -> visible to the tensor core
-      bar_sync(1 + e, 128);
-      if (wt == 0) mbar_arrive(&stg_full[e]);
-      // ---- P.V result: lanes 0-63 = features of the even group of a pair, lanes 64-127 = of the odd group ------------
-      mbar_wait(&pv_full[e], (ui >> 1) & 1);
-      tc_fence_after();
-      const int feat = hh * 64 + (q & 1) * 32 + lane;
-      for (int r0 = 0; r0 < U.rv; r0 += 2) {
-        const int r = r0 + (q >> 1);
-        uint32_t v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + 256u + (uint32_t)(e * 128 + (r0 >> 1) * 32 + (q >> 1) * S1_LQP), v);
-        if (r < U.rv) {
-          __nv_bfloat16* o = D.c1 + (((long long)U.b * p.Lq) * D.G + (U.g0 + r)) * p.d + feat;
-          const long long ol = (long long)D.G * p.d;
+          for (int o = D.parts >> 1; o > 0; o >>= 1) {
+            mx.x = fmaxf(mx.x, __shfl_xor_sync(0xffffffffu, mx.x, o)); mx.y = fmaxf(mx.y, __shfl_xor_sync(0xffffffffu, mx.y, o));
+            mx.z = fmaxf(mx.z, __shfl_xor_sync(0xffffffffu, mx.z, o)); mx.w = fmaxf(mx.w, __shfl_xor_sync(0xffffffffu, mx.w, o));
+          }
+          float4 sm = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (act) {
 #pragma unroll
-          for (int l = 0; l < S1_LQP; ++l)
-            if (l < p.Lq) o[l * ol] = __float2bfloat16_rn(__uint_as_float(v[l]) + bias_v);
+            for (int j = 0; j < 8; ++j) {
+              x[j].x = __expf(x[j].x - mx.x); x[j].y = __expf(x[j].y - mx.y); x[j].z = __expf(x[j].z - mx.z); x[j].w = __expf(x[j].w - mx.w);
+              sm.x += x[j].x; sm.y += x[j].y; sm.z += x[j].z; sm.w += x[j].w;
+            }
+          }
+          for (int o = D.parts >> 1; o > 0; o >>= 1) {
+            sm.x += __shfl_xor_sync(0xffffffffu, sm.x, o); sm.y += __shfl_xor_sync(0xffffffffu, sm.y, o);
+            sm.z += __shfl_xor_sync(0xffffffffu, sm.z, o); sm.w += __shfl_xor_sync(0xffffffffu, sm.w, o);
+          }
+          S1FINE(4);
+          bar_sync(1 + e, 128);   // all scores are in registers: the probabilities take their place
+          S1FINE(5);
+          if (act) {
+            const float ix = 1.f / sm.x, iy = 1.f / sm.y, iz = 1.f / sm.z, iw = 1.f / sm.w;
+            // probabilities of a pair of groups: [key][2 x 16 query tokens] bf16, 64-byte rows, 16-byte chunks XOR-swizzled by (key >> 1) & 3
+            const uint32_t pbase = pp + (uint32_t)((sgrp >> 1) * D.Kp16 * 64);
+            const int ch = (sgrp & 1) * 2 + (slq >> 1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int k = part + j * D.parts;
+              if (j < D.kpp && k < D.Kp16) {   // keys Kp8 .. Kp16 are written as zeros (exp(-inf))
+                const uint32_t a = pbase + (uint32_t)(k * 64 + ((ch ^ ((k >> 1) & 3)) << 4) + (slq & 1) * 8);
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(pack2(x[j].x * ix, x[j].y * iy)), "r"(pack2(x[j].z * iz, x[j].w * iw)) : "memory");
+              }
+            }
+          }
         }
+        S1FINE(6);
+        fence_proxy_async_smem();   // generic-proxy writes of values and probabilities -> visible to the tensor core
+        S1FINE(7);
+        bar_sync(1 + e, 128);
+        S1FINE(8);
+        if (wt == 0) { mbar_arrive(&stg_full[e]); S1TRACE(3 + e, (pc % 40) * 6 + 3); }
+        // ---- P.V results: lanes 0-63 = features of the even group of a pair, lanes 64-127 = of the odd group.  The staged
+        //      values are dead now: the [l][group][64 features] output tile is assembled in their place ---------------------
+        mbar_wait(&pv_full[e], pc & 1);
+        if (wt == 0) S1TRACE(3 + e, (pc % 40) * 6 + 4);
+        tc_fence_after();
+        {
+          const float bias_v = __ldg(D.bv + hd * 64 + (q & 1) * 32 + lane);
+          __nv_bfloat16* ot = reinterpret_cast<__nv_bfloat16*>(xvp) + (q & 1) * 32 + lane;
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {   // two pairs of groups at a time
+            uint32_t v[2][16];
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+              if (2 * (2 * jj + j) < U.rv) tmem_ld16_nw(tmem_base + ((uint32_t)(q * 32) << 16) + TM_PV + (uint32_t)((2 * jj + j) * 32 + (q >> 1) * S1_LQP), v[j]);
+            tmem_ld_wait();
+            if (jj == 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(pv_empty);   // the P.V window may be overwritten by the other head's product
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const int r = 2 * (2 * jj + j) + (q >> 1);
+              if (r < U.rv) {
+#pragma unroll
+                for (int l = 0; l < S1_LQP; ++l) ot[(l * D.R + r) * 64] = __float2bfloat16_rn(__uint_as_float(v[j][l]) + bias_v);
+              }
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        bar_sync(1 + e, 128);
+        if (store_leader) {
+          tma_store_4d(mc, xv, hd * 64, U.g0, 0, U.b);   // rows beyond G / Lq are clipped by the tensor map
+          S1TRACE(3 + e, (pc % 40) * 6 + 5);
+        }
+        store_pending = true;
       }
-      tc_fence_before();
     }
+    if (store_leader) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();   // peers may still arrive on this CTA's barriers / multicast into it until here
   if (warp == 2) tmem_dealloc(tmem_base, 512);
 }
 
-int make_map_x(CUtensorMap* m, const void* vft, int64_t B, int64_t T, int64_t S, int64_t d, bool keys_are_clips) {
+int make_map_x(CUtensorMap* m, const void* vft, int64_t B, int64_t T, int64_t S, int64_t d, bool keys_are_clips, int Kp8, int R) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
   cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)S, (cuuint64_t)T, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)d * 2, (cuuint64_t)S * d * 2, (cuuint64_t)T * S * d * 2};
-  cuuint32_t box[4] = {64, keys_are_clips ? 1u : 8u, keys_are_clips ? 8u : 1u, 1};
+  // one box = one tile slab: s2t (keys = regions) R clips x Kp8 regions, t2s (keys = clips) Kp8 clips x R regions; out-of-range
+  // regions / clips are zero-filled
+  cuuint32_t box[4] = {64, (cuuint32_t)(keys_are_clips ? R : Kp8), (cuuint32_t)(keys_are_clips ? Kp8 : R), 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(vft), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (4d video view) failed (%d)", (int)r); return BIST_ERR_CUDA; }
+  return 0;
+}
+
+// c1 [B, Lq, G, d] bf16 as (d, G, Lq, B); box = 64 features x R groups x 16 query tokens
+int make_map_c(CUtensorMap* m, void* c1, int64_t B, int64_t Lq, int64_t G, int64_t d, int R) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
+  cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)G, (cuuint64_t)Lq, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)d * 2, (cuuint64_t)G * d * 2, (cuuint64_t)Lq * G * d * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)R, (cuuint32_t)S1_LQP, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, c1, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (c1 view) failed (%d)", (int)r); return BIST_ERR_CUDA; }
   return 0;
 }
 
@@ -410,10 +538,10 @@ int make_map_x(CUtensorMap* m, const void* vft, int64_t B, int64_t T, int64_t S,
 bool stage1_fused_supported(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h) {
   static const bool off = getenv("BIST_STAGE1_UNFUSED") != nullptr;
   if (off) return false;
-  if (h != 1 && h != 2 && h != 4 && h != 8) return false;
+  if (h != 2 && h != 4 && h != 6 && h != 8) return false;   // two heads per pass
   if (d != 64 * h || Lq < 1 || Lq > S1_LQP) return false;
   if (T < 1 || S < 1 || T > 128 || S > 128 || B < 1) return false;
-  if (B * (T + S) >= (1LL << 30)) return false;
+  if (B * (T + S) >= (1LL << 29)) return false;
   return true;
 }
 
@@ -426,66 +554,53 @@ int stage1_fused(const void* vft, const uint8_t* tmask, int nd, const int* kinds
   BIST_CHECK_ARG(((uintptr_t)vft & 15) == 0, "stage1_fused: vft must be 16-byte aligned");
   S1Args p = {};
   p.tmask = tmask; p.dbg = dbg;
-  p.B = (int)B; p.T = (int)T; p.S = (int)S; p.Lq = (int)Lq; p.d = (int)d; p.h = (int)h; p.nks = (int)(d / 64);
-  CUtensorMap mx[2], mw[2], mq[2];
-  long long tiles[2] = {0, 0};
+  static const bool trace = getenv("BIST_S1_TRACE") != nullptr;
+  p.trace = trace ? 1 : 0;
+  p.B = (int)B; p.T = (int)T; p.S = (int)S; p.Lq = (int)Lq; p.d = (int)d; p.nh = (int)h; p.nks = (int)(d / 64);
+  CUtensorMap mx[2], mw[2], mq[2], mc[2];
   for (int u = 0; u < nd; ++u) {
     S1Dir& D = p.dir[u];
     const bool t2s = kinds[u] == 0;
     BIST_CHECK_ARG(qf[u] && wv[u] && bv[u] && c1[u], "stage1_fused: null pointer");
-    BIST_CHECK_ARG((((uintptr_t)qf[u] | (uintptr_t)wv[u]) & 15) == 0, "stage1_fused: operands must be 16-byte aligned");
+    BIST_CHECK_ARG((((uintptr_t)qf[u] | (uintptr_t)wv[u] | (uintptr_t)c1[u]) & 15) == 0, "stage1_fused: operands must be 16-byte aligned");
+    BIST_CHECK_ARG(((uintptr_t)bv[u] & 7) == 0, "stage1_fused: bias must be 8-byte aligned");
     BIST_CHECK_ARG(!t2s || tmask, "stage1_fused: t2s needs the temporal mask");
-    D.bv = bv[u]; D.c1 = (__nv_bfloat16*)c1[u];
+    D.bv = bv[u];
     D.G = (int)(t2s ? S : T); D.Kn = (int)(t2s ? T : S);
     D.Kp8 = (D.Kn + 7) & ~7; D.Kp16 = (D.Kn + 15) & ~15;
     D.R = 128 / D.Kp8; if (D.R > S1_MAXR) D.R = S1_MAXR;
-    while (D.R > 1 && D.R * D.Kp16 > S1_XV_ROWS) --D.R;   // staged value rows of a tile fit one staging buffer
-    D.tiles_per_b = (D.G + D.R - 1) / D.R; D.units = (int)(B * D.tiles_per_b);
-    D.use_mask = t2s ? 1 : 0;
-    tiles[u] = D.units;
-    BIST_TRY(make_map_x(&mx[u], vft, B, T, S, d, t2s));
-    BIST_TRY(make_map_2d(&mw[u], wv[u], false, d, d, 64, 64, 128));
-    // folded queries [B*Lq, h, d]: (d, h, B*Lq) view, box 64 x 1 x 16
-    BIST_TRY(make_map_3d(&mq[u], qf[u], false, d, h, B * Lq, d * 2, h * d * 2, 64, 1, S1_LQP));
+    while (D.R > 1 && D.R * D.Kp16 > 160) --D.R;   // probability rows of a tile fit their buffer
+    D.tpb = (D.G + D.R - 1) / D.R; D.units = (int)(B * D.tpb);
+    D.kclips = t2s ? 1 : 0;
+    D.parts = 1;
+    while (D.parts < 32 && D.R * 4 * D.parts * 2 <= 128) D.parts *= 2;
+    D.kpp = (D.Kp16 + D.parts - 1) / D.parts;
+    BIST_CHECK_ARG(D.kpp <= 8, "stage1_fused: softmax key chunk too long");
+    BIST_TRY(make_map_x(&mx[u], vft, B, T, S, d, t2s, D.Kp8, D.R));
+    BIST_TRY(make_map_c(&mc[u], c1[u], B, Lq, D.G, d, D.R));
+    BIST_TRY(make_map_2d(&mw[u], wv[u], false, d, d, 32, 128, 64));   // half-slab: 32 k x the two heads' 128 value-weight rows
+    // folded queries [B*Lq, h, d]: (d, h, B*Lq) view, box 32 k x 2 heads x 16 query tokens (rows l*2 + head in shared memory)
+    BIST_TRY(make_map_3d(&mq[u], qf[u], false, d, h, B * Lq, d * 2, h * d * 2, 32, 2, S1_LQP, 64));
   }
-  if (nd == 1) { p.dir[1] = p.dir[0]; mx[1] = mx[0]; mw[1] = mw[0]; mq[1] = mq[0]; }
+  if (nd == 1) { p.dir[1] = p.dir[0]; p.dir[1].units = 0; mx[1] = mx[0]; mw[1] = mw[0]; mq[1] = mq[0]; mc[1] = mc[0]; }
+  p.total_units = p.dir[0].units + p.dir[1].units;
 
   static bool configured = false;
-  static int max_clusters[9] = {0};
   if (!configured) {
     BIST_CUDA(cudaFuncSetAttribute(stage1_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S1_SMEM));
     configured = true;
   }
+  int ctas = num_sms();
+  if (ctas > p.total_units) ctas = p.total_units;
   cudaLaunchConfig_t cfg = {};
-  cudaLaunchAttribute at[2];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = (unsigned)h; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
-  cfg.blockDim = dim3(384); cfg.dynamicSmemBytes = S1_SMEM; cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 2;
-  if (max_clusters[h] == 0) {
-    cfg.gridDim = dim3((unsigned)(num_sms() / h * h));
-    int n = 0;
-    cfg.numAttrs = 1;
-    BIST_CUDA(cudaOccupancyMaxActiveClusters(&n, stage1_fused_kernel, &cfg));
-    cfg.numAttrs = 2;
-    max_clusters[h] = n > 0 ? n : 1;
-  }
-  long long total = tiles[0] + (nd == 2 ? tiles[1] : 0);
-  int C = (int)(total < max_clusters[h] ? total : max_clusters[h]);
-  if (nd == 2 && C < 2) C = 2;
-  if (nd == 2) {
-    int c0 = (int)((tiles[0] * C + total / 2) / total);
-    c0 = c0 < 1 ? 1 : (c0 > C - 1 ? C - 1 : c0);
-    p.dir[0].cl_begin = 0; p.dir[0].cl_end = c0;
-    p.dir[1].cl_begin = c0; p.dir[1].cl_end = C;
-  } else {
-    p.dir[0].cl_begin = 0; p.dir[0].cl_end = C;
-    p.dir[1].cl_begin = C; p.dir[1].cl_end = C;
-  }
-  cfg.gridDim = dim3((unsigned)(C * h));
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(384); cfg.dynamicSmemBytes = S1_SMEM; cfg.stream = st;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  if (trace) fprintf(stderr, "[stage1_fused] %d CTAs, tiles %d + %d\n", ctas, p.dir[0].units, p.dir[1].units);
   ProfScope ps("stage1_fused", st);
-  BIST_CUDA(cudaLaunchKernelEx(&cfg, stage1_fused_kernel, mx[0], mx[1], mw[0], mw[1], mq[0], mq[1], p));
+  BIST_CUDA(cudaLaunchKernelEx(&cfg, stage1_fused_kernel, mx[0], mx[1], mw[0], mw[1], mq[0], mq[1], mc[0], mc[1], p));
   BIST_LAUNCHED();
   return 0;
 }
@@ -498,6 +613,9 @@ extern "C" int bist_stage1_fused(const void* vft, const uint8_t* temporal_mask, 
                                  const void* const* wv, const float* const* bv, void* const* c1, int64_t B, int64_t T, int64_t S,
                                  int64_t Lq, int64_t d, int64_t h, float* dbg, void* stream) {
   return bist::stage1_fused(vft, temporal_mask, nd, kinds, qf, wv, bv, c1, B, T, S, Lq, d, h, dbg, (cudaStream_t)stream);
+}
+extern "C" int bist_debug_s1_trace(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, bist::g_s1trace, sizeof(bist::g_s1trace)) == cudaSuccess ? 0 : 1;
 }
 extern "C" int bist_stage1_fused_supported(int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h) {
   return bist::stage1_fused_supported(B, T, S, Lq, d, h) ? 1 : 0;

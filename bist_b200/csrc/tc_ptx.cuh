@@ -204,7 +204,7 @@ inline int make_map_2d(CUtensorMap* m, const void* base, bool f32, long long ld,
 
 // 3-D view [d2, d1, d0] (d0 contiguous) with byte strides st1, st2 and a [b2, b1, b0] box, 128B swizzle.
 inline int make_map_3d(CUtensorMap* m, const void* base, bool f32, long long d0, long long d1, long long d2, long long st1_bytes,
-                       long long st2_bytes, int b0, int b1, int b2) {
+                       long long st2_bytes, int b0, int b1, int b2, int swizzle_bytes = 128) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
   cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
@@ -212,7 +212,8 @@ inline int make_map_3d(CUtensorMap* m, const void* base, bool f32, long long d0,
   cuuint32_t box[3] = {(cuuint32_t)b0, (cuuint32_t)b1, (cuuint32_t)b2};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base),
-                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (3d) failed (%d)", (int)r); return BIST_ERR_CUDA; }
   return 0;

@@ -17,7 +17,8 @@ CASES = [
     (4, 2, 128, 49, 16, 512, 8),
     (5, 5, 6, 16, 5, 128, 2),
     (6, 2, 64, 16, 1, 256, 4),
-    (7, 2, 17, 20, 9, 64, 1),
+    (7, 2, 17, 20, 9, 384, 6),
+    (8, 3, 9, 12, 3, 128, 2),
 ]
 
 
@@ -59,6 +60,16 @@ def main():
                 ts.append(ev0.elapsed_time(ev1) * 1e3)
         ts.sort()
         print("config 2 kinds %s: median %.1f us, min %.1f us (L2 flushed between launches)" % (kinds, ts[len(ts) // 2], ts[0]), flush=True)
+        if os.environ.get("BIST_S1_TRACE"):
+            buf = (ctypes.c_longlong * (6 * 256))()
+            L.bist_debug_s1_trace.argtypes = [ctypes.c_void_p]
+            L.bist_debug_s1_trace(buf)
+            tr = [[buf[r * 256 + i] for i in range(256)] for r in range(6)]
+            t0 = min(x for r in tr for x in r if x > 0)
+            names = ["x producer: slab requested", "mma: operands landed", "b producer: slot free", "epi0 (wait,acc,staged,softmax,pv,store)", "epi1", "epi0 fine (prebar,bar,ld sc,staged,smx,bar,Pst,fence,bar,-)"]
+            for r in range(6):
+                vals = [x - t0 for x in tr[r][:(60 if r == 5 else 96)] if x > 0]
+                print("   trace %-32s %s" % (names[r], " ".join(str(v) for v in vals)), flush=True)
 
 
 if __name__ == "__main__":

@@ -72,7 +72,7 @@ def run_kernel(vft, tmask, dirs, kinds, Lq, h, want_dbg=False):
         G, Kn = (S, T) if k == 0 else (T, S)
         outs.append(torch.full((B, Lq, G, d), float("nan"), dtype=torch.bfloat16, device=vft.device))
         _, _, R = tile_geometry(Kn)
-        units.append(B * ((G + R - 1) // R))
+        units.append(B * ((G + R - 1) // R))                  # a unit = one tile of up to R groups
     dbg = None
     if want_dbg:
         dbg = torch.zeros(sum(units), h, 128, 80, dtype=torch.float32, device=vft.device)
@@ -120,7 +120,8 @@ def check_case(seed, B, T, S, Lq, d, h, kinds=(0, 1), device="cuda:0", verbose=F
                     g = g0 + r
                     rows = x[b, :, g, :] if k == 0 else x[b, g, :, :]          # [Kn, d]
                     for hh in (0, h - 1):
-                        tile = dbg[off + u, hh, r * kp8:r * kp8 + Kn]            # [Kn, 80]
+                        # tile rows: group-major for s2t (r*kp8 + key), key-major for t2s (key*R + r)
+                        tile = dbg[off + u, hh, r:r + Kn * R:R] if k == 0 else dbg[off + u, hh, r * kp8:r * kp8 + Kn]
                         es = rows @ q[b, :, hh, :].t()                           # [Kn, Lq]
                         ev = rows @ wv.float()[hh * 64:(hh + 1) * 64].t()        # [Kn, 64]
                         worst_s = max(worst_s, nerr(tile[:, :Lq], es))
