@@ -72,7 +72,7 @@ struct S1Dir {
   int G, Kn;              // groups per sample, keys per group
   int Kp8, Kp16, R;       // keys padded to 8 (tile rows) / 16 (UMMA K of P.V); groups per tile
   int tpb, units;         // tiles per sample; B * tpb
-  int kclips;             // keys are clips (t2s): temporal_mask[b][k], tile rows are key-major (k * R + group)
+  int kclips;             // keys are clips (t2s): temporal_mask[b][k]; the tile is gathered region by region (one TMA box each)
   int parts, kpp;         // softmax team: `parts` threads per (group, 4 query tokens), kpp keys each (key = part + j * parts)
 };
 struct S1Args {
@@ -144,12 +144,16 @@ __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync
 // unit (tile) -> direction, sample, first group, valid groups
 struct Unit { int di, b, g0, rv; };
 __device__ __forceinline__ Unit decode_unit(const S1Args& p, int u) {
+  // sample-major order: all tiles of sample b (direction 0, then direction 1) are adjacent, so CTAs that run at the same time
+  // read the same video rows and the second direction finds them in L2
   Unit x;
-  x.di = u >= p.dir[0].units ? 1 : 0;
+  const int per_b = p.dir[0].tpb + p.dir[1].tpb;
+  x.b = u / per_b;
+  int j = u - x.b * per_b;
+  x.di = j >= p.dir[0].tpb ? 1 : 0;
+  if (x.di) j -= p.dir[0].tpb;
   const S1Dir& D = p.dir[x.di];
-  const int uu = u - (x.di ? p.dir[0].units : 0);
-  x.b = uu / D.tpb;
-  x.g0 = (uu - x.b * D.tpb) * D.R;
+  x.g0 = j * D.R;
   const int left = D.G - x.g0;
   x.rv = left < D.R ? left : D.R;
   return x;
@@ -221,8 +225,14 @@ __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_const
         if (elect_one()) {
           mbar_expect_tx(&xfull[ks], slab_bytes);
           // one box = R groups x Kp8 keys x 64 k; out-of-range groups / keys are zero-filled
-          if (D.kclips) tma_load_4d(smem + OFF_X + ks * S1_XSLAB, mx, &xfull[ks], ks * 64, U.g0, 0, U.b);
-          else tma_load_4d(smem + OFF_X + ks * S1_XSLAB, mx, &xfull[ks], ks * 64, 0, U.g0, U.b);
+          // tile rows are group-major (group * Kp8 + key) in both directions: s2t groups (clips) are adjacent in memory, one box
+          // R clips x Kp8 regions; t2s groups (regions) are gathered one box of Kp8 clips at stride S*d each
+          if (D.kclips) {
+            for (int g = 0; g < D.R; ++g)
+              tma_load_4d(smem + OFF_X + ks * S1_XSLAB + g * D.Kp8 * 128, mx, &xfull[ks], ks * 64, U.g0 + g, 0, U.b);
+          } else {
+            tma_load_4d(smem + OFF_X + ks * S1_XSLAB, mx, &xfull[ks], ks * 64, 0, U.g0, U.b);
+          }
           S1TRACE(0, ui * nks + ks);
         }
         __syncwarp();
@@ -333,8 +343,8 @@ __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_const
       const S1Dir& D = p.dir[U.di];
       const CUtensorMap* mc = U.di ? &map_c1 : &map_c0;
       const bool kclips = D.kclips != 0;
-      // this row's group / key inside the tile: group-major rows for s2t, key-major rows for t2s; staged group-major
-      const int grp = kclips ? row % D.R : row / D.Kp8, kin = kclips ? row / D.R : row - (row / D.Kp8) * D.Kp8;
+      // this row's group / key inside the tile (group-major rows); the values are staged in the same order
+      const int grp = row / D.Kp8, kin = row - grp * D.Kp8;
       const bool row_used = row < D.R * D.Kp8;
       const int srow = grp * D.Kp8 + kin;
       const uint32_t my_xv = xv + (uint32_t)(srow * 128);
@@ -415,7 +425,7 @@ __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_const
           for (int j = 0; j < 8; ++j) {
             const int k = part + j * D.parts;
             x[j] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-            if (j < D.kpp && act && k < D.Kp8) x[j] = s4[sc_f4(kclips ? k * D.R + sgrp : sgrp * D.Kp8 + k, slq)];
+            if (j < D.kpp && act && k < D.Kp8) x[j] = s4[sc_f4(sgrp * D.Kp8 + k, slq)];
             mx.x = fmaxf(mx.x, x[j].x); mx.y = fmaxf(mx.y, x[j].y); mx.z = fmaxf(mx.z, x[j].z); mx.w = fmaxf(mx.w, x[j].w);
           }
           for (int o = D.parts >> 1; o > 0; o >>= 1) {
@@ -509,9 +519,9 @@ int make_map_x(CUtensorMap* m, const void* vft, int64_t B, int64_t T, int64_t S,
   if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
   cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)S, (cuuint64_t)T, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)d * 2, (cuuint64_t)S * d * 2, (cuuint64_t)T * S * d * 2};
-  // one box = one tile slab: s2t (keys = regions) R clips x Kp8 regions, t2s (keys = clips) Kp8 clips x R regions; out-of-range
-  // regions / clips are zero-filled
-  cuuint32_t box[4] = {64, (cuuint32_t)(keys_are_clips ? R : Kp8), (cuuint32_t)(keys_are_clips ? Kp8 : R), 1};
+  // s2t (keys = regions): one box = R clips x Kp8 regions = the whole tile slab; t2s (keys = clips): one box = Kp8 clips of ONE
+  // region (rows at stride S*d), R boxes per slab; out-of-range regions / clips are zero-filled
+  cuuint32_t box[4] = {64, (cuuint32_t)(keys_are_clips ? 1 : Kp8), (cuuint32_t)(keys_are_clips ? Kp8 : R), 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(vft), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -582,7 +592,7 @@ int stage1_fused(const void* vft, const uint8_t* tmask, int nd, const int* kinds
     // folded queries [B*Lq, h, d]: (d, h, B*Lq) view, box 32 k x 2 heads x 16 query tokens (rows l*2 + head in shared memory)
     BIST_TRY(make_map_3d(&mq[u], qf[u], false, d, h, B * Lq, d * 2, h * d * 2, 32, 2, S1_LQP, 64));
   }
-  if (nd == 1) { p.dir[1] = p.dir[0]; p.dir[1].units = 0; mx[1] = mx[0]; mw[1] = mw[0]; mq[1] = mq[0]; mc[1] = mc[0]; }
+  if (nd == 1) { p.dir[1] = p.dir[0]; p.dir[1].units = 0; p.dir[1].tpb = 0; mx[1] = mx[0]; mw[1] = mw[0]; mq[1] = mq[0]; mc[1] = mc[0]; }
   p.total_units = p.dir[0].units + p.dir[1].units;
 
   static bool configured = false;

@@ -254,6 +254,64 @@ __global__ void __launch_bounds__(128, 1) issue2_kernel(int N, int NM, int iters
   if (threadIdx.x >= 32 && threadIdx.x < 64) tmem_dealloc(tm, 512);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------- 6. CUDA-core work under UMMA load
+// 4 warps run (a) a dependent FFMA chain, (b) dependent shared-memory loads, (c) dependent shuffles, (d) independent 16-byte
+// shared-memory stores, with and without a saturating tcgen05 stream (M = 128, N = 160 from shared memory) on the same SM.
+__global__ void __launch_bounds__(256, 1) mix_kernel(int with_umma, int N, int nmma, int what, int iters, long long* out, float* sink) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* done = (uint64_t*)(smem + 65536);
+  uint32_t* slot = (uint32_t*)(done + 1);
+  for (int i = threadIdx.x; i < 65536 / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) { mbar_init(done, 1); fence_barrier_init(); }
+  if (threadIdx.x < 32) tmem_alloc(slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = *slot;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) {
+    if (with_umma) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      const uint64_t ad = make_desc(smem_u32(smem)), bd = make_desc(smem_u32(smem + 16384));
+      if (elect_one()) {
+        for (int i = 0; i < nmma; ++i) tc_mma<false>(tm, ad + 2 * (i & 3), bd + 2 * (i & 3), idesc, 1u);
+        tc_commit(done);
+      }
+      __syncwarp();
+      mbar_wait(done, 0);
+    }
+  } else if (warp >= 4) {
+    volatile uint32_t* sm32 = reinterpret_cast<volatile uint32_t*>(smem + 49152);
+    float a = (float)threadIdx.x, acc = 0.f;
+    uint32_t idx = threadIdx.x & 31;
+    long long t0 = clock64();
+    if (what == 0) {
+      for (int i = 0; i < iters; ++i) { a = fmaf(a, 1.000001f, 0.5f); }
+      acc = a;
+    } else if (what == 1) {
+      for (int i = 0; i < iters; ++i) { idx = sm32[idx] + (threadIdx.x & 31); }
+      acc = (float)idx;
+    } else if (what == 2) {
+      for (int i = 0; i < iters; ++i) { a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1 + (i & 15))); }
+      acc = a;
+    } else {
+      uint4 v = make_uint4(idx, idx, idx, idx);
+      uint4* dst = reinterpret_cast<uint4*>(smem + 49152) + threadIdx.x;
+      for (int i = 0; i < iters; ++i) { dst[(i & 3) * 256] = v; }
+      __syncwarp();
+      acc = 1.f;
+    }
+    long long t1 = clock64();
+    if (acc == 12345.678f) sink[0] = acc;
+    if ((threadIdx.x & 31) == 0) out[blockIdx.x * 4 + (warp - 4)] = t1 - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) tmem_dealloc(tm, 512);
+}
+
 template <typename T>
 static double mean_of(const std::vector<T>& v) { double s = 0; for (auto x : v) s += (double)x; return s / v.size(); }
 
@@ -378,6 +436,22 @@ int main() {
           printf("converged issue loop N=%3d, %d UMMAs per iteration, mode %2d (1 try_wait, 2 commit, 4 poll): %.0f cycles per iteration (pipe time %.0f)\n",
                  N, NM, mode, mean_of(v) / iters, NM * (N <= 80 ? 52.2 : N / 2.0));
         }
+      }
+    }
+  }
+  // ---- 6. CUDA-core work under UMMA load
+  {
+    const int smem = 65536 + 64;
+    CK(cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const char* names[4] = {"dependent FFMA", "dependent LDS.32", "dependent SHFL", "independent STS.128"};
+    const int iters = 2048;
+    for (int what = 0; what < 4; ++what) {
+      for (int with : {0, 1}) {
+        mix_kernel<<<sms, 256, smem>>>(with, 160, 16384, what, iters, d_out, d_sink);
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(h.data(), d_out, sizeof(long long) * sms * 4, cudaMemcpyDeviceToHost));
+        std::vector<long long> v(h.begin(), h.begin() + sms * 4);
+        printf("mix %-20s tcgen05 stream (N=160) %s: %.1f cycles per op per warp\n", names[what], with ? "ON " : "off", mean_of(v) / iters);
       }
     }
   }

@@ -114,14 +114,17 @@ def check_case(seed, B, T, S, Lq, d, h, kinds=(0, 1), device="cuda:0", verbose=F
             x = vft.float()
             q = qf.float().view(B, Lq, h, d)
             worst_s = worst_v = 0.0
+            per_b = sum(units) // B                     # tiles of one sample, both directions (sample-major unit order)
+            base = sum(units[:i]) // B                  # tiles of the directions launched before this one
             for u in (0, units[i] // 2, units[i] - 1):
-                b, g0 = u // tpb, (u % tpb) * R
+                b, j = u // tpb, u % tpb
+                g0 = j * R
+                gu = b * per_b + base + j               # global unit index of the kernel
                 for r in range(min(R, G - g0)):
                     g = g0 + r
                     rows = x[b, :, g, :] if k == 0 else x[b, g, :, :]          # [Kn, d]
                     for hh in (0, h - 1):
-                        # tile rows: group-major for s2t (r*kp8 + key), key-major for t2s (key*R + r)
-                        tile = dbg[off + u, hh, r:r + Kn * R:R] if k == 0 else dbg[off + u, hh, r * kp8:r * kp8 + Kn]
+                        tile = dbg[gu, hh, r * kp8:r * kp8 + Kn]                 # group-major tile rows
                         es = rows @ q[b, :, hh, :].t()                           # [Kn, Lq]
                         ev = rows @ wv.float()[hh * 64:(hh + 1) * 64].t()        # [Kn, 64]
                         worst_s = max(worst_s, nerr(tile[:, :Lq], es))
