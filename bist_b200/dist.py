@@ -45,6 +45,27 @@ def gather_rows(local, n_rows):
     return torch.cat(out, 0)
 
 
+def sync_token_counts(batch):
+    """Loss normalisers of a row-sharded batch (reference normaliser /root/reference/model/optimize.py:46-50).
+
+    The reference divides the summed loss by the token counts of the WHOLE batch.  With the rows sharded over ranks and the
+    gradients AVERAGED by the all-reduce, every rank must divide its local sums by (global count / world size) for the
+    averaged gradient to equal the single-GPU gradient on the concatenated batch.  This all-reduces the two counts
+    (``ntokens``, ``qntokens``) and keeps ``count / world`` in ``batch.loss_norm`` (a STATIC fp32 [2] device tensor, updated in
+    place so that a captured training step sees the new values); ``SimpleLossCompute.loss`` uses it when present.
+    Without a process group it holds the local counts (world = 1)."""
+    t = torch.stack([batch.ntokens.float(), batch.qntokens.float()])
+    world = 1
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        world = dist.get_world_size()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    norm = getattr(batch, "loss_norm", None)
+    if norm is None or norm.device != t.device:
+        batch.loss_norm = norm = torch.empty(2, dtype=torch.float32, device=t.device)
+    norm.copy_(t / world)
+    return norm
+
+
 _pending = None          # [(work, storage_ptr)] while overlap_grad_allreduce() is active, else None
 
 
@@ -60,7 +81,12 @@ class overlap_grad_allreduce:
             _pending = []
         return self
 
-    def __exit__(self, *exc):
+    def __exit__(self, exc_type, *exc):
+        global _pending
+        if exc_type is not None and _pending is not None:   # backward raised: finish what was started, disarm
+            for work, *_ in _pending:
+                work.wait()
+            _pending = None
         return False
 
 

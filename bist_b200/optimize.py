@@ -61,7 +61,10 @@ class SimpleLossCompute:
         from .decoder import _branch_streams_enabled, _loss_streams
         from .modules import refresh_weight_copies
         pad, eps = self.criterion.padding_idx, self.criterion.smoothing
-        norm, ae_norm = batch.ntokens.float(), batch.qntokens.float()
+        # row-sharded training: dist.sync_token_counts(batch) leaves (global count / world size) in batch.loss_norm, which makes
+        # the all-reduce-averaged gradient equal the reference's single-process one (optimize.py:46-50 on the whole batch)
+        gn = getattr(batch, "loss_norm", None)
+        norm, ae_norm = (gn[0], gn[1]) if gn is not None else (batch.ntokens.float(), batch.qntokens.float())
         keys = self.ae_keys()
         x = ft['decoded_text']
         side = bool(keys) and x.is_cuda and _branch_streams_enabled()

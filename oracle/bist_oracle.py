@@ -220,6 +220,16 @@ def video_path(P, h, fts, encoded_query, query_mask, temporal_mask, n_blocks,
 # SURVEY.md §8 a2).  `cfg` carries the args fields the reference reads: nb_venc_blocks, nb_cenc_blocks,
 # nb_aenc_blocks, enc_vc_combine, include_caption, dec_st_combine, t2s, s2t.  `masks`: trg, his, query, cap, audio,
 # temporal.  Pinned by tests/golden/decoder_*.npz (outputs of the unmodified reference, oracle/make_golden.py).
+def tgifqa_head(ft, query_mask, w, b):
+    """Answer head of BASELINE config 4.  NOT a restatement of reference code: the TGIF-QA branch is not in the tree
+    (/root/reference/README.md:105-106), so this is the build's own spec and parity for it is UNPINNED:
+    masked mean over the query positions of LN(s2t) + LN(t2s) (= temporal_ft + spatial_ft, model/decoder.py:126-129),
+    then Linear(d_model, n_answers)."""
+    m = query_mask.reshape(query_mask.shape[0], -1, 1).to(ft["temporal_ft"].dtype)
+    pooled = ((ft["temporal_ft"] + ft["spatial_ft"]) * m).sum(1) / m.sum(1).clamp_min(1.0)
+    return linear(pooled, w, b)
+
+
 def memory_encoder_layer(P, pre, h, x, mem, self_mask, mem_mask, drop=None):
     """CapEncoderLayer.forward / AudioEncoderLayer.forward: self attention, attention over the memory, FFN."""
     x = sublayer(P, pre + "sublayer.0.", x, lambda z: mha(P, pre + "attn.0.", h, z, z, z, self_mask, drop)[0], drop)
@@ -351,7 +361,7 @@ def embed(P, pre, ids, drop=None, site=None):
     """query_embed = Sequential(Embeddings, PositionalEncoding) (mtn.py:78-80): lut(x) * sqrt(d) + pe, then dropout."""
     lut = P[pre + "0.lut.weight"]
     d = lut.shape[1]
-    x = lut[ids] * math.sqrt(d) + positional_table(ids.shape[1], d).unsqueeze(0)
+    x = lut[ids] * math.sqrt(d) + positional_table(ids.shape[1], d).to(lut.device).unsqueeze(0)
     return _apply(drop, site, x)
 
 
