@@ -80,9 +80,11 @@ class FeatureCache:
                     fts[b, :n].copy_(self.arena[off:off + n], non_blocking=True)
                     if n < T:
                         fts[b, n:].zero_()
-            host_mask = self._mask_stage(B, T)                                                  # pinned, ring of 4
+            host_mask, done = self._mask_stage(B, T)                                            # pinned ring, guarded by events
             torch.lt(torch.arange(T).unsqueeze(0), torch.tensor(lens).unsqueeze(1), out=host_mask)
             mask.copy_(host_mask.unsqueeze(1), non_blocking=True)
+            if done is not None:
+                done.record(torch.cuda.current_stream(mask.device))    # the buffer may be rewritten once this copy has run
         return fts, mask
 
     def _gather(self, vids, fts, T):
@@ -102,11 +104,21 @@ class FeatureCache:
                    "bist_ingest_gather")
 
     def _mask_stage(self, B, T):
-        ring = self.__dict__.setdefault("_stage", {}).setdefault((B, T), [[], 0])
-        if len(ring[0]) < 4:
-            ring[0].append(torch.empty((B, T), dtype=torch.bool, pin_memory=self.arena.is_pinned()))
-        ring[1] = (ring[1] + 1) % 4
-        return ring[0][ring[1] % len(ring[0])]
+        """Next pinned staging buffer for a [B, T] mask and the event that guards it.  The H2D copy of a mask is queued behind
+        the gather kernel and never blocks the host, so a buffer is only reused after the event recorded behind ITS copy
+        has completed (waited for here, on the host) — otherwise batch i could run with batch i+1's mask."""
+        ring = self.__dict__.setdefault("_stage", {}).setdefault((B, T), {"bufs": [], "events": [], "next": 0})
+        pinned = self.arena.is_pinned()
+        if len(ring["bufs"]) < 4:
+            ring["bufs"].append(torch.empty((B, T), dtype=torch.bool, pin_memory=pinned))
+            ring["events"].append(torch.cuda.Event() if pinned and torch.cuda.is_available() else None)
+            i = len(ring["bufs"]) - 1
+        else:
+            i = ring["next"]
+            if ring["events"][i] is not None:
+                ring["events"][i].synchronize()
+        ring["next"] = (i + 1) % 4
+        return ring["bufs"][i], ring["events"][i]
 
 
 class _null:

@@ -76,3 +76,29 @@ def test_bf16_features_through_the_two_byte_projection():
     for k in ("spatiotemporal_ft", "temporal_ft", "spatial_ft"):
         assert O.norm_err(out16[k].float().cpu(), out32[k].float().cpu()) < 1e-2, k     # same math, different kernels
         assert O.norm_err(out16[k].float().cpu(), ref[k]) < 2e-2, k
+
+
+@pytest.mark.gpu
+def test_back_to_back_collates_keep_their_own_masks():
+    """Eight ragged batches collated back to back WITHOUT synchronising in between, behind a long-running kernel on the same
+    stream (so the mask copies are still queued when the next collate rewrites a staging buffer): every batch keeps its own
+    temporal mask (the pinned staging ring is guarded by CUDA events)."""
+    import numpy as np
+    import torch
+    from bist_b200.ingest import FeatureCache
+    rs = np.random.RandomState(3)
+    S, D, T, B, n_vid = 4, 64, 12, 6, 20
+    lens = rs.randint(3, T + 1, size=n_vid)
+    cache = FeatureCache(D, S, int(lens.sum()), dtype=torch.float32)
+    for v in range(n_vid):
+        cache.add(v, rs.uniform(0.1, 1, size=(int(lens[v]), S, D)).astype(np.float32))
+    dev = torch.device("cuda:0")
+    picks = [[int(v) for v in rs.permutation(n_vid)[:B]] for _ in range(8)]
+    torch.cuda.synchronize()
+    torch.cuda._sleep(200_000_000)          # ~0.1 s of GPU spin: everything below queues up behind it
+    outs = [cache.collate(vids, dev, T=T) for vids in picks]
+    torch.cuda.synchronize()
+    for vids, (fts, mask) in zip(picks, outs):
+        want = torch.tensor([[t < lens[v] for t in range(T)] for v in vids])
+        assert torch.equal(mask[:, 0].cpu(), want)
+        assert torch.equal((fts.float().sum((2, 3)) != 0).cpu(), want)
