@@ -1,5 +1,7 @@
 // VidEncoder8.forward, video branch — /root/reference/model/encoder.py:72-80:
 //   out = LayerNorm(relu(fts . W^T + bias)).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace bist {
@@ -46,6 +48,62 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
   g.allow_tf32 = compute_dtype == BIST_BF16;
   BIST_TRY(gemm(g, st));
   return layer_norm(act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                  // :80
+}
+
+
+/* No-allocation variant of the bf16-mode projection.  It has no counterpart in the reference; it was added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  The one piece of scratch the fused kernel needs -- the bf16 copy of W [d, D] -- lives in a
+ * file-scope device array of BIST_VIDPROJ_NOALLOC_MAX_BYTES (2 MiB: d = 512, D = 2048) that every GPU loading the library
+ * holds until exit.  In host code `g_vp_noalloc_scratch` is only a stand-in for the symbol: the device address is taken once
+ * per device with cudaGetSymbolAddress (that device current) and passed to the kernels.  Every call rewrites the whole
+ * [d, D] region it reads, so nothing has to start at zero; all calls share the array, so calls that overlap on the GPU
+ * (different streams, or graphs replayed concurrently) race. */
+static __device__ __align__(256) unsigned char g_vp_noalloc_scratch[BIST_VIDPROJ_NOALLOC_MAX_BYTES];
+
+namespace {
+constexpr int VP_NOALLOC_MAX_DEVICES = 64;
+std::mutex g_vp_noalloc_mu;
+void* g_vp_noalloc_ptr[VP_NOALLOC_MAX_DEVICES] = {};
+
+int vp_noalloc_scratch(void** out) {
+  int dev = -1;
+  BIST_CUDA(cudaGetDevice(&dev));
+  BIST_CHECK_ARG(dev >= 0 && dev < VP_NOALLOC_MAX_DEVICES, "vidproj_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_vp_noalloc_mu);
+  if (!g_vp_noalloc_ptr[dev]) {
+    void* ptr = nullptr;
+    BIST_CUDA(cudaGetSymbolAddress((void**)&ptr, g_vp_noalloc_scratch));   // this device's instance of the array
+    g_vp_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_vp_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+int bist_vidproj_fwd_noalloc(const float* fts, const float* W, const float* bias, const float* a_2, const float* b_2,
+                             void* out, int64_t N, int64_t D, int64_t d, float eps, int out_dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  BIST_CHECK_ARG(fts && W && bias && a_2 && b_2 && out, "vidproj_noalloc: null pointer");
+  BIST_CHECK_ARG(N > 0 && D > 0 && d > 1 && N < (1LL << 31), "vidproj_noalloc: bad shape N=%lld D=%lld d=%lld",
+                 (long long)N, (long long)D, (long long)d);
+  BIST_CHECK_ARG(dtype_ok(out_dtype), "vidproj_noalloc: bad dtype");
+  if ((unsigned long long)d * (unsigned long long)D * 2ull > (unsigned long long)BIST_VIDPROJ_NOALLOC_MAX_BYTES) {
+    set_error("vidproj_noalloc: d*D*2 = %llu bytes of weight scratch exceed the built-in %d-byte array (limit d*D <= %d); "
+              "use bist_vidproj_fwd with a caller-owned workspace", (unsigned long long)d * D * 2ull,
+              (int)BIST_VIDPROJ_NOALLOC_MAX_BYTES, (int)(BIST_VIDPROJ_NOALLOC_MAX_BYTES / 2));
+    return BIST_ERR_WORKSPACE;
+  }
+  void* wb = nullptr;
+  BIST_TRY(vp_noalloc_scratch(&wb));
+  bool taken = false;
+  const int rc = vidproj_fused(fts, W, bias, a_2, b_2, out, N, D, d, eps, wb, out_dtype, st, &taken);
+  if (!taken) {   // the GEMM + LayerNorm pair needs an [N, d] fp32 buffer: not available without a workspace
+    set_error("vidproj_noalloc: shape d=%lld D=%lld is not taken by the fused kernel (needs d %% 64 == 0, d <= 512, D %% 32 == 0, "
+              "16-byte aligned pointers); use bist_vidproj_fwd with a caller-owned workspace", (long long)d, (long long)D);
+    return BIST_ERR_UNSUPPORTED;
+  }
+  return rc;
 }
 
 

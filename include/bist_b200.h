@@ -329,6 +329,16 @@ int bist_vidproj_fwd_bf16in(const void* fts16, const void* W16, const float* bia
                             void* out, int64_t N, int64_t D, int64_t d, float eps, void* ws, size_t ws_bytes,
                             int out_dtype, void* stream);
 
+/* No-allocation variant of bist_vidproj_fwd (bf16 compute).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).
+ * Same inputs, outputs and result as bist_vidproj_fwd(..., compute_dtype = BIST_BF16, ...), but the scratch (the bf16 copy
+ * of W) is a static device array inside the library: d*D*2 <= BIST_VIDPROJ_NOALLOC_MAX_BYTES, else BIST_ERR_WORKSPACE;
+ * shapes the fused kernel does not take (d % 64 != 0, d > 512, D % 32 != 0) return BIST_ERR_UNSUPPORTED.  Calls no
+ * cudaMalloc / cudaFree.  All calls on a device share the array: calls that overlap on the GPU race. */
+#define BIST_VIDPROJ_NOALLOC_MAX_BYTES (2 * 1024 * 1024)
+int bist_vidproj_fwd_noalloc(const float* fts, const float* W, const float* bias, const float* a_2, const float* b_2,
+                             void* out, int64_t N, int64_t D, int64_t d, float eps, int out_dtype, void* stream);
+
 /* n ragged host->device copies (src[i]: page-locked host rows, nbytes[i] to dst_base + dst_off[i]) each followed by the
  * zero fill of that video's padding (pad_nbytes[i] at dst_base + pad_off[i]), all on `stream`: the collate of
  * data/dataset.py:164-174 without a padded host copy. */
