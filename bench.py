@@ -430,9 +430,12 @@ def measure_train(args, env, mod, loss_fn, what, static_batch=None, host_batch=N
     """One training step = forward with tape + loss + backward (ONE CUDA graph: bist_b200/graph.py) + gradient all-reduce
     (NCCL, N > 1) + fused Adam.  With `host_batch`, also the end-to-end step: the whole batch crosses PCIe from pinned host
     memory into the static device batch and the loss comes back, inside the timed region."""
-    from bist_b200.dist import allreduce_grads, overlap_grad_allreduce, sync_token_counts
+    from bist_b200.dist import allreduce_grads, overlap_grad_allreduce, set_grad_comm_dtype, sync_token_counts
     from bist_b200.graph import GraphedTrainStep
     L, dev, world, timed = env["L"], env["dev"], env["world"], env["timed"]
+    # bf16 mode exchanges bf16 gradients (fp32 accumulation inside every rank; BIST_GRAD_COMM=fp32 keeps the wire in fp32)
+    wire_bf16 = args.precision == "bf16" and os.environ.get("BIST_GRAD_COMM", "bf16") == "bf16"
+    set_grad_comm_dtype(torch.bfloat16 if wire_bf16 else torch.float32)
     B = env["rows_per_gpu"]
     plist = list(mod.parameters())
     opt = torch.optim.Adam(plist, lr=1e-4, fused=True)
@@ -479,6 +482,8 @@ def measure_train(args, env, mod, loss_fn, what, static_batch=None, host_batch=N
          "gpu_launches_per_step": int(per_step), "collectives_per_step": ncoll[0],
          "launch": "eager" if args.no_graph else ("cuda_graph(fwd+loss+bwd%s) + fused Adam" % (" + all-reduce" if world > 1 and gstep and gstep.collectives else "")),
          "what": what}
+    if world > 1:
+        r["grad_comm_dtype"] = "bf16" if wire_bf16 else "fp32"
     if clocks:
         r["clocks"] = clocks
     if host_batch is not None:

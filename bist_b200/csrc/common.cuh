@@ -306,6 +306,17 @@ int stage1_fused(const void* vft, const uint8_t* tmask, int nd, const int* kinds
                  const float* const* bv, void* const* c1, int64_t B, int64_t T, int64_t S, int64_t Lq, int64_t d, int64_t h,
                  float* dbg, cudaStream_t st);
 
+// ---- query side of the BiST layer in three kernels (qside.cu; bf16, d_k = 64, h even, Lq <= 16, d_ff % 256 == 0) ---------------
+// Host arrays of per-direction device pointers; see qside.cu for layouts.
+bool qside_supported(int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h);
+int qside_attn(const float* const* x_in, const float* const* ln_a, const float* const* ln_b, const void* const* wqkv, const float* const* bqkv,
+               const uint8_t* qmask, void* ctx, int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
+int qside_fold(const float* x, const float* const* ln1_a, const float* const* ln1_b, const float* const* ln2_a, const float* const* ln2_b,
+               const void* const* wq, const float* const* bq, const void* const* wkt, void* qf, void* xv2, int nd, int64_t B, int64_t Lq,
+               int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
+int qside_ffn1(const float* ts, const float* const* ln_a, const float* const* ln_b, const void* const* w1, const float* const* b1, void* ffh,
+               int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
+
 // ---- weight packing helpers ------------------------------------------------------------------
 // dst[r, c] = scale * src[r, c] (transpose = 0) or scale * src[c, r] (transpose = 1); dst is
 // [rows, cols] dense of dst_dtype, src fp32 dense.

@@ -304,6 +304,21 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   // whose stride is the pointer difference (zero when both are ft['encoded_query'], decoder.py:109-110)
   const long long in_dir = nd == 2 ? (long long)(x_in[1] - x_in[0]) : 0;
   const long long out_dir = nd == 2 ? (long long)(x_out[1] - x_out[0]) : 0;
+  // bf16 mode at the shapes the fused stage 1 takes: the query-side chain runs as three kernels that normalise their fp32 rows
+  // themselves and finish with the attention / fold / ReLU epilogue (qside.cu) instead of ten launches.
+  const bool fusedq = fused1 && s2mma && qside_supported(B, Lq, d, dff, h);
+  const float *lnA[4][2], *lnB[4][2], *bq0[2], *bq12[2], *bf1[2];
+  const void *wq0[2], *wq12[2], *wkt[2], *wf1[2];
+  for (int u = 0; u < nd; ++u) {
+    const float* fu = fs + (size_t)u * L.fdir_stride;
+    for (int i = 0; i < 4; ++i) { lnA[i][u] = fu + L.ln_a + (size_t)i * d; lnB[i][u] = fu + L.ln_b + (size_t)i * d; }
+    bq0[u] = fu + L.bqkv0; bq12[u] = fu + L.bq12x; bf1[u] = fu + L.b1;
+    const char* mu = mat + (size_t)u * L.dir_stride * e;
+    wq0[u] = mu + L.wqkv0 * e; wq12[u] = mu + L.wq12x * e; wkt[u] = mu + L.wkt12 * e; wf1[u] = mu + L.w1 * e;
+  }
+  if (fusedq) {
+    BIST_TRY(qside_attn(x_in, lnA[0], lnB[0], wq0, bq0, query_mask, W.cbuf, nd, B, Lq, d, dff, h, eps, st));
+  } else {
   BIST_TRY(layer_norm(x_in[0], fs + L.ln_a, fs + L.ln_b, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd, in_dir, true));
   BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0));
   {
@@ -329,12 +344,16 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       BIST_TRY(softmax_pv(a, st));
     }
   }
+  }
   // output projection + residual with the layer inputs (modules.py:44)
   BIST_TRY(lin(W.cbuf, Qd, L.wo0, L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir));
 
   // ---- query side of stage 1 and stage 2 in three launches ------------------------------------------------------
   // n12x = [LN1(x) | LN2(x) | x] (encoder.py:121,130 / :148,161 norm the same x with different gains)
   void* xcopy = act(W.n12x, 2 * nd * Qd);
+  if (fusedq) {
+    BIST_TRY(qside_fold(W.x, lnA[1], lnB[1], lnA[2], lnB[2], wq12, bq12, wkt, W.qf12, act(W.q12x, 2 * nd * Qd), nd, B, Lq, d, dff, h, eps, st));
+  } else {
   BIST_TRY(layer_norm2(W.x, fs + L.ln_a + d, fs + L.ln_b + d, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.n12x,
                        act(W.n12x, nd * Qd), xcopy, (int64_t)nd * Q, d, eps, adt, st, Q, fsd));
   {
@@ -365,6 +384,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       g.Z = 2 * nd * hi;
       BIST_TRY(gemm(g, st));
     }
+  }
   }
 
   // ---- stage 1 (encoder.py:111-121 / :143-148) ------------------------------------------------------
@@ -488,8 +508,12 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd));
 
   // ---- feed-forward (encoder.py:134-135 / :165-166) -----------------------------------------------
-  BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
-  BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0));
+  if (fusedq) {
+    BIST_TRY(qside_ffn1(W.ts, lnA[3], lnB[3], wf1, bf1, W.ffh, nd, B, Lq, d, dff, h, eps, st));
+  } else {
+    BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
+    BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0));
+  }
   BIST_TRY(lin(W.ffh, (long long)Q * dff, L.w2, L.b2, x_out[0], out_dir, BIST_F32, di, (int)dff, 0, W.ts, Qd));
   return 0;
 }

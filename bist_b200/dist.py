@@ -66,7 +66,28 @@ def sync_token_counts(batch):
     return norm
 
 
-_pending = None          # [(work, storage_ptr)] while overlap_grad_allreduce() is active, else None
+_pending = None          # [(work, storage_ptr, block, need_div, wire)] while overlap_grad_allreduce() is active, else None
+_comm_dtype = torch.float32
+_wire_cache = {}
+
+
+def set_grad_comm_dtype(dtype):
+    """Element type the gradients cross NVLink in.  ``torch.float32`` (default): the fp32 gradient blocks are reduced in place.
+    ``torch.bfloat16``: each block is cast into a persistent bf16 wire buffer, that buffer is all-reduced (half the bytes) and
+    the result is written back over the fp32 block — the accumulation inside every rank stays fp32, only the exchanged
+    values are rounded (what bf16-mode training does with every activation anyway).  bench.py selects bf16 for bf16 mode."""
+    global _comm_dtype
+    assert dtype in (torch.float32, torch.bfloat16)
+    _comm_dtype = dtype
+
+
+def _wire(numel, device, slot):
+    "Persistent wire buffer (one per slot = per call site / block, so that captured graphs keep valid addresses)."
+    key = (slot, numel, str(device))
+    buf = _wire_cache.get(key)
+    if buf is None:
+        buf = _wire_cache[key] = torch.empty(numel, dtype=torch.bfloat16, device=device)
+    return buf
 
 
 class overlap_grad_allreduce:
@@ -100,8 +121,12 @@ def grad_block_ready(block, average=True):
     if _pending is None:
         return
     op = _reduce_op() if average else dist.ReduceOp.SUM
-    work = dist.all_reduce(block, op=op, async_op=True)
-    _pending.append((work, block.untyped_storage().data_ptr(), block, average and op == dist.ReduceOp.SUM))
+    wire = None
+    if _comm_dtype == torch.bfloat16 and block.dtype == torch.float32 and dist.get_backend() == "nccl":
+        wire = _wire(block.numel(), block.device, ("block", len(_pending)))   # blocks arrive in the same order every step
+        wire.copy_(block.reshape(-1))
+    work = dist.all_reduce(block if wire is None else wire, op=op, async_op=True)
+    _pending.append((work, block.untyped_storage().data_ptr(), block, average and op == dist.ReduceOp.SUM, wire))
 
 
 def allreduce_grads(params, average=True):
@@ -123,8 +148,10 @@ def allreduce_grads(params, average=True):
     div = average and op == dist.ReduceOp.SUM
     started = {}
     n = 0
-    for work, sp, block, need_div in (_pending or []):
+    for work, sp, block, need_div, wire in (_pending or []):
         work.wait()
+        if wire is not None:
+            block.reshape(-1).copy_(wire)
         if need_div:
             block.div_(world)
         started[sp] = True
@@ -154,7 +181,16 @@ def allreduce_grads(params, average=True):
         # every block and every stand-alone gradient in place, as ONE grouped NCCL launch (ncclGroupStart/End)
         tensors = flats + [g for g in loose if g.is_contiguous()]
         odd = [g for g in loose if not g.is_contiguous()]
-        if tensors:
+        if tensors and _comm_dtype == torch.bfloat16 and all(t.dtype == torch.float32 for t in tensors):
+            # one bf16 wire buffer for everything that is left: cast in (one multi-tensor launch), ONE all-reduce, cast back
+            sizes = [t.numel() for t in tensors]
+            wire = _wire(sum(sizes), tensors[0].device, ("rest", len(tensors)))
+            views = [v.view_as(t) for v, t in zip(torch.split(wire, sizes), tensors)]
+            torch._foreach_copy_(views, tensors)
+            dist.all_reduce(wire, op=op)
+            torch._foreach_copy_(tensors, views)
+            n += 1
+        elif tensors:
             with dist._coalescing_manager(device=tensors[0].device, async_ops=False):
                 for t in tensors:
                     dist.all_reduce(t, op=op)

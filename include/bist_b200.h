@@ -375,6 +375,11 @@ int bist_genloss_fwd_bwd(void* Z, float* logp, int n_ptr, const float* const* P,
                          const int64_t* target, float* row_loss, int64_t R, int64_t V, int64_t Lt, int64_t pad,
                          float smoothing, int want_grad, int dtype, void* stream);
 
+/* Test switch for the fused query-side kernels of bist_st_layer_fwd (csrc/qside.cu: LN0 + QKV + self-attention, LN1/LN2 + Q
+ * projections + key folds, LN3 + first FFN layer — encoder.py:176-201 on the query rows): 0 = the separate launches,
+ * 1 = fused where supported (bf16, d_k = 64, h even, Lq <= 16, d_ff % 256 == 0), -1 = default (on unless BIST_QSIDE_UNFUSED). */
+int bist_debug_qside(int on);
+
 /* Stage 1 of temporal2spatial / spatial2temporal for up to two directions as ONE launch (bf16; the video tensor is read
  * once per launch, projected values and scores stay on chip) — encoder.py:109-121 (t2s) and :143-148 (s2t), attention()
  * of modules.py:54-64.  bist_st_layer_fwd calls it when bist_stage1_fused_supported(); exported for the kernel-level tests.
