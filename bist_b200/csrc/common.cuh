@@ -210,6 +210,7 @@ struct GemmArgs {
   const void* A = nullptr;  // [M,K] rows via `a`, K contiguous
   const void* W = nullptr;  // [N,K] rows via `w`, K contiguous
   void* C = nullptr;        // [M,N] rows via `c`, N contiguous
+  void* C2 = nullptr;       // optional bf16 copy of the output at the same element offsets as C (tensor-core path only)
   const float* bias = nullptr;  // [N] fp32 or null
   const void* R = nullptr;      // residual rows via `r`, N contiguous, or null
   int M = 0, N = 0, K = 0;
@@ -309,12 +310,12 @@ int stage1_fused(const void* vft, const uint8_t* tmask, int nd, const int* kinds
 // ---- query side of the BiST layer in three kernels (qside.cu; bf16, d_k = 64, h even, Lq <= 16, d_ff % 256 == 0) ---------------
 // Host arrays of per-direction device pointers; see qside.cu for layouts.
 bool qside_supported(int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h);
-int qside_attn(const float* const* x_in, const float* const* ln_a, const float* const* ln_b, const void* const* wqkv, const float* const* bqkv,
-               const uint8_t* qmask, void* ctx, int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
-int qside_fold(const float* x, const float* const* ln1_a, const float* const* ln1_b, const float* const* ln2_a, const float* const* ln2_b,
+int qside_attn(const void* xn, const void* const* wqkv, const float* const* bqkv, const uint8_t* qmask, void* ctx, int nd, int64_t B,
+               int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
+int qside_fold(const void* xb, const float* const* ln1_a, const float* const* ln1_b, const float* const* ln2_a, const float* const* ln2_b,
                const void* const* wq, const float* const* bq, const void* const* wkt, void* qf, void* xv2, int nd, int64_t B, int64_t Lq,
                int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
-int qside_ffn1(const float* ts, const float* const* ln_a, const float* const* ln_b, const void* const* w1, const float* const* b1, void* ffh,
+int qside_ffn1(const void* tsb, const float* const* ln_a, const float* const* ln_b, const void* const* w1, const float* const* b1, void* ffh,
                int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st);
 
 // ---- weight packing helpers ------------------------------------------------------------------

@@ -188,6 +188,7 @@ bool mult4(long long v) { return (v & 3) == 0; }
 
 int gemm_simt(const GemmArgs& g, cudaStream_t st) {
   BIST_CHECK_ARG(g.A && g.W && g.C, "gemm: null operand");
+  BIST_CHECK_ARG(!g.C2, "gemm: the bf16 output copy is only written by the tensor-core kernel (shape declined)");
   BIST_CHECK_ARG(g.M > 0 && g.N > 0 && g.K > 0 && g.Z > 0 && g.zin > 0, "gemm: bad shape M=%d N=%d K=%d Z=%d",
                  g.M, g.N, g.K, g.Z);
   BIST_CHECK_ARG(g.Z <= 65535 && (g.M + 63) / 64 <= 65535, "gemm: grid too large");

@@ -260,6 +260,11 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
             for (int rr = 0; rr < 8; ++rr)
               if (ok_r[rr]) st4(reinterpret_cast<float*>(g.C) + co_r[rr] + cc, v[rr]);
           }
+          if (g.C2) {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              if (ok_r[rr]) st4(reinterpret_cast<__nv_bfloat16*>(g.C2) + co_r[rr] + cc, v[rr]);
+          }
         } else {
           const int cc = col + lane;
           const float bv = (bias && cc < Ntot) ? bias[cc] : 0.f;
@@ -275,6 +280,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
                             : reinterpret_cast<const float*>(g.R)[ro + cc];
               if (c_bf16) reinterpret_cast<__nv_bfloat16*>(g.C)[co + cc] = __float2bfloat16_rn(v);
               else reinterpret_cast<float*>(g.C)[co + cc] = v;
+              if (g.C2) reinterpret_cast<__nv_bfloat16*>(g.C2)[co + cc] = __float2bfloat16_rn(v);
             }
           }
         }

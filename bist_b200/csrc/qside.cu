@@ -31,7 +31,8 @@ constexpr int QS_RING_BYTES = 96 * 1024;
 constexpr int QS_OFF_A2 = QS_OFF_RING + 64 * 1024;   // FOLD: the head pair's projected queries (2 x 16 KB) behind a 4 x 16 KB ring
 constexpr int QS_OFF_BAR = QS_OFF_RING + QS_RING_BYTES;
 constexpr int QS_MAXST = 4;
-constexpr int QS_SMEM = QS_OFF_BAR + 256;
+constexpr int QS_OFF_BIAS = QS_OFF_BAR + 256;       // 512 floats: the unit's bias slice, fetched while the main product runs
+constexpr int QS_SMEM = QS_OFF_BIAS + 2048;
 static_assert(QS_SMEM <= 227 * 1024, "qside: shared memory budget");
 // ATTN epilogue scratch inside the dead A region
 constexpr int QS_KV_ROW = 256;                       // 64 fp32 per row
@@ -44,7 +45,6 @@ template <> struct QsCfg<QS_FOLD> { static constexpr int NB = 128, STAGES = 4; }
 template <> struct QsCfg<QS_FFN1> { static constexpr int NB = 256, STAGES = 3; };
 
 struct QsArgs {
-  const float* x[2];         // per direction: fp32 rows [B*Lq, d]
   const float* ln_a[2][2];   // [direction][which] LayerNorm gain / bias (FOLD: which = 0, 1; others: [u][0])
   const float* ln_b[2][2];
   const float* bias[2];      // per direction: ATTN [3][d] (q | k | v); FOLD [3][d] (q1 | q2 | raw-x value term); FFN1 [dff]
@@ -52,12 +52,19 @@ struct QsArgs {
   int nd, B, Lq, d, h, dff, nks, tpd;   // tpd: tiles per direction = ceil(B / 8)
   int nlong;                 // FOLD: units that run the fold (the rest are the short raw-x units)
   float eps, scale;          // scale = 1 / sqrt(d_k)
+  float inv_d, inv_dm1;      // 1 / d, 1 / (d - 1)
   int trace;
 };
 __device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define QTRACE(ev) do { if (p.trace && tslot >= 0) g_qtrace[MODE][tslot][ev] = gtimer(); } while (0)
 
 // ---- PTX ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
@@ -96,7 +103,7 @@ __device__ __forceinline__ void stage_bf16_32(uint32_t row_addr, int row, int c0
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; i += 4) {
-      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + 8 * c + i));
+      const float4 b = *reinterpret_cast<const float4*>(bias + 8 * c + i);
       v[i] = __uint_as_float(r[8 * c + i]) + b.x; v[i + 1] = __uint_as_float(r[8 * c + i + 1]) + b.y;
       v[i + 2] = __uint_as_float(r[8 * c + i + 2]) + b.z; v[i + 3] = __uint_as_float(r[8 * c + i + 3]) + b.w;
     }
@@ -112,7 +119,8 @@ template <int MODE>
 __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ CUtensorMap map_b0, const __grid_constant__ CUtensorMap map_b1,
                                                        const __grid_constant__ CUtensorMap map_c0, const __grid_constant__ CUtensorMap map_c1,
                                                        const __grid_constant__ CUtensorMap map_o0, const __grid_constant__ CUtensorMap map_o1,
-                                                       const __grid_constant__ CUtensorMap map_o2, const QsArgs p) {
+                                                       const __grid_constant__ CUtensorMap map_o2, const __grid_constant__ CUtensorMap map_a,
+                                                       const QsArgs p) {
   constexpr int NB = QsCfg<MODE>::NB, ST = QsCfg<MODE>::STAGES, SLAB = NB * 128;
   static_assert(ST * SLAB <= QS_RING_BYTES && ST <= QS_MAXST, "qside: ring");
   pdl_trigger();
@@ -125,7 +133,8 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
   uint64_t* a2_full = acc_full + 1;           // FOLD: projected queries of the head pair staged (8 warp arrivals)
   uint64_t* d2_full = a2_full + 1;            // [3] FOLD: a 128-column chunk of folded queries is in TMEM
   uint64_t* d2_empty = d2_full + 3;           // [3] (8 warp arrivals)
-  uint32_t* tmem_slot = (uint32_t*)(d2_empty + 3);
+  uint64_t* a_land = d2_empty + 3;            // the bf16 rows of the tile have landed (TMA)
+  uint32_t* tmem_slot = (uint32_t*)(a_land + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nks = p.nks, d = p.d;
   const int tslot = (threadIdx.x & 31) != 0 ? -1 : blockIdx.x < 2 ? (int)blockIdx.x : blockIdx.x + 2 >= gridDim.x ? (int)(blockIdx.x + 4 - gridDim.x) : -1;
@@ -148,7 +157,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
   if ((smem_u32(smem) & 1023u) != 0u) __trap();
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < QS_MAXST; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
-    mbar_init(a_full, 8); mbar_init(acc_full, 1); mbar_init(a2_full, 8);
+    mbar_init(a_full, 8); mbar_init(acc_full, 1); mbar_init(a2_full, 8); mbar_init(a_land, 1);
     for (int s = 0; s < 3; ++s) { mbar_init(&d2_full[s], 1); mbar_init(&d2_empty[s], 8); }
     fence_barrier_init();
   }
@@ -162,7 +171,12 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
   if (warp == 2) QTRACE(2);
 
   if (warp == 0) {
-    // ---- B-operand producer ------------------------------------------------------------------------------------------------------
+    // ---- A tile (8 samples x 16 token slots x d of the bf16 rows; slots >= Lq and samples >= B are zero-filled), then the B ring ----
+    if (elect_one()) {
+      mbar_expect_tx(a_land, (uint32_t)(nks * QS_ASLAB));
+      for (int ks = 0; ks < nks; ++ks) tma_load_4d(smem + QS_OFF_A + ks * QS_ASLAB, &map_a, a_land, ks * 64, 0, b0, u);
+    }
+    __syncwarp();
     int it = 0;
     for (int ks = 0; ks < nks; ++ks, ++it) {
       const int s = it % ST;
@@ -260,36 +274,51 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
     // ================================ worker warps ==================================================================================
     const int w8 = warp - 2;                      // 0..7: during the LayerNorm, warp w8 owns sample slot w8 (16 token rows)
     {
-      const bool do_ln = !(MODE == QS_FOLD && which == 2);
-      const int lw = MODE == QS_FOLD ? (which & 1) : 0;
-      const int nj = d >> 7;                      // float4s per lane per row
-      const int b = b0 + w8;
-      const float* xs = p.x[u] + (long long)b * p.Lq * d + 4 * lane;
-      const uint32_t a_lane = smem_u32(smem + QS_OFF_A) + (uint32_t)((lane >> 4) * QS_ASLAB + (lane & 1) * 8);
-      const int chunk = (lane & 15) >> 1;
-      const float* gap = p.ln_a[u][lw] + 4 * lane;
-      const float* gbp = p.ln_b[u][lw] + 4 * lane;
-      // four rows at a time, the next four already in flight (a row is 2 KB from L2 / HBM: the loads are latency, not bandwidth)
-      auto load4 = [&](float4 (&v)[4][4], int l0) {
+      // LayerNorm IN PLACE on the landed tile (modules.py:28-31: unbiased std, eps on the std; statistics in fp32): warp w8 owns
+      // sample slot w8; a lane holds chunk (lane & 7) of k-slabs (lane >> 3) and (lane >> 3) + 4 of a row = 16 values.
+      const bool do_ln = MODE == QS_FFN1 || (MODE == QS_FOLD && which < 2);
+      mbar_wait(a_land, 0);
+      if (warp == 2) QTRACE(8);
+      if (do_ln && b0 + w8 < p.B) {
+        const int lw = MODE == QS_FOLD ? (which & 1) : 0;
+        const int chunk = lane & 7, sl0 = lane >> 3;
+        const bool on0 = sl0 < nks, on1 = sl0 + 4 < nks;
+        float ga[16], gb[16];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const bool valid = b < p.B && l0 + i < p.Lq;
+        for (int t = 0; t < 2; ++t) {
+          const int col = (sl0 + 4 * t) * 64 + chunk * 8;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            v[i][j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (valid && j < nj) v[i][j] = __ldg(reinterpret_cast<const float4*>(xs + (long long)(l0 + i) * d + 128 * j));
+          for (int i = 0; i < 8; i += 4) {
+            float4 a4 = make_float4(0.f, 0.f, 0.f, 0.f), b4 = a4;
+            if (t ? on1 : on0) { a4 = __ldg(reinterpret_cast<const float4*>(p.ln_a[u][lw] + col + i)); b4 = __ldg(reinterpret_cast<const float4*>(p.ln_b[u][lw] + col + i)); }
+            ga[8 * t + i] = a4.x; ga[8 * t + i + 1] = a4.y; ga[8 * t + i + 2] = a4.z; ga[8 * t + i + 3] = a4.w;
+            gb[8 * t + i] = b4.x; gb[8 * t + i + 1] = b4.y; gb[8 * t + i + 2] = b4.z; gb[8 * t + i + 3] = b4.w;
           }
         }
-      };
-      auto emit4 = [&](float4 (&v)[4][4], int l0) {
-        float inv[4];
-        if (do_ln) {
-          float s[4], ss[4];
+        const uint32_t abase = smem_u32(smem + QS_OFF_A) + (uint32_t)(sl0 * QS_ASLAB);
+        if (warp == 2) QTRACE(9);
+#pragma unroll 1
+        for (int l0 = 0; l0 < p.Lq; l0 += 4) {     // four rows at a time: their reductions interleave
+          float x[4][16], s[4], ss[4];
+          uint32_t ra[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
+            const int r = w8 * 16 + ((l0 + i) & 15);   // (slots past Lq hold zeros: computed with the others, never stored)
+            ra[i] = abase + (uint32_t)(r * 128 + ((chunk ^ (r & 7)) << 4));
+            uint32_t w[8];
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              w[4 * t] = w[4 * t + 1] = w[4 * t + 2] = w[4 * t + 3] = 0u;
+              if (t ? on1 : on0)
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[4 * t]), "=r"(w[4 * t + 1]), "=r"(w[4 * t + 2]), "=r"(w[4 * t + 3])
+                             : "r"(ra[i] + (uint32_t)(4 * t * QS_ASLAB)) : "memory");
+            }
             s[i] = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) s[i] += (v[i][j].x + v[i][j].y) + (v[i][j].z + v[i][j].w);
+            for (int j = 0; j < 8; ++j) {
+              x[i][2 * j] = __uint_as_float(w[j] << 16); x[i][2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+              s[i] += x[i][2 * j] + x[i][2 * j + 1];
+            }
           }
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1)
@@ -297,14 +326,12 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
             for (int i = 0; i < 4; ++i) s[i] += __shfl_xor_sync(0xffffffffu, s[i], o);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float mean = s[i] / (float)d;
+            const float mean = s[i] * p.inv_d;
             ss[i] = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (j < nj) {
-                v[i][j].x -= mean; v[i][j].y -= mean; v[i][j].z -= mean; v[i][j].w -= mean;
-                ss[i] += (v[i][j].x * v[i][j].x + v[i][j].y * v[i][j].y) + (v[i][j].z * v[i][j].z + v[i][j].w * v[i][j].w);
-              }
+            for (int j = 0; j < 16; ++j) {
+              x[i][j] -= mean;
+              if (j < 8 ? on0 : on1) ss[i] = fmaf(x[i][j], x[i][j], ss[i]);
             }
           }
 #pragma unroll
@@ -312,45 +339,44 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
 #pragma unroll
             for (int i = 0; i < 4; ++i) ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], o);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) inv[i] = 1.f / (sqrtf(ss[i] / (float)(d - 1)) + p.eps);   // modules.py:30-31
-        }
+          for (int i = 0; i < 4; ++i) {
+            if (l0 + i >= p.Lq) continue;         // zero slots stay zero
+            // (MUFU-based square root and reciprocal: the IEEE routines are subroutine calls that serialise the four rows; the
+            //  result is rounded to bf16 anyway)
+            const float var = ss[i] * p.inv_dm1;
+            const float inv = __fdividef(1.f, var * rsqrtf(fmaxf(var, 1e-30f)) + p.eps);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (j < nj) {
-            float4 ga = make_float4(1.f, 1.f, 1.f, 1.f), gb = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (do_ln) { ga = __ldg(reinterpret_cast<const float4*>(gap + 128 * j)); gb = __ldg(reinterpret_cast<const float4*>(gbp + 128 * j)); }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int r = w8 * 16 + l0 + i;
-              const bool valid = b < p.B && l0 + i < p.Lq;
-              float4 y = v[i][j];
-              if (do_ln) {
-                y.x = fmaf(ga.x * inv[i], y.x, gb.x); y.y = fmaf(ga.y * inv[i], y.y, gb.y);
-                y.z = fmaf(ga.z * inv[i], y.z, gb.z); y.w = fmaf(ga.w * inv[i], y.w, gb.w);
-              }
-              if (!valid) y = make_float4(0.f, 0.f, 0.f, 0.f);
-              // column 4*lane + 128*j -> k-slab 2j + (lane >> 4), 16-byte chunk ((lane & 15) >> 1) ^ (r & 7), 8-byte half lane & 1
-              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a_lane + (uint32_t)(2 * j * QS_ASLAB + r * 128 + ((chunk ^ (r & 7)) << 4))),
-                           "r"(pack2(y.x, y.y)), "r"(pack2(y.z, y.w)) : "memory");
-            }
+            for (int t = 0; t < 2; ++t)
+              if (t ? on1 : on0)
+                st_shared_v4(ra[i] + (uint32_t)(4 * t * QS_ASLAB),
+                             pack2(fmaf(ga[8 * t] * inv, x[i][8 * t], gb[8 * t]), fmaf(ga[8 * t + 1] * inv, x[i][8 * t + 1], gb[8 * t + 1])),
+                             pack2(fmaf(ga[8 * t + 2] * inv, x[i][8 * t + 2], gb[8 * t + 2]), fmaf(ga[8 * t + 3] * inv, x[i][8 * t + 3], gb[8 * t + 3])),
+                             pack2(fmaf(ga[8 * t + 4] * inv, x[i][8 * t + 4], gb[8 * t + 4]), fmaf(ga[8 * t + 5] * inv, x[i][8 * t + 5], gb[8 * t + 5])),
+                             pack2(fmaf(ga[8 * t + 6] * inv, x[i][8 * t + 6], gb[8 * t + 6]), fmaf(ga[8 * t + 7] * inv, x[i][8 * t + 7], gb[8 * t + 7])));
           }
         }
-      };
-      {
-        float4 va[4][4], vb[4][4];
-        load4(va, 0);
-        load4(vb, 4);
-        emit4(va, 0);
-        load4(va, 8);
-        emit4(vb, 4);
-        load4(vb, 12);
-        emit4(va, 8);
-        emit4(vb, 12);
+        if (warp == 2) QTRACE(10);
+        fence_proxy_async_smem();
       }
-      fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(a_full);
       if (warp == 2) QTRACE(3);
+    }
+    // ---- the unit's bias slice -> shared memory (the epilogue would otherwise wait for global loads after the product is done) ----
+    float* sbias = reinterpret_cast<float*>(smem + QS_OFF_BIAS);
+    {
+      const int t = threadIdx.x - 64;   // 0..255
+      if (MODE == QS_ATTN) { if (t < 192) sbias[t] = __ldg(p.bias[u] + (t >> 6) * d + sub * 64 + (t & 63)); }
+      else if (MODE == QS_FFN1) sbias[t] = __ldg(p.bias[u] + sub * 256 + t);
+      else if (fold) { if (t < 128) sbias[t] = __ldg(p.bias[u] + which * d + sub * 128 + t); }
+      else { for (int i = t; i < d; i += 256) sbias[i] = __ldg(p.bias[u] + 2 * d + i); }
+      bar_sync(3, 256);
+    }
+    uint32_t mask_bits = 0;   // ATTN: key mask of this thread's sample (query_mask[b, j] == 0 -> -1e9), one bit per token slot
+    if (MODE == QS_ATTN) {
+      const int mrow = (warp & 3) * 32 + lane, mb_ = b0 + (mrow >> 4);
+      const bool keep = mb_ < p.B && (mrow & 15) < p.Lq && p.qmask[(long long)mb_ * p.Lq + (mrow & 15)] != 0;
+      mask_bits = (__ballot_sync(0xffffffffu, keep) >> (16 * (lane >> 4))) & 0xffffu;
     }
     // ---- epilogues: two warps per TMEM lane quarter -------------------------------------------------------------------------------
     const int q = warp & 3, ch = w8 >> 2;
@@ -371,7 +397,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t r[32];
           tmem_ld32(tlane + (uint32_t)(box * 64 + hf * 32), r);
-          stage_bf16_32(ra, row, hf * 4, r, p.bias[u] + sub * 256 + box * 64 + hf * 32, true);
+          stage_bf16_32(ra, row, hf * 4, r, sbias + box * 64 + hf * 32, true);
         }
       }
       fence_proxy_async_smem();
@@ -396,7 +422,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t r[32];
           tmem_ld32(tlane + (uint32_t)(c * 128 + ch * 64 + hf * 32), r);
-          stage_bf16_32(box + (uint32_t)(row * 128), row, hf * 4, r, p.bias[u] + 2 * d + c * 128 + ch * 64 + hf * 32, false);
+          stage_bf16_32(box + (uint32_t)(row * 128), row, hf * 4, r, sbias + c * 128 + ch * 64 + hf * 32, false);
         }
         fence_proxy_async_smem();
         bar_sync(1 + ch, 128);
@@ -411,7 +437,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t r[32];
           tmem_ld32(tlane + (uint32_t)(ch * 64 + hf * 32), r);
-          stage_bf16_32(ra, row, hf * 4, r, p.bias[u] + which * d + sub * 128 + ch * 64 + hf * 32, false);
+          stage_bf16_32(ra, row, hf * 4, r, sbias + ch * 64 + hf * 32, false);
         }
         fence_proxy_async_smem();
         __syncwarp();
@@ -459,7 +485,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
       const int sl = row >> 4;
       const uint32_t kv_row = (uint32_t)(row * QS_KV_ROW + sl * 16);
       const uint32_t kbase = stg + QS_OFF_K, vbase = stg + QS_OFF_V, pbase = stg + QS_OFF_P + (uint32_t)(row * 64);
-      const float* bq = p.bias[u] + sub * 64;
+      const float* bq = sbias;
       float qv[64];             // both warps of a lane quarter hold the token's scaled query: each scores half of the keys
 #pragma unroll
       for (int hf = 0; hf < 2; ++hf) {
@@ -467,7 +493,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
         tmem_ld32(tlane + (uint32_t)(hf * 32), r);
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bq + hf * 32 + 4 * c));
+          const float4 b4 = *reinterpret_cast<const float4*>(bq + hf * 32 + 4 * c);
           qv[hf * 32 + 4 * c] = (__uint_as_float(r[4 * c]) + b4.x) * p.scale; qv[hf * 32 + 4 * c + 1] = (__uint_as_float(r[4 * c + 1]) + b4.y) * p.scale;
           qv[hf * 32 + 4 * c + 2] = (__uint_as_float(r[4 * c + 2]) + b4.z) * p.scale; qv[hf * 32 + 4 * c + 3] = (__uint_as_float(r[4 * c + 3]) + b4.w) * p.scale;
         }
@@ -476,20 +502,19 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
       for (int hf = 0; hf < 2; ++hf) {          // ch 0 stages k, ch 1 stages v
         uint32_t r[32];
         tmem_ld32(tlane + (uint32_t)(64 + ch * 64 + hf * 32), r);
-        const float* bb = bq + (1 + ch) * d + hf * 32;
+        const float* bb = bq + (1 + ch) * 64 + hf * 32;
         const uint32_t dst = (ch ? vbase : kbase) + kv_row + (uint32_t)(hf * 128);
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bb + 4 * c));
+          const float4 b4 = *reinterpret_cast<const float4*>(bb + 4 * c);
           asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16 * c), "f"(__uint_as_float(r[4 * c]) + b4.x),
                        "f"(__uint_as_float(r[4 * c + 1]) + b4.y), "f"(__uint_as_float(r[4 * c + 2]) + b4.z), "f"(__uint_as_float(r[4 * c + 3]) + b4.w) : "memory");
         }
       }
-      // key mask of the sample (query_mask[b, j] == 0 -> -1e9), one bit per token slot
-      const int b = b0 + sl;
-      const bool keep = b < p.B && (row & 15) < p.Lq && p.qmask[(long long)b * p.Lq + (row & 15)] != 0;
-      const uint32_t bits = (__ballot_sync(0xffffffffu, keep) >> (16 * (lane >> 4))) & 0xffffu;
+      const uint32_t bits = mask_bits;
+      if (warp == 2) QTRACE(11);
       bar_sync(1, 256);
+      if (warp == 2) QTRACE(12);
       {
         // raw scores of keys ch*8 .. ch*8+7 (four independent partial sums per key)
         float sc[8];
@@ -514,6 +539,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
           asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(pbase + (uint32_t)(ch * 32 + 16 * c)), "f"(sc[4 * c]), "f"(sc[4 * c + 1]),
                        "f"(sc[4 * c + 2]), "f"(sc[4 * c + 3]) : "memory");
       }
+      if (warp == 2) QTRACE(13);
       bar_sync(1, 256);
       {
         // softmax over the sample's keys (both warps, redundantly), then ctx[token, ch*32 .. +32) = sum_j p_j v_j
@@ -528,7 +554,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
         float sum = 0.f;
 #pragma unroll
         for (int j = 0; j < 16; ++j) { pj[j] = j < p.Lq ? __expf(pj[j] - mx) : 0.f; sum += pj[j]; }
-        const float inv = 1.f / sum;
+        const float inv = __fdividef(1.f, sum);
         float o[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0.f;
@@ -551,6 +577,7 @@ __global__ void __launch_bounds__(320, 1) qside_kernel(const __grid_constant__ C
           st_shared_v4(ra + (uint32_t)((((ch * 4 + c) ^ row) & 7) << 4), pack2(o[8 * c], o[8 * c + 1]), pack2(o[8 * c + 2], o[8 * c + 3]),
                        pack2(o[8 * c + 4], o[8 * c + 5]), pack2(o[8 * c + 6], o[8 * c + 7]));
       }
+      if (warp == 2) QTRACE(14);
       fence_proxy_async_smem();
       bar_sync(1, 256);
       if (leader && ch == 0) tma_store_4d(&map_o0, stg + QS_OFF_CTX, sub * 64, 0, b0, u);   // ctx[(u, b, l), head*64 ..)
@@ -597,7 +624,7 @@ int qside_launch(const CUtensorMap* maps, const QsArgs& p, int grid, const char*
   cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(320); cfg.dynamicSmemBytes = QS_SMEM; cfg.stream = st;
   cfg.attrs = at; cfg.numAttrs = 1;
   ProfScope ps(tag, st);
-  BIST_CUDA(cudaLaunchKernelEx(&cfg, qside_kernel<MODE>, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], maps[6], p));
+  BIST_CUDA(cudaLaunchKernelEx(&cfg, qside_kernel<MODE>, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], maps[6], maps[7], p));
   BIST_LAUNCHED();
   return 0;
 }
@@ -606,6 +633,7 @@ int qs_common(QsArgs& p, int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, 
   BIST_CHECK_ARG(qside_supported(B, Lq, d, dff, h) && (nd == 1 || nd == 2), "qside: unsupported shape");
   p.nd = nd; p.B = (int)B; p.Lq = (int)Lq; p.d = (int)d; p.h = (int)h; p.dff = (int)dff; p.nks = (int)(d / 64);
   p.tpd = (int)((B + 7) / 8); p.eps = eps; p.scale = 1.f / sqrtf((float)(d / h));
+  p.inv_d = 1.f / (float)d; p.inv_dm1 = 1.f / (float)(d - 1);
   static const bool trace = getenv("BIST_QSIDE_TRACE") != nullptr;
   p.trace = trace ? 1 : 0;
   return 0;
@@ -624,38 +652,39 @@ bool qside_supported(int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h) {
   return true;
 }
 
-// LN0 + QKV projection + masked self-attention of the query tokens -> ctx [nd][B*Lq][d] bf16 (encoder.py:176 / :184).
-// x_in[u]: fp32 [B*Lq, d]; wqkv[u]: packed bf16 [3][d][d]; bqkv[u]: fp32 [3][d].
-int qside_attn(const float* const* x_in, const float* const* ln_a, const float* const* ln_b, const void* const* wqkv, const float* const* bqkv,
-               const uint8_t* qmask, void* ctx, int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st) {
+// QKV projection + masked self-attention of the query tokens -> ctx [nd][B*Lq][d] bf16 (encoder.py:176 / :184).
+// xn: bf16 [nd][B*Lq][d] normalised layer inputs; wqkv[u]: packed bf16 [3][d][d]; bqkv[u]: fp32 [3][d].
+int qside_attn(const void* xn, const void* const* wqkv, const float* const* bqkv, const uint8_t* qmask, void* ctx, int nd, int64_t B,
+               int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st) {
   QsArgs p = {};
   BIST_TRY(qs_common(p, nd, B, Lq, d, dff, h, eps));
-  CUtensorMap maps[7];
+  CUtensorMap maps[8];
   for (int u = 0; u < 2; ++u) {
     const int v = u < nd ? u : 0;
-    BIST_CHECK_ARG(x_in[v] && ln_a[v] && ln_b[v] && wqkv[v] && bqkv[v] && qmask && ctx, "qside_attn: null pointer");
-    p.x[u] = x_in[v]; p.ln_a[u][0] = ln_a[v]; p.ln_b[u][0] = ln_b[v]; p.bias[u] = bqkv[v];
+    BIST_CHECK_ARG(xn && wqkv[v] && bqkv[v] && qmask && ctx, "qside_attn: null pointer");
+    p.bias[u] = bqkv[v];
     BIST_TRY(make_map_2d(&maps[u], wqkv[v], false, d, 3 * d, 64, 64, 128));
   }
   p.qmask = qmask;
   BIST_TRY(make_map_rows(&maps[4], ctx, d, Lq, B, nd));
+  BIST_TRY(make_map_rows(&maps[7], xn, d, Lq, B, nd));
   maps[2] = maps[3] = maps[0]; maps[5] = maps[6] = maps[4];
   return qside_launch<QS_ATTN>(maps, p, nd * p.tpd * (int)h, "qside_attn", st);
 }
 
 // LN1 / LN2 + stage-1 / stage-2 query projections + key folds -> qf [2][nd][B*Lq][h][d] bf16, and the raw-x value term
-// x . W_v2^T + b -> xv2 [nd][B*Lq][d] bf16.  x: fp32 [nd][B*Lq][d]; wq[u]: packed bf16 [3][d][d] (W_q1 | W_q2 | W_v2); bq[u]: fp32
-// [3][d]; wkt[u]: packed bf16 [2][d][d], row n = output feature of the fold, column = head*64 + k (pre-scaled by 1/sqrt(dk)).
-int qside_fold(const float* x, const float* const* ln1_a, const float* const* ln1_b, const float* const* ln2_a, const float* const* ln2_b,
+// x . W_v2^T + b -> xv2 [nd][B*Lq][d] bf16.  xb: bf16 copy of x [nd][B*Lq][d] (the statistics are taken in fp32 from the bf16
+// values); wq[u]: packed bf16 [3][d][d] (W_q1 | W_q2 | W_v2); bq[u]: fp32 [3][d]; wkt[u]: packed bf16 [2][d][d], row n = output
+// feature of the fold, column = head*64 + k (pre-scaled by 1/sqrt(dk)).
+int qside_fold(const void* xb, const float* const* ln1_a, const float* const* ln1_b, const float* const* ln2_a, const float* const* ln2_b,
                const void* const* wq, const float* const* bq, const void* const* wkt, void* qf, void* xv2, int nd, int64_t B, int64_t Lq,
                int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st) {
   QsArgs p = {};
   BIST_TRY(qs_common(p, nd, B, Lq, d, dff, h, eps));
-  CUtensorMap maps[7];
+  CUtensorMap maps[8];
   for (int u = 0; u < 2; ++u) {
     const int v = u < nd ? u : 0;
-    BIST_CHECK_ARG(x && ln1_a[v] && ln1_b[v] && ln2_a[v] && ln2_b[v] && wq[v] && bq[v] && wkt[v] && qf && xv2, "qside_fold: null pointer");
-    p.x[u] = x + (long long)v * B * Lq * d;
+    BIST_CHECK_ARG(xb && ln1_a[v] && ln1_b[v] && ln2_a[v] && ln2_b[v] && wq[v] && bq[v] && wkt[v] && qf && xv2, "qside_fold: null pointer");
     p.ln_a[u][0] = ln1_a[v]; p.ln_b[u][0] = ln1_b[v]; p.ln_a[u][1] = ln2_a[v]; p.ln_b[u][1] = ln2_b[v];
     p.bias[u] = bq[v];
     BIST_TRY(make_map_2d(&maps[u], wq[v], false, d, 3 * d, 64, 128, 128));
@@ -668,23 +697,25 @@ int qside_fold(const float* x, const float* const* ln1_a, const float* const* ln
     BIST_TRY(make_map_nd(&maps[4 + w], (const char*)qf + (size_t)w * nd * B * Lq * h * d * 2, 5, dims, strides, box));
   }
   BIST_TRY(make_map_rows(&maps[6], xv2, d, Lq, B, nd));
+  BIST_TRY(make_map_rows(&maps[7], xb, d, Lq, B, nd));
   p.nlong = nd * p.tpd * 2 * (int)(h / 2);
   return qside_launch<QS_FOLD>(maps, p, p.nlong + nd * p.tpd, "qside_fold", st);
 }
 
-// LN3 + first feed-forward layer: ffh [nd][B*Lq][dff] bf16 = relu(LN(ts) . W_1^T + b_1) (modules.py:113).
-int qside_ffn1(const float* ts, const float* const* ln_a, const float* const* ln_b, const void* const* w1, const float* const* b1, void* ffh,
+// LN3 + first feed-forward layer: ffh [nd][B*Lq][dff] bf16 = relu(LN(ts) . W_1^T + b_1) (modules.py:113); tsb: bf16 copy of ts.
+int qside_ffn1(const void* tsb, const float* const* ln_a, const float* const* ln_b, const void* const* w1, const float* const* b1, void* ffh,
                int nd, int64_t B, int64_t Lq, int64_t d, int64_t dff, int64_t h, float eps, cudaStream_t st) {
   QsArgs p = {};
   BIST_TRY(qs_common(p, nd, B, Lq, d, dff, h, eps));
-  CUtensorMap maps[7];
+  CUtensorMap maps[8];
   for (int u = 0; u < 2; ++u) {
     const int v = u < nd ? u : 0;
-    BIST_CHECK_ARG(ts && ln_a[v] && ln_b[v] && w1[v] && b1[v] && ffh, "qside_ffn1: null pointer");
-    p.x[u] = ts + (long long)v * B * Lq * d; p.ln_a[u][0] = ln_a[v]; p.ln_b[u][0] = ln_b[v]; p.bias[u] = b1[v];
+    BIST_CHECK_ARG(tsb && ln_a[v] && ln_b[v] && w1[v] && b1[v] && ffh, "qside_ffn1: null pointer");
+    p.ln_a[u][0] = ln_a[v]; p.ln_b[u][0] = ln_b[v]; p.bias[u] = b1[v];
     BIST_TRY(make_map_2d(&maps[u], w1[v], false, d, dff, 64, 256, 128));
   }
   BIST_TRY(make_map_rows(&maps[4], ffh, dff, Lq, B, nd));
+  BIST_TRY(make_map_rows(&maps[7], tsb, d, Lq, B, nd));
   maps[2] = maps[3] = maps[0]; maps[5] = maps[6] = maps[4];
   return qside_launch<QS_FFN1>(maps, p, nd * p.tpd * (int)(dff / 256), "qside_ffn1", st);
 }

@@ -260,9 +260,9 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
 
   // Batched (over the active directions) linear layer  C[u] = act(A[u] . W[u]^T + b[u]) (+ R[u]).
   auto lin = [&](const void* Ain, long long a_dir, size_t w_off, size_t b_off, void* Cout, long long c_dir, int c_dtype,
-                 int N, int K, int relu, const float* R, long long r_dir) {
+                 int N, int K, int relu, const float* R, long long r_dir, void* C2 = nullptr) {
     GemmArgs g;
-    g.A = Ain; g.W = Mw(w_off); g.C = Cout; g.bias = fs + b_off; g.R = R;
+    g.A = Ain; g.W = Mw(w_off); g.C = Cout; g.bias = fs + b_off; g.R = R; g.C2 = C2;
     g.M = Q; g.N = N; g.K = K;
     g.a = rows_dense(K); g.w = rows_dense(K); g.c = rows_dense(N); g.r = rows_dense(N);
     g.Z = nd; g.zin = 1;
@@ -316,10 +316,10 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     const char* mu = mat + (size_t)u * L.dir_stride * e;
     wq0[u] = mu + L.wqkv0 * e; wq12[u] = mu + L.wq12x * e; wkt[u] = mu + L.wkt12 * e; wf1[u] = mu + L.w1 * e;
   }
-  if (fusedq) {
-    BIST_TRY(qside_attn(x_in, lnA[0], lnB[0], wq0, bq0, query_mask, W.cbuf, nd, B, Lq, d, dff, h, eps, st));
-  } else {
   BIST_TRY(layer_norm(x_in[0], fs + L.ln_a, fs + L.ln_b, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd, in_dir, true));
+  if (fusedq) {
+    BIST_TRY(qside_attn(W.nbuf, wq0, bq0, query_mask, W.cbuf, nd, B, Lq, d, dff, h, eps, st));
+  } else {
   BIST_TRY(lin(W.nbuf, Qd, L.wqkv0, L.bqkv0, W.qkv0, 3 * Qd, adt, 3 * di, di, 0, nullptr, 0));
   {
     bool fused = false;
@@ -346,13 +346,14 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   }
   }
   // output projection + residual with the layer inputs (modules.py:44)
-  BIST_TRY(lin(W.cbuf, Qd, L.wo0, L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir));
+  // (the fused chain also takes a bf16 copy of x: its kernels load their rows by TMA and normalise them in shared memory)
+  BIST_TRY(lin(W.cbuf, Qd, L.wo0, L.bo0, W.x, Qd, BIST_F32, di, di, 0, x_in[0], in_dir, fusedq ? act(W.n12x, 2 * nd * Qd) : nullptr));
 
   // ---- query side of stage 1 and stage 2 in three launches ------------------------------------------------------
   // n12x = [LN1(x) | LN2(x) | x] (encoder.py:121,130 / :148,161 norm the same x with different gains)
   void* xcopy = act(W.n12x, 2 * nd * Qd);
   if (fusedq) {
-    BIST_TRY(qside_fold(W.x, lnA[1], lnB[1], lnA[2], lnB[2], wq12, bq12, wkt, W.qf12, act(W.q12x, 2 * nd * Qd), nd, B, Lq, d, dff, h, eps, st));
+    BIST_TRY(qside_fold(xcopy, lnA[1], lnB[1], lnA[2], lnB[2], wq12, bq12, wkt, W.qf12, act(W.q12x, 2 * nd * Qd), nd, B, Lq, d, dff, h, eps, st));
   } else {
   BIST_TRY(layer_norm2(W.x, fs + L.ln_a + d, fs + L.ln_b + d, fs + L.ln_a + 2 * d, fs + L.ln_b + 2 * d, W.n12x,
                        act(W.n12x, nd * Qd), xcopy, (int64_t)nd * Q, d, eps, adt, st, Q, fsd));
@@ -505,11 +506,11 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.r_dtype = adt; g.tag = "vfold2_gemm";
     BIST_TRY(gemm(g, st));
   }
-  BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd));
+  BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd, fusedq ? W.nbuf : nullptr));
 
   // ---- feed-forward (encoder.py:134-135 / :165-166) -----------------------------------------------
   if (fusedq) {
-    BIST_TRY(qside_ffn1(W.ts, lnA[3], lnB[3], wf1, bf1, W.ffh, nd, B, Lq, d, dff, h, eps, st));
+    BIST_TRY(qside_ffn1(W.nbuf, lnA[3], lnB[3], wf1, bf1, W.ffh, nd, B, Lq, d, dff, h, eps, st));
   } else {
     BIST_TRY(layer_norm(W.ts, fs + L.ln_a + 3 * d, fs + L.ln_b + 3 * d, W.nbuf, (int64_t)nd * Q, d, eps, BIST_F32, adt, st, Q, fsd));
     BIST_TRY(lin(W.nbuf, Qd, L.w1, L.b1, W.ffh, (long long)Q * dff, adt, (int)dff, di, 1, nullptr, 0));

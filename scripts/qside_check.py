@@ -18,18 +18,18 @@ b = synth.make_batch(1, B, T, S, D, Lq).to(dev)
 eq = synth.make_encoded_query(1, B, Lq, d).to(dev)
 L = _lib.lib()
 with torch.no_grad():
-    for _ in range(3):
+    for _ in range(200):          # long enough for the SM clock to ramp: the stamps of the LAST pass are read
         model(b, eq)
 torch.cuda.synchronize()
 buf = (ctypes.c_longlong * (3 * 4 * 16))()
 assert L.bist_debug_qside_trace(buf) == 0
 names = ["attn", "fold", "ffn1"]
-ev = ["start", "setup", "prev_done", "ln_done", "acc_full", "epi_done", "stores", "exit"]
+ev = ["start", "setup", "prev_done", "ln_done", "acc_full", "epi_done", "stores", "exit", "a_land", "gains", "ln_loop", "attn_staged", "attn_bar", "attn_scores", "attn_pv", "-"]
 for m in range(3):
     t0 = min(buf[(m * 4 + s) * 16] for s in range(4) if buf[(m * 4 + s) * 16])
     for s in range(4):
-        row = [buf[(m * 4 + s) * 16 + e] for e in range(8)]
-        print("%-5s cta-slot %d: " % (names[m], s) + "  ".join("%s %6d" % (ev[e], row[e] - t0) for e in range(8)))
+        row = [buf[(m * 4 + s) * 16 + e] for e in range(16)]
+        print("%-5s cta-slot %d: " % (names[m], s) + "  ".join("%s %6d" % (ev[e], row[e] - t0) for e in sorted(range(15), key=lambda e: row[e]) if row[e]))
 L.bist_prof_enable(1)
 with torch.no_grad():
     for _ in range(5):
