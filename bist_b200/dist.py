@@ -8,6 +8,7 @@ training step, ONE gradient all-reduce per step (`allreduce_grads`).
 import torch
 import torch.distributed as dist
 
+from . import arena as _arena
 from .synth import SynthBatch, shard_rows
 
 
@@ -126,7 +127,8 @@ def grad_block_ready(block, average=True):
         wire = _wire(block.numel(), block.device, ("block", len(_pending)))   # blocks arrive in the same order every step
         wire.copy_(block.reshape(-1))
     work = dist.all_reduce(block if wire is None else wire, op=op, async_op=True)
-    _pending.append((work, block.untyped_storage().data_ptr(), block, average and op == dist.ReduceOp.SUM, wire))
+    _pending.append((work, (block.data_ptr(), block.data_ptr() + block.numel() * block.element_size()), block,
+                     average and op == dist.ReduceOp.SUM, wire))
 
 
 def allreduce_grads(params, average=True):
@@ -146,24 +148,27 @@ def allreduce_grads(params, average=True):
     world = dist.get_world_size()
     op = _reduce_op() if average else dist.ReduceOp.SUM
     div = average and op == dist.ReduceOp.SUM
-    started = {}
+    started = []             # address ranges already reduced by overlap_grad_allreduce
     n = 0
-    for work, sp, block, need_div, wire in (_pending or []):
+    for work, rng, block, need_div, wire in (_pending or []):
         work.wait()
         if wire is not None:
             block.reshape(-1).copy_(wire)
         if need_div:
             block.div_(world)
-        started[sp] = True
+        started.append(rng)
         n += 1
     _pending = None
-    blocks, loose = {}, []
+    blocks, loose, runs = {}, [], []
     for p in params:
         g = p.grad
         if g is None:
             continue
         st = g.untyped_storage()
-        if st.data_ptr() in started:
+        if any(lo <= g.data_ptr() < hi for lo, hi in started):
+            continue
+        if g.dtype == torch.float32 and g.is_contiguous() and _arena.owns(g):
+            runs.append(g)       # carved from the step's gradient arena: merged into contiguous runs below
             continue
         if g.dtype == torch.float32 and g.is_contiguous() and st.nbytes() > g.numel() * 4:
             blocks.setdefault(st.data_ptr(), [st, 0, []])
@@ -172,6 +177,20 @@ def allreduce_grads(params, average=True):
         else:
             loose.append(g)
     flats = []
+    if runs:
+        # neighbours in the arena (gaps are alignment padding, which is zero on every rank) become ONE flat tensor per run
+        runs.sort(key=lambda g: g.data_ptr())
+        base = runs[0].untyped_storage()
+        lo = hi = None
+        for g in runs:
+            a, b = g.data_ptr(), g.data_ptr() + g.numel() * 4
+            if hi is not None and a - hi <= 1024 and not any(x < a and y > hi for x, y in started):
+                hi = max(hi, b)
+                continue
+            if hi is not None:
+                flats.append(torch.empty(0, dtype=torch.float32, device=g.device).set_(base, (lo - base.data_ptr()) // 4, ((hi - lo) // 4,)))
+            lo, hi = a, b
+        flats.append(torch.empty(0, dtype=torch.float32, device=runs[0].device).set_(base, (lo - base.data_ptr()) // 4, ((hi - lo) // 4,)))
     for st, covered, gs in blocks.values():
         if covered == st.nbytes():           # the storage holds nothing but these gradients: reduce it in place
             flats.append(torch.empty(0, dtype=torch.float32, device=gs[0].device).set_(st, 0, (st.nbytes() // 4,)))

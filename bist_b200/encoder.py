@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from . import arena as _arena
 from . import dist as _dist
 from .modules import (LayerNorm, SublayerConnection, clones, _needs_grad, _ws, _WEIGHT_EPOCH,
                       _reg_hook, weights_updated)
@@ -95,8 +96,8 @@ class _VidProjFn(torch.autograd.Function):
             acc = g_out.float().reshape(N, d) if acc is None else acc.add_(g_out.float().reshape(acc.shape))
         if acc is None:
             return (None,) * 8
-        dW = torch.zeros_like(W)
-        vec = torch.zeros((3, d), dtype=torch.float32, device=W.device)
+        dW = _arena.zeros(tuple(W.shape), W.device)
+        vec = _arena.zeros((3, d), W.device)
         L = _lib.lib()
         ws = _ws(L.bist_vidproj_bwd_workspace_bytes(N, D, d, ctx.cdt), W.device)
         _lib.check(L.bist_vidproj_bwd(_lib.ptr(acc), _lib.ptr(fts), _lib.ptr(tape), tape.numel(), _lib.ptr(a_2), _lib.ptr(dW),
@@ -180,7 +181,7 @@ class _StLayerFn(torch.autograd.Function):
         L = _lib.lib()
         if total != L.bist_st_layer_grad_elems(d, d_ff, nd):
             raise RuntimeError("gradient block layout mismatch between bist_b200/encoder.py and libbist_b200.so")
-        grads = torch.zeros(total, dtype=torch.float32, device=vft.device)
+        grads = _arena.zeros(total, vft.device)
         ws = _ws(L.bist_st_layer_bwd_workspace_bytes(B, T, S, Lq, d, d_ff, h, nd, vdt), vft.device)
         _lib.check(L.bist_st_layer_bwd(_lib.ptr(g_t2s), _lib.ptr(g_s2t), _lib.ptr(x_t2s), _lib.ptr(x_s2t), _lib.ptr(vft),
                                        _lib.ptr(qm), _lib.ptr(tm), _lib.ptr(packed), _lib.ptr(tape), tape.numel(),

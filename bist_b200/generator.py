@@ -15,6 +15,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from . import arena as _arena
 from .modules import _BF16Cache, _LinearFn, _ptr_array
 
 
@@ -100,7 +101,7 @@ class _GenLossFn(torch.autograd.Function):
         dZ = (dZ * g.to(dZ.dtype)).contiguous()
         ET = ctx.cache.get(E, x.dtype, transposed=True)                                          # [d, V]
         dx = torch.empty_like(x)
-        dE = torch.zeros_like(E, dtype=torch.float32)
+        dE = _arena.zeros(tuple(E.shape), E.device)
         _lib.check(_lib.lib().bist_linear_bwd(_lib.ptr(dZ), _lib.ptr(x), _lib.ptr(ET), _lib.ptr(dx), _lib.ptr(dE), None, R,
                                               V, d, dt, dt, dt, dt, _lib.stream_ptr()), "bist_linear_bwd")
         d_sw = (dsw * g).view(B, Lt, -1) if ctx.has_sw else None

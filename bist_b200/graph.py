@@ -15,6 +15,7 @@ costs one launch on the host instead of several hundred.  Three things make a re
 import torch
 
 from . import _lib
+from . import arena as _arena
 from .modules import weights_updated
 
 
@@ -43,6 +44,13 @@ class GraphedTrainStep:
                 loss.backward()
             self.collectives = _dist.allreduce_grads(self.params)
 
+        def step_once():
+            # every zero-initialised gradient block of the step is carved from one arena: ONE memset per step (arena.py)
+            with _arena.step(dev):
+                loss = loss_fn()
+                backward(loss)
+            return loss
+
         self.params = [p for p in params if p.requires_grad]
         dev = self.params[0].device
         _lib.require_cuda(self.params[0])
@@ -55,7 +63,7 @@ class GraphedTrainStep:
             for _ in range(max(1, warmup)):            # sets kernel attributes, warms the allocator
                 for p in self.params:
                     p.grad = None
-                backward(loss_fn())
+                step_once()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         for p in self.params:
@@ -64,8 +72,7 @@ class GraphedTrainStep:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.counter.add_(1)
-            self.loss = loss_fn()
-            backward(self.loss)
+            self.loss = step_once()
         weights_updated()                              # the copies made during capture are not valid eager caches
 
     def __call__(self):

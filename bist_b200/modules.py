@@ -21,6 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from . import arena as _arena
 
 
 def clones(module, N):
@@ -53,8 +54,8 @@ class _LayerNormFn(torch.autograd.Function):
         gy = gy.contiguous()
         d = x.shape[-1]
         dx = torch.empty_like(x)
-        da = torch.zeros_like(a_2, dtype=torch.float32)
-        db = torch.zeros_like(a_2, dtype=torch.float32)
+        dab = _arena.zeros((2,) + tuple(a_2.shape), a_2.device)
+        da, db = dab[0], dab[1]
         _lib.check(_lib.lib().bist_ln_bwd(_lib.ptr(gy), _lib.ptr(x), _lib.ptr(a_2), _lib.ptr(dx), _lib.ptr(da),
                                           _lib.ptr(db), x.numel() // d, d, ctx.eps, _lib.dtype_code(gy.dtype),
                                           _lib.dtype_code(x.dtype), _lib.dtype_code(dx.dtype), _lib.stream_ptr()),
@@ -300,7 +301,7 @@ class _MhaFn(torch.autograd.Function):
         PT, keep = mod._param_struct(dt, transposed=True)
         # one flat fp32 block for the eight parameter gradients (one all-reduce per module, dist.allreduce_grads)
         nw, nb = d * d_in, (d, d, d, d_in)
-        block = torch.zeros(4 * nw + sum(nb), dtype=torch.float32, device=query.device)
+        block = _arena.zeros(4 * nw + sum(nb), query.device)
         dW = [block[i * nw:(i + 1) * nw] for i in range(4)]
         db, off = [], 4 * nw
         for n in nb:
@@ -347,7 +348,7 @@ class _FfnFn(torch.autograd.Function):
         w1T = ctx.mod._bf16.get(ctx.mod.w_1.weight, x.dtype, transposed=True)
         w2T = ctx.mod._bf16.get(ctx.mod.w_2.weight, x.dtype, transposed=True)
         o1, o2, o3 = d_ff * d, d_ff * d + d_ff, d_ff * d + d_ff + d_out * d_ff
-        block = torch.zeros(o3 + d_out, dtype=torch.float32, device=x.device)     # one block: one all-reduce per module
+        block = _arena.zeros(o3 + d_out, x.device)     # one block: one all-reduce per module
         dW1, db1, dW2, db2 = block[:o1], block[o1:o2], block[o2:o3], block[o3:]
         dx = torch.empty_like(x) if ctx.needs_input_grad[1] else None
         ws = _ws(rows * d_ff * x.element_size() + 256, x.device)
@@ -543,7 +544,7 @@ class _LinearFn(torch.autograd.Function):
         gy = gy.to(x.dtype).contiguous()
         wT = ctx.cache.get(weight, x.dtype, transposed=True)
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        block = torch.zeros(N * K + N, dtype=torch.float32, device=x.device)
+        block = _arena.zeros(N * K + N, x.device)
         _lib.check(_lib.lib().bist_linear_bwd(_lib.ptr(gy), _lib.ptr(x), _lib.ptr(wT), _lib.ptr(dx), _lib.ptr(block),
                                               _lib.ptr(block[N * K:]), M, N, K, dt, dt, dt, dt, _lib.stream_ptr()),
                    "bist_linear_bwd")
@@ -616,7 +617,7 @@ class _EmbedFn(torch.autograd.Function):
         (ids,) = ctx.saved_tensors
         V, d, p_drop, seed = ctx.cfg
         gy = gy.contiguous()
-        dlut = torch.zeros((V, d), dtype=torch.float32, device=gy.device)
+        dlut = _arena.zeros((V, d), gy.device)
         _lib.check(_lib.lib().bist_embed_bwd(_lib.ptr(ids), _lib.ptr(gy), _lib.ptr(dlut), ids.numel(), d, p_drop, seed,
                                              SITE_EMBED, _lib.dtype_code(gy.dtype), _lib.stream_ptr()), "bist_embed_bwd")
         return None, dlut, None, None, None, None
