@@ -77,9 +77,9 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const VpSmem L = vp_smem(p.d, NCTA);
   uint64_t* afull = (uint64_t*)(smem + L.bar_off);  // fp32 A slab landed
-  uint64_t* aempty = afull + VP_MAX_A;              // fp32 A slab converted (8 worker-warp arrivals)
+  uint64_t* aempty = afull + VP_MAX_A;              // fp32 A slab converted (4 worker-warp arrivals: one conversion group)
   uint64_t* wfull = aempty + VP_MAX_A;              // bf16 W slab landed
-  uint64_t* conv = wfull + VP_STAGES;               // bf16 A written (8 worker-warp arrivals per CTA, counted at the leader)
+  uint64_t* conv = wfull + VP_STAGES;               // bf16 A written (4 worker-warp arrivals per CTA, counted at the leader)
   uint64_t* empty = conv + VP_STAGES;               // UMMAs that read the MMA-ring slot have completed
   uint64_t* acc_full = empty + VP_STAGES;
   uint64_t* acc_empty = acc_full + 1;
@@ -97,8 +97,8 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   const int wrows = nmma / NCTA;                         // W rows per UMMA held by this CTA
 
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < VP_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 8); }
-    for (int s = 0; s < VP_STAGES; ++s) { mbar_init(&wfull[s], 1); mbar_init(&conv[s], 8 * NCTA); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < VP_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 4); }
+    for (int s = 0; s < VP_STAGES; ++s) { mbar_init(&wfull[s], 1); mbar_init(&conv[s], 4 * NCTA); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
     mbar_init(acc_empty, 8 * NCTA);
     fence_barrier_init();
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   } else {
     // ================================ worker warps =====================================================
     const int wt = threadIdx.x - 64;                 // 0..255
-    const int crow = wt >> 1, chalf = wt & 1;        // conversion: row of the slab, which 16 of its 32 k
+    const int crow = wt & 127, cgrp = wt >> 7;       // conversion: row of the slab; the group takes slabs it % 2 == cgrp
     const int lg = warp & 3, ch = (warp - 2) >> 2;   // epilogue: TMEM lane quarter, column half
     const int hcols = d >> 1;                        // columns per half (multiple of 32)
     const uint32_t stg = smem_u32(smem + L.stg_off) + (uint32_t)((warp - 2) * 32 * VP_STG_LD * 4);
@@ -195,36 +195,35 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
     const uint32_t stg_w = stg + (uint32_t)(lane * VP_STG_LD * 4);
     const uint32_t stg_r = stg + (uint32_t)((sub_r * VP_STG_LD + sub_c) * 4);
     float* red = (float*)(smem + L.red_off);         // [2][128][3]
-    int it = 0, tc_ = 0, sa = 0, pa = 0;
+    int it = 0, tc_ = 0;
     for (int u = unit0; u < units; u += ustep, ++tc_) {
       const int tile = NCTA * u + rank;
-      // ---- main loop: fp32 slab -> bf16 slab ------------------------------------------------------------
+      // ---- main loop: fp32 slab -> bf16 slab.  The two groups of four warps take alternate slabs (a thread converts one row of
+      //      its slab), so a slab's wait -> load -> convert -> store -> fence -> arrive chain has two slab periods to complete in
+      //      instead of one: with all eight warps on every slab that chain, not the tensor core, set the pace.
       for (int kb = 0; kb < p.nkb; ++kb, ++it) {
-        const int s = it % L.ms;
+        if ((it & 1) != cgrp) continue;
+        const int s = it % L.ms, sa = it % L.na, pa = (it / L.na) & 1;
         mbar_wait(&afull[sa], pa);
         if (warp == 2 && lane == 0) VTRACE(2, it);
         const uint32_t af = smem_u32(smem + sa * VP_AF) + (uint32_t)(crow * 128);
         const uint32_t ab = smem_u32(smem + L.mma_off + s * L.stage_bytes) + (uint32_t)(crow * 64);
-        float4 v[4];
+        uint32_t pk[16];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {   // logical 16-byte chunk 4*chalf + j of a SWIZZLE_128B row
-          const uint32_t a = af + (uint32_t)((((4 * chalf + j) ^ (crow & 7))) << 4);
-          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[j].x), "=f"(v[j].y), "=f"(v[j].z), "=f"(v[j].w) : "r"(a) : "memory");
-        }
-        uint32_t pk[8];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          __nv_bfloat162 lo = __floats2bfloat162_rn(v[j].x, v[j].y), hi = __floats2bfloat162_rn(v[j].z, v[j].w);
+        for (int j = 0; j < 8; ++j) {   // logical 16-byte chunk j of a SWIZZLE_128B row
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(af + (uint32_t)((j ^ (crow & 7)) << 4)) : "memory");
+          __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
           pk[2 * j] = *reinterpret_cast<uint32_t*>(&lo);
           pk[2 * j + 1] = *reinterpret_cast<uint32_t*>(&hi);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&aempty[sa]);     // the fp32 slot is in registers: the next slab may land
-        if (++sa == L.na) { sa = 0; pa ^= 1; }
         mbar_wait(&empty[s], ((it / L.ms) & 1) ^ 1);   // the UMMAs that read this bf16 slot have retired
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {  // logical 16-byte chunk 2*chalf + jj of a SWIZZLE_64B row
-          const uint32_t a = ab + (uint32_t)((((2 * chalf + jj) ^ ((crow >> 1) & 3))) << 4);
+        for (int jj = 0; jj < 4; ++jj) {  // logical 16-byte chunk jj of a SWIZZLE_64B row
+          const uint32_t a = ab + (uint32_t)((jj ^ ((crow >> 1) & 3)) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pk[4 * jj]), "r"(pk[4 * jj + 1]),
                        "r"(pk[4 * jj + 2]), "r"(pk[4 * jj + 3])
                        : "memory");
