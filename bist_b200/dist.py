@@ -5,6 +5,8 @@ LayerNorm is per row — so the path shards by rows with NO data-path collective
 bookkeeping (the max-over-ranks step time of bench.py and, in tests, gathering the shards back) and, for the
 training step, ONE gradient all-reduce per step (`allreduce_grads`).
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -82,13 +84,38 @@ def set_grad_comm_dtype(dtype):
     _comm_dtype = dtype
 
 
-def _wire(numel, device, slot):
+def _wire(numel, device, slot, dtype=torch.bfloat16):
     "Persistent wire buffer (one per slot = per call site / block, so that captured graphs keep valid addresses)."
-    key = (slot, numel, str(device))
+    key = (slot, numel, str(device), dtype)
     buf = _wire_cache.get(key)
     if buf is None:
-        buf = _wire_cache[key] = torch.empty(numel, dtype=torch.bfloat16, device=device)
+        buf = _wire_cache[key] = torch.empty(numel, dtype=dtype, device=device)
     return buf
+
+
+# Buckets: the decoder-side modules (attention, feed-forward) hand in their gradient blocks as their backward is enqueued; blocks
+# of the SAME stream (autograd runs a node's backward on its forward's stream, and the model's branches live on different streams)
+# are packed into one wire buffer and all-reduced as soon as BIST_GRAD_BUCKET_MB of them are there, so the transfer runs beside the
+# rest of the backward instead of after it.  0 (the default) disables bucketing: everything left goes in the final launch.
+# Measured on 8 B200 (config 3 with audio, bf16 wire): 24 MB buckets 11.86 ms, 48 MB 11.90 ms, none 11.94 ms per step, while the
+# end-to-end step (host batches prefetched over PCIe during the backward) went from 14.9 to 16.2 ms — so it stays opt-in.
+_BUCKET_BYTES = int(float(os.environ.get("BIST_GRAD_BUCKET_MB", "0")) * (1 << 20))
+_buckets = {}
+
+
+def _flush_bucket(sid):
+    blocks = _buckets.pop(sid, None)
+    if not blocks:
+        return
+    op = _reduce_op()
+    flat = [b.reshape(-1) for b in blocks]
+    sizes = [b.numel() for b in flat]
+    wire = _wire(sum(sizes), flat[0].device, ("bucket", len(_pending)), _comm_dtype)
+    views = list(torch.split(wire, sizes))
+    torch._foreach_copy_(views, flat)
+    work = dist.all_reduce(wire, op=op, async_op=True)
+    rng = [(b.data_ptr(), b.data_ptr() + b.numel() * b.element_size()) for b in flat]
+    _pending.append((work, rng, flat, op == dist.ReduceOp.SUM, views))
 
 
 class overlap_grad_allreduce:
@@ -109,6 +136,7 @@ class overlap_grad_allreduce:
             for work, *_ in _pending:
                 work.wait()
             _pending = None
+            _buckets.clear()
         return False
 
 
@@ -117,9 +145,19 @@ def _reduce_op():
     return dist.ReduceOp.AVG if dist.get_backend() == "nccl" else dist.ReduceOp.SUM
 
 
-def grad_block_ready(block, average=True):
-    """Called by the layer backward (encoder.py) with its freshly written gradient block."""
+def grad_block_ready(block, average=True, bucket=False):
+    """Called by a backward (encoder.py, modules.py) with its freshly written gradient block.  ``bucket=True``: a small block
+    that is collected with its stream's other blocks (see above); else the block is all-reduced on its own right away."""
     if _pending is None:
+        return
+    if bucket:
+        if _BUCKET_BYTES <= 0 or not average or block.dtype != torch.float32 or dist.get_backend() != "nccl":
+            return
+        sid = torch.cuda.current_stream(block.device).cuda_stream
+        lst = _buckets.setdefault(sid, [])
+        lst.append(block)
+        if sum(b.numel() for b in lst) * 4 >= _BUCKET_BYTES:
+            _flush_bucket(sid)
         return
     op = _reduce_op() if average else dist.ReduceOp.SUM
     wire = None
@@ -127,8 +165,8 @@ def grad_block_ready(block, average=True):
         wire = _wire(block.numel(), block.device, ("block", len(_pending)))   # blocks arrive in the same order every step
         wire.copy_(block.reshape(-1))
     work = dist.all_reduce(block if wire is None else wire, op=op, async_op=True)
-    _pending.append((work, (block.data_ptr(), block.data_ptr() + block.numel() * block.element_size()), block,
-                     average and op == dist.ReduceOp.SUM, wire))
+    _pending.append((work, [(block.data_ptr(), block.data_ptr() + block.numel() * block.element_size())], [block.reshape(-1)],
+                     average and op == dist.ReduceOp.SUM, None if wire is None else [wire]))
 
 
 def allreduce_grads(params, average=True):
@@ -150,15 +188,19 @@ def allreduce_grads(params, average=True):
     div = average and op == dist.ReduceOp.SUM
     started = []             # address ranges already reduced by overlap_grad_allreduce
     n = 0
-    for work, rng, block, need_div, wire in (_pending or []):
+    if _pending is not None:
+        for sid in list(_buckets):       # what the buckets still hold (the backward is complete: every stream has joined this one)
+            _flush_bucket(sid)
+    for work, rng, flat, need_div, views in (_pending or []):
         work.wait()
-        if wire is not None:
-            block.reshape(-1).copy_(wire)
+        if views is not None:
+            torch._foreach_copy_(flat, views)
         if need_div:
-            block.div_(world)
-        started.append(rng)
+            torch._foreach_div_(flat, world)
+        started.extend(rng)
         n += 1
     _pending = None
+    _buckets.clear()
     blocks, loose, runs = {}, [], []
     for p in params:
         g = p.grad

@@ -63,6 +63,15 @@ class _LayerNormFn(torch.autograd.Function):
         return dx, da, db, None
 
 
+def _bucket_block(block, params):
+    """Hand a module's gradient block to the bucketed all-reduce (dist.grad_block_ready) when autograd is going to ADOPT its slices
+    as the parameters' .grad (all of them still None); a module applied twice in one step accumulates instead and is left to the
+    final all-reduce."""
+    from . import dist as _dist
+    if _dist._pending is not None and all(p.grad is None for p in params):
+        _dist.grad_block_ready(block, bucket=True)
+
+
 def _ws(nbytes, device):
     return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
 
@@ -318,6 +327,7 @@ class _MhaFn(torch.autograd.Function):
         grads = []
         for i, lin in enumerate(mod.linears):
             grads += [dW[i].view(lin.weight.shape), db[i]]
+        _bucket_block(block, mod.parameters())
         return (None, d_in_t[0], d_in_t[1], d_in_t[2], None, None, None, None) + tuple(grads)
 
 
@@ -356,6 +366,7 @@ class _FfnFn(torch.autograd.Function):
                                            _lib.ptr(dx), _lib.ptr(dW1), _lib.ptr(db1), _lib.ptr(dW2), _lib.ptr(db2), rows,
                                            d, d_ff, d_out, _lib.ptr(ws), ws.numel(), dt, p_drop, _lib.stream_ptr()),
                    "bist_ffn_bwd")
+        _bucket_block(block, ctx.mod.parameters())
         return None, dx, None, None, dW1.view(w1.shape), db1, dW2.view(w2.shape), db2
 
 
