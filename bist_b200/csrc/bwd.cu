@@ -456,9 +456,18 @@ __global__ void __launch_bounds__(256) ln_bwd_vec_kernel(LnBwdArgs a, int rows_p
     __syncthreads();
     float* da = a.da + grp * a.gstride;
     float* db = a.db + grp * a.gstride;
-    for (int i = threadIdx.x; i < d; i += blockDim.x) {
-      atomicAdd(da + i, sacc[i]);
-      atomicAdd(db + i, sacc[d + i]);
+    if ((((uintptr_t)da | (uintptr_t)db) & 15) == 0) {
+      // 16-byte vector reductions: a quarter of the L2 atomic operations (every CTA of the launch adds into the same 2*d floats)
+      const float4* s4 = reinterpret_cast<const float4*>(sacc);
+      for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+        atomicAdd(reinterpret_cast<float4*>(da) + i, s4[i]);
+        atomicAdd(reinterpret_cast<float4*>(db) + i, s4[nv + i]);
+      }
+    } else {
+      for (int i = threadIdx.x; i < d; i += blockDim.x) {
+        atomicAdd(da + i, sacc[i]);
+        atomicAdd(db + i, sacc[d + i]);
+      }
     }
   }
 }
