@@ -253,203 +253,6 @@ int pv_num_sms() {
   return n;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Persistent, software-pipelined variant of the same computation (Lq <= 16, key mask shared by the query rows,
-// contiguous 16-byte aligned score rows): each CTA walks groups g = blockIdx.x, += gridDim.x and, while the tensor cores
-// work on group i, the V rows AND the fp32 scores of group i+1 are already in flight (cp.async into the other half of a
-// two-stage ring).  The one-group-per-CTA kernel above exposes the full HBM latency of its loads once per group and
-// reaches ~46 % of the HBM roofline with three CTAs per SM; here the loads of the next group overlap the math and the
-// stores of the current one.
-// smem: V ring [2][16*KS][d+8] bf16 | score ring [2][16][h*16*KS + 8] f32 | context tile [16][d+8] bf16.
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-template <int KS, int NT>
-__global__ void __launch_bounds__(256, (KS <= 1 ? 2 : 1)) softmax_pv_pipe_kernel(SoftmaxPvArgs a) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  pdl_trigger();
-  const int d = a.h * a.dk, ldv = d + 8;
-  constexpr int NKP = 16 * KS;
-  const int RS = a.h * NKP + 8;                       // floats per query row of the score ring (+8: rows on distinct banks)
-  __nv_bfloat16* Vs = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-  float* Ss = reinterpret_cast<float*>(Vs + (size_t)2 * NKP * ldv);
-  __nv_bfloat16* Os = reinterpret_cast<__nv_bfloat16*>(Ss + (size_t)2 * 16 * RS);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x;
-  const int nk = a.nk, Lq = a.Lq, h = a.h;
-  const int vchunks = d / 8, schunks = nk / 4;        // 16-byte chunks per V row / per (row, head) score row
-
-  // padding key rows of both V buffers are zero for the whole kernel (cp.async only ever writes rows < nk)
-  for (int buf = 0; buf < 2; ++buf)
-    for (int k = nk + warp; k < NKP; k += 8) {
-      __nv_bfloat16* drow = Vs + ((size_t)buf * NKP + k) * ldv;
-      for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(drow + c) = make_uint4(0u, 0u, 0u, 0u);
-    }
-  pdl_wait();
-
-  auto prefetch = [&](int g, int buf) {
-    const __nv_bfloat16* Vg = reinterpret_cast<const __nv_bfloat16*>(a.V) + a.vg.off(g);
-    __nv_bfloat16* vdst = Vs + (size_t)buf * NKP * ldv;
-    for (int i = tid; i < nk * vchunks; i += 256) {
-      const int k = i / vchunks, c = (i - k * vchunks) * 8;
-      cp_async16(smem_addr(vdst + (size_t)k * ldv + c), Vg + a.v.off(k) + c);
-    }
-    const float* Sg = a.S + a.sg.off(g);
-    float* sdst = Ss + (size_t)buf * 16 * RS;
-    for (int i = tid; i < Lq * h * schunks; i += 256) {
-      const int c = i % schunks, rh = i / schunks;
-      const int hh = rh % h, row = rh / h;
-      cp_async16(smem_addr(sdst + (size_t)row * RS + hh * NKP + c * 4), Sg + (long long)row * a.s_l + (long long)hh * a.s_h + c * 4);
-    }
-    cp_async_commit();
-  };
-
-  const int r0 = lane >> 2, r1 = r0 + 8;
-  const int kq = (lane & 3) * 2;
-  const bool ok0 = r0 < Lq, ok1 = r1 < Lq;
-  int g = blockIdx.x, it = 0;
-  if (g < a.G) prefetch(g, 0);
-  for (; g < a.G; g += gridDim.x, ++it) {
-    const int buf = it & 1;
-    const int gn = g + gridDim.x;
-    if (gn < a.G) {
-      prefetch(gn, buf ^ 1);
-      cp_async_wait_group<1>();
-    } else {
-      cp_async_wait_group<0>();
-    }
-    __syncthreads();                                   // group g's V rows and scores are visible to every warp
-    const __nv_bfloat16* Vb = Vs + (size_t)buf * NKP * ldv;
-    const float* Sb = Ss + (size_t)buf * 16 * RS;
-    const uint8_t* Mg = a.mask ? a.mask + (long long)((g / a.mask_gdiv) % a.mask_gmod) * a.m_b : nullptr;
-    for (int hh = warp; hh < h; hh += 8) {
-      float s[KS][8];
-      const float* p0 = Sb + (size_t)r0 * RS + hh * NKP;
-      const float* p1 = p0 + 8 * RS;
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const int k = ks * 16 + half * 8 + kq;     // nk % 4 == 0 and k even: k < nk implies k + 1 < nk
-          float2 t0 = make_float2(-INFINITY, -INFINITY), t1 = t0;
-          if (k < nk) {
-            if (ok0) t0 = *reinterpret_cast<const float2*>(p0 + k);
-            if (ok1) t1 = *reinterpret_cast<const float2*>(p1 + k);
-            if (Mg) {
-              const uchar2 m = *reinterpret_cast<const uchar2*>(Mg + k);
-              if (m.x == 0) { t0.x = ok0 ? kMaskFill : t0.x; t1.x = ok1 ? kMaskFill : t1.x; }
-              if (m.y == 0) { t0.y = ok0 ? kMaskFill : t0.y; t1.y = ok1 ? kMaskFill : t1.y; }
-            }
-          }
-          s[ks][half * 4 + 0] = t0.x; s[ks][half * 4 + 1] = t0.y;
-          s[ks][half * 4 + 2] = t1.x; s[ks][half * 4 + 3] = t1.y;
-        }
-      }
-      float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-        mx0 = fmaxf(mx0, fmaxf(fmaxf(s[ks][0], s[ks][1]), fmaxf(s[ks][4], s[ks][5])));
-        mx1 = fmaxf(mx1, fmaxf(fmaxf(s[ks][2], s[ks][3]), fmaxf(s[ks][6], s[ks][7])));
-      }
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      if (mx0 == -INFINITY) mx0 = 0.f;
-      if (mx1 == -INFINITY) mx1 = 0.f;
-      float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const bool row1 = (j & 2) != 0;
-          const float e = __expf(s[ks][j] - (row1 ? mx1 : mx0));
-          s[ks][j] = e;
-          if (row1) sum1 += e; else sum0 += e;
-        }
-      }
-      sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
-      sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-      const float inv0 = sum0 > 0.f ? 1.f / sum0 : 0.f, inv1 = sum1 > 0.f ? 1.f / sum1 : 0.f;
-      if (a.drop.thresh != 0u) {
-        const unsigned long long base0 = (((unsigned long long)g * h + hh) * Lq + r0) * nk;
-        const unsigned long long base1 = (((unsigned long long)g * h + hh) * Lq + r1) * nk;
-#pragma unroll
-        for (int ks = 0; ks < KS; ++ks)
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int key = ks * 16 + (j >> 2) * 8 + kq + (j & 1);
-            s[ks][j] *= drop_mul(a.drop, ((j & 2) ? base1 : base0) + key);
-          }
-      }
-      uint32_t pa[KS][4];
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-        pa[ks][0] = pack_bf16(s[ks][0] * inv0, s[ks][1] * inv0);
-        pa[ks][1] = pack_bf16(s[ks][2] * inv1, s[ks][3] * inv1);
-        pa[ks][2] = pack_bf16(s[ks][4] * inv0, s[ks][5] * inv0);
-        pa[ks][3] = pack_bf16(s[ks][6] * inv1, s[ks][7] * inv1);
-      }
-      float acc[NT][4];
-#pragma unroll
-      for (int n = 0; n < NT; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
-      const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
-      const uint32_t vbase = smem_addr(Vb) + (uint32_t)((lrow * ldv + hh * a.dk + lcol) * 2);
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-#pragma unroll
-        for (int np = 0; np < NT / 2; ++np) {
-          uint32_t b0, b1, b2, b3;
-          ldmatrix_x4_trans(vbase + (uint32_t)((ks * 16 * ldv + np * 16) * 2), b0, b1, b2, b3);
-          mma_bf16_16816(acc[2 * np], pa[ks], b0, b1);
-          mma_bf16_16816(acc[2 * np + 1], pa[ks], b2, b3);
-        }
-      }
-      const int orow = lane >> 2, ocol = hh * a.dk + kq;
-#pragma unroll
-      for (int n = 0; n < NT; ++n) {
-        *reinterpret_cast<uint32_t*>(Os + (size_t)orow * ldv + ocol + n * 8) = pack_bf16(acc[n][0], acc[n][1]);
-        *reinterpret_cast<uint32_t*>(Os + (size_t)(orow + 8) * ldv + ocol + n * 8) = pack_bf16(acc[n][2], acc[n][3]);
-      }
-    }
-    __syncthreads();                                   // context tile complete; ring half `buf` free for the next prefetch
-    {
-      __nv_bfloat16* Cg = reinterpret_cast<__nv_bfloat16*>(a.ctx) + a.og.off(g);
-      for (int li = warp; li < Lq; li += 8) {
-        __nv_bfloat16* crow = Cg + (long long)li * a.o_l;
-        for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(crow + c) = *reinterpret_cast<const uint4*>(Os + (size_t)li * ldv + c);
-      }
-    }
-    __syncthreads();                                   // the context tile is reused by the next group
-  }
-}
-
-template <int KS, int NT>
-int launch_pv_pipe(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken) {
-  const int d = a.h * a.dk;
-  const size_t smem = (size_t)2 * 16 * KS * (d + 8) * 2 + (size_t)2 * 16 * (a.h * 16 * KS + 8) * 4 + (size_t)16 * (d + 8) * 2;
-  if (smem > 200 * 1024) return 0;
-  auto kern = softmax_pv_pipe_kernel<KS, NT>;
-  static bool configured = false;
-  if (!configured) {
-    BIST_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    configured = true;
-  }
-  const int per_sm = smem <= 100 * 1024 ? 2 : 1;
-  const int grid = std::min(a.G, pv_num_sms() * per_sm);
-  ProfScope ps("softmax_pv_mma", st);
-  BIST_LAUNCH(kern, grid, 256, smem, st, a);
-  BIST_LAUNCHED();
-  *taken = true;
-  return 0;
-}
-
-template <int KS>
-int pick_nt_pipe(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken) {
-  switch (a.dk / 8) {
-    case 4: return launch_pv_pipe<KS, 4>(a, st, taken);
-    case 8: return launch_pv_pipe<KS, 8>(a, st, taken);
-    default: return 0;
-  }
-}
 
 template <int KS>
 int pick_nt(const SoftmaxPvArgs& a, cudaStream_t st) {
@@ -714,22 +517,6 @@ int softmax_pv_mma(const SoftmaxPvArgs& a, cudaStream_t st, bool* taken) {
   if (a.v.inner != kNoSplit && a.v.inner <= 0) return 0;
   const int ks = (a.nk + 15) / 16;
   if ((size_t)(16 * ks + 16) * (d + 8) * 2 > 200 * 1024) return 0;
-  {
-    // pipelined persistent variant: Lq <= 16, key mask shared by the query rows, 16-byte aligned contiguous score rows
-    // Measured at config 2 (r01g): 40 us per launch against 31 us for the one-group-per-CTA kernel above — a group is so
-    // little work (16-48 keys) that the per-group barriers of ONE resident CTA cost more than the exposed load latency
-    // they were meant to hide, which three or four co-resident CTAs already cover.  Kept for larger groups; opt-in.
-    static const bool pipe_on = getenv("BIST_PV_PIPE") != nullptr;
-    const bool aligned = a.s_k == 1 && a.nk % 4 == 0 && (a.s_l | a.s_h | a.sg.so | a.sg.si) % 4 == 0 &&
-                         (reinterpret_cast<uintptr_t>(a.S) & 15) == 0 &&
-                         (!a.mask || (a.m_l == 0 && a.m_b % 2 == 0 && (reinterpret_cast<uintptr_t>(a.mask) & 1) == 0));
-    if (pipe_on && aligned && a.Lq <= 16 && ks <= 3 && a.G >= 2 * pv_num_sms()) {
-      bool tk = false;
-      int rc2 = ks == 1 ? pick_nt_pipe<1>(a, st, &tk) : ks == 2 ? pick_nt_pipe<2>(a, st, &tk) : pick_nt_pipe<3>(a, st, &tk);
-      if (rc2 != 0) return rc2;
-      if (tk) { *taken = true; return 0; }
-    }
-  }
   int rc = -1;
   if (ks == 1) rc = pick_nt<1>(a, st);
   else if (ks == 2) rc = pick_nt<2>(a, st);
