@@ -221,6 +221,7 @@ struct GemmArgs {
   int relu = 0;
   const char* tag = "gemm";  // label for bist_prof_collect
   int allow_tf32 = 0;        // fp32 operands may be multiplied as tf32 on the tensor cores
+  int accumulate = 0;        // tensor-core path: the fp32 values already in C are added before the activation (split products)
   int max_ctas = 0;          // persistent tensor-core GEMM: cap on the grid (0 = one CTA per SM); a GEMM forked onto the side
                              // stream leaves some SMs to the serial chain it overlaps with
   // Region-major W (tensor-core path only): W is a [*, wr_T, wr_S, K] tensor (row (bt, s) at (bt*wr_S + s)*w.si) and
@@ -236,6 +237,18 @@ struct SideStream { cudaStream_t s; cudaEvent_t fork, join, fork2, join2; };
 bool dir_overlap_enabled();  // second direction's stage-1/stage-2 kernels on the side stream (BIST_DIR_OVERLAP)
 int side_stream(SideStream** out);
 bool overlap_enabled();
+
+// fp32 accuracy on the tensor cores: three tf32 products over hi / lo splits (gemm_x3.cu)
+struct SplitRef {
+  const float* src = nullptr;   // first element of the memory range that holds the operand (all batches)
+  long long n = 0;              // elements in the range (multiple of 4)
+  float* hi = nullptr;          // scratch mirrors of the range
+  float* lo = nullptr;
+  int ready = 0;                // the mirrors have been written already
+};
+int split_tf32(const float* x, float* hi, float* lo, long long n, cudaStream_t st);
+bool fp32x3_enabled();
+int gemm_fp32x3(const GemmArgs& g, const SplitRef& sa, const SplitRef& sw, cudaStream_t st);
 
 int gemm(const GemmArgs& g, cudaStream_t st);       // dispatches to the kernels below
 int gemm_simt(const GemmArgs& g, cudaStream_t st);  // CUDA-core fp32-accumulate GEMM, any shape

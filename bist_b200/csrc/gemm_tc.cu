@@ -245,6 +245,10 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
           for (int rr = 0; rr < 8; ++rr) {
             v[rr].x = fmaf(v[rr].x, alpha, bv.x); v[rr].y = fmaf(v[rr].y, alpha, bv.y);
             v[rr].z = fmaf(v[rr].z, alpha, bv.z); v[rr].w = fmaf(v[rr].w, alpha, bv.w);
+            if (g.accumulate && ok_r[rr]) {   // earlier partial products of a split fp32 product (fp32 C)
+              const float4 c0 = ld4(reinterpret_cast<const float*>(g.C) + co_r[rr] + cc);
+              v[rr].x += c0.x; v[rr].y += c0.y; v[rr].z += c0.z; v[rr].w += c0.w;
+            }
             if (relu) {
               v[rr].x = fmaxf(v[rr].x, 0.f); v[rr].y = fmaxf(v[rr].y, 0.f);
               v[rr].z = fmaxf(v[rr].z, 0.f); v[rr].w = fmaxf(v[rr].w, 0.f);
@@ -274,6 +278,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
               float sv;
               asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sv) : "r"(stg + (uint32_t)((lr * STG_LD + lane) * 4)) : "memory");
               float v = fmaf(sv, alpha, bv);
+              if (g.accumulate) v += reinterpret_cast<const float*>(g.C)[co + cc];
               if (relu) v = fmaxf(v, 0.f);
               if (has_r)
                 v += r_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g.R)[ro + cc])

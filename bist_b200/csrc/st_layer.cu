@@ -64,6 +64,10 @@ struct Workspace {
   float *sc0, *x, *ts, *sc1, *sc1b, *qf2f;                    // fp32
   void* xv;
   void* ctx1[2];
+  // fp32 mode: hi / lo splits for the tensor-core products (gemm_x3.cu): the video tensor, the layer's packed matrices, and the
+  // activation operand of the product at hand
+  float *v_hi, *v_lo, *w_hi, *w_lo, *a_hi, *a_lo;
+  size_t a_cap;
   size_t bytes;
   bool ok;
 };
@@ -93,6 +97,13 @@ Workspace carve(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   W.xv = A.take((size_t)B * T * S * nd * d * e);
   for (int u = 0; u < 2; ++u) W.ctx1[u] = nullptr;
   for (int u = 0; u < nd; ++u) W.ctx1[u] = A.take((size_t)B * (kinds[u] == 0 ? S : T) * Lq * d * e);
+  W.v_hi = W.v_lo = W.w_hi = W.w_lo = W.a_hi = W.a_lo = nullptr;
+  W.a_cap = 0;
+  if (dtype == BIST_F32 && fp32x3_enabled()) {
+    const size_t nv = (size_t)B * T * S * d, nw = packed_layout(d, dff, 2, dtype).mat_elems;
+    W.a_cap = nd * Q * (size_t)(h * d > dff ? (h * d > 3 * d ? h * d : 3 * d) : (dff > 3 * d ? dff : 3 * d));   // largest activation range one product reads
+    W.v_hi = f(nv); W.v_lo = f(nv); W.w_hi = f(nw); W.w_lo = f(nw); W.a_hi = f(W.a_cap); W.a_lo = f(W.a_cap);
+  }
   W.bytes = A.used + 256;
   W.ok = A.ok;
   return W;
@@ -257,6 +268,24 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   const int Q = (int)(B * Lq), dk = (int)(d / h), di = (int)d, hi = (int)h;
   const long long Qd = (long long)Q * d, dd = (long long)d * d;
   const bool s2mma = use_stage2_mma(dtype, T, S, h, d, nd, kinds);
+  // fp32 mode: the products run on the tensor cores as three tf32 products over hi / lo splits (gemm_x3.cu).  The video tensor and
+  // the layer's packed matrices are split once per call; an activation operand is split right before the product that reads it.
+  const bool x3 = dtype == BIST_F32 && W.v_hi != nullptr;
+  SplitRef sv, swt;
+  if (x3) {
+    sv.src = (const float*)vft; sv.n = B * T * S * d; sv.hi = W.v_hi; sv.lo = W.v_lo; sv.ready = 1;
+    swt.src = (const float*)packed; swt.n = (long long)L.mat_elems; swt.hi = W.w_hi; swt.lo = W.w_lo; swt.ready = 1;
+    BIST_TRY(split_tf32(sv.src, sv.hi, sv.lo, sv.n, st));
+    BIST_TRY(split_tf32(swt.src, swt.hi, swt.lo, swt.n, st));
+  }
+  auto mm = [&](const GemmArgs& g, const void* a_base, long long a_n, cudaStream_t s_, int a_ready = 0) -> int {
+    if (!x3) return gemm(g, s_);
+    SplitRef sa;
+    if (a_base == vft) sa = sv;
+    else { sa.src = (const float*)a_base; sa.n = a_n; sa.hi = W.a_hi; sa.lo = W.a_lo; sa.ready = a_ready; }
+    const bool w_is_video = (const char*)g.W >= (const char*)vft && (const char*)g.W < (const char*)vft + sv.n * 4;
+    return gemm_fp32x3(g, sa, w_is_video ? sv : swt, s_);
+  };
 
   // Batched (over the active directions) linear layer  C[u] = act(A[u] . W[u]^T + b[u]) (+ R[u]).
   auto lin = [&](const void* Ain, long long a_dir, size_t w_off, size_t b_off, void* Cout, long long c_dir, int c_dtype,
@@ -268,7 +297,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.Z = nd; g.zin = 1;
     g.az = {a_dir, 0}; g.wz = {ms, 0}; g.cz = {c_dir, 0}; g.rz = {r_dir, 0}; g.bz = {fsd, 0};
     g.relu = relu; g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = c_dtype; g.tag = "query_side_gemm";
-    return gemm(g, st);
+    return mm(g, Ain, (long long)(nd - 1) * a_dir + (long long)Q * K, st);
   };
 
   // The stage-1 values XV = vft . [Wv1]^T + bv1 (the one big GEMM of the block) depend only on the video tensor: launch
@@ -282,7 +311,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.a = rows_dense(d); g.w = rows_dense(d); g.c = rows_dense(xvld);
     g.a_dtype = dtype; g.w_dtype = dtype; g.c_dtype = dtype; g.tag = "xv_gemm";
     if (s != st) g.max_ctas = xv_side_ctas();
-    return gemm(g, s);
+    return mm(g, vft, 0, s);
   };
   // bf16 mode, d_k = 64, Lq <= 16, T and S <= 128: stage 1 of both directions is ONE kernel that reads the video tensor once
   // and keeps projected values and scores on chip (stage1_fused.cu); otherwise the value GEMM + score GEMM + softmax.V chain.
@@ -365,7 +394,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.Z = 3 * nd; g.zin = nd;  // z = which * nd + u
     g.az = {nd * Qd, Qd}; g.wz = {dd, ms}; g.cz = {nd * Qd, Qd}; g.bz = {d, fsd};
     g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.tag = "query_side_gemm";
-    BIST_TRY(gemm(g, st));
+    BIST_TRY(mm(g, W.n12x, 3 * nd * Qd, st));
   }
   {
     // Query-side folds of the key projections: qf[which][u][q,hh,:] = q[which][u][q, hh*dk:(hh+1)*dk] . WkT[:, hh*dk:(hh+1)*dk]^T
@@ -383,7 +412,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
       BIST_TRY(gemm(g, st));
     } else {
       g.Z = 2 * nd * hi;
-      BIST_TRY(gemm(g, st));
+      BIST_TRY(mm(g, W.q12x, 2 * nd * Qd, st));
     }
   }
   }
@@ -406,6 +435,8 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
   }
   // The two directions are independent from here to the stage-2 outputs: the second one's kernels can run on the
   // side stream (behind the value GEMM it needs anyway) beside the first one's, with its own score buffer.
+  // fp32 tensor-core mode: the folded stage-1 queries of both directions are split once, before the second direction forks
+  if (x3 && !fused1) BIST_TRY(split_tf32((const float*)W.qf12, W.a_hi, W.a_lo, (long long)nd * Qd * h, st));
   const bool dir_ovl = (fused1 ? side != nullptr : xv_forked) && nd == 2 && dir_overlap_enabled();
   if (dir_ovl) {
     BIST_CUDA(cudaEventRecord(side->fork2, st));  // the folded queries are ready
@@ -450,7 +481,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
         g.Z = (int)B; g.zin = 1;
         g.az = {Lq * h * d, 0}; g.wz = {TS * d, 0}; g.cz = {Lq * h * TS, 0};
       }
-      if (!done) { const int rc = gemm(g, su); if (rc != 0) { join_dirs(); return rc; } }
+      if (!done) { const int rc = mm(g, W.qf12, (long long)nd * Qd * h, su, 1); if (rc != 0) { join_dirs(); return rc; } }
     }
     SoftmaxPvArgs a;
     a.S = sc1;
@@ -504,7 +535,7 @@ extern "C" int bist_st_layer_fwd(const float* in_t2s, const float* in_s2t, const
     g.Z = nd * hi; g.zin = hi;
     g.az = {Qd * h, d}; g.wz = {ms, (long long)dk * d}; g.cz = {Qd, dk}; g.rz = {Qd, dk};
     g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = adt; g.r_dtype = adt; g.tag = "vfold2_gemm";
-    BIST_TRY(gemm(g, st));
+    BIST_TRY(mm(g, W.u2, (long long)nd * Qd * h, st));
   }
   BIST_TRY(lin(W.cbuf, Qd, L.wo2, L.bo2, W.ts, Qd, BIST_F32, di, di, 0, W.x, Qd, fusedq ? W.nbuf : nullptr));
 

@@ -15,6 +15,7 @@ extern "C" {
 size_t bist_vidproj_workspace_bytes(int64_t N, int64_t D, int64_t d, int compute_dtype) {
   size_t n = align_up((size_t)N * d * 4, 256);                        // relu(fts W^T + b), fp32
   if (compute_dtype == BIST_BF16) n += align_up((size_t)d * D * 2, 256);  // bf16 copy of W
+  else n += 2 * align_up((size_t)N * D * 4, 256) + 2 * align_up((size_t)d * D * 4, 256);   // hi / lo splits of fts and W (gemm_x3.cu)
   return n + 512;
 }
 
@@ -29,6 +30,11 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
   Arena A(ws, ws_bytes);
   float* act = (float*)A.take((size_t)N * d * 4);
   void* wb = compute_dtype == BIST_BF16 ? A.take((size_t)d * D * 2) : nullptr;
+  SplitRef sa, sw;
+  if (compute_dtype == BIST_F32) {
+    sa.src = fts; sa.n = N * D; sa.hi = (float*)A.take((size_t)N * D * 4); sa.lo = (float*)A.take((size_t)N * D * 4);
+    sw.src = W; sw.n = d * D; sw.hi = (float*)A.take((size_t)d * D * 4); sw.lo = (float*)A.take((size_t)d * D * 4);
+  }
   if (!A.ok) { set_error("vidproj: workspace too small (%zu bytes)", ws_bytes); return BIST_ERR_WORKSPACE; }
   if (compute_dtype == BIST_BF16) {
     // bf16 mode: one fused kernel (TMA fp32 -> in-smem bf16 -> tcgen05 -> LayerNorm epilogue), see vidproj_tc.cu
@@ -46,7 +52,9 @@ int bist_vidproj_fwd(const float* fts, const float* W, const float* bias, const 
   g.a = rows_dense(D); g.w = rows_dense(D); g.c = rows_dense(d);
   g.relu = 1; g.w_dtype = w_dtype; g.tag = "vidproj_gemm";
   g.allow_tf32 = compute_dtype == BIST_BF16;
-  BIST_TRY(gemm(g, st));
+  // fp32 mode: three tf32 products over hi / lo splits of the features and the weight (fp32 accuracy on the tensor cores)
+  if (compute_dtype == BIST_F32) BIST_TRY(gemm_fp32x3(g, sa, sw, st));
+  else BIST_TRY(gemm(g, st));
   return layer_norm(act, a_2, b_2, out, N, d, eps, BIST_F32, out_dtype, st);                                  // :80
 }
 
