@@ -18,16 +18,20 @@
 //     3 regions x 40 clips for t2s at config 2; the t2s tile is gathered by the TMA unit itself from rows at stride S*d
 //     (a box of the (d, S, T, B) view), so the softmax over T completes inside the tile like the softmax over S does.
 //     The tile stays RESIDENT in shared memory (A operand, d/64 k-slabs of 16 KB) for all heads.
-//   * [qf_hh ; W_v,hh] (80 rows) streams through a 4-slot ring as the B operand, one head per pass: 4 UMMAs (M = 128,
-//     N = 80, K = 16) per k-slab into one of two TMEM accumulators.
-//   * Two epilogue groups take alternate passes: TMEM -> registers; values -> bf16 tile in the UMMA MN-major SWIZZLE_128B
-//     layout, scores -> shared memory (transposed); masked softmax over the keys of each (group, query token)
-//     (modules.py:57-61; a team of threads per row, warp-shuffle max / sum); probabilities -> bf16 K-major core-matrix
-//     layout; the UMMA issuer then multiplies P.V for two groups per instruction (A = staged values of groups r, r+1 as the
-//     two 64-row atoms, B = their probabilities, N = 32: lanes 0-63 x columns 0-15 and lanes 64-127 x columns 16-31 are the
-//     two results); the group reads them back, adds b_v and assembles the [l][group][64] output tile in place of the dead
-//     staged values; ONE TMA store writes it into c1[b, l, g, hh*64 .. +64) — the layout stage 2 reads.
-// Warps: 0 video-tile producer, 1 UMMA issuer, 2 TMEM allocation + [qf ; W_v] producer, 4-7 / 8-11 epilogue groups.
+//   * [qf_h0 ; qf_h1 ; W_v,h0 ; W_v,h1] (160 rows: two heads per pass, so that the UMMA runs at N = 160 instead of the slower
+//     N = 80) streams through a 5-slot ring of 10 KB half-slabs as the B operand: 4 UMMAs (M = 128, N = 160, K = 16) per k-slab
+//     into one of two TMEM accumulators.  Accumulator columns: [0,32) scores (2*l + head), [32,96) / [96,160) the heads' values.
+//   * Two epilogue groups of four warps take one head of the pass each: TMEM -> registers; values -> bf16 tile in the UMMA
+//     MN-major SWIZZLE_128B layout, scores -> shared memory as fp32 [row][16] (XOR-swizzled float4s), key mask / padding
+//     applied while staging; masked softmax over the keys of each (group, query token) (modules.py:57-61; a team of `parts`
+//     threads per (group, 4 query tokens), float4 loads, warp-shuffle max / sum); probabilities -> bf16 [key][2 groups x 16 l]
+//     in the MN-major SWIZZLE_64B layout; the P.V issuer warp then multiplies two groups per UMMA chain (A = staged values of
+//     groups r, r+1 as the two 64-row atoms, B = their probabilities, N = 32: lanes 0-63 x columns 0-15 and lanes 64-127 x
+//     columns 16-31 are the two results); the group reads them back, adds b_v and assembles the [l][group][64] output tile in
+//     place of the dead staged values; ONE TMA store writes it into c1[b, l, g, hh*64 .. +64) — the layout stage 2 reads.
+// Warps: 0 video-tile producer, 1 UMMA issuer, 2 TMEM allocation + B producer, 3 P.V issuer, 4-7 / 8-11 epilogue groups.
+// Issue warps stay converged and elect one lane (elect.sync): a divergent single-lane region makes the compiler wrap every
+// UMMA / TMA instruction in a uniform-register waterfall loop.
 #include <stdlib.h>
 
 #include "tc_ptx.cuh"
