@@ -66,12 +66,14 @@ struct VpArgs {
   const float* b2;
   void* out;
   int N, D, d, out_bf16, tiles, nkb;
+  int rpc;   // > 0 (single-CTA form): CTA c owns rows [c*rpc, (c+1)*rpc) — equal shares, the last tile of a share is partial
   float eps;
 };
 
 template <int NCTA>
 __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                         const __grid_constant__ CUtensorMap map_w, const VpArgs p) {
+                                                         const __grid_constant__ CUtensorMap map_w,
+                                                         const __grid_constant__ CUtensorMap map_a32, const VpArgs p) {
   pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -95,6 +97,18 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   const int ustep = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const int units = NCTA == 2 ? (p.tiles + 1) >> 1 : p.tiles;
   const int wrows = nmma / NCTA;                         // W rows per UMMA held by this CTA
+  // This CTA's tiles: tile i starts at row m_first + i * m_step; rows >= row_hi are not its own.
+  //   round-robin form: whole 128-row tiles dealt out to the CTAs (pairs); 320 tiles on 148 SMs are three rounds for 2.16 of work
+  //   equal-share form (rpc > 0, NCTA == 1): every CTA owns the same number of consecutive rows; the last tile of a share is
+  //   partial and fetches only its own rows (32-row boxes), so the third round costs its weight stream, not a full tile
+  int n_my, m_first, m_step, row_hi;
+  if (NCTA == 1 && p.rpc > 0) {
+    const long long lo = (long long)blockIdx.x * p.rpc, hi = lo + p.rpc < p.N ? lo + p.rpc : p.N;
+    n_my = lo < hi ? (int)((hi - lo + 127) / 128) : 0; m_first = (int)lo; m_step = 128; row_hi = (int)hi;
+  } else {
+    n_my = unit0 < units ? (units - unit0 + ustep - 1) / ustep : 0;
+    m_first = (NCTA * unit0 + rank) * 128; m_step = NCTA * ustep * 128; row_hi = p.N;
+  }
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < VP_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 4); }
@@ -117,8 +131,12 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   if (warp == 0) {
     if (lane == 0) {
       int sa = 0, pa = 0, it = 0;
-      for (int u = unit0; u < units; u += ustep) {
-        const int m0 = (NCTA * u + rank) * 128;   // a tile past the end (odd tile count) loads zeros
+      // (Measured and dropped: prefetching the next 8-64 slabs into L2 with cp.async.bulk.prefetch.tensor makes the kernel
+      //  SLOWER, 141.6 -> 144.9 .. 173.4 us — the prefetch boxes go through the same TMA unit as the ring's loads.)
+      for (int ti = 0; ti < n_my; ++ti) {
+        const int m0 = m_first + ti * m_step;     // a tile past the end (odd tile count) loads zeros
+        const int own = row_hi - m0;              // equal-share form: rows of this tile that belong to the CTA
+        const int nb32 = (NCTA == 1 && p.rpc > 0 && own < 128) ? (own + 31) / 32 : 4;
         // two slabs (adjacent 128-byte segments of the same 128 feature rows) are requested back to back, so the second
         // finds the DRAM pages the first opened: 154.7 -> 144.9 us at config 2
         const int grp = L.na >= 4 ? 2 : 1;
@@ -130,8 +148,13 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
             if (++s2 == L.na) { s2 = 0; p2 ^= 1; }
           }
           for (int j = 0; j < n; ++j, ++it) {
-            mbar_expect_tx(&afull[sa], VP_AF);
-            tma_load_2d(smem + sa * VP_AF, &map_a, &afull[sa], (kb + j) * VP_BK, m0);
+            if (nb32 == 4) {
+              mbar_expect_tx(&afull[sa], VP_AF);
+              tma_load_2d(smem + sa * VP_AF, &map_a, &afull[sa], (kb + j) * VP_BK, m0);
+            } else {   // partial tile: only the CTA's own rows (the other rows of the slab keep stale, finite data nobody stores)
+              mbar_expect_tx(&afull[sa], (uint32_t)(nb32 * (VP_AF / 4)));
+              for (int q = 0; q < nb32; ++q) tma_load_2d(smem + sa * VP_AF + q * (VP_AF / 4), &map_a32, &afull[sa], (kb + j) * VP_BK, m0 + 32 * q);
+            }
             VTRACE(0, it);
             if (++sa == L.na) { sa = 0; pa ^= 1; }
           }
@@ -141,7 +164,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   } else if (warp == 10) {
     if (lane == 0) {
       int it = 0;
-      for (int u = unit0; u < units; u += ustep) {
+      for (int ti = 0; ti < n_my; ++ti) {
         for (int kb = 0; kb < p.nkb; ++kb, ++it) {
           const int s = it % L.ms;
           mbar_wait(&empty[s], ((it / L.ms) & 1) ^ 1);
@@ -156,7 +179,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
     if (lane == 0 && rank == 0) {   // the leader CTA issues for the pair
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nmma >> 3) << 17) | ((uint32_t)((128 * NCTA) >> 4) << 24);
       int it = 0, tc_ = 0;
-      for (int u = unit0; u < units; u += ustep, ++tc_) {
+      for (int ti = 0; ti < n_my; ++ti, ++tc_) {
         if (NCTA == 2) mbar_wait_cluster(acc_empty, (tc_ & 1) ^ 1);
         else mbar_wait(acc_empty, (tc_ & 1) ^ 1);
         tc_fence_after();
@@ -196,8 +219,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
     const uint32_t stg_r = stg + (uint32_t)((sub_r * VP_STG_LD + sub_c) * 4);
     float* red = (float*)(smem + L.red_off);         // [2][128][3]
     int it = 0, tc_ = 0;
-    for (int u = unit0; u < units; u += ustep, ++tc_) {
-      const int tile = NCTA * u + rank;
+    for (int ti = 0; ti < n_my; ++ti, ++tc_) {
       // ---- main loop: fp32 slab -> bf16 slab.  The two groups of four warps take alternate slabs (a thread converts one row of
       //      its slab), so a slab's wait -> load -> convert -> store -> fence -> arrive chain has two slab periods to complete in
       //      instead of one: with all eight warps on every slab that chain, not the tensor core, set the pace.
@@ -241,7 +263,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         if (warp == 2 && lane == 0) VTRACE(3, it);
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
-      const int m0 = tile * 128;
+      const int m0 = m_first + ti * m_step;
       const int row_w0 = m0 + lg * 32;
       mbar_wait(acc_full, tc_ & 1);
       tc_fence_after();
@@ -320,7 +342,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
 #pragma unroll
         for (int rr = 0; rr < 8; ++rr) {
           const int row = row_w0 + rr * 4 + sub_r;
-          if (row < p.N) {
+          if (row < row_hi) {
             const float4 o = make_float4(fmaf(y[rr].x, ga.x, gb.x), fmaf(y[rr].y, ga.y, gb.y), fmaf(y[rr].z, ga.z, gb.z),
                                          fmaf(y[rr].w, ga.w, gb.w));
             if (p.out_bf16) st4(reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * d + cc, o);
@@ -365,8 +387,9 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   *taken = true;
   BIST_TRY(pack_matrix(W, wb, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
   const int nmma = (int)(d > 256 ? d / 2 : d);
-  CUtensorMap ma, mw;
+  CUtensorMap ma, mw, ma32;
   BIST_TRY(make_map_2d(&ma, fts, true, D, N, VP_BK, 128, 128));
+  BIST_TRY(make_map_2d(&ma32, fts, true, D, N, VP_BK, 32, 128));
   BIST_TRY(make_map_2d(&mw, wb, false, D, d, VP_BK, nmma / ncta, 64));
   static bool configured = false;
   if (!configured) {
@@ -378,6 +401,7 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   p.bias = bias; p.a2 = a2; p.b2 = b2; p.out = out;
   p.N = (int)N; p.D = (int)D; p.d = (int)d; p.out_bf16 = out_dtype == BIST_BF16;
   p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
+  p.rpc = 0;
   ProfScope ps("vidproj_fused", st);
   if (ncta == 2) {
     const int pairs = (p.tiles + 1) / 2, max_pairs = num_sms() / 2;
@@ -390,10 +414,14 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
     at[1].id = cudaLaunchAttributeClusterDimension;
     at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 2;
-    BIST_CUDA(cudaLaunchKernelEx(&cfg, vidproj_kernel<2>, ma, mw, p));
+    BIST_CUDA(cudaLaunchKernelEx(&cfg, vidproj_kernel<2>, ma, mw, ma32, p));
   } else {
-    const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
-    BIST_LAUNCH(vidproj_kernel<1>, grid, 352, L.total, st, ma, mw, p);
+    int grid = p.tiles < num_sms() ? p.tiles : num_sms();
+    if (p.tiles > grid && p.tiles % grid != 0) {   // uneven rounds: equal shares of rows instead (multiples of 32 for the partial boxes)
+      p.rpc = (int)(((N + grid - 1) / grid + 31) / 32 * 32);
+      grid = (int)((N + p.rpc - 1) / p.rpc);
+    }
+    BIST_LAUNCH(vidproj_kernel<1>, grid, 352, L.total, st, ma, mw, ma32, p);
   }
   BIST_LAUNCHED();
   return 0;
