@@ -41,23 +41,36 @@ __device__ long long g_vtrace[4][64];   // CTA 0 only: [role][event]
 #endif
 __host__ __device__ inline int vp_pair_stages() { return VP_PAIR_STAGES; }
 struct VpSmem {
-  int wb_bytes, stage_bytes, na, ms, mma_off, stg_off, red_off, bar_off, total;
+  int wb_bytes, na, ms, a16_off, w_off, stg_off, red_off, bar_off, total;
 };
-__host__ __device__ inline VpSmem vp_smem(int d, int ncta) {
+__host__ __device__ inline VpSmem vp_smem(int d, int ncta, int ms_override = 0) {
   VpSmem s;
   s.wb_bytes = d * VP_BK * 2 / ncta;            // bf16 W slab (SWIZZLE_64B): d rows, or this CTA's half of each UMMA's N
-  s.stage_bytes = VP_AB + s.wb_bytes;           // MMA-ring slot; multiple of 1024 for d % 16 == 0
   // a CTA pair hands slots back and forth across two SMs (multicast commit, remote arrive): its MMA ring is deeper
-  s.ms = ncta == 2 ? vp_pair_stages() : 3;
-  const int fixed = s.ms * s.stage_bytes + 8 * 32 * VP_STG_LD * 4 + 2 * 128 * 3 * 4 + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
+  s.ms = ms_override > 0 ? ms_override : (ncta == 2 ? vp_pair_stages() : 3);
+  // The epilogue's transposition buffers (8 warps x [32][36] floats) live IN the bf16 A ring when it is large enough: when the
+  // epilogue of a tile runs, every UMMA that read the ring has retired (acc_full) and the warps that would refill it are the ones
+  // running the epilogue.  The 36 KB this saves are two more fp32 slabs in flight.
+  const int stg_bytes = 8 * 32 * VP_STG_LD * 4;
+  const bool alias = s.ms * VP_AB >= stg_bytes;
+  const int fixed = s.ms * (VP_AB + s.wb_bytes) + (alias ? 0 : stg_bytes) + 2 * 128 * 3 * 4 + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
   int na = (227 * 1024 - fixed) / VP_AF;        // every byte left over goes to fp32 slabs in flight
   s.na = na > VP_MAX_A ? VP_MAX_A : na;
-  s.mma_off = s.na * VP_AF;
-  s.stg_off = s.mma_off + s.ms * s.stage_bytes;        // 8 worker warps x [32][36] floats
-  s.red_off = s.stg_off + 8 * 32 * VP_STG_LD * 4;      // row statistics exchange: [2][128] x (n, mean, M2)
+  s.a16_off = s.na * VP_AF;                     // bf16 A ring: ms slabs of 8 KB
+  s.w_off = s.a16_off + s.ms * VP_AB;           // W ring: ms slabs
+  const int end = s.w_off + s.ms * s.wb_bytes;
+  s.stg_off = alias ? s.a16_off : end;
+  s.red_off = alias ? end : end + stg_bytes;    // row statistics exchange: [2][128] x (n, mean, M2)
   s.bar_off = s.red_off + 2 * 128 * 3 * 4;
   s.total = s.bar_off + (2 * VP_MAX_A + 3 * VP_STAGES + 2) * 8 + 16 + 1024;
   return s;
+}
+
+// true in exactly one lane of a converged warp
+__device__ __forceinline__ bool vp_elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 
 struct VpArgs {
@@ -65,7 +78,7 @@ struct VpArgs {
   const float* a2;
   const float* b2;
   void* out;
-  int N, D, d, out_bf16, tiles, nkb;
+  int N, D, d, out_bf16, tiles, nkb, ms;
   int rpc;   // > 0 (single-CTA form): CTA c owns rows [c*rpc, (c+1)*rpc) — equal shares, the last tile of a share is partial
   float eps;
 };
@@ -77,7 +90,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
   pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const VpSmem L = vp_smem(p.d, NCTA);
+  const VpSmem L = vp_smem(p.d, NCTA, p.ms);
   uint64_t* afull = (uint64_t*)(smem + L.bar_off);  // fp32 A slab landed
   uint64_t* aempty = afull + VP_MAX_A;              // fp32 A slab converted (4 worker-warp arrivals: one conversion group)
   uint64_t* wfull = aempty + VP_MAX_A;              // bf16 W slab landed
@@ -169,14 +182,16 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
           const int s = it % L.ms;
           mbar_wait(&empty[s], ((it / L.ms) & 1) ^ 1);
           mbar_expect_tx(&wfull[s], L.wb_bytes);
-          uint8_t* st = smem + L.mma_off + s * L.stage_bytes + VP_AB;
+          uint8_t* st = smem + L.w_off + s * L.wb_bytes;
           for (int hN = 0; hN < nhalf; ++hN)
             tma_load_2d(st + hN * wrows * VP_BK * 2, &map_w, &wfull[s], kb * VP_BK, hN * nmma + rank * wrows);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {   // the leader CTA issues for the pair
+    if (rank == 0) {   // the leader CTA issues for the pair.  The whole warp stays converged and one elected lane issues: in a
+                       // divergent single-lane region the compiler wraps every tcgen05 instruction in a uniform-register waterfall
+                       // loop, and the issue stream (~820 clk per slab in the timeline) was slower than the UMMAs it issues (512)
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nmma >> 3) << 17) | ((uint32_t)((128 * NCTA) >> 4) << 24);
       int it = 0, tc_ = 0;
       for (int ti = 0; ti < n_my; ++ti, ++tc_) {
@@ -189,22 +204,27 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
           if (NCTA == 2) mbar_wait_cluster(&conv[s], (it / L.ms) & 1);   // both A slabs converted, the peer's W half landed
           else mbar_wait(&conv[s], (it / L.ms) & 1);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + L.mma_off + s * L.stage_bytes);
-          const uint64_t ad = make_desc_sw64(sa);
+          if (vp_elect_one()) {
+            const uint32_t sa = smem_u32(smem + L.a16_off + s * VP_AB), sw = smem_u32(smem + L.w_off + s * L.wb_bytes);
+            const uint64_t ad = make_desc_sw64(sa);
 #pragma unroll
-          for (int k = 0; k < VP_BK / 16; ++k) {
-            for (int hN = 0; hN < nhalf; ++hN) {
-              const uint64_t wd = make_desc_sw64(sa + VP_AB + hN * wrows * VP_BK * 2);
-              if (NCTA == 2) tc_mma2(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
-              else tc_mma<false>(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            for (int k = 0; k < VP_BK / 16; ++k) {
+              for (int hN = 0; hN < nhalf; ++hN) {
+                const uint64_t wd = make_desc_sw64(sw + hN * wrows * VP_BK * 2);
+                if (NCTA == 2) tc_mma2(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                else tc_mma<false>(tmem_base + (uint32_t)(hN * nmma), ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+              }
             }
+            if (NCTA == 2) tc_commit2(&empty[s]);
+            else tc_commit(&empty[s]);
+            if (kb == p.nkb - 1) {
+              if (NCTA == 2) tc_commit2(acc_full);
+              else tc_commit(acc_full);
+            }
+            VTRACE(1, it);
           }
-          if (NCTA == 2) tc_commit2(&empty[s]);
-          else tc_commit(&empty[s]);
-          VTRACE(1, it);
+          __syncwarp();
         }
-        if (NCTA == 2) tc_commit2(acc_full);
-        else tc_commit(acc_full);
       }
     }
   } else {
@@ -229,7 +249,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         mbar_wait(&afull[sa], pa);
         if (warp == 2 && lane == 0) VTRACE(2, it);
         const uint32_t af = smem_u32(smem + sa * VP_AF) + (uint32_t)(crow * 128);
-        const uint32_t ab = smem_u32(smem + L.mma_off + s * L.stage_bytes) + (uint32_t)(crow * 64);
+        const uint32_t ab = smem_u32(smem + L.a16_off + s * VP_AB) + (uint32_t)(crow * 64);
         uint32_t pk[16];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {   // logical 16-byte chunk j of a SWIZZLE_128B row
@@ -382,7 +402,8 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
     return 0;
   static const int pair = getenv("BIST_VP_2CTA") ? atoi(getenv("BIST_VP_2CTA")) : 1;   // 0: one CTA per tile
   const int ncta = (pair && (d / (d > 256 ? 2 : 1)) % 32 == 0) ? 2 : 1;   // cta_group::2: UMMA N a multiple of 16 per CTA
-  const VpSmem L = vp_smem((int)d, ncta);
+  static const int ms_env = getenv("BIST_VP_STAGES") ? atoi(getenv("BIST_VP_STAGES")) : 0;   // MMA-ring depth (tuning aid)
+  const VpSmem L = vp_smem((int)d, ncta, ms_env);
   if (L.total > 227 * 1024 || L.na < 2) return 0;
   *taken = true;
   BIST_TRY(pack_matrix(W, wb, (int)d, (int)D, 0, 1.f, BIST_BF16, st));
@@ -402,6 +423,7 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   p.N = (int)N; p.D = (int)D; p.d = (int)d; p.out_bf16 = out_dtype == BIST_BF16;
   p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
   p.rpc = 0;
+  p.ms = ms_env;
   ProfScope ps("vidproj_fused", st);
   if (ncta == 2) {
     const int pairs = (p.tiles + 1) / 2, max_pairs = num_sms() / 2;
