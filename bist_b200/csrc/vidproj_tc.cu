@@ -371,6 +371,9 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         }
         __syncwarp();
       }
+      // the transposition buffers alias the bf16 A ring: no warp may start converting the next tile's slabs into it while another
+      // warp is still in its epilogue
+      if (L.stg_off == L.a16_off) asm volatile("bar.sync 1, 256;" ::: "memory");
     }
   }
   tc_fence_before();
