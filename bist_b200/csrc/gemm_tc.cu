@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
   const int ustep = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int it = 0;
       for (int tile = unit0; tile < t.total_tiles; tile += ustep) {
         const int z = tile / per_z, rem = tile - z * per_z;
@@ -110,23 +110,28 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
-          uint8_t* st = smem + s * S::STAGE_BYTES;
-          if (NCTA == 2) {
-            if (rank == 0) mbar_expect_tx(&full[s], 2 * S::STAGE_BYTES);   // both CTAs' A and W bytes land on the leader's barrier
-            tma_load_2d_pair(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-            tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
-          } else {
-            mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
-            tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-            if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
-            else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+          if (elect_one_lane()) {
+            uint8_t* st = smem + s * S::STAGE_BYTES;
+            if (NCTA == 2) {
+              if (rank == 0) mbar_expect_tx(&full[s], 2 * S::STAGE_BYTES);   // both CTAs' A and W bytes land on the leader's barrier
+              tma_load_2d_pair(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+              tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+            } else {
+              mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
+              tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+              if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
+              else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+            }
+            TRACE(0, it);
           }
-          TRACE(0, it);
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {
+      // The whole warp stays converged and ONE elected lane issues (elect.sync): in a divergent single-lane region the compiler wraps
+      // every tcgen05 instruction in a uniform-register waterfall loop (~110 clk per UMMA issued; an N = 64 UMMA executes in 32).
       // instruction descriptor (cute::UMMA::InstrDescriptor): D = f32, A/B = bf16 | tf32, K-major both
       const uint32_t fmt = TF32 ? 2u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
@@ -141,19 +146,24 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
           const int s = it % STAGES;
           mbar_wait(&full[s], (it / STAGES) & 1);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
-          const uint64_t ad = make_desc(sa), wd = make_desc(sa + S::A_BYTES);
+          if (elect_one_lane()) {
+            const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+            const uint64_t ad = make_desc(sa), wd = make_desc(sa + S::A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BKE / UMMA_K; ++k) {  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
-            if (NCTA == 2) tc_mma2(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
-            else tc_mma<TF32>(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            for (int k = 0; k < BKE / UMMA_K; ++k) {  // advance 32 bytes of K inside the swizzle atom: +2 in the address field
+              if (NCTA == 2) tc_mma2(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+              else tc_mma<TF32>(tacc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            }
+            if (NCTA == 2) tc_commit2(&empty[s]);
+            else tc_commit(&empty[s]);
+            if (kb == t.nkb - 1) {
+              if (NCTA == 2) tc_commit2(&acc_full[a]);
+              else tc_commit(&acc_full[a]);
+            }
+            TRACE(1, it);
           }
-          if (NCTA == 2) tc_commit2(&empty[s]);
-          else tc_commit(&empty[s]);
-          TRACE(1, it);
+          __syncwarp();
         }
-        if (NCTA == 2) tc_commit2(&acc_full[a]);
-        else tc_commit(&acc_full[a]);
       }
     }
   } else {

@@ -105,6 +105,13 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // generic-proxy smem writes -> visible to the async proxy (tcgen05.mma / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// true in exactly one lane of a converged warp (keeps issue instructions on the uniform datapath)
+__device__ __forceinline__ bool elect_one_lane() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- CTA-pair (cta_group::2) variants ---------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

@@ -80,24 +80,27 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
   const int nslab = min(t.slabs_per_split, t.total_slabs - slab0);  // >= 1 by construction
 
   if (warp == 0) {
-    if (lane == 0) {
+    {   // converged warp, one elected lane issues (see gemm_tc.cu)
       const long long ao = w.az.off(z, w.zin, 1), bo = w.bz.off(z, w.zin, 1);
       const int a_row = (int)(ao / t.a_ld), a_col = (int)(ao % t.a_ld) + n0;
       const int b_row = (int)(bo / t.b_ld), b_col = (int)(bo % t.b_ld) + k0;
       for (int i = 0; i < nslab; ++i) {
         const int s = i % STAGES;
         mbar_wait(&empty[s], ((i / STAGES) & 1) ^ 1);
-        mbar_expect_tx(&full[s], S::STAGE);
-        uint8_t* st = smem + s * S::STAGE;
-        const int m = (slab0 + i) * WT_R;
+        if (elect_one_lane()) {
+          mbar_expect_tx(&full[s], S::STAGE);
+          uint8_t* st = smem + s * S::STAGE;
+          const int m = (slab0 + i) * WT_R;
 #pragma unroll
-        for (int j = 0; j < 2; ++j) tma_load_2d(st + j * WT_BOX, &map_a, &full[s], a_col + j * 64, a_row + m);
+          for (int j = 0; j < 2; ++j) tma_load_2d(st + j * WT_BOX, &map_a, &full[s], a_col + j * 64, a_row + m);
 #pragma unroll
-        for (int j = 0; j < TN / 64; ++j) tma_load_2d(st + S::A_BYTES + j * WT_BOX, &map_b, &full[s], b_col + j * 64, b_row + m);
+          for (int j = 0; j < TN / 64; ++j) tma_load_2d(st + S::A_BYTES + j * WT_BOX, &map_b, &full[s], b_col + j * 64, b_row + m);
+        }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // D = f32, A = B = bf16, both MN-major (bits 15, 16), N = TN, M = 128
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(TN >> 3) << 17) |
                              ((uint32_t)(WT_TM >> 4) << 24);
@@ -105,14 +108,17 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
         const int s = i % STAGES;
         mbar_wait(&full[s], (i / STAGES) & 1);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * S::STAGE);
-        const uint64_t ad = make_desc_mn(sa, t.lbo, t.sbo), bd = make_desc_mn(sa + S::A_BYTES, t.lbo, t.sbo);
+        if (elect_one_lane()) {
+          const uint32_t sa = smem_u32(smem + s * S::STAGE);
+          const uint64_t ad = make_desc_mn(sa, t.lbo, t.sbo), bd = make_desc_mn(sa + S::A_BYTES, t.lbo, t.sbo);
 #pragma unroll
-        for (int k = 0; k < WT_R / 16; ++k)  // 16 m-rows per instruction = two 8-row groups = 2048 bytes
-          tc_mma<false>(tmem_base, ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc, (i | k) ? 1u : 0u);
-        tc_commit(&empty[s]);
+          for (int k = 0; k < WT_R / 16; ++k)  // 16 m-rows per instruction = two 8-row groups = 2048 bytes
+            tc_mma<false>(tmem_base, ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc, (i | k) ? 1u : 0u);
+          tc_commit(&empty[s]);
+          if (i == nslab - 1) tc_commit(acc_full);
+        }
+        __syncwarp();
       }
-      tc_commit(acc_full);
     }
   } else {
     const int lg = warp & 3;  // TMEM lane quarter this warp may read
