@@ -66,6 +66,20 @@ __host__ __device__ inline VpSmem vp_smem(int d, int ncta, int ms_override = 0) 
   return s;
 }
 
+// 32 accumulator columns -> registers without waiting (pair with vp_tmem_wait): the next chunk's load overlaps this chunk's math
+__device__ __forceinline__ void vp_tmem_ld32_nw(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void vp_tmem_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // true in exactly one lane of a converged warp
 __device__ __forceinline__ bool vp_elect_one() {
   uint32_t pred = 0;
@@ -78,7 +92,8 @@ struct VpArgs {
   const float* a2;
   const float* b2;
   void* out;
-  int N, D, d, out_bf16, tiles, nkb, ms;
+  int N, D, d, out_bf16, tiles, nkb, ms, grp;
+  float inv_dm1;   // 1 / (d - 1)
   int rpc;   // > 0 (single-CTA form): CTA c owns rows [c*rpc, (c+1)*rpc) — equal shares, the last tile of a share is partial
   float eps;
 };
@@ -152,7 +167,7 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         const int nb32 = (NCTA == 1 && p.rpc > 0 && own < 128) ? (own + 31) / 32 : 4;
         // two slabs (adjacent 128-byte segments of the same 128 feature rows) are requested back to back, so the second
         // finds the DRAM pages the first opened: 154.7 -> 144.9 us at config 2
-        const int grp = L.na >= 4 ? 2 : 1;
+        const int grp = p.grp > 0 ? p.grp : (L.na >= 4 ? 2 : 1);
         for (int kb = 0; kb < p.nkb; kb += grp) {
           const int n = p.nkb - kb < grp ? p.nkb - kb : grp;
           int s2 = sa, p2 = pa;
@@ -290,10 +305,15 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
       const uint32_t tacc = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * hcols);
       // pass 1: row statistics of relu(acc + bias) over this warp's column half (Chan's parallel update per 32 columns)
       float cnt = 0.f, mean = 0.f, m2 = 0.f;
+      uint32_t rn[32];                       // the next chunk's columns, in flight while this chunk is reduced
+      vp_tmem_ld32_nw(tacc, rn);
 #pragma unroll 1
       for (int c0 = 0; c0 < hcols; c0 += 32) {
         uint32_t r[32];
-        tmem_ld32(tacc + c0, r);
+        vp_tmem_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = rn[j];
+        if (c0 + 32 < hcols) vp_tmem_ld32_nw(tacc + c0 + 32, rn);
         const float* bp = p.bias + ch * hcols + c0;
         float sum = 0.f;
 #pragma unroll
@@ -309,9 +329,10 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         float qc = 0.f;
 #pragma unroll
         for (int j = 0; j < 32; ++j) { const float t = __uint_as_float(r[j]) - mc; qc = fmaf(t, t, qc); }
-        const float ncnt = cnt + 32.f, delta = mc - mean;
-        mean += delta * (32.f / ncnt);
-        m2 += qc + delta * delta * (cnt * 32.f / ncnt);
+        // (MUFU reciprocal: an IEEE division is a subroutine call per chunk; the ratio is 1 / (chunks so far))
+        const float ncnt = cnt + 32.f, delta = mc - mean, w32 = __fdividef(32.f, ncnt);
+        mean += delta * w32;
+        m2 += qc + delta * delta * (cnt * w32);
         cnt = ncnt;
       }
       {
@@ -320,16 +341,21 @@ __global__ void __launch_bounds__(352, 1) vidproj_kernel(const __grid_constant__
         asm volatile("bar.sync 1, 256;" ::: "memory");
         const float* oth = red + ((ch ^ 1) * 128 + lg * 32 + lane) * 3;
         const float on = oth[0], om = oth[1], oq = oth[2];
-        const float ncnt = cnt + on, delta = om - mean;
-        mean += delta * (on / ncnt);
-        m2 += oq + delta * delta * (cnt * on / ncnt);
+        const float ncnt = cnt + on, delta = om - mean, won = __fdividef(on, ncnt);
+        mean += delta * won;
+        m2 += oq + delta * delta * (cnt * won);
       }
-      const float inv = 1.f / (sqrtf(m2 / (float)(d - 1)) + p.eps);   // modules.py:30-31: unbiased std, eps on the std
+      vp_tmem_ld32_nw(tacc, rn);             // pass 2's first chunk
+      const float var = m2 * p.inv_dm1;
+      const float inv = __fdividef(1.f, var * rsqrtf(fmaxf(var, 1e-30f)) + p.eps);   // modules.py:30-31: unbiased std, eps on the std
       // pass 2: normalise, transpose through smem, gains + coalesced stores
 #pragma unroll 1
       for (int c0 = 0; c0 < hcols; c0 += 32) {
         uint32_t r[32];
-        tmem_ld32(tacc + c0, r);
+        vp_tmem_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = rn[j];
+        if (c0 + 32 < hcols) vp_tmem_ld32_nw(tacc + c0 + 32, rn);
         if (c0 + 32 >= hcols) {  // accumulator fully read by this warp
           tc_fence_before();
           __syncwarp();
@@ -426,7 +452,10 @@ int vidproj_fused(const float* fts, const float* W, const float* bias, const flo
   p.N = (int)N; p.D = (int)D; p.d = (int)d; p.out_bf16 = out_dtype == BIST_BF16;
   p.tiles = (int)((N + 127) / 128); p.nkb = (int)(D / VP_BK); p.eps = eps;
   p.rpc = 0;
+  p.inv_dm1 = 1.f / (float)(d - 1);
   p.ms = ms_env;
+  static const int grp_env = getenv("BIST_VP_GRP") ? atoi(getenv("BIST_VP_GRP")) : 0;
+  p.grp = grp_env;
   ProfScope ps("vidproj_fused", st);
   if (ncta == 2) {
     const int pairs = (p.tiles + 1) / 2, max_pairs = num_sms() / 2;
