@@ -452,7 +452,8 @@ __global__ void __launch_bounds__(384, 1) stage1_fused_kernel(const __grid_const
           bar_sync(1 + e, 128);   // all scores are in registers: the probabilities take their place
           S1FINE(5);
           if (act) {
-            const float ix = 1.f / sm.x, iy = 1.f / sm.y, iz = 1.f / sm.z, iw = 1.f / sm.w;
+            // (MUFU reciprocals: four IEEE divisions are four subroutine calls on the critical path of every pass)
+            const float ix = __fdividef(1.f, sm.x), iy = __fdividef(1.f, sm.y), iz = __fdividef(1.f, sm.z), iw = __fdividef(1.f, sm.w);
             // probabilities of a pair of groups: [key][2 x 16 query tokens] bf16, 64-byte rows, 16-byte chunks XOR-swizzled by (key >> 1) & 3
             const uint32_t pbase = pp + (uint32_t)((sgrp >> 1) * D.Kp16 * 64);
             const int ch = (sgrp & 1) * 2 + (slq >> 1);
