@@ -285,6 +285,8 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
   const int bl = blockIdx.x, b = bl / Lq;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cpr = d >> 3;
+  __shared__ uint8_t s_mask[256];   // key mask of the sample, fetched beside the tile (G <= 256 by the host check)
+  if (mask) { for (int g = threadIdx.x; g < G; g += 256) s_mask[g] = mask[(long long)b * G + g]; }
   // ---- stage X (G rows) and Q (h rows); zero the padding rows ---------------------------------------------------
   {
     const __nv_bfloat16* xg = x1 + (long long)bl * G * d;
@@ -331,7 +333,7 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
       float mx = -INFINITY;
       for (int g = lane; g < G; g += 32) {
         float sc = Ss[hh * Gp + g];
-        if (mask && mask[(long long)b * G + g] == 0) sc = kMaskFill;
+        if (mask && s_mask[g] == 0) sc = kMaskFill;
         Ss[hh * Gp + g] = sc;
         mx = fmaxf(mx, sc);
       }
@@ -343,7 +345,7 @@ __global__ void __launch_bounds__(256) stage2_mma_kernel(const __nv_bfloat16* __
         sum += e;
       }
       sum = warp_sum(sum);
-      const float inv = 1.f / sum;
+      const float inv = __fdividef(1.f, sum);
       float rs = 0.f;
       for (int g = lane; g < Gp; g += 32) {
         float pv = 0.f;
@@ -691,7 +693,7 @@ int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx,
 bool stage2_mma_supported(int G, int h, int d) {
   const int Gp = (G + 15) / 16 * 16;
   const size_t smem = (size_t)(Gp + 16) * (d + 8) * 2 + (size_t)16 * Gp * 4 + (size_t)16 * (Gp + 8) * 2;
-  return h <= 16 && d % 128 == 0 && smem <= 200 * 1024;
+  return h <= 16 && d % 128 == 0 && smem <= 200 * 1024 && G <= 256;
 }
 
 // bf16 tensor-core stage 2 (q, x1, out all bf16); *taken = false when the shape is left to the other kernels.
@@ -700,7 +702,7 @@ int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, in
   *taken = false;
   const int Gp = (G + 15) / 16 * 16;
   const size_t smem = (size_t)(Gp + 16) * (d + 8) * 2 + (size_t)16 * Gp * 4 + (size_t)16 * (Gp + 8) * 2;
-  if (h > 16 || d % 128 != 0 || smem > 200 * 1024) return 0;
+  if (h > 16 || d % 128 != 0 || smem > 200 * 1024 || G > 256) return 0;
   if ((reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(x1) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) return 0;
   *taken = true;
   static bool configured = false;

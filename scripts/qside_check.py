@@ -26,6 +26,9 @@ assert L.bist_debug_qside_trace(buf) == 0
 names = ["attn", "fold", "ffn1"]
 ev = ["start", "setup", "prev_done", "ln_done", "acc_full", "epi_done", "stores", "exit", "a_land", "gains", "ln_loop", "attn_staged", "attn_bar", "attn_scores", "attn_pv", "-"]
 for m in range(3):
+    if not any(buf[(m * 4 + s) * 16] for s in range(4)):
+        print("(no timeline: run with BIST_QSIDE_TRACE=1)")
+        break
     t0 = min(buf[(m * 4 + s) * 16] for s in range(4) if buf[(m * 4 + s) * 16])
     for s in range(4):
         row = [buf[(m * 4 + s) * 16 + e] for e in range(16)]
