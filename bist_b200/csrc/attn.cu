@@ -215,37 +215,88 @@ struct PackTable {
   int n;
 };
 
-// grid = total 32x32 destination tiles over all items; block (32, 8).  Both directions of the copy are coalesced
-// (transposes go through a padded shared-memory tile).
+// grid = total 64x64 destination tiles over all items; block 256.  Both directions of the copy are coalesced (transposes go
+// through a padded shared-memory tile) and, where the shapes allow, 16 bytes wide on the fp32 side and 8 bytes on the bf16 side:
+// the weights are re-packed after every optimizer step (68 M parameters into two bf16 orientations), so this is an HBM stream.
+constexpr int PK_T = 64;
+template <typename TD>
+__device__ __forceinline__ void pack_store4(TD* base, float* fbase, int to_f32, long long o, float a, float b, float c, float d) {
+  if (to_f32) *reinterpret_cast<float4*>(fbase + o) = make_float4(a, b, c, d);
+  else st4(base + o, make_float4(a, b, c, d));
+}
 template <typename TD>
 __global__ void __launch_bounds__(256) pack_many_kernel(const __grid_constant__ PackTable tab, TD* __restrict__ base, float* __restrict__ fbase) {
-  __shared__ float tile[32][33];
+  __shared__ float tile[PK_T][PK_T + 1];
   pdl_trigger();
   pdl_wait();
-  int i = 0;
-  while (i + 1 < tab.n && (int)blockIdx.x >= tab.it[i + 1].tile_begin) ++i;
-  const PackItem& p = tab.it[i];
+  int lo = 0, hi = tab.n - 1;   // item of this tile (tile_begin is increasing)
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if ((int)blockIdx.x >= tab.it[mid].tile_begin) lo = mid; else hi = mid - 1;
+  }
+  const PackItem& p = tab.it[lo];
   const int t = blockIdx.x - p.tile_begin;
-  const int tiles_c = (p.cols + 31) / 32;
-  const int r0 = (t / tiles_c) * 32, c0 = (t % tiles_c) * 32;
-  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int tiles_c = (p.cols + PK_T - 1) / PK_T;
+  const int r0 = (t / tiles_c) * PK_T, c0 = (t % tiles_c) * PK_T;
+  const int q = threadIdx.x & 15, rr = threadIdx.x >> 4;   // 16 threads x 4 elements per 64-wide row, 16 rows per pass
+  const TD* bchk = base + p.dst_off;
+  const float* fchk = fbase + p.dst_off;
+  const bool dst_vec = p.cols % 4 == 0 && p.dst_off % 4 == 0 &&
+                       ((p.to_f32 ? reinterpret_cast<uintptr_t>(fchk) % 16 : reinterpret_cast<uintptr_t>(bchk) % (4 * sizeof(TD))) == 0);
   if (p.transpose) {  // src is [cols, rows]: read rows c0.. of src (contiguous in r), write rows r0.. of dst (contiguous in c)
-    for (int j = ty; j < 32; j += 8)
-      if (c0 + j < p.cols && r0 + tx < p.rows) tile[j][tx] = p.src[(long long)(c0 + j) * p.rows + r0 + tx];
+    const bool src_vec = p.rows % 4 == 0 && reinterpret_cast<uintptr_t>(p.src) % 16 == 0;
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) {
+      const int j = ps * 16 + rr, c = c0 + j, r = r0 + 4 * q;
+      if (c < p.cols) {
+        if (src_vec && r + 3 < p.rows) {
+          const float4 v = *reinterpret_cast<const float4*>(p.src + (long long)c * p.rows + r);
+          tile[j][4 * q] = v.x; tile[j][4 * q + 1] = v.y; tile[j][4 * q + 2] = v.z; tile[j][4 * q + 3] = v.w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) if (r + e < p.rows) tile[j][4 * q + e] = p.src[(long long)c * p.rows + r + e];
+        }
+      }
+    }
     __syncthreads();
-    for (int j = ty; j < 32; j += 8)
-      if (r0 + j < p.rows && c0 + tx < p.cols) {
-        const float v = tile[tx][j] * p.scale;
-        const long long o = p.dst_off + (long long)(r0 + j) * p.cols + c0 + tx;
-        if (p.to_f32) fbase[o] = v; else base[o] = from_f32<TD>(v);
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) {
+      const int i = ps * 16 + rr, r = r0 + i, c = c0 + 4 * q;
+      if (r < p.rows) {
+        const long long o = p.dst_off + (long long)r * p.cols + c;
+        if (dst_vec && c + 3 < p.cols) {
+          pack_store4<TD>(base, fbase, p.to_f32, o, tile[4 * q][i] * p.scale, tile[4 * q + 1][i] * p.scale, tile[4 * q + 2][i] * p.scale,
+                          tile[4 * q + 3][i] * p.scale);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (c + e < p.cols) {
+              const float v = tile[4 * q + e][i] * p.scale;
+              if (p.to_f32) fbase[o + e] = v; else base[o + e] = from_f32<TD>(v);
+            }
+        }
       }
+    }
   } else {
-    for (int j = ty; j < 32; j += 8)
-      if (r0 + j < p.rows && c0 + tx < p.cols) {
-        const float v = p.src[(long long)(r0 + j) * p.cols + c0 + tx] * p.scale;
-        const long long o = p.dst_off + (long long)(r0 + j) * p.cols + c0 + tx;
-        if (p.to_f32) fbase[o] = v; else base[o] = from_f32<TD>(v);
+    const bool src_vec = p.cols % 4 == 0 && reinterpret_cast<uintptr_t>(p.src) % 16 == 0;
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) {
+      const int r = r0 + ps * 16 + rr, c = c0 + 4 * q;
+      if (r < p.rows) {
+        const long long si = (long long)r * p.cols + c, o = p.dst_off + si;
+        if (src_vec && dst_vec && c + 3 < p.cols) {
+          const float4 v = *reinterpret_cast<const float4*>(p.src + si);
+          pack_store4<TD>(base, fbase, p.to_f32, o, v.x * p.scale, v.y * p.scale, v.z * p.scale, v.w * p.scale);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (c + e < p.cols) {
+              const float v = p.src[si + e] * p.scale;
+              if (p.to_f32) fbase[o + e] = v; else base[o + e] = from_f32<TD>(v);
+            }
+        }
       }
+    }
   }
 }
 
@@ -260,11 +311,11 @@ int pack_many(const PackItem* items, int n, void* base, float* f32_base, int dty
     tab.it[i] = items[i];
     BIST_CHECK_ARG(items[i].src && items[i].rows > 0 && items[i].cols > 0, "pack_many: bad item");
     tab.it[i].tile_begin = tiles;
-    tiles += ((items[i].rows + 31) / 32) * ((items[i].cols + 31) / 32);
+    tiles += ((items[i].rows + PK_T - 1) / PK_T) * ((items[i].cols + PK_T - 1) / PK_T);
   }
   ProfScope ps("pack", st);
-  if (dtype == BIST_BF16) BIST_LAUNCH(pack_many_kernel<__nv_bfloat16>, dim3((unsigned)tiles), dim3(32, 8), 0, st, tab, (__nv_bfloat16*)base, f32_base);
-  else BIST_LAUNCH(pack_many_kernel<float>, dim3((unsigned)tiles), dim3(32, 8), 0, st, tab, (float*)base, f32_base);
+  if (dtype == BIST_BF16) BIST_LAUNCH(pack_many_kernel<__nv_bfloat16>, dim3((unsigned)tiles), 256, 0, st, tab, (__nv_bfloat16*)base, f32_base);
+  else BIST_LAUNCH(pack_many_kernel<float>, dim3((unsigned)tiles), 256, 0, st, tab, (float*)base, f32_base);
   BIST_LAUNCHED();
   return 0;
 }

@@ -1,0 +1,61 @@
+"""Where the headline training step's time goes: torch.profiler (CUPTI) kernel records of a few CUDA-graph replays of the config-3
+(+audio) step -> GPU-busy time (union of kernel intervals), concurrency, and the kernels by total time.  GPU box only."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from torch.profiler import ProfilerActivity, profile
+
+from bist_b200 import synth
+from bist_b200.core import FULL_SHAPES, full_model
+from bist_b200.graph import GraphedTrainStep
+
+dev = torch.device("cuda:0")
+fc = FULL_SHAPES
+model, lc = full_model("bf16", audio=True)
+model = model.to(dev).train()
+b = synth.make_full_batch(1, 64, fc["T"], fc["S"], fc["D"], fc["Lq"], fc["Lh"], fc["Lc"], fc["Lt"], fc["V"], Ta=fc["Ta"], Da=fc["Da"]).to(dev)
+params = list(model.parameters())
+opt = torch.optim.Adam(params, lr=1e-4, fused=True)
+step = GraphedTrainStep(lambda: lc.loss(model(b), b)[0], params, warmup=3)
+for _ in range(5):
+    step(); opt.step()
+torch.cuda.synchronize()
+n = 3
+with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+    for _ in range(n):
+        step(); opt.step()
+    torch.cuda.synchronize()
+iv = []
+import collections
+by = collections.defaultdict(lambda: [0, 0.0])
+for e in prof.events():
+    if e.device_type != torch.autograd.DeviceType.CUDA:
+        continue
+    t0 = e.time_range.start
+    t1 = e.time_range.end
+    if t1 <= t0:
+        continue
+    iv.append((t0, t1))
+    import re
+    m = re.search(r"(\w+_kernel\w*|ln_rows\w*|ln2_rows\w*)(<[^(]*>)?\(", e.name)
+    k = (m.group(1) + (m.group(2) or ""))[:60] if m else e.name.split("(")[0][-60:]
+    by[k][0] += 1
+    by[k][1] += (t1 - t0)
+iv.sort()
+busy, cur0, cur1 = 0.0, None, None
+for a, c in iv:
+    if cur1 is None or a > cur1:
+        if cur1 is not None:
+            busy += cur1 - cur0
+        cur0, cur1 = a, c
+    else:
+        cur1 = max(cur1, c)
+busy += (cur1 - cur0) if cur1 is not None else 0
+span = iv[-1][1] - iv[0][0]
+tot = sum(c - a for a, c in iv)
+print("kernel records %d over %d steps; span %.2f ms/step, GPU busy (union) %.2f ms/step, sum of kernel times %.2f ms/step (avg concurrency %.2f), idle %.2f ms/step"
+      % (len(iv), n, span / n / 1e3, busy / n / 1e3, tot / n / 1e3, tot / max(busy, 1), (span - busy) / n / 1e3))
+for k, (c, t) in sorted(by.items(), key=lambda kv: -kv[1][1])[:45]:
+    print("%-62s n/step %6.1f  %8.3f ms/step  avg %7.1f us" % (k, c / n, t / n / 1e3, t / c))
