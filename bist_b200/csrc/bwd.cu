@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(LnBwdArgs a, int rows_per_c
 // lane keeps the gain/offset gradients of its own columns in registers over all rows of the warp.
 template <typename TDY, typename TX, typename TDX, int MAXV>
 __global__ void __launch_bounds__(256) ln_bwd_vec_kernel(LnBwdArgs a, int rows_per_cta, int ctas_per_group) {
-  extern __shared__ float sacc[];  // [2][d]
+  extern __shared__ float sacc[];  // [8 warps][2][d]: per-warp partial sums, added up without atomics
   pdl_trigger();
   pdl_wait();
   const int d = (int)a.d, nv = d >> 2;
@@ -375,9 +375,6 @@ __global__ void __launch_bounds__(256) ln_bwd_vec_kernel(LnBwdArgs a, int rows_p
   const int64_t r_begin = grp * grows + (int64_t)cg * rows_per_cta;
   const int64_t r_end = min(grp * grows + grows, r_begin + rows_per_cta);
   const bool want_p = a.da != nullptr;
-  if (want_p)
-    for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) sacc[i] = 0.f;
-  __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float* a2 = a.a2 + grp * a.pstride;
   float4 ga[MAXV], pa[MAXV], pb[MAXV];
@@ -445,29 +442,27 @@ __global__ void __launch_bounds__(256) ln_bwd_vec_kernel(LnBwdArgs a, int rows_p
     }
   }
   if (want_p) {
+    // (shared-memory atomics from eight warps onto the same 2*d floats were most of this kernel's time)
+    float4* mine = reinterpret_cast<float4*>(sacc + (size_t)warp * 2 * d);
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
-      const int c = (lane + i * 32) * 4;
-      if (c < d) {
-        atomicAdd(&sacc[c], pa[i].x); atomicAdd(&sacc[c + 1], pa[i].y); atomicAdd(&sacc[c + 2], pa[i].z); atomicAdd(&sacc[c + 3], pa[i].w);
-        atomicAdd(&sacc[d + c], pb[i].x); atomicAdd(&sacc[d + c + 1], pb[i].y); atomicAdd(&sacc[d + c + 2], pb[i].z); atomicAdd(&sacc[d + c + 3], pb[i].w);
-      }
+      const int c = lane + i * 32;
+      if (c < nv) { mine[c] = pa[i]; mine[nv + c] = pb[i]; }
     }
     __syncthreads();
     float* da = a.da + grp * a.gstride;
     float* db = a.db + grp * a.gstride;
-    if ((((uintptr_t)da | (uintptr_t)db) & 15) == 0) {
-      // 16-byte vector reductions: a quarter of the L2 atomic operations (every CTA of the launch adds into the same 2*d floats)
-      const float4* s4 = reinterpret_cast<const float4*>(sacc);
-      for (int i = threadIdx.x; i < nv; i += blockDim.x) {
-        atomicAdd(reinterpret_cast<float4*>(da) + i, s4[i]);
-        atomicAdd(reinterpret_cast<float4*>(db) + i, s4[nv + i]);
+    const bool vec = (((uintptr_t)da | (uintptr_t)db) & 15) == 0;
+    for (int i = threadIdx.x; i < 2 * nv; i += blockDim.x) {   // float4 i of [da | db]
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < 8; ++w) {
+        const float4 v = reinterpret_cast<const float4*>(sacc + (size_t)w * 2 * d)[i];
+        t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
       }
-    } else {
-      for (int i = threadIdx.x; i < d; i += blockDim.x) {
-        atomicAdd(da + i, sacc[i]);
-        atomicAdd(db + i, sacc[d + i]);
-      }
+      float* dst = i < nv ? da + 4 * i : db + 4 * (i - nv);
+      if (vec) atomicAdd(reinterpret_cast<float4*>(dst), t);   // 16-byte vector reductions: a quarter of the L2 atomic operations
+      else { atomicAdd(dst, t.x); atomicAdd(dst + 1, t.y); atomicAdd(dst + 2, t.z); atomicAdd(dst + 3, t.w); }
     }
   }
 }
@@ -485,7 +480,7 @@ int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
   const int64_t cpg = (grows + per - 1) / per;
   ProfScope ps("ln_bwd", st);
   if (vec)
-    BIST_LAUNCH((ln_bwd_vec_kernel<TDY, TX, TDX, 4>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
+    BIST_LAUNCH((ln_bwd_vec_kernel<TDY, TX, TDX, 4>), (unsigned)(groups * cpg), 256, 8 * 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
   else
     BIST_LAUNCH((ln_bwd_kernel<TDY, TX, TDX>), (unsigned)(groups * cpg), 256, 2 * a.d * sizeof(float), st, a, (int)per, (int)cpg);
   BIST_LAUNCHED();
