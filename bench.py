@@ -438,7 +438,12 @@ def measure_train(args, env, mod, loss_fn, what, static_batch=None, host_batch=N
     set_grad_comm_dtype(torch.bfloat16 if wire_bf16 else torch.float32)
     B = env["rows_per_gpu"]
     plist = list(mod.parameters())
-    opt = torch.optim.Adam(plist, lr=1e-4, fused=True)
+    # Adam (what the reference's NoamOpt wraps) as ONE launch over all parameters (bist_adam_step); BIST_TORCH_ADAM=1: torch's fused Adam
+    if os.environ.get("BIST_TORCH_ADAM"):
+        opt = torch.optim.Adam(plist, lr=1e-4, fused=True)
+    else:
+        from bist_b200.optimize import FusedAdam
+        opt = FusedAdam(plist, lr=1e-4)
     ncoll = [0]
     has_counts = static_batch is not None and hasattr(static_batch, "ntokens")
     if has_counts:
@@ -480,7 +485,7 @@ def measure_train(args, env, mod, loss_fn, what, static_batch=None, host_batch=N
     clocks = sampler.stop() if sampler else None
     r = {"value": world * B / (tms * 1e-3), "unit": UNIT, "ms_per_step": tms, "steps": tsteps,
          "gpu_launches_per_step": int(per_step), "collectives_per_step": ncoll[0],
-         "launch": "eager" if args.no_graph else ("cuda_graph(fwd+loss+bwd%s) + fused Adam" % (" + all-reduce" if world > 1 and gstep and gstep.collectives else "")),
+         "launch": "eager" if args.no_graph else ("cuda_graph(fwd+loss+bwd%s) + one-launch Adam" % (" + all-reduce" if world > 1 and gstep and gstep.collectives else "")),
          "what": what}
     if world > 1:
         r["grad_comm_dtype"] = "bf16" if wire_bf16 else "fp32"

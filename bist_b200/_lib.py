@@ -102,6 +102,8 @@ SIGNATURES = {
                                  ctypes.POINTER(c_i64), ctypes.POINTER(c_i64), c_i64, c_p]),
     "bist_vidproj_fwd_bf16in": (c_i, [c_p] * 6 + [c_i64] * 3 + [c_f, c_p, c_sz, c_i, c_p]),
     "bist_debug_qside": (c_i, [c_i]),
+    "bist_adam_chunk_elems": (c_i, []),
+    "bist_adam_step": (c_i, [c_p, c_p, c_i, c_f, c_f, c_f, c_f, c_i64, c_p]),
     "bist_vidproj_fwd_noalloc": (c_i, [c_p] * 6 + [c_i64] * 3 + [c_f, c_i, c_p]),
     "bist_embed_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),
     "bist_embed_bwd": (c_i, [c_p, c_p, c_p, c_i64, c_i64, c_f, ctypes.c_uint64, ctypes.c_uint32, c_i, c_p]),

@@ -6,6 +6,8 @@ auto-encoder heads on ``cap_ft`` / ``temporal_ft`` / ``spatial_ft`` (/ ``audio_f
  """
 import torch
 
+from . import _lib
+
 
 class NoamOpt:
     "optimize.py:9-34 — lr = factor * d_model^-0.5 * min(step^-0.5, step * warmup^-1.5)."
@@ -103,3 +105,77 @@ class SimpleLossCompute:
         return {'out': parts['out'].item() * batch.ntokens.float(),
                 'temporal_ae': (parts['temporal_ft_ae'].detach() * batch.qntokens.float()) if 'temporal_ft_ae' in parts else zero,
                 'spatial_ae': (parts['spatial_ft_ae'].detach() * batch.qntokens.float()) if 'spatial_ft_ae' in parts else zero}
+
+
+class FusedAdam:
+    """torch.optim.Adam's update (no weight decay, no amsgrad — what the reference's NoamOpt wraps, optimize.py:9-34, train.py) for
+    all parameters in ONE kernel launch (bist_adam_step): a device table of {p, g, m, v, n} rows, rebuilt only when a gradient
+    tensor's address changes (inside a captured training step they never do).  Duck-types the parts of ``torch.optim.Optimizer``
+    that NoamOpt and the training loops use: ``param_groups`` (lr, betas, eps), ``step()``, ``zero_grad()``, ``state_dict()``."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        import numpy as np
+        self._np = np
+        self.params = [p for p in params if p.requires_grad]
+        assert self.params and all(p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() for p in self.params), \
+            "FusedAdam: contiguous fp32 CUDA parameters only"
+        self.param_groups = [{"params": self.params, "lr": lr, "betas": tuple(betas), "eps": eps}]
+        dev = self.params[0].device
+        n = sum(p.numel() for p in self.params)
+        self._m = torch.zeros(n, dtype=torch.float32, device=dev)      # one flat buffer each: views per parameter
+        self._v = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.state, off = {}, 0
+        for p in self.params:
+            self.state[p] = {"exp_avg": self._m[off:off + p.numel()].view_as(p), "exp_avg_sq": self._v[off:off + p.numel()].view_as(p)}
+            off += p.numel()
+        self.step_count = 0
+        self._key, self._rows, self._chunks, self._n_chunks, self._live = None, None, None, 0, None
+
+    def _table(self, live):
+        np = self._np
+        key = tuple((p.data_ptr(), p.grad.data_ptr()) for p in live)
+        if key == self._key:
+            return
+        L = _lib.lib()
+        ce = L.bist_adam_chunk_elems()
+        rows = np.zeros((len(live), 5), dtype=np.int64)
+        chunks = []
+        for i, p in enumerate(live):
+            g = p.grad
+            if g.dtype != torch.float32 or not g.is_contiguous():
+                raise RuntimeError("FusedAdam: gradients must be contiguous fp32 tensors")
+            st = self.state[p]
+            rows[i] = (p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel())
+            chunks += [(i, c) for c in range((p.numel() + ce - 1) // ce)]
+        dev = live[0].device
+        self._rows = torch.from_numpy(rows.view(np.uint8).reshape(-1).copy()).to(dev)
+        self._chunks = torch.tensor(chunks, dtype=torch.int32).reshape(-1).to(dev)
+        self._n_chunks, self._key, self._live = len(chunks), key, live
+
+    @torch.no_grad()
+    def step(self):
+        live = [p for p in self.params if p.grad is not None]
+        if not live:
+            return
+        self._table(live)
+        self.step_count += 1
+        g = self.param_groups[0]
+        _lib.check(_lib.lib().bist_adam_step(_lib.ptr(self._rows), _lib.ptr(self._chunks), self._n_chunks, float(g["lr"]), float(g["betas"][0]),
+                                             float(g["betas"][1]), float(g["eps"]), self.step_count, _lib.stream_ptr()), "bist_adam_step")
+        from .modules import weights_updated
+        weights_updated()                      # cached bf16 / packed / transposed weight copies are stale now
+
+    def zero_grad(self, set_to_none=True):
+        for p in self.params:
+            if set_to_none:
+                p.grad = None
+            elif p.grad is not None:
+                p.grad.zero_()
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self._m, "exp_avg_sq": self._v, "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}
+
+    def load_state_dict(self, sd):
+        self.step_count = int(sd["step"])
+        self._m.copy_(sd["exp_avg"])
+        self._v.copy_(sd["exp_avg_sq"])

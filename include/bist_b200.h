@@ -339,6 +339,14 @@ int bist_vidproj_fwd_bf16in(const void* fts16, const void* W16, const float* bia
 int bist_vidproj_fwd_noalloc(const float* fts, const float* W, const float* bias, const float* a_2, const float* b_2,
                              void* out, int64_t N, int64_t D, int64_t d, float eps, int out_dtype, void* stream);
 
+/* Adam step for every parameter in ONE launch — the optimizer of the reference's training loop (torch.optim.Adam behind NoamOpt,
+ * model/optimize.py:9-34; no weight decay, no amsgrad), same arithmetic as torch.optim.Adam.  `rows`: DEVICE array of
+ * {float* p, const float* g, float* m, float* v, int64 n} records (40 bytes each); `chunks`: DEVICE array of {int row, int piece}
+ * pairs, one per piece of bist_adam_chunk_elems() elements of a row; step >= 1 is the 1-based step count (bias correction). */
+int bist_adam_chunk_elems(void);
+int bist_adam_step(const void* rows, const void* chunks, int n_chunks, float lr, float beta1, float beta2, float eps, int64_t step,
+                   void* stream);
+
 /* n ragged host->device copies (src[i]: page-locked host rows, nbytes[i] to dst_base + dst_off[i]) each followed by the
  * zero fill of that video's padding (pad_nbytes[i] at dst_base + pad_off[i]), all on `stream`: the collate of
  * data/dataset.py:164-174 without a padded host copy. */

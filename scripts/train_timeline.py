@@ -17,7 +17,8 @@ model, lc = full_model("bf16", audio=True)
 model = model.to(dev).train()
 b = synth.make_full_batch(1, 64, fc["T"], fc["S"], fc["D"], fc["Lq"], fc["Lh"], fc["Lc"], fc["Lt"], fc["V"], Ta=fc["Ta"], Da=fc["Da"]).to(dev)
 params = list(model.parameters())
-opt = torch.optim.Adam(params, lr=1e-4, fused=True)
+from bist_b200.optimize import FusedAdam
+opt = torch.optim.Adam(params, lr=1e-4, fused=True) if os.environ.get('BIST_TORCH_ADAM') else FusedAdam(params, lr=1e-4)
 step = GraphedTrainStep(lambda: lc.loss(model(b), b)[0], params, warmup=3)
 for _ in range(5):
     step(); opt.step()
