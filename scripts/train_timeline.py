@@ -29,6 +29,7 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         step(); opt.step()
     torch.cuda.synchronize()
 iv = []
+named = []
 import collections
 by = collections.defaultdict(lambda: [0, 0.0])
 for e in prof.events():
@@ -44,6 +45,7 @@ for e in prof.events():
     k = (m.group(1) + (m.group(2) or ""))[:60] if m else e.name.split("(")[0][-60:]
     by[k][0] += 1
     by[k][1] += (t1 - t0)
+    named.append((t0, t1, k))
 iv.sort()
 busy, cur0, cur1 = 0.0, None, None
 for a, c in iv:
@@ -60,3 +62,24 @@ print("kernel records %d over %d steps; span %.2f ms/step, GPU busy (union) %.2f
       % (len(iv), n, span / n / 1e3, busy / n / 1e3, tot / n / 1e3, tot / max(busy, 1), (span - busy) / n / 1e3))
 for k, (c, t) in sorted(by.items(), key=lambda kv: -kv[1][1])[:45]:
     print("%-62s n/step %6.1f  %8.3f ms/step  avg %7.1f us" % (k, c / n, t / n / 1e3, t / c))
+
+# exclusive time: how long each kernel is the ONLY one on the GPU (the step's critical path runs through these)
+pts = []
+for a, c, k in named:
+    pts.append((a, 1, k))
+    pts.append((c, -1, k))
+pts.sort(key=lambda x: (x[0], x[1]))
+active, last, excl = {}, None, collections.defaultdict(float)
+for t, d_, k in pts:
+    if last is not None and len(active) == 1:
+        excl[next(iter(active))] += t - last
+    if d_ == 1:
+        active[k] = active.get(k, 0) + 1
+    else:
+        active[k] -= 1
+        if active[k] == 0:
+            del active[k]
+    last = t
+print("exclusive time (only kernel running), ms/step: total %.2f" % (sum(excl.values()) / n / 1e3))
+for k, t in sorted(excl.items(), key=lambda kv: -kv[1])[:22]:
+    print("   %-62s %7.3f" % (k, t / n / 1e3))
