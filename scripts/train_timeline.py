@@ -13,15 +13,34 @@ from bist_b200.graph import GraphedTrainStep
 
 dev = torch.device("cuda:0")
 fc = FULL_SHAPES
-model, lc = full_model("bf16", audio=True)
-model = model.to(dev).train()
-b = synth.make_full_batch(1, 64, fc["T"], fc["S"], fc["D"], fc["Lq"], fc["Lh"], fc["Lc"], fc["Lt"], fc["V"], Ta=fc["Ta"], Da=fc["Da"]).to(dev)
-params = list(model.parameters())
-from bist_b200.optimize import FusedAdam
-opt = torch.optim.Adam(params, lr=1e-4, fused=True) if os.environ.get('BIST_TORCH_ADAM') else FusedAdam(params, lr=1e-4)
-step = GraphedTrainStep(lambda: lc.loss(model(b), b)[0], params, warmup=3)
-for _ in range(5):
-    step(); opt.step()
+FORWARD = "--forward" in sys.argv      # the config-2 encoder forward (graph replay) instead of the training step
+if FORWARD:
+    from bist_b200 import VideoPath
+    vm = VideoPath(512, 8, 3, 2048, precision="bf16").to(dev)
+    vm.load_state_dict(synth.make_params(0, 512, 2048, 3), strict=True)
+    vb = synth.make_batch(1, 64, 40, 16, 2048, 16).to(dev)
+    veq = synth.make_encoded_query(1, 64, 16, 512).to(dev)
+    with torch.no_grad():
+        for _ in range(3):
+            vm(vb, veq)
+        gr = vm.capture(vb, veq)
+
+    class _Opt:
+        def step(self):
+            pass
+    step, opt = gr.replay, _Opt()
+    for _ in range(5):
+        step()
+model, lc = (None, None) if FORWARD else full_model("bf16", audio=True)
+if not FORWARD:
+    model = model.to(dev).train()
+    b = synth.make_full_batch(1, 64, fc["T"], fc["S"], fc["D"], fc["Lq"], fc["Lh"], fc["Lc"], fc["Lt"], fc["V"], Ta=fc["Ta"], Da=fc["Da"]).to(dev)
+    params = list(model.parameters())
+    from bist_b200.optimize import FusedAdam
+    opt = torch.optim.Adam(params, lr=1e-4, fused=True) if os.environ.get('BIST_TORCH_ADAM') else FusedAdam(params, lr=1e-4)
+    step = GraphedTrainStep(lambda: lc.loss(model(b), b)[0], params, warmup=3)
+    for _ in range(5):
+        step(); opt.step()
 torch.cuda.synchronize()
 n = 3
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:

@@ -61,6 +61,8 @@ def test_stage1_and_projection_outputs_keep_their_borders():
     from tests import stage1_ref as R
     L = _lib.lib()
     B, T, S, Lq, d, h = 5, 37, 9, 11, 256, 4
+    if not L.bist_stage1_fused_supported(B, T, S, Lq, d, h):
+        pytest.skip("fused stage 1 switched off (BIST_STAGE1_UNFUSED)")
     vft, tmask, dirs = R.make_inputs(3, B, T, S, Lq, d, h, DEV)
     raws, outs = [], []
     for k in (0, 1):
