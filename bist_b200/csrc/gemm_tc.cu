@@ -78,6 +78,9 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
+    // the first TMA instruction otherwise waits for its descriptor to be fetched: ask for both now, while the rest of the set-up runs
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_w)) : "memory");
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8 * NCTA); }
     fence_barrier_init();
@@ -101,12 +104,17 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
     {
       int it = 0;
       for (int tile = unit0; tile < t.total_tiles; tile += ustep) {
-        const int z = tile / per_z, rem = tile - z * per_z;
+        // (unbatched products skip the batch arithmetic: its 64-bit divisions were ~1.7 k clk in front of the first TMA request)
+        const int z = g.Z == 1 ? 0 : tile / per_z, rem = tile - z * per_z;
         const int m0 = (NCTA * (rem / t.tiles_n) + rank) * BM, nt = rem % t.tiles_n, n0 = nt * BN + rank * (BN / 2);
         // batch offsets become (row, column) coordinates inside the 2-D tensors
-        const long long ao = g.az.off(z, g.zin, g.zmid), wo = g.wz.off(z, g.zin, g.zmid);
-        const int a_row = (int)(ao / t.a_ld) + m0, a_col = (int)(ao % t.a_ld);
-        const int w_row = (int)(wo / t.w_ld) + n0, w_col = (int)(wo % t.w_ld);
+        long long ao = 0, wo = 0;
+        int a_row = m0, a_col = 0, w_row = n0, w_col = 0;
+        if (g.Z != 1) {
+          ao = g.az.off(z, g.zin, g.zmid); wo = g.wz.off(z, g.zin, g.zmid);
+          a_row = (int)(ao / t.a_ld) + m0; a_col = (int)(ao % t.a_ld);
+          w_row = (int)(wo / t.w_ld) + n0; w_col = (int)(wo % t.w_ld);
+        }
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
