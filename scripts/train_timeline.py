@@ -31,8 +31,27 @@ if FORWARD:
     step, opt = gr.replay, _Opt()
     for _ in range(5):
         step()
-model, lc = (None, None) if FORWARD else full_model("bf16", audio=True)
-if not FORWARD:
+model, lc = (None, None) if (FORWARD or "--video" in sys.argv) else full_model("bf16", audio=True)
+VIDEO = "--video" in sys.argv          # the video path alone in training (projection + 3 blocks + norms, MSE loss)
+if VIDEO and not FORWARD:
+    from bist_b200 import VideoPath
+    from bist_b200.optimize import FusedAdam
+    tm = VideoPath(512, 8, 3, 2048, dropout=0.1, precision="bf16").to(dev)
+    tm.load_state_dict(synth.make_params(0, 512, 2048, 3), strict=True)
+    tm.train()
+    vb = synth.make_batch(1, 64, 40, 16, 2048, 16).to(dev)
+    veq = synth.make_encoded_query(1, 64, 16, 512).to(dev)
+    tgt = torch.randn(64, 16, 512, device=dev)
+
+    def vloss():
+        o = tm(vb, veq)
+        return ((o["temporal_ft"] - tgt) ** 2).mean() + ((o["spatial_ft"] - tgt) ** 2).mean()
+    params = list(tm.parameters())
+    opt = FusedAdam(params, lr=1e-4)
+    step = GraphedTrainStep(vloss, params, warmup=3)
+    for _ in range(5):
+        step(); opt.step()
+if not FORWARD and not VIDEO:
     model = model.to(dev).train()
     b = synth.make_full_batch(1, 64, fc["T"], fc["S"], fc["D"], fc["Lq"], fc["Lh"], fc["Lc"], fc["Lt"], fc["V"], Ta=fc["Ta"], Da=fc["Da"]).to(dev)
     params = list(model.parameters())
