@@ -28,6 +28,7 @@ struct TcArgs {
   long long a_ld, w_ld;  // leading dimensions (elements) of the 2-D tensors the TMA maps describe
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
+  int lean;              // 1 = one batch, dense C (and R) rows, offsets below 2^31, no accumulate: the short epilogue
   int tiles_m, tiles_n, total_tiles;
   int bn_valid;          // output columns per N tile (== BN except in region mode)
   int w3d, s_box;        // region mode: W tile = 3-D box [s_box regions][wr_T rows][128 B]; w_stage_bytes of it land per slot
@@ -189,6 +190,153 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
     const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M;
     const bool c_bf16 = g.c_dtype == BIST_BF16, r_bf16 = g.r_dtype == BIST_BF16, has_r = g.R != nullptr;
     int tc_ = 0;
+    if (t.lean) {
+      // ---- short form for one batch with dense output (and residual) rows: the general form below spends ~300 instructions per
+      // 32-column chunk on row maps, 64-bit offsets and predicates, which made K <= 512 products epilogue-bound (8.4 k clk per
+      // 128 x 256 tile against 4.1 k clk of UMMAs).  Here offsets are 32-bit, the tile's bias slices are fetched before the
+      // accumulator is waited for, and the next chunk's TMEM load is in flight while this chunk is transposed and stored.
+      constexpr int NCH = CH_COLS / 32;
+      const uint32_t ldc = (uint32_t)g.c.si, ldr = (uint32_t)g.r.si;
+      const float* bias = g.bias;
+      char* const Cb = reinterpret_cast<char*>(g.C);
+      const char* const Rb = reinterpret_cast<const char*>(g.R);
+      __nv_bfloat16* const C2 = reinterpret_cast<__nv_bfloat16*>(g.C2);
+      for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
+        const int tm = tile / t.tiles_n, nt = tile - tm * t.tiles_n;
+        const int m0 = (NCTA * tm + rank) * BM, n0 = nt * t.bn_valid;
+        const int Ntot = min(g.N, n0 + t.bn_valid);
+        const int a = tc_ & 1;
+        const int colw = n0 + ch * CH_COLS;            // first column of this warp
+        const int row_w0 = m0 + lg * 32, row0 = row_w0 + sub_r;   // phase-2 rows of this lane: row0 + 4 * rr
+        float4 bvs[NCH];
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+          bvs[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (bias && colw + 32 * k + 32 <= Ntot) bvs[k] = __ldg(reinterpret_cast<const float4*>(bias + colw + 32 * k + sub_c));
+        }
+        const uint32_t co0 = (uint32_t)row0 * ldc + (uint32_t)(colw + sub_c);
+        const uint32_t ro0 = (uint32_t)row0 * ldr + (uint32_t)(colw + sub_c);
+        mbar_wait(&acc_full[a], (tc_ >> 1) & 1);
+        tc_fence_after();
+        if (warp == 2 && lane == 0) TRACE(2, 2 * tc_);
+        const uint32_t tacc = tmem_base + (uint32_t)(a * BN) + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * CH_COLS);
+        uint32_t r[32];
+        if (colw < Ntot) tmem_ld32_nowait(tacc, r);
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+          const int col = colw + 32 * k;
+          const bool live = col < Ntot;                // warp-uniform
+          const bool vec_chunk = col + 32 <= Ntot;
+          // this chunk's residual rows are requested before its accumulator columns are waited for
+          uint4 xr[8];
+          if (has_r && vec_chunk) {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+              xr[rr] = make_uint4(0u, 0u, 0u, 0u);
+              if (row0 + 4 * rr < Mtot) {
+                const uint32_t ro = ro0 + (uint32_t)(4 * rr) * ldr + (uint32_t)(32 * k);
+                if (r_bf16) {
+                  const uint2 u = *reinterpret_cast<const uint2*>(Rb + (size_t)ro * 2);
+                  xr[rr].x = u.x; xr[rr].y = u.y;
+                } else {
+                  xr[rr] = *reinterpret_cast<const uint4*>(Rb + (size_t)ro * 4);
+                }
+              }
+            }
+          }
+          if (live) tmem_ld_wait_all();
+          if (k == NCH - 1) {   // every TMEM load of this warp has landed: hand the accumulator stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (rank == 0) mbar_arrive(&acc_empty[a]);
+              else mbar_arrive_cta(&acc_empty[a], 0);
+            }
+          }
+          if (!live) continue;
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg_w + 16 * q), "r"(r[4 * q]), "r"(r[4 * q + 1]),
+                         "r"(r[4 * q + 2]), "r"(r[4 * q + 3])
+                         : "memory");
+          if (k + 1 < NCH && col + 32 < Ntot) tmem_ld32_nowait(tacc + 32 * (k + 1), r);   // r was consumed by the stores above
+          __syncwarp();
+          if (vec_chunk) {
+            float4 v[8];
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                           : "=f"(v[rr].x), "=f"(v[rr].y), "=f"(v[rr].z), "=f"(v[rr].w)
+                           : "r"(stg_r + (uint32_t)(rr * 4 * STG_LD * 4))
+                           : "memory");
+            const float4 bv = bvs[k];
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+              v[rr].x = fmaf(v[rr].x, alpha, bv.x); v[rr].y = fmaf(v[rr].y, alpha, bv.y);
+              v[rr].z = fmaf(v[rr].z, alpha, bv.z); v[rr].w = fmaf(v[rr].w, alpha, bv.w);
+            }
+            if (relu) {
+#pragma unroll
+              for (int rr = 0; rr < 8; ++rr) {
+                v[rr].x = fmaxf(v[rr].x, 0.f); v[rr].y = fmaxf(v[rr].y, 0.f);
+                v[rr].z = fmaxf(v[rr].z, 0.f); v[rr].w = fmaxf(v[rr].w, 0.f);
+              }
+            }
+            if (has_r) {
+              if (r_bf16) {
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) {
+                  v[rr].x += __uint_as_float(xr[rr].x << 16); v[rr].y += __uint_as_float(xr[rr].x & 0xffff0000u);
+                  v[rr].z += __uint_as_float(xr[rr].y << 16); v[rr].w += __uint_as_float(xr[rr].y & 0xffff0000u);
+                }
+              } else {
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) {
+                  v[rr].x += __uint_as_float(xr[rr].x); v[rr].y += __uint_as_float(xr[rr].y);
+                  v[rr].z += __uint_as_float(xr[rr].z); v[rr].w += __uint_as_float(xr[rr].w);
+                }
+              }
+            }
+            if (c_bf16) {
+#pragma unroll
+              for (int rr = 0; rr < 8; ++rr)
+                if (row0 + 4 * rr < Mtot)
+                  st4(reinterpret_cast<__nv_bfloat16*>(Cb) + (co0 + (uint32_t)(4 * rr) * ldc + (uint32_t)(32 * k)), v[rr]);
+            } else {
+#pragma unroll
+              for (int rr = 0; rr < 8; ++rr)
+                if (row0 + 4 * rr < Mtot)
+                  st4(reinterpret_cast<float*>(Cb) + (co0 + (uint32_t)(4 * rr) * ldc + (uint32_t)(32 * k)), v[rr]);
+            }
+            if (C2) {
+#pragma unroll
+              for (int rr = 0; rr < 8; ++rr)
+                if (row0 + 4 * rr < Mtot) st4(C2 + (co0 + (uint32_t)(4 * rr) * ldc + (uint32_t)(32 * k)), v[rr]);
+            }
+          } else {   // ragged last chunk of the matrix: one column per lane, row by row
+            const int cc = col + lane;
+            const float bs = (bias && cc < Ntot) ? bias[cc] : 0.f;
+            for (int lr = 0; lr < 32; ++lr) {
+              const int row = row_w0 + lr;
+              if (row < Mtot && cc < Ntot) {
+                float sv;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sv) : "r"(stg + (uint32_t)((lr * STG_LD + lane) * 4)) : "memory");
+                float o = fmaf(sv, alpha, bs);
+                if (relu) o = fmaxf(o, 0.f);
+                const size_t ro = (size_t)((uint32_t)row * ldr + (uint32_t)cc), co = (size_t)((uint32_t)row * ldc + (uint32_t)cc);
+                if (has_r)
+                  o += r_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(Rb)[ro]) : reinterpret_cast<const float*>(Rb)[ro];
+                if (c_bf16) reinterpret_cast<__nv_bfloat16*>(Cb)[co] = __float2bfloat16_rn(o);
+                else reinterpret_cast<float*>(Cb)[co] = o;
+                if (C2) C2[co] = __float2bfloat16_rn(o);
+              }
+            }
+          }
+          __syncwarp();
+        }
+        if (warp == 2 && lane == 0) TRACE(2, 2 * tc_ + 1);
+      }
+    } else
     for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
       const int z = tile / per_z, rem = tile - z * per_z;
       const int m0 = (NCTA * (rem / t.tiles_n) + rank) * BM, n0 = (rem % t.tiles_n) * t.bn_valid;
@@ -438,6 +586,13 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     const int rsz = g.r_dtype == BIST_BF16 ? 2 : 4;
     t.vec_c = t.vec_c && ((uintptr_t)g.R % 16 == 0) && al(g.r.si, rsz) && al(g.r.so, rsz) && al(g.rz.s0, rsz) && al(g.rz.s1, rsz) && al(g.rz.s2, rsz);
   }
+  {
+    static const bool lean_off = getenv("BIST_GEMM_GENERAL_EPILOGUE") != nullptr;   // debugging aid: A/B against the general epilogue
+    auto dense = [](const RowMap& m) { return m.inner == kNoSplit && m.mod == kNoSplit; };
+    const long long lim = 1ll << 31;
+    t.lean = !lean_off && t.vec_c && g.Z == 1 && !g.accumulate && dense(g.c) && g.c.si >= g.N && (long long)g.M * g.c.si < lim &&
+             (!g.R || (dense(g.r) && g.r.si >= g.N && (long long)g.M * g.r.si < lim));
+  }
   // tile width: minimise (waves over the SMs) x (per-tile cost ~ BN + fixed overhead)
   int bn = 64;
   {
@@ -467,7 +622,7 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     t.bn_valid = t.s_box * g.wr_T;
     t.w_stage_bytes = t.bn_valid * SLAB_BYTES;
     t.w_bt_elems = (long long)g.wr_S * w_ld;
-    if (t.bn_valid % 4 != 0) t.vec_c = 0;  // N tiles must start on a 16-byte boundary for the vector epilogue
+    if (t.bn_valid % 4 != 0) t.vec_c = t.lean = 0;  // N tiles must start on a 16-byte boundary for the vector epilogue
     BIST_TRY(make_map_3d(&mw, g.W, false, w_ld, w_rows / g.wr_S, g.wr_S, (long long)g.wr_S * w_ld * esz, w_ld * esz, SLAB_BYTES / esz,
                          g.wr_T, t.s_box));
   } else {
