@@ -29,6 +29,7 @@ struct TcArgs {
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
   int lean;              // 1 = one batch, dense C (and R) rows, offsets below 2^31, no accumulate: the short epilogue
+  int tma_c;             // 1 = lean, and no residual / second output / regions: the output leaves through TMA stores (map_c)
   int tiles_m, tiles_n, total_tiles;
   int bn_valid;          // output columns per N tile (== BN except in region mode)
   int w3d, s_box;        // region mode: W tile = 3-D box [s_box regions][wr_T rows][128 B]; w_stage_bytes of it land per slot
@@ -61,7 +62,8 @@ struct Smem {
 // and `acc_full` to both CTAs, the peer's epilogue warps hand the accumulator back with remote arrives.
 template <int BN, int STAGES, bool TF32, int NCTA = 1>
 __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                         const __grid_constant__ CUtensorMap map_w, const TcArgs t) {
+                                                         const __grid_constant__ CUtensorMap map_w,
+                                                         const __grid_constant__ CUtensorMap map_c, const TcArgs t) {
   using S = Smem<BN, STAGES, NCTA>;
   constexpr int ESZ = TF32 ? 4 : 2;
   constexpr int BKE = SLAB_BYTES / ESZ;        // elements of K per slab: 64 bf16 / 32 tf32
@@ -190,7 +192,113 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
     const int relu = g.relu, vec_c = t.vec_c, Mtot = g.M;
     const bool c_bf16 = g.c_dtype == BIST_BF16, r_bf16 = g.r_dtype == BIST_BF16, has_r = g.R != nullptr;
     int tc_ = 0;
-    if (t.lean) {
+    if (t.tma_c) {
+      // ---- plain products (bias / ReLU only): each lane keeps its accumulator row, adds the bias from a shared-memory copy of the
+      // tile's slice, converts, and writes 64 bytes of the row into a SWIZZLE_64B box that one TMA store per 32 x 64-byte box sends
+      // out (clipped at the matrix edge).  No transposition round trip, no global store instructions, no row predicates.
+      constexpr int NCH = CH_COLS / 32;
+      const uint32_t sbias = stg + 4096u;                      // behind the two 2 KB boxes of this warp (4608 B per warp)
+      const uint32_t my_box_row = (uint32_t)lane * 64u, swz = (uint32_t)((lane >> 1) & 3);
+      const float* bias = g.bias;
+      const int Ncols = g.N;
+      uint32_t nbox = 0;                                       // boxes sent so far: box buffer = nbox & 1
+      for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
+        const int tm = tile / t.tiles_n, nt = tile - tm * t.tiles_n;
+        const int m0 = (NCTA * tm + rank) * BM, n0 = nt * BN;
+        const int a = tc_ & 1;
+        const int colw = n0 + ch * CH_COLS, row_w0 = m0 + lg * 32;
+        if (4 * lane < CH_COLS) {                              // this warp's bias slice -> shared memory (zeros without a bias)
+          float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+          const int c = colw + 4 * lane;
+          if (bias) {
+            if (c + 3 < Ncols) b = __ldg(reinterpret_cast<const float4*>(bias + c));
+            else {
+              if (c < Ncols) b.x = bias[c];
+              if (c + 1 < Ncols) b.y = bias[c + 1];
+              if (c + 2 < Ncols) b.z = bias[c + 2];
+            }
+          }
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sbias + 16u * lane), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+        }
+        __syncwarp();
+        mbar_wait(&acc_full[a], (tc_ >> 1) & 1);
+        tc_fence_after();
+        if (warp == 2 && lane == 0) TRACE(2, 2 * tc_);
+        const uint32_t tacc = tmem_base + (uint32_t)(a * BN) + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * CH_COLS);
+        uint32_t r[32];
+        if (colw < Ncols) tmem_ld32_nowait(tacc, r);
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+          const int col = colw + 32 * k;
+          const bool live = col < Ncols;                       // warp-uniform
+          if (live) tmem_ld_wait_all();
+          if (k == NCH - 1) {   // every TMEM load of this warp has landed: hand the accumulator stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (rank == 0) mbar_arrive(&acc_empty[a]);
+              else mbar_arrive_cta(&acc_empty[a], 0);
+            }
+          }
+          if (!live) continue;
+          float o[32];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            float4 b;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "r"(sbias + (uint32_t)((32 * k + 4 * q) * 4)) : "memory");
+            o[4 * q] = fmaf(__uint_as_float(r[4 * q]), alpha, b.x);
+            o[4 * q + 1] = fmaf(__uint_as_float(r[4 * q + 1]), alpha, b.y);
+            o[4 * q + 2] = fmaf(__uint_as_float(r[4 * q + 2]), alpha, b.z);
+            o[4 * q + 3] = fmaf(__uint_as_float(r[4 * q + 3]), alpha, b.w);
+          }
+          if (k + 1 < NCH && col + 32 < Ncols) tmem_ld32_nowait(tacc + 32 * (k + 1), r);   // r is free: overlaps the stores below
+          if (relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o[j] = fmaxf(o[j], 0.f);
+          }
+          if (c_bf16) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const __nv_bfloat162 h = __floats2bfloat162_rn(o[2 * j], o[2 * j + 1]);
+              pk[j] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            const uint32_t box = stg + (nbox & 1u) * 2048u;
+            if (lane == 0) tma_store_wait_read<1>();           // the store that last read this box has finished with it
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box + my_box_row + (((uint32_t)q ^ swz) << 4)), "r"(pk[4 * q]),
+                           "r"(pk[4 * q + 1]), "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                           : "memory");
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) tma_store_2d(&map_c, box, col, row_w0);
+            ++nbox;
+          } else {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              if (col + 16 * hh < Ncols) {
+                const uint32_t box = stg + (nbox & 1u) * 2048u;
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(box + my_box_row + (((uint32_t)q ^ swz) << 4)),
+                               "f"(o[16 * hh + 4 * q]), "f"(o[16 * hh + 4 * q + 1]), "f"(o[16 * hh + 4 * q + 2]), "f"(o[16 * hh + 4 * q + 3])
+                               : "memory");
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) tma_store_2d(&map_c, box, col + 16 * hh, row_w0);
+                ++nbox;
+              }
+            }
+          }
+        }
+        if (warp == 2 && lane == 0) TRACE(2, 2 * tc_ + 1);
+      }
+      if (lane == 0) tma_store_wait_read<0>();                 // shared memory must outlive the last reads
+    } else if (t.lean) {
       // ---- short form for one batch with dense output (and residual) rows: the general form below spends ~300 instructions per
       // 32-column chunk on row maps, 64-bit offsets and predicates, which made K <= 512 products epilogue-bound (8.4 k clk per
       // 128 x 256 tile against 4.1 k clk of UMMAs).  Here offsets are 32-bit, the tile's bias slices are fetched before the
@@ -472,7 +580,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
 
 // ---------------------------------------------------------------------------------- host side
 template <int BN, int STAGES, bool TF32>
-int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
+int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, cudaStream_t st) {
   auto kern = gemm_tc_kernel<BN, STAGES, TF32>;
   constexpr int smem = Smem<BN, STAGES>::TOTAL;
   static bool configured = false;  // per instantiation
@@ -488,13 +596,13 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaSt
   int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
   if (t.g.max_ctas > 0 && grid > t.g.max_ctas) grid = t.g.max_ctas;
   ProfScope ps(t.g.tag, st);
-  BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, tt);
+  BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, mc, tt);
   BIST_LAUNCHED();
   return 0;
 }
 
 // CTA-pair form (bf16, BN = 256, plain W tiles): units are pairs of vertically adjacent row tiles, clusters of two CTAs.
-int launch_pair(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
+int launch_pair(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, cudaStream_t st) {
   auto kern = gemm_tc_kernel<256, 5, false, 2>;
   constexpr int smem = Smem<256, 5, 2>::TOTAL;
   static bool configured = false;
@@ -518,7 +626,7 @@ int launch_pair(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, c
   at[1].id = cudaLaunchAttributeClusterDimension;
   at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 2;
-  BIST_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, tt));
+  BIST_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, mc, tt));
   BIST_LAUNCHED();
   return 0;
 }
@@ -593,6 +701,10 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     t.lean = !lean_off && t.vec_c && g.Z == 1 && !g.accumulate && dense(g.c) && g.c.si >= g.N && (long long)g.M * g.c.si < lim &&
              (!g.R || (dense(g.r) && g.r.si >= g.N && (long long)g.M * g.r.si < lim));
   }
+  {
+    static const bool tma_off = getenv("BIST_GEMM_NO_TMA_STORE") != nullptr;   // debugging aid: A/B against the transposing epilogues
+    t.tma_c = !tma_off && t.lean && !regions && !g.R && !g.C2 && ((uintptr_t)g.C % 16 == 0) && (g.c.si * csz) % 16 == 0;
+  }
   // tile width: minimise (waves over the SMs) x (per-tile cost ~ BN + fixed overhead)
   int bn = 64;
   {
@@ -605,8 +717,10 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
       if (best < 0 || cost < best) { best = cost; bn = cand; }
     }
   }
-  CUtensorMap ma, mw;
+  CUtensorMap ma, mw, mc;
   BIST_TRY(make_map_2d(&ma, g.A, !bf, a_ld, a_rows, SLAB_BYTES / esz, BM, 128));
+  if (t.tma_c) BIST_TRY(make_map_c(&mc, g.C, g.c_dtype != BIST_BF16, g.N, g.c.si, g.M));
+  else mc = ma;   // never used, but a valid descriptor
   if (regions) {
     // N tiles own whole regions: s_box regions x wr_T rows each (<= BN rows of the MMA tile, the rest is never stored)
     const long long tm = (g.M + BM - 1) / BM, sms = num_sms();
@@ -626,21 +740,24 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     BIST_TRY(make_map_3d(&mw, g.W, false, w_ld, w_rows / g.wr_S, g.wr_S, (long long)g.wr_S * w_ld * esz, w_ld * esz, SLAB_BYTES / esz,
                          g.wr_T, t.s_box));
   } else {
-    static const int pair_rows = getenv("BIST_GEMM_2CTA") ? atoi(getenv("BIST_GEMM_2CTA")) : 0;   // min M for the CTA-pair form; 0 = off
+    // min M for the CTA-pair form (0 = off).  With the TMA-store epilogue the single-CTA form is bound by what an SM can pull from
+    // L2 (48 KB per K slab: ~7 k clk per K = 512 tile against 4.1 k clk of UMMAs); the pair pulls 32 KB: 44 -> 38 us at M = 40960,
+    // N = 1024, K = 512, no difference at M = 16384
+    static const int pair_rows = getenv("BIST_GEMM_2CTA") ? atoi(getenv("BIST_GEMM_2CTA")) : 24576;
     if (bf && bn == 256 && pair_rows > 0 && g.M >= pair_rows) {
       BIST_TRY(make_map_2d(&mw, g.W, false, w_ld, w_rows, SLAB_BYTES / esz, 128, 128));
-      return launch_pair(t, ma, mw, st);
+      return launch_pair(t, ma, mw, mc, st);
     }
     BIST_TRY(make_map_2d(&mw, g.W, !bf, w_ld, w_rows, SLAB_BYTES / esz, bn, 128));
   }
   if (bf) {
-    if (bn == 256) return launch<256, 3, false>(t, ma, mw, st);
-    if (bn == 128) return launch<128, 5, false>(t, ma, mw, st);
-    return launch<64, 7, false>(t, ma, mw, st);
+    if (bn == 256) return launch<256, 3, false>(t, ma, mw, mc, st);
+    if (bn == 128) return launch<128, 5, false>(t, ma, mw, mc, st);
+    return launch<64, 7, false>(t, ma, mw, mc, st);
   }
-  if (bn == 256) return launch<256, 3, true>(t, ma, mw, st);
-  if (bn == 128) return launch<128, 5, true>(t, ma, mw, st);
-  return launch<64, 7, true>(t, ma, mw, st);
+  if (bn == 256) return launch<256, 3, true>(t, ma, mw, mc, st);
+  if (bn == 128) return launch<128, 5, true>(t, ma, mw, mc, st);
+  return launch<64, 7, true>(t, ma, mw, mc, st);
 }
 
 }  // namespace bist

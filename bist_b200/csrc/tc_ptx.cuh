@@ -93,6 +93,16 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait_all() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// shared memory box -> global tensor (clipped at the tensor's bounds), as one bulk group of the issuing thread
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// the issuing thread waits until all but the newest `N` of its bulk groups have finished READING shared memory
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address
 // >> 4 in [0,14), LBO (ignored for swizzled K-major) = 1 in [16,30), SBO = 1024 B (8 rows x 128 B)
 // >> 4 in [32,46), version = 1 in [46,48), layout type SWIZZLE_128B = 2 in [61,64).
@@ -220,6 +230,23 @@ inline int make_map_2d(CUtensorMap* m, const void* base, bool f32, long long ld,
                   swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d): ld=%lld rows=%lld", (int)r, ld, rows); return BIST_ERR_CUDA; }
+  return 0;
+}
+
+// Output tensor of a product for TMA stores: [rows, cols] with leading dimension ld, boxes of 64-byte rows (16 fp32 / 32 bf16) x 32
+// rows in SWIZZLE_64B layout.  The inner extent is `cols`, not ld, so that stores are clipped at the last column.
+inline int make_map_c(CUtensorMap* m, const void* base, bool f32, long long cols, long long ld, long long rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return BIST_ERR_CUDA; }
+  const int esz = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(64 / esz), 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base),
+                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d) for an output map: cols=%lld ld=%lld rows=%lld", (int)r, cols, ld, rows); return BIST_ERR_CUDA; }
   return 0;
 }
 
