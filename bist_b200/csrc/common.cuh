@@ -210,6 +210,8 @@ struct GemmArgs {
   const void* A = nullptr;  // [M,K] rows via `a`, K contiguous
   const void* W = nullptr;  // [N,K] rows via `w`, K contiguous
   void* C = nullptr;        // [M,N] rows via `c`, N contiguous
+  const void* A2 = nullptr; // split-tf32 products (gemm_x3.cu; tensor-core path only): low halves with the layout of A and W;
+  const void* W2 = nullptr; //   C = act(alpha (A W^T + A2 W^T + A W2^T) + bias) + R in one launch, summed in the accumulator
   void* C2 = nullptr;       // optional bf16 copy of the output at the same element offsets as C (tensor-core path only)
   const float* bias = nullptr;  // [N] fp32 or null
   const void* R = nullptr;      // residual rows via `r`, N contiguous, or null

@@ -29,6 +29,7 @@ struct TcArgs {
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
   int lean;              // 1 = one batch, dense C (and R) rows, offsets below 2^31, no accumulate: the short epilogue
+  int npass;             // 1, or 3 = split-tf32 product A W^T + A2 W^T + A W2^T accumulated in TMEM (GemmArgs::A2 / W2)
   int tma_c;             // 1 = lean, and no residual / second output / regions: the output leaves through TMA stores (map_c)
   int tiles_m, tiles_n, total_tiles;
   int bn_valid;          // output columns per N tile (== BN except in region mode)
@@ -63,7 +64,9 @@ struct Smem {
 template <int BN, int STAGES, bool TF32, int NCTA = 1>
 __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                          const __grid_constant__ CUtensorMap map_w,
-                                                         const __grid_constant__ CUtensorMap map_c, const TcArgs t) {
+                                                         const __grid_constant__ CUtensorMap map_c,
+                                                         const __grid_constant__ CUtensorMap map_a2,
+                                                         const __grid_constant__ CUtensorMap map_w2, const TcArgs t) {
   using S = Smem<BN, STAGES, NCTA>;
   constexpr int ESZ = TF32 ? 4 : 2;
   constexpr int BKE = SLAB_BYTES / ESZ;        // elements of K per slab: 64 bf16 / 32 tf32
@@ -118,6 +121,10 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
           a_row = (int)(ao / t.a_ld) + m0; a_col = (int)(ao % t.a_ld);
           w_row = (int)(wo / t.w_ld) + n0; w_col = (int)(wo % t.w_ld);
         }
+        for (int pass = 0; pass < t.npass; ++pass) {
+        // split-tf32 products: pass 1 reads the low halves of A, pass 2 the low halves of W, into the same accumulator
+        const CUtensorMap* const pa = pass == 1 ? &map_a2 : &map_a;
+        const CUtensorMap* const pw = pass == 2 ? &map_w2 : &map_w;
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
@@ -129,13 +136,14 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
               tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
             } else {
               mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
-              tma_load_2d(st, &map_a, &full[s], a_col + kb * BKE, a_row);
+              tma_load_2d(st, pa, &full[s], a_col + kb * BKE, a_row);
               if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
-              else tma_load_2d(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+              else tma_load_2d(st + S::A_BYTES, pw, &full[s], w_col + kb * BKE, w_row);
             }
             TRACE(0, it);
           }
           __syncwarp();
+        }
         }
       }
     }
@@ -153,7 +161,8 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         else mbar_wait(&acc_empty[a], ((tc_ >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(a * BN);
-        for (int kb = 0; kb < t.nkb; ++kb, ++it) {
+        const int nkb_all = t.nkb * t.npass;
+        for (int kb = 0; kb < nkb_all; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&full[s], (it / STAGES) & 1);
           tc_fence_after();
@@ -167,7 +176,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
             }
             if (NCTA == 2) tc_commit2(&empty[s]);
             else tc_commit(&empty[s]);
-            if (kb == t.nkb - 1) {
+            if (kb == nkb_all - 1) {
               if (NCTA == 2) tc_commit2(&acc_full[a]);
               else tc_commit(&acc_full[a]);
             }
@@ -580,7 +589,8 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
 
 // ---------------------------------------------------------------------------------- host side
 template <int BN, int STAGES, bool TF32>
-int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, cudaStream_t st) {
+int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, const CUtensorMap& ma2,
+           const CUtensorMap& mw2, cudaStream_t st) {
   auto kern = gemm_tc_kernel<BN, STAGES, TF32>;
   constexpr int smem = Smem<BN, STAGES>::TOTAL;
   static bool configured = false;  // per instantiation
@@ -596,7 +606,7 @@ int launch(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, const 
   int grid = tt.total_tiles < num_sms() ? tt.total_tiles : num_sms();
   if (t.g.max_ctas > 0 && grid > t.g.max_ctas) grid = t.g.max_ctas;
   ProfScope ps(t.g.tag, st);
-  BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, mc, tt);
+  BIST_LAUNCH(kern, grid, 320, smem, st, ma, mw, mc, ma2, mw2, tt);
   BIST_LAUNCHED();
   return 0;
 }
@@ -626,7 +636,7 @@ int launch_pair(const TcArgs& t, const CUtensorMap& ma, const CUtensorMap& mw, c
   at[1].id = cudaLaunchAttributeClusterDimension;
   at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 2;
-  BIST_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, mc, tt));
+  BIST_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, mc, ma, mw, tt));
   BIST_LAUNCHED();
   return 0;
 }
@@ -717,8 +727,15 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
       if (best < 0 || cost < best) { best = cost; bn = cand; }
     }
   }
-  CUtensorMap ma, mw, mc;
+  CUtensorMap ma, mw, mc, ma2, mw2;
+  t.npass = 1;
+  if (g.A2 || g.W2) {   // split-tf32: the low halves mirror the layout of A and W
+    if (!tf || !g.A2 || !g.W2 || regions || (((uintptr_t)g.A2 | (uintptr_t)g.W2) % 16)) { *taken = false; return 0; }
+    t.npass = 3;
+  }
   BIST_TRY(make_map_2d(&ma, g.A, !bf, a_ld, a_rows, SLAB_BYTES / esz, BM, 128));
+  ma2 = ma;
+  if (t.npass == 3) BIST_TRY(make_map_2d(&ma2, g.A2, true, a_ld, a_rows, SLAB_BYTES / esz, BM, 128));
   if (t.tma_c) BIST_TRY(make_map_c(&mc, g.C, g.c_dtype != BIST_BF16, g.N, g.c.si, g.M));
   else mc = ma;   // never used, but a valid descriptor
   if (regions) {
@@ -750,14 +767,16 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     }
     BIST_TRY(make_map_2d(&mw, g.W, !bf, w_ld, w_rows, SLAB_BYTES / esz, bn, 128));
   }
+  mw2 = mw;
+  if (t.npass == 3) BIST_TRY(make_map_2d(&mw2, g.W2, true, w_ld, w_rows, SLAB_BYTES / esz, bn, 128));
   if (bf) {
-    if (bn == 256) return launch<256, 3, false>(t, ma, mw, mc, st);
-    if (bn == 128) return launch<128, 5, false>(t, ma, mw, mc, st);
-    return launch<64, 7, false>(t, ma, mw, mc, st);
+    if (bn == 256) return launch<256, 3, false>(t, ma, mw, mc, ma2, mw2, st);
+    if (bn == 128) return launch<128, 5, false>(t, ma, mw, mc, ma2, mw2, st);
+    return launch<64, 7, false>(t, ma, mw, mc, ma2, mw2, st);
   }
-  if (bn == 256) return launch<256, 3, true>(t, ma, mw, mc, st);
-  if (bn == 128) return launch<128, 5, true>(t, ma, mw, mc, st);
-  return launch<64, 7, true>(t, ma, mw, mc, st);
+  if (bn == 256) return launch<256, 3, true>(t, ma, mw, mc, ma2, mw2, st);
+  if (bn == 128) return launch<128, 5, true>(t, ma, mw, mc, ma2, mw2, st);
+  return launch<64, 7, true>(t, ma, mw, mc, ma2, mw2, st);
 }
 
 }  // namespace bist

@@ -2,8 +2,8 @@
 //   A = A_hi + A_lo,  W = W_hi + W_lo   with  x_hi = x with its 13 low mantissa bits cleared (exactly a tf32 value, so the
 //   tensor core's fp32 -> tf32 conversion cannot change it) and x_lo = x - x_hi (exact in fp32; 2^-11 of x at most)
 //   A W^T  ~=  A_hi W_hi^T + A_lo W_hi^T + A_hi W_lo^T          (the dropped A_lo W_lo^T term is 2^-22 relative)
-// as three tcgen05 kind::tf32 products accumulated in fp32 into C (GemmArgs::accumulate); bias, ReLU and the residual belong
-// to the last one.  The splits of the activations are written by one elementwise launch into caller-provided scratch that
+// as three tcgen05 kind::tf32 products summed in the TMEM accumulator of ONE launch (GemmArgs::A2 / W2: the K loop runs three
+// times over different operand pairs), so C is written once, with bias, ReLU and the residual, by the ordinary epilogue.  The splits of the activations are written by one elementwise launch into caller-provided scratch that
 // mirrors the operand's memory range; an operand that several products share (the video tensor) is split once.
 #include "common.cuh"
 
@@ -64,16 +64,10 @@ int gemm_fp32x3(const GemmArgs& g, const SplitRef& sa, const SplitRef& sw, cudaS
   if (!sw.ready) BIST_TRY(split_tf32(sw.src, sw.hi, sw.lo, sw.n, st));
   GemmArgs p = g;
   p.allow_tf32 = 1;
-  p.A = sa.hi + a_off; p.W = sw.hi + w_off; p.bias = nullptr; p.relu = 0; p.R = nullptr; p.accumulate = 0;
+  p.A = sa.hi + a_off; p.A2 = sa.lo + a_off; p.W = sw.hi + w_off; p.W2 = sw.lo + w_off;
   bool taken = false;
-  BIST_TRY(gemm_tc(p, st, &taken));
-  if (!taken) return gemm(g, st);           // (nothing has been written to C yet)
-  p.A = sa.lo + a_off; p.accumulate = 1;
-  BIST_TRY(gemm_tc(p, st, &taken));
-  BIST_CHECK_ARG(taken, "gemm_fp32x3: second pass declined");
-  p.A = sa.hi + a_off; p.W = sw.lo + w_off; p.bias = g.bias; p.relu = g.relu; p.R = g.R;
-  BIST_TRY(gemm_tc(p, st, &taken));
-  BIST_CHECK_ARG(taken, "gemm_fp32x3: third pass declined");
+  BIST_TRY(gemm_tc(p, st, &taken));      // one launch: the three products meet in the TMEM accumulator
+  if (!taken) return gemm(g, st);
   return 0;
 }
 
