@@ -705,6 +705,12 @@ int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, in
   if (h > 16 || d % 128 != 0 || smem > 200 * 1024 || G > 256) return 0;
   if ((reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(x1) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) return 0;
   *taken = true;
+  {
+    // pipelined persistent form (stage2_pipe.cu) when the shape fits it
+    bool piped = false;
+    BIST_TRY(stage2_pipe(q, x1, mask, out, B, G, Lq, h, d, st, &piped, ex));
+    if (piped) return 0;
+  }
   static bool configured = false;
   if (!configured) {
     BIST_CUDA(cudaFuncSetAttribute(stage2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -308,6 +308,9 @@ int stage2_attn(const float* qf, const void* x1, const uint8_t* mask, void* ctxx
 int stage2_mma(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d,
                cudaStream_t st, bool* taken, const Stage2Extra* ex = nullptr);  // bf16 q / x1 / out; attn_mma.cu
 bool stage2_mma_supported(int G, int h, int d);
+// persistent, TMA-pipelined form of stage2_mma (stage2_pipe.cu); *taken = false when the shape is left to stage2_mma's own kernel
+int stage2_pipe(const void* q, const void* x1, const uint8_t* mask, void* out, int B, int G, int Lq, int h, int d, cudaStream_t st,
+                bool* taken, const Stage2Extra* ex);
 // Fused self-attention over the query tokens (bf16): qkv [G*Lq, 3d] -> ctx [G*Lq, d]; key mask uint8 [(g % mask_mod), Lq].
 int self_attn_mma(const void* qkv, const uint8_t* mask, int mask_mod, void* ctx, int G, int Lq, int h, int dk, cudaStream_t st,
                   bool* taken);
