@@ -34,7 +34,7 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 }
 // SWIZZLE_128B: the 16-byte chunk index (address bits 4-6) is XORed with the 128-byte row index (bits 7-9); stage bases are 1 KB aligned
 __device__ __forceinline__ uint32_t sw128(uint32_t a) { return a ^ ((a >> 3) & 0x70u); }
-__device__ __forceinline__ void group_sync(int group) { asm volatile("bar.sync %0, 256;" ::"r"(group + 1) : "memory"); }
+__device__ __forceinline__ void group_sync(int group) { asm volatile("bar.sync %0, 256;" ::"r"(group + 1) : "memory"); }   // barrier 0 = __syncthreads
 __device__ __forceinline__ void bulk_store(void* gdst, uint32_t ssrc, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(ssrc), "r"(bytes) : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -49,7 +49,8 @@ struct S2Args {
   uint32_t x_bytes, q_bytes, stage_bytes, sp_bytes, s_floats;
 };
 
-__global__ void __launch_bounds__(544) stage2_pipe_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
+template <int NG>   // consumer groups
+__global__ void __launch_bounds__(32 * (8 * NG + 1)) stage2_pipe_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
                                                           const S2Args p) {
   extern __shared__ uint8_t smem_dyn[];
   pdl_trigger();
@@ -57,10 +58,10 @@ __global__ void __launch_bounds__(544) stage2_pipe_kernel(const __grid_constant_
   const int G = p.G, Gp = p.Gp, h = p.h, d = p.d, NS = p.NS, KS = p.KS;
   const int ldp = Gp + 8;
   const int lane = threadIdx.x & 31, warp_all = threadIdx.x >> 5;
-  const int group = warp_all >> 3, warp = warp_all & 7;                   // group 2 = the producer warp
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NS * p.stage_bytes + 2 * p.sp_bytes);
+  const int group = warp_all >> 3, warp = warp_all & 7;                   // group NG = the producer warp
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NS * p.stage_bytes + NG * p.sp_bytes);
   uint64_t* empty = full + NS;
-  float* Ss = reinterpret_cast<float*>(smem + (size_t)NS * p.stage_bytes + (size_t)(group & 1) * p.sp_bytes);
+  float* Ss = reinterpret_cast<float*>(smem + (size_t)NS * p.stage_bytes + (size_t)(group % NG) * p.sp_bytes);
   __nv_bfloat16* Ps = reinterpret_cast<__nv_bfloat16*>(Ss + p.s_floats);
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
@@ -70,7 +71,7 @@ __global__ void __launch_bounds__(544) stage2_pipe_kernel(const __grid_constant_
   }
   __syncthreads();
   pdl_wait();
-  if (group == 2) {
+  if (group == NG) {
     // ---- producer: the x1 tile and the query rows of a unit as two TMA requests, the key mask of the sample beside them
     int it = 0;
     for (int unit = blockIdx.x; unit < p.units; unit += gridDim.x, ++it) {
@@ -99,9 +100,9 @@ __global__ void __launch_bounds__(544) stage2_pipe_kernel(const __grid_constant_
     }
     return;
   }
-  // ---- consumers: group 0 takes the CTA's units 0, 2, 4, .., group 1 the others
+  // ---- consumers: group g takes the CTA's units g, g + NG, ..
   const uint32_t xpitch = (uint32_t)G * 128u, qpitch = (uint32_t)h * 128u;   // bytes between 64-column slabs
-  for (int it = group, unit = blockIdx.x + group * gridDim.x; unit < p.units; unit += 2 * gridDim.x, it += 2) {
+  for (int it = group, unit = blockIdx.x + group * gridDim.x; unit < p.units; unit += NG * gridDim.x, it += NG) {
     const int s = it % NS;
     uint8_t* st = smem + (size_t)s * p.stage_bytes;
     const uint32_t xs = smem_u32(st), qs = xs + p.x_bytes;
@@ -252,9 +253,16 @@ int stage2_pipe(const void* q, const void* x1, const uint8_t* mask, void* out, i
   p.stage_bytes = (p.x_bytes + p.q_bytes + 256u + 1023u) & ~1023u;
   p.s_floats = 8u * (uint32_t)(p.Gp > 128 ? p.Gp : 128);
   p.sp_bytes = p.s_floats * 4u + 16u * (uint32_t)(p.Gp + 8) * 2u;
-  const size_t fixed = 2 * (size_t)p.sp_bytes + 2 * 4 * 8 + 64 + 1024;
+  static const int ng_env = getenv("BIST_STAGE2_GROUPS") ? atoi(getenv("BIST_STAGE2_GROUPS")) : 0;
+  int ng = ng_env == 2 || ng_env == 3 ? ng_env : 3;
+  size_t fixed = ng * (size_t)p.sp_bytes + 2 * 4 * 8 + 64 + 1024;
   int ns = (int)((225 * 1024 - fixed) / p.stage_bytes);
-  ns = ns > 4 ? 4 : ns;
+  if (ns < ng + 1 && ng == 3) {   // three groups want four stages (one in flight beside the three in use)
+    ng = 2;
+    fixed = ng * (size_t)p.sp_bytes + 2 * 4 * 8 + 64 + 1024;
+    ns = (int)((225 * 1024 - fixed) / p.stage_bytes);
+  }
+  ns = ns > ng + 2 ? ng + 2 : ns;
   if (ns < 2) return 0;
   int ksplit = 1;                               // K splits of the score product: (Gp / 16) * ksplit <= 8 work items for 8 warps
   while (ksplit < 8 && (p.Gp / 16) * ksplit * 2 <= 8 && d / (ksplit * 2) % 64 == 0) ksplit *= 2;
@@ -270,13 +278,15 @@ int stage2_pipe(const void* q, const void* x1, const uint8_t* mask, void* out, i
   p.units = (int)units; p.G = G; p.Lq = Lq; p.h = h; p.d = d; p.NS = ns; p.KS = ksplit;
   static bool configured = false;
   if (!configured) {
-    BIST_CUDA(cudaFuncSetAttribute(stage2_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    BIST_CUDA(cudaFuncSetAttribute(stage2_pipe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    BIST_CUDA(cudaFuncSetAttribute(stage2_pipe_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     configured = true;
   }
   const size_t smem = (size_t)ns * p.stage_bytes + fixed;
   const int grid = units < num_sms() ? (int)units : num_sms();
   ProfScope ps("stage2_mma", st);
-  BIST_LAUNCH(stage2_pipe_kernel, dim3((unsigned)grid), 544, smem, st, mx, mq, p);
+  if (ng == 3) BIST_LAUNCH(stage2_pipe_kernel<3>, dim3((unsigned)grid), 800, smem, st, mx, mq, p);
+  else BIST_LAUNCH(stage2_pipe_kernel<2>, dim3((unsigned)grid), 544, smem, st, mx, mq, p);
   BIST_LAUNCHED();
   return 0;
 }
