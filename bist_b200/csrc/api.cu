@@ -87,6 +87,19 @@ int gemm(const GemmArgs& g, cudaStream_t st) {
   bool taken = false;
   int rc = gemm_tc(g, st, &taken);
   if (taken) return rc;
+  if (g.kcat > 1) {   // K-concatenated product outside the tensor-core path: one launch per part, parts after the first add onto C
+    BIST_CHECK_ARG(!g.relu && !g.C2 && g.Z == 1, "gemm: a K-concatenated product takes no ReLU, second output or batches");
+    for (int p = 0; p < g.kcat; ++p) {
+      GemmArgs q = g;
+      q.kcat = 1;
+      const int asz = g.a_dtype == BIST_BF16 ? 2 : 4, wsz = g.w_dtype == BIST_BF16 ? 2 : 4;
+      q.A = reinterpret_cast<const char*>(g.A) + (size_t)p * g.a_cat * asz;
+      q.W = reinterpret_cast<const char*>(g.W) + (size_t)p * g.w_cat * wsz;
+      if (p > 0) { q.bias = nullptr; q.R = g.C; q.r = g.c; q.rz = g.cz; q.r_dtype = g.c_dtype; }
+      BIST_TRY(gemm(q, st));
+    }
+    return 0;
+  }
   return gemm_simt(g, st);
 }
 

@@ -212,6 +212,9 @@ struct GemmArgs {
   void* C = nullptr;        // [M,N] rows via `c`, N contiguous
   const void* A2 = nullptr; // split-tf32 products (gemm_x3.cu; tensor-core path only): low halves with the layout of A and W;
   const void* W2 = nullptr; //   C = act(alpha (A W^T + A2 W^T + A W2^T) + bias) + R in one launch, summed in the accumulator
+  int kcat = 1;             // K concatenation: C = act(alpha sum_p A_p W_p^T + bias) + R with A_p = A + p * a_cat (columns of the same
+  long long a_cat = 0;      //   rows), W_p = W + p * w_cat (elements; a multiple of w's row stride), each part [., K]; one batch.  One
+  long long w_cat = 0;      //   launch on the tensor-core path; gemm() falls back to kcat accumulating launches
   void* C2 = nullptr;       // optional bf16 copy of the output at the same element offsets as C (tensor-core path only)
   const float* bias = nullptr;  // [N] fp32 or null
   const void* R = nullptr;      // residual rows via `r`, N contiguous, or null

@@ -29,7 +29,9 @@ struct TcArgs {
   int nkb;               // K / (elements per 128-byte slab)
   int vec_c;             // 1 = 16-byte aligned output rows (vector stores)
   int lean;              // 1 = one batch, dense C (and R) rows, offsets below 2^31, no accumulate: the short epilogue
-  int npass;             // 1, or 3 = split-tf32 product A W^T + A2 W^T + A W2^T accumulated in TMEM (GemmArgs::A2 / W2)
+  int npass;             // passes of the K loop into one accumulator: 3 = split-tf32 product A W^T + A2 W^T + A W2^T (GemmArgs::A2 /
+                         // W2, split = 1), or kcat parts of a K-concatenated product (split = 0)
+  int split, a_cat, w_cat_rows;
   int tma_c;             // 1 = lean, and no residual / second output / regions: the output leaves through TMA stores (map_c)
   int tiles_m, tiles_n, total_tiles;
   int bn_valid;          // output columns per N tile (== BN except in region mode)
@@ -123,8 +125,10 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
         }
         for (int pass = 0; pass < t.npass; ++pass) {
         // split-tf32 products: pass 1 reads the low halves of A, pass 2 the low halves of W, into the same accumulator
-        const CUtensorMap* const pa = pass == 1 ? &map_a2 : &map_a;
-        const CUtensorMap* const pw = pass == 2 ? &map_w2 : &map_w;
+        const CUtensorMap* const pa = (t.split && pass == 1) ? &map_a2 : &map_a;
+        const CUtensorMap* const pw = (t.split && pass == 2) ? &map_w2 : &map_w;
+        // K concatenation (GemmArgs::kcat): part `pass` of A sits a_cat columns further right, its W block w_cat_rows rows further down
+        const int a_colp = a_col + (t.split ? 0 : pass * t.a_cat), w_rowp = w_row + (t.split ? 0 : pass * t.w_cat_rows);
         for (int kb = 0; kb < t.nkb; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
@@ -132,13 +136,13 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
             uint8_t* st = smem + s * S::STAGE_BYTES;
             if (NCTA == 2) {
               if (rank == 0) mbar_expect_tx(&full[s], 2 * S::STAGE_BYTES);   // both CTAs' A and W bytes land on the leader's barrier
-              tma_load_2d_pair(st, &map_a, &full[s], a_col + kb * BKE, a_row);
-              tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_row);
+              tma_load_2d_pair(st, &map_a, &full[s], a_colp + kb * BKE, a_row);
+              tma_load_2d_pair(st + S::A_BYTES, &map_w, &full[s], w_col + kb * BKE, w_rowp);
             } else {
               mbar_expect_tx(&full[s], S::A_BYTES + t.w_stage_bytes);
-              tma_load_2d(st, pa, &full[s], a_col + kb * BKE, a_row);
+              tma_load_2d(st, pa, &full[s], a_colp + kb * BKE, a_row);
               if (t.w3d) tma_load_3d(st + S::A_BYTES, &map_w, &full[s], kb * BKE, (int)(wo / t.w_bt_elems), nt * t.s_box);
-              else tma_load_2d(st + S::A_BYTES, pw, &full[s], w_col + kb * BKE, w_row);
+              else tma_load_2d(st + S::A_BYTES, pw, &full[s], w_col + kb * BKE, w_rowp);
             }
             TRACE(0, it);
           }
@@ -728,10 +732,18 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     }
   }
   CUtensorMap ma, mw, mc, ma2, mw2;
-  t.npass = 1;
+  t.npass = 1; t.split = 0; t.a_cat = 0; t.w_cat_rows = 0;
+  if (g.kcat > 1) {   // C = A_0 W_0^T + A_1 W_1^T + ..: parts side by side in A's rows, W blocks one below the other
+    if (g.A2 || g.W2 || regions || g.Z != 1 || g.w_cat % w_ld != 0 || g.a_cat * (g.kcat - 1) + g.K > a_ld || g.a_cat % bke != 0) {
+      *taken = false;
+      return 0;
+    }
+    t.npass = g.kcat; t.a_cat = (int)g.a_cat; t.w_cat_rows = (int)(g.w_cat / w_ld);
+    w_rows += (long long)(g.kcat - 1) * t.w_cat_rows;
+  }
   if (g.A2 || g.W2) {   // split-tf32: the low halves mirror the layout of A and W
     if (!tf || !g.A2 || !g.W2 || regions || (((uintptr_t)g.A2 | (uintptr_t)g.W2) % 16)) { *taken = false; return 0; }
-    t.npass = 3;
+    t.npass = 3; t.split = 1;
   }
   BIST_TRY(make_map_2d(&ma, g.A, !bf, a_ld, a_rows, SLAB_BYTES / esz, BM, 128));
   ma2 = ma;

@@ -748,14 +748,17 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
       v.a_dtype = adt; v.b_dtype = dtype; v.tag = "bwd_scores_dqf";
       BIST_TRY(wgrad(v, st));
     }
-    {
-      GemmArgs g;  // d_vft += dXV[:, u-slice] . W_v1
-      g.A = c.act(D.dxv, (long long)u * d); g.W = c.Mshared(L.wv1T + (size_t)(c.pu0 + u) * dd); g.C = d_vft; g.R = d_vft;
-      g.M = (int)(B * TS); g.N = di; g.K = di;
-      g.a = rows_dense(xvld); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
-      g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = BIST_F32; g.r_dtype = BIST_F32; g.tag = "bwd_xv_gemm";
-      BIST_TRY(gemm(g, st));
-    }
+  }
+  {
+    // d_vft += sum_u dXV[:, u-slice] . W_v1[u]: the directions' value gradients sit side by side in dXV's rows and their weights one
+    // after the other, so the sum over u is ONE K-concatenated product and d_vft (fp32, 84 MB at config 3) is read and written once
+    GemmArgs g;
+    g.A = c.act(D.dxv, 0); g.W = c.Mshared(L.wv1T + (size_t)c.pu0 * dd); g.C = d_vft; g.R = d_vft;
+    g.M = (int)(B * TS); g.N = di; g.K = di;
+    g.kcat = nd; g.a_cat = d; g.w_cat = dd;
+    g.a = rows_dense(xvld); g.w = rows_dense(d); g.c = rows_dense(d); g.r = rows_dense(d);
+    g.a_dtype = adt; g.w_dtype = dtype; g.c_dtype = BIST_F32; g.r_dtype = BIST_F32; g.tag = "bwd_xv_gemm";
+    BIST_TRY(gemm(g, st));
   }
   {
     WgradArgs w;  // dW_v1[u] += dXV[:, u-slice]^T vft ; db_v1[u] += colsum
