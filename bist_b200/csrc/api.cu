@@ -88,7 +88,7 @@ int gemm(const GemmArgs& g, cudaStream_t st) {
   int rc = gemm_tc(g, st, &taken);
   if (taken) return rc;
   if (g.kcat > 1) {   // K-concatenated product outside the tensor-core path: one launch per part, parts after the first add onto C
-    BIST_CHECK_ARG(!g.relu && !g.C2 && g.Z == 1, "gemm: a K-concatenated product takes no ReLU, second output or batches");
+    BIST_CHECK_ARG(!g.relu && !g.C2, "gemm: a K-concatenated product takes no ReLU or second output");
     for (int p = 0; p < g.kcat; ++p) {
       GemmArgs q = g;
       q.kcat = 1;

@@ -987,7 +987,8 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
   const int b = g / a.gdiv, gi = g % a.gdiv;
   const int R = Lq * h;
   TS* ds = reinterpret_cast<TS*>(a.ds) + (long long)b * R * a.TS;
-  TS* dsT = reinterpret_cast<TS*>(a.dsT) + (long long)b * a.TS * R;
+  const long long ldt = a.dsT_ld > 0 ? a.dsT_ld : R;
+  TS* dsT = reinterpret_cast<TS*>(a.dsT) + (long long)b * a.TS * ldt;
   if (a.ds)
     for (int i = t; i < R * nk; i += nt) {  // k fastest: ds[b][r][ts]
       const int r = i / nk, k = i % nk;
@@ -995,7 +996,7 @@ __global__ void __launch_bounds__(256) stage1_bwd_kernel(Stage1BwdArgs a) {
     }
   for (int i = t; i < R * nk; i += nt) {  // r fastest: dsT[b][ts][r]
     const int k = i / R, r = i % R;
-    dsT[((long long)gi * a.ts_g + k * a.ts_k) * R + r] = from_f32<TS>(Ps[r * nkp + k]);
+    dsT[((long long)gi * a.ts_g + k * a.ts_k) * ldt + r] = from_f32<TS>(Ps[r * nkp + k]);
   }
 }
 

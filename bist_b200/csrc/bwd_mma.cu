@@ -271,10 +271,11 @@ __global__ void __launch_bounds__(256) stage1_bwd_mma_kernel(Stage1BwdArgs a) {
       for (int c = lane * 8; c < d; c += 256) *reinterpret_cast<uint4*>(drow + c) = *reinterpret_cast<const uint4*>(Vs + (size_t)k * ldv + c);
     }
     const int b = g / a.gdiv, gi = g % a.gdiv;
-    __nv_bfloat16* dsT = reinterpret_cast<__nv_bfloat16*>(a.dsT) + (long long)b * a.TS * R;
-    const bool v8 = (R % 8) == 0;
+    const long long ldt = a.dsT_ld > 0 ? a.dsT_ld : R;
+    __nv_bfloat16* dsT = reinterpret_cast<__nv_bfloat16*>(a.dsT) + (long long)b * a.TS * ldt;
+    const bool v8 = (R % 8) == 0 && (ldt % 8) == 0;
     for (int k = warp; k < nk; k += 8) {
-      __nv_bfloat16* drow = dsT + ((long long)gi * a.ts_g + (long long)k * a.ts_k) * R;
+      __nv_bfloat16* drow = dsT + ((long long)gi * a.ts_g + (long long)k * a.ts_k) * ldt;
       if (v8) {
         for (int c = lane * 8; c < R; c += 256) *reinterpret_cast<uint4*>(drow + c) = *reinterpret_cast<const uint4*>(Ts + (size_t)k * ldr + c);
       } else {

@@ -213,7 +213,7 @@ struct GemmArgs {
   const void* A2 = nullptr; // split-tf32 products (gemm_x3.cu; tensor-core path only): low halves with the layout of A and W;
   const void* W2 = nullptr; //   C = act(alpha (A W^T + A2 W^T + A W2^T) + bias) + R in one launch, summed in the accumulator
   int kcat = 1;             // K concatenation: C = act(alpha sum_p A_p W_p^T + bias) + R with A_p = A + p * a_cat (columns of the same
-  long long a_cat = 0;      //   rows), W_p = W + p * w_cat (elements; a multiple of w's row stride), each part [., K]; one batch.  One
+  long long a_cat = 0;      //   rows), W_p = W + p * w_cat (elements; a multiple of w's row stride), each part [., K], in every batch.  One
   long long w_cat = 0;      //   launch on the tensor-core path; gemm() falls back to kcat accumulating launches
   void* C2 = nullptr;       // optional bf16 copy of the output at the same element offsets as C (tensor-core path only)
   const float* bias = nullptr;  // [N] fp32 or null
@@ -453,6 +453,7 @@ struct Stage1BwdArgs {
   int gdiv = 1, TS = 0;
   long long ts_g = 0, ts_k = 0;
   int ds_dtype = BIST_F32;
+  int dsT_ld = 0;   // elements between rows of dsT (0 = Lq * h: dense); wider when several directions' dsT sit side by side
 };
 int stage1_bwd(const Stage1BwdArgs& a, cudaStream_t st);      // a.ds may be null (only dsT is written); tensor cores when possible
 int stage1_bwd_mma(const Stage1BwdArgs& a, cudaStream_t st, bool* taken);  // bwd_mma.cu

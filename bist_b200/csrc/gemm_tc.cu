@@ -318,12 +318,20 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
       // accumulator is waited for, and the next chunk's TMEM load is in flight while this chunk is transposed and stored.
       constexpr int NCH = CH_COLS / 32;
       const uint32_t ldc = (uint32_t)g.c.si, ldr = (uint32_t)g.r.si;
-      const float* bias = g.bias;
       char* const Cb = reinterpret_cast<char*>(g.C);
       const char* const Rb = reinterpret_cast<const char*>(g.R);
       __nv_bfloat16* const C2 = reinterpret_cast<__nv_bfloat16*>(g.C2);
       for (int tile = unit0; tile < t.total_tiles; tile += ustep, ++tc_) {
-        const int tm = tile / t.tiles_n, nt = tile - tm * t.tiles_n;
+        int z = 0, rem = tile;
+        uint32_t cz0 = 0, rz0 = 0;
+        const float* bias = g.bias;
+        if (g.Z != 1) {                                 // batch offsets once per tile (host check: all below 2^31)
+          z = tile / per_z; rem = tile - z * per_z;
+          cz0 = (uint32_t)g.cz.off(z, g.zin, g.zmid);
+          if (has_r) rz0 = (uint32_t)g.rz.off(z, g.zin, g.zmid);
+          if (bias) bias += g.bz.off(z, g.zin, g.zmid);
+        }
+        const int tm = rem / t.tiles_n, nt = rem - tm * t.tiles_n;
         const int m0 = (NCTA * tm + rank) * BM, n0 = nt * t.bn_valid;
         const int Ntot = min(g.N, n0 + t.bn_valid);
         const int a = tc_ & 1;
@@ -335,8 +343,8 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
           bvs[k] = make_float4(0.f, 0.f, 0.f, 0.f);
           if (bias && colw + 32 * k + 32 <= Ntot) bvs[k] = __ldg(reinterpret_cast<const float4*>(bias + colw + 32 * k + sub_c));
         }
-        const uint32_t co0 = (uint32_t)row0 * ldc + (uint32_t)(colw + sub_c);
-        const uint32_t ro0 = (uint32_t)row0 * ldr + (uint32_t)(colw + sub_c);
+        const uint32_t co0 = cz0 + (uint32_t)row0 * ldc + (uint32_t)(colw + sub_c);
+        const uint32_t ro0 = rz0 + (uint32_t)row0 * ldr + (uint32_t)(colw + sub_c);
         mbar_wait(&acc_full[a], (tc_ >> 1) & 1);
         tc_fence_after();
         if (warp == 2 && lane == 0) TRACE(2, 2 * tc_);
@@ -444,7 +452,7 @@ __global__ void __launch_bounds__(320, 1) gemm_tc_kernel(const __grid_constant__
                 asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sv) : "r"(stg + (uint32_t)((lr * STG_LD + lane) * 4)) : "memory");
                 float o = fmaf(sv, alpha, bs);
                 if (relu) o = fmaxf(o, 0.f);
-                const size_t ro = (size_t)((uint32_t)row * ldr + (uint32_t)cc), co = (size_t)((uint32_t)row * ldc + (uint32_t)cc);
+                const size_t ro = (size_t)(rz0 + (uint32_t)row * ldr + (uint32_t)cc), co = (size_t)(cz0 + (uint32_t)row * ldc + (uint32_t)cc);
                 if (has_r)
                   o += r_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(Rb)[ro]) : reinterpret_cast<const float*>(Rb)[ro];
                 if (c_bf16) reinterpret_cast<__nv_bfloat16*>(Cb)[co] = __float2bfloat16_rn(o);
@@ -712,12 +720,20 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
     static const bool lean_off = getenv("BIST_GEMM_GENERAL_EPILOGUE") != nullptr;   // debugging aid: A/B against the general epilogue
     auto dense = [](const RowMap& m) { return m.inner == kNoSplit && m.mod == kNoSplit; };
     const long long lim = 1ll << 31;
-    t.lean = !lean_off && t.vec_c && g.Z == 1 && !g.accumulate && dense(g.c) && g.c.si >= g.N && (long long)g.M * g.c.si < lim &&
-             (!g.R || (dense(g.r) && g.r.si >= g.N && (long long)g.M * g.r.si < lim));
+    // batches: the largest batch offset of C (and R) must keep element offsets below 2^31 as well
+    long long cmax = 0, rmax = 0;
+    bool zok = g.Z <= 4096;
+    for (int z = 0; zok && z < g.Z; ++z) {
+      const long long co = g.cz.off(z, g.zin, g.zmid), ro = g.R ? g.rz.off(z, g.zin, g.zmid) : 0;
+      if (co < 0 || ro < 0) zok = false;
+      cmax = co > cmax ? co : cmax; rmax = ro > rmax ? ro : rmax;
+    }
+    t.lean = !lean_off && t.vec_c && zok && !g.accumulate && dense(g.c) && g.c.si >= g.N && cmax + (long long)g.M * g.c.si < lim &&
+             (!g.R || (dense(g.r) && g.r.si >= g.N && rmax + (long long)g.M * g.r.si < lim));
   }
   {
     static const bool tma_off = getenv("BIST_GEMM_NO_TMA_STORE") != nullptr;   // debugging aid: A/B against the transposing epilogues
-    t.tma_c = !tma_off && t.lean && !regions && !g.R && !g.C2 && ((uintptr_t)g.C % 16 == 0) && (g.c.si * csz) % 16 == 0;
+    t.tma_c = !tma_off && t.lean && g.Z == 1 && !regions && !g.R && !g.C2 && ((uintptr_t)g.C % 16 == 0) && (g.c.si * csz) % 16 == 0;
   }
   // tile width: minimise (waves over the SMs) x (per-tile cost ~ BN + fixed overhead)
   int bn = 64;
@@ -734,7 +750,7 @@ int gemm_tc(const GemmArgs& g, cudaStream_t st, bool* taken) {
   CUtensorMap ma, mw, mc, ma2, mw2;
   t.npass = 1; t.split = 0; t.a_cat = 0; t.w_cat_rows = 0;
   if (g.kcat > 1) {   // C = A_0 W_0^T + A_1 W_1^T + ..: parts side by side in A's rows, W blocks one below the other
-    if (g.A2 || g.W2 || regions || g.Z != 1 || g.w_cat % w_ld != 0 || g.a_cat * (g.kcat - 1) + g.K > a_ld || g.a_cat % bke != 0) {
+    if (g.A2 || g.W2 || regions || g.w_cat % w_ld != 0 || g.a_cat * (g.kcat - 1) + g.K > a_ld || g.a_cat % bke != 0) {
       *taken = false;
       return 0;
     }

@@ -132,7 +132,7 @@ BwdWs carve_bwd(void* base, size_t cap, int64_t B, int64_t T, int64_t S, int64_t
   W.dffh = a(nd * Q * dff); W.dn = a(2 * nd * Q * d); W.dc = a(nd * Q * d); W.du2 = a(nd * Q * h * d);
   W.dqf12 = a(2 * nd * Q * h * d); W.dq12 = a(2 * nd * Q * d);
   W.dxv = a((size_t)B * T * S * nd * d);
-  W.qf1T = a(Q * h * d); W.dsT = a(Q * h * T * S);
+  W.qf1T = a(nd * Q * h * d); W.dsT = a(nd * Q * h * T * S);   // both directions side by side (one product into d_vft)
   W.dqkv0 = a(nd * Q * 3 * d);
   for (int u = 0; u < 2; ++u) { W.dout1[u] = nullptr; W.dc1[u] = nullptr; }
   for (int u = 0; u < nd; ++u) {
@@ -724,30 +724,35 @@ extern "C" int bist_st_layer_bwd(const float* d_out_t2s, const float* d_out_s2t,
                       c.drop(S_ST1_P + u, c.p_attn));
     a.dctx = D.dc1[u];
     a.dV = c.act(D.dxv, (long long)u * d);
-    a.ds = nullptr; a.dsT = D.dsT; a.gdiv = G; a.TS = (int)TS;
+    const int R = (int)(Lq * h);
+    a.ds = nullptr; a.dsT = c.act(D.dsT, (long long)u * R); a.dsT_ld = nd * R; a.gdiv = G; a.TS = (int)TS;   // dsT [B][TS][nd * R]
     a.ts_g = t2s ? 1 : S; a.ts_k = t2s ? S : 1;
     a.ds_dtype = adt;
     BIST_TRY(stage1_bwd(a, st));
-    const int R = (int)(Lq * h);
     {
-      // d_vft[b][ts, :] += sum_r dsT[b][ts, r] qf1[b][r, :]  as an NT product against qf1^T [d, R]
-      BIST_TRY(transpose_batched(c.act(W.qf12, (long long)u * Qd * h), D.qf1T, B, R, d, adt, st));
-      GemmArgs g;
-      g.A = D.dsT; g.W = D.qf1T; g.C = d_vft; g.R = d_vft;
-      g.M = (int)TS; g.N = di; g.K = R;
-      g.a = rows_dense(R); g.w = rows_dense(R); g.c = rows_dense(d); g.r = rows_dense(d);
-      g.Z = (int)B; g.zin = 1;
-      g.az = {TS * R, 0}; g.wz = {(long long)d * R, 0}; g.cz = {TS * d, 0}; g.rz = {TS * d, 0};
-      g.a_dtype = adt; g.w_dtype = adt; g.c_dtype = BIST_F32; g.r_dtype = BIST_F32; g.tag = "bwd_scores_dvft";
-      BIST_TRY(gemm(g, st));
+      // qf1^T [B][d][R] of this direction for the product into d_vft below
+      BIST_TRY(transpose_batched(c.act(W.qf12, (long long)u * Qd * h), c.act(D.qf1T, (long long)u * B * d * R), B, R, d, adt, st));
       WgradArgs v;  // dqf1[b][r, :] += sum_ts dsT[b][ts, r] vft[b][ts, :]
-      v.A = D.dsT; v.B = vft; v.C = D.dqf1 + u * Qd * h;
-      v.M = (int)TS; v.N = R; v.K = di; v.lda = R; v.ldb = d; v.ldc = d;
+      v.A = c.act(D.dsT, (long long)u * R); v.B = vft; v.C = D.dqf1 + u * Qd * h;
+      v.M = (int)TS; v.N = R; v.K = di; v.lda = nd * R; v.ldb = d; v.ldc = d;
       v.Z = (int)B; v.zin = 1;
-      v.az = {TS * R, 0}; v.bz = {TS * d, 0}; v.cz = {(long long)R * d, 0};
+      v.az = {TS * nd * R, 0}; v.bz = {TS * d, 0}; v.cz = {(long long)R * d, 0};
       v.a_dtype = adt; v.b_dtype = dtype; v.tag = "bwd_scores_dqf";
       BIST_TRY(wgrad(v, st));
     }
+  }
+  {
+    // d_vft[b][ts, :] += sum_u sum_r dsT_u[b][ts, r] qf1_u[b][r, :]: NT products against qf1_u^T [d, R], the directions K-concatenated
+    const int R = (int)(Lq * h);
+    GemmArgs g;
+    g.A = D.dsT; g.W = D.qf1T; g.C = d_vft; g.R = d_vft;
+    g.M = (int)TS; g.N = di; g.K = R;
+    g.kcat = nd; g.a_cat = R; g.w_cat = (long long)B * d * R;
+    g.a = rows_dense((long long)nd * R); g.w = rows_dense(R); g.c = rows_dense(d); g.r = rows_dense(d);
+    g.Z = (int)B; g.zin = 1;
+    g.az = {TS * nd * R, 0}; g.wz = {(long long)d * R, 0}; g.cz = {TS * d, 0}; g.rz = {TS * d, 0};
+    g.a_dtype = adt; g.w_dtype = adt; g.c_dtype = BIST_F32; g.r_dtype = BIST_F32; g.tag = "bwd_scores_dvft";
+    BIST_TRY(gemm(g, st));
   }
   {
     // d_vft += sum_u dXV[:, u-slice] . W_v1[u]: the directions' value gradients sit side by side in dXV's rows and their weights one
