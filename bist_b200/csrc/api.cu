@@ -180,6 +180,54 @@ __global__ void __launch_bounds__(256) dropout_residual_kernel(const T* __restri
     out[i] = from_f32<T>(fmaf(to_f32(y[i]), drop_mul(drop, (unsigned long long)i), to_f32(x[i])));
 }
 
+// eight elements per thread and iteration, hash key computed once (n % 8 == 0, n < 2^32, 16-byte aligned pointers)
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_residual8_kernel(const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ out,
+                                                                uint32_t n8, DropCfg drop) {
+  pdl_trigger();
+  pdl_wait();
+  uint32_t key = 0u;
+  const bool on = drop.thresh != 0u;
+  if (on) {   // drop_hash() with the high half of the element index equal to zero
+    const unsigned long long seed = drop.step ? drop.seed + __ldg(drop.step) : drop.seed;
+    key = mix32((uint32_t)(seed >> 32) + drop.site * 0x85EBCA6Bu) ^ (uint32_t)seed;
+  }
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += gridDim.x * blockDim.x) {
+    float yv[8], xv[8];
+    if (sizeof(T) == 2) {
+      const uint4 uy = *reinterpret_cast<const uint4*>(y + (size_t)i * 8), ux = *reinterpret_cast<const uint4*>(x + (size_t)i * 8);
+      const uint32_t wy[4] = {uy.x, uy.y, uy.z, uy.w}, wx[4] = {ux.x, ux.y, ux.z, ux.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        yv[2 * j] = __uint_as_float(wy[j] << 16); yv[2 * j + 1] = __uint_as_float(wy[j] & 0xffff0000u);
+        xv[2 * j] = __uint_as_float(wx[j] << 16); xv[2 * j + 1] = __uint_as_float(wx[j] & 0xffff0000u);
+      }
+    } else {
+      const float4 a = reinterpret_cast<const float4*>(y)[(size_t)i * 2], b = reinterpret_cast<const float4*>(y)[(size_t)i * 2 + 1];
+      const float4 c = reinterpret_cast<const float4*>(x)[(size_t)i * 2], e = reinterpret_cast<const float4*>(x)[(size_t)i * 2 + 1];
+      yv[0] = a.x; yv[1] = a.y; yv[2] = a.z; yv[3] = a.w; yv[4] = b.x; yv[5] = b.y; yv[6] = b.z; yv[7] = b.w;
+      xv[0] = c.x; xv[1] = c.y; xv[2] = c.z; xv[3] = c.w; xv[4] = e.x; xv[5] = e.y; xv[6] = e.z; xv[7] = e.w;
+    }
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float m = on ? (mix32((i * 8u + (uint32_t)j) ^ key) >= drop.thresh ? drop.scale : 0.f) : drop.scale;
+      o[j] = fmaf(yv[j], m, xv[j]);
+    }
+    if (sizeof(T) == 2) {
+      uint4 u;
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(o[0], o[1]), h1 = __floats2bfloat162_rn(o[2], o[3]);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(o[4], o[5]), h3 = __floats2bfloat162_rn(o[6], o[7]);
+      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+      u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+      *reinterpret_cast<uint4*>(out + (size_t)i * 8) = u;
+    } else {
+      reinterpret_cast<float4*>(out)[(size_t)i * 2] = make_float4(o[0], o[1], o[2], o[3]);
+      reinterpret_cast<float4*>(out)[(size_t)i * 2 + 1] = make_float4(o[4], o[5], o[6], o[7]);
+    }
+  }
+}
+
 // Ingest gather: the zero-padded device batch is written by ONE kernel whose threads read the page-locked host rows of
 // each video directly over PCIe (unified addressing maps pinned host memory into the device's address space) — every
 // video's transfer is in flight at once, instead of one DMA descriptor after the other with a set-up gap between them.
@@ -546,6 +594,15 @@ int bist_dropout_add_fwd(const void* y, const void* x, void* out, int64_t rows, 
   const int64_t n = rows * d;
   const DropCfg drop = make_drop(p, seed, site);
   ProfScope ps("dropout", st);
+  if (n % 8 == 0 && n < (1LL << 32) && (((uintptr_t)y | (uintptr_t)x | (uintptr_t)out) & 15) == 0) {
+    const unsigned g8 = (unsigned)std::min<int64_t>((n / 8 + 255) / 256, 148 * 8);
+    if (dtype == BIST_BF16)
+      BIST_LAUNCH(dropout_residual8_kernel<__nv_bfloat16>, g8, 256, 0, st, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, (uint32_t)(n / 8), drop);
+    else
+      BIST_LAUNCH(dropout_residual8_kernel<float>, g8, 256, 0, st, (const float*)y, (const float*)x, (float*)out, (uint32_t)(n / 8), drop);
+    BIST_LAUNCHED();
+    return 0;
+  }
   const unsigned grid = (unsigned)std::min<int64_t>((n + 255) / 256, 148 * 8);
   if (dtype == BIST_BF16)
     BIST_LAUNCH(dropout_residual_kernel<__nv_bfloat16>, grid, 256, 0, st, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, n, drop);

@@ -816,8 +816,54 @@ inline unsigned ew_grid(int64_t n) {
 
 }  // namespace
 
+namespace {
+// eight elements per thread and iteration (n % 8 == 0, 16-byte aligned pointers)
+template <typename T>
+__global__ void relu_gate8_kernel(T* __restrict__ dy, const T* __restrict__ y, int64_t n8, float scale) {
+  pdl_trigger();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    float g[8], v[8];
+    ld8(dy + i * 8, g);
+    ld8(y + i * 8, v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) g[e] = v[e] > 0.f ? g[e] * scale : 0.f;
+    st8(dy + i * 8, g);
+  }
+}
+// one thread sums eight columns of a (q, :) row group over its G rows (d % 8 == 0, 16-byte aligned input)
+template <typename T>
+__global__ void group_sum8_kernel(const T* __restrict__ in, float* __restrict__ out, int64_t Qrows, int G, int d) {
+  pdl_trigger();
+  pdl_wait();
+  const int d8 = d >> 3;
+  const int64_t total = Qrows * d8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t q = i / d8;
+    const int c = (int)(i - q * d8) * 8;
+    const T* p = in + q * G * d + c;
+    float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int g = 0; g < G; ++g) {
+      float v[8];
+      ld8(p + (int64_t)g * d, v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s[e] += v[e];
+    }
+    float* o = out + q * d + c;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[e] += s[e];
+  }
+}
+}  // namespace
+
 int relu_gate(void* dy, const void* y, int64_t n, int dtype, cudaStream_t st, float scale) {
   ProfScope ps("relu_gate", st);
+  if (n % 8 == 0 && (((uintptr_t)dy | (uintptr_t)y) & 15) == 0) {
+    if (dtype == BIST_BF16) BIST_LAUNCH(relu_gate8_kernel<__nv_bfloat16>, ew_grid(n / 8), 256, 0, st, (__nv_bfloat16*)dy, (const __nv_bfloat16*)y, n / 8, scale);
+    else BIST_LAUNCH(relu_gate8_kernel<float>, ew_grid(n / 8), 256, 0, st, (float*)dy, (const float*)y, n / 8, scale);
+    BIST_LAUNCHED();
+    return 0;
+  }
   if (dtype == BIST_BF16) BIST_LAUNCH(relu_gate_kernel<__nv_bfloat16>, ew_grid(n), 256, 0, st, (__nv_bfloat16*)dy, (const __nv_bfloat16*)y, n, scale);
   else BIST_LAUNCH(relu_gate_kernel<float>, ew_grid(n), 256, 0, st, (float*)dy, (const float*)y, n, scale);
   BIST_LAUNCHED();
@@ -923,6 +969,12 @@ int dropout_mask(float* out, int64_t n, const DropCfg& drop, cudaStream_t st) {
 
 int group_sum(const void* in, float* out, int64_t Qrows, int64_t G, int64_t d, int in_dtype, cudaStream_t st) {
   ProfScope ps("group_sum", st);
+  if (d % 8 == 0 && ((uintptr_t)in & 15) == 0) {
+    if (in_dtype == BIST_BF16) BIST_LAUNCH(group_sum8_kernel<__nv_bfloat16>, ew_grid(Qrows * d / 8), 256, 0, st, (const __nv_bfloat16*)in, out, Qrows, (int)G, (int)d);
+    else BIST_LAUNCH(group_sum8_kernel<float>, ew_grid(Qrows * d / 8), 256, 0, st, (const float*)in, out, Qrows, (int)G, (int)d);
+    BIST_LAUNCHED();
+    return 0;
+  }
   if (in_dtype == BIST_BF16) BIST_LAUNCH(group_sum_kernel<__nv_bfloat16>, ew_grid(Qrows * d), 256, 0, st, (const __nv_bfloat16*)in, out, Qrows, (int)G, (int)d);
   else BIST_LAUNCH(group_sum_kernel<float>, ew_grid(Qrows * d), 256, 0, st, (const float*)in, out, Qrows, (int)G, (int)d);
   BIST_LAUNCHED();
