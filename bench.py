@@ -210,7 +210,8 @@ def kernel_model(c, e_act, nd=2):
         "wgrad_vidproj": (2.0 * N * D * d, N * D * e_act + N * d * e_act + d * D * 4),
         "xv_gemm": (L * 2.0 * N * d * nd * d, L * (N * d * e_act + nd * d * d * e_act + N * nd * d * e_act)),
         "wgrad_xv": (L * 2.0 * N * d * nd * d, L * (N * d * e_act + N * nd * d * e_act + nd * d * d * 4)),
-        "bwd_xv_gemm": (L * nd * 2.0 * N * d * d, L * nd * (N * d * e_act + d * d * e_act + N * d * 4)),
+        # one K-concatenated launch per block: both directions' value gradients and weights read once, d_vft (fp32) read and written once
+        "bwd_xv_gemm": (L * nd * 2.0 * N * d * d, L * (nd * (N * d * e_act + d * d * e_act) + 2 * N * d * 4)),
         "stage2_mma": (L * 4.0 * c1 * h, L * (c1 * e_act + 2 * nd * Q * h * d * e_act)),
     }
 
